@@ -1,0 +1,346 @@
+/*
+ * vgpu.h — C ABI of the B200 (sm_100a) filter-and-aggregate engine.
+ *
+ * This is the drop-in boundary: everything the reference's operators would bind through FFI to
+ * run FilterProject -> HashAggregation on the GPU.  Plain pointers and sizes only; no C++ or
+ * torch types.  Every call returns a vgpu_status (0 = OK); the message of the last failure on the
+ * calling thread is available from vgpu_last_error().  No exception crosses this boundary — the
+ * C++ operators (velox-1_b200/host) translate a non-zero status into VELOX_USER_FAIL / VELOX_FAIL
+ * the way velox/common/base/Exceptions.h does for the CPU operators.
+ *
+ * Reference interfaces each group of entry points replaces (paths under the reference tree):
+ *   vgpu_column            <- velox/vector/DecodedVector.h:76-140 (base values + indices + nulls)
+ *   vgpu_op / vgpu_program <- velox/expression/Expr.h (ExprSet, compiled Expr tree),
+ *                             velox/expression/ExprCompiler.cpp:302-335
+ *   vgpu_filter_project    <- velox/exec/FilterProject.cpp:125-191 (getOutput/filter/project),
+ *                             velox/exec/OperatorUtils.cpp:177-255 (processFilterResults)
+ *   vgpu_agg_*             <- velox/exec/HashAggregation.cpp:235-274,388-464,
+ *                             velox/exec/GroupingSet.cpp:177-307,513-559,644-712,
+ *                             velox/exec/HashTable.cpp:426-562, velox/exec/VectorHasher.cpp:68-332,
+ *                             velox/functions/lib/aggregates/{SumAggregateBase,AverageAggregateBase}.h,
+ *                             velox/functions/prestosql/aggregates/{Count,MinMax}Aggregate*.cpp
+ *   vgpu_agg_partition / vgpu_agg_merge_rows / vgpu_comm_*
+ *                          <- velox/exec/HashPartitionFunction.cpp:59-92 + PartitionedOutput/Exchange
+ *                             (partial -> repartition by key -> final,
+ *                             velox/exec/tests/MultiFragmentTest.cpp:180-212)
+ *   vgpu_tpch_lineitem     <- velox/tpch/gen/TpchGen.cpp:401-489 (genTpchLineItem),
+ *                             velox/connectors/tpch/TpchConnector.cpp:139-163
+ *
+ * Bitmaps follow velox/common/base/Nulls.h:26-35: uint64 little-endian words, bit i of a nulls
+ * bitmap is 1 when row i is NOT null; a NULL bitmap pointer means "no nulls".
+ * All device pointers must be valid on the device the call runs on (the current CUDA device);
+ * `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ */
+#ifndef VGPU_H_
+#define VGPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VGPU_ABI_VERSION 1
+
+typedef enum {
+  VGPU_OK = 0,
+  VGPU_ERR_INVALID = 1,     /* bad argument / malformed program (VELOX_CHECK analogue)          */
+  VGPU_ERR_CUDA = 2,        /* CUDA runtime failure                                             */
+  VGPU_ERR_USER = 3,        /* data error raised by a kernel: integer overflow, division by zero,
+                               cast out of range (VeloxUserError analogue)                      */
+  VGPU_ERR_UNSUPPORTED = 4, /* valid Velox plan shape this build does not cover                 */
+  VGPU_ERR_NCCL = 5
+} vgpu_status;
+
+/* Device value types.  Numbering of the first seven follows velox/type/Type.h:62-84 (TypeKind).
+ * DATE is INTEGER (days since epoch).  VARCHAR never reaches the device as bytes: the host maps
+ * strings to int32 value ids (VectorHasher::makeValueIds analogue) and keeps the dictionary. */
+typedef enum {
+  VGPU_BOOLEAN = 0, /* bit-packed, 1 bit per row */
+  VGPU_TINYINT = 1,
+  VGPU_SMALLINT = 2,
+  VGPU_INTEGER = 3,
+  VGPU_BIGINT = 4,
+  VGPU_REAL = 5,
+  VGPU_DOUBLE = 6
+} vgpu_type;
+
+typedef enum { VGPU_FLAT = 0, VGPU_DICTIONARY = 1, VGPU_CONSTANT = 2 } vgpu_encoding;
+
+typedef union {
+  int64_t i;
+  double d;
+} vgpu_scalar;
+
+/* One input column as the kernels see it (the DecodedVector triple). */
+typedef struct {
+  int32_t type;               /* vgpu_type of the (base) values                                   */
+  int32_t encoding;           /* vgpu_encoding                                                    */
+  const void* values;         /* FLAT: `nrows` values.  DICTIONARY: `base_length` base values.     */
+  const int32_t* indices;     /* DICTIONARY: `nrows` indices into values; else NULL               */
+  const uint64_t* nulls;      /* per OUTER row; NULL = none                                       */
+  const uint64_t* base_nulls; /* DICTIONARY: per base value; NULL = none                          */
+  int64_t base_length;        /* DICTIONARY only                                                  */
+  vgpu_scalar constant;       /* CONSTANT only                                                    */
+  int32_t constant_is_null;   /* CONSTANT only                                                    */
+  int32_t reserved;
+} vgpu_column;
+
+/* ---- expression programs ------------------------------------------------------------------ */
+
+/* Operand kinds of an op. */
+typedef enum {
+  VGPU_OPND_NONE = 0,
+  VGPU_OPND_ACC = 1,  /* result of the previous value op (kept in registers)                   */
+  VGPU_OPND_SLOT = 2, /* scratch value slot `index` (shared memory)                            */
+  VGPU_OPND_COL = 3,  /* input column `index`                                                  */
+  VGPU_OPND_IMM = 4,  /* the op's immediate (typed like the op); never null                    */
+  VGPU_OPND_NULL = 5  /* typed NULL constant                                                   */
+} vgpu_operand_kind;
+
+typedef struct {
+  uint8_t kind;  /* vgpu_operand_kind */
+  uint8_t type;  /* vgpu_type of the value read through this operand                            */
+  uint16_t index;
+} vgpu_operand;
+
+/* Opcodes.  Semantics cite the reference function each one restates.
+ * "default null": result is NULL when any argument is NULL (velox/expression/Expr.cpp:371-441). */
+typedef enum {
+  VGPU_OP_NOP = 0,
+  /* arithmetic, default null.  DOUBLE/REAL: IEEE (velox/functions/prestosql/Arithmetic.h:45-86);
+   * integers: checked, raising VGPU_ERR_USER on overflow or division by zero
+   * (velox/functions/prestosql/registration/CheckedArithmeticRegistration.cpp:23-27,
+   *  velox/common/base/CheckedArithmetic.h). */
+  VGPU_OP_ADD = 1,
+  VGPU_OP_SUB = 2,
+  VGPU_OP_MUL = 3,
+  VGPU_OP_DIV = 4,
+  VGPU_OP_NEG = 5,
+  VGPU_OP_MOD = 6,
+  /* cast a -> op.type, default null; FP->integer rounds half away from zero and range-checks,
+   * NaN raises (velox/type/Conversions.h:176-302); integer->FP is static_cast (:304-374);
+   * integer narrowing range-checks. */
+  VGPU_OP_CAST = 8,
+  /* move a value operand into ACC (and optionally a slot) — FieldReference / ConstantExpr. */
+  VGPU_OP_MOV = 9,
+  /* comparisons a ? b on op.type, default null, boolean result
+   * (velox/functions/prestosql/Comparisons.h:43-80; NaN compares false except NE). */
+  VGPU_OP_EQ = 16,
+  VGPU_OP_NE = 17,
+  VGPU_OP_LT = 18,
+  VGPU_OP_LE = 19,
+  VGPU_OP_GT = 20,
+  VGPU_OP_GE = 21,
+  /* a BETWEEN b AND c, inclusive, default null (Comparisons.h:175-185). */
+  VGPU_OP_BETWEEN = 22,
+  /* boolean special forms with SQL three-valued logic; an error or NULL in one conjunct is
+   * dropped when another conjunct decides the row (velox/expression/ConjunctExpr.cpp:24-174). */
+  VGPU_OP_AND = 24,
+  VGPU_OP_OR = 25,
+  VGPU_OP_NOT = 26,     /* default null (velox/functions/prestosql/Not.cpp)                    */
+  VGPU_OP_IS_NULL = 27, /* never null (velox/functions/lib/IsNull.cpp)                          */
+  /* a IN (set of up to 8 immediates packed in the following VGPU_OP_NOP ops' imm fields) is
+   * compiled by the host into OR of EQ; not a device opcode. */
+  VGPU_OP_MAX_ = 32
+} vgpu_opcode;
+
+/* One instruction.  The result always lands in ACC; when dst_slot >= 0 it is also stored to that
+ * scratch slot.  Boolean results live in the boolean ACC / boolean slots (separate numbering). */
+typedef struct {
+  uint8_t opcode;   /* vgpu_opcode */
+  uint8_t type;     /* operand type the op computes in (result type for CAST / MOV)            */
+  int16_t dst_slot; /* -1 = ACC only                                                            */
+  vgpu_operand a, b, c;
+  vgpu_scalar imm;  /* value read by VGPU_OPND_IMM operands of this op                          */
+  vgpu_scalar imm2; /* second immediate (BETWEEN upper bound when c is IMM)                     */
+} vgpu_op;
+
+/* A compiled pipeline program: ops, an optional filter and the output list.
+ *   filter : boolean operand (ACC/SLOT/COL) or kind NONE.  A row passes when the filter is TRUE
+ *            and not NULL (velox/exec/OperatorUtils.cpp:187-210).
+ *   outputs: value operands evaluated for passing rows — the projections of FilterProject, or the
+ *            grouping keys followed by aggregate inputs when the program feeds an aggregation. */
+typedef struct {
+  const vgpu_op* ops;
+  int32_t n_ops;
+  vgpu_operand filter;
+  const vgpu_operand* outputs;
+  int32_t n_outputs;
+  int32_t n_columns; /* number of input columns the program refers to (for validation)          */
+} vgpu_program_desc;
+
+typedef struct vgpu_program_s* vgpu_program_t;
+
+/* ---- library / device -------------------------------------------------------------------- */
+
+int vgpu_abi_version(void);
+/* Copies the calling thread's last error message (NUL-terminated, truncated to cap). */
+int vgpu_last_error(char* buf, size_t cap);
+/* Selects `device` for the calling thread and checks it is an sm_100 part. */
+int vgpu_init(int device);
+int vgpu_device_count(int* count);
+int vgpu_shutdown(void);
+
+/* Device / pinned-host memory and copies (the operators' pool()->allocate analogue). */
+int vgpu_alloc(size_t bytes, void** dptr);
+int vgpu_free(void* dptr);
+int vgpu_alloc_host(size_t bytes, void** hptr); /* pinned */
+int vgpu_free_host(void* hptr);
+int vgpu_h2d_async(void* dst, const void* src, size_t bytes, void* stream);
+int vgpu_d2h_async(void* dst, const void* src, size_t bytes, void* stream);
+int vgpu_memset_async(void* dst, int value, size_t bytes, void* stream);
+int vgpu_stream_create(void** stream);
+int vgpu_stream_destroy(void* stream);
+int vgpu_stream_sync(void* stream);
+
+/* ---- FilterProject ----------------------------------------------------------------------- */
+
+/* Validates and uploads a program (ExprSet construction; velox/exec/FilterProject.cpp:59-103). */
+int vgpu_program_create(const vgpu_program_desc* desc, vgpu_program_t* out);
+int vgpu_program_destroy(vgpu_program_t program);
+
+/* One projected output column, written at the ORIGINAL row positions (rows that do not pass the
+ * filter are left undefined) — Velox wraps the full-length result in a dictionary over
+ * selectedIndices (velox/exec/Operator.cpp:195-228), so no value compaction is needed. */
+typedef struct {
+  void* values;    /* device, nrows values of the output operand's type (BOOLEAN: bit-packed)   */
+  uint64_t* nulls; /* device bitmap, may be NULL when the caller knows the result has no nulls  */
+} vgpu_out_column;
+
+/* Evaluates the program over `nrows` rows.
+ *   in_rows/n_in_rows : optional ascending input selection (the SelectivityVector of the batch as
+ *                       an index list); NULL = all rows [0, nrows).
+ *   sel_bits          : out, device bitmap of nrows bits — selectedBits of FilterEvalCtx.
+ *   sel_idx           : out, device int32[>= nrows] ascending passing row numbers, may be NULL.
+ *   num_selected      : out, device int64.
+ *   outs              : n_outputs entries (may be NULL when the program has no outputs).
+ * Asynchronous on `stream`; data errors are latched and reported by vgpu_check_errors(). */
+int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t ncols,
+                        int64_t nrows, const int32_t* in_rows, int64_t n_in_rows,
+                        uint64_t* sel_bits, int32_t* sel_idx, int64_t* num_selected,
+                        const vgpu_out_column* outs, void* stream);
+
+/* Synchronises `stream` and returns VGPU_ERR_USER (with the Velox-style message) when a kernel
+ * launched through this library latched a data error since the last check. */
+int vgpu_check_errors(void* stream);
+
+/* ---- HashAggregation ---------------------------------------------------------------------- */
+
+/* Device accumulator kinds.  Raw-input and intermediate-input steps of every Presto aggregate on
+ * the path decompose into these (AVG raw = SUM_F64 + COUNT; AVG/COUNT final = SUM_F64 + SUM_I64
+ * over the intermediate columns; velox/functions/lib/aggregates/AverageAggregateBase.h:65-390,
+ * velox/functions/prestosql/aggregates/CountAggregate.cpp:81-90). */
+typedef enum {
+  VGPU_ACC_SUM_F64 = 0,  /* double += (double)x, nulls ignored                                  */
+  VGPU_ACC_SUM_I64 = 1,  /* checked int64 += x (SumAggregateBase.h:150-158)                     */
+  VGPU_ACC_COUNT = 2,    /* += 1 per passing row whose input is not null; input NONE = count(*) */
+  VGPU_ACC_MIN = 3,      /* typed by the input operand (integers or double)                     */
+  VGPU_ACC_MAX = 4
+} vgpu_acc_kind;
+
+typedef struct {
+  int32_t kind;  /* vgpu_acc_kind */
+  int32_t input; /* index into the program's outputs, or -1 (count(*))                          */
+} vgpu_acc_spec;
+
+/* How one grouping key becomes bits of the 64-bit normalized key
+ * (VectorHasher value ids / kNormalizedKey, velox/exec/VectorHasher.h:118-578,
+ *  velox/exec/HashTable.cpp:1376-1461).  id = value - min + 1, 0 = NULL; `bits` wide. */
+typedef struct {
+  int32_t output; /* index into the program's outputs                                          */
+  int32_t bits;   /* width of the id field; 64 = use the raw value (single BIGINT key)          */
+  int64_t min;    /* subtracted before packing (range mode)                                    */
+  int64_t max;    /* values outside [min,max] latch "key out of range" for a host redo         */
+} vgpu_key_spec;
+
+typedef enum {
+  VGPU_AGG_GLOBAL = 0, /* no keys: one group, present even with no input                       */
+  VGPU_AGG_ARRAY = 1,  /* product of key cardinalities small: per-thread shared-memory partial
+                          tables, merged per block (kArray analogue)                           */
+  VGPU_AGG_HASH = 2    /* open-addressing table in HBM keyed by the normalized key             */
+} vgpu_agg_mode;
+
+typedef struct {
+  int32_t mode; /* vgpu_agg_mode */
+  int32_t n_keys;
+  const vgpu_key_spec* keys;
+  int32_t n_accs;
+  const vgpu_acc_spec* accs;
+  int32_t ignore_null_keys;   /* drop rows with a NULL key (velox/exec/OperatorUtils.cpp:141-157) */
+  int32_t reserved;
+  int64_t expected_groups;    /* HASH: initial capacity hint (0 = default)                       */
+} vgpu_agg_desc;
+
+typedef struct vgpu_agg_s* vgpu_agg_t;
+
+int vgpu_agg_create(const vgpu_agg_desc* desc, vgpu_agg_t* out);
+int vgpu_agg_destroy(vgpu_agg_t agg);
+/* Drops all groups, keeps the configuration (partial-aggregation flush). */
+int vgpu_agg_reset(vgpu_agg_t agg, void* stream);
+
+/* Fused filter -> project -> accumulate over one batch: evaluates `program` (filter + outputs)
+ * and folds passing rows into the groups (GroupingSet::addInput).  Never materialises the
+ * selection or the projections. */
+int vgpu_agg_add_input(vgpu_agg_t agg, vgpu_program_t program, const vgpu_column* cols,
+                       int32_t ncols, int64_t nrows, const int32_t* in_rows, int64_t n_in_rows,
+                       void* stream);
+
+/* Number of groups so far (synchronises the stream). */
+int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* num_groups);
+
+/* Row width of vgpu_agg_extract output: 8 bytes normalized key, then 8 bytes per accumulator
+ * (SUM_F64 as double; everything else int64, MIN/MAX of doubles as double), then 8 bytes per
+ * accumulator of "non-null input count" — a group's SUM/MIN/MAX is NULL when that count is 0
+ * (velox/exec/Aggregate.h:305-337). */
+int vgpu_agg_row_bytes(vgpu_agg_t agg, int32_t* bytes);
+
+/* Writes up to max_groups packed group rows into device memory `rows`, starting at group number
+ * `offset` of an arbitrary but stable enumeration; *n_written (host) receives the count.
+ * Synchronises the stream.  (GroupingSet::getOutput / RowContainer::listRows.) */
+int vgpu_agg_extract(vgpu_agg_t agg, int64_t offset, int64_t max_groups, void* rows,
+                     int64_t* n_written, void* stream);
+
+/* Folds packed group rows (same layout, e.g. received from another GPU) into the groups:
+ * sums and counts add, MIN/MAX combine (Aggregate::addIntermediateResults). */
+int vgpu_agg_merge_rows(vgpu_agg_t agg, const void* rows, int64_t n_rows, void* stream);
+
+/* Hash-partitions the current groups into n_parts contiguous segments of packed rows:
+ * part = mix64(normalized key) % n_parts.  rows_out must hold num_groups rows; counts_out is a
+ * HOST array of n_parts int64 (segment lengths, in order).  Synchronises the stream. */
+int vgpu_agg_partition(vgpu_agg_t agg, int32_t n_parts, void* rows_out, int64_t* counts_out,
+                       void* stream);
+
+/* ---- multi-GPU exchange (one process per GPU) ------------------------------------------- */
+
+#define VGPU_COMM_ID_BYTES 128
+typedef struct vgpu_comm_s* vgpu_comm_t;
+int vgpu_comm_unique_id(uint8_t id[VGPU_COMM_ID_BYTES]); /* rank 0; broadcast out of band */
+int vgpu_comm_create(const uint8_t id[VGPU_COMM_ID_BYTES], int32_t rank, int32_t world,
+                     vgpu_comm_t* out);
+int vgpu_comm_destroy(vgpu_comm_t comm);
+/* Variable-size all-to-all of bytes between device buffers over NCCL (grouped send/recv).
+ * send_counts/recv_counts/send_offsets/recv_offsets: HOST arrays of `world` byte counts. */
+int vgpu_comm_alltoallv(vgpu_comm_t comm, const void* send, const int64_t* send_counts,
+                        const int64_t* send_offsets, void* recv, const int64_t* recv_counts,
+                        const int64_t* recv_offsets, void* stream);
+/* All-gather of `bytes` per rank between device buffers (used for segment counts). */
+int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t bytes,
+                        void* stream);
+
+/* ---- statistics -------------------------------------------------------------------------- */
+
+typedef struct {
+  int64_t kernel_launches; /* kernels launched by this library on the calling thread's device   */
+  int64_t rows_in;
+  int64_t bytes_h2d;
+  int64_t bytes_d2h;
+} vgpu_stats;
+int vgpu_get_stats(vgpu_stats* out);
+int vgpu_reset_stats(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VGPU_H_ */

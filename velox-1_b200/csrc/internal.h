@@ -1,0 +1,162 @@
+// Internal declarations shared by the CUDA translation units of libvgpu.so.
+// Nothing here is part of the ABI (include/vgpu.h is).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "vgpu.h"
+
+namespace vg {
+
+// ---- tile geometry of the pipeline kernel ---------------------------------------------------
+// One CTA of 256 threads walks tiles of 1024 rows; a thread owns 2 pairs of adjacent rows
+// (warp-contiguous pair layout, see pipeline.cu) so every staged 8-byte column is read with
+// conflict-free 128-bit shared loads.
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kRowsPerThread = 4;
+constexpr int kTile = kThreads * kRowsPerThread; // 1024 rows
+constexpr int kMaxStages = 4;
+
+constexpr int kMaxOps = 48;
+constexpr int kMaxCols = 16;
+constexpr int kMaxOutputs = 24;
+constexpr int kMaxKeys = 8;
+constexpr int kMaxCells = 40;
+constexpr int kMaxSlots = 12;
+
+// Error bits latched by kernels into a device word (vgpu_check_errors reports them).
+enum : uint32_t {
+  kErrOverflow = 1u,     // "integer overflow" (checked arithmetic / checked sum)
+  kErrDivZero = 2u,      // "division by zero"
+  kErrCastRange = 4u,    // cast out of range / NaN to integer
+  kErrKeyRange = 8u,     // grouping key outside the declared [min,max] or unexpected NULL
+  kErrTableFull = 16u    // HBM hash table could not place a key (internal; host grows + retries)
+};
+
+struct DevCol {
+  const void* values;
+  const int32_t* indices;
+  const uint64_t* nulls;
+  const uint64_t* base_nulls;
+  int64_t constant;
+  int32_t stage_off; // byte offset of the staged values (FLAT) / indices (DICTIONARY) tile; -1 none
+  int32_t nulls_off; // byte offset of the staged outer-nulls tile (128 B); -1 none
+  uint8_t type;
+  uint8_t encoding;
+  uint8_t const_null;
+  uint8_t elem_log2; // log2 bytes of a staged element (BOOLEAN flat: bits, marked 255)
+  uint8_t bulk_ok;   // staged tile may be fetched with cp.async.bulk (16 B aligned, flat walk)
+  uint8_t pad[3];
+};
+
+// Cell = one 8-byte lane of group state.  An accumulator maps to a value cell and (for
+// SUM/MIN/MAX) a "non-null input count" cell; count cells of the same input are shared.
+enum CellKind : uint8_t {
+  kCellSumF64 = 0,
+  kCellSumI64 = 1,
+  kCellCount = 2, // counts rows whose `input` is not null (input < 0: all passing rows)
+  kCellMinI64 = 3,
+  kCellMaxI64 = 4,
+  kCellMinF64 = 5,
+  kCellMaxF64 = 6
+};
+
+struct DevCell {
+  uint8_t kind;
+  int8_t input;     // program output index feeding the cell, -1 = none (count(*))
+  uint8_t skip;     // launch-time: input cannot be NULL => count cell aliases the rows cell
+  uint8_t alias;    // cell whose value this one copies at merge time when skip != 0
+  int32_t smem_off; // ARRAY mode: byte offset of this cell's block inside the partial tables
+};
+
+struct DevKey {
+  int64_t min;
+  int64_t max;
+  int64_t mult;  // ARRAY mode: multiplier of this key's id inside the group number
+  int8_t output; // program output index
+  uint8_t bits;  // HASH mode: width of the id field (64 = raw value)
+  uint8_t shift; // HASH mode: bit position of the id field
+  uint8_t nullable;
+  uint8_t pad[4];
+};
+
+enum SinkMode : int32_t { kSinkFilterProject = 0, kSinkArray = 1, kSinkHash = 2 };
+
+struct DevOut {
+  void* values;
+  uint64_t* nulls;
+};
+
+struct PipelineParams {
+  // program
+  vgpu_op ops[kMaxOps];
+  vgpu_operand outputs[kMaxOutputs];
+  vgpu_operand filter;
+  int32_t n_ops, n_outputs, n_cols, n_slots, n_bslots;
+  DevCol cols[kMaxCols];
+  // rows
+  int64_t n_rows;         // rows to walk (n_in_rows when in_rows != nullptr)
+  const int32_t* in_rows; // optional indirection
+  int32_t n_stages, stage_bytes;
+  int32_t smem_slots_off, smem_meta_off, smem_bmeta_off, smem_tab_off;
+  uint32_t* err_word;
+  // sink
+  int32_t mode;
+  int32_t n_keys, n_cells, n_groups; // ARRAY: n_groups = product of key cardinalities
+  int32_t ignore_null_keys;
+  int32_t warp_private; // ARRAY: 1 = one table per warp (match.any leaders), 0 = one per thread
+  int32_t warp_tab_bytes; // ARRAY, warp_private: bytes of one warp's table
+  int32_t tab_bytes;      // ARRAY: bytes of all partial tables of the CTA
+  DevKey keys[kMaxKeys];
+  DevCell cells[kMaxCells];
+  // ARRAY sink: per-block partials [gridDim][n_cells][n_groups] of 8-byte values
+  uint64_t* partials;
+  // HASH sink
+  uint64_t* table; // (capacity + 2) rows of row_words 8-byte words: key, cells...
+  uint64_t cap_mask;
+  int32_t row_words;
+  int32_t raw_key; // single 64-bit raw key
+  unsigned long long* n_groups_ctr;
+  // FILTER_PROJECT sink
+  uint32_t* sel_words;
+  int32_t* tile_counts;
+  unsigned long long* num_selected;
+  DevOut outs[kMaxOutputs];
+};
+
+// ---- host-side objects behind the opaque ABI handles ---------------------------------------
+struct Program {
+  std::vector<vgpu_op> ops;
+  std::vector<vgpu_operand> outputs;
+  vgpu_operand filter;
+  int n_cols = 0, n_slots = 0, n_bslots = 0;
+};
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+#define VG_CUDA(x)                                   \
+  do {                                               \
+    cudaError_t e_ = (x);                            \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #x); \
+  } while (0)
+
+uint32_t* device_err_word();  // per-device latched error bits
+void count_launch(int n = 1);
+int num_sms();
+
+// Fills the program/column part of PipelineParams and the shared-memory plan.  Returns status.
+int plan_pipeline(const Program& prog, const vgpu_column* cols, int32_t ncols, int64_t nrows,
+                  const int32_t* in_rows, int64_t n_in_rows, PipelineParams& p);
+// Launches the pipeline kernel for p.mode; `tab_bytes` = shared memory wanted by the sink.
+int launch_pipeline(PipelineParams& p, int tab_bytes, int grid, cudaStream_t stream);
+int pipeline_grid(int64_t n_rows);
+// Whether program output `idx` can be NULL given the columns bound in `p`.
+bool output_nullable(const PipelineParams& p, int idx);
+int launch_selection_indices(const uint32_t* words, int32_t* tile_counts, int64_t* tile_offsets,
+                             int64_t n_rows, int32_t* sel_idx, unsigned long long* total,
+                             cudaStream_t stream);
+
+} // namespace vg
