@@ -1,0 +1,630 @@
+// Group state that outlives one pipeline launch: the dense ARRAY/GLOBAL state, the HBM hash
+// table (init / rehash), extraction of packed group rows, merging packed rows
+// (Aggregate::addIntermediateResults) and hash partitioning for the multi-GPU exchange.
+//
+// Reference behaviour restated (paths under the reference tree):
+//   velox/exec/GroupingSet.cpp:644-712 (getOutput/extractGroups), velox/exec/RowContainer.cpp
+//   (listRows), velox/exec/HashTable.cpp:684-747 (checkSize/rehash),
+//   velox/exec/HashPartitionFunction.cpp:59-92 (partition = hash % numPartitions).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <algorithm>
+
+#include "agg.h"
+#include "device_common.cuh"
+
+namespace vg {
+
+// ---- ARRAY / GLOBAL ---------------------------------------------------------------------------
+struct CellMeta {
+  uint8_t kind[kMaxCells];
+  uint8_t skip[kMaxCells];
+  uint8_t alias[kMaxCells];
+  int32_t n_cells;
+};
+
+__global__ void init_state_kernel(uint64_t* state, CellMeta m, int G) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m.n_cells * G) return;
+  state[i] = cell_identity(m.kind[i / G]);
+}
+
+// state[c][g] = fold(state[c][g], partials[0][c][g], partials[1][c][g], ...) in block order.
+__global__ void merge_partials_kernel(uint64_t* state, const uint64_t* partials, int n_blocks,
+                                      CellMeta m, int G, uint32_t* err_word) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m.n_cells * G) return;
+  const int c = i / G, g = i - c * G;
+  const int src = m.skip[c] ? m.alias[c] : c;
+  const uint8_t kind = m.kind[c];
+  uint32_t err = 0;
+  uint64_t acc = cell_identity(kind);
+  const size_t stride = (size_t)m.n_cells * G;
+  for (int b = 0; b < n_blocks; ++b) acc = fold2(kind, acc, partials[b * stride + (size_t)src * G + g], err);
+  state[i] = fold2(kind, state[i], acc, err);
+  if (err) atomicOr(err_word, err);
+}
+
+// Packed group row (the ABI layout): key, flags, rows, value per accumulator, non-null count per
+// accumulator.
+__device__ __forceinline__ void write_packed(uint64_t* out, uint64_t key, uint64_t flags, uint64_t rows,
+                                             const RowMap& rm, const uint64_t* cells, size_t cell_stride,
+                                             bool ordered_f64) {
+  out[0] = key;
+  out[1] = flags;
+  out[2] = rows;
+  for (int a = 0; a < rm.n_accs; ++a) {
+    uint64_t v = cells[(size_t)rm.value_cell[a] * cell_stride];
+    const uint8_t k = rm.value_kind[a];
+    if (ordered_f64 && (k == kCellMinF64 || k == kCellMaxF64)) v = (uint64_t)f64_ordered(v); // involution
+    out[3 + a] = v;
+    out[3 + rm.n_accs + a] = rm.nn_cell[a] >= 0 ? cells[(size_t)rm.nn_cell[a] * cell_stride] : rows;
+  }
+}
+
+__global__ void extract_array_kernel(const uint64_t* state, int G, RowMap rm, int always,
+                                     uint64_t* rows_out, unsigned long long* counter) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  const uint64_t rows = state[(size_t)rm.rows_cell * G + g];
+  if (rows == 0 && !always) return;
+  const unsigned long long pos = atomicAdd(counter, 1ull);
+  write_packed(rows_out + pos * rm.row_words_out, (uint64_t)g, 0, rows, rm, state + g, (size_t)G, false);
+}
+
+// ---- HASH -------------------------------------------------------------------------------------
+__global__ void init_table_kernel(uint64_t* table, uint64_t n_slots, int row_words, CellMeta m) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t total = n_slots * row_words;
+  for (uint64_t k = i; k < total; k += (uint64_t)gridDim.x * blockDim.x) {
+    const int w = (int)(k % row_words);
+    uint64_t v = kEmptyKey;
+    if (w > 0) {
+      v = cell_identity(m.kind[w - 1]);
+      if (m.kind[w - 1] == kCellMinF64 || m.kind[w - 1] == kCellMaxF64) v = (uint64_t)f64_ordered(v);
+    }
+    table[k] = v;
+  }
+}
+
+// Moves every occupied row of `from` into `to` (keys are unique, so plain stores after the claim).
+__global__ void rehash_kernel(const uint64_t* from, uint64_t from_slots, HashRef to, uint32_t* err_word) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= from_slots) return;
+  const uint64_t* src = from + i * to.row_words;
+  if (src[0] == kEmptyKey) return;
+  const bool special = i >= from_slots - 2;
+  uint32_t err = 0;
+  int64_t slot;
+  if (special) {
+    slot = (int64_t)to.cap_mask + 1 + (int64_t)(i - (from_slots - 2));
+    to.table[slot * to.row_words] = 0;
+    atomicAdd(to.n_groups_ctr, 1ull);
+  } else {
+    slot = hash_find_or_insert(to, src[0], false, err);
+  }
+  if (slot < 0) { atomicOr(err_word, err); return; }
+  uint64_t* dst = to.table + slot * to.row_words;
+  for (int w = 1; w < to.row_words; ++w) dst[w] = src[w];
+}
+
+__global__ void extract_hash_kernel(const uint64_t* table, uint64_t n_slots, int row_words, RowMap rm,
+                                    uint64_t* rows_out, unsigned long long* counter) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_slots) return;
+  const uint64_t* src = table + i * row_words;
+  if (src[0] == kEmptyKey) return;
+  const unsigned long long pos = atomicAdd(counter, 1ull);
+  uint64_t key = src[0], flags = 0;
+  if (i == n_slots - 2) { key = 0; flags = 1; }      // NULL key group
+  if (i == n_slots - 1) { key = kEmptyKey; }         // the key that equals the empty marker
+  write_packed(rows_out + pos * rm.row_words_out, key, flags, src[1 + rm.rows_cell], rm, src + 1, 1, true);
+}
+
+// ---- merging packed rows ---------------------------------------------------------------------
+// Global-memory fold with atomics (rows from different producers may hit the same group).
+__device__ __forceinline__ void atomic_fold(uint8_t kind, uint64_t* addr, uint64_t v, bool ordered_f64,
+                                            uint32_t& err) {
+  switch (kind) {
+    case kCellSumF64: atomicAdd(reinterpret_cast<double*>(addr), u2d(v)); break;
+    case kCellSumI64: {
+      const int64_t y = (int64_t)v;
+      const int64_t x = (int64_t)atomicAdd(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)v);
+      const int64_t z = (int64_t)((uint64_t)x + (uint64_t)y);
+      if (((x ^ z) & (y ^ z)) < 0) err |= kErrOverflow;
+      break;
+    }
+    case kCellCount: atomicAdd(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)v); break;
+    case kCellMinI64: atomicMin(reinterpret_cast<long long*>(addr), (long long)v); break;
+    case kCellMaxI64: atomicMax(reinterpret_cast<long long*>(addr), (long long)v); break;
+    default: {
+      if (u2d(v) != u2d(v)) break;
+      if (ordered_f64) {
+        if (kind == kCellMinF64) atomicMin(reinterpret_cast<long long*>(addr), (long long)f64_ordered(v));
+        else atomicMax(reinterpret_cast<long long*>(addr), (long long)f64_ordered(v));
+      } else {
+        unsigned long long* p = reinterpret_cast<unsigned long long*>(addr);
+        unsigned long long cur = *p;
+        while (true) {
+          const bool better = kind == kCellMinF64 ? u2d(v) < u2d(cur) : u2d(cur) < u2d(v);
+          if (!better) break;
+          const unsigned long long seen = atomicCAS(p, cur, (unsigned long long)v);
+          if (seen == cur) break;
+          cur = seen;
+        }
+      }
+    }
+  }
+}
+
+// cells: base of the group's cells, `stride` words apart.
+__device__ __forceinline__ void merge_packed(const uint64_t* row, const RowMap& rm, uint64_t* cells,
+                                             size_t stride, bool ordered_f64, const uint8_t* cell_done,
+                                             uint32_t& err) {
+  atomic_fold(kCellCount, cells + (size_t)rm.rows_cell * stride, row[2], ordered_f64, err);
+  for (int a = 0; a < rm.n_accs; ++a) {
+    const uint8_t k = rm.value_kind[a];
+    const uint64_t nn = row[3 + rm.n_accs + a];
+    if (!cell_done[a * 2]) {
+      // a value whose non-null count is 0 is the identity (or garbage for MIN/MAX): skip it
+      if (k == kCellCount || rm.nn_cell[a] < 0 || nn != 0) {
+        if (rm.value_cell[a] != rm.rows_cell) atomic_fold(k, cells + (size_t)rm.value_cell[a] * stride, row[3 + a], ordered_f64, err);
+      }
+    }
+    if (!cell_done[a * 2 + 1] && rm.nn_cell[a] >= 0 && rm.nn_cell[a] != rm.rows_cell) {
+      atomic_fold(kCellCount, cells + (size_t)rm.nn_cell[a] * stride, nn, ordered_f64, err);
+    }
+  }
+}
+
+struct DoneMap { uint8_t d[2 * kMaxOutputs]; }; // 1 = an earlier accumulator already covers the cell
+
+__global__ void merge_rows_array_kernel(const uint64_t* rows, int64_t n, RowMap rm, DoneMap dm,
+                                        uint64_t* state, int G, uint32_t* err_word) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t* row = rows + i * rm.row_words_out;
+  uint32_t err = 0;
+  if (row[0] >= (uint64_t)G) { atomicOr(err_word, kErrKeyRange); return; }
+  merge_packed(row, rm, state + row[0], (size_t)G, false, dm.d, err);
+  if (err) atomicOr(err_word, err);
+}
+
+__global__ void merge_rows_hash_kernel(const uint64_t* rows, int64_t n, RowMap rm, DoneMap dm, HashRef h,
+                                       uint32_t* err_word) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t* row = rows + i * rm.row_words_out;
+  uint32_t err = 0;
+  const int64_t slot = hash_find_or_insert(h, row[0], (row[1] & 1ull) != 0, err);
+  if (slot >= 0) merge_packed(row, rm, h.table + slot * h.row_words + 1, 1, true, dm.d, err);
+  if (err) atomicOr(err_word, err);
+}
+
+// ---- partitioning packed rows ----------------------------------------------------------------
+__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts) {
+  return (int)(mix64(row[0] ^ (row[1] << 63)) % (uint64_t)n_parts);
+}
+__global__ void partition_count_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
+                                       unsigned long long* counts) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  atomicAdd(&counts[part_of(rows + i * row_words, n_parts)], 1ull);
+}
+__global__ void partition_scatter_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
+                                         unsigned long long* cursors, uint64_t* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t* row = rows + i * row_words;
+  const unsigned long long pos = atomicAdd(&cursors[part_of(row, n_parts)], 1ull);
+  uint64_t* dst = out + pos * row_words;
+  for (int w = 0; w < row_words; ++w) dst[w] = row[w];
+}
+
+// ------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------
+static CellMeta cell_meta(const Agg& a) {
+  CellMeta m{};
+  m.n_cells = a.n_cells;
+  for (int c = 0; c < a.n_cells; ++c) { m.kind[c] = a.cells[c].kind; m.skip[c] = a.cells[c].skip; m.alias[c] = a.cells[c].alias; }
+  return m;
+}
+
+static int find_or_add_cell(Agg& a, uint8_t kind, int input) {
+  for (int c = 0; c < a.n_cells; ++c) if (a.cells[c].kind == kind && a.cells[c].input == input) return c;
+  if (a.n_cells >= kMaxCells) return -1;
+  DevCell& cell = a.cells[a.n_cells];
+  cell = DevCell{};
+  cell.kind = kind; cell.input = (int8_t)input;
+  return a.n_cells++;
+}
+
+// Builds the cell plan from the accumulator list once operand types are known.
+int agg_resolve(Agg& a, const Program& prog) {
+  if (a.resolved) return VGPU_OK;
+  a.n_cells = 0;
+  find_or_add_cell(a, kCellCount, -1); // cell 0: passing rows per group
+  a.rm = RowMap{};
+  a.rm.n_accs = (int)a.accs.size();
+  a.rm.rows_cell = 0;
+  a.rm.row_words_out = 3 + 2 * a.rm.n_accs;
+  for (size_t i = 0; i < a.accs.size(); ++i) {
+    const vgpu_acc_spec& s = a.accs[i];
+    if (s.input >= (int)prog.outputs.size()) { set_error("accumulator %zu reads output %d, program has %zu", i, s.input, prog.outputs.size()); return VGPU_ERR_INVALID; }
+    const int t = s.input >= 0 ? prog.outputs[s.input].type : VGPU_BIGINT;
+    const bool fp = t == VGPU_REAL || t == VGPU_DOUBLE;
+    int kind;
+    switch (s.kind) {
+      case VGPU_ACC_SUM_F64: kind = kCellSumF64; break;
+      case VGPU_ACC_SUM_I64: kind = kCellSumI64; if (fp) { set_error("SUM_I64 over a floating point input"); return VGPU_ERR_INVALID; } break;
+      case VGPU_ACC_COUNT: kind = kCellCount; break;
+      case VGPU_ACC_MIN: kind = fp ? kCellMinF64 : kCellMinI64; break;
+      case VGPU_ACC_MAX: kind = fp ? kCellMaxF64 : kCellMaxI64; break;
+      default: set_error("bad accumulator kind %d", s.kind); return VGPU_ERR_INVALID;
+    }
+    if (s.kind != VGPU_ACC_COUNT && s.input < 0) { set_error("accumulator %zu needs an input", i); return VGPU_ERR_INVALID; }
+    if (s.kind != VGPU_ACC_COUNT && t == VGPU_BOOLEAN) { set_error("boolean aggregate inputs are not supported"); return VGPU_ERR_UNSUPPORTED; }
+    const int vc = find_or_add_cell(a, (uint8_t)kind, s.input);
+    int nc = -1;
+    if (s.kind != VGPU_ACC_COUNT) nc = find_or_add_cell(a, kCellCount, s.input);
+    if (vc < 0 || (s.kind != VGPU_ACC_COUNT && nc < 0)) { set_error("too many accumulator cells (max %d)", kMaxCells); return VGPU_ERR_UNSUPPORTED; }
+    a.rm.value_cell[i] = (int16_t)vc;
+    a.rm.nn_cell[i] = (int16_t)nc;
+    a.rm.value_kind[i] = (uint8_t)kind;
+  }
+  // keys
+  if (a.mode == VGPU_AGG_ARRAY || a.mode == VGPU_AGG_GLOBAL) {
+    int64_t G = 1;
+    for (size_t k = 0; k < a.keys.size(); ++k) {
+      const vgpu_key_spec& ks = a.keys[k];
+      const int64_t card = ks.max - ks.min + 1 + (a.ignore_null_keys ? 0 : 1);
+      if (ks.max < ks.min || card > (1 << 20)) { set_error("ARRAY key %zu: bad domain [%lld, %lld]", k, (long long)ks.min, (long long)ks.max); return VGPU_ERR_INVALID; }
+      a.mults[k] = G;
+      G *= card;
+      if (G > (1 << 20)) { set_error("ARRAY mode supports at most 2^20 groups; use HASH"); return VGPU_ERR_UNSUPPORTED; }
+    }
+    a.n_groups = (int)G;
+    const size_t words = (size_t)a.n_cells * a.n_groups;
+    VG_CUDA(cudaMalloc(&a.state, words * 8));
+    init_state_kernel<<<(int)((words + 255) / 256), 256>>>(a.state, cell_meta(a), a.n_groups);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+  } else {
+    int shift = 0;
+    for (size_t k = 0; k < a.keys.size(); ++k) {
+      const vgpu_key_spec& ks = a.keys[k];
+      if (ks.bits == 64) {
+        if (a.keys.size() != 1) { set_error("a raw 64-bit key must be the only key"); return VGPU_ERR_UNSUPPORTED; }
+        continue;
+      }
+      if (ks.bits < 1 || ks.bits > 63) { set_error("key %zu: bits %d", k, ks.bits); return VGPU_ERR_INVALID; }
+      a.shifts[k] = (uint8_t)shift;
+      shift += ks.bits;
+      if (shift > 63) { set_error("normalized key wider than 63 bits"); return VGPU_ERR_UNSUPPORTED; }
+    }
+    a.row_words = 1 + a.n_cells;
+  }
+  VG_CUDA(cudaMalloc(&a.ctr, 64 * sizeof(unsigned long long)));
+  VG_CUDA(cudaMemset(a.ctr, 0, 64 * sizeof(unsigned long long)));
+  a.resolved = true;
+  return VGPU_OK;
+}
+
+static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
+
+static HashRef href_of(const Agg& a) {
+  HashRef h; h.table = a.table; h.cap_mask = a.capacity - 1; h.row_words = a.row_words; h.n_groups_ctr = a.ctr;
+  return h;
+}
+
+// (Re)allocates the table with `capacity` slots and moves existing groups over.
+static int hash_resize(Agg& a, uint64_t capacity, cudaStream_t stream) {
+  uint64_t* old = a.table;
+  const uint64_t old_slots = a.capacity ? a.capacity + 2 : 0;
+  uint64_t* fresh = nullptr;
+  const uint64_t slots = capacity + 2;
+  VG_CUDA(cudaMalloc(&fresh, slots * a.row_words * 8));
+  const int blocks = std::max(1, std::min(num_sms() * 8, (int)((slots * a.row_words + 255) / 256)));
+  init_table_kernel<<<blocks, 256, 0, stream>>>(fresh, slots, a.row_words, cell_meta(a));
+  VG_CUDA(cudaGetLastError());
+  count_launch();
+  a.table = fresh;
+  a.capacity = capacity;
+  if (old) {
+    VG_CUDA(cudaMemsetAsync(a.ctr, 0, sizeof(unsigned long long), stream));
+    rehash_kernel<<<(unsigned)((old_slots + 255) / 256), 256, 0, stream>>>(old, old_slots, href_of(a), device_err_word());
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+    VG_CUDA(cudaStreamSynchronize(stream));
+    VG_CUDA(cudaFree(old));
+  }
+  return VGPU_OK;
+}
+
+static int read_group_count(Agg& a, cudaStream_t stream, uint64_t* out) {
+  unsigned long long v = 0;
+  VG_CUDA(cudaMemcpyAsync(&v, a.ctr, sizeof(v), cudaMemcpyDeviceToHost, stream));
+  VG_CUDA(cudaStreamSynchronize(stream));
+  *out = v;
+  return VGPU_OK;
+}
+
+static void slice_columns(const vgpu_column* in, int n, int64_t off, vgpu_column* out) {
+  for (int c = 0; c < n; ++c) {
+    out[c] = in[c];
+    if (off == 0 || in[c].encoding == VGPU_CONSTANT) continue;
+    if (in[c].nulls) out[c].nulls = in[c].nulls + (off >> 6);
+    if (in[c].encoding == VGPU_DICTIONARY) { out[c].indices = in[c].indices + off; continue; }
+    int lg;
+    switch (in[c].type) { case VGPU_BOOLEAN: lg = -3; break; case VGPU_TINYINT: lg = 0; break; case VGPU_SMALLINT: lg = 1; break;
+      case VGPU_INTEGER: case VGPU_REAL: lg = 2; break; default: lg = 3; }
+    out[c].values = (const char*)in[c].values + (lg < 0 ? (off >> 3) : (off << lg));
+  }
+}
+
+static int fill_sink(Agg& a, PipelineParams& p) {
+  p.n_keys = (int)a.keys.size();
+  p.ignore_null_keys = a.ignore_null_keys ? 1 : 0;
+  for (int k = 0; k < p.n_keys; ++k) {
+    DevKey& d = p.keys[k];
+    d = DevKey{};
+    d.min = a.keys[k].min; d.max = a.keys[k].max; d.mult = a.mults[k];
+    d.output = (int8_t)a.keys[k].output; d.bits = (uint8_t)a.keys[k].bits; d.shift = a.shifts[k];
+    d.nullable = a.ignore_null_keys ? 0 : 1;
+    if (a.keys[k].output < 0 || a.keys[k].output >= p.n_outputs) { set_error("key %d reads output %d", k, a.keys[k].output); return VGPU_ERR_INVALID; }
+  }
+  p.n_cells = a.n_cells;
+  for (int c = 0; c < a.n_cells; ++c) {
+    DevCell& d = p.cells[c];
+    d = a.cells[c];
+    d.skip = 0; d.alias = 0;
+    // a count cell whose input cannot be NULL counts exactly the passing rows: alias cell 0
+    if (c > 0 && d.kind == kCellCount && (d.input < 0 || !output_nullable(p, d.input))) { d.skip = 1; d.alias = 0; }
+    a.cells[c].skip = d.skip; a.cells[c].alias = d.alias;
+  }
+  return VGPU_OK;
+}
+
+// HASH mode: count cells that have aliased the rows cell so far get their own value before a
+// batch (or a merge) that needs them to diverge.
+__global__ void materialize_alias_kernel(uint64_t* table, uint64_t n_slots, int row_words, int cell) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_slots) return;
+  uint64_t* row = table + i * row_words;
+  if (row[0] != kEmptyKey) row[1 + cell] = row[1];
+}
+
+static int hash_materialize(Agg& a, int cell, cudaStream_t stream) {
+  if (a.table) {
+    const uint64_t slots = a.capacity + 2;
+    materialize_alias_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, stream>>>(a.table, slots, a.row_words, cell);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  a.hash_aliased[cell] = false;
+  return VGPU_OK;
+}
+
+int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t ncols, int64_t nrows,
+                  const int32_t* in_rows, int64_t n_in_rows, cudaStream_t stream) {
+  int rc = agg_resolve(a, prog);
+  if (rc) return rc;
+  a.packed_rows = -1;
+  const int64_t total = in_rows ? n_in_rows : nrows;
+  if (total <= 0) return VGPU_OK;
+  PipelineParams p{};
+  if (a.mode != VGPU_AGG_HASH) {
+    rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
+    if (rc) return rc;
+    p.mode = kSinkArray;
+    rc = fill_sink(a, p);
+    if (rc) return rc;
+    p.n_groups = a.n_groups;
+    // shared-memory plan of the partial tables: one table per thread when it fits next to at
+    // least two stages, else one per warp.
+    auto layout = [&](int copies) {
+      int off = 0;
+      for (int c = 0; c < p.n_cells; ++c) {
+        if (p.cells[c].skip) { p.cells[c].smem_off = 0; continue; }
+        const int w = p.cells[c].kind == kCellCount ? 4 : 8;
+        off = (off + 7) & ~7;
+        p.cells[c].smem_off = off;
+        off += a.n_groups * copies * w;
+      }
+      return (off + 15) & ~15;
+    };
+    const int fixed = 128 + p.n_slots * (kTile * 8 + kThreads * 4) + p.n_bslots * kThreads * 4;
+    const int budget = 227 * 1024 - fixed - 2 * p.stage_bytes - 256;
+    int tab = layout(kThreads);
+    p.warp_private = 0;
+    if (tab > budget) {
+      const int one = layout(1);
+      p.warp_private = 1;
+      p.warp_tab_bytes = one;
+      tab = one * kWarps;
+      if (tab > budget) { set_error("ARRAY mode: %d groups x %d cells do not fit shared memory; use HASH", a.n_groups, a.n_cells); return VGPU_ERR_UNSUPPORTED; }
+    }
+    p.tab_bytes = tab;
+    const int grid = pipeline_grid(p.n_rows);
+    const size_t need = (size_t)grid * a.n_cells * a.n_groups;
+    if (need > a.partials_cap) {
+      if (a.partials) VG_CUDA(cudaFree(a.partials));
+      VG_CUDA(cudaMalloc(&a.partials, need * 8));
+      a.partials_cap = need;
+    }
+    p.partials = a.partials;
+    rc = launch_pipeline(p, tab, grid, stream);
+    if (rc) return rc;
+    const int cells = a.n_cells * a.n_groups;
+    merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), a.n_groups, device_err_word());
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+    return VGPU_OK;
+  }
+  // HASH: walk the batch in pieces small enough that the table cannot exceed 50 % load.
+  int64_t done = 0;
+  std::vector<vgpu_column> sliced(ncols);
+  while (done < total) {
+    uint64_t known = 0;
+    if (a.table) { rc = read_group_count(a, stream, &known); if (rc) return rc; }
+    const int64_t rem = total - done;
+    uint64_t room = a.capacity / 2 > known ? a.capacity / 2 - known : 0;
+    if (room < (uint64_t)std::min<int64_t>(rem, kTile)) {
+      uint64_t want = known + (uint64_t)std::min<int64_t>(rem, std::max<int64_t>(4 << 20, (int64_t)known));
+      if (a.expected_groups > 0) want = std::max<uint64_t>(want, (uint64_t)a.expected_groups);
+      rc = hash_resize(a, next_pow2(2 * want), stream);
+      if (rc) return rc;
+      room = a.capacity / 2 - known;
+    }
+    int64_t piece = std::min<int64_t>(rem, (int64_t)room);
+    if (piece < rem) piece = std::max<int64_t>(kTile, piece / kTile * kTile); // keep slices tile aligned
+    const vgpu_column* use = cols;
+    if (in_rows == nullptr && done > 0) { slice_columns(cols, ncols, done, sliced.data()); use = sliced.data(); }
+    p = PipelineParams{};
+    rc = plan_pipeline(prog, use, ncols, piece, in_rows ? in_rows + done : nullptr, piece, p);
+    if (rc) return rc;
+    p.mode = kSinkHash;
+    rc = fill_sink(a, p);
+    if (rc) return rc;
+    for (int c = 1; c < a.n_cells; ++c) {
+      if (a.cells[c].kind != kCellCount) continue;
+      if (!p.cells[c].skip && a.hash_aliased[c]) { rc = hash_materialize(a, c, stream); if (rc) return rc; }
+      if (!a.hash_aliased[c]) p.cells[c].skip = 0; // once materialised the cell is always updated
+    }
+    p.table = a.table; p.cap_mask = a.capacity - 1; p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
+    rc = launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
+    if (rc) return rc;
+    done += piece;
+  }
+  return VGPU_OK;
+}
+
+int agg_extract_all(Agg& a, cudaStream_t stream) {
+  if (a.packed_rows >= 0) return VGPU_OK;
+  if (!a.resolved) { set_error("aggregation has seen no input; call add_input (an empty batch is fine) first"); return VGPU_ERR_INVALID; }
+  size_t max_rows;
+  if (a.mode == VGPU_AGG_HASH) {
+    uint64_t known = 0;
+    if (a.table) { int rc = read_group_count(a, stream, &known); if (rc) return rc; }
+    max_rows = known;
+  } else {
+    max_rows = a.n_groups;
+  }
+  if (max_rows > a.packed_cap || a.packed == nullptr) {
+    if (a.packed) VG_CUDA(cudaFree(a.packed));
+    a.packed_cap = std::max<size_t>(max_rows, 16);
+    VG_CUDA(cudaMalloc(&a.packed, a.packed_cap * a.rm.row_words_out * 8));
+  }
+  VG_CUDA(cudaMemsetAsync(a.ctr + 1, 0, sizeof(unsigned long long), stream));
+  if (a.mode == VGPU_AGG_HASH) {
+    if (a.table && max_rows > 0) {
+      RowMap rm = a.rm;
+      for (int i = 0; i < rm.n_accs; ++i) {
+        if (rm.nn_cell[i] >= 0 && a.hash_aliased[rm.nn_cell[i]]) rm.nn_cell[i] = (int16_t)rm.rows_cell;
+        if (rm.value_kind[i] == kCellCount && a.hash_aliased[rm.value_cell[i]]) rm.value_cell[i] = (int16_t)rm.rows_cell;
+      }
+      const uint64_t slots = a.capacity + 2;
+      extract_hash_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, stream>>>(a.table, slots, a.row_words, rm, a.packed, a.ctr + 1);
+      VG_CUDA(cudaGetLastError());
+      count_launch();
+    }
+  } else {
+    extract_array_kernel<<<(a.n_groups + 255) / 256, 256, 0, stream>>>(a.state, a.n_groups, a.rm, a.mode == VGPU_AGG_GLOBAL ? 1 : 0, a.packed, a.ctr + 1);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  unsigned long long n = 0;
+  VG_CUDA(cudaMemcpyAsync(&n, a.ctr + 1, sizeof(n), cudaMemcpyDeviceToHost, stream));
+  VG_CUDA(cudaStreamSynchronize(stream));
+  a.packed_rows = (int64_t)n;
+  return VGPU_OK;
+}
+
+static DoneMap done_map(const RowMap& rm) {
+  DoneMap dm{};
+  for (int i = 0; i < rm.n_accs; ++i) {
+    for (int j = 0; j < i; ++j) {
+      if (rm.value_cell[j] == rm.value_cell[i] || rm.nn_cell[j] == rm.value_cell[i]) dm.d[2 * i] = 1;
+      if (rm.nn_cell[i] >= 0 && (rm.nn_cell[j] == rm.nn_cell[i] || rm.value_cell[j] == rm.nn_cell[i])) dm.d[2 * i + 1] = 1;
+    }
+    if (rm.nn_cell[i] >= 0 && rm.nn_cell[i] == rm.value_cell[i]) dm.d[2 * i + 1] = 1;
+  }
+  return dm;
+}
+
+int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
+  if (!a.resolved) { set_error("merge_rows before the cell plan is known; call add_input with an empty batch first"); return VGPU_ERR_INVALID; }
+  a.packed_rows = -1;
+  if (n <= 0) return VGPU_OK;
+  const DoneMap dm = done_map(a.rm);
+  if (a.mode != VGPU_AGG_HASH) {
+    merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, a.state, a.n_groups, device_err_word());
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+    return VGPU_OK;
+  }
+  uint64_t known = 0;
+  if (a.table) { int rc = read_group_count(a, stream, &known); if (rc) return rc; }
+  if (a.capacity / 2 < known + (uint64_t)n) {
+    int rc = hash_resize(a, next_pow2(2 * (known + (uint64_t)n)), stream);
+    if (rc) return rc;
+  }
+  for (int c = 1; c < a.n_cells; ++c) {
+    if (a.cells[c].kind == kCellCount && a.hash_aliased[c]) { int rc = hash_materialize(a, c, stream); if (rc) return rc; }
+  }
+  merge_rows_hash_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), device_err_word());
+  VG_CUDA(cudaGetLastError());
+  count_launch();
+  return VGPU_OK;
+}
+
+int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cudaStream_t stream) {
+  if (n_parts < 1 || n_parts > 32) { set_error("n_parts %d out of range", n_parts); return VGPU_ERR_INVALID; }
+  int rc = agg_extract_all(a, stream);
+  if (rc) return rc;
+  const int64_t n = a.packed_rows;
+  unsigned long long* counts = a.ctr + 2;   // [32]
+  VG_CUDA(cudaMemsetAsync(counts, 0, 32 * sizeof(unsigned long long), stream));
+  unsigned long long h[32] = {0};
+  if (n > 0) {
+    partition_count_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+    VG_CUDA(cudaMemcpyAsync(h, counts, n_parts * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    VG_CUDA(cudaStreamSynchronize(stream));
+    unsigned long long cur[32], run = 0;
+    for (int i = 0; i < n_parts; ++i) { cur[i] = run; run += h[i]; }
+    VG_CUDA(cudaMemcpyAsync(counts, cur, n_parts * sizeof(unsigned long long), cudaMemcpyHostToDevice, stream));
+    partition_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts, (uint64_t*)rows_out);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+    VG_CUDA(cudaStreamSynchronize(stream));
+  }
+  for (int i = 0; i < n_parts; ++i) counts_out[i] = (int64_t)h[i];
+  return VGPU_OK;
+}
+
+int agg_reset(Agg& a, cudaStream_t stream) {
+  a.packed_rows = -1;
+  if (!a.resolved) return VGPU_OK;
+  if (a.mode == VGPU_AGG_HASH) {
+    if (a.table) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(a.table)); a.table = nullptr; a.capacity = 0; }
+    for (int c = 0; c < kMaxCells; ++c) a.hash_aliased[c] = true;
+    VG_CUDA(cudaMemsetAsync(a.ctr, 0, sizeof(unsigned long long), stream));
+  } else {
+    const size_t words = (size_t)a.n_cells * a.n_groups;
+    init_state_kernel<<<(int)((words + 255) / 256), 256, 0, stream>>>(a.state, cell_meta(a), a.n_groups);
+    VG_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  return VGPU_OK;
+}
+
+void agg_free(Agg& a) {
+  cudaFree(a.state); cudaFree(a.partials); cudaFree(a.table); cudaFree(a.ctr); cudaFree(a.packed);
+  a.state = a.partials = a.table = a.packed = nullptr; a.ctr = nullptr;
+}
+
+} // namespace vg

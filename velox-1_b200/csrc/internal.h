@@ -133,6 +133,8 @@ struct Program {
   std::vector<vgpu_operand> outputs;
   vgpu_operand filter;
   int n_cols = 0, n_slots = 0, n_bslots = 0;
+  void* scratch = nullptr; // FilterProject: per-tile counts/offsets (grow-only)
+  size_t scratch_bytes = 0;
 };
 
 void set_error(const char* fmt, ...);

@@ -1,0 +1,231 @@
+"""Device-side helpers over the C-ABI: columns in HBM (torch tensors as the allocator), programs,
+FilterProject and aggregation calls.  Mirrors what the C++ operators in host/ do with RowVectors.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import abi, expr as ex
+
+NP_OF = {abi.TINYINT: np.int8, abi.SMALLINT: np.int16, abi.INTEGER: np.int32, abi.BIGINT: np.int64,
+         abi.REAL: np.float32, abi.DOUBLE: np.float64}
+
+
+def pack_bits(mask: np.ndarray) -> np.ndarray:
+    """bool[n] -> uint64 words, bit i of word i//64 = mask[i] (velox/common/base/Nulls.h layout)."""
+    n = len(mask)
+    words = (n + 63) // 64
+    b = np.zeros(words * 64, dtype=np.uint8)
+    b[:n] = mask
+    return np.packbits(b, bitorder="little").view(np.uint64)
+
+
+def unpack_bits(words: np.ndarray, n: int) -> np.ndarray:
+    return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+
+def stream_ptr() -> int:
+    return int(torch.cuda.current_stream().cuda_stream)
+
+
+@dataclass
+class DeviceColumn:
+    """One column resident in HBM, described the way DecodedVector exposes it."""
+    type: int
+    encoding: int = abi.FLAT
+    values: Optional[torch.Tensor] = None      # flat values / dictionary base values (uint8 view for BOOLEAN bits)
+    indices: Optional[torch.Tensor] = None     # int32
+    nulls: Optional[torch.Tensor] = None       # int64 words, bit=1 -> not null
+    base_nulls: Optional[torch.Tensor] = None
+    constant: object = None
+    constant_is_null: bool = False
+    length: int = 0
+
+    def desc(self) -> abi.Column:
+        c = abi.Column()
+        c.type, c.encoding = self.type, self.encoding
+        c.values = self.values.data_ptr() if self.values is not None else None
+        c.indices = self.indices.data_ptr() if self.indices is not None else None
+        c.nulls = self.nulls.data_ptr() if self.nulls is not None else None
+        c.base_nulls = self.base_nulls.data_ptr() if self.base_nulls is not None else None
+        c.base_length = len(self.values) if (self.encoding == abi.DICTIONARY and self.values is not None) else 0
+        if self.encoding == abi.CONSTANT and not self.constant_is_null:
+            if self.type in (abi.REAL, abi.DOUBLE):
+                c.constant.d = float(self.constant)
+            else:
+                c.constant.i = int(self.constant)
+        c.constant_is_null = 1 if self.constant_is_null else 0
+        return c
+
+    def nbytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.values, self.indices, self.nulls, self.base_nulls)
+                   if t is not None)
+
+
+def _dev(a: np.ndarray, device) -> torch.Tensor:
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device)
+
+
+def _bits_dev(mask: Optional[np.ndarray], device):
+    return None if mask is None else _dev(pack_bits(np.asarray(mask, dtype=bool)).view(np.int64), device)
+
+
+def flat_column(type: int, values: np.ndarray, not_null: Optional[np.ndarray] = None, device="cuda") -> DeviceColumn:
+    """Flat vector; `not_null` is a bool mask (True = present) or None."""
+    if type == abi.BOOLEAN:
+        v = _dev(pack_bits(np.asarray(values, dtype=bool)).view(np.int64), device)
+    else:
+        v = _dev(np.asarray(values, dtype=NP_OF[type]), device)
+    return DeviceColumn(type, abi.FLAT, v, nulls=_bits_dev(not_null, device), length=len(values))
+
+
+def dictionary_column(type: int, base: np.ndarray, indices: np.ndarray, not_null: Optional[np.ndarray] = None,
+                      base_not_null: Optional[np.ndarray] = None, device="cuda") -> DeviceColumn:
+    if type == abi.BOOLEAN:
+        b = _dev(pack_bits(np.asarray(base, dtype=bool)).view(np.int64), device)
+    else:
+        b = _dev(np.asarray(base, dtype=NP_OF[type]), device)
+    return DeviceColumn(type, abi.DICTIONARY, b, _dev(np.asarray(indices, dtype=np.int32), device),
+                        _bits_dev(not_null, device), _bits_dev(base_not_null, device), length=len(indices))
+
+
+def constant_column(type: int, value, length: int) -> DeviceColumn:
+    return DeviceColumn(type, abi.CONSTANT, constant=value, constant_is_null=value is None, length=length)
+
+
+def _col_array(cols: Sequence[DeviceColumn]):
+    arr = (abi.Column * max(1, len(cols)))(*[c.desc() for c in cols])
+    return arr
+
+
+class Program:
+    """ExprSet analogue: a filter plus output expressions lowered once, reused per batch."""
+
+    def __init__(self, filter: Optional[ex.Expr], outputs: Sequence[ex.Expr], n_columns: Optional[int] = None):
+        self.lowered = ex.lower(filter, list(outputs))
+        self.output_types = [o.type for o in outputs]
+        desc, keep = ex.to_desc(self.lowered, n_columns)
+        self._keep = keep
+        self.handle = C.c_void_p()
+        abi.check(abi.lib().vgpu_program_create(C.byref(desc), C.byref(self.handle)))
+
+    def __del__(self):
+        try:
+            if self.handle:
+                abi.lib().vgpu_program_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def check_errors():
+    abi.check(abi.lib().vgpu_check_errors(stream_ptr()))
+
+
+@dataclass
+class FilterProjectResult:
+    sel_bits: torch.Tensor           # int64 words
+    sel_idx: Optional[torch.Tensor]  # int32, first num_selected entries valid
+    num_selected: int
+    values: List[Optional[torch.Tensor]]
+    nulls: List[Optional[torch.Tensor]]
+
+
+def filter_project(program: Program, cols: Sequence[DeviceColumn], nrows: int, in_rows: Optional[torch.Tensor] = None,
+                   want_indices=True, want_nulls=True, sync=True) -> FilterProjectResult:
+    """vgpu_filter_project over device-resident columns (FilterProject::getOutput for one batch)."""
+    dev = "cuda"
+    total = nrows if in_rows is None else len(in_rows)
+    words = (total + 63) // 64
+    sel_bits = torch.zeros(max(words, 1), dtype=torch.int64, device=dev)
+    sel_idx = torch.empty(max(total, 1), dtype=torch.int32, device=dev) if want_indices else None
+    nsel = torch.zeros(1, dtype=torch.int64, device=dev)
+    outs = (abi.OutColumn * max(1, len(program.output_types)))()
+    values, nulls = [], []
+    for i, t in enumerate(program.output_types):
+        if t == abi.BOOLEAN:
+            v = torch.zeros(max(words, 1), dtype=torch.int64, device=dev)
+        else:
+            v = torch.empty(max(total, 1), dtype=getattr(torch, np.dtype(NP_OF[t]).name), device=dev)
+        nb = torch.zeros(max(words, 1), dtype=torch.int64, device=dev) if want_nulls else None
+        outs[i].values = v.data_ptr()
+        outs[i].nulls = nb.data_ptr() if nb is not None else None
+        values.append(v)
+        nulls.append(nb)
+    arr = _col_array(cols)
+    abi.check(abi.lib().vgpu_filter_project(
+        program.handle, arr, len(cols), nrows, in_rows.data_ptr() if in_rows is not None else None,
+        0 if in_rows is None else len(in_rows), sel_bits.data_ptr(),
+        sel_idx.data_ptr() if sel_idx is not None else None, nsel.data_ptr(), outs, stream_ptr()))
+    n = -1
+    if sync:
+        check_errors()
+        n = int(nsel.item())
+    return FilterProjectResult(sel_bits, sel_idx, n, values, nulls)
+
+
+class Aggregation:
+    """GroupingSet analogue over the C-ABI."""
+
+    def __init__(self, mode: int, keys: Sequence[tuple], accs: Sequence[tuple], ignore_null_keys=False,
+                 expected_groups=0):
+        """keys: (output index, bits, min, max); accs: (vgpu_acc_kind, output index or -1)."""
+        self.n_accs = len(accs)
+        self._keys = (abi.KeySpec * max(1, len(keys)))(*[abi.KeySpec(*k) for k in keys])
+        self._accs = (abi.AccSpec * max(1, len(accs)))(*[abi.AccSpec(*a) for a in accs])
+        d = abi.AggDesc()
+        d.mode, d.n_keys, d.n_accs = mode, len(keys), len(accs)
+        d.keys = C.cast(self._keys, C.POINTER(abi.KeySpec))
+        d.accs = C.cast(self._accs, C.POINTER(abi.AccSpec))
+        d.ignore_null_keys = 1 if ignore_null_keys else 0
+        d.expected_groups = expected_groups
+        self.handle = C.c_void_p()
+        abi.check(abi.lib().vgpu_agg_create(C.byref(d), C.byref(self.handle)))
+        self.row_words = 3 + 2 * self.n_accs
+
+    def __del__(self):
+        try:
+            if self.handle:
+                abi.lib().vgpu_agg_destroy(self.handle)
+        except Exception:
+            pass
+
+    def add_input(self, program: Program, cols: Sequence[DeviceColumn], nrows: int,
+                  in_rows: Optional[torch.Tensor] = None):
+        arr = _col_array(cols)
+        abi.check(abi.lib().vgpu_agg_add_input(
+            self.handle, program.handle, arr, len(cols), nrows,
+            in_rows.data_ptr() if in_rows is not None else None, 0 if in_rows is None else len(in_rows),
+            stream_ptr()))
+
+    def reset(self):
+        abi.check(abi.lib().vgpu_agg_reset(self.handle, stream_ptr()))
+
+    def num_groups(self) -> int:
+        n = C.c_int64()
+        abi.check(abi.lib().vgpu_agg_num_groups(self.handle, stream_ptr(), C.byref(n)))
+        return n.value
+
+    def extract(self) -> np.ndarray:
+        """All groups as an int64 array [n_groups, 3 + 2*n_accs] (key, flags, rows, values, counts)."""
+        n = self.num_groups()
+        buf = torch.empty((max(n, 1), self.row_words), dtype=torch.int64, device="cuda")
+        got = C.c_int64()
+        abi.check(abi.lib().vgpu_agg_extract(self.handle, 0, n, buf.data_ptr(), C.byref(got), stream_ptr()))
+        check_errors()
+        return buf[: got.value].cpu().numpy()
+
+    def merge_rows(self, rows: torch.Tensor):
+        assert rows.dtype == torch.int64 and rows.is_contiguous()
+        n = rows.shape[0] if rows.dim() == 2 else rows.numel() // self.row_words
+        abi.check(abi.lib().vgpu_agg_merge_rows(self.handle, rows.data_ptr(), n, stream_ptr()))
+
+    def partition(self, n_parts: int):
+        """Returns (rows tensor [n_groups, row_words] grouped by destination, counts list)."""
+        n = self.num_groups()
+        out = torch.empty((max(n, 1), self.row_words), dtype=torch.int64, device="cuda")
+        counts = (C.c_int64 * n_parts)()
+        abi.check(abi.lib().vgpu_agg_partition(self.handle, n_parts, out.data_ptr(), counts, stream_ptr()))
+        return out[:n], list(counts)
