@@ -194,7 +194,7 @@ struct Ctx {
   uint32_t* bmeta;   // [n_bslots][kThreads]  v | n << 8 | e << 16
   int pos0, pos1;    // first row of pair 0 / pair 1 inside the tile
   uint32_t valid;    // rows that exist
-  uint32_t ecode;    // error bits raised by this thread's ops
+  uint32_t ecode;    // error bits raised by this thread's ops, one byte per row
   Val acc;
   BoolVal bacc;
 };
@@ -662,7 +662,7 @@ __device__ __forceinline__ void run_program(Ctx& cx) {
       for (int j = 0; j < 4; ++j) {
         r.v[j] = 0;
         const uint32_t err = cast_value(op.a.type, op.type, a.v[j], r.v[j]);
-        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err; }
+        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
       }
       r.e |= bad;
     } else if (oc == VGPU_OP_NEG) {
@@ -671,7 +671,7 @@ __device__ __forceinline__ void run_program(Ctx& cx) {
       for (int j = 0; j < 4; ++j) {
         r.v[j] = 0;
         const uint32_t err = arith(oc, op.type, a.v[j], 0, r.v[j]);
-        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err; }
+        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
       }
       r.e |= bad;
     } else {
@@ -697,7 +697,7 @@ __device__ __forceinline__ void run_program(Ctx& cx) {
         for (int j = 0; j < 4; ++j) {
           r.v[j] = 0;
           const uint32_t err = arith(oc, op.type, a.v[j], b.v[j], r.v[j]);
-          if (err && !((r.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err; }
+          if (err && !((r.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
         }
         r.e |= bad;
       }
@@ -720,6 +720,16 @@ __device__ __forceinline__ uint32_t interleave16(uint32_t even, uint32_t odd) {
   t = (x ^ (x >> 2)) & 0x0c0c0c0cu; x ^= t ^ (t << 2);
   t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
   return x;
+}
+
+// Error bits of the rows in `raise` (cx.ecode keeps one byte of bits per row).
+__device__ __forceinline__ uint32_t raised_code(uint32_t ecode, uint32_t raise) {
+  uint32_t code = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if ((raise >> j) & 1u) code |= (ecode >> (8 * j)) & 0xffu;
+  }
+  return code ? code : kErrOverflow;
 }
 
 // Filter operand -> rows that pass; raises latched errors for rows the filter left undecided.
@@ -842,7 +852,7 @@ __device__ void sink_filter_project(Ctx& cx, int64_t tile, int cnt) {
       }
     }
   }
-  if (raise) atomicOr(p.err_word, cx.ecode ? cx.ecode : kErrOverflow);
+  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
 }
 
 // ---- group-by accumulation -------------------------------------------------------------------
@@ -932,7 +942,7 @@ __device__ __forceinline__ void compute_keys(Ctx& cx, uint32_t& pass, uint32_t& 
       key[j] += (p.mode == kSinkArray) ? id * (uint64_t)ks.mult : (id << ks.shift);
     }
     if (bad & pass) {
-      cx.ecode |= kErrKeyRange;
+      cx.ecode |= kErrKeyRange * 0x01010101u;
       raise |= bad & pass;
       pass &= ~bad;
     }
@@ -1017,7 +1027,7 @@ __device__ void sink_array(Ctx& cx, char* tab) {
       }
     }
   }
-  if (raise) atomicOr(p.err_word, cx.ecode ? cx.ecode : kErrOverflow);
+  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
   if (acc_err) atomicOr(p.err_word, acc_err);
 }
 
@@ -1091,7 +1101,7 @@ __device__ void sink_hash(Ctx& cx) {
       if (a1) update_hbm_cell(cell.kind, p.table + slot[j1] * p.row_words + 1 + c, x1, acc_err);
     }
   }
-  if (raise) atomicOr(p.err_word, cx.ecode ? cx.ecode : kErrOverflow);
+  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
   if (acc_err) atomicOr(p.err_word, acc_err);
 }
 

@@ -104,7 +104,8 @@ class _Lowerer:
         self.free_b = list(range(12))[::-1]
         self.uses = {}     # expr -> remaining uses (common sub-expression elimination)
         self.where = {}    # expr -> (is_bool, slot) of a materialised shared value
-        self.pinned = set()
+        self.pinned = set()   # slots of shared values with uses left
+        self.keep = set()     # slots read by the sink (filter / outputs): never recycled
         self.max_col = -1
 
     def count(self, e):
@@ -124,7 +125,8 @@ class _Lowerer:
         return pool.pop()
 
     def release(self, operand):
-        if operand.kind == abi.OPND_SLOT and (operand.type == abi.BOOLEAN, operand.index) not in self.pinned:
+        key = (operand.type == abi.BOOLEAN, operand.index)
+        if operand.kind == abi.OPND_SLOT and key not in self.pinned and key not in self.keep:
             (self.free_b if operand.type == abi.BOOLEAN else self.free_v).append(operand.index)
 
     def leaf(self, e):
@@ -250,7 +252,7 @@ def lower(filter: Optional[Expr], outputs: List[Expr]) -> Lowered:
         f, imm = lw.gen(filter, want_slot=isinstance(filter, Call))
         if f.kind == abi.OPND_IMM:  # constant filter: materialise through NOT NOT
             raise ValueError("constant filter: fold it before lowering")
-        lw.pinned.add((True, f.index)) if f.kind == abi.OPND_SLOT else None
+        lw.keep.add((True, f.index)) if f.kind == abi.OPND_SLOT else None
         res.filter = f
     for o in outputs:
         operand, imm = lw.gen(o, want_slot=isinstance(o, Call))
@@ -263,7 +265,7 @@ def lower(filter: Optional[Expr], outputs: List[Expr]) -> Lowered:
             lw.ops[-1].dst_slot = slot
             operand = lw.opnd(abi.OPND_SLOT, o.type, slot)
         if operand.kind == abi.OPND_SLOT:
-            lw.pinned.add((operand.type == abi.BOOLEAN, operand.index))
+            lw.keep.add((operand.type == abi.BOOLEAN, operand.index))
         res.outputs.append(operand)
     res.ops = lw.ops
     res.n_columns = lw.max_col + 1
