@@ -1,0 +1,286 @@
+#!/usr/bin/env python
+"""Headline benchmark: TPC-H Q1 (filter + 4-group aggregation) over lineitem SF10 per GPU.
+
+  python bench.py --gpus N --steps K --warmup W            # the CUDA path (libvgpu.so)
+  python bench.py --impl reference --gpus N ...            # the reference's CPU path (oracle/)
+
+A step is one pass of the hot path over one resident batch: reset groups, fused filter ->
+project -> partial aggregation over every row, (N > 1: hash-partition the partial groups,
+all-to-all over NCCL, final aggregation), extract the result rows.  Prints ONE JSON line.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+Q1_COLS = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate"]
+Q1_BYTES_PER_ROW = 4 + 4 + 8 + 8 + 8 + 8 + 4  # 44 B/row
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.samples, self.stop_flag, self.index = [], False, index
+        self.thread = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        self.thread.join(timeout=6)
+        sm = [int(s[0]) for s in self.samples if s[0].isdigit()]
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def q1_plan():
+    import helpers as H
+    f, outs = H.q1_exprs()
+    return H, f, outs
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU path (oracle/velox_cpu.cpp: batch-at-a-time interpreter + HashAggregation,
+    one driver thread per core, partial -> final) on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    import cpu_oracle as cpu
+    H, f, outs = q1_plan()
+    tpch = importlib.import_module("velox-1_b200.tpch_synth")
+    sample = min(tpch.row_count(args.sf), args.ref_rows)
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    data = tpch.lineitem(args.sf, Q1_COLS, rows=sample, device=dev)
+    types = [3, 3, 6, 6, 6, 6, 3]
+    cols = [(t, data[c].cpu().numpy(), None) for c, t in zip(Q1_COLS, types)]
+    accs = [(H.KIND_NAME[k], i) for k, i in H.Q1_ACCS]
+    threads = os.cpu_count() or 1
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        _, secs = cpu.run(f, outs, cols, sample, [0, 1], accs, threads=threads, batch_rows=4096, max_groups=64)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = sample * len(times) / total
+    line = {
+        "impl": "reference", "metric": "TPC-H Q1 lineitem rows/sec", "value": value, "unit": "rows/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"TPC-H Q1 SF{args.sf:g}: filter + group-by (4 groups) sum/avg/count", "sf": args.sf},
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port",
+                         "sample": f"first {sample} rows of the SF{args.sf:g} workload per step, {threads} driver threads"},
+        "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    pkg = importlib.import_module("velox-1_b200")
+    abi = pkg.abi
+    torch.cuda.set_device(local_rank)
+    abi.check(abi.lib().vgpu_init(local_rank))
+    engine = importlib.import_module("velox-1_b200.engine")
+    tpch = importlib.import_module("velox-1_b200.tpch_synth")
+    H, f, outs = q1_plan()
+    dist = None
+    exchange = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        ids = [engine.Exchange.make_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        exchange = engine.Exchange(rank, world, ids[0])
+
+    n = tpch.row_count(args.sf)
+    data = tpch.lineitem(args.sf, Q1_COLS, order_offset=rank * (n // 4 + n // 50 + 16), seed=rank)
+    types = [abi.INTEGER, abi.INTEGER, abi.DOUBLE, abi.DOUBLE, abi.DOUBLE, abi.DOUBLE, abi.INTEGER]
+    cols = [engine.DeviceColumn(t, abi.FLAT, data[c], length=n) for c, t in zip(Q1_COLS, types)]
+    prog = engine.Program(f, outs)
+    partial = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS)
+    final = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS) if world > 1 else None
+    empty = [engine.DeviceColumn(t, abi.FLAT, data[c][:0], length=0) for c, t in zip(Q1_COLS, types)]
+
+    kernel_ms = []
+
+    def step(timed):
+        partial.reset()
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        partial.add_input(prog, cols, n)
+        if timed:
+            e1.record()
+            kernel_ms.append((e0, e1))
+        if world > 1:
+            final.reset()
+            final.add_input(prog, empty, 0)
+            exchange.shuffle(partial, final)
+            return final.num_groups()
+        return partial.num_groups()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(False)
+    stats0 = abi.Stats()
+    abi.lib().vgpu_get_stats(stats0)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    groups = 0
+    for _ in range(args.steps):
+        groups = step(True)
+    t1.record()
+    barrier()
+    clocks = sampler.stop()
+    stats1 = abi.Stats()
+    abi.lib().vgpu_get_stats(stats1)
+    ms = t0.elapsed_time(t1)
+    kms = float(np.mean([a.elapsed_time(b) for a, b in kernel_ms]))
+    engine.check_errors()
+
+    # ---- end to end: HOST batches through the public API (H2D inside the timed region) ----------
+    host = [data[c].cpu().pin_memory() for c in Q1_COLS]
+    runner = engine.HostBatchRunner(types, chunk_rows=args.chunk_rows)
+    e2e_agg = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS)
+    result_bytes = 0
+
+    def e2e_step():
+        nonlocal result_bytes
+        e2e_agg.reset()
+        runner.run(e2e_agg, prog, host, n)
+        rows = e2e_agg.extract()  # device -> host read of the result rows
+        result_bytes = rows.nbytes
+        return rows
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        e2e_step()
+    barrier()
+    w0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_rows = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - w0
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+    if rank != 0:
+        return
+    peak, peak_src = load_peaks()
+    value = n * world * args.steps / (ms * 1e-3)
+    achieved = n * Q1_BYTES_PER_ROW / (kms * 1e-3) / 1e9
+    line = {
+        "metric": "TPC-H Q1 lineitem rows/sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"TPC-H Q1 SF{args.sf:g}: filter + group-by (4 groups) sum/avg/count",
+                   "rows_per_gpu": n, "sf": args.sf, "bytes_per_row": Q1_BYTES_PER_ROW, "groups": int(groups),
+                   "l2": "input (2.6 GB per step) is larger than L2 (126 MB); no flush needed",
+                   "generator": "velox-1_b200/tpch_synth.py (lineitem-shaped, dbgen value domains)"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "pipeline_kernel<ARRAY> (+ merge_partials)", "kernel_ms": kms,
+                     "peak_source": peak_src},
+        "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": runner.h2d_bytes,
+                "d2h_bytes_per_step": int(result_bytes), "steps": e2e_steps, "chunk_rows": args.chunk_rows},
+        "gpu_launches": int(stats1.kernel_launches - stats0.kernel_launches),
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args, H, f, outs, data, types)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, H, f, outs, data, types):
+    """oracle/velox_cpu.cpp timed on this box's host cores on a bounded sample of the same rows."""
+    import cpu_oracle as cpu
+    threads = os.cpu_count() or 1
+    accs = [(H.KIND_NAME[k], i) for k, i in H.Q1_ACCS]
+    probe = 2_000_000
+    pc = [(t, data[c][:probe].cpu().numpy(), None) for c, t in zip(Q1_COLS, types)]
+    _, secs = cpu.run(f, outs, pc, probe, [0, 1], accs, threads=threads, max_groups=64)
+    rate = probe / max(secs, 1e-6)
+    cpu_seconds_budget = 12.0 * threads  # about 10-30 s of CPU work
+    sample = int(min(len(data[Q1_COLS[0]]), max(probe, rate * cpu_seconds_budget / threads)))
+    sc = [(t, data[c][:sample].cpu().numpy(), None) for c, t in zip(Q1_COLS, types)]
+    best = None
+    for _ in range(2):
+        _, secs = cpu.run(f, outs, sc, sample, [0, 1], accs, threads=threads, max_groups=64)
+        best = secs if best is None else min(best, secs)
+    return {"value": sample / best, "unit": "rows/s", "cores": threads, "kind": "port",
+            "sample": f"first {sample} rows of the workload, {threads} driver threads, batches of 4096 rows"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sf", type=float, default=10.0)
+    ap.add_argument("--chunk-rows", type=int, default=4 << 20)
+    ap.add_argument("--ref-rows", type=int, default=20_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

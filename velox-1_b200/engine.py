@@ -229,3 +229,88 @@ class Aggregation:
         counts = (C.c_int64 * n_parts)()
         abi.check(abi.lib().vgpu_agg_partition(self.handle, n_parts, out.data_ptr(), counts, stream_ptr()))
         return out[:n], list(counts)
+
+
+class HostBatchRunner:
+    """End-to-end path for HOST-resident batches: pinned host columns are copied to HBM in chunks on
+    a copy stream (double-buffered) while the compute stream runs the fused pipeline on the previous
+    chunk — what the C++ operator does with a host RowVector handed to addInput."""
+
+    def __init__(self, types: Sequence[int], chunk_rows: int = 4 << 20, n_buffers: int = 2):
+        assert chunk_rows % 1024 == 0
+        self.types = list(types)
+        self.chunk = chunk_rows
+        self.copy_stream = torch.cuda.Stream()
+        self.bufs = [[torch.empty(chunk_rows, dtype=getattr(torch, np.dtype(NP_OF[t]).name), device="cuda")
+                      for t in self.types] for _ in range(n_buffers)]
+        self.ready = [torch.cuda.Event() for _ in range(n_buffers)]
+        self.free = [torch.cuda.Event() for _ in range(n_buffers)]
+        self.h2d_bytes = 0
+
+    def run(self, agg: "Aggregation", program: Program, host_cols: Sequence[torch.Tensor], n: int):
+        compute = torch.cuda.current_stream()
+        nb = len(self.bufs)
+        self.h2d_bytes = 0
+        for i, off in enumerate(range(0, n, self.chunk)):
+            m = min(self.chunk, n - off)
+            b = i % nb
+            if i >= nb:
+                self.copy_stream.wait_event(self.free[b])
+            with torch.cuda.stream(self.copy_stream):
+                for dst, src in zip(self.bufs[b], host_cols):
+                    dst[:m].copy_(src[off:off + m], non_blocking=True)
+                    self.h2d_bytes += m * src.element_size()
+                self.ready[b].record(self.copy_stream)
+            compute.wait_event(self.ready[b])
+            cols = [DeviceColumn(t, abi.FLAT, buf, length=m) for t, buf in zip(self.types, self.bufs[b])]
+            agg.add_input(program, cols, m)
+            self.free[b].record(compute)
+
+
+class Exchange:
+    """Multi-GPU step between partial and final aggregation (one process per GPU): hash-partition the
+    partial groups, all-to-all the packed rows over NCCL, fold them into the final aggregation
+    (partialAggregation -> partitionedOutput -> exchange -> finalAggregation of the reference)."""
+
+    def __init__(self, rank: int, world: int, unique_id: bytes):
+        self.rank, self.world = rank, world
+        idbuf = (C.c_uint8 * abi.COMM_ID_BYTES).from_buffer_copy(unique_id)
+        self.handle = C.c_void_p()
+        abi.check(abi.lib().vgpu_comm_create(idbuf, rank, world, C.byref(self.handle)))
+        self.bytes_sent = 0
+
+    @staticmethod
+    def make_unique_id() -> bytes:
+        idbuf = (C.c_uint8 * abi.COMM_ID_BYTES)()
+        abi.check(abi.lib().vgpu_comm_unique_id(idbuf))
+        return bytes(idbuf)
+
+    def shuffle(self, partial: "Aggregation", final: "Aggregation"):
+        W = self.world
+        rows, counts = partial.partition(W)
+        row_bytes = partial.row_words * 8
+        send_counts = torch.tensor(counts, dtype=torch.int64, device="cuda")
+        all_counts = torch.empty(W * W, dtype=torch.int64, device="cuda")
+        abi.check(abi.lib().vgpu_comm_allgather(self.handle, send_counts.data_ptr(), all_counts.data_ptr(), W * 8,
+                                                stream_ptr()))
+        matrix = all_counts.cpu().numpy().reshape(W, W)  # [src][dst]
+        recv_counts = matrix[:, self.rank]
+        sc, so, rc, ro = plan_alltoall(counts, recv_counts, row_bytes)
+        recv = torch.empty((max(int(recv_counts.sum()), 1), partial.row_words), dtype=torch.int64, device="cuda")
+        arr = lambda xs: (C.c_int64 * W)(*[int(x) for x in xs])
+        abi.check(abi.lib().vgpu_comm_alltoallv(self.handle, rows.data_ptr(), arr(sc), arr(so), recv.data_ptr(), arr(rc),
+                                                arr(ro), stream_ptr()))
+        self.bytes_sent = int(sum(sc)) - int(sc[self.rank])
+        final.merge_rows(recv[: int(recv_counts.sum())])
+
+
+def plan_alltoall(send_rows, recv_rows, row_bytes):
+    """Row counts per peer -> byte counts and byte offsets of the contiguous send / receive segments."""
+    sc = [int(x) * row_bytes for x in send_rows]
+    rc = [int(x) * row_bytes for x in recv_rows]
+    so = [0] * len(sc)
+    ro = [0] * len(rc)
+    for i in range(1, len(sc)):
+        so[i] = so[i - 1] + sc[i - 1]
+        ro[i] = ro[i - 1] + rc[i - 1]
+    return sc, so, rc, ro
