@@ -340,6 +340,19 @@ typedef struct {
 int vgpu_get_stats(vgpu_stats* out);
 int vgpu_reset_stats(void);
 
+/* ---- diagnostics of the plan-specialised kernels ---------------------------------------------- */
+
+/* Dry run (no device needed): vgpu_agg_add_input / vgpu_filter_project only generate the source
+ * of the plan-specialised kernel for the shape they are given.  build() uses this to prebuild the
+ * cubins of velox-1_b200/aot_plans.py. */
+int vgpu_debug_set_dry_run(int on);
+/* Source body of the last kernel generated on this thread and the hash that names its cubin.
+ * Returns VGPU_ERR_INVALID when `cap` is too small (the text is truncated). */
+int vgpu_debug_last_kernel_source(char* buf, size_t cap, uint64_t* hash);
+/* How the last shape was handled on this thread: "built from aot|disk|nvrtc", "declined: ...",
+ * "nvrtc failed: ...". */
+int vgpu_debug_last_kernel_note(char* buf, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

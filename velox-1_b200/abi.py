@@ -123,6 +123,9 @@ PROTOTYPES = {
     "vgpu_comm_allgather": [_P, _P, _P, _SZ, _P],
     "vgpu_get_stats": [C.POINTER(Stats)],
     "vgpu_reset_stats": [],
+    "vgpu_debug_set_dry_run": [C.c_int],
+    "vgpu_debug_last_kernel_source": [C.c_char_p, _SZ, C.POINTER(C.c_uint64)],
+    "vgpu_debug_last_kernel_note": [C.c_char_p, _SZ],
 }
 
 _lib = None
@@ -154,6 +157,20 @@ def last_error():
     buf = C.create_string_buffer(512)
     lib().vgpu_last_error(buf, 512)
     return buf.value.decode(errors="replace")
+
+
+def last_kernel_note():
+    buf = C.create_string_buffer(4096)
+    lib().vgpu_debug_last_kernel_note(buf, 4096)
+    return buf.value.decode(errors="replace")
+
+
+def last_kernel_source():
+    """(source body, cubin hash) of the last plan-specialised kernel generated on this thread."""
+    buf = C.create_string_buffer(1 << 20)
+    h = C.c_uint64()
+    lib().vgpu_debug_last_kernel_source(buf, 1 << 20, C.byref(h))
+    return buf.value.decode(), h.value
 
 
 def check(status):

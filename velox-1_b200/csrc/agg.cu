@@ -12,6 +12,7 @@
 #include <algorithm>
 
 #include "agg.h"
+#include "fused.h"
 #include "device_common.cuh"
 
 namespace vg {
@@ -30,19 +31,40 @@ __global__ void init_state_kernel(uint64_t* state, CellMeta m, int G) {
   state[i] = cell_identity(m.kind[i / G]);
 }
 
-// state[c][g] = fold(state[c][g], partials[0][c][g], partials[1][c][g], ...) in block order.
+// Launch-time ("compact") group numbering -> the aggregation's state numbering.  A launch whose key
+// columns cannot be NULL drops the NULL id of those keys so that the per-thread shared-memory
+// tables stay small; the state always keeps it (a later batch may carry NULLs).
+struct GroupMap {
+  int32_t n_keys;
+  int32_t card[kMaxKeys];   // compact cardinality of key k
+  int32_t shift[kMaxKeys];  // added to the compact digit to get the state digit (0 or 1)
+  int64_t mult[kMaxKeys];   // state multiplier of key k
+};
+__device__ __forceinline__ int state_group(const GroupMap& gm, int g) {
+  int64_t out = 0;
+  for (int k = 0; k < gm.n_keys; ++k) {
+    const int d = g % gm.card[k];
+    g /= gm.card[k];
+    out += (int64_t)(d + gm.shift[k]) * gm.mult[k];
+  }
+  return (int)out;
+}
+
+// state[c][sg] = fold(state[c][sg], partials[0][c][g], partials[1][c][g], ...) in block order
+// (fixed order => run-to-run deterministic); Gc = groups of the launch, G = groups of the state.
 __global__ void merge_partials_kernel(uint64_t* state, const uint64_t* partials, int n_blocks,
-                                      CellMeta m, int G, uint32_t* err_word) {
+                                      CellMeta m, int Gc, int G, GroupMap gm, uint32_t* err_word) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m.n_cells * G) return;
-  const int c = i / G, g = i - c * G;
+  if (i >= m.n_cells * Gc) return;
+  const int c = i / Gc, g = i - c * Gc;
   const int src = m.skip[c] ? m.alias[c] : c;
   const uint8_t kind = m.kind[c];
   uint32_t err = 0;
   uint64_t acc = cell_identity(kind);
-  const size_t stride = (size_t)m.n_cells * G;
-  for (int b = 0; b < n_blocks; ++b) acc = fold2(kind, acc, partials[b * stride + (size_t)src * G + g], err);
-  state[i] = fold2(kind, state[i], acc, err);
+  const size_t stride = (size_t)m.n_cells * Gc;
+  for (int b = 0; b < n_blocks; ++b) acc = fold2(kind, acc, partials[b * stride + (size_t)src * Gc + g], err);
+  const size_t si = (size_t)c * G + state_group(gm, g);
+  state[si] = fold2(kind, state[si], acc, err);
   if (err) atomicOr(err_word, err);
 }
 
@@ -287,10 +309,12 @@ int agg_resolve(Agg& a, const Program& prog) {
     }
     a.n_groups = (int)G;
     const size_t words = (size_t)a.n_cells * a.n_groups;
-    VG_CUDA(cudaMalloc(&a.state, words * 8));
-    init_state_kernel<<<(int)((words + 255) / 256), 256>>>(a.state, cell_meta(a), a.n_groups);
-    VG_CUDA(cudaGetLastError());
-    count_launch();
+    if (!fused_dry_run()) {
+      VG_CUDA(cudaMalloc(&a.state, words * 8));
+      init_state_kernel<<<(int)((words + 255) / 256), 256>>>(a.state, cell_meta(a), a.n_groups);
+      VG_CUDA(cudaGetLastError());
+      count_launch();
+    }
   } else {
     int shift = 0;
     for (size_t k = 0; k < a.keys.size(); ++k) {
@@ -306,8 +330,10 @@ int agg_resolve(Agg& a, const Program& prog) {
     }
     a.row_words = 1 + a.n_cells;
   }
-  VG_CUDA(cudaMalloc(&a.ctr, 64 * sizeof(unsigned long long)));
-  VG_CUDA(cudaMemset(a.ctr, 0, 64 * sizeof(unsigned long long)));
+  if (!fused_dry_run()) {
+    VG_CUDA(cudaMalloc(&a.ctr, 64 * sizeof(unsigned long long)));
+    VG_CUDA(cudaMemset(a.ctr, 0, 64 * sizeof(unsigned long long)));
+  }
   a.resolved = true;
   return VGPU_OK;
 }
@@ -364,17 +390,31 @@ static void slice_columns(const vgpu_column* in, int n, int64_t off, vgpu_column
   }
 }
 
-static int fill_sink(Agg& a, PipelineParams& p) {
+static int fill_sink(Agg& a, PipelineParams& p, GroupMap* gm = nullptr) {
   p.n_keys = (int)a.keys.size();
   p.ignore_null_keys = a.ignore_null_keys ? 1 : 0;
+  int64_t compact = 1;
+  if (gm) { *gm = GroupMap{}; gm->n_keys = p.n_keys; }
   for (int k = 0; k < p.n_keys; ++k) {
     DevKey& d = p.keys[k];
     d = DevKey{};
+    if (a.keys[k].output < 0 || a.keys[k].output >= p.n_outputs) { set_error("key %d reads output %d", k, a.keys[k].output); return VGPU_ERR_INVALID; }
     d.min = a.keys[k].min; d.max = a.keys[k].max; d.mult = a.mults[k];
     d.output = (int8_t)a.keys[k].output; d.bits = (uint8_t)a.keys[k].bits; d.shift = a.shifts[k];
     d.nullable = a.ignore_null_keys ? 0 : 1;
-    if (a.keys[k].output < 0 || a.keys[k].output >= p.n_outputs) { set_error("key %d reads output %d", k, a.keys[k].output); return VGPU_ERR_INVALID; }
+    if (gm) {
+      // ARRAY: this launch numbers groups without the NULL id of keys that cannot be NULL here
+      const bool can_null = !a.ignore_null_keys && output_nullable(p, a.keys[k].output);
+      const int64_t card = a.keys[k].max - a.keys[k].min + 1 + (can_null ? 1 : 0);
+      gm->card[k] = (int32_t)card;
+      gm->shift[k] = (!a.ignore_null_keys && !can_null) ? 1 : 0;
+      gm->mult[k] = a.mults[k];
+      d.nullable = can_null ? 1 : 0;
+      d.mult = compact;
+      compact *= card;
+    }
   }
+  if (gm) p.n_groups = (int)compact;
   p.n_cells = a.n_cells;
   for (int c = 0; c < a.n_cells; ++c) {
     DevCell& d = p.cells[c];
@@ -419,9 +459,32 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
     if (rc) return rc;
     p.mode = kSinkArray;
-    rc = fill_sink(a, p);
+    GroupMap gm;
+    rc = fill_sink(a, p, &gm);
     if (rc) return rc;
-    p.n_groups = a.n_groups;
+    const int Gc = p.n_groups;
+    {
+      // plan-specialised kernel first; the interpreter takes the shapes it declines
+      int fgrid = 0;
+      FusedKernel* fk = fused_prepare(p, &fgrid);
+      if (fused_dry_run()) return VGPU_OK;
+      if (fk) {
+        const size_t need = (size_t)fgrid * a.n_cells * Gc;
+        if (need > a.partials_cap) {
+          if (a.partials) VG_CUDA(cudaFree(a.partials));
+          VG_CUDA(cudaMalloc(&a.partials, need * 8));
+          a.partials_cap = need;
+        }
+        p.partials = a.partials;
+        rc = fused_launch(fk, p, fgrid, stream);
+        if (rc) return rc;
+        const int cells = a.n_cells * Gc;
+        merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, fgrid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
+        VG_CUDA(cudaGetLastError());
+        count_launch();
+        return VGPU_OK;
+      }
+    }
     // shared-memory plan of the partial tables: one table per thread when it fits next to at
     // least two stages, else one per warp.
     auto layout = [&](int copies) {
@@ -431,7 +494,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
         const int w = p.cells[c].kind == kCellCount ? 4 : 8;
         off = (off + 7) & ~7;
         p.cells[c].smem_off = off;
-        off += a.n_groups * copies * w;
+        off += Gc * copies * w;
       }
       return (off + 15) & ~15;
     };
@@ -444,11 +507,11 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       p.warp_private = 1;
       p.warp_tab_bytes = one;
       tab = one * kWarps;
-      if (tab > budget) { set_error("ARRAY mode: %d groups x %d cells do not fit shared memory; use HASH", a.n_groups, a.n_cells); return VGPU_ERR_UNSUPPORTED; }
+      if (tab > budget) { set_error("ARRAY mode: %d groups x %d cells do not fit shared memory; use HASH", Gc, a.n_cells); return VGPU_ERR_UNSUPPORTED; }
     }
     p.tab_bytes = tab;
     const int grid = pipeline_grid(p.n_rows);
-    const size_t need = (size_t)grid * a.n_cells * a.n_groups;
+    const size_t need = (size_t)grid * a.n_cells * Gc;
     if (need > a.partials_cap) {
       if (a.partials) VG_CUDA(cudaFree(a.partials));
       VG_CUDA(cudaMalloc(&a.partials, need * 8));
@@ -457,10 +520,21 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     p.partials = a.partials;
     rc = launch_pipeline(p, tab, grid, stream);
     if (rc) return rc;
-    const int cells = a.n_cells * a.n_groups;
-    merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), a.n_groups, device_err_word());
+    const int cells = a.n_cells * Gc;
+    merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
     VG_CUDA(cudaGetLastError());
     count_launch();
+    return VGPU_OK;
+  }
+  if (fused_dry_run()) {
+    rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
+    if (rc) return rc;
+    p.mode = kSinkHash;
+    rc = fill_sink(a, p);
+    if (rc) return rc;
+    p.row_words = a.row_words;
+    int fgrid = 0;
+    fused_prepare(p, &fgrid);
     return VGPU_OK;
   }
   // HASH: walk the batch in pieces small enough that the table cannot exceed 50 % load.
@@ -494,7 +568,9 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       if (!a.hash_aliased[c]) p.cells[c].skip = 0; // once materialised the cell is always updated
     }
     p.table = a.table; p.cap_mask = a.capacity - 1; p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
-    rc = launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
+    int fgrid = 0;
+    FusedKernel* fk = fused_prepare(p, &fgrid);
+    rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
     if (rc) return rc;
     done += piece;
   }

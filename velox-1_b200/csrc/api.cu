@@ -11,6 +11,7 @@
 #include <new>
 
 #include "agg.h"
+#include "fused.h"
 #include "internal.h"
 
 namespace vg {
@@ -257,14 +258,14 @@ int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t
   p.mode = kSinkFilterProject;
   const int64_t n_tiles = (total + kTile - 1) / kTile;
   const size_t need = (size_t)n_tiles * 12 + 64;
-  if (need > prog.scratch_bytes) {
+  if (need > prog.scratch_bytes && !fused_dry_run()) {
     if (prog.scratch) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(prog.scratch)); }
     VG_CUDA(cudaMalloc(&prog.scratch, need));
     prog.scratch_bytes = need;
   }
   int64_t* tile_offsets = (int64_t*)prog.scratch;
   int32_t* tile_counts = (int32_t*)((char*)prog.scratch + (size_t)n_tiles * 8);
-  VG_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)n_tiles * 4, stream));
+  if (!fused_dry_run()) VG_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)n_tiles * 4, stream));
   p.sel_words = (uint32_t*)sel_bits;
   p.tile_counts = tile_counts;
   p.num_selected = (unsigned long long*)num_selected;
@@ -273,7 +274,12 @@ int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t
     p.outs[i].nulls = outs ? outs[i].nulls : nullptr;
     if (p.outs[i].values && (((uintptr_t)p.outs[i].values) & 15u)) { set_error("output %d: values must be 16-byte aligned", i); return VGPU_ERR_INVALID; }
   }
-  rc = launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
+  {
+    int fgrid = 0;
+    FusedKernel* fk = fused_prepare(p, &fgrid);
+    if (fused_dry_run()) return VGPU_OK;
+    rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
+  }
   if (rc) return rc;
   __atomic_fetch_add(&g_stats.rows_in, total, __ATOMIC_RELAXED);
   return launch_selection_indices(p.sel_words, tile_counts, tile_offsets, total, sel_idx, (unsigned long long*)num_selected, stream);
@@ -345,6 +351,21 @@ int vgpu_agg_merge_rows(vgpu_agg_t agg, const void* rows, int64_t n_rows, void* 
 int vgpu_agg_partition(vgpu_agg_t agg, int32_t n_parts, void* rows_out, int64_t* counts_out, void* stream) {
   if (!agg || !counts_out) return VGPU_ERR_INVALID;
   return agg_partition(agg->agg, n_parts, rows_out, counts_out, (cudaStream_t)stream);
+}
+
+// ---- diagnostics of the plan-specialised kernels ------------------------------------------------
+int vgpu_debug_set_dry_run(int on) { fused_set_dry_run(on != 0); return VGPU_OK; }
+int vgpu_debug_last_kernel_source(char* buf, size_t cap, uint64_t* hash) {
+  const std::string& s = fused_last_source();
+  if (hash) *hash = fused_source_hash(s);
+  if (buf && cap) { strncpy(buf, s.c_str(), cap - 1); buf[cap - 1] = 0; }
+  return s.size() + 1 > cap ? VGPU_ERR_INVALID : VGPU_OK;
+}
+int vgpu_debug_last_kernel_note(char* buf, size_t cap) {
+  if (!buf || cap == 0) return VGPU_ERR_INVALID;
+  strncpy(buf, fused_last_note().c_str(), cap - 1);
+  buf[cap - 1] = 0;
+  return VGPU_OK;
 }
 
 // ---- multi-GPU exchange over NCCL (dlopen'ed) -------------------------------------------------

@@ -1,0 +1,498 @@
+// Plan-specialised kernels: source generation.
+//
+// For one pipeline shape — the ABI program, the encodings / nullability of the bound columns, the
+// sink (FilterProject, ARRAY/GLOBAL group-by, HASH group-by) with its keys and accumulator cells —
+// gen_source() writes a straight-line CUDA kernel over the helpers of fused_prelude.cuh.  A warp
+// owns 128-row blocks; a thread owns rows 2*lane, 2*lane+1, 64+2*lane, 64+2*lane+1 of the block
+// (every column load is one fully coalesced 16- or 8-byte access per thread), evaluates the
+// expression tree in registers and folds the rows into
+//   * register accumulators (few groups: one predicated add per group and cell),
+//   * shared-memory tables with atomics (medium cardinality), or
+//   * the HBM open-addressing table (HASH sink).
+// fused_rt.cu compiles the text (prebuilt cubin from build(), else NVRTC) and launches it; the
+// micro-op interpreter of pipeline.cu runs every shape this generator declines.
+//
+// The scalar semantics come from the same functions as the interpreter's (arith, cast_value,
+// compare, and3/or3), called with compile-time opcodes so they fold to single instructions.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+
+#include "fused.h"
+
+namespace vg {
+
+namespace {
+
+struct Gen {
+  const PipelineParams& p;
+  const Program& prog;
+  std::string s;
+  FusedPlan& plan;
+  bool ok = true;
+  std::string why;
+
+  Gen(const PipelineParams& pp, FusedPlan& pl) : p(pp), prog(*pp.prog), plan(pl) {}
+
+  void out(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    s += buf;
+  }
+  void decline(const char* reason) { if (ok) { ok = false; why = reason; } }
+
+  static std::string hex(uint64_t v) {
+    char b[32];
+    snprintf(b, sizeof(b), "0x%llxull", (unsigned long long)v);
+    return b;
+  }
+
+  bool col_used[kMaxCols] = {false};
+  void mark(const vgpu_operand& o) { if (o.kind == VGPU_OPND_COL && o.index < kMaxCols) col_used[o.index] = true; }
+
+  // ---- operands ---------------------------------------------------------------------------
+  std::string val(const vgpu_operand& o, uint64_t imm) {
+    switch (o.kind) {
+      case VGPU_OPND_ACC: return "acc";
+      case VGPU_OPND_SLOT: return "s" + std::to_string(o.index);
+      case VGPU_OPND_COL: return "c" + std::to_string(o.index);
+      case VGPU_OPND_IMM: return "V{" + hex(imm) + ", false, false}";
+      default: return "V{0ull, true, false}";
+    }
+  }
+  std::string bval(const vgpu_operand& o, uint64_t imm) {
+    switch (o.kind) {
+      case VGPU_OPND_ACC: return "bacc";
+      case VGPU_OPND_SLOT: return "bs" + std::to_string(o.index);
+      case VGPU_OPND_COL: return "cb" + std::to_string(o.index);
+      case VGPU_OPND_IMM: return imm ? "B{true, false, false}" : "B{false, false, false}";
+      default: return "B{false, true, false}";
+    }
+  }
+
+  // ---- column loads -------------------------------------------------------------------------
+  // full: whole 128-row block (vector loads); else per-row guarded loads.
+  void gen_loads(bool full) {
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c]) continue;
+      const DevCol& d = p.cols[c];
+      if (d.encoding == VGPU_CONSTANT) continue;
+      const bool dict = d.encoding == VGPU_DICTIONARY;
+      const int lg = dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : 3));
+      const char* src = dict ? "indices" : "values";
+      if (d.nulls) {
+        if (full) out("    const u32 N%d = bits2(p.nulls[%d], r0) | (bits2(p.nulls[%d], r1) << 2);\n", c, c, c);
+        else out("    const u32 N%d = (r0 < n ? bits2(p.nulls[%d], r0) : 0u) | ((r1 < n ? bits2(p.nulls[%d], r1) : 0u) << 2);\n", c, c, c);
+      }
+      if (lg == -1) { // bit-packed BOOLEAN
+        if (full) out("    const u32 Q%d = bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) | (bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) << 2);\n", c, c, c);
+        else out("    const u32 Q%d = (r0 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u) | ((r1 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) : 0u) << 2);\n", c, c, c);
+        continue;
+      }
+      const bool real = !dict && d.type == VGPU_REAL;
+      if (full && lg == 3) {
+        out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 8), qb%d = ld16(p.%s[%d], r1 * 8);\n", c, src, c, c, src, c);
+        out("    const u64 Q%d[4] = {pack64(qa%d.x, qa%d.y), pack64(qa%d.z, qa%d.w), pack64(qb%d.x, qb%d.y), pack64(qb%d.z, qb%d.w)};\n", c, c, c, c, c, c, c, c, c);
+      } else if (full && lg == 2) {
+        out("    const uint2 qa%d = ld8(p.%s[%d], r0 * 4), qb%d = ld8(p.%s[%d], r1 * 4);\n", c, src, c, c, src, c);
+        if (real) out("    const u64 Q%d[4] = {d2u((double)__uint_as_float(qa%d.x)), d2u((double)__uint_as_float(qa%d.y)), d2u((double)__uint_as_float(qb%d.x)), d2u((double)__uint_as_float(qb%d.y))};\n", c, c, c, c, c);
+        else out("    const u64 Q%d[4] = {sext32(qa%d.x), sext32(qa%d.y), sext32(qb%d.x), sext32(qb%d.y)};\n", c, c, c, c, c);
+      } else {
+        const char* ty = lg == 0 ? "signed char" : lg == 1 ? "short" : lg == 2 ? (real ? "float" : "int") : "u64";
+        out("    u64 Q%d[4];\n", c);
+        out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
+        out("      const i64 r = (j < 2 ? r0 : r1) + (j & 1);\n");
+        if (real) out("      Q%d[j] = r < n ? d2u((double)reinterpret_cast<const float*>(p.%s[%d])[r]) : 0ull;\n", c, src, c);
+        else if (lg == 3) out("      Q%d[j] = r < n ? reinterpret_cast<const u64*>(p.%s[%d])[r] : 0ull;\n", c, src, c);
+        else out("      Q%d[j] = r < n ? (u64)(i64)reinterpret_cast<const %s*>(p.%s[%d])[r] : 0ull;\n", c, ty, src, c);
+        out("    }\n");
+      }
+    }
+  }
+
+  // Per-row decoded column values (inside the row loop).
+  void gen_row_columns() {
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c]) continue;
+      const DevCol& d = p.cols[c];
+      const bool is_bool = d.type == VGPU_BOOLEAN;
+      if (d.encoding == VGPU_CONSTANT) {
+        if (is_bool) out("      const B cb%d = {%s, %s, false};\n", c, d.constant ? "true" : "false", d.const_null ? "true" : "false");
+        else out("      const V c%d = {%s, %s, false};\n", c, hex((uint64_t)d.constant).c_str(), d.const_null ? "true" : "false");
+        continue;
+      }
+      std::string nn = d.nulls ? "!((N" + std::to_string(c) + " >> j) & 1u)" : "false";
+      if (d.encoding == VGPU_DICTIONARY) {
+        out("      V c%d_; bool cv%d_ = false; {\n", c, c);
+        out("        bool isn = %s; u64 raw = 0;\n", nn.c_str());
+        out("        if (valid && !isn) {\n          const i64 ix = (i64)Q%d[j];\n", c);
+        if (is_bool) out("          cv%d_ = bit1(reinterpret_cast<const u64*>(p.values[%d]), ix);\n", c, c);
+        else {
+          const char* ty = d.type == VGPU_TINYINT ? "signed char" : d.type == VGPU_SMALLINT ? "short" : d.type == VGPU_INTEGER ? "int" : d.type == VGPU_REAL ? "float" : "u64";
+          if (d.type == VGPU_REAL) out("          raw = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + ix));\n", c);
+          else if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) out("          raw = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + ix);\n", c);
+          else out("          raw = (u64)(i64)__ldg(reinterpret_cast<const %s*>(p.values[%d]) + ix);\n", ty, c);
+        }
+        if (d.base_nulls) out("          if (!bit1(p.base_nulls[%d], ix)) isn = true;\n", c);
+        out("        }\n        c%d_ = V{raw, isn, false};\n      }\n", c);
+        if (is_bool) out("      const B cb%d = {cv%d_ && !c%d_.n, c%d_.n, false};\n", c, c, c, c);
+        else out("      const V c%d = c%d_;\n", c, c);
+        continue;
+      }
+      if (is_bool) out("      const B cb%d = {(bool)((Q%d >> j) & 1u), %s, false};\n", c, c, nn.c_str());
+      else out("      const V c%d = {Q%d[j], %s, false};\n", c, c, nn.c_str());
+    }
+  }
+
+  // ---- the ABI ops, one row --------------------------------------------------------------------
+  void gen_ops() {
+    for (int k = 0; k < p.n_slots; ++k) out("      V s%d = {0ull, false, false};\n", k);
+    for (int k = 0; k < p.n_bslots; ++k) out("      B bs%d = {false, false, false};\n", k);
+    out("      V acc = {0ull, false, false}; B bacc = {false, false, false};\n");
+    for (const vgpu_op& op : prog.ops) {
+      const int oc = op.opcode;
+      const uint64_t imm = (uint64_t)op.imm.i, imm2 = (uint64_t)op.imm2.i;
+      out("      {\n");
+      if ((oc >= VGPU_OP_ADD && oc <= VGPU_OP_MOD)) {
+        out("        const V a = %s;\n", val(op.a, imm).c_str());
+        if (oc == VGPU_OP_NEG) out("        const V b = {0ull, false, false};\n");
+        else out("        const V b = %s;\n", val(op.b, imm).c_str());
+        out("        V r; r.n = a.n || b.n; r.e = a.e || b.e;\n");
+        out("        const u32 er = arith(%d, %d, a.v, b.v, r.v);\n", oc, op.type);
+        out("        if (er && !r.n && valid) { r.e = true; ec |= er; }\n");
+        out("        acc = r;\n");
+        if (op.dst_slot >= 0) out("        s%d = r;\n", op.dst_slot);
+      } else if (oc == VGPU_OP_CAST) {
+        out("        const V a = %s;\n", val(op.a, imm).c_str());
+        out("        V r; r.n = a.n; r.e = a.e;\n");
+        out("        const u32 er = cast_value(%d, %d, a.v, r.v);\n", op.a.type, op.type);
+        out("        if (er && !r.n && valid) { r.e = true; ec |= er; }\n");
+        out("        acc = r;\n");
+        if (op.dst_slot >= 0) out("        s%d = r;\n", op.dst_slot);
+      } else if (oc == VGPU_OP_MOV) {
+        out("        acc = %s;\n", val(op.a, imm).c_str());
+        if (op.dst_slot >= 0) out("        s%d = acc;\n", op.dst_slot);
+      } else if (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) {
+        if (op.type == VGPU_BOOLEAN) {
+          out("        const B a = %s, b = %s;\n", bval(op.a, imm).c_str(), bval(op.b, imm).c_str());
+          out("        B r; r.n = a.n || b.n; r.e = a.e || b.e; r.v = (a.v %s b.v) && !r.n;\n", oc == VGPU_OP_EQ ? "==" : "!=");
+        } else if (oc == VGPU_OP_BETWEEN) {
+          out("        const V a = %s, b = %s, c = %s;\n", val(op.a, imm).c_str(), val(op.b, imm).c_str(), val(op.c, imm2).c_str());
+          out("        B r; r.n = a.n || b.n || c.n; r.e = a.e || b.e || c.e;\n");
+          out("        r.v = compare(%d, %d, a.v, b.v) && compare(%d, %d, a.v, c.v) && !r.n;\n", VGPU_OP_GE, op.type, VGPU_OP_LE, op.type);
+        } else {
+          out("        const V a = %s, b = %s;\n", val(op.a, imm).c_str(), val(op.b, imm).c_str());
+          out("        B r; r.n = a.n || b.n; r.e = a.e || b.e; r.v = compare(%d, %d, a.v, b.v) && !r.n;\n", oc, op.type);
+        }
+        out("        bacc = r;\n");
+        if (op.dst_slot >= 0) out("        bs%d = r;\n", op.dst_slot);
+      } else {
+        if (oc == VGPU_OP_IS_NULL) {
+          if (op.a.type == VGPU_BOOLEAN) out("        const B a = %s; B r = {a.n, false, a.e};\n", bval(op.a, imm).c_str());
+          else out("        const V a = %s; B r = {a.n, false, a.e};\n", val(op.a, imm).c_str());
+        } else if (oc == VGPU_OP_NOT) {
+          out("        const B a = %s; B r = {!a.v, a.n, a.e};\n", bval(op.a, imm).c_str());
+        } else {
+          out("        const B r = %s(%s, %s);\n", oc == VGPU_OP_AND ? "and3" : "or3", bval(op.a, imm).c_str(), bval(op.b, imm).c_str());
+        }
+        out("        bacc = r;\n");
+        if (op.dst_slot >= 0) out("        bs%d = r;\n", op.dst_slot);
+      }
+      out("      }\n");
+    }
+  }
+
+  void gen_filter() {
+    out("      bool pass = valid, raise = false;\n");
+    if (prog.filter.kind != VGPU_OPND_NONE) {
+      out("      { const B f = %s; raise = valid && f.e; pass = valid && f.v && !f.n && !f.e; }\n", bval(prog.filter, 1).c_str());
+    }
+  }
+
+  std::string out_val(int idx) {
+    const vgpu_operand& o = p.outputs[idx];
+    if (o.kind == VGPU_OPND_IMM || o.kind == VGPU_OPND_ACC) decline("output operand kind");
+    if (o.type == VGPU_BOOLEAN) return "";
+    return val(o, 0);
+  }
+
+  // Group number (ARRAY) or normalized key (HASH) of the row.
+  void gen_keys(bool hash) {
+    if (hash) out("      u64 key = 0; bool knull = false;\n"); else out("      u32 g = 0;\n");
+    for (int k = 0; k < p.n_keys; ++k) {
+      const DevKey& ks = p.keys[k];
+      const vgpu_operand& o = p.outputs[ks.output];
+      if (o.type == VGPU_BOOLEAN) { decline("boolean grouping key"); return; }
+      out("      { const V k = %s; raise = raise || (pass && k.e);\n", out_val(ks.output).c_str());
+      if (p.ignore_null_keys) out("        pass = pass && !k.n;\n");
+      if (hash && ks.bits == 64) {
+        out("        key = k.v; knull = k.n; }\n");
+        continue;
+      }
+      out("        const u64 u = k.v - %s;\n", hex((uint64_t)ks.min).c_str());
+      out("        const bool bad = k.n ? %s : u > %s;\n", ks.nullable ? "false" : "true", hex((uint64_t)(ks.max - ks.min)).c_str());
+      out("        const u32 id = k.n ? 0u : (u32)u + %uu;\n", ks.nullable ? 1u : 0u);
+      if (hash) out("        key += (u64)id << %d;\n", (int)ks.shift);
+      else out("        g += id * %uu;\n", (unsigned)ks.mult);
+      out("        if (bad && pass) { ec |= VGF_ERR_KEYRANGE; raise = true; pass = false; } }\n");
+    }
+  }
+
+  // Value and liveness of cell `c` for the row: declares x<c> (u64) and l<c> (bool).
+  void gen_cell_input(int c) {
+    const DevCell& cell = p.cells[c];
+    if (cell.input < 0) {
+      out("      const u64 x%d = 1ull; const bool l%d = pass;\n", c, c);
+      return;
+    }
+    const vgpu_operand& o = p.outputs[cell.input];
+    if (o.type == VGPU_BOOLEAN) {
+      out("      const B xb%d = %s; raise = raise || (pass && xb%d.e);\n", c, bval(o, 0).c_str(), c);
+      out("      const u64 x%d = %s; const bool l%d = pass && !xb%d.n;\n", c, cell.kind == kCellCount ? "1ull" : ("(u64)xb" + std::to_string(c) + ".v").c_str(), c, c);
+      return;
+    }
+    out("      const V xv%d = %s; raise = raise || (pass && xv%d.e);\n", c, out_val(cell.input).c_str(), c);
+    std::string x = "xv" + std::to_string(c) + ".v";
+    const bool fp_in = o.type == VGPU_REAL || o.type == VGPU_DOUBLE;
+    if (cell.kind == kCellCount) x = "1ull";
+    else if (cell.kind == kCellSumF64 && !fp_in) x = "d2u((double)(i64)" + x + ")";
+    std::string live = "pass && !xv" + std::to_string(c) + ".n";
+    if (cell.kind == kCellMinF64 || cell.kind == kCellMaxF64) live += " && (u2d(" + x + ") == u2d(" + x + "))";
+    out("      const u64 x%d = %s; const bool l%d = %s;\n", c, x.c_str(), c, live.c_str());
+  }
+
+  void gen_raise() {
+    out("      if (raise) atomicOr(p.err_word, ec ? ec : VGF_ERR_OVERFLOW);\n");
+  }
+
+  // ---- whole kernels ----------------------------------------------------------------------------
+  void gen_block_header(bool full) {
+    out("    const i64 r0 = blk * 128 + 2 * lane, r1 = r0 + 64;\n");
+    gen_loads(full);
+  }
+  void gen_row_begin(bool full) {
+    out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
+    if (full) out("      const bool valid = true;\n");
+    else out("      const bool valid = ((j < 2 ? r0 : r1) + (j & 1)) < n;\n");
+    out("      u32 ec = 0;\n");
+    gen_row_columns();
+    gen_ops();
+    gen_filter();
+  }
+
+  int live_cells[kMaxCells];
+  int n_live = 0;
+
+  void gen_array_body(bool full, bool regs, int G) {
+    gen_block_header(full);
+    gen_row_begin(full);
+    gen_keys(false);
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      gen_cell_input(c);
+      if (regs) {
+        if (p.cells[c].kind == kCellCount) out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] += 1u;\n", G, c, c);
+        else out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] = cell_comb<%d>(A%d[gg], x%d, accerr);\n", G, c, c, p.cells[c].kind, c, c);
+      } else {
+        if (p.cells[c].kind == kCellCount) out("      if (l%d) atomicAdd(reinterpret_cast<u32*>(mytab + %d * %d + g), 1u);\n", c, i, G);
+        else out("      if (l%d) smem_update<%d>(mytab + %d * %d + g, x%d, accerr);\n", c, p.cells[c].kind, i, G, c);
+      }
+    }
+    gen_raise();
+    out("    }\n");
+  }
+
+  void gen_hash_body(bool full) {
+    gen_block_header(full);
+    out("    u64 KEY[4]; bool KN[4], PASS[4];\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 X%d[4]; bool L%d[4];\n", live_cells[i], live_cells[i]);
+    gen_row_begin(full);
+    gen_keys(true);
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      gen_cell_input(c);
+      out("      X%d[j] = x%d; L%d[j] = l%d;\n", c, c, c, c);
+    }
+    out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
+    gen_raise();
+    out("    }\n");
+    // adjacent rows of a pair share the probe when their keys are equal (sorted / clustered keys)
+    out("    _Pragma(\"unroll\") for (int pr = 0; pr < 2; ++pr) {\n");
+    out("      const int j0 = 2 * pr, j1 = j0 + 1;\n");
+    out("      const bool same = PASS[j0] && PASS[j1] && KEY[j0] == KEY[j1] && KN[j0] == KN[j1];\n");
+    out("      i64 sl0 = -1, sl1 = -1;\n");
+    out("      if (PASS[j0]) sl0 = hash_find_or_insert<%d>(p, KEY[j0], KN[j0], accerr);\n", p.row_words);
+    out("      if (same) sl1 = sl0; else if (PASS[j1]) sl1 = hash_find_or_insert<%d>(p, KEY[j1], KN[j1], accerr);\n", p.row_words);
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      const int kind = p.cells[c].kind;
+      out("      {\n        const bool a0 = L%d[j0] && sl0 >= 0, a1 = L%d[j1] && sl1 >= 0;\n", c, c);
+      out("        if (same && a0 && a1) hbm_update<%d>(p.table + sl0 * %d + %d, cell_comb<%d>(X%d[j0], X%d[j1], accerr), accerr);\n", kind, p.row_words, 1 + c, kind, c, c);
+      out("        else {\n          if (a0) hbm_update<%d>(p.table + sl0 * %d + %d, X%d[j0], accerr);\n", kind, p.row_words, 1 + c, c);
+      out("          if (a1) hbm_update<%d>(p.table + sl1 * %d + %d, X%d[j1], accerr);\n        }\n      }\n", kind, p.row_words, 1 + c, c);
+    }
+    out("    }\n");
+  }
+
+  void gen_fp_body(bool full) {
+    gen_block_header(full);
+    out("    bool PASS[4];\n");
+    for (int k = 0; k < p.n_outputs; ++k) {
+      if (!p.outs[k].values) continue;
+      out("    u64 O%d[4]; bool ON%d[4];\n", k, k);
+    }
+    gen_row_begin(full);
+    for (int k = 0; k < p.n_outputs; ++k) {
+      if (!p.outs[k].values) continue;
+      const vgpu_operand& o = p.outputs[k];
+      if (o.kind == VGPU_OPND_IMM || o.kind == VGPU_OPND_ACC) decline("output operand kind");
+      if (o.type == VGPU_BOOLEAN) out("      { const B o = %s; raise = raise || (pass && o.e); O%d[j] = o.v; ON%d[j] = o.n; }\n", bval(o, 0).c_str(), k, k);
+      else out("      { const V o = %s; raise = raise || (pass && o.e); O%d[j] = o.v; ON%d[j] = o.n; }\n", val(o, 0).c_str(), k, k);
+    }
+    out("      PASS[j] = pass;\n");
+    gen_raise();
+    out("    }\n");
+    if (full) out("    const int nw = 4;\n");
+    else out("    const int nw = (int)((n - blk * 128 + 31) >> 5);\n");
+    out("    store_block_bits(p.sel_words, blk * 4, nw, PASS);\n");
+    out("    { int cnt = (int)PASS[0] + (int)PASS[1] + (int)PASS[2] + (int)PASS[3];\n");
+    out("      _Pragma(\"unroll\") for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);\n");
+    out("      if (lane == 0 && cnt) atomicAdd(&p.tile_counts[blk >> 3], cnt); }\n");
+    for (int k = 0; k < p.n_outputs; ++k) {
+      if (!p.outs[k].values) continue;
+      const vgpu_operand& o = p.outputs[k];
+      const int t = o.type;
+      if (t == VGPU_BOOLEAN) {
+        out("    { bool m[4] = {O%d[0] != 0, O%d[1] != 0, O%d[2] != 0, O%d[3] != 0}; store_block_bits(reinterpret_cast<u32*>(p.out_values[%d]), blk * 4, nw, m); }\n", k, k, k, k, k);
+      } else {
+        if (t == VGPU_REAL) out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) O%d[j] = __float_as_uint((float)u2d(O%d[j]));\n", k, k);
+        const int lg = t == VGPU_TINYINT ? 0 : t == VGPU_SMALLINT ? 1 : (t == VGPU_INTEGER || t == VGPU_REAL) ? 2 : 3;
+        if (full && lg == 3) {
+          out("    { uint4* d = reinterpret_cast<uint4*>(p.out_values[%d]);\n", k);
+          out("      d[r0 >> 1] = make_uint4((u32)O%d[0], (u32)(O%d[0] >> 32), (u32)O%d[1], (u32)(O%d[1] >> 32));\n", k, k, k, k);
+          out("      d[r1 >> 1] = make_uint4((u32)O%d[2], (u32)(O%d[2] >> 32), (u32)O%d[3], (u32)(O%d[3] >> 32)); }\n", k, k, k, k);
+        } else if (full && lg == 2) {
+          out("    { uint2* d = reinterpret_cast<uint2*>(p.out_values[%d]);\n", k);
+          out("      d[r0 >> 1] = make_uint2((u32)O%d[0], (u32)O%d[1]); d[r1 >> 1] = make_uint2((u32)O%d[2], (u32)O%d[3]); }\n", k, k, k, k);
+        } else {
+          const char* ty = lg == 0 ? "unsigned char" : lg == 1 ? "unsigned short" : lg == 2 ? "u32" : "u64";
+          out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) { const i64 r = (j < 2 ? r0 : r1) + (j & 1); if (r < n) reinterpret_cast<%s*>(p.out_values[%d])[r] = (%s)O%d[j]; }\n", ty, k, ty, k);
+        }
+      }
+      if (p.outs[k].nulls) {
+        out("    { bool m[4]; _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) m[j] = !ON%d[j] && (((j < 2 ? r0 : r1) + (j & 1)) < n);\n", k);
+        out("      store_block_bits(reinterpret_cast<u32*>(p.out_nulls[%d]), blk * 4, nw, m); }\n", k);
+      }
+    }
+  }
+
+  void generate() {
+    for (const auto& op : prog.ops) { mark(op.a); mark(op.b); mark(op.c); }
+    for (const auto& o : prog.outputs) mark(o);
+    mark(prog.filter);
+    if (p.in_rows) { decline("row indirection"); return; }
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c] || p.cols[c].encoding == VGPU_CONSTANT) continue;
+      const DevCol& d = p.cols[c];
+      const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
+      if ((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) { decline("unaligned column"); return; }
+      if (d.nulls && (reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) { decline("unaligned nulls"); return; }
+    }
+    n_live = 0;
+    for (int c = 0; c < p.n_cells; ++c) if (!p.cells[c].skip) live_cells[n_live++] = c;
+
+    const int G = p.n_groups;
+    bool regs = false;
+    int copies = 1;
+    if (p.mode == kSinkArray) regs = (int64_t)G * n_live <= 48;
+    // Registers the body needs: the 4 rows of every staged column, the accumulators (register
+    // path), addressing.  Pick the widest CTA shape whose per-thread budget covers it.
+    int need = 30;
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c] || p.cols[c].encoding == VGPU_CONSTANT) continue;
+      const DevCol& d = p.cols[c];
+      need += (d.encoding == VGPU_DICTIONARY || d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 4 : (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) ? 8 : 2;
+      if (d.encoding == VGPU_DICTIONARY) need += 4;
+    }
+    if (regs) for (int i = 0; i < n_live; ++i) need += (p.cells[live_cells[i]].kind == kCellCount ? 1 : 2) * G;
+    if (p.mode == kSinkHash) need += 8 + 3 * n_live * 4;
+    static const int shapes[][2] = {{512, 2}, {384, 2}, {512, 1}, {384, 1}, {256, 1}};
+    int NT = 256, CTAS = 1;
+    for (const auto& sh : shapes) {
+      const int budget = std::min(255, (65536 / (sh[0] * sh[1])) & ~7);
+      if (budget >= need) { NT = sh[0]; CTAS = sh[1]; break; }
+    }
+    plan.threads = NT;
+    plan.smem_bytes = 0;
+    out("#define NT %d\n", NT);
+    out("using namespace vgf;\n");
+    if (p.mode == kSinkArray && !regs) {
+      const int64_t one = (int64_t)G * n_live * 8;
+      const int64_t limit = 200 * 1024 / CTAS;
+      if (one > limit) { decline("group table exceeds shared memory"); return; }
+      copies = one * (NT / 32) <= limit ? NT / 32 : 1;
+      plan.smem_bytes = (int)(one * copies);
+    }
+    out("extern \"C\" __global__ void __launch_bounds__(NT, %d) vgpu_fused(const FusedParams p) {\n", CTAS);
+    out("  const int lane = threadIdx.x & 31;\n  const i64 n = p.n_rows;\n");
+    out("  const i64 n_blocks = (n + 127) >> 7, n_full = n >> 7;\n");
+    out("  const i64 wid = (i64)blockIdx.x * (NT / 32) + (threadIdx.x >> 5), nwarps = (i64)gridDim.x * (NT / 32);\n");
+    out("  u32 accerr = 0;\n");
+    if (p.mode == kSinkArray) {
+      if (regs) {
+        for (int i = 0; i < n_live; ++i) {
+          const int c = live_cells[i];
+          if (p.cells[c].kind == kCellCount) out("  u32 A%d[%d];\n  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) A%d[gg] = 0u;\n", c, G, G, c);
+          else out("  u64 A%d[%d];\n  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) A%d[gg] = cell_identity<%d>();\n", c, G, G, c, p.cells[c].kind);
+        }
+      } else {
+        out("  extern __shared__ __align__(16) u64 tab[];\n");
+        out("  for (int i = threadIdx.x; i < %d; i += NT) {\n    const int ci = (i / %d) %% %d;\n    u64 idv = 0;\n", copies * n_live * G, G, n_live);
+        for (int i = 0; i < n_live; ++i) out("    if (ci == %d) idv = cell_identity<%d>();\n", i, p.cells[live_cells[i]].kind);
+        out("    tab[i] = idv;\n  }\n  __syncthreads();\n");
+        if (copies > 1) out("  u64* mytab = tab + (threadIdx.x >> 5) * %d;\n", n_live * G);
+        else out("  u64* mytab = tab;\n");
+      }
+    }
+    out("  for (i64 blk = wid; blk < n_blocks; blk += nwarps) {\n   if (blk < n_full) {\n");
+    if (p.mode == kSinkArray) gen_array_body(true, regs, G); else if (p.mode == kSinkHash) gen_hash_body(true); else gen_fp_body(true);
+    out("   } else {\n");
+    if (p.mode == kSinkArray) gen_array_body(false, regs, G); else if (p.mode == kSinkHash) gen_hash_body(false); else gen_fp_body(false);
+    out("   }\n  }\n");
+    if (p.mode == kSinkArray) {
+      if (regs) {
+        out("  __shared__ u64 scratch[NT / 32];\n");
+        for (int i = 0; i < n_live; ++i) {
+          const int c = live_cells[i];
+          out("  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) block_fold<%d, NT / 32>((u64)A%d[gg], scratch, p.partials + ((size_t)blockIdx.x * %d + %d) * %d + gg, accerr);\n", G, p.cells[c].kind, c, p.n_cells, c, G);
+        }
+      } else {
+        out("  __syncthreads();\n  for (int i = threadIdx.x; i < %d; i += NT) {\n    const int ci = i / %d, gg = i - ci * %d;\n    u64 acc = tab[i];\n", n_live * G, G, G);
+        out("    for (int k = 1; k < %d; ++k) {\n      const u64 v = tab[k * %d + i];\n", copies, n_live * G);
+        for (int i = 0; i < n_live; ++i) out("      if (ci == %d) acc = cell_comb<%d>(acc, v, accerr);\n", i, p.cells[live_cells[i]].kind);
+        out("    }\n    int c = 0;\n");
+        for (int i = 0; i < n_live; ++i) out("    if (ci == %d) c = %d;\n", i, live_cells[i]);
+        out("    p.partials[((size_t)blockIdx.x * %d + c) * %d + gg] = acc;\n  }\n", p.n_cells, G);
+      }
+    }
+    out("  if (accerr) atomicOr(p.err_word, accerr);\n}\n");
+  }
+};
+
+} // namespace
+
+bool fused_gen_source(const PipelineParams& p, FusedPlan& plan, std::string& source, std::string& why) {
+  Gen g(p, plan);
+  g.generate();
+  if (!g.ok) { why = g.why; return false; }
+  source.swap(g.s);
+  return true;
+}
+
+} // namespace vg

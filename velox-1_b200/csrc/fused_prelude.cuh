@@ -1,0 +1,397 @@
+// Prelude of the plan-specialised ("fused") kernels.  fused.cpp generates, per pipeline shape, a
+// straight-line kernel body over these helpers and compiles it for sm_100a — ahead of time with
+// nvcc for the shapes listed in velox-1_b200/aot_plans.py, or at first use with NVRTC — so the
+// expression tree, the column encodings, the key layout and the accumulator list are compile-time
+// facts of the kernel.  Self-contained: no #include, so the same text compiles under nvcc and
+// NVRTC.  Scalar semantics are the interpreter's (pipeline.cu), restating the reference:
+//   velox/functions/prestosql/{Arithmetic.h:45-86,Comparisons.h:43-185},
+//   velox/common/base/CheckedArithmetic.h, velox/type/Conversions.h:176-374,
+//   velox/expression/ConjunctExpr.cpp:24-174, velox/exec/OperatorUtils.cpp:187-210.
+#ifndef VGPU_FUSED_PRELUDE_CUH_
+#define VGPU_FUSED_PRELUDE_CUH_
+
+namespace vgf {
+
+typedef unsigned long long u64;
+typedef long long i64;
+typedef unsigned int u32;
+typedef int i32;
+
+// vgpu_type (include/vgpu.h)
+#define VGF_BOOLEAN 0
+#define VGF_TINYINT 1
+#define VGF_SMALLINT 2
+#define VGF_INTEGER 3
+#define VGF_BIGINT 4
+#define VGF_REAL 5
+#define VGF_DOUBLE 6
+// vgpu_opcode
+#define VGF_ADD 1
+#define VGF_SUB 2
+#define VGF_MUL 3
+#define VGF_DIV 4
+#define VGF_NEG 5
+#define VGF_MOD 6
+#define VGF_EQ 16
+#define VGF_NE 17
+#define VGF_LT 18
+#define VGF_LE 19
+#define VGF_GT 20
+#define VGF_GE 21
+// error bits (internal.h)
+#define VGF_ERR_OVERFLOW 1u
+#define VGF_ERR_DIVZERO 2u
+#define VGF_ERR_CAST 4u
+#define VGF_ERR_KEYRANGE 8u
+#define VGF_ERR_TABLEFULL 16u
+// CellKind (internal.h)
+#define VGF_SUMF64 0
+#define VGF_SUMI64 1
+#define VGF_COUNT 2
+#define VGF_MINI64 3
+#define VGF_MAXI64 4
+#define VGF_MINF64 5
+#define VGF_MAXF64 6
+
+#define VGF_I64_MIN (-9223372036854775807ll - 1ll)
+#define VGF_I64_MAX 9223372036854775807ll
+#define VGF_EMPTY_KEY 0xffffffffffffffffull
+
+struct FusedParams {
+  const void* values[16];
+  const i32* indices[16];
+  const u64* nulls[16];
+  const u64* base_nulls[16];
+  i64 n_rows;
+  u32* err_word;
+  // ARRAY / GLOBAL sink: per-CTA partials [gridDim][n_cells][n_groups]
+  u64* partials;
+  // HASH sink
+  u64* table;
+  u64 cap_mask;
+  u64* n_groups_ctr;
+  // FilterProject sink
+  u32* sel_words;
+  i32* tile_counts;
+  void* out_values[24];
+  u64* out_nulls[24];
+};
+
+__device__ __forceinline__ u64 d2u(double d) { return (u64)__double_as_longlong(d); }
+__device__ __forceinline__ double u2d(u64 u) { return __longlong_as_double((i64)u); }
+__device__ __forceinline__ u64 pack64(u32 lo, u32 hi) { return (u64)lo | ((u64)hi << 32); }
+__device__ __forceinline__ u64 sext32(u32 x) { return (u64)(i64)(i32)x; }
+
+// ---- loads (streaming: every input byte is read once) -------------------------------------------
+__device__ __forceinline__ uint4 ld16(const void* base, i64 byte_off) {
+  return __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(base) + byte_off));
+}
+__device__ __forceinline__ uint2 ld8(const void* base, i64 byte_off) {
+  return __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(base) + byte_off));
+}
+// rows r, r+1 of a bitmap (r even): 2 bits
+__device__ __forceinline__ u32 bits2(const u64* bits, i64 r) {
+  const u32 w = __ldg(reinterpret_cast<const u32*>(bits) + (r >> 5));
+  return (w >> (r & 31)) & 3u;
+}
+__device__ __forceinline__ bool bit1(const u64* bits, i64 i) {
+  return (__ldg(bits + (i >> 6)) >> (i & 63)) & 1ull;
+}
+
+// ---- scalar semantics -----------------------------------------------------------------------
+__device__ __forceinline__ bool is_fp(int t) { return t == VGF_REAL || t == VGF_DOUBLE; }
+__device__ __forceinline__ void int_limits(int type, i64& lo, i64& hi) {
+  switch (type) {
+    case VGF_TINYINT: lo = -128; hi = 127; break;
+    case VGF_SMALLINT: lo = -32768; hi = 32767; break;
+    case VGF_INTEGER: lo = -2147483648ll; hi = 2147483647ll; break;
+    default: lo = VGF_I64_MIN; hi = VGF_I64_MAX;
+  }
+}
+// REAL arithmetic is done in double and rounded back to float: for + - * / the double-rounded
+// result equals the float operation (53 >= 2*24+2 bits).
+__device__ __forceinline__ double fp_round(int type, double x) {
+  return type == VGF_REAL ? (double)__double2float_rn(x) : x;
+}
+
+// Returns error bits (0 = fine).  Integer ops are the checked ones; FP ops never raise.
+__device__ __forceinline__ u32 arith(int opcode, int type, u64 a, u64 b, u64& r) {
+  if (is_fp(type)) {
+    const double x = u2d(a), y = u2d(b);
+    double z;
+    switch (opcode) {
+      case VGF_ADD: z = __dadd_rn(x, y); break;
+      case VGF_SUB: z = __dsub_rn(x, y); break;
+      case VGF_MUL: z = __dmul_rn(x, y); break;
+      case VGF_DIV: z = __ddiv_rn(x, y); break;
+      case VGF_NEG: z = -x; break;
+      default: z = (y == 0.0) ? __longlong_as_double(0x7ff8000000000000ll) : fmod(x, y);
+    }
+    r = d2u(fp_round(type, z));
+    return 0;
+  }
+  const i64 x = (i64)a, y = (i64)b;
+  i64 lo, hi;
+  int_limits(type, lo, hi);
+  i64 z = 0;
+  u32 err = 0;
+  switch (opcode) {
+    case VGF_ADD:
+      z = (i64)((u64)x + (u64)y);
+      if (((x ^ z) & (y ^ z)) < 0) err = VGF_ERR_OVERFLOW;
+      break;
+    case VGF_SUB:
+      z = (i64)((u64)x - (u64)y);
+      if (((x ^ y) & (x ^ z)) < 0) err = VGF_ERR_OVERFLOW;
+      break;
+    case VGF_MUL: {
+      z = (i64)((u64)x * (u64)y);
+      const i64 h = __mul64hi(x, y);
+      if (h != (z >> 63)) err = VGF_ERR_OVERFLOW;
+      break;
+    }
+    case VGF_DIV:
+      if (y == 0) err = VGF_ERR_DIVZERO;
+      else if (x == lo && y == -1) err = VGF_ERR_OVERFLOW;
+      else z = x / y;
+      break;
+    case VGF_NEG:
+      if (x == lo) err = VGF_ERR_OVERFLOW; else z = -x;
+      break;
+    default:
+      if (y == 0) err = VGF_ERR_DIVZERO; else z = (y == -1) ? 0 : x % y;
+  }
+  if (!err && (z < lo || z > hi)) err = VGF_ERR_OVERFLOW;
+  r = (u64)z;
+  return err;
+}
+
+// CAST from -> to (non-truncating flavour: FP -> integer rounds half away from zero, range-checks).
+__device__ __forceinline__ u32 cast_value(int from, int to, u64 a, u64& r) {
+  r = 0;
+  if (is_fp(from)) {
+    const double x = u2d(a);
+    if (is_fp(to)) { r = d2u(fp_round(to, x)); return 0; }
+    if (x != x) return VGF_ERR_CAST;
+    const double y = round(x);
+    i64 lo, hi;
+    int_limits(to, lo, hi);
+    if (!(y >= -9223372036854775808.0 && y < 9223372036854775808.0)) return VGF_ERR_CAST;
+    const i64 z = (i64)y;
+    if (z < lo || z > hi) return VGF_ERR_CAST;
+    r = (u64)z;
+    return 0;
+  }
+  const i64 x = (i64)a;
+  if (is_fp(to)) { r = d2u(to == VGF_REAL ? (double)(float)x : (double)x); return 0; }
+  i64 lo, hi;
+  int_limits(to, lo, hi);
+  if (x < lo || x > hi) return VGF_ERR_CAST;
+  r = a;
+  return 0;
+}
+
+__device__ __forceinline__ bool compare(int opcode, int type, u64 a, u64 b) {
+  if (is_fp(type)) {
+    const double x = u2d(a), y = u2d(b);
+    switch (opcode) {
+      case VGF_EQ: return x == y;
+      case VGF_NE: return x != y;
+      case VGF_LT: return x < y;
+      case VGF_LE: return x <= y;
+      case VGF_GT: return x > y;
+      default: return x >= y;
+    }
+  }
+  const i64 x = (i64)a, y = (i64)b;
+  switch (opcode) {
+    case VGF_EQ: return x == y;
+    case VGF_NE: return x != y;
+    case VGF_LT: return x < y;
+    case VGF_LE: return x <= y;
+    case VGF_GT: return x > y;
+    default: return x >= y;
+  }
+}
+
+// A value / boolean of one row with its NULL and latched-error flags.
+struct V { u64 v; bool n, e; };
+struct B { bool v, n, e; };
+
+// SQL three-valued AND / OR; an error or NULL on one side is dropped when the other side decides.
+__device__ __forceinline__ B and3(const B a, const B b) {
+  const bool okA = !a.n && !a.e, okB = !b.n && !b.e;
+  const bool decided = (okA && !a.v) || (okB && !b.v);
+  B r;
+  r.v = okA && a.v && okB && b.v;
+  r.e = !decided && (a.e || b.e);
+  r.n = !decided && !r.e && (a.n || b.n);
+  return r;
+}
+__device__ __forceinline__ B or3(const B a, const B b) {
+  const bool okA = !a.n && !a.e, okB = !b.n && !b.e;
+  const bool decided = (okA && a.v) || (okB && b.v);
+  B r;
+  r.v = decided;
+  r.e = !decided && (a.e || b.e);
+  r.n = !decided && !r.e && (a.n || b.n);
+  return r;
+}
+
+__device__ __forceinline__ u32 interleave16(u32 even, u32 odd) {
+  u32 x = (even & 0xffffu) | (odd << 16);
+  u32 t;
+  t = (x ^ (x >> 8)) & 0x0000ff00u; x ^= t ^ (t << 8);
+  t = (x ^ (x >> 4)) & 0x00f000f0u; x ^= t ^ (t << 4);
+  t = (x ^ (x >> 2)) & 0x0c0c0c0cu; x ^= t ^ (t << 2);
+  t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
+  return x;
+}
+// Bits of the warp's 128-row block (4 words) from the per-thread flags m[0..3] in pair layout
+// (thread rows: 2*lane, 2*lane+1, 64+2*lane, 64+2*lane+1).  n_words = words of the block that
+// exist, rounded up to an even count so whole 64-bit words are written.
+__device__ __forceinline__ void store_block_bits(u32* dst, i64 word_base, int n_words, const bool m[4]) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int pr = 0; pr < 2; ++pr) {
+    const u32 even = __ballot_sync(0xffffffffu, m[2 * pr]);
+    const u32 odd = __ballot_sync(0xffffffffu, m[2 * pr + 1]);
+    if ((lane & 15) == 0) {
+      const int h = lane >> 4;
+      const int w = pr * 2 + h;
+      if (w < ((n_words + 1) & ~1)) dst[word_base + w] = interleave16(even >> (16 * h), odd >> (16 * h));
+    }
+  }
+}
+
+// ---- accumulator cells --------------------------------------------------------------------------
+template <int KIND>
+__device__ __forceinline__ u64 cell_identity() {
+  if (KIND == VGF_MINI64) return (u64)VGF_I64_MAX;
+  if (KIND == VGF_MAXI64) return (u64)VGF_I64_MIN;
+  if (KIND == VGF_MINF64) return 0x7fefffffffffffffull;
+  if (KIND == VGF_MAXF64) return 0xffefffffffffffffull;
+  return 0;
+}
+template <int KIND>
+__device__ __forceinline__ u64 cell_comb(u64 a, u64 b, u32& err) {
+  if (KIND == VGF_SUMF64) return d2u(__dadd_rn(u2d(a), u2d(b)));
+  if (KIND == VGF_SUMI64) {
+    const i64 x = (i64)a, y = (i64)b, z = (i64)(a + b);
+    if (((x ^ z) & (y ^ z)) < 0) err |= VGF_ERR_OVERFLOW;
+    return (u64)z;
+  }
+  if (KIND == VGF_COUNT) return a + b;
+  if (KIND == VGF_MINI64) return (i64)b < (i64)a ? b : a;
+  if (KIND == VGF_MAXI64) return (i64)a < (i64)b ? b : a;
+  if (KIND == VGF_MINF64) return u2d(b) < u2d(a) ? b : a;
+  return u2d(a) < u2d(b) ? b : a;
+}
+
+// Fixed-order fold of one accumulator over the CTA: xor-butterfly inside each warp, then warp 0
+// ... in warp order through shared memory.  `scratch` holds NT/32 words per value.
+template <int KIND, int NWARPS>
+__device__ __forceinline__ void block_fold(u64 v, u64* scratch, u64* out, u32& err) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const u64 other = __shfl_xor_sync(0xffffffffu, v, o);
+    v = cell_comb<KIND>(v, other, err);
+  }
+  if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 acc = scratch[0];
+#pragma unroll 1
+    for (int w = 1; w < NWARPS; ++w) acc = cell_comb<KIND>(acc, scratch[w], err);
+    *out = acc;
+  }
+  __syncthreads();
+}
+
+// Shared-memory table update with atomics (medium cardinality: one table per warp or per CTA).
+template <int KIND>
+__device__ __forceinline__ void smem_update(u64* cell, u64 v, u32& err) {
+  if (KIND == VGF_COUNT) {
+    atomicAdd(cell, 1ull);
+  } else if (KIND == VGF_SUMF64) {
+    atomicAdd(reinterpret_cast<double*>(cell), u2d(v));
+  } else if (KIND == VGF_SUMI64) {
+    const i64 y = (i64)v;
+    const i64 x = (i64)atomicAdd(cell, v);
+    const i64 z = (i64)((u64)x + (u64)y);
+    if (((x ^ z) & (y ^ z)) < 0) err |= VGF_ERR_OVERFLOW;
+  } else if (KIND == VGF_MINI64) {
+    if ((i64)v < (i64)*reinterpret_cast<volatile u64*>(cell)) atomicMin(reinterpret_cast<i64*>(cell), (i64)v);
+  } else if (KIND == VGF_MAXI64) {
+    if ((i64)*reinterpret_cast<volatile u64*>(cell) < (i64)v) atomicMax(reinterpret_cast<i64*>(cell), (i64)v);
+  } else {
+    u64 cur = *reinterpret_cast<volatile u64*>(cell);
+    while (KIND == VGF_MINF64 ? u2d(v) < u2d(cur) : u2d(cur) < u2d(v)) {
+      const u64 seen = atomicCAS(cell, cur, v);
+      if (seen == cur) break;
+      cur = seen;
+    }
+  }
+}
+
+// ---- HBM hash table (same layout as device_common.cuh) -------------------------------------------
+__device__ __forceinline__ u64 mix64(u64 k) {
+  k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
+  k ^= k >> 27; k *= 0x94d049bb133111ebull;
+  k ^= k >> 31;
+  return k;
+}
+__device__ __forceinline__ i64 f64_ordered(u64 bits) {
+  const i64 s = (i64)bits;
+  return s >= 0 ? s : (i64)(bits ^ 0x7fffffffffffffffull);
+}
+template <int ROW_WORDS>
+__device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key, bool isnull, u32& err) {
+  u64* table = p.table;
+  if (isnull || key == VGF_EMPTY_KEY) {
+    const i64 slot = (i64)p.cap_mask + (isnull ? 1 : 2);
+    u64* kp = table + slot * ROW_WORDS;
+    if (*reinterpret_cast<volatile u64*>(kp) == VGF_EMPTY_KEY) {
+      if (atomicCAS(kp, VGF_EMPTY_KEY, 0ull) == VGF_EMPTY_KEY) atomicAdd(p.n_groups_ctr, 1ull);
+    }
+    return slot;
+  }
+  u64 h = mix64(key) & p.cap_mask;
+  for (u64 probes = 0; probes <= p.cap_mask; ++probes) {
+    u64* kp = table + h * ROW_WORDS;
+    u64 cur = *reinterpret_cast<volatile u64*>(kp);
+    if (cur == key) return (i64)h;
+    if (cur == VGF_EMPTY_KEY) {
+      cur = atomicCAS(kp, VGF_EMPTY_KEY, key);
+      if (cur == VGF_EMPTY_KEY) { atomicAdd(p.n_groups_ctr, 1ull); return (i64)h; }
+      if (cur == key) return (i64)h;
+    }
+    h = (h + 1) & p.cap_mask;
+  }
+  err |= VGF_ERR_TABLEFULL;
+  return -1;
+}
+template <int KIND>
+__device__ __forceinline__ void hbm_update(u64* addr, u64 v, u32& err) {
+  if (KIND == VGF_SUMF64) {
+    atomicAdd(reinterpret_cast<double*>(addr), u2d(v));
+  } else if (KIND == VGF_SUMI64) {
+    const i64 y = (i64)v;
+    const i64 x = (i64)atomicAdd(addr, v);
+    const i64 z = (i64)((u64)x + (u64)y);
+    if (((x ^ z) & (y ^ z)) < 0) err |= VGF_ERR_OVERFLOW;
+  } else if (KIND == VGF_COUNT) {
+    atomicAdd(addr, v);
+  } else if (KIND == VGF_MINI64) {
+    atomicMin(reinterpret_cast<i64*>(addr), (i64)v);
+  } else if (KIND == VGF_MAXI64) {
+    atomicMax(reinterpret_cast<i64*>(addr), (i64)v);
+  } else if (KIND == VGF_MINF64) {
+    if (u2d(v) == u2d(v)) atomicMin(reinterpret_cast<i64*>(addr), f64_ordered(v));
+  } else {
+    if (u2d(v) == u2d(v)) atomicMax(reinterpret_cast<i64*>(addr), f64_ordered(v));
+  }
+}
+
+} // namespace vgf
+#endif // VGPU_FUSED_PRELUDE_CUH_

@@ -90,12 +90,75 @@ struct DevOut {
   uint64_t* nulls;
 };
 
+// ---- micro-ops --------------------------------------------------------------------------------
+// The ABI program (vgpu_op list + filter + outputs) and the sink (keys, cells, projections) are
+// lowered per launch into ONE stream of micro-ops whose operands are already resolved to
+// shared-memory offsets, so that a device handler is straight-line code over the thread's 4 rows.
+enum XKind : uint8_t {
+  XK_NONE = 0,
+  XK_ACC,      // value / boolean accumulator registers
+  XK_IMM,      // XOp::imm
+  XK_NULL,     // typed NULL constant
+  XK_SLOT,     // value slot (off = smem byte offset of the 8 KB tile, noff = its meta words)
+  XK_COL8,     // staged flat column of 8-byte elements (BIGINT / DOUBLE)
+  XK_COL4I,    // staged INTEGER
+  XK_COL4F,    // staged REAL
+  XK_COL2,     // staged SMALLINT
+  XK_COL1,     // staged TINYINT
+  XK_DICT,     // staged int32 indices + base values in global memory (col = column number)
+  XK_BSLOT,    // boolean slot (off = smem byte offset of its meta words)
+  XK_BCOL,     // staged bit-packed BOOLEAN column
+  XK_BDICT     // staged indices over a bit-packed BOOLEAN base
+};
+
+struct XOp {
+  uint8_t kind;
+  uint8_t has_nulls; // staged outer null bitmap present (noff valid)
+  uint8_t type;      // vgpu_type of the value
+  uint8_t col;       // XK_DICT / XK_BDICT: column number (base pointer, base nulls)
+  int32_t off;       // stage-relative (columns) or absolute (slots) shared-memory byte offset
+  int32_t noff;      // stage-relative null bitmap offset / absolute slot meta offset
+  int32_t pad;
+  uint64_t imm;      // XK_IMM: the literal (int64 or double bits)
+};
+
+enum Handler : uint8_t {
+  H_END = 0,
+  H_LD,      // acc = x
+  H_ARITH,   // acc = x (sub) y          sub = vgpu_opcode ADD..MOD, NEG (y unused)
+  H_CAST,    // acc = cast(x) to `type`
+  H_CMP,     // bacc = combine(bacc, x (sub) y [, z for BETWEEN])
+  H_BOOL,    // bacc = x AND/OR y, NOT x, IS_NULL x
+  H_FILTER,  // pass = x is TRUE
+  H_KEY,     // fold value x into the group number / normalized key (dst = key index)
+  H_KEYEND,  // ARRAY: table offsets + in-thread duplicate plan; HASH: find-or-insert
+  H_ACCUM,   // fold value x into cell `dst` (sub = CellKind)
+  H_SEL,     // FilterProject: selection bitmap + per-tile count
+  H_PROJ     // FilterProject: write output `dst` from x
+};
+
+enum MFlags : uint8_t {
+  MF_STORE = 1,     // also store the result to slot (dst / dstn)
+  MF_COMB_AND = 2,  // H_CMP: bacc = bacc AND cmp (three-valued)
+  MF_COMB_OR = 4,   // H_CMP: bacc = bacc OR cmp
+  MF_NO_VALUE = 8   // H_ACCUM: count(*) style cell without an input operand
+};
+
+struct MOp {
+  uint8_t h, sub, type, flags;
+  int32_t dst;   // slot tile offset (MF_STORE), cell offset (H_ACCUM), key / output index
+  int32_t dstn;  // slot meta offset (MF_STORE)
+  int32_t pad;
+  XOp x, y, z;
+};
+constexpr int kMaxMops = 112;
+
 struct PipelineParams {
-  // program
-  vgpu_op ops[kMaxOps];
+  // program (ABI form; lowered to mops by launch_pipeline)
+  MOp mops[kMaxMops];
+  int32_t n_mops;
   vgpu_operand outputs[kMaxOutputs];
-  vgpu_operand filter;
-  int32_t n_ops, n_outputs, n_cols, n_slots, n_bslots;
+  int32_t n_outputs, n_cols, n_slots, n_bslots;
   DevCol cols[kMaxCols];
   // rows
   int64_t n_rows;         // rows to walk (n_in_rows when in_rows != nullptr)
@@ -105,9 +168,9 @@ struct PipelineParams {
   uint32_t* err_word;
   // sink
   int32_t mode;
-  int32_t n_keys, n_cells, n_groups; // ARRAY: n_groups = product of key cardinalities
+  int32_t n_keys, n_cells, n_groups; // ARRAY: n_groups = product of key cardinalities of this launch
   int32_t ignore_null_keys;
-  int32_t warp_private; // ARRAY: 1 = one table per warp (match.any leaders), 0 = one per thread
+  int32_t warp_private; // ARRAY: 1 = one table per warp (shared-memory atomics), 0 = one per thread
   int32_t warp_tab_bytes; // ARRAY, warp_private: bytes of one warp's table
   int32_t tab_bytes;      // ARRAY: bytes of all partial tables of the CTA
   DevKey keys[kMaxKeys];
@@ -125,6 +188,8 @@ struct PipelineParams {
   int32_t* tile_counts;
   unsigned long long* num_selected;
   DevOut outs[kMaxOutputs];
+  // host only: the program being lowered
+  const struct Program* prog;
 };
 
 // ---- host-side objects behind the opaque ABI handles ---------------------------------------

@@ -1,10 +1,12 @@
-// The fused scan pipeline: stage column tiles -> evaluate the expression program -> sink
-// (selection + projections, or group-by accumulation).  One persistent CTA per SM slot walks
-// tiles of 1024 rows.  Column tiles are fetched by the bulk-copy engine (cp.async.bulk, SASS
-// UBLKCP) into a ring of shared-memory stages guarded by mbarriers, so the bytes in flight do
-// not depend on occupancy; the 256 threads then interpret the program over the staged tile,
-// 4 rows per thread, keeping the running value in registers and spilling only named
-// intermediates to shared-memory slots.
+// The fused scan pipeline: stage column tiles -> run the micro-op stream -> sink (selection +
+// projections, or group-by accumulation).  One persistent CTA per SM walks tiles of 1024 rows.
+// Column tiles are fetched by the bulk-copy engine (cp.async.bulk, SASS UBLKCP) into a ring of
+// shared-memory stages guarded by mbarriers, so the bytes in flight do not depend on occupancy.
+// The 256 threads then run ONE stream of micro-ops over the staged tile, 4 rows per thread: the
+// expression program, the filter, the grouping keys and the accumulator updates are all
+// micro-ops whose operands were resolved to shared-memory offsets on the host (lower_mops), so a
+// handler is straight-line code.  The running value stays in registers; only values used more
+// than once go through shared-memory slots.
 //
 // Reference behaviour restated here (paths under the reference tree):
 //   filter -> selection: velox/exec/FilterProject.cpp:125-191, velox/exec/OperatorUtils.cpp:187-210
@@ -20,6 +22,7 @@
 
 #include "internal.h"
 #include "device_common.cuh"
+#include "fused.h"
 
 namespace vg {
 
@@ -188,35 +191,34 @@ struct BoolVal {
 
 struct Ctx {
   const PipelineParams* p;
-  const char* stage;
-  uint64_t* slots;   // [n_slots][kTile]
-  uint32_t* meta;    // [n_slots][kThreads]   n | e << 8
-  uint32_t* bmeta;   // [n_bslots][kThreads]  v | n << 8 | e << 16
+  const char* stage; // current stage (column operands are relative to it)
+  char* smem;        // base of dynamic shared memory (slot operands are absolute)
   int pos0, pos1;    // first row of pair 0 / pair 1 inside the tile
   uint32_t valid;    // rows that exist
   uint32_t ecode;    // error bits raised by this thread's ops, one byte per row
   Val acc;
   BoolVal bacc;
+  // sink state of the current tile
+  uint32_t pass;     // rows that passed the filter (and ignore_null_keys)
+  uint32_t raise;    // rows whose latched error must be reported
+  uint32_t acc_err;  // checked-sum overflow
+  uint32_t goff[4];  // ARRAY: element offset of the row's group inside a cell block
+  uint32_t prev;     // ARRAY thread tables: 2 bits per row j: 0 = no earlier equal row, else 1 + i
+  uint32_t store;    // ARRAY thread tables: rows that are the last of their group in this thread
+  uint64_t key[4];   // HASH: normalized key
+  uint32_t keynull;
+  int64_t slot[4];   // HASH: table slot of the row's group
 };
 
 __device__ __forceinline__ bool is_fp(uint8_t t) { return t == VGPU_REAL || t == VGPU_DOUBLE; }
 
-// Widen a raw staged/base element to the register representation.
-__device__ __forceinline__ uint64_t widen(uint8_t type, uint64_t raw) {
-  switch (type) {
-    case VGPU_TINYINT: return (uint64_t)(int64_t)(int8_t)raw;
-    case VGPU_SMALLINT: return (uint64_t)(int64_t)(int16_t)raw;
-    case VGPU_INTEGER: return (uint64_t)(int64_t)(int32_t)raw;
-    case VGPU_REAL: return d2u((double)__uint_as_float((uint32_t)raw));
-    default: return raw;
-  }
-}
-
 __device__ __forceinline__ uint64_t load_base(const DevCol& c, int64_t idx) {
   switch (elem_bytes_log2(c.type)) {
-    case 0: return reinterpret_cast<const uint8_t*>(c.values)[idx];
-    case 1: return reinterpret_cast<const uint16_t*>(c.values)[idx];
-    case 2: return reinterpret_cast<const uint32_t*>(c.values)[idx];
+    case 0: return (uint64_t)(int64_t)reinterpret_cast<const int8_t*>(c.values)[idx];
+    case 1: return (uint64_t)(int64_t)reinterpret_cast<const int16_t*>(c.values)[idx];
+    case 2:
+      if (c.type == VGPU_REAL) return d2u((double)reinterpret_cast<const float*>(c.values)[idx]);
+      return (uint64_t)(int64_t)reinterpret_cast<const int32_t*>(c.values)[idx];
     default: return reinterpret_cast<const uint64_t*>(c.values)[idx];
   }
 }
@@ -226,184 +228,161 @@ __device__ __forceinline__ uint32_t pair_bits(const char* tile_bits, int pos) {
   const uint32_t w = reinterpret_cast<const uint32_t*>(tile_bits)[pos >> 5];
   return (w >> (pos & 31)) & 3u;
 }
-
-__device__ __forceinline__ void load_col(const Ctx& cx, const DevCol& c, Val& out) {
-  out.e = 0;
-  if (c.encoding == VGPU_CONSTANT) {
-    const uint64_t k = (uint64_t)c.constant;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) out.v[j] = k;
-    out.n = c.const_null ? 0xFu : 0u;
-    return;
-  }
-  uint32_t notnull = 0xFu;
-  if (c.nulls_off >= 0) {
-    notnull = pair_bits(cx.stage + c.nulls_off, cx.pos0) | (pair_bits(cx.stage + c.nulls_off, cx.pos1) << 2);
-  }
-  const char* t = cx.stage + c.stage_off;
-  if (c.encoding == VGPU_DICTIONARY) {
-    const uint2 i0 = reinterpret_cast<const uint2*>(t)[cx.pos0 >> 1];
-    const uint2 i1 = reinterpret_cast<const uint2*>(t)[cx.pos1 >> 1];
-    const int32_t idx[4] = {(int32_t)i0.x, (int32_t)i0.y, (int32_t)i1.x, (int32_t)i1.y};
-    const uint32_t live = cx.valid & notnull;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      uint64_t raw = 0;
-      if ((live >> j) & 1u) {
-        raw = load_base(c, idx[j]);
-        if (c.base_nulls != nullptr && !bit_at(c.base_nulls, idx[j])) notnull &= ~(1u << j);
-      }
-      out.v[j] = widen(c.type, raw);
-    }
-    out.n = (~notnull) & 0xFu;
-    return;
-  }
-  switch (c.elem_log2) {
-    case 3: {
-      const uint4 q0 = reinterpret_cast<const uint4*>(t)[cx.pos0 >> 1];
-      const uint4 q1 = reinterpret_cast<const uint4*>(t)[cx.pos1 >> 1];
-      out.v[0] = (uint64_t)q0.x | ((uint64_t)q0.y << 32);
-      out.v[1] = (uint64_t)q0.z | ((uint64_t)q0.w << 32);
-      out.v[2] = (uint64_t)q1.x | ((uint64_t)q1.y << 32);
-      out.v[3] = (uint64_t)q1.z | ((uint64_t)q1.w << 32);
-      break;
-    }
-    case 2: {
-      const uint2 q0 = reinterpret_cast<const uint2*>(t)[cx.pos0 >> 1];
-      const uint2 q1 = reinterpret_cast<const uint2*>(t)[cx.pos1 >> 1];
-      out.v[0] = widen(c.type, q0.x);
-      out.v[1] = widen(c.type, q0.y);
-      out.v[2] = widen(c.type, q1.x);
-      out.v[3] = widen(c.type, q1.y);
-      break;
-    }
-    case 1: {
-      const uint32_t q0 = reinterpret_cast<const uint32_t*>(t)[cx.pos0 >> 1];
-      const uint32_t q1 = reinterpret_cast<const uint32_t*>(t)[cx.pos1 >> 1];
-      out.v[0] = widen(c.type, q0 & 0xffffu);
-      out.v[1] = widen(c.type, q0 >> 16);
-      out.v[2] = widen(c.type, q1 & 0xffffu);
-      out.v[3] = widen(c.type, q1 >> 16);
-      break;
-    }
-    default: {
-      const uint32_t q0 = reinterpret_cast<const uint16_t*>(t)[cx.pos0 >> 1];
-      const uint32_t q1 = reinterpret_cast<const uint16_t*>(t)[cx.pos1 >> 1];
-      out.v[0] = widen(c.type, q0 & 0xffu);
-      out.v[1] = widen(c.type, q0 >> 8);
-      out.v[2] = widen(c.type, q1 & 0xffu);
-      out.v[3] = widen(c.type, q1 >> 8);
-    }
-  }
-  out.n = (~notnull) & 0xFu;
+__device__ __forceinline__ uint32_t quad_bits(const Ctx& cx, int off) {
+  const char* b = cx.stage + off;
+  return pair_bits(b, cx.pos0) | (pair_bits(b, cx.pos1) << 2);
 }
+__device__ __forceinline__ uint64_t pack64(uint32_t lo, uint32_t hi) { return (uint64_t)lo | ((uint64_t)hi << 32); }
+__device__ __forceinline__ uint64_t sext32(uint32_t x) { return (uint64_t)(int64_t)(int32_t)x; }
 
-// which: 0 = a/b (reads op.imm), 1 = c (reads op.imm2)
-__device__ __forceinline__ void load_value(const Ctx& cx, const vgpu_op& op, const vgpu_operand o,
-                                           int which, Val& out) {
-  switch (o.kind) {
-    case VGPU_OPND_ACC:
+// Reads a value operand for the thread's 4 rows.
+__device__ __forceinline__ void fetch(const Ctx& cx, const XOp& x, Val& out) {
+  out.e = 0;
+  out.n = 0;
+  switch (x.kind) {
+    case XK_ACC:
       out = cx.acc;
-      break;
-    case VGPU_OPND_SLOT: {
-      const uint4* s = reinterpret_cast<const uint4*>(cx.slots + (size_t)o.index * kTile);
+      return;
+    case XK_IMM:
+#pragma unroll
+      for (int j = 0; j < 4; ++j) out.v[j] = x.imm;
+      return;
+    case XK_SLOT: {
+      const uint4* s = reinterpret_cast<const uint4*>(cx.smem + x.off);
       const uint4 q0 = s[cx.pos0 >> 1];
       const uint4 q1 = s[cx.pos1 >> 1];
-      out.v[0] = (uint64_t)q0.x | ((uint64_t)q0.y << 32);
-      out.v[1] = (uint64_t)q0.z | ((uint64_t)q0.w << 32);
-      out.v[2] = (uint64_t)q1.x | ((uint64_t)q1.y << 32);
-      out.v[3] = (uint64_t)q1.z | ((uint64_t)q1.w << 32);
-      const uint32_t m = cx.meta[o.index * kThreads + threadIdx.x];
-      out.n = m & 0xFu;
-      out.e = (m >> 8) & 0xFu;
+      out.v[0] = pack64(q0.x, q0.y); out.v[1] = pack64(q0.z, q0.w);
+      out.v[2] = pack64(q1.x, q1.y); out.v[3] = pack64(q1.z, q1.w);
+      if (x.has_nulls) { // slot may carry nulls / errors
+        const uint32_t m = reinterpret_cast<const uint32_t*>(cx.smem + x.noff)[threadIdx.x];
+        out.n = m & 0xFu;
+        out.e = (m >> 8) & 0xFu;
+      }
+      return;
+    }
+    case XK_COL8: {
+      const uint4* s = reinterpret_cast<const uint4*>(cx.stage + x.off);
+      const uint4 q0 = s[cx.pos0 >> 1];
+      const uint4 q1 = s[cx.pos1 >> 1];
+      out.v[0] = pack64(q0.x, q0.y); out.v[1] = pack64(q0.z, q0.w);
+      out.v[2] = pack64(q1.x, q1.y); out.v[3] = pack64(q1.z, q1.w);
       break;
     }
-    case VGPU_OPND_COL:
-      load_col(cx, cx.p->cols[o.index], out);
+    case XK_COL4I: {
+      const uint2* s = reinterpret_cast<const uint2*>(cx.stage + x.off);
+      const uint2 q0 = s[cx.pos0 >> 1];
+      const uint2 q1 = s[cx.pos1 >> 1];
+      out.v[0] = sext32(q0.x); out.v[1] = sext32(q0.y);
+      out.v[2] = sext32(q1.x); out.v[3] = sext32(q1.y);
       break;
-    case VGPU_OPND_IMM: {
-      const uint64_t k = (uint64_t)(which ? op.imm2.i : op.imm.i);
+    }
+    case XK_COL4F: {
+      const float2* s = reinterpret_cast<const float2*>(cx.stage + x.off);
+      const float2 q0 = s[cx.pos0 >> 1];
+      const float2 q1 = s[cx.pos1 >> 1];
+      out.v[0] = d2u((double)q0.x); out.v[1] = d2u((double)q0.y);
+      out.v[2] = d2u((double)q1.x); out.v[3] = d2u((double)q1.y);
+      break;
+    }
+    case XK_COL2: {
+      const uint32_t* s = reinterpret_cast<const uint32_t*>(cx.stage + x.off);
+      const uint32_t q0 = s[cx.pos0 >> 1], q1 = s[cx.pos1 >> 1];
+      out.v[0] = (uint64_t)(int64_t)(int16_t)(q0 & 0xffffu); out.v[1] = (uint64_t)(int64_t)(int16_t)(q0 >> 16);
+      out.v[2] = (uint64_t)(int64_t)(int16_t)(q1 & 0xffffu); out.v[3] = (uint64_t)(int64_t)(int16_t)(q1 >> 16);
+      break;
+    }
+    case XK_COL1: {
+      const uint16_t* s = reinterpret_cast<const uint16_t*>(cx.stage + x.off);
+      const uint32_t q0 = s[cx.pos0 >> 1], q1 = s[cx.pos1 >> 1];
+      out.v[0] = (uint64_t)(int64_t)(int8_t)(q0 & 0xffu); out.v[1] = (uint64_t)(int64_t)(int8_t)(q0 >> 8);
+      out.v[2] = (uint64_t)(int64_t)(int8_t)(q1 & 0xffu); out.v[3] = (uint64_t)(int64_t)(int8_t)(q1 >> 8);
+      break;
+    }
+    case XK_DICT: {
+      const DevCol& c = cx.p->cols[x.col];
+      const uint2* s = reinterpret_cast<const uint2*>(cx.stage + x.off);
+      const uint2 i0 = s[cx.pos0 >> 1];
+      const uint2 i1 = s[cx.pos1 >> 1];
+      const int32_t idx[4] = {(int32_t)i0.x, (int32_t)i0.y, (int32_t)i1.x, (int32_t)i1.y};
+      uint32_t notnull = x.has_nulls ? quad_bits(cx, x.noff) : 0xFu;
+      const uint32_t live = cx.valid & notnull;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) out.v[j] = k;
-      out.n = 0;
-      out.e = 0;
-      break;
+      for (int j = 0; j < 4; ++j) {
+        uint64_t raw = 0;
+        if ((live >> j) & 1u) {
+          raw = load_base(c, idx[j]);
+          if (c.base_nulls != nullptr && !bit_at(c.base_nulls, idx[j])) notnull &= ~(1u << j);
+        }
+        out.v[j] = raw;
+      }
+      out.n = (~notnull) & 0xFu;
+      return;
     }
-    default: // NULL constant
+    default: // XK_NULL
 #pragma unroll
       for (int j = 0; j < 4; ++j) out.v[j] = 0;
       out.n = 0xFu;
-      out.e = 0;
+      return;
   }
+  if (x.has_nulls) out.n = (~quad_bits(cx, x.noff)) & 0xFu;
 }
 
-__device__ __forceinline__ void store_slot(const Ctx& cx, int slot, const Val& v) {
-  uint4* s = reinterpret_cast<uint4*>(cx.slots + (size_t)slot * kTile);
+__device__ __forceinline__ void store_slot(const Ctx& cx, const MOp& op, const Val& v) {
+  uint4* s = reinterpret_cast<uint4*>(cx.smem + op.dst);
   s[cx.pos0 >> 1] = make_uint4((uint32_t)v.v[0], (uint32_t)(v.v[0] >> 32), (uint32_t)v.v[1],
                                (uint32_t)(v.v[1] >> 32));
   s[cx.pos1 >> 1] = make_uint4((uint32_t)v.v[2], (uint32_t)(v.v[2] >> 32), (uint32_t)v.v[3],
                                (uint32_t)(v.v[3] >> 32));
-  cx.meta[slot * kThreads + threadIdx.x] = v.n | (v.e << 8);
+  if (op.dstn >= 0) reinterpret_cast<uint32_t*>(cx.smem + op.dstn)[threadIdx.x] = v.n | (v.e << 8);
 }
 
-__device__ __forceinline__ void load_bool(const Ctx& cx, const vgpu_op& op, const vgpu_operand o,
-                                          BoolVal& out) {
-  switch (o.kind) {
-    case VGPU_OPND_ACC:
+// Reads a boolean operand.
+__device__ __forceinline__ void fetchb(const Ctx& cx, const XOp& x, BoolVal& out) {
+  out.e = 0;
+  out.n = 0;
+  switch (x.kind) {
+    case XK_ACC:
       out = cx.bacc;
-      break;
-    case VGPU_OPND_SLOT: {
-      const uint32_t m = cx.bmeta[o.index * kThreads + threadIdx.x];
+      return;
+    case XK_BSLOT: {
+      const uint32_t m = reinterpret_cast<const uint32_t*>(cx.smem + x.off)[threadIdx.x];
       out.v = m & 0xFu;
       out.n = (m >> 8) & 0xFu;
       out.e = (m >> 16) & 0xFu;
-      break;
+      return;
     }
-    case VGPU_OPND_COL: {
-      const DevCol& c = cx.p->cols[o.index];
-      out.e = 0;
-      if (c.encoding == VGPU_CONSTANT) {
-        out.v = c.constant ? 0xFu : 0u;
-        out.n = c.const_null ? 0xFu : 0u;
-        break;
-      }
-      uint32_t notnull = 0xFu;
-      if (c.nulls_off >= 0) {
-        notnull = pair_bits(cx.stage + c.nulls_off, cx.pos0) |
-            (pair_bits(cx.stage + c.nulls_off, cx.pos1) << 2);
-      }
-      if (c.encoding == VGPU_DICTIONARY) {
-        const char* t = cx.stage + c.stage_off;
-        const uint2 i0 = reinterpret_cast<const uint2*>(t)[cx.pos0 >> 1];
-        const uint2 i1 = reinterpret_cast<const uint2*>(t)[cx.pos1 >> 1];
-        const int32_t idx[4] = {(int32_t)i0.x, (int32_t)i0.y, (int32_t)i1.x, (int32_t)i1.y};
-        const uint32_t live = cx.valid & notnull;
-        uint32_t v = 0;
+    case XK_IMM:
+      out.v = x.imm ? 0xFu : 0u;
+      return;
+    case XK_BCOL:
+      out.v = quad_bits(cx, x.off);
+      break;
+    case XK_BDICT: {
+      const DevCol& c = cx.p->cols[x.col];
+      const uint2* s = reinterpret_cast<const uint2*>(cx.stage + x.off);
+      const uint2 i0 = s[cx.pos0 >> 1];
+      const uint2 i1 = s[cx.pos1 >> 1];
+      const int32_t idx[4] = {(int32_t)i0.x, (int32_t)i0.y, (int32_t)i1.x, (int32_t)i1.y};
+      uint32_t notnull = x.has_nulls ? quad_bits(cx, x.noff) : 0xFu;
+      const uint32_t live = cx.valid & notnull;
+      uint32_t v = 0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if ((live >> j) & 1u) {
-            if (bit_at(reinterpret_cast<const uint64_t*>(c.values), idx[j])) v |= 1u << j;
-            if (c.base_nulls != nullptr && !bit_at(c.base_nulls, idx[j])) notnull &= ~(1u << j);
-          }
+      for (int j = 0; j < 4; ++j) {
+        if ((live >> j) & 1u) {
+          if (bit_at(reinterpret_cast<const uint64_t*>(c.values), idx[j])) v |= 1u << j;
+          if (c.base_nulls != nullptr && !bit_at(c.base_nulls, idx[j])) notnull &= ~(1u << j);
         }
-        out.v = v;
-      } else {
-        out.v = pair_bits(cx.stage + c.stage_off, cx.pos0) |
-            (pair_bits(cx.stage + c.stage_off, cx.pos1) << 2);
       }
+      out.v = v;
       out.n = (~notnull) & 0xFu;
-      break;
+      return;
     }
-    case VGPU_OPND_IMM:
-      out.v = op.imm.i ? 0xFu : 0u;
-      out.n = 0;
-      out.e = 0;
-      break;
-    default:
+    default: // XK_NULL
       out.v = 0;
       out.n = 0xFu;
-      out.e = 0;
+      return;
   }
+  if (x.has_nulls) out.n = (~quad_bits(cx, x.noff)) & 0xFu;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -565,161 +544,69 @@ __device__ __forceinline__ uint32_t cmp4(uint8_t oc, uint8_t type, const uint64_
 }
 
 // ------------------------------------------------------------------------------------------
-// The interpreter: one pass over the program for the thread's 4 rows.
+// Boolean helpers
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void run_program(Ctx& cx) {
-  const PipelineParams& p = *cx.p;
-#pragma unroll 1
-  for (int i = 0; i < p.n_ops; ++i) {
-    const vgpu_op& op = p.ops[i];
-    const uint8_t oc = op.opcode;
-    if (oc >= VGPU_OP_AND && oc <= VGPU_OP_IS_NULL) {
-      BoolVal r;
-      if (oc == VGPU_OP_IS_NULL) {
-        if (op.a.type == VGPU_BOOLEAN) {
-          BoolVal a;
-          load_bool(cx, op, op.a, a);
-          r.v = a.n; r.e = a.e;
-        } else {
-          Val a;
-          load_value(cx, op, op.a, 0, a);
-          r.v = a.n; r.e = a.e;
-        }
-        r.n = 0;
-      } else {
-        BoolVal a;
-        load_bool(cx, op, op.a, a);
-        if (oc == VGPU_OP_NOT) {
-          r.v = (~a.v) & 0xFu; r.n = a.n; r.e = a.e;
-        } else {
-          BoolVal b;
-          load_bool(cx, op, op.b, b);
-          const uint32_t okA = ~a.n & ~a.e, okB = ~b.n & ~b.e;
-          if (oc == VGPU_OP_AND) {
-            const uint32_t decided = (okA & ~a.v) | (okB & ~b.v); // some conjunct is FALSE
-            r.v = okA & a.v & okB & b.v & 0xFu;
-            r.e = ~decided & (a.e | b.e) & 0xFu;
-            r.n = ~decided & ~r.e & (a.n | b.n) & 0xFu;
-          } else {
-            const uint32_t decided = (okA & a.v) | (okB & b.v); // some disjunct is TRUE
-            r.v = decided & 0xFu;
-            r.e = ~decided & (a.e | b.e) & 0xFu;
-            r.n = ~decided & ~r.e & (a.n | b.n) & 0xFu;
-          }
-        }
-      }
-      cx.bacc = r;
-      if (op.dst_slot >= 0) {
-        cx.bmeta[op.dst_slot * kThreads + threadIdx.x] = r.v | (r.n << 8) | (r.e << 16);
-      }
-      continue;
-    }
-    if (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) {
-      BoolVal r;
-      if (op.type == VGPU_BOOLEAN) { // boolean = / <> boolean
-        BoolVal a, b;
-        load_bool(cx, op, op.a, a);
-        load_bool(cx, op, op.b, b);
-        const uint32_t x = a.v ^ b.v;
-        r.v = (oc == VGPU_OP_EQ ? ~x : x) & 0xFu;
-        r.n = a.n | b.n;
-        r.e = a.e | b.e;
-      } else {
-        Val a, b;
-        load_value(cx, op, op.a, 0, a);
-        load_value(cx, op, op.b, 0, b);
-        r.n = a.n | b.n;
-        r.e = a.e | b.e;
-        r.v = 0;
-        if (oc == VGPU_OP_BETWEEN) {
-          Val c;
-          load_value(cx, op, op.c, 1, c);
-          r.n |= c.n;
-          r.e |= c.e;
-          r.v = cmp4(VGPU_OP_GE, op.type, a.v, b.v) & cmp4(VGPU_OP_LE, op.type, a.v, c.v);
-        } else {
-          r.v = cmp4(oc, op.type, a.v, b.v);
-        }
-      }
-      r.v &= ~r.n;
-      cx.bacc = r;
-      if (op.dst_slot >= 0) {
-        cx.bmeta[op.dst_slot * kThreads + threadIdx.x] = r.v | (r.n << 8) | (r.e << 16);
-      }
-      continue;
-    }
-    // value ops
-    Val a, r;
-    load_value(cx, op, op.a, 0, a);
-    r.n = a.n;
-    r.e = a.e;
-    if (oc == VGPU_OP_MOV) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) r.v[j] = a.v[j];
-    } else if (oc == VGPU_OP_CAST) {
-      uint32_t bad = 0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        r.v[j] = 0;
-        const uint32_t err = cast_value(op.a.type, op.type, a.v[j], r.v[j]);
-        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
-      }
-      r.e |= bad;
-    } else if (oc == VGPU_OP_NEG) {
-      uint32_t bad = 0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        r.v[j] = 0;
-        const uint32_t err = arith(oc, op.type, a.v[j], 0, r.v[j]);
-        if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
-      }
-      r.e |= bad;
-    } else {
-      Val b;
-      load_value(cx, op, op.b, 0, b);
-      r.n |= b.n;
-      r.e |= b.e;
-      if (op.type == VGPU_DOUBLE && oc <= VGPU_OP_MUL) {
-        // hot path of Q1/Q6: plain IEEE double ops, dispatch hoisted out of the row loop
-        if (oc == VGPU_OP_MUL) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dmul_rn(u2d(a.v[j]), u2d(b.v[j])));
-        } else if (oc == VGPU_OP_ADD) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dadd_rn(u2d(a.v[j]), u2d(b.v[j])));
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dsub_rn(u2d(a.v[j]), u2d(b.v[j])));
-        }
-      } else {
-        uint32_t bad = 0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          r.v[j] = 0;
-          const uint32_t err = arith(oc, op.type, a.v[j], b.v[j], r.v[j]);
-          if (err && !((r.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
-        }
-        r.e |= bad;
-      }
-    }
-    cx.acc = r;
-    if (op.dst_slot >= 0) store_slot(cx, op.dst_slot, r);
-  }
+// SQL three-valued AND / OR of two evaluated operands; an error or NULL in one side is dropped
+// when the other side decides the row (velox/expression/ConjunctExpr.cpp:24-174).
+__device__ __forceinline__ BoolVal and3(const BoolVal& a, const BoolVal& b) {
+  const uint32_t okA = ~a.n & ~a.e, okB = ~b.n & ~b.e;
+  const uint32_t decided = (okA & ~a.v) | (okB & ~b.v); // some conjunct is FALSE
+  BoolVal r;
+  r.v = okA & a.v & okB & b.v & 0xFu;
+  r.e = ~decided & (a.e | b.e) & 0xFu;
+  r.n = ~decided & ~r.e & (a.n | b.n) & 0xFu;
+  return r;
+}
+__device__ __forceinline__ BoolVal or3(const BoolVal& a, const BoolVal& b) {
+  const uint32_t okA = ~a.n & ~a.e, okB = ~b.n & ~b.e;
+  const uint32_t decided = (okA & a.v) | (okB & b.v); // some disjunct is TRUE
+  BoolVal r;
+  r.v = decided & 0xFu;
+  r.e = ~decided & (a.e | b.e) & 0xFu;
+  r.n = ~decided & ~r.e & (a.n | b.n) & 0xFu;
+  return r;
 }
 
-// ------------------------------------------------------------------------------------------
-// Sinks
-// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cmp4_i32(uint8_t oc, const int32_t a[4], int32_t k) {
+  uint32_t m = 0;
+  switch (oc) {
+#define VG_ROWS(OP) _Pragma("unroll") for (int j = 0; j < 4; ++j) m |= (a[j] OP k ? 1u : 0u) << j;
+    case VGPU_OP_EQ: VG_ROWS(==) break;
+    case VGPU_OP_NE: VG_ROWS(!=) break;
+    case VGPU_OP_LT: VG_ROWS(<) break;
+    case VGPU_OP_LE: VG_ROWS(<=) break;
+    case VGPU_OP_GT: VG_ROWS(>) break;
+    default: VG_ROWS(>=)
+#undef VG_ROWS
+  }
+  return m;
+}
+
 __device__ __forceinline__ uint32_t interleave16(uint32_t even, uint32_t odd) {
-  // bit i of even -> bit 2i, bit i of odd -> bit 2i+1
+  // bit i of even -> bit 2i, bit i of odd -> bit 2i+1 (perfect-shuffle network)
   uint32_t x = (even & 0xffffu) | (odd << 16);
-  // spread the two 16-bit halves: classic perfect-shuffle network
   uint32_t t;
   t = (x ^ (x >> 8)) & 0x0000ff00u; x ^= t ^ (t << 8);
   t = (x ^ (x >> 4)) & 0x00f000f0u; x ^= t ^ (t << 4);
   t = (x ^ (x >> 2)) & 0x0c0c0c0cu; x ^= t ^ (t << 2);
   t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
   return x;
+}
+
+// Writes the 4-bit-per-thread mask `m` of the tile as packed words at dst[word_base ...].
+__device__ __forceinline__ void store_tile_bits(uint32_t* dst, int64_t word_base, int n_words, uint32_t m) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int pr = 0; pr < 2; ++pr) {
+    const uint32_t even = __ballot_sync(0xffffffffu, (m >> (2 * pr)) & 1u);
+    const uint32_t odd = __ballot_sync(0xffffffffu, (m >> (2 * pr + 1)) & 1u);
+    if ((lane & 15) == 0) {
+      const int h = lane >> 4;
+      const int w = warp * 4 + pr * 2 + h;
+      // words past the data but inside the last 64-bit word are written as zero
+      if (w < ((n_words + 1) & ~1)) dst[word_base + w] = interleave16(even >> (16 * h), odd >> (16 * h));
+    }
+  }
 }
 
 // Error bits of the rows in `raise` (cx.ecode keeps one byte of bits per row).
@@ -732,377 +619,454 @@ __device__ __forceinline__ uint32_t raised_code(uint32_t ecode, uint32_t raise) 
   return code ? code : kErrOverflow;
 }
 
-// Filter operand -> rows that pass; raises latched errors for rows the filter left undecided.
-__device__ __forceinline__ uint32_t eval_filter(Ctx& cx, uint32_t& raise) {
-  const PipelineParams& p = *cx.p;
-  if (p.filter.kind == VGPU_OPND_NONE) return cx.valid;
-  BoolVal f;
-  vgpu_op dummy;
-  dummy.imm.i = 1;
-  load_bool(cx, dummy, p.filter, f);
-  raise |= f.e & cx.valid;
-  return f.v & ~f.n & ~f.e & cx.valid;
+// ------------------------------------------------------------------------------------------
+// ARRAY sink: per-thread (or per-warp) partial tables in shared memory.
+// Layout of a cell block: [group][copy] elements of 8 bytes (4 for counts); copies = 256
+// (thread tables: a warp touches 32 adjacent elements, conflict-free) or 1 (warp tables).
+// ------------------------------------------------------------------------------------------
+template <int KIND>
+__device__ __forceinline__ uint64_t cell_comb(uint64_t a, uint64_t b, uint32_t& err) {
+  if (KIND == kCellSumF64) return d2u(__dadd_rn(u2d(a), u2d(b)));
+  if (KIND == kCellSumI64) {
+    const int64_t x = (int64_t)a, y = (int64_t)b, z = (int64_t)(a + b);
+    if (((x ^ z) & (y ^ z)) < 0) err |= kErrOverflow;
+    return (uint64_t)z;
+  }
+  if (KIND == kCellCount) return a + b;
+  if (KIND == kCellMinI64) return (int64_t)b < (int64_t)a ? b : a;
+  if (KIND == kCellMaxI64) return (int64_t)a < (int64_t)b ? b : a;
+  if (KIND == kCellMinF64) return u2d(b) < u2d(a) ? b : a;
+  return u2d(a) < u2d(b) ? b : a;
 }
 
-__device__ void sink_filter_project(Ctx& cx, int64_t tile, int cnt) {
-  const PipelineParams& p = *cx.p;
-  uint32_t raise = 0;
-  const uint32_t pass = eval_filter(cx, raise);
-  const int64_t word_base = tile * (kTile / 32);
-  const int n_words = (cnt + 31) >> 5; // words of this tile that exist (partial last tile)
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool full = cnt == kTile;
-  // selection bitmap
-  {
-#pragma unroll
-    for (int pr = 0; pr < 2; ++pr) {
-      const uint32_t even = __ballot_sync(0xffffffffu, (pass >> (2 * pr)) & 1u);
-      const uint32_t odd = __ballot_sync(0xffffffffu, (pass >> (2 * pr + 1)) & 1u);
-      if ((lane & 15) == 0) {
-        const int h = lane >> 4;
-        const int w = warp * 4 + pr * 2 + h;
-        // words past the data but inside the last 64-bit word are written as zero
-        if (w < ((n_words + 1) & ~1)) {
-          p.sel_words[word_base + w] = interleave16(even >> (16 * h), odd >> (16 * h));
-        }
-      }
-    }
-    const int c = __popc(pass);
-    int wsum = c;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
-    if (lane == 0 && wsum) atomicAdd(&p.tile_counts[tile], wsum);
-  }
-  // projections
-  for (int k = 0; k < p.n_outputs; ++k) {
-    const vgpu_operand o = p.outputs[k];
-    const DevOut out = p.outs[k];
-    if (out.values == nullptr) continue;
-    vgpu_op dummy;
-    dummy.imm.i = 0;
-    uint32_t nmask;
-    const int64_t r0 = tile * kTile + cx.pos0, r1 = tile * kTile + cx.pos1;
-    if (o.type == VGPU_BOOLEAN) {
-      BoolVal b;
-      load_bool(cx, dummy, o, b);
-      raise |= b.e & pass;
-      nmask = b.n;
-      // value bits
-#pragma unroll
-      for (int pr = 0; pr < 2; ++pr) {
-        const uint32_t even = __ballot_sync(0xffffffffu, (b.v >> (2 * pr)) & 1u);
-        const uint32_t odd = __ballot_sync(0xffffffffu, (b.v >> (2 * pr + 1)) & 1u);
-        if ((lane & 15) == 0) {
-          const int h = lane >> 4;
-          const int w = warp * 4 + pr * 2 + h;
-          if (w < ((n_words + 1) & ~1)) {
-            reinterpret_cast<uint32_t*>(out.values)[word_base + w] =
-                interleave16(even >> (16 * h), odd >> (16 * h));
-          }
-        }
-      }
-    } else {
-      Val v;
-      load_value(cx, dummy, o, 0, v);
-      raise |= v.e & pass;
-      nmask = v.n;
-      const int lg = elem_bytes_log2(o.type);
-      if (o.type == VGPU_REAL) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v.v[j] = __float_as_uint((float)u2d(v.v[j]));
-      }
-      if (full && lg == 3) {
-        uint4* d = reinterpret_cast<uint4*>(out.values);
-        d[r0 >> 1] = make_uint4((uint32_t)v.v[0], (uint32_t)(v.v[0] >> 32), (uint32_t)v.v[1],
-                                (uint32_t)(v.v[1] >> 32));
-        d[r1 >> 1] = make_uint4((uint32_t)v.v[2], (uint32_t)(v.v[2] >> 32), (uint32_t)v.v[3],
-                                (uint32_t)(v.v[3] >> 32));
-      } else if (full && lg == 2) {
-        uint2* d = reinterpret_cast<uint2*>(out.values);
-        d[r0 >> 1] = make_uint2((uint32_t)v.v[0], (uint32_t)v.v[1]);
-        d[r1 >> 1] = make_uint2((uint32_t)v.v[2], (uint32_t)v.v[3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (!((cx.valid >> j) & 1u)) continue;
-          const int64_t r = (j < 2 ? r0 : r1) + (j & 1);
-          switch (lg) {
-            case 0: reinterpret_cast<uint8_t*>(out.values)[r] = (uint8_t)v.v[j]; break;
-            case 1: reinterpret_cast<uint16_t*>(out.values)[r] = (uint16_t)v.v[j]; break;
-            case 2: reinterpret_cast<uint32_t*>(out.values)[r] = (uint32_t)v.v[j]; break;
-            default: reinterpret_cast<uint64_t*>(out.values)[r] = v.v[j];
-          }
-        }
-      }
-    }
-    if (out.nulls != nullptr) {
-      const uint32_t notnull = ~nmask & cx.valid & 0xFu;
-#pragma unroll
-      for (int pr = 0; pr < 2; ++pr) {
-        const uint32_t even = __ballot_sync(0xffffffffu, (notnull >> (2 * pr)) & 1u);
-        const uint32_t odd = __ballot_sync(0xffffffffu, (notnull >> (2 * pr + 1)) & 1u);
-        if ((lane & 15) == 0) {
-          const int h = lane >> 4;
-          const int w = warp * 4 + pr * 2 + h;
-          if (w < ((n_words + 1) & ~1)) {
-            reinterpret_cast<uint32_t*>(out.nulls)[word_base + w] =
-                interleave16(even >> (16 * h), odd >> (16 * h));
-          }
-        }
-      }
-    }
-  }
-  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
-}
-
-// ---- group-by accumulation -------------------------------------------------------------------
-// Converts the raw register value of output operand type `t` into what cell `kind` consumes.
-__device__ __forceinline__ uint64_t cell_input(uint8_t kind, uint8_t t, uint64_t v) {
-  if (kind == kCellSumF64 && !is_fp(t)) return d2u((double)(int64_t)v);
-  return v;
-}
-
-// One shared-memory cell update (thread- or leader-exclusive, so no atomics).
-__device__ __forceinline__ void update_smem_cell(uint8_t kind, char* addr, uint64_t v, uint32_t& ecode) {
-  switch (kind) {
-    case kCellSumF64: {
-      double* d = reinterpret_cast<double*>(addr);
-      *d = __dadd_rn(*d, u2d(v));
-      break;
-    }
-    case kCellSumI64: {
-      int64_t* d = reinterpret_cast<int64_t*>(addr);
-      const int64_t x = *d, y = (int64_t)v, z = (int64_t)((uint64_t)x + (uint64_t)y);
-      if (((x ^ z) & (y ^ z)) < 0) ecode |= kErrOverflow;
-      *d = z;
-      break;
-    }
-    case kCellCount: {
-      uint32_t* d = reinterpret_cast<uint32_t*>(addr);
-      *d = *d + 1;
-      break;
-    }
-    case kCellMinI64: {
-      int64_t* d = reinterpret_cast<int64_t*>(addr);
-      if ((int64_t)v < *d) *d = (int64_t)v;
-      break;
-    }
-    case kCellMaxI64: {
-      int64_t* d = reinterpret_cast<int64_t*>(addr);
-      if (*d < (int64_t)v) *d = (int64_t)v;
-      break;
-    }
-    case kCellMinF64: {
-      double* d = reinterpret_cast<double*>(addr);
-      if (u2d(v) < *d) *d = u2d(v);
-      break;
-    }
-    default: {
-      double* d = reinterpret_cast<double*>(addr);
-      if (*d < u2d(v)) *d = u2d(v);
-    }
-  }
-}
-
-// Group number / normalized key of the thread's rows; clears rows dropped by ignore_null_keys
-// from `pass` and latches kErrKeyRange for values outside the declared key domain.
-__device__ __forceinline__ void compute_keys(Ctx& cx, uint32_t& pass, uint32_t& raise, uint64_t key[4],
-                                             uint32_t& keynull) {
-  const PipelineParams& p = *cx.p;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) key[j] = 0;
-  keynull = 0;
-  vgpu_op dummy;
-  dummy.imm.i = 0;
-  for (int k = 0; k < p.n_keys; ++k) {
-    const DevKey& ks = p.keys[k];
-    Val v;
-    load_value(cx, dummy, p.outputs[ks.output], 0, v);
-    raise |= v.e & pass;
-    if (p.ignore_null_keys) pass &= ~v.n;
-    if (ks.bits == 64) { // raw 64-bit key
-#pragma unroll
-      for (int j = 0; j < 4; ++j) key[j] = v.v[j];
-      keynull = v.n;
-      continue;
-    }
-    uint32_t bad = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int64_t x = (int64_t)v.v[j];
-      const bool isnull = (v.n >> j) & 1u;
-      uint64_t id;
-      if (isnull) {
-        id = 0;
-        if (!ks.nullable) bad |= 1u << j;
-      } else {
-        if (x < ks.min || x > ks.max) bad |= 1u << j;
-        id = (uint64_t)(x - ks.min) + (ks.nullable ? 1u : 0u);
-      }
-      key[j] += (p.mode == kSinkArray) ? id * (uint64_t)ks.mult : (id << ks.shift);
-    }
-    if (bad & pass) {
-      cx.ecode |= kErrKeyRange * 0x01010101u;
-      raise |= bad & pass;
-      pass &= ~bad;
-    }
-  }
-}
-
-__device__ void sink_array(Ctx& cx, char* tab) {
-  const PipelineParams& p = *cx.p;
-  uint32_t raise = 0;
-  uint32_t pass = eval_filter(cx, raise);
-  uint64_t key[4];
-  uint32_t keynull;
-  compute_keys(cx, pass, raise, key, keynull);
-  const int lane = threadIdx.x & 31;
-  // Conflict schedule: thread-private tables need none; warp-private tables let the lanes that
-  // share a group take turns (rank among the peers found with match.any).
-  uint32_t rank[4] = {0, 0, 0, 0};
-  uint32_t rounds[4] = {1, 1, 1, 1};
-  if (p.warp_private) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const bool act = (pass >> j) & 1u;
-      const uint32_t todo = __ballot_sync(0xffffffffu, act);
-      uint32_t r = 0;
-      if (act) {
-        const uint32_t peers = __match_any_sync(todo, (uint32_t)key[j]);
-        r = __popc(peers & ((1u << lane) - 1u));
-      }
-      rank[j] = r;
-      uint32_t m = act ? r + 1 : 0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-      rounds[j] = m;
-    }
-  }
-  const int owner = p.warp_private ? 0 : threadIdx.x;
-  const int copies = p.warp_private ? 1 : kThreads;
-  char* base = tab;
-  if (p.warp_private) base += (size_t)(threadIdx.x >> 5) * (size_t)p.warp_tab_bytes;
-  vgpu_op dummy;
-  dummy.imm.i = 0;
-  uint32_t acc_err = 0; // checked-sum overflow of rows that did pass
-  for (int c = 0; c < p.n_cells; ++c) {
-    const DevCell cell = p.cells[c];
-    if (cell.skip) continue;
-    Val v;
-    uint32_t live = pass;
-    uint8_t in_type = VGPU_BIGINT;
-    if (cell.input >= 0) {
-      const vgpu_operand o = p.outputs[cell.input];
-      in_type = o.type;
-      if (o.type == VGPU_BOOLEAN) {
-        BoolVal b;
-        load_bool(cx, dummy, o, b);
-        raise |= b.e & pass;
-        live &= ~b.n;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v.v[j] = (b.v >> j) & 1u;
-      } else {
-        load_value(cx, dummy, o, 0, v);
-        raise |= v.e & pass;
-        live &= ~v.n;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) v.v[j] = 0;
-    }
-    const int w = cell_width(cell.kind);
-    char* cbase = base + cell.smem_off;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const bool act = (live >> j) & 1u;
-      char* addr = cbase + ((size_t)key[j] * copies + owner) * w;
-      const uint64_t x = cell_input(cell.kind, in_type, v.v[j]);
-      if (!p.warp_private) {
-        if (act) update_smem_cell(cell.kind, addr, x, acc_err);
-      } else {
-        for (uint32_t r = 0; r < rounds[j]; ++r) {
-          if (act && rank[j] == r) update_smem_cell(cell.kind, addr, x, acc_err);
-          __syncwarp();
-        }
-      }
-    }
-  }
-  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
-  if (acc_err) atomicOr(p.err_word, acc_err);
-}
-
-__device__ void sink_hash(Ctx& cx) {
-  const PipelineParams& p = *cx.p;
-  uint32_t raise = 0;
-  uint32_t pass = eval_filter(cx, raise);
-  uint64_t key[4];
-  uint32_t keynull;
-  compute_keys(cx, pass, raise, key, keynull);
-  uint32_t acc_err = 0;
-  HashRef href;
-  href.table = p.table; href.cap_mask = p.cap_mask; href.row_words = p.row_words; href.n_groups_ctr = p.n_groups_ctr;
-  // Rows of a thread are adjacent in the input; fold a row into its left neighbour's slot lookup
-  // when the keys are equal (sorted / clustered keys such as l_orderkey).
-  int64_t slot[4];
+// Thread-private tables.  The thread first folds rows of the same group together in registers
+// (cx.prev names the previous row of the same group), then does one read-modify-write per
+// distinct group with all loads issued before the stores: no two of those touch one address.
+template <int KIND>
+__device__ __forceinline__ void accum_thread(Ctx& cx, char* cbase, const uint64_t v[4], uint32_t live) {
+  const uint64_t idv = cell_identity(KIND);
+  uint64_t x[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    slot[j] = -1;
-    if (!((pass >> j) & 1u)) continue;
-    const bool isnull = (keynull >> j) & 1u;
-    if ((j & 1) && ((pass >> (j - 1)) & 1u) && key[j] == key[j - 1] &&
-        isnull == (bool)((keynull >> (j - 1)) & 1u)) {
-      slot[j] = slot[j - 1];
-    } else {
-      slot[j] = hash_find_or_insert(href, key[j], isnull, acc_err);
-    }
-    if (slot[j] < 0) pass &= ~(1u << j);
+    const bool on = (live >> j) & 1u;
+    if (KIND == kCellCount) x[j] = on ? 1u : 0u;
+    else if (KIND == kCellMinF64 || KIND == kCellMaxF64) x[j] = (on && u2d(v[j]) == u2d(v[j])) ? v[j] : idv;
+    else x[j] = on ? v[j] : idv;
   }
-  vgpu_op dummy;
-  dummy.imm.i = 0;
-  for (int c = 0; c < p.n_cells; ++c) {
-    const DevCell cell = p.cells[c];
-    if (cell.skip) continue;
-    Val v;
-    uint32_t live = pass;
-    uint8_t in_type = VGPU_BIGINT;
-    if (cell.input >= 0) {
-      const vgpu_operand o = p.outputs[cell.input];
-      in_type = o.type;
-      if (o.type == VGPU_BOOLEAN) {
-        BoolVal b;
-        load_bool(cx, dummy, o, b);
-        raise |= b.e & pass;
-        live &= ~b.n;
+  const uint32_t p1 = (cx.prev >> 2) & 3u, p2 = (cx.prev >> 4) & 3u, p3 = (cx.prev >> 6) & 3u;
+  x[1] = cell_comb<KIND>(p1 ? x[0] : idv, x[1], cx.acc_err);
+  x[2] = cell_comb<KIND>(p2 == 2 ? x[1] : (p2 == 1 ? x[0] : idv), x[2], cx.acc_err);
+  x[3] = cell_comb<KIND>(p3 == 3 ? x[2] : (p3 == 2 ? x[1] : (p3 == 1 ? x[0] : idv)), x[3], cx.acc_err);
+  if (KIND == kCellCount) {
+    uint32_t* t = reinterpret_cast<uint32_t*>(cbase);
+    uint32_t old[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) v.v[j] = (b.v >> j) & 1u;
-      } else {
-        load_value(cx, dummy, o, 0, v);
-        raise |= v.e & pass;
-        live &= ~v.n;
-      }
-    } else {
+    for (int j = 0; j < 4; ++j) old[j] = ((cx.store >> j) & 1u) ? t[cx.goff[j]] : 0u;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) v.v[j] = 0;
+    for (int j = 0; j < 4; ++j) if ((cx.store >> j) & 1u) t[cx.goff[j]] = old[j] + (uint32_t)x[j];
+  } else {
+    uint64_t* t = reinterpret_cast<uint64_t*>(cbase);
+    uint64_t old[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) old[j] = ((cx.store >> j) & 1u) ? t[cx.goff[j]] : idv;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) if ((cx.store >> j) & 1u) t[cx.goff[j]] = cell_comb<KIND>(old[j], x[j], cx.acc_err);
+  }
+}
+
+// Warp-private tables (more groups than per-thread tables can hold): shared-memory atomics.
+// MIN/MAX read first and only go atomic when the row improves the cell, which is rare once the
+// cell has seen a few rows.
+template <int KIND>
+__device__ __forceinline__ void accum_warp(Ctx& cx, char* cbase, const uint64_t v[4], uint32_t live) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (!((live >> j) & 1u)) continue;
+    if (KIND == kCellCount) {
+      atomicAdd(reinterpret_cast<uint32_t*>(cbase) + cx.goff[j], 1u);
+      continue;
     }
-#pragma unroll
-    for (int pr = 0; pr < 2; ++pr) {
-      const int j0 = 2 * pr, j1 = 2 * pr + 1;
-      const bool a0 = (live >> j0) & 1u, a1 = (live >> j1) & 1u;
-      uint64_t x0 = cell_input(cell.kind, in_type, v.v[j0]);
-      const uint64_t x1 = cell_input(cell.kind, in_type, v.v[j1]);
-      // pre-combine the pair when both rows fall in the same group (sum / count only)
-      if (a0 && a1 && slot[j0] == slot[j1] && cell.kind == kCellSumF64) {
-        // Keep row order: (x0 + x1) then one atomic.
-        x0 = d2u(__dadd_rn(u2d(x0), u2d(x1)));
-        update_hbm_cell(cell.kind, p.table + slot[j0] * p.row_words + 1 + c, x0, acc_err);
-        continue;
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(cbase) + cx.goff[j];
+    if (KIND == kCellSumF64) {
+      atomicAdd(reinterpret_cast<double*>(a), u2d(v[j]));
+    } else if (KIND == kCellSumI64) {
+      const int64_t y = (int64_t)v[j];
+      const int64_t x = (int64_t)atomicAdd(a, (unsigned long long)v[j]);
+      const int64_t z = (int64_t)((uint64_t)x + (uint64_t)y);
+      if (((x ^ z) & (y ^ z)) < 0) cx.acc_err |= kErrOverflow;
+    } else if (KIND == kCellMinI64) {
+      if ((int64_t)v[j] < (int64_t)*reinterpret_cast<volatile unsigned long long*>(a)) atomicMin(reinterpret_cast<long long*>(a), (long long)v[j]);
+    } else if (KIND == kCellMaxI64) {
+      if ((int64_t)*reinterpret_cast<volatile unsigned long long*>(a) < (int64_t)v[j]) atomicMax(reinterpret_cast<long long*>(a), (long long)v[j]);
+    } else {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(a);
+      while (KIND == kCellMinF64 ? u2d(v[j]) < u2d(cur) : u2d(cur) < u2d(v[j])) {
+        const unsigned long long seen = atomicCAS(a, cur, (unsigned long long)v[j]);
+        if (seen == cur) break;
+        cur = seen;
       }
-      if (a0) update_hbm_cell(cell.kind, p.table + slot[j0] * p.row_words + 1 + c, x0, acc_err);
-      if (a1) update_hbm_cell(cell.kind, p.table + slot[j1] * p.row_words + 1 + c, x1, acc_err);
     }
   }
-  if (raise) atomicOr(p.err_word, raised_code(cx.ecode, raise));
-  if (acc_err) atomicOr(p.err_word, acc_err);
+}
+
+template <int KIND>
+__device__ __forceinline__ void accum_array(Ctx& cx, char* cbase, const uint64_t v[4], uint32_t live) {
+  if (cx.p->warp_private) accum_warp<KIND>(cx, cbase, v, live);
+  else accum_thread<KIND>(cx, cbase, v, live);
+}
+
+// ------------------------------------------------------------------------------------------
+// The interpreter: one pass over the micro-op stream for the thread's 4 rows.
+// ------------------------------------------------------------------------------------------
+template <int MODE>
+__device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int cnt) {
+  const PipelineParams& p = *cx.p;
+#pragma unroll 1
+  for (int i = 0; i < p.n_mops; ++i) {
+    const MOp& op = p.mops[i];
+    switch (op.h) {
+      case H_LD: {
+        fetch(cx, op.x, cx.acc);
+        if (op.flags & MF_STORE) store_slot(cx, op, cx.acc);
+        break;
+      }
+      case H_ARITH: {
+        Val a, r;
+        fetch(cx, op.x, a);
+        const uint8_t oc = op.sub, type = op.type;
+        if (oc == VGPU_OP_NEG) {
+          r.n = a.n; r.e = a.e;
+          uint32_t bad = 0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            r.v[j] = 0;
+            const uint32_t err = arith(oc, type, a.v[j], 0, r.v[j]);
+            if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
+          }
+          r.e |= bad;
+        } else {
+          Val b;
+          fetch(cx, op.y, b);
+          r.n = a.n | b.n;
+          r.e = a.e | b.e;
+          if (type == VGPU_DOUBLE && oc <= VGPU_OP_MUL) {
+            // hot path of Q1/Q6: plain IEEE double ops, dispatch hoisted out of the row loop
+            if (oc == VGPU_OP_MUL) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dmul_rn(u2d(a.v[j]), u2d(b.v[j])));
+            } else if (oc == VGPU_OP_ADD) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dadd_rn(u2d(a.v[j]), u2d(b.v[j])));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) r.v[j] = d2u(__dsub_rn(u2d(a.v[j]), u2d(b.v[j])));
+            }
+          } else {
+            uint32_t bad = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              r.v[j] = 0;
+              const uint32_t err = arith(oc, type, a.v[j], b.v[j], r.v[j]);
+              if (err && !((r.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
+            }
+            r.e |= bad;
+          }
+        }
+        cx.acc = r;
+        if (op.flags & MF_STORE) store_slot(cx, op, r);
+        break;
+      }
+      case H_CAST: {
+        Val a, r;
+        fetch(cx, op.x, a);
+        r.n = a.n; r.e = a.e;
+        uint32_t bad = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          r.v[j] = 0;
+          const uint32_t err = cast_value(op.x.type, op.type, a.v[j], r.v[j]);
+          if (err && !((a.n >> j) & 1u) && ((cx.valid >> j) & 1u)) { bad |= 1u << j; cx.ecode |= err << (8 * j); }
+        }
+        r.e |= bad;
+        cx.acc = r;
+        if (op.flags & MF_STORE) store_slot(cx, op, r);
+        break;
+      }
+      case H_CMP: {
+        BoolVal r;
+        const uint8_t oc = op.sub;
+        if (op.type == VGPU_BOOLEAN) { // boolean = / <> boolean
+          BoolVal a, b;
+          fetchb(cx, op.x, a);
+          fetchb(cx, op.y, b);
+          const uint32_t x = a.v ^ b.v;
+          r.v = (oc == VGPU_OP_EQ ? ~x : x) & 0xFu;
+          r.n = a.n | b.n;
+          r.e = a.e | b.e;
+        } else if (op.x.kind == XK_COL4I && op.y.kind == XK_IMM && (oc != VGPU_OP_BETWEEN || op.z.kind == XK_IMM)) {
+          // INTEGER / DATE column against literals: 32-bit compares straight off the staged tile
+          const uint2* s = reinterpret_cast<const uint2*>(cx.stage + op.x.off);
+          const uint2 q0 = s[cx.pos0 >> 1];
+          const uint2 q1 = s[cx.pos1 >> 1];
+          const int32_t a[4] = {(int32_t)q0.x, (int32_t)q0.y, (int32_t)q1.x, (int32_t)q1.y};
+          if (oc == VGPU_OP_BETWEEN) r.v = cmp4_i32(VGPU_OP_GE, a, (int32_t)op.y.imm) & cmp4_i32(VGPU_OP_LE, a, (int32_t)op.z.imm);
+          else r.v = cmp4_i32(oc, a, (int32_t)op.y.imm);
+          r.n = op.x.has_nulls ? (~quad_bits(cx, op.x.noff)) & 0xFu : 0u;
+          r.e = 0;
+        } else {
+          Val a, b;
+          fetch(cx, op.x, a);
+          fetch(cx, op.y, b);
+          r.n = a.n | b.n;
+          r.e = a.e | b.e;
+          if (oc == VGPU_OP_BETWEEN) {
+            Val c;
+            fetch(cx, op.z, c);
+            r.n |= c.n;
+            r.e |= c.e;
+            r.v = cmp4(VGPU_OP_GE, op.type, a.v, b.v) & cmp4(VGPU_OP_LE, op.type, a.v, c.v);
+          } else {
+            r.v = cmp4(oc, op.type, a.v, b.v);
+          }
+        }
+        r.v &= ~r.n;
+        if (op.flags & MF_COMB_AND) r = and3(cx.bacc, r);
+        else if (op.flags & MF_COMB_OR) r = or3(cx.bacc, r);
+        cx.bacc = r;
+        if (op.flags & MF_STORE) reinterpret_cast<uint32_t*>(cx.smem + op.dst)[threadIdx.x] = r.v | (r.n << 8) | (r.e << 16);
+        break;
+      }
+      case H_BOOL: {
+        BoolVal r;
+        const uint8_t oc = op.sub;
+        if (oc == VGPU_OP_IS_NULL) {
+          if (op.x.type == VGPU_BOOLEAN) {
+            BoolVal a;
+            fetchb(cx, op.x, a);
+            r.v = a.n; r.e = a.e;
+          } else {
+            Val a;
+            fetch(cx, op.x, a);
+            r.v = a.n; r.e = a.e;
+          }
+          r.n = 0;
+        } else {
+          BoolVal a;
+          fetchb(cx, op.x, a);
+          if (oc == VGPU_OP_NOT) {
+            r.v = (~a.v) & 0xFu; r.n = a.n; r.e = a.e;
+          } else {
+            BoolVal b;
+            fetchb(cx, op.y, b);
+            r = (oc == VGPU_OP_AND) ? and3(a, b) : or3(a, b);
+          }
+        }
+        cx.bacc = r;
+        if (op.flags & MF_STORE) reinterpret_cast<uint32_t*>(cx.smem + op.dst)[threadIdx.x] = r.v | (r.n << 8) | (r.e << 16);
+        break;
+      }
+      case H_FILTER: {
+        if (op.x.kind == XK_NONE) {
+          cx.pass = cx.valid;
+        } else {
+          BoolVal f;
+          fetchb(cx, op.x, f);
+          cx.raise |= f.e & cx.valid;
+          cx.pass = f.v & ~f.n & ~f.e & cx.valid;
+        }
+        break;
+      }
+      case H_KEY: {
+        const DevKey& ks = p.keys[op.dst];
+        Val v;
+        fetch(cx, op.x, v);
+        cx.raise |= v.e & cx.pass;
+        if (p.ignore_null_keys) cx.pass &= ~v.n;
+        if (MODE == kSinkHash && ks.bits == 64) { // raw 64-bit key
+#pragma unroll
+          for (int j = 0; j < 4; ++j) cx.key[j] = v.v[j];
+          cx.keynull = v.n;
+          break;
+        }
+        uint32_t bad = 0;
+        const uint64_t span = (uint64_t)(ks.max - ks.min);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint64_t u = v.v[j] - (uint64_t)ks.min;
+          const bool isnull = (v.n >> j) & 1u;
+          if (isnull ? !ks.nullable : u > span) bad |= 1u << j;
+          const uint32_t id = isnull ? 0u : (uint32_t)u + ks.nullable;
+          if (MODE == kSinkHash) cx.key[j] += (uint64_t)id << ks.shift;
+          else cx.goff[j] += id * (uint32_t)ks.mult;
+        }
+        if (bad & cx.pass) {
+          cx.ecode |= kErrKeyRange * 0x01010101u;
+          cx.raise |= bad & cx.pass;
+          cx.pass &= ~bad;
+        }
+        break;
+      }
+      case H_KEYEND: {
+        if (MODE == kSinkArray) {
+          if (p.warp_private) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) cx.goff[j] = ((cx.pass >> j) & 1u) ? cx.goff[j] : 0u;
+          } else {
+            uint32_t* g = cx.goff;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) g[j] = (((cx.pass >> j) & 1u) ? g[j] * kThreads : 0u) + threadIdx.x;
+            const bool e01 = g[0] == g[1], e02 = g[0] == g[2], e03 = g[0] == g[3];
+            const bool e12 = g[1] == g[2], e13 = g[1] == g[3], e23 = g[2] == g[3];
+            const uint32_t p1 = e01 ? 1u : 0u;
+            const uint32_t p2 = e12 ? 2u : (e02 ? 1u : 0u);
+            const uint32_t p3 = e23 ? 3u : (e13 ? 2u : (e03 ? 1u : 0u));
+            cx.prev = (p1 << 2) | (p2 << 4) | (p3 << 6);
+            cx.store = (!(e01 | e02 | e03) ? 1u : 0u) | (!(e12 | e13) ? 2u : 0u) | (!e23 ? 4u : 0u) | 8u;
+          }
+        } else if (MODE == kSinkHash) {
+          HashRef href;
+          href.table = p.table; href.cap_mask = p.cap_mask; href.row_words = p.row_words; href.n_groups_ctr = p.n_groups_ctr;
+          // Rows of a thread are adjacent in the input; a row reuses its left neighbour's slot
+          // when the keys are equal (sorted / clustered keys such as l_orderkey).
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            cx.slot[j] = -1;
+            if (!((cx.pass >> j) & 1u)) continue;
+            const bool isnull = (cx.keynull >> j) & 1u;
+            if ((j & 1) && ((cx.pass >> (j - 1)) & 1u) && cx.key[j] == cx.key[j - 1] &&
+                isnull == (bool)((cx.keynull >> (j - 1)) & 1u)) {
+              cx.slot[j] = cx.slot[j - 1];
+            } else {
+              cx.slot[j] = hash_find_or_insert(href, cx.key[j], isnull, cx.acc_err);
+            }
+            if (cx.slot[j] < 0) cx.pass &= ~(1u << j);
+          }
+        }
+        break;
+      }
+      case H_ACCUM: {
+        Val v;
+        uint32_t live = cx.pass;
+        if (op.flags & MF_NO_VALUE) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v.v[j] = 0;
+        } else if (op.x.type == VGPU_BOOLEAN) {
+          BoolVal b;
+          fetchb(cx, op.x, b);
+          cx.raise |= b.e & cx.pass;
+          live &= ~b.n;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v.v[j] = (b.v >> j) & 1u;
+        } else {
+          fetch(cx, op.x, v);
+          cx.raise |= v.e & cx.pass;
+          live &= ~v.n;
+        }
+        const uint8_t kind = op.sub;
+        if (kind == kCellSumF64 && !is_fp(op.x.type)) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v.v[j] = d2u((double)(int64_t)v.v[j]);
+        }
+        if (MODE == kSinkArray) {
+          char* cbase = tab + op.dst + (p.warp_private ? (threadIdx.x >> 5) * p.warp_tab_bytes : 0);
+          switch (kind) {
+            case kCellSumF64: accum_array<kCellSumF64>(cx, cbase, v.v, live); break;
+            case kCellCount: accum_array<kCellCount>(cx, cbase, v.v, live); break;
+            case kCellSumI64: accum_array<kCellSumI64>(cx, cbase, v.v, live); break;
+            case kCellMinI64: accum_array<kCellMinI64>(cx, cbase, v.v, live); break;
+            case kCellMaxI64: accum_array<kCellMaxI64>(cx, cbase, v.v, live); break;
+            case kCellMinF64: accum_array<kCellMinF64>(cx, cbase, v.v, live); break;
+            default: accum_array<kCellMaxF64>(cx, cbase, v.v, live);
+          }
+        } else if (MODE == kSinkHash) {
+          const int c = op.dst; // cell index inside the table row
+#pragma unroll
+          for (int pr = 0; pr < 2; ++pr) {
+            const int j0 = 2 * pr, j1 = 2 * pr + 1;
+            const bool a0 = (live >> j0) & 1u, a1 = (live >> j1) & 1u;
+            uint64_t x0 = v.v[j0];
+            const uint64_t x1 = v.v[j1];
+            // pre-combine the pair when both rows fall in the same group (row order kept)
+            if (a0 && a1 && cx.slot[j0] == cx.slot[j1] && kind == kCellSumF64) {
+              x0 = d2u(__dadd_rn(u2d(x0), u2d(x1)));
+              update_hbm_cell(kind, p.table + cx.slot[j0] * p.row_words + 1 + c, x0, cx.acc_err);
+              continue;
+            }
+            if (a0) update_hbm_cell(kind, p.table + cx.slot[j0] * p.row_words + 1 + c, x0, cx.acc_err);
+            if (a1) update_hbm_cell(kind, p.table + cx.slot[j1] * p.row_words + 1 + c, x1, cx.acc_err);
+          }
+        }
+        break;
+      }
+      case H_SEL: {
+        if (MODE == kSinkFilterProject) {
+          store_tile_bits(p.sel_words, tile * (kTile / 32), (cnt + 31) >> 5, cx.pass);
+          int wsum = __popc(cx.pass);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+          if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(&p.tile_counts[tile], wsum);
+        }
+        break;
+      }
+      case H_PROJ: {
+        if (MODE == kSinkFilterProject) {
+          const DevOut out = p.outs[op.dst];
+          const int64_t word_base = tile * (kTile / 32);
+          const int n_words = (cnt + 31) >> 5;
+          const bool full = cnt == kTile;
+          uint32_t nmask;
+          const int64_t r0 = tile * kTile + cx.pos0, r1 = tile * kTile + cx.pos1;
+          if (op.x.type == VGPU_BOOLEAN) {
+            BoolVal b;
+            fetchb(cx, op.x, b);
+            cx.raise |= b.e & cx.pass;
+            nmask = b.n;
+            store_tile_bits(reinterpret_cast<uint32_t*>(out.values), word_base, n_words, b.v);
+          } else {
+            Val v;
+            fetch(cx, op.x, v);
+            cx.raise |= v.e & cx.pass;
+            nmask = v.n;
+            const uint8_t t = op.x.type;
+            const int lg = elem_bytes_log2(t);
+            if (t == VGPU_REAL) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) v.v[j] = __float_as_uint((float)u2d(v.v[j]));
+            }
+            if (full && lg == 3) {
+              uint4* d = reinterpret_cast<uint4*>(out.values);
+              d[r0 >> 1] = make_uint4((uint32_t)v.v[0], (uint32_t)(v.v[0] >> 32), (uint32_t)v.v[1], (uint32_t)(v.v[1] >> 32));
+              d[r1 >> 1] = make_uint4((uint32_t)v.v[2], (uint32_t)(v.v[2] >> 32), (uint32_t)v.v[3], (uint32_t)(v.v[3] >> 32));
+            } else if (full && lg == 2) {
+              uint2* d = reinterpret_cast<uint2*>(out.values);
+              d[r0 >> 1] = make_uint2((uint32_t)v.v[0], (uint32_t)v.v[1]);
+              d[r1 >> 1] = make_uint2((uint32_t)v.v[2], (uint32_t)v.v[3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (!((cx.valid >> j) & 1u)) continue;
+                const int64_t r = (j < 2 ? r0 : r1) + (j & 1);
+                switch (lg) {
+                  case 0: reinterpret_cast<uint8_t*>(out.values)[r] = (uint8_t)v.v[j]; break;
+                  case 1: reinterpret_cast<uint16_t*>(out.values)[r] = (uint16_t)v.v[j]; break;
+                  case 2: reinterpret_cast<uint32_t*>(out.values)[r] = (uint32_t)v.v[j]; break;
+                  default: reinterpret_cast<uint64_t*>(out.values)[r] = v.v[j];
+                }
+              }
+            }
+          }
+          if (out.nulls != nullptr) {
+            store_tile_bits(reinterpret_cast<uint32_t*>(out.nulls), word_base, n_words, ~nmask & cx.valid & 0xFu);
+          }
+        }
+        break;
+      }
+      default:
+        break;
+    }
+  }
+  if (cx.raise) atomicOr(p.err_word, raised_code(cx.ecode, cx.raise));
+  if (cx.acc_err) atomicOr(p.err_word, cx.acc_err);
 }
 
 // ---- per-CTA fold of the partial tables (ARRAY mode), fixed order => run-to-run deterministic ---
@@ -1161,9 +1125,7 @@ pipeline_kernel(const __grid_constant__ PipelineParams p) {
   char* stages = smem + 128;
   Ctx cx;
   cx.p = &p;
-  cx.slots = reinterpret_cast<uint64_t*>(smem + p.smem_slots_off);
-  cx.meta = reinterpret_cast<uint32_t*>(smem + p.smem_meta_off);
-  cx.bmeta = reinterpret_cast<uint32_t*>(smem + p.smem_bmeta_off);
+  cx.smem = smem;
   char* tab = smem + p.smem_tab_off;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   cx.pos0 = warp * 128 + 2 * lane;
@@ -1204,23 +1166,30 @@ pipeline_kernel(const __grid_constant__ PipelineParams p) {
       if (t < n_full) issue_tile(p, stages + (size_t)s * p.stage_bytes, &bars[s], t * kTile);
     }
   }
-  bool any_bulk = false;
-  for (int c = 0; c < p.n_cols; ++c) any_bulk |= (p.cols[c].bulk_ok != 0) && (p.cols[c].stage_off >= 0 || p.cols[c].nulls_off >= 0);
+  bool any_bulk = false, any_generic = false;
+  for (int c = 0; c < p.n_cols; ++c) {
+    const bool staged = p.cols[c].stage_off >= 0 || p.cols[c].nulls_off >= 0;
+    any_bulk |= staged && p.cols[c].bulk_ok != 0;
+    any_generic |= staged && p.cols[c].bulk_ok == 0;
+  }
 
-  int it = 0;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-    const int s = it % S;
+  int s = 0;
+  uint32_t parity = 0;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     char* stage = stages + (size_t)s * p.stage_bytes;
     const int64_t row0 = tile * kTile;
     const int cnt = (int)min((int64_t)kTile, p.n_rows - row0);
     const bool bulk = tile < n_full;
     if (bulk) {
-      if (any_bulk) mbar_wait(&bars[s], (uint32_t)((it / S) & 1));
-      stage_generic(p, stage, row0, cnt, false); // columns the bulk engine could not take
+      if (any_bulk) mbar_wait(&bars[s], parity);
+      if (any_generic) { // columns the bulk engine could not take
+        stage_generic(p, stage, row0, cnt, false);
+        __syncthreads();
+      }
     } else {
       stage_generic(p, stage, row0, cnt, true);
+      __syncthreads();
     }
-    __syncthreads();
     cx.stage = stage;
     cx.valid = 0;
 #pragma unroll
@@ -1230,11 +1199,16 @@ pipeline_kernel(const __grid_constant__ PipelineParams p) {
     }
     cx.acc.n = cx.acc.e = 0;
     cx.bacc.v = cx.bacc.n = cx.bacc.e = 0;
-    run_program(cx);
-    if (MODE == kSinkFilterProject) sink_filter_project(cx, tile, cnt);
-    else if (MODE == kSinkArray) sink_array(cx, tab);
-    else sink_hash(cx);
-    __syncthreads(); // every thread is done reading this stage
+    cx.pass = cx.valid;
+    cx.raise = 0;
+    cx.acc_err = 0;
+    cx.prev = 0;
+    cx.store = 0xFu;
+    cx.keynull = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { cx.goff[j] = 0; cx.key[j] = 0; cx.slot[j] = -1; }
+    run_mops<MODE>(cx, tab, tile, cnt);
+    __syncthreads(); // every thread is done reading this stage (and the slots)
     if (tid == 0) {
       const int64_t next = tile + (int64_t)S * gridDim.x;
       if (next < n_full) {
@@ -1242,6 +1216,7 @@ pipeline_kernel(const __grid_constant__ PipelineParams p) {
         issue_tile(p, stage, &bars[s], next * kTile);
       }
     }
+    if (++s == S) { s = 0; parity ^= 1u; }
   }
   if (MODE == kSinkArray) {
     __syncthreads();
@@ -1316,7 +1291,7 @@ __global__ void expand_selection(const uint32_t* words, const int64_t* offsets, 
 }
 
 // ------------------------------------------------------------------------------------------
-// Host side: planning and launch
+// Host side: planning, lowering to micro-ops and launch
 // ------------------------------------------------------------------------------------------
 static int host_elem_log2(int type) {
   switch (type) {
@@ -1350,17 +1325,15 @@ int plan_pipeline(const Program& prog, const vgpu_column* cols, int32_t ncols, i
     set_error("at most %d input columns per pipeline, got %d", kMaxCols, ncols);
     return VGPU_ERR_UNSUPPORTED;
   }
-  p.n_ops = (int)prog.ops.size();
-  for (int i = 0; i < p.n_ops; ++i) p.ops[i] = prog.ops[i];
+  p.prog = &prog;
   p.n_outputs = (int)prog.outputs.size();
   for (int i = 0; i < p.n_outputs; ++i) p.outputs[i] = prog.outputs[i];
-  p.filter = prog.filter;
   p.n_cols = ncols;
   p.n_slots = prog.n_slots;
   p.n_bslots = prog.n_bslots;
   p.in_rows = in_rows;
   p.n_rows = in_rows ? n_in_rows : nrows;
-  p.err_word = device_err_word();
+  p.err_word = fused_dry_run() ? nullptr : device_err_word();
 
   bool used[kMaxCols] = {false};
   for (const auto& op : prog.ops) { mark_used(op.a, used); mark_used(op.b, used); mark_used(op.c, used); }
@@ -1395,35 +1368,263 @@ int plan_pipeline(const Program& prog, const vgpu_column* cols, int32_t ncols, i
   return VGPU_OK;
 }
 
-bool output_nullable(const PipelineParams& p, int idx) {
+// ---- nullability / error analysis of the ABI program ------------------------------------------
+struct Flow {
   bool slot_n[kMaxSlots + 1] = {false}, bslot_n[kMaxSlots + 1] = {false};
   bool acc_n = false, bacc_n = false;
-  auto opnd = [&](const vgpu_operand& o) -> bool {
-    switch (o.kind) {
-      case VGPU_OPND_ACC: return o.type == VGPU_BOOLEAN ? bacc_n : acc_n;
-      case VGPU_OPND_SLOT: return o.type == VGPU_BOOLEAN ? bslot_n[std::min<int>(o.index, kMaxSlots)] : slot_n[std::min<int>(o.index, kMaxSlots)];
-      case VGPU_OPND_COL: {
-        const DevCol& c = p.cols[o.index];
-        if (c.encoding == VGPU_CONSTANT) return c.const_null != 0;
-        return c.nulls != nullptr || c.base_nulls != nullptr;
-      }
-      case VGPU_OPND_NULL: return true;
-      default: return false;
-    }
-  };
-  for (int i = 0; i < p.n_ops; ++i) {
-    const vgpu_op& op = p.ops[i];
-    bool n = false;
-    if (op.opcode != VGPU_OP_IS_NULL) {
-      if (op.a.kind != VGPU_OPND_NONE) n |= opnd(op.a);
-      if (op.b.kind != VGPU_OPND_NONE) n |= opnd(op.b);
-      if (op.c.kind != VGPU_OPND_NONE) n |= opnd(op.c);
-    }
-    const bool is_bool = op.opcode >= VGPU_OP_EQ && op.opcode <= VGPU_OP_IS_NULL;
-    if (is_bool) { bacc_n = n; if (op.dst_slot >= 0) bslot_n[std::min<int>(op.dst_slot, kMaxSlots)] = n; }
-    else { acc_n = n; if (op.dst_slot >= 0) slot_n[std::min<int>(op.dst_slot, kMaxSlots)] = n; }
+};
+static bool col_nullable(const DevCol& c) {
+  if (c.encoding == VGPU_CONSTANT) return c.const_null != 0;
+  return c.nulls != nullptr || c.base_nulls != nullptr;
+}
+static bool opnd_dirty(const PipelineParams& p, const Flow& f, const vgpu_operand& o) {
+  switch (o.kind) {
+    case VGPU_OPND_ACC: return o.type == VGPU_BOOLEAN ? f.bacc_n : f.acc_n;
+    case VGPU_OPND_SLOT: return o.type == VGPU_BOOLEAN ? f.bslot_n[std::min<int>(o.index, kMaxSlots)] : f.slot_n[std::min<int>(o.index, kMaxSlots)];
+    case VGPU_OPND_COL: return col_nullable(p.cols[o.index]);
+    case VGPU_OPND_NULL: return true;
+    default: return false;
   }
-  return opnd(p.outputs[idx]);
+}
+static bool op_is_bool(int oc) { return oc >= VGPU_OP_EQ && oc <= VGPU_OP_IS_NULL; }
+// with_errors: also count "may carry a latched error" (integer arithmetic, casts).
+static void flow_step(const PipelineParams& p, Flow& f, const vgpu_op& op, bool with_errors) {
+  bool n = false;
+  if (op.opcode != VGPU_OP_IS_NULL || with_errors) {
+    if (op.a.kind != VGPU_OPND_NONE) n |= opnd_dirty(p, f, op.a);
+    if (op.b.kind != VGPU_OPND_NONE) n |= opnd_dirty(p, f, op.b);
+    if (op.c.kind != VGPU_OPND_NONE) n |= opnd_dirty(p, f, op.c);
+  }
+  if (with_errors) {
+    const bool fp = op.type == VGPU_REAL || op.type == VGPU_DOUBLE;
+    if (op.opcode == VGPU_OP_CAST) n = true;
+    if (op.opcode >= VGPU_OP_ADD && op.opcode <= VGPU_OP_MOD && !fp) n = true;
+  }
+  if (op_is_bool(op.opcode)) { f.bacc_n = n; if (op.dst_slot >= 0) f.bslot_n[std::min<int>(op.dst_slot, kMaxSlots)] = n; }
+  else { f.acc_n = n; if (op.dst_slot >= 0) f.slot_n[std::min<int>(op.dst_slot, kMaxSlots)] = n; }
+}
+
+bool output_nullable(const PipelineParams& p, int idx) {
+  Flow f;
+  for (const vgpu_op& op : p.prog->ops) flow_step(p, f, op, false);
+  return opnd_dirty(p, f, p.outputs[idx]);
+}
+
+// ---- lowering: ABI ops + sink -> micro-ops ------------------------------------------------------
+namespace {
+struct MopInfo {
+  int st_v = -1, st_b = -1;          // slot stored by the mop (value / boolean numbering)
+  int rd_v[3] = {-1, -1, -1}, rd_b[3] = {-1, -1, -1};
+};
+
+struct Lowerer {
+  PipelineParams& p;
+  Flow f;                 // nullability + latched-error flow ("dirty")
+  MopInfo info[kMaxMops];
+  int n = 0;
+  int acc_mirror = -1;    // value slot whose content equals the value accumulator
+  int bacc_mirror = -1;   // boolean slot whose content equals the boolean accumulator
+  int bacc_mirror_prev = -1;
+  bool overflow = false;
+  bool bad_output = false;
+
+  explicit Lowerer(PipelineParams& pp) : p(pp) {}
+
+  MOp* emit(uint8_t h) {
+    if (n >= kMaxMops) { overflow = true; n = kMaxMops - 1; }
+    MOp& m = p.mops[n];
+    m = MOp{};
+    m.h = h;
+    m.dst = -1; m.dstn = -1;
+    info[n] = MopInfo{};
+    return &p.mops[n++];
+  }
+
+  XOp opnd(const vgpu_operand& o, uint64_t imm, int which) {
+    XOp x{};
+    x.type = o.type;
+    MopInfo& mi = info[n - 1];
+    switch (o.kind) {
+      case VGPU_OPND_NONE: x.kind = XK_NONE; break;
+      case VGPU_OPND_ACC: x.kind = XK_ACC; break;
+      case VGPU_OPND_IMM: x.kind = XK_IMM; x.imm = imm; break;
+      case VGPU_OPND_NULL: x.kind = XK_NULL; break;
+      case VGPU_OPND_SLOT:
+        if (o.type == VGPU_BOOLEAN) {
+          if (bacc_mirror == (int)o.index) { x.kind = XK_ACC; break; }
+          x.kind = XK_BSLOT;
+          x.off = p.smem_bmeta_off + o.index * kThreads * 4;
+          mi.rd_b[which] = o.index;
+        } else {
+          if (acc_mirror == (int)o.index) { x.kind = XK_ACC; break; }
+          x.kind = XK_SLOT;
+          x.off = p.smem_slots_off + o.index * kTile * 8;
+          x.noff = p.smem_meta_off + o.index * kThreads * 4;
+          x.has_nulls = f.slot_n[o.index] ? 1 : 0;
+          mi.rd_v[which] = o.index;
+        }
+        break;
+      default: { // column
+        const DevCol& c = p.cols[o.index];
+        x.col = (uint8_t)o.index;
+        x.type = c.type;
+        if (c.encoding == VGPU_CONSTANT) {
+          if (c.const_null) x.kind = XK_NULL; else { x.kind = XK_IMM; x.imm = (uint64_t)c.constant; }
+          break;
+        }
+        x.off = c.stage_off;
+        x.noff = c.nulls_off;
+        x.has_nulls = c.nulls_off >= 0 ? 1 : 0;
+        if (c.encoding == VGPU_DICTIONARY) { x.kind = c.type == VGPU_BOOLEAN ? XK_BDICT : XK_DICT; break; }
+        switch (c.type) {
+          case VGPU_BOOLEAN: x.kind = XK_BCOL; break;
+          case VGPU_TINYINT: x.kind = XK_COL1; break;
+          case VGPU_SMALLINT: x.kind = XK_COL2; break;
+          case VGPU_INTEGER: x.kind = XK_COL4I; break;
+          case VGPU_REAL: x.kind = XK_COL4F; break;
+          default: x.kind = XK_COL8;
+        }
+      }
+    }
+    return x;
+  }
+
+  void store(MOp* m, const vgpu_op& op, bool is_bool, bool dirty) {
+    if (op.dst_slot < 0) return;
+    m->flags |= MF_STORE;
+    if (is_bool) {
+      m->dst = p.smem_bmeta_off + op.dst_slot * kThreads * 4;
+      info[n - 1].st_b = op.dst_slot;
+    } else {
+      m->dst = p.smem_slots_off + op.dst_slot * kTile * 8;
+      m->dstn = dirty ? p.smem_meta_off + op.dst_slot * kThreads * 4 : -1;
+      info[n - 1].st_v = op.dst_slot;
+    }
+  }
+
+  void lower_op(const vgpu_op& op) {
+    const int oc = op.opcode;
+    const bool is_bool = op_is_bool(oc);
+    // AND/OR of (boolean slot the accumulator mirrored before the last compare) with that
+    // compare: fold into the compare (Q6's conjunct chain becomes one micro-op per conjunct).
+    if ((oc == VGPU_OP_AND || oc == VGPU_OP_OR) && n > 0 && p.mops[n - 1].h == H_CMP &&
+        !(p.mops[n - 1].flags & (MF_STORE | MF_COMB_AND | MF_COMB_OR))) {
+      const vgpu_operand* slot = nullptr;
+      if (op.a.kind == VGPU_OPND_SLOT && op.b.kind == VGPU_OPND_ACC) slot = &op.a;
+      if (op.b.kind == VGPU_OPND_SLOT && op.a.kind == VGPU_OPND_ACC) slot = &op.b;
+      if (slot && bacc_mirror_prev == (int)slot->index) {
+        MOp* m = &p.mops[n - 1];
+        m->flags |= (oc == VGPU_OP_AND) ? MF_COMB_AND : MF_COMB_OR;
+        flow_step(p, f, op, true);
+        store(m, op, true, true);
+        bacc_mirror = op.dst_slot;
+        return;
+      }
+    }
+    MOp* m;
+    if (oc >= VGPU_OP_ADD && oc <= VGPU_OP_MOD) {
+      m = emit(H_ARITH);
+      m->sub = (uint8_t)oc; m->type = op.type;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+      if (oc != VGPU_OP_NEG) m->y = opnd(op.b, (uint64_t)op.imm.i, 1);
+    } else if (oc == VGPU_OP_CAST) {
+      m = emit(H_CAST);
+      m->type = op.type;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+      m->x.type = op.a.type;
+    } else if (oc == VGPU_OP_MOV) {
+      m = emit(H_LD);
+      m->type = op.type;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+    } else if (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) {
+      m = emit(H_CMP);
+      m->sub = (uint8_t)oc; m->type = op.type;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+      m->y = opnd(op.b, (uint64_t)op.imm.i, 1);
+      if (oc == VGPU_OP_BETWEEN) m->z = opnd(op.c, (uint64_t)op.imm2.i, 2);
+    } else {
+      m = emit(H_BOOL);
+      m->sub = (uint8_t)oc; m->type = VGPU_BOOLEAN;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+      if (oc == VGPU_OP_AND || oc == VGPU_OP_OR) m->y = opnd(op.b, (uint64_t)op.imm.i, 1);
+    }
+    flow_step(p, f, op, true);
+    const bool dirty = is_bool ? f.bacc_n : f.acc_n;
+    store(m, op, is_bool, dirty);
+    if (is_bool) { bacc_mirror_prev = bacc_mirror; bacc_mirror = op.dst_slot; }
+    else acc_mirror = op.dst_slot;
+  }
+
+  XOp out_opnd(int idx) {
+    const vgpu_operand& o = p.outputs[idx];
+    if (o.kind == VGPU_OPND_IMM || o.kind == VGPU_OPND_ACC) bad_output = true;
+    return opnd(o, 0, 0);
+  }
+
+  void lower_sink() {
+    const Program& prog = *p.prog;
+    MOp* m = emit(H_FILTER);
+    m->x = opnd(prog.filter, 1, 0);
+    if (prog.filter.kind == VGPU_OPND_ACC) m->x.kind = XK_ACC;
+    if (p.mode == kSinkFilterProject) {
+      emit(H_SEL);
+      for (int k = 0; k < p.n_outputs; ++k) {
+        if (p.outs[k].values == nullptr) continue;
+        m = emit(H_PROJ);
+        m->dst = k;
+        m->x = out_opnd(k);
+      }
+      return;
+    }
+    for (int k = 0; k < p.n_keys; ++k) {
+      m = emit(H_KEY);
+      m->dst = k;
+      m->x = out_opnd(p.keys[k].output);
+    }
+    emit(H_KEYEND);
+    for (int c = 0; c < p.n_cells; ++c) {
+      const DevCell& cell = p.cells[c];
+      if (cell.skip) continue;
+      m = emit(H_ACCUM);
+      m->sub = cell.kind;
+      m->dst = p.mode == kSinkArray ? cell.smem_off : c;
+      if (cell.input >= 0) m->x = out_opnd(cell.input);
+      else m->flags |= MF_NO_VALUE;
+    }
+  }
+
+  // Drops slot stores nobody reads (after accumulator forwarding most are dead).
+  void dead_stores() {
+    bool live_v[kMaxSlots + 1] = {false}, live_b[kMaxSlots + 1] = {false};
+    for (int i = n - 1; i >= 0; --i) {
+      MopInfo& mi = info[i];
+      MOp& m = p.mops[i];
+      if (mi.st_v >= 0) {
+        if (!live_v[mi.st_v]) { m.flags &= ~MF_STORE; }
+        live_v[mi.st_v] = false;
+      }
+      if (mi.st_b >= 0) {
+        if (!live_b[mi.st_b]) { m.flags &= ~MF_STORE; }
+        live_b[mi.st_b] = false;
+      }
+      for (int k = 0; k < 3; ++k) {
+        if (mi.rd_v[k] >= 0) live_v[mi.rd_v[k]] = true;
+        if (mi.rd_b[k] >= 0) live_b[mi.rd_b[k]] = true;
+      }
+    }
+  }
+};
+} // namespace
+
+static int lower_mops(PipelineParams& p) {
+  Lowerer lw(p);
+  for (const vgpu_op& op : p.prog->ops) lw.lower_op(op);
+  lw.lower_sink();
+  lw.dead_stores();
+  if (lw.overflow) { set_error("pipeline lowers to more than %d micro-ops", kMaxMops); return VGPU_ERR_UNSUPPORTED; }
+  if (lw.bad_output) { set_error("program outputs must be columns, slots or NULL"); return VGPU_ERR_INVALID; }
+  p.n_mops = lw.n;
+  return VGPU_OK;
 }
 
 constexpr int kSmemLimit = 227 * 1024;
@@ -1445,6 +1646,8 @@ int launch_pipeline(PipelineParams& p, int tab_bytes, int grid, cudaStream_t str
   p.smem_bmeta_off = p.smem_meta_off + meta_bytes;
   p.smem_tab_off = (p.smem_bmeta_off + bmeta_bytes + 127) & ~127;
   const int smem = p.smem_tab_off + tab_bytes;
+  int rc = lower_mops(p);
+  if (rc) return rc;
   auto run = [&](auto kernel) -> int {
     VG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     kernel<<<grid, kThreads, smem, stream>>>(p);
