@@ -71,6 +71,18 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.samples)}
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the Q1 kernel, from the committed
+    ncu capture (profiles/r01_q1_ncu_summary.json); None when the summary is absent."""
+    path = os.path.join(ROOT, "profiles", "r01_q1_ncu_summary.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return d["dram_bytes_read"] + d["dram_bytes_write"]
+    except Exception:
+        return None
+
+
 def q1_plan():
     import helpers as H
     f, outs = H.q1_exprs()
@@ -139,23 +151,18 @@ def run_ours(args, rank, world, local_rank):
     final = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS) if world > 1 else None
     empty = [engine.DeviceColumn(t, abi.FLAT, data[c][:0], length=0) for c, t in zip(Q1_COLS, types)]
 
-    kernel_ms = []
+    lib = abi.lib()
 
-    def step(timed):
+    def step():
+        """One pass of the hot path over the resident batch: reset the groups, fused filter ->
+        project -> partial aggregation, (N > 1: partition, all-to-all, final aggregation).  The
+        result (the group state) stays on the device; it is extracted and checked after the loop."""
         partial.reset()
-        if timed:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
         partial.add_input(prog, cols, n)
-        if timed:
-            e1.record()
-            kernel_ms.append((e0, e1))
         if world > 1:
             final.reset()
             final.add_input(prog, empty, 0)
             exchange.shuffle(partial, final)
-            return final.num_groups()
-        return partial.num_groups()
 
     def barrier():
         torch.cuda.synchronize()
@@ -164,25 +171,40 @@ def run_ours(args, rank, world, local_rank):
             torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        step(False)
+        step()
+    barrier()
     stats0 = abi.Stats()
-    abi.lib().vgpu_get_stats(stats0)
+    lib.vgpu_get_stats(stats0)
+    abi.check(lib.vgpu_debug_kernel_timing(1))  # events around the scan kernel, on its own stream
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
-    groups = 0
     for _ in range(args.steps):
-        groups = step(True)
+        step()
     t1.record()
     barrier()
     clocks = sampler.stop()
     stats1 = abi.Stats()
-    abi.lib().vgpu_get_stats(stats1)
+    lib.vgpu_get_stats(stats1)
     ms = t0.elapsed_time(t1)
-    kms = float(np.mean([a.elapsed_time(b) for a, b in kernel_ms]))
+    import ctypes as C
+    k_total, k_n = C.c_double(), C.c_int64()
+    abi.check(lib.vgpu_debug_kernel_time(C.byref(k_total), C.byref(k_n)))
+    abi.check(lib.vgpu_debug_kernel_timing(0))
+    kms = k_total.value / max(1, k_n.value)
+    kernel_note = abi.last_kernel_note()
     engine.check_errors()
+    groups = (final if world > 1 else partial).num_groups()
+    checked = None
+    if world == 1:  # the resident result against an independent count of the rows the filter keeps
+        got = H.decode_rows(partial.extract(), H.Q1_KEYS, H.Q1_ACCS, [o.type for o in outs], abi.AGG_ARRAY)
+        want_rows = int((data["l_shipdate"] <= H.DATE_1998_09_02).sum())
+        have_rows = sum(v[-1][0] for v in got.values())
+        if have_rows != want_rows:
+            raise RuntimeError(f"result check failed: count(*) over groups {have_rows} != {want_rows}")
+        checked = f"sum of count(*) over {len(got)} groups == {want_rows} rows passing the filter"
 
     # ---- end to end: HOST batches through the public API (H2D inside the timed region) ----------
     host = [data[c].cpu().pin_memory() for c in Q1_COLS]
@@ -194,7 +216,13 @@ def run_ours(args, rank, world, local_rank):
         nonlocal result_bytes
         e2e_agg.reset()
         runner.run(e2e_agg, prog, host, n)
-        rows = e2e_agg.extract()  # device -> host read of the result rows
+        if world > 1:
+            final.reset()
+            final.add_input(prog, empty, 0)
+            exchange.shuffle(e2e_agg, final)
+            rows = final.extract()
+        else:
+            rows = e2e_agg.extract()  # device -> host read of the result rows
         result_bytes = rows.nbytes
         return rows
 
@@ -227,11 +255,14 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "input (2.6 GB per step) is larger than L2 (126 MB); no flush needed",
                    "generator": "velox-1_b200/tpch_synth.py (lineitem-shaped, dbgen value domains)"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "pipeline_kernel<ARRAY> (+ merge_partials)", "kernel_ms": kms,
+                     "traffic": ncu_traffic(), "kernel": "vgpu_fused (plan-specialised Q1 scan: filter + project + "
+                     "per-thread shared-memory partial aggregation)", "kernel_ms": kms, "kernel_launches": int(k_n.value),
+                     "kernel_origin": kernel_note, "algorithmic_bytes_per_launch": n * Q1_BYTES_PER_ROW,
                      "peak_source": peak_src},
         "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": runner.h2d_bytes,
                 "d2h_bytes_per_step": int(result_bytes), "steps": e2e_steps, "chunk_rows": args.chunk_rows},
         "gpu_launches": int(stats1.kernel_launches - stats0.kernel_launches),
+        "result_check": checked,
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
@@ -264,7 +295,7 @@ def cpu_baseline(args, H, f, outs, data, types):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sf", type=float, default=10.0)

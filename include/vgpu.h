@@ -252,7 +252,11 @@ typedef struct {
   int32_t output; /* index into the program's outputs                                          */
   int32_t bits;   /* width of the id field; 64 = use the raw value (single BIGINT key)          */
   int64_t min;    /* subtracted before packing (range mode)                                    */
-  int64_t max;    /* values outside [min,max] latch "key out of range" for a host redo         */
+  int64_t max;    /* values outside [min,max] latch "key out of range" for a host redo.
+                     bits == 64: optional range statistics of the key (min < max; 0,0 = unknown,
+                     the VectorHasher min/max of the reference).  A hint: results never depend on
+                     it.  With VGPU_RANGED_KEYS=1 keys inside the range are placed monotonically
+                     in the HBM table (experimental; hashing is the default and measured faster). */
 } vgpu_key_spec;
 
 typedef enum {
@@ -352,6 +356,13 @@ int vgpu_debug_last_kernel_source(char* buf, size_t cap, uint64_t* hash);
 /* How the last shape was handled on this thread: "built from aot|disk|nvrtc", "declined: ...",
  * "nvrtc failed: ...". */
 int vgpu_debug_last_kernel_note(char* buf, size_t cap);
+
+/* Timing of the scan kernels (the fused / interpreter kernel of vgpu_agg_add_input and
+ * vgpu_filter_project, not the small bookkeeping kernels): while on, CUDA events are recorded on
+ * the launching stream right before and after each such kernel.  vgpu_debug_kernel_time waits for
+ * them, returns the summed duration and the number of launches, and clears the list. */
+int vgpu_debug_kernel_timing(int on);
+int vgpu_debug_kernel_time(double* ms_total, int64_t* launches);
 
 #ifdef __cplusplus
 }

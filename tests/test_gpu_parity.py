@@ -93,13 +93,16 @@ def test_q1_two_batches_equals_one(engine, sf1):
 
 
 # ---- C3: high-cardinality group-by -----------------------------------------------------------
-@pytest.mark.parametrize("hint", [0, 1_500_000])
-def test_orderkey_groupby(engine, sf1, hint):
+@pytest.mark.parametrize("hint,ranged", [(0, False), (1_500_000, False), (1_500_000, True), (0, True)])
+def test_orderkey_groupby(engine, sf1, hint, ranged):
+    """ranged: the key's min/max statistics are declared (monotone table placement); a too-narrow
+    range is legal too (keys outside it are hashed)."""
     n = len(sf1["l_orderkey"])
     outs = [ex.col(0, I64), ex.col(1, D)]
     cols = [engine.flat_column(I64, sf1["l_orderkey"]), engine.flat_column(D, sf1["l_extendedprice"])]
     prog = engine.Program(None, outs)
-    keys = [(0, 64, 0, 0)]
+    kmax = int(sf1["l_orderkey"].max())
+    keys = [(0, 64, 1, kmax if hint else kmax // 3)] if ranged else [(0, 64, 0, 0)]
     accs = [(abi.ACC_SUM_F64, 1), (abi.ACC_COUNT, -1)]
     agg = engine.Aggregation(abi.AGG_HASH, keys, accs, expected_groups=hint)
     agg.add_input(prog, cols, n)

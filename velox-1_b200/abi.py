@@ -126,6 +126,8 @@ PROTOTYPES = {
     "vgpu_debug_set_dry_run": [C.c_int],
     "vgpu_debug_last_kernel_source": [C.c_char_p, _SZ, C.POINTER(C.c_uint64)],
     "vgpu_debug_last_kernel_note": [C.c_char_p, _SZ],
+    "vgpu_debug_kernel_timing": [C.c_int],
+    "vgpu_debug_kernel_time": [C.POINTER(C.c_double), C.POINTER(_I64)],
 }
 
 _lib = None

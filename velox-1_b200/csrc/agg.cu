@@ -8,6 +8,7 @@
 //   velox/exec/HashPartitionFunction.cpp:59-92 (partition = hash % numPartitions).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -50,11 +51,14 @@ __device__ __forceinline__ int state_group(const GroupMap& gm, int g) {
   return (int)out;
 }
 
-// state[c][sg] = fold(state[c][sg], partials[0][c][g], partials[1][c][g], ...) in block order
-// (fixed order => run-to-run deterministic); Gc = groups of the launch, G = groups of the state.
+// state[c][sg] = fold(state[c][sg], partials[0][c][g], partials[1][c][g], ...): one warp per
+// (cell, group).  Lane l folds CTAs l, l+32, ... in order, then a fixed xor-butterfly joins the
+// lanes: the order depends only on the launch width, so results are run-to-run deterministic.
+// Gc = groups of the launch, G = groups of the state.
 __global__ void merge_partials_kernel(uint64_t* state, const uint64_t* partials, int n_blocks,
                                       CellMeta m, int Gc, int G, GroupMap gm, uint32_t* err_word) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (i >= m.n_cells * Gc) return;
   const int c = i / Gc, g = i - c * Gc;
   const int src = m.skip[c] ? m.alias[c] : c;
@@ -62,9 +66,16 @@ __global__ void merge_partials_kernel(uint64_t* state, const uint64_t* partials,
   uint32_t err = 0;
   uint64_t acc = cell_identity(kind);
   const size_t stride = (size_t)m.n_cells * Gc;
-  for (int b = 0; b < n_blocks; ++b) acc = fold2(kind, acc, partials[b * stride + (size_t)src * Gc + g], err);
-  const size_t si = (size_t)c * G + state_group(gm, g);
-  state[si] = fold2(kind, state[si], acc, err);
+  for (int b = lane; b < n_blocks; b += 32) acc = fold2(kind, acc, partials[b * stride + (size_t)src * Gc + g], err);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const uint64_t other = __shfl_xor_sync(0xffffffffu, acc, o);
+    acc = fold2(kind, acc, other, err);
+  }
+  if (lane == 0) {
+    const size_t si = (size_t)c * G + state_group(gm, g);
+    state[si] = fold2(kind, state[si], acc, err);
+  }
   if (err) atomicOr(err_word, err);
 }
 
@@ -102,7 +113,9 @@ __global__ void init_table_kernel(uint64_t* table, uint64_t n_slots, int row_wor
   for (uint64_t k = i; k < total; k += (uint64_t)gridDim.x * blockDim.x) {
     const int w = (int)(k % row_words);
     uint64_t v = kEmptyKey;
-    if (w > 0) {
+    if (w > m.n_cells) {
+      v = 0; // padding
+    } else if (w > 0) {
       v = cell_identity(m.kind[w - 1]);
       if (m.kind[w - 1] == kCellMinF64 || m.kind[w - 1] == kCellMaxF64) v = (uint64_t)f64_ordered(v);
     }
@@ -328,7 +341,10 @@ int agg_resolve(Agg& a, const Program& prog) {
       shift += ks.bits;
       if (shift > 63) { set_error("normalized key wider than 63 bits"); return VGPU_ERR_UNSUPPORTED; }
     }
-    a.row_words = 1 + a.n_cells;
+    // key + cells, padded so that a row never straddles more 32-byte sectors than it has to
+    int rw = 1 + a.n_cells;
+    if (rw == 3) rw = 4; else if (rw > 4 && rw < 8) rw = 8; else if (rw > 8) rw = (rw + 3) & ~3;
+    a.row_words = rw;
   }
   if (!fused_dry_run()) {
     VG_CUDA(cudaMalloc(&a.ctr, 64 * sizeof(unsigned long long)));
@@ -340,8 +356,28 @@ int agg_resolve(Agg& a, const Program& prog) {
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
+static KeyMap key_map_of(const Agg& a) {
+  KeyMap m{};
+  // Measured on B200 (profiles/r01_notes.md): for sorted l_orderkey the monotone placement is
+  // SLOWER than hashing (3.3 ms vs 2.75 ms at SF10) — neighbouring groups land in one 128-byte line
+  // and their CAS / RED operations serialise in the L2 atomic unit.  Kept behind
+  // VGPU_RANGED_KEYS=1 for experiments; the default is the hashed placement.
+  static const bool enabled = getenv("VGPU_RANGED_KEYS") != nullptr && getenv("VGPU_RANGED_KEYS")[0] == '1';
+  if (enabled && a.keys.size() == 1 && a.keys[0].bits == 64 && a.keys[0].max > a.keys[0].min && a.capacity > 0) {
+    m.min = (uint64_t)a.keys[0].min;
+    m.span = (uint64_t)a.keys[0].max - (uint64_t)a.keys[0].min;
+    if (m.span < a.capacity) {
+      m.mode = 1;
+    } else {
+      m.mode = 2;
+      m.scale = (uint64_t)((((unsigned __int128)a.capacity) << 64) / ((unsigned __int128)m.span + 1));
+    }
+  }
+  return m;
+}
+
 static HashRef href_of(const Agg& a) {
-  HashRef h; h.table = a.table; h.cap_mask = a.capacity - 1; h.row_words = a.row_words; h.n_groups_ctr = a.ctr;
+  HashRef h; h.table = a.table; h.cap_mask = a.capacity - 1; h.key_map = key_map_of(a); h.row_words = a.row_words; h.n_groups_ctr = a.ctr;
   return h;
 }
 
@@ -479,7 +515,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
         rc = fused_launch(fk, p, fgrid, stream);
         if (rc) return rc;
         const int cells = a.n_cells * Gc;
-        merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, fgrid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
+        merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, fgrid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
         VG_CUDA(cudaGetLastError());
         count_launch();
         return VGPU_OK;
@@ -521,7 +557,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = launch_pipeline(p, tab, grid, stream);
     if (rc) return rc;
     const int cells = a.n_cells * Gc;
-    merge_partials_kernel<<<(cells + 255) / 256, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
+    merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
     VG_CUDA(cudaGetLastError());
     count_launch();
     return VGPU_OK;
@@ -537,20 +573,24 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     fused_prepare(p, &fgrid);
     return VGPU_OK;
   }
-  // HASH: walk the batch in pieces small enough that the table cannot exceed 50 % load.
+  // HASH: walk the batch in pieces small enough that the table cannot fill up.
   int64_t done = 0;
   std::vector<vgpu_column> sliced(ncols);
   while (done < total) {
     uint64_t known = 0;
     if (a.table) { rc = read_group_count(a, stream, &known); if (rc) return rc; }
     const int64_t rem = total - done;
-    uint64_t room = a.capacity / 2 > known ? a.capacity / 2 - known : 0;
+    // every row of a piece may start a group: a piece may take the table to 7/8 full at worst
+    // (the reference rehashes at the same load, velox/exec/HashTable.h:562-565); tables are sized
+    // for <= 50 % load, so real inputs with repeated keys stay far below that
+    const uint64_t limit = a.capacity - a.capacity / 8;
+    uint64_t room = limit > known ? limit - known : 0;
     if (room < (uint64_t)std::min<int64_t>(rem, kTile)) {
       uint64_t want = known + (uint64_t)std::min<int64_t>(rem, std::max<int64_t>(4 << 20, (int64_t)known));
       if (a.expected_groups > 0) want = std::max<uint64_t>(want, (uint64_t)a.expected_groups);
       rc = hash_resize(a, next_pow2(2 * want), stream);
       if (rc) return rc;
-      room = a.capacity / 2 - known;
+      room = a.capacity - a.capacity / 8 - known;
     }
     int64_t piece = std::min<int64_t>(rem, (int64_t)room);
     if (piece < rem) piece = std::max<int64_t>(kTile, piece / kTile * kTile); // keep slices tile aligned
@@ -567,7 +607,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       if (!p.cells[c].skip && a.hash_aliased[c]) { rc = hash_materialize(a, c, stream); if (rc) return rc; }
       if (!a.hash_aliased[c]) p.cells[c].skip = 0; // once materialised the cell is always updated
     }
-    p.table = a.table; p.cap_mask = a.capacity - 1; p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
+    p.table = a.table; p.cap_mask = a.capacity - 1; p.key_map = key_map_of(a); p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
     int fgrid = 0;
     FusedKernel* fk = fused_prepare(p, &fgrid);
     rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
@@ -686,7 +726,13 @@ int agg_reset(Agg& a, cudaStream_t stream) {
   a.packed_rows = -1;
   if (!a.resolved) return VGPU_OK;
   if (a.mode == VGPU_AGG_HASH) {
-    if (a.table) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(a.table)); a.table = nullptr; a.capacity = 0; }
+    if (a.table) { // keep the allocation, wipe it in place
+      const uint64_t slots = a.capacity + 2;
+      const int blocks = std::max(1, std::min(num_sms() * 8, (int)((slots * a.row_words + 255) / 256)));
+      init_table_kernel<<<blocks, 256, 0, stream>>>(a.table, slots, a.row_words, cell_meta(a));
+      VG_CUDA(cudaGetLastError());
+      count_launch();
+    }
     for (int c = 0; c < kMaxCells; ++c) a.hash_aliased[c] = true;
     VG_CUDA(cudaMemsetAsync(a.ctr, 0, sizeof(unsigned long long), stream));
   } else {

@@ -9,6 +9,8 @@
 
 #include <mutex>
 #include <new>
+#include <utility>
+#include <vector>
 
 #include "agg.h"
 #include "fused.h"
@@ -43,6 +45,24 @@ uint32_t* device_err_word() {
   }
   return g_err_words[dev];
 }
+// ---- kernel timing (diagnostics) -------------------------------------------------------------
+static bool g_timing = false;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_timing_events;
+void kernel_timing_begin(cudaStream_t stream) {
+  if (!g_timing) return;
+  cudaEvent_t a, b;
+  cudaEventCreate(&a);
+  cudaEventCreate(&b);
+  cudaEventRecord(a, stream);
+  std::lock_guard<std::mutex> l(g_mu);
+  g_timing_events.emplace_back(a, b);
+}
+void kernel_timing_end(cudaStream_t stream) {
+  if (!g_timing) return;
+  std::lock_guard<std::mutex> l(g_mu);
+  if (!g_timing_events.empty()) cudaEventRecord(g_timing_events.back().second, stream);
+}
+
 void count_launch(int n) { __atomic_fetch_add(&g_stats.kernel_launches, (int64_t)n, __ATOMIC_RELAXED); }
 int num_sms() {
   int dev = 0;
@@ -365,6 +385,33 @@ int vgpu_debug_last_kernel_note(char* buf, size_t cap) {
   if (!buf || cap == 0) return VGPU_ERR_INVALID;
   strncpy(buf, fused_last_note().c_str(), cap - 1);
   buf[cap - 1] = 0;
+  return VGPU_OK;
+}
+
+int vgpu_debug_kernel_timing(int on) {
+  std::lock_guard<std::mutex> l(g_mu);
+  g_timing = on != 0;
+  for (auto& e : g_timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+  g_timing_events.clear();
+  return VGPU_OK;
+}
+int vgpu_debug_kernel_time(double* ms_total, int64_t* launches) {
+  if (!ms_total || !launches) return VGPU_ERR_INVALID;
+  std::lock_guard<std::mutex> l(g_mu);
+  double sum = 0;
+  int64_t n = 0;
+  for (auto& e : g_timing_events) {
+    VG_CUDA(cudaEventSynchronize(e.second));
+    float ms = 0;
+    VG_CUDA(cudaEventElapsedTime(&ms, e.first, e.second));
+    sum += ms;
+    ++n;
+    cudaEventDestroy(e.first);
+    cudaEventDestroy(e.second);
+  }
+  g_timing_events.clear();
+  *ms_total = sum;
+  *launches = n;
   return VGPU_OK;
 }
 

@@ -13,6 +13,7 @@ __device__ __forceinline__ double u2d(uint64_t u) { return __longlong_as_double(
 struct HashRef {
   uint64_t* table; // (capacity + 2) rows of row_words words: key, cells...
   uint64_t cap_mask;
+  KeyMap key_map;
   int32_t row_words;
   unsigned long long* n_groups_ctr;
 };
@@ -24,6 +25,12 @@ __device__ __forceinline__ uint64_t mix64(uint64_t k) { // splitmix64 finaliser
   return k;
 }
 constexpr uint64_t kEmptyKey = 0xffffffffffffffffull;
+
+__device__ __forceinline__ uint64_t home_slot(const KeyMap& m, uint64_t cap_mask, uint64_t key) {
+  const uint64_t d = key - m.min;
+  if (m.mode != 0 && d <= m.span) return m.mode == 1 ? d : __umul64hi(d, m.scale);
+  return mix64(key) & cap_mask;
+}
 
 // Order-preserving int64 image of a double (for atomicMin/Max on doubles in HBM).
 __device__ __forceinline__ int64_t f64_ordered(uint64_t bits) {
@@ -76,7 +83,7 @@ __device__ __forceinline__ int64_t hash_find_or_insert(const HashRef& p, uint64_
     }
     return slot;
   }
-  uint64_t h = mix64(key) & p.cap_mask;
+  uint64_t h = home_slot(p.key_map, p.cap_mask, key);
   for (uint64_t probes = 0; probes <= p.cap_mask; ++probes) {
     unsigned long long* kp = reinterpret_cast<unsigned long long*>(table + h * rw);
     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(kp);

@@ -16,6 +16,7 @@
 // compare, and3/or3), called with compile-time opcodes so they fold to single instructions.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -289,19 +290,31 @@ struct Gen {
   int live_cells[kMaxCells];
   int n_live = 0;
 
-  void gen_array_body(bool full, bool regs, int G) {
+  // How the ARRAY / GLOBAL sink keeps its partial groups.
+  enum ArrayStrategy {
+    AS_REGS,    // registers: one predicated update per (group, cell)
+    AS_THREAD,  // per-thread tables in shared memory: plain read-modify-write, no conflicts
+    AS_ATOMIC   // per-warp (or per-CTA) tables in shared memory: atomics
+  };
+  int cell_boff[kMaxCells]; // AS_THREAD: byte offset of the cell's block [G][NT]
+
+  void gen_array_body(bool full, ArrayStrategy st, int G) {
     gen_block_header(full);
     gen_row_begin(full);
     gen_keys(false);
     for (int i = 0; i < n_live; ++i) {
       const int c = live_cells[i];
+      const int kind = p.cells[c].kind;
       gen_cell_input(c);
-      if (regs) {
-        if (p.cells[c].kind == kCellCount) out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] += 1u;\n", G, c, c);
-        else out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] = cell_comb<%d>(A%d[gg], x%d, accerr);\n", G, c, c, p.cells[c].kind, c, c);
+      if (st == AS_REGS) {
+        if (kind == kCellCount) out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] += 1u;\n", G, c, c);
+        else out("      _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) if (l%d && g == (u32)gg) A%d[gg] = cell_comb<%d>(A%d[gg], x%d, accerr);\n", G, c, c, kind, c, c);
+      } else if (st == AS_THREAD) {
+        if (kind == kCellCount) out("      if (l%d) { u32* a = reinterpret_cast<u32*>(tabc + %d) + g * NT + threadIdx.x; *a = *a + 1u; }\n", c, cell_boff[i]);
+        else out("      if (l%d) { u64* a = reinterpret_cast<u64*>(tabc + %d) + g * NT + threadIdx.x; *a = cell_comb<%d>(*a, x%d, accerr); }\n", c, cell_boff[i], kind, c);
       } else {
-        if (p.cells[c].kind == kCellCount) out("      if (l%d) atomicAdd(reinterpret_cast<u32*>(mytab + %d * %d + g), 1u);\n", c, i, G);
-        else out("      if (l%d) smem_update<%d>(mytab + %d * %d + g, x%d, accerr);\n", c, p.cells[c].kind, i, G, c);
+        if (kind == kCellCount) out("      if (l%d) atomicAdd(reinterpret_cast<u32*>(mytab + %d * %d + g), 1u);\n", c, i, G);
+        else out("      if (l%d) smem_update<%d>(mytab + %d * %d + g, x%d, accerr);\n", c, kind, i, G, c);
       }
     }
     gen_raise();
@@ -322,22 +335,58 @@ struct Gen {
     out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
     gen_raise();
     out("    }\n");
-    // adjacent rows of a pair share the probe when their keys are equal (sorted / clustered keys)
+    // Run aggregation before the table is touched.  Equal keys tend to arrive together (sorted or
+    // clustered inputs such as l_orderkey), so per 64-row half block: (1) a thread folds its two
+    // rows when their keys match, (2) a segmented scan over the lanes carries a run's partial
+    // from lane to lane, (3) only the last lane of a run probes the table and issues the
+    // atomics.  Any two rows with equal keys may be folded, so this is exact for every input;
+    // it just saves nothing when neighbours differ.
+    out("    u64 SK[4]; bool SN[4], SA[4];\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4];\n", live_cells[i]);
     out("    _Pragma(\"unroll\") for (int pr = 0; pr < 2; ++pr) {\n");
     out("      const int j0 = 2 * pr, j1 = j0 + 1;\n");
-    out("      const bool same = PASS[j0] && PASS[j1] && KEY[j0] == KEY[j1] && KN[j0] == KN[j1];\n");
-    out("      i64 sl0 = -1, sl1 = -1;\n");
-    out("      if (PASS[j0]) sl0 = hash_find_or_insert<%d>(p, KEY[j0], KN[j0], accerr);\n", p.row_words);
-    out("      if (same) sl1 = sl0; else if (PASS[j1]) sl1 = hash_find_or_insert<%d>(p, KEY[j1], KN[j1], accerr);\n", p.row_words);
+    out("      const bool p0 = PASS[j0], p1 = PASS[j1];\n");
+    out("      const bool merged = p0 && p1 && KEY[j0] == KEY[j1] && KN[j0] == KN[j1];\n");
+    out("      // tail segment = the lane's last passing row (plus the first when merged); head = a distinct first row\n");
+    out("      const bool hasT = p0 || p1, hasH = p0 && p1 && !merged;\n");
+    out("      const u64 tk = p1 ? KEY[j1] : KEY[j0]; const bool tn = p1 ? KN[j1] : KN[j0];\n");
+    out("      const u64 hk = KEY[j0]; const bool hn = KN[j0];\n");
     for (int i = 0; i < n_live; ++i) {
       const int c = live_cells[i];
       const int kind = p.cells[c].kind;
-      out("      {\n        const bool a0 = L%d[j0] && sl0 >= 0, a1 = L%d[j1] && sl1 >= 0;\n", c, c);
-      out("        if (same && a0 && a1) hbm_update<%d>(p.table + sl0 * %d + %d, cell_comb<%d>(X%d[j0], X%d[j1], accerr), accerr);\n", kind, p.row_words, 1 + c, kind, c, c);
-      out("        else {\n          if (a0) hbm_update<%d>(p.table + sl0 * %d + %d, X%d[j0], accerr);\n", kind, p.row_words, 1 + c, c);
-      out("          if (a1) hbm_update<%d>(p.table + sl1 * %d + %d, X%d[j1], accerr);\n        }\n      }\n", kind, p.row_words, 1 + c, c);
+      out("      const u64 v0_%d = L%d[j0] ? X%d[j0] : cell_identity<%d>(), v1_%d = L%d[j1] ? X%d[j1] : cell_identity<%d>();\n", c, c, c, kind, c, c, c, kind);
+      out("      u64 h%d = v0_%d;\n", c, c);
+      out("      u64 t%d = p1 ? (merged ? cell_comb<%d>(v0_%d, v1_%d, accerr) : v1_%d) : v0_%d;\n", c, kind, c, c, c, c);
     }
+    out("      const u64 fk = hasH ? hk : tk; const bool fn = hasH ? hn : tn;\n");
+    out("      const u64 ptk = __shfl_up_sync(0xffffffffu, tk, 1);\n");
+    out("      const u32 pfl = __shfl_up_sync(0xffffffffu, (u32)hasT | ((u32)tn << 1), 1);\n");
+    out("      const bool link = lane > 0 && hasT && (pfl & 1u) && ptk == fk && (bool)((pfl >> 1) & 1u) == fn;\n");
+    out("      bool f = !(link && !hasH); // the carry flows through this lane's tail only when it has no separate head\n");
+    out("      _Pragma(\"unroll\") for (int d = 1; d < 32; d <<= 1) {\n");
+    for (int i = 0; i < n_live; ++i) out("        const u64 u%d = __shfl_up_sync(0xffffffffu, t%d, d);\n", live_cells[i], live_cells[i]);
+    out("        const bool uf = __shfl_up_sync(0xffffffffu, (u32)f, d) != 0u;\n");
+    out("        if (lane >= d && !f) {\n");
+    for (int i = 0; i < n_live; ++i) out("          t%d = cell_comb<%d>(u%d, t%d, accerr);\n", live_cells[i], p.cells[live_cells[i]].kind, live_cells[i], live_cells[i]);
+    out("          f = uf;\n        }\n      }\n");
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      out("      { const u64 c%d_ = __shfl_up_sync(0xffffffffu, t%d, 1); if (hasH && link) h%d = cell_comb<%d>(c%d_, h%d, accerr); }\n", c, c, c, p.cells[c].kind, c, c);
+    }
+    out("      const bool next_link = __shfl_down_sync(0xffffffffu, (u32)link, 1) != 0u && lane < 31;\n");
+    out("      SK[j0] = hk; SN[j0] = hn; SA[j0] = hasH;\n");
+    out("      SK[j1] = tk; SN[j1] = tn; SA[j1] = hasT && !next_link;\n");
+    for (int i = 0; i < n_live; ++i) out("      SV%d[j0] = h%d; SV%d[j1] = t%d;\n", live_cells[i], live_cells[i], live_cells[i], live_cells[i]);
     out("    }\n");
+    // the (up to) four segments of the thread probe the table together: their first reads and
+    // their claims overlap instead of forming four dependent round trips to HBM
+    out("    i64 SL[4];\n    hash_probe4<%d>(p, SK, SN, SA, SL, inserted, accerr);\n", p.row_words);
+    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (SA[sgm] && SL[sgm] >= 0) {\n");
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      out("        if (SV%d[sgm] != cell_identity<%d>()) hbm_update<%d>(p.table + SL[sgm] * %d + %d, SV%d[sgm], accerr);\n", c, p.cells[c].kind, p.cells[c].kind, p.row_words, 1 + c, c);
+    }
+    out("      }\n    }\n");
   }
 
   void gen_fp_body(bool full) {
@@ -408,48 +457,94 @@ struct Gen {
     for (int c = 0; c < p.n_cells; ++c) if (!p.cells[c].skip) live_cells[n_live++] = c;
 
     const int G = p.n_groups;
-    bool regs = false;
     int copies = 1;
-    if (p.mode == kSinkArray) regs = (int64_t)G * n_live <= 48;
-    // Registers the body needs: the 4 rows of every staged column, the accumulators (register
-    // path), addressing.  Pick the widest CTA shape whose per-thread budget covers it.
-    int need = 30;
+    // Registers the body needs: the 4 rows of every staged column, addressing, and (register
+    // strategy) the accumulators.  Pick the widest CTA shape whose per-thread budget covers it.
+    int need = 24;
     for (int c = 0; c < p.n_cols; ++c) {
       if (!col_used[c] || p.cols[c].encoding == VGPU_CONSTANT) continue;
       const DevCol& d = p.cols[c];
       need += (d.encoding == VGPU_DICTIONARY || d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 4 : (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) ? 8 : 2;
       if (d.encoding == VGPU_DICTIONARY) need += 4;
     }
-    if (regs) for (int i = 0; i < n_live; ++i) need += (p.cells[live_cells[i]].kind == kCellCount ? 1 : 2) * G;
     if (p.mode == kSinkHash) need += 8 + 3 * n_live * 4;
+    int acc_regs = 0, group_bytes = 0; // per thread: accumulator registers / bytes of one thread table
+    for (int i = 0; i < n_live; ++i) {
+      const bool cnt = p.cells[live_cells[i]].kind == kCellCount;
+      acc_regs += (cnt ? 1 : 2) * G;
+      group_bytes += (cnt ? 4 : 8) * G;
+    }
     static const int shapes[][2] = {{512, 2}, {384, 2}, {512, 1}, {384, 1}, {256, 1}};
+    auto pick = [&](int regs_needed, int smem_per_thread, int& nt, int& ctas) {
+      for (const auto& sh : shapes) {
+        const int budget = std::min(255, (65536 / (sh[0] * sh[1])) & ~7);
+        const int64_t smem = (int64_t)smem_per_thread * sh[0] + 1024;
+        if (budget >= regs_needed && smem * sh[1] <= 226 * 1024) { nt = sh[0]; ctas = sh[1]; return true; }
+      }
+      return false;
+    };
+    ArrayStrategy st = AS_REGS;
     int NT = 256, CTAS = 1;
-    for (const auto& sh : shapes) {
-      const int budget = std::min(255, (65536 / (sh[0] * sh[1])) & ~7);
-      if (budget >= need) { NT = sh[0]; CTAS = sh[1]; break; }
+    if (p.mode != kSinkArray) {
+      pick(need, 0, NT, CTAS);
+    } else if (acc_regs <= 24) {
+      pick(need + acc_regs, 0, NT, CTAS);
+    } else {
+      int nt_r = 0, ctas_r = 0, nt_t = 0, ctas_t = 0;
+      const bool can_regs = G * n_live <= 48 && pick(need + acc_regs, 0, nt_r, ctas_r);
+      const bool can_thread = pick(need + 8, group_bytes, nt_t, ctas_t);
+      // thread tables win when they keep more warps resident than the register file would
+      if (can_thread && (!can_regs || nt_t * ctas_t > nt_r * ctas_r)) { st = AS_THREAD; NT = nt_t; CTAS = ctas_t; }
+      else if (can_regs) { st = AS_REGS; NT = nt_r; CTAS = ctas_r; }
+      else {
+        // shared tables with atomics: one wide CTA per SM gives the most warp-private copies
+        st = AS_ATOMIC;
+        if (need <= 64) { NT = 1024; CTAS = 1; } else pick(need + 8, 0, NT, CTAS);
+      }
+    }
+    if (const char* e = getenv("VGPU_FUSED_SHAPE")) { // tuning aid: "threads,ctas_per_sm"
+      int a = 0, b = 0;
+      if (sscanf(e, "%d,%d", &a, &b) == 2 && a >= 64 && a <= 1024 && a % 32 == 0 && b >= 1 && b <= 8 && st != AS_THREAD) { NT = a; CTAS = b; }
     }
     plan.threads = NT;
     plan.smem_bytes = 0;
     out("#define NT %d\n", NT);
     out("using namespace vgf;\n");
-    if (p.mode == kSinkArray && !regs) {
+    if (p.mode == kSinkArray && st == AS_ATOMIC) {
       const int64_t one = (int64_t)G * n_live * 8;
       const int64_t limit = 200 * 1024 / CTAS;
       if (one > limit) { decline("group table exceeds shared memory"); return; }
       copies = one * (NT / 32) <= limit ? NT / 32 : 1;
       plan.smem_bytes = (int)(one * copies);
     }
+    if (p.mode == kSinkArray && st == AS_THREAD) {
+      int off = 0;
+      for (int i = 0; i < n_live; ++i) {
+        cell_boff[i] = off;
+        off += (p.cells[live_cells[i]].kind == kCellCount ? 4 : 8) * G * NT;
+        off = (off + 15) & ~15;
+      }
+      plan.smem_bytes = off;
+    }
     out("extern \"C\" __global__ void __launch_bounds__(NT, %d) vgpu_fused(const FusedParams p) {\n", CTAS);
     out("  const int lane = threadIdx.x & 31;\n  const i64 n = p.n_rows;\n");
     out("  const i64 n_blocks = (n + 127) >> 7, n_full = n >> 7;\n");
     out("  const i64 wid = (i64)blockIdx.x * (NT / 32) + (threadIdx.x >> 5), nwarps = (i64)gridDim.x * (NT / 32);\n");
     out("  u32 accerr = 0;\n");
+    if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
     if (p.mode == kSinkArray) {
-      if (regs) {
+      if (st == AS_REGS) {
         for (int i = 0; i < n_live; ++i) {
           const int c = live_cells[i];
           if (p.cells[c].kind == kCellCount) out("  u32 A%d[%d];\n  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) A%d[gg] = 0u;\n", c, G, G, c);
           else out("  u64 A%d[%d];\n  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) A%d[gg] = cell_identity<%d>();\n", c, G, G, c, p.cells[c].kind);
+        }
+      } else if (st == AS_THREAD) {
+        out("  extern __shared__ __align__(16) char tabc[];\n");
+        for (int i = 0; i < n_live; ++i) {
+          const int kind = p.cells[live_cells[i]].kind;
+          if (kind == kCellCount) out("  for (int gg = 0; gg < %d; ++gg) (reinterpret_cast<u32*>(tabc + %d))[gg * NT + threadIdx.x] = 0u;\n", G, cell_boff[i]);
+          else out("  for (int gg = 0; gg < %d; ++gg) (reinterpret_cast<u64*>(tabc + %d))[gg * NT + threadIdx.x] = cell_identity<%d>();\n", G, cell_boff[i], kind);
         }
       } else {
         out("  extern __shared__ __align__(16) u64 tab[];\n");
@@ -461,16 +556,22 @@ struct Gen {
       }
     }
     out("  for (i64 blk = wid; blk < n_blocks; blk += nwarps) {\n   if (blk < n_full) {\n");
-    if (p.mode == kSinkArray) gen_array_body(true, regs, G); else if (p.mode == kSinkHash) gen_hash_body(true); else gen_fp_body(true);
+    if (p.mode == kSinkArray) gen_array_body(true, st, G); else if (p.mode == kSinkHash) gen_hash_body(true); else gen_fp_body(true);
     out("   } else {\n");
-    if (p.mode == kSinkArray) gen_array_body(false, regs, G); else if (p.mode == kSinkHash) gen_hash_body(false); else gen_fp_body(false);
+    if (p.mode == kSinkArray) gen_array_body(false, st, G); else if (p.mode == kSinkHash) gen_hash_body(false); else gen_fp_body(false);
     out("   }\n  }\n");
     if (p.mode == kSinkArray) {
-      if (regs) {
+      if (st == AS_REGS || st == AS_THREAD) {
         out("  __shared__ u64 scratch[NT / 32];\n");
         for (int i = 0; i < n_live; ++i) {
           const int c = live_cells[i];
-          out("  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) block_fold<%d, NT / 32>((u64)A%d[gg], scratch, p.partials + ((size_t)blockIdx.x * %d + %d) * %d + gg, accerr);\n", G, p.cells[c].kind, c, p.n_cells, c, G);
+          const int kind = p.cells[c].kind;
+          if (st == AS_REGS) {
+            out("  _Pragma(\"unroll\") for (int gg = 0; gg < %d; ++gg) block_fold<%d, NT / 32>((u64)A%d[gg], scratch, p.partials + ((size_t)blockIdx.x * %d + %d) * %d + gg, accerr);\n", G, kind, c, p.n_cells, c, G);
+          } else {
+            out("  for (int gg = 0; gg < %d; ++gg) block_fold<%d, NT / 32>((u64)(reinterpret_cast<%s*>(tabc + %d))[gg * NT + threadIdx.x], scratch, p.partials + ((size_t)blockIdx.x * %d + %d) * %d + gg, accerr);\n",
+                G, kind, kind == kCellCount ? "u32" : "u64", cell_boff[i], p.n_cells, c, G);
+          }
         }
       } else {
         out("  __syncthreads();\n  for (int i = threadIdx.x; i < %d; i += NT) {\n    const int ci = i / %d, gg = i - ci * %d;\n    u64 acc = tab[i];\n", n_live * G, G, G);
@@ -480,6 +581,10 @@ struct Gen {
         for (int i = 0; i < n_live; ++i) out("    if (ci == %d) c = %d;\n", i, live_cells[i]);
         out("    p.partials[((size_t)blockIdx.x * %d + c) * %d + gg] = acc;\n  }\n", p.n_cells, G);
       }
+    }
+    if (p.mode == kSinkHash) {
+      out("  _Pragma(\"unroll\") for (int o = 16; o > 0; o >>= 1) inserted += __shfl_xor_sync(0xffffffffu, inserted, o);\n");
+      out("  if (lane == 0 && inserted) atomicAdd(p.n_groups_ctr, (u64)inserted);\n");
     }
     out("  if (accerr) atomicOr(p.err_word, accerr);\n}\n");
   }

@@ -70,6 +70,8 @@ struct FusedParams {
   u64* table;
   u64 cap_mask;
   u64* n_groups_ctr;
+  u64 key_min, key_span, key_scale; // monotone home slots for a ranged raw key (internal.h KeyMap)
+  u32 key_mode, key_pad;
   // FilterProject sink
   u32* sel_words;
   i32* tile_counts;
@@ -345,6 +347,11 @@ __device__ __forceinline__ i64 f64_ordered(u64 bits) {
   const i64 s = (i64)bits;
   return s >= 0 ? s : (i64)(bits ^ 0x7fffffffffffffffull);
 }
+__device__ __forceinline__ u64 home_slot(const FusedParams& p, u64 key) {
+  const u64 d = key - p.key_min;
+  if (p.key_mode != 0 && d <= p.key_span) return p.key_mode == 1 ? d : __umul64hi(d, p.key_scale);
+  return mix64(key) & p.cap_mask;
+}
 template <int ROW_WORDS>
 __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key, bool isnull, u32& err) {
   u64* table = p.table;
@@ -356,7 +363,7 @@ __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key
     }
     return slot;
   }
-  u64 h = mix64(key) & p.cap_mask;
+  u64 h = home_slot(p, key);
   for (u64 probes = 0; probes <= p.cap_mask; ++probes) {
     u64* kp = table + h * ROW_WORDS;
     u64 cur = *reinterpret_cast<volatile u64*>(kp);
@@ -371,6 +378,87 @@ __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key
   err |= VGF_ERR_TABLEFULL;
   return -1;
 }
+// Find-or-insert for up to four keys of one thread at once.  Phase 1 reads the home slot of every
+// active key (independent loads, all in flight together); phase 2 claims the empty ones with CAS
+// (again all in flight together); whatever is still unresolved (collision, lost race, special
+// keys) walks the table one key at a time.  `inserted` counts new groups; the caller adds it to
+// the group counter once per warp.
+template <int ROW_WORDS>
+__device__ __forceinline__ i64 hash_walk(const FusedParams& p, u64 key, u64 h, u32& inserted, u32& err) {
+  u64* table = p.table;
+  for (u64 probes = 0; probes <= p.cap_mask; ++probes) {
+    u64* kp = table + h * ROW_WORDS;
+    u64 cur = __ldcg(kp);
+    if (cur == key) return (i64)h;
+    if (cur == VGF_EMPTY_KEY) {
+      cur = atomicCAS(kp, VGF_EMPTY_KEY, key);
+      if (cur == VGF_EMPTY_KEY) { ++inserted; return (i64)h; }
+      if (cur == key) return (i64)h;
+    }
+    h = (h + 1) & p.cap_mask;
+  }
+  err |= VGF_ERR_TABLEFULL;
+  return -1;
+}
+template <int ROW_WORDS>
+__device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[4], const bool isnull[4],
+                                            const bool active[4], i64 slot[4], u32& inserted, u32& err) {
+  u64* table = p.table;
+  u64 h[4], cur[4], seen[4];
+  bool pend[4];
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    pend[s] = active[s] && !isnull[s] && key[s] != VGF_EMPTY_KEY;
+    h[s] = pend[s] ? home_slot(p, key[s]) : 0ull;
+    slot[s] = -1;
+  }
+  // Round 1 reads the home slots (plain L2 loads, all four in flight together; inactive segments
+  // read slot 0) and claims the empty ones.  A stale EMPTY is corrected by the CAS; keys never
+  // change once set, so a non-empty read is final.
+#pragma unroll
+  for (int s = 0; s < 4; ++s) cur[s] = __ldcg(table + h[s] * ROW_WORDS);
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    seen[s] = cur[s];
+    if (pend[s] && cur[s] == VGF_EMPTY_KEY) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
+  }
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    if (!pend[s]) continue;
+    if (seen[s] == VGF_EMPTY_KEY) ++inserted;
+    if (seen[s] == VGF_EMPTY_KEY || seen[s] == key[s]) { slot[s] = (i64)h[s]; pend[s] = false; }
+    else h[s] = (h[s] + 1) & p.cap_mask;
+  }
+  // Later rounds (collisions): one CAS per pending segment per round, again all in flight
+  // together, so a thread pays one round trip per probe step, not one per segment and step.
+  u64 steps = 0;
+  while (pend[0] || pend[1] || pend[2] || pend[3]) {
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (!pend[s]) continue;
+      if (seen[s] == VGF_EMPTY_KEY) ++inserted;
+      if (seen[s] == VGF_EMPTY_KEY || seen[s] == key[s]) { slot[s] = (i64)h[s]; pend[s] = false; }
+      else h[s] = (h[s] + 1) & p.cap_mask;
+    }
+    if (++steps > p.cap_mask) { err |= VGF_ERR_TABLEFULL; break; }
+  }
+  // NULL key / the key that equals the empty marker: dedicated slots past the table
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    if (!active[s] || !(isnull[s] || key[s] == VGF_EMPTY_KEY)) continue;
+    const i64 sl = (i64)p.cap_mask + (isnull[s] ? 1 : 2);
+    u64* kp = table + sl * ROW_WORDS;
+    if (__ldcg(kp) == VGF_EMPTY_KEY) {
+      if (atomicCAS(kp, VGF_EMPTY_KEY, 0ull) == VGF_EMPTY_KEY) ++inserted;
+    }
+    slot[s] = sl;
+  }
+}
+
 template <int KIND>
 __device__ __forceinline__ void hbm_update(u64* addr, u64 v, u32& err) {
   if (KIND == VGF_SUMF64) {

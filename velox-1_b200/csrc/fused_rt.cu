@@ -315,11 +315,13 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
   fp.partials = (vgf::u64*)p.partials;
   fp.table = (vgf::u64*)p.table;
   fp.cap_mask = p.cap_mask;
+  fp.key_min = p.key_map.min; fp.key_span = p.key_map.span; fp.key_scale = p.key_map.scale; fp.key_mode = p.key_map.mode;
   fp.n_groups_ctr = (vgf::u64*)p.n_groups_ctr;
   fp.sel_words = p.sel_words;
   fp.tile_counts = p.tile_counts;
   for (int i = 0; i < p.n_outputs && i < 24; ++i) { fp.out_values[i] = p.outs[i].values; fp.out_nulls[i] = (vgf::u64*)p.outs[i].nulls; }
   void* args[] = {&fp};
+  kernel_timing_begin(stream);
   const int rc = g_cu.launch_kernel(k->function, (unsigned)grid, 1, 1, (unsigned)k->threads, 1, 1, (unsigned)k->smem_bytes, (void*)stream, args, nullptr);
   if (rc != 0) {
     const char* msg = "?";
@@ -327,6 +329,7 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
     set_error("cuLaunchKernel failed: %s", msg ? msg : "?");
     return VGPU_ERR_CUDA;
   }
+  kernel_timing_end(stream);
   count_launch();
   return VGPU_OK;
 }

@@ -83,6 +83,20 @@ struct DevKey {
   uint8_t pad[4];
 };
 
+// Home slot of a key in the HBM table.  mode 0: mix64(key) & cap_mask.  When the caller declares
+// the value range of a single raw key (vgpu_key_spec min < max — the VectorHasher range statistics
+// of the reference, velox/exec/VectorHasher.h:118-578), keys inside it map MONOTONICALLY onto the
+// table (mode 1: key - min when the range fits; mode 2: (key - min) * capacity / range), so sorted
+// or clustered inputs walk the table sequentially instead of scattering one sector per group.
+// Keys outside the range fall back to mode 0.  Every kernel that probes the table uses this.
+struct KeyMap {
+  uint64_t min;
+  uint64_t span;  // max - min
+  uint64_t scale; // mode 2: floor(2^64 * capacity / (span + 1))
+  uint32_t mode;
+  uint32_t pad;
+};
+
 enum SinkMode : int32_t { kSinkFilterProject = 0, kSinkArray = 1, kSinkHash = 2 };
 
 struct DevOut {
@@ -180,6 +194,7 @@ struct PipelineParams {
   // HASH sink
   uint64_t* table; // (capacity + 2) rows of row_words 8-byte words: key, cells...
   uint64_t cap_mask;
+  KeyMap key_map;
   int32_t row_words;
   int32_t raw_key; // single 64-bit raw key
   unsigned long long* n_groups_ctr;
@@ -211,6 +226,10 @@ int cuda_fail(cudaError_t e, const char* what);
   } while (0)
 
 uint32_t* device_err_word();  // per-device latched error bits
+// Optional timing of the scan kernels (vgpu_debug_kernel_timing): events on the launching stream
+// right before / after the kernel, summed by vgpu_debug_kernel_time.
+void kernel_timing_begin(cudaStream_t stream);
+void kernel_timing_end(cudaStream_t stream);
 void count_launch(int n = 1);
 int num_sms();
 

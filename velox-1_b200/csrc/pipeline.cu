@@ -925,7 +925,7 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
           }
         } else if (MODE == kSinkHash) {
           HashRef href;
-          href.table = p.table; href.cap_mask = p.cap_mask; href.row_words = p.row_words; href.n_groups_ctr = p.n_groups_ctr;
+          href.table = p.table; href.cap_mask = p.cap_mask; href.key_map = p.key_map; href.row_words = p.row_words; href.n_groups_ctr = p.n_groups_ctr;
           // Rows of a thread are adjacent in the input; a row reuses its left neighbour's slot
           // when the keys are equal (sorted / clustered keys such as l_orderkey).
 #pragma unroll
@@ -1650,7 +1650,9 @@ int launch_pipeline(PipelineParams& p, int tab_bytes, int grid, cudaStream_t str
   if (rc) return rc;
   auto run = [&](auto kernel) -> int {
     VG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    kernel_timing_begin(stream);
     kernel<<<grid, kThreads, smem, stream>>>(p);
+    kernel_timing_end(stream);
     VG_CUDA(cudaGetLastError());
     count_launch();
     return VGPU_OK;
