@@ -237,6 +237,38 @@ __global__ void merge_rows_hash_kernel(const uint64_t* rows, int64_t n, RowMap r
   if (err) atomicOr(err_word, err);
 }
 
+// Inserts the segments the fused HASH kernels parked ({key, cell values...}, row_words words each):
+// one segment per thread, so a long probe chain delays 31 neighbours, not a scan warp's 128 rows.
+__global__ void drain_overflow_kernel(const uint64_t* ovf, const unsigned long long* cursor, uint64_t cap,
+                                      HashRef h, CellMeta m, uint32_t* err_word) {
+  const uint64_t n = min((uint64_t)*cursor, cap);
+  const int rw = h.row_words;
+  uint32_t err = 0, inserted = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t* e = ovf + i * rw;
+    const uint64_t key = e[0];
+    uint64_t slot = home_slot(h.key_map, h.cap_mask, key);
+    bool found = false;
+    for (uint64_t probes = 0; probes <= h.cap_mask + kBucketSteps; ++probes) {
+      const unsigned long long seen = atomicCAS(reinterpret_cast<unsigned long long*>(h.table + slot * rw), kEmptyKey, (unsigned long long)key);
+      if (seen == kEmptyKey) { ++inserted; found = true; break; }
+      if (seen == key) { found = true; break; }
+      slot = next_slot(h.key_map, h.cap_mask, slot, probes);
+    }
+    if (!found) { err |= kErrTableFull; continue; }
+    for (int c = 0; c < m.n_cells; ++c) {
+      const uint64_t v = e[1 + c];
+      if (v == cell_identity(m.kind[c])) continue;
+      uint64_t* cell = h.table + slot * rw + 1 + c;
+      if (m.kind[c] == kCellCount) atomicAdd(reinterpret_cast<unsigned long long*>(cell), (unsigned long long)v); // a run's row count
+      else update_hbm_cell(m.kind[c], cell, v, err);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) inserted += __shfl_xor_sync(0xffffffffu, inserted, o);
+  if ((threadIdx.x & 31) == 0 && inserted) atomicAdd(h.n_groups_ctr, (unsigned long long)inserted);
+  if (err) atomicOr(err_word, err);
+}
+
 // ---- partitioning packed rows ----------------------------------------------------------------
 __device__ __forceinline__ int part_of(const uint64_t* row, int n_parts) {
   return (int)(mix64(row[0] ^ (row[1] << 63)) % (uint64_t)n_parts);
@@ -356,6 +388,7 @@ int agg_resolve(Agg& a, const Program& prog) {
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
+constexpr int kDefaultBucketBits = 5;
 static KeyMap key_map_of(const Agg& a) {
   KeyMap m{};
   // Measured on B200 (profiles/r01_notes.md): for sorted l_orderkey the monotone placement is
@@ -363,6 +396,15 @@ static KeyMap key_map_of(const Agg& a) {
   // and their CAS / RED operations serialise in the L2 atomic unit.  Kept behind
   // VGPU_RANGED_KEYS=1 for experiments; the default is the hashed placement.
   static const bool enabled = getenv("VGPU_RANGED_KEYS") != nullptr && getenv("VGPU_RANGED_KEYS")[0] == '1';
+  // Bucketed placement (mode 3): keys that share key >> b land in one aligned bucket of 2^b slots,
+  // each at its own (rotated) position, so sorted / clustered keys fill whole lines of the table
+  // while random keys still spread uniformly.  VGPU_BUCKET_BITS=0 selects the plain hash.
+  static const int bucket_bits = getenv("VGPU_BUCKET_BITS") ? atoi(getenv("VGPU_BUCKET_BITS")) : kDefaultBucketBits;
+  if (!enabled && bucket_bits > 0 && bucket_bits <= 8) {
+    m.mode = 3;
+    m.pad = (uint32_t)bucket_bits;
+    return m;
+  }
   if (enabled && a.keys.size() == 1 && a.keys[0].bits == 64 && a.keys[0].max > a.keys[0].min && a.capacity > 0) {
     m.min = (uint64_t)a.keys[0].min;
     m.span = (uint64_t)a.keys[0].max - (uint64_t)a.keys[0].min;
@@ -610,8 +652,24 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     p.table = a.table; p.cap_mask = a.capacity - 1; p.key_map = key_map_of(a); p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
     int fgrid = 0;
     FusedKernel* fk = fused_prepare(p, &fgrid);
+    static const bool parking = !(getenv("VGPU_NO_PARKING") && getenv("VGPU_NO_PARKING")[0] == '1');
+    if (fk && parking) {
+      const uint64_t want = std::max<uint64_t>(1u << 20, a.capacity / 8);
+      if (a.ovf_cap < want) {
+        if (a.ovf) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(a.ovf)); a.ovf = nullptr; }
+        VG_CUDA(cudaMalloc(&a.ovf, want * a.row_words * 8));
+        a.ovf_cap = want;
+      }
+      VG_CUDA(cudaMemsetAsync(a.ctr + 2, 0, sizeof(unsigned long long), stream));
+      p.ovf = a.ovf; p.ovf_cap = a.ovf_cap; p.ovf_cursor = a.ctr + 2;
+    }
     rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
     if (rc) return rc;
+    if (p.ovf) {
+      drain_overflow_kernel<<<num_sms() * 8, 256, 0, stream>>>(a.ovf, a.ctr + 2, a.ovf_cap, href_of(a), cell_meta(a), device_err_word());
+      VG_CUDA(cudaGetLastError());
+      count_launch();
+    }
     done += piece;
   }
   return VGPU_OK;
@@ -745,7 +803,8 @@ int agg_reset(Agg& a, cudaStream_t stream) {
 }
 
 void agg_free(Agg& a) {
-  cudaFree(a.state); cudaFree(a.partials); cudaFree(a.table); cudaFree(a.ctr); cudaFree(a.packed);
+  cudaFree(a.state); cudaFree(a.partials); cudaFree(a.table); cudaFree(a.ctr); cudaFree(a.packed); cudaFree(a.ovf);
+  a.ovf = nullptr; a.ovf_cap = 0;
   a.state = a.partials = a.table = a.packed = nullptr; a.ctr = nullptr;
 }
 

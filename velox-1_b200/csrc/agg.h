@@ -39,7 +39,9 @@ struct Agg {
   int row_words = 0;
   uint8_t shifts[kMaxKeys] = {0};
   bool hash_aliased[kMaxCells]; // count cell still equals the rows cell (never updated on its own)
-  unsigned long long* ctr = nullptr; // device: [0] groups, [1] scratch counter
+  unsigned long long* ctr = nullptr; // device: [0] groups, [1] scratch counter, [2] overflow cursor
+  uint64_t* ovf = nullptr;     // parked segments of the fused HASH kernels (see PipelineParams::ovf)
+  uint64_t ovf_cap = 0;        // entries
   // extraction cache
   uint64_t* packed = nullptr;
   int64_t packed_rows = -1;    // -1 = stale

@@ -27,9 +27,19 @@ __device__ __forceinline__ uint64_t mix64(uint64_t k) { // splitmix64 finaliser
 constexpr uint64_t kEmptyKey = 0xffffffffffffffffull;
 
 __device__ __forceinline__ uint64_t home_slot(const KeyMap& m, uint64_t cap_mask, uint64_t key) {
+  if (m.mode == 3) {
+    const uint32_t b = m.pad;
+    const uint64_t g = mix64(key >> b), lowmask = (1ull << b) - 1ull;
+    return (((g << b) & cap_mask) & ~lowmask) | ((key + (g >> 56)) & lowmask);
+  }
   const uint64_t d = key - m.min;
   if (m.mode != 0 && d <= m.span) return m.mode == 1 ? d : __umul64hi(d, m.scale);
   return mix64(key) & cap_mask;
+}
+constexpr uint64_t kBucketSteps = 24; // same probe sequence as fused_prelude.cuh next_slot()
+__device__ __forceinline__ uint64_t next_slot(const KeyMap& m, uint64_t cap_mask, uint64_t h, uint64_t probes) {
+  const uint64_t step = (m.mode == 3 && probes < kBucketSteps) ? (1ull << m.pad) : 1ull;
+  return (h + step) & cap_mask;
 }
 
 // Order-preserving int64 image of a double (for atomicMin/Max on doubles in HBM).
@@ -84,7 +94,7 @@ __device__ __forceinline__ int64_t hash_find_or_insert(const HashRef& p, uint64_
     return slot;
   }
   uint64_t h = home_slot(p.key_map, p.cap_mask, key);
-  for (uint64_t probes = 0; probes <= p.cap_mask; ++probes) {
+  for (uint64_t probes = 0; probes <= p.cap_mask + kBucketSteps; ++probes) {
     unsigned long long* kp = reinterpret_cast<unsigned long long*>(table + h * rw);
     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(kp);
     if (cur == key) return (int64_t)h;
@@ -96,7 +106,7 @@ __device__ __forceinline__ int64_t hash_find_or_insert(const HashRef& p, uint64_
       }
       if (cur == key) return (int64_t)h;
     }
-    h = (h + 1) & p.cap_mask;
+    h = next_slot(p.key_map, p.cap_mask, h, probes);
   }
   err |= kErrTableFull;
   return -1;

@@ -321,7 +321,25 @@ struct Gen {
     out("    }\n");
   }
 
+  // Next block's input lines -> L2 (no registers held): the warp's following iteration then starts
+  // from L2 latency instead of HBM latency.  One 128-byte line per lane per column.
+  void gen_input_prefetch() {
+    out("    if (blk + nwarps < n_full) {\n");
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c]) continue;
+      const DevCol& d = p.cols[c];
+      if (d.encoding == VGPU_CONSTANT) continue;
+      const bool dict = d.encoding == VGPU_DICTIONARY;
+      const int w = dict ? 4 : (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) ? 8 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 4 : 0;
+      if (!w) continue;
+      out("      if (lane < %d) prefetch_l2(reinterpret_cast<const char*>(p.%s[%d]) + (blk + nwarps) * %d + lane * 128);\n",
+          w, dict ? "indices" : "values", c, 128 * w);
+    }
+    out("    }\n");
+  }
+
   void gen_hash_body(bool full) {
+    if (full) gen_input_prefetch();
     gen_block_header(full);
     out("    u64 KEY[4]; bool KN[4], PASS[4];\n");
     for (int i = 0; i < n_live; ++i) out("    u64 X%d[4]; bool L%d[4];\n", live_cells[i], live_cells[i]);
@@ -334,6 +352,10 @@ struct Gen {
     }
     out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
     gen_raise();
+    out("    }\n");
+    // home slots of the rows' keys -> L2 while the run aggregation below computes
+    out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
+    out("      if (PASS[j] && !KN[j] && (j == 0 || KEY[j] != KEY[j - 1])) prefetch_l2(p.table + home_slot(p, KEY[j]) * %d);\n", p.row_words);
     out("    }\n");
     // Run aggregation before the table is touched.  Equal keys tend to arrive together (sorted or
     // clustered inputs such as l_orderkey), so per 64-row half block: (1) a thread folds its two
@@ -380,7 +402,40 @@ struct Gen {
     out("    }\n");
     // the (up to) four segments of the thread probe the table together: their first reads and
     // their claims overlap instead of forming four dependent round trips to HBM
-    out("    i64 SL[4];\n    hash_probe4<%d>(p, SK, SN, SA, SL, inserted, accerr);\n", p.row_words);
+    const char* stage_env = getenv("VGPU_DEBUG_STAGE"); // experiments only: 1 = no table access, 2 = table loads only
+    const int stage = stage_env ? atoi(stage_env) : 0;
+    if (stage == 1) {
+      out("    u32 chk = 0; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm]) chk += (u32)(SK[sgm] ^ SV%d[sgm]);\n    if (chk == 0x9e3779b9u) ++inserted;\n", live_cells[0]);
+      out("    /* debug stage 1 */\n");
+      return;
+    }
+    if (stage == 2) {
+      out("    u32 chk = 0; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm]) chk += (u32)__ldcg(p.table + home_slot(p, SK[sgm]) * %d);\n    if (chk == 0x9e3779b9u) ++inserted;\n", p.row_words);
+      out("    /* debug stage 2 */\n");
+      return;
+    }
+    if (stage == 4) { // REDs at the home slots, no claim
+      out("    i64 SL[4]; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) SL[sgm] = SA[sgm] ? (i64)home_slot(p, SK[sgm]) : -1;\n");
+    } else {
+      out("    i64 SL[4]; bool PK[4];\n    hash_probe4<%d>(p, SK, SN, SA, SL, PK, inserted, accerr);\n", p.row_words);
+      // park what the first claim did not settle (or, buffer full, walk the table here)
+      out("    if (p.ovf != nullptr) {\n      i64 OE[4]; ovf_reserve(p, PK, OE);\n");
+      out("      _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n        if (!PK[sgm]) continue;\n");
+      out("        if (OE[sgm] < (i64)p.ovf_cap) {\n          u64* e = p.ovf + OE[sgm] * %d;\n          e[0] = SK[sgm];\n", p.row_words);
+      for (int c = 0; c < p.n_cells && 1 + c < p.row_words; ++c) {
+        bool live = false;
+        for (int i = 0; i < n_live; ++i) live = live || live_cells[i] == c;
+        if (live) out("          e[%d] = SV%d[sgm];\n", 1 + c, c);
+        else out("          e[%d] = cell_identity<%d>();\n", 1 + c, p.cells[c].kind);
+      }
+      out("        } else {\n          SL[sgm] = hash_walk<%d>(p, SK[sgm], home_slot(p, SK[sgm]), inserted, accerr);\n        }\n      }\n    }\n", p.row_words);
+    }
+    if (stage == 3) { out("    /* debug stage 3: claims only */\n"); return; }
+    if (stage == 5 || stage == 6) { // claims + only one of the two updates
+      out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm] && SL[sgm] >= 0) hbm_update<%d>(p.table + SL[sgm] * %d + %d, SV%d[sgm], accerr);\n",
+          p.cells[live_cells[stage - 5]].kind, p.row_words, 1 + live_cells[stage - 5], live_cells[stage - 5]);
+      return;
+    }
     out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (SA[sgm] && SL[sgm] >= 0) {\n");
     for (int i = 0; i < n_live; ++i) {
       const int c = live_cells[i];

@@ -77,6 +77,10 @@ struct FusedParams {
   i32* tile_counts;
   void* out_values[24];
   u64* out_nulls[24];
+  // HASH sink: parked segments (see hash_probe4 / ovf_reserve)
+  u64* ovf;
+  u64 ovf_cap;
+  u64* ovf_cursor;
 };
 
 __device__ __forceinline__ u64 d2u(double d) { return (u64)__double_as_longlong(d); }
@@ -90,6 +94,10 @@ __device__ __forceinline__ uint4 ld16(const void* base, i64 byte_off) {
 }
 __device__ __forceinline__ uint2 ld8(const void* base, i64 byte_off) {
   return __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(base) + byte_off));
+}
+// pulls one 128-byte line into L2 without occupying a register (next block's input, a key's home slot)
+__device__ __forceinline__ void prefetch_l2(const void* ptr) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
 }
 // rows r, r+1 of a bitmap (r even): 2 bits
 __device__ __forceinline__ u32 bits2(const u64* bits, i64 r) {
@@ -349,8 +357,21 @@ __device__ __forceinline__ i64 f64_ordered(u64 bits) {
 }
 __device__ __forceinline__ u64 home_slot(const FusedParams& p, u64 key) {
   const u64 d = key - p.key_min;
+  if (p.key_mode == 3) { // bucketed placement: see internal.h KeyMap
+    const u32 b = p.key_pad;
+    const u64 g = mix64(key >> b), lowmask = (1ull << b) - 1ull;
+    return (((g << b) & p.cap_mask) & ~lowmask) | ((key + (g >> 56)) & lowmask);
+  }
   if (p.key_mode != 0 && d <= p.key_span) return p.key_mode == 1 ? d : __umul64hi(d, p.key_scale);
   return mix64(key) & p.cap_mask;
+}
+// Next slot of a probe sequence.  Bucketed placement first steps bucket by bucket (keeping the
+// position inside the bucket, so a displaced run of neighbouring keys stays together), then
+// falls back to slot-by-slot so that every slot is eventually visited.
+#define VGF_BUCKET_STEPS 24ull
+__device__ __forceinline__ u64 next_slot(const FusedParams& p, u64 h, u64 probes) {
+  const u64 step = (p.key_mode == 3 && probes < VGF_BUCKET_STEPS) ? (1ull << p.key_pad) : 1ull;
+  return (h + step) & p.cap_mask;
 }
 template <int ROW_WORDS>
 __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key, bool isnull, u32& err) {
@@ -364,7 +385,7 @@ __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key
     return slot;
   }
   u64 h = home_slot(p, key);
-  for (u64 probes = 0; probes <= p.cap_mask; ++probes) {
+  for (u64 probes = 0; probes <= p.cap_mask + VGF_BUCKET_STEPS; ++probes) {
     u64* kp = table + h * ROW_WORDS;
     u64 cur = *reinterpret_cast<volatile u64*>(kp);
     if (cur == key) return (i64)h;
@@ -373,7 +394,7 @@ __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key
       if (cur == VGF_EMPTY_KEY) { atomicAdd(p.n_groups_ctr, 1ull); return (i64)h; }
       if (cur == key) return (i64)h;
     }
-    h = (h + 1) & p.cap_mask;
+    h = next_slot(p, h, probes);
   }
   err |= VGF_ERR_TABLEFULL;
   return -1;
@@ -386,7 +407,7 @@ __device__ __forceinline__ i64 hash_find_or_insert(const FusedParams& p, u64 key
 template <int ROW_WORDS>
 __device__ __forceinline__ i64 hash_walk(const FusedParams& p, u64 key, u64 h, u32& inserted, u32& err) {
   u64* table = p.table;
-  for (u64 probes = 0; probes <= p.cap_mask; ++probes) {
+  for (u64 probes = 0; probes <= p.cap_mask + VGF_BUCKET_STEPS; ++probes) {
     u64* kp = table + h * ROW_WORDS;
     u64 cur = __ldcg(kp);
     if (cur == key) return (i64)h;
@@ -395,16 +416,16 @@ __device__ __forceinline__ i64 hash_walk(const FusedParams& p, u64 key, u64 h, u
       if (cur == VGF_EMPTY_KEY) { ++inserted; return (i64)h; }
       if (cur == key) return (i64)h;
     }
-    h = (h + 1) & p.cap_mask;
+    h = next_slot(p, h, probes);
   }
   err |= VGF_ERR_TABLEFULL;
   return -1;
 }
 template <int ROW_WORDS>
 __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[4], const bool isnull[4],
-                                            const bool active[4], i64 slot[4], u32& inserted, u32& err) {
+                                            const bool active[4], i64 slot[4], bool parked[4], u32& inserted, u32& err) {
   u64* table = p.table;
-  u64 h[4], cur[4], seen[4];
+  u64 h[4], seen[4];
   bool pend[4];
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
@@ -412,39 +433,21 @@ __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[
     h[s] = pend[s] ? home_slot(p, key[s]) : 0ull;
     slot[s] = -1;
   }
-  // Round 1 reads the home slots (plain L2 loads, all four in flight together; inactive segments
-  // read slot 0) and claims the empty ones.  A stale EMPTY is corrected by the CAS; keys never
-  // change once set, so a non-empty read is final.
-#pragma unroll
-  for (int s = 0; s < 4; ++s) cur[s] = __ldcg(table + h[s] * ROW_WORDS);
+  // Round 1 claims the home slots directly (one atomic round trip, all four in flight together;
+  // the caller prefetched the lines into L2 while the run aggregation was computing).  The CAS
+  // returns the resident key when the slot is taken, which is all a lookup needs: keys never
+  // change once set.
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
-    seen[s] = cur[s];
-    if (pend[s] && cur[s] == VGF_EMPTY_KEY) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
+    seen[s] = VGF_EMPTY_KEY;
+    if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
   }
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     if (!pend[s]) continue;
     if (seen[s] == VGF_EMPTY_KEY) ++inserted;
     if (seen[s] == VGF_EMPTY_KEY || seen[s] == key[s]) { slot[s] = (i64)h[s]; pend[s] = false; }
-    else h[s] = (h[s] + 1) & p.cap_mask;
-  }
-  // Later rounds (collisions): one CAS per pending segment per round, again all in flight
-  // together, so a thread pays one round trip per probe step, not one per segment and step.
-  u64 steps = 0;
-  while (pend[0] || pend[1] || pend[2] || pend[3]) {
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
-    }
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      if (!pend[s]) continue;
-      if (seen[s] == VGF_EMPTY_KEY) ++inserted;
-      if (seen[s] == VGF_EMPTY_KEY || seen[s] == key[s]) { slot[s] = (i64)h[s]; pend[s] = false; }
-      else h[s] = (h[s] + 1) & p.cap_mask;
-    }
-    if (++steps > p.cap_mask) { err |= VGF_ERR_TABLEFULL; break; }
+    else h[s] = next_slot(p, h[s], 0ull);
   }
   // NULL key / the key that equals the empty marker: dedicated slots past the table
 #pragma unroll
@@ -456,6 +459,51 @@ __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[
       if (atomicCAS(kp, VGF_EMPTY_KEY, 0ull) == VGF_EMPTY_KEY) ++inserted;
     }
     slot[s] = sl;
+  }
+  // A warp waits for its slowest lane, and at 50 % load a few of its ~32 claims always need several
+  // more round trips.  With a parking buffer those segments leave the scan here: the caller stores
+  // {key, partials} and drain_overflow_kernel (agg.cu) inserts them with one segment per thread.
+#pragma unroll
+  for (int s = 0; s < 4; ++s) parked[s] = pend[s] && p.ovf != nullptr;
+  if (p.ovf != nullptr) return;
+  // Later rounds (collisions): one CAS per pending segment per round, again all in flight
+  // together, so a thread pays one round trip per probe step, not one per segment and step.
+  u64 steps = 1;
+  while (pend[0] || pend[1] || pend[2] || pend[3]) {
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (!pend[s]) continue;
+      if (seen[s] == VGF_EMPTY_KEY) ++inserted;
+      if (seen[s] == VGF_EMPTY_KEY || seen[s] == key[s]) { slot[s] = (i64)h[s]; pend[s] = false; }
+      else h[s] = next_slot(p, h[s], steps);
+    }
+    if (++steps > p.cap_mask + VGF_BUCKET_STEPS) { err |= VGF_ERR_TABLEFULL; break; }
+  }
+}
+
+// Entry numbers in the parking buffer for the warp's unresolved segments (one atomic per warp).
+// Must be called by all 32 lanes.  Numbers >= p.ovf_cap mean "buffer full": the caller walks the
+// table itself for those.
+__device__ __forceinline__ void ovf_reserve(const FusedParams& p, const bool parked[4], i64 entry[4]) {
+  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  u32 m[4], total = 0;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) { m[s] = __ballot_sync(0xffffffffu, parked[s]); total += __popc(m[s]); }
+#pragma unroll
+  for (int s = 0; s < 4; ++s) entry[s] = -1;
+  if (total == 0) return;
+  u64 base = 0;
+  if (lane == 0) base = atomicAdd(p.ovf_cursor, (u64)total);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  u32 off = 0;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    if (parked[s]) entry[s] = (i64)(base + off + __popc(m[s] & lt));
+    off += __popc(m[s]);
   }
 }
 

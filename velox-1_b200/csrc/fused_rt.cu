@@ -315,8 +315,9 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
   fp.partials = (vgf::u64*)p.partials;
   fp.table = (vgf::u64*)p.table;
   fp.cap_mask = p.cap_mask;
-  fp.key_min = p.key_map.min; fp.key_span = p.key_map.span; fp.key_scale = p.key_map.scale; fp.key_mode = p.key_map.mode;
+  fp.key_min = p.key_map.min; fp.key_span = p.key_map.span; fp.key_scale = p.key_map.scale; fp.key_mode = p.key_map.mode; fp.key_pad = p.key_map.pad;
   fp.n_groups_ctr = (vgf::u64*)p.n_groups_ctr;
+  fp.ovf = (vgf::u64*)p.ovf; fp.ovf_cap = p.ovf_cap; fp.ovf_cursor = (vgf::u64*)p.ovf_cursor;
   fp.sel_words = p.sel_words;
   fp.tile_counts = p.tile_counts;
   for (int i = 0; i < p.n_outputs && i < 24; ++i) { fp.out_values[i] = p.outs[i].values; fp.out_nulls[i] = (vgf::u64*)p.outs[i].nulls; }

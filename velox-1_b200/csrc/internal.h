@@ -198,6 +198,11 @@ struct PipelineParams {
   int32_t row_words;
   int32_t raw_key; // single 64-bit raw key
   unsigned long long* n_groups_ctr;
+  // HASH sink, fused kernels: segments whose first claim met another key are parked here as
+  // {key, cell values...} (row_words words each) and inserted by drain_overflow_kernel afterwards
+  uint64_t* ovf;
+  uint64_t ovf_cap; // entries
+  unsigned long long* ovf_cursor;
   // FILTER_PROJECT sink
   uint32_t* sel_words;
   int32_t* tile_counts;
