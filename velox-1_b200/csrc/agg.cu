@@ -388,7 +388,7 @@ int agg_resolve(Agg& a, const Program& prog) {
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
-constexpr int kDefaultBucketBits = 5;
+constexpr int kDefaultBucketBits = 6; // profiles/r01_c3_experiments.md: 3..7 measured within 4 % of each other
 static KeyMap key_map_of(const Agg& a) {
   KeyMap m{};
   // Measured on B200 (profiles/r01_notes.md): for sorted l_orderkey the monotone placement is

@@ -402,21 +402,7 @@ struct Gen {
     out("    }\n");
     // the (up to) four segments of the thread probe the table together: their first reads and
     // their claims overlap instead of forming four dependent round trips to HBM
-    const char* stage_env = getenv("VGPU_DEBUG_STAGE"); // experiments only: 1 = no table access, 2 = table loads only
-    const int stage = stage_env ? atoi(stage_env) : 0;
-    if (stage == 1) {
-      out("    u32 chk = 0; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm]) chk += (u32)(SK[sgm] ^ SV%d[sgm]);\n    if (chk == 0x9e3779b9u) ++inserted;\n", live_cells[0]);
-      out("    /* debug stage 1 */\n");
-      return;
-    }
-    if (stage == 2) {
-      out("    u32 chk = 0; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm]) chk += (u32)__ldcg(p.table + home_slot(p, SK[sgm]) * %d);\n    if (chk == 0x9e3779b9u) ++inserted;\n", p.row_words);
-      out("    /* debug stage 2 */\n");
-      return;
-    }
-    if (stage == 4) { // REDs at the home slots, no claim
-      out("    i64 SL[4]; _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) SL[sgm] = SA[sgm] ? (i64)home_slot(p, SK[sgm]) : -1;\n");
-    } else {
+    {
       out("    i64 SL[4]; bool PK[4];\n    hash_probe4<%d>(p, SK, SN, SA, SL, PK, inserted, accerr);\n", p.row_words);
       // park what the first claim did not settle (or, buffer full, walk the table here)
       out("    if (p.ovf != nullptr) {\n      i64 OE[4]; ovf_reserve(p, PK, OE);\n");
@@ -429,12 +415,6 @@ struct Gen {
         else out("          e[%d] = cell_identity<%d>();\n", 1 + c, p.cells[c].kind);
       }
       out("        } else {\n          SL[sgm] = hash_walk<%d>(p, SK[sgm], home_slot(p, SK[sgm]), inserted, accerr);\n        }\n      }\n    }\n", p.row_words);
-    }
-    if (stage == 3) { out("    /* debug stage 3: claims only */\n"); return; }
-    if (stage == 5 || stage == 6) { // claims + only one of the two updates
-      out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (SA[sgm] && SL[sgm] >= 0) hbm_update<%d>(p.table + SL[sgm] * %d + %d, SV%d[sgm], accerr);\n",
-          p.cells[live_cells[stage - 5]].kind, p.row_words, 1 + live_cells[stage - 5], live_cells[stage - 5]);
-      return;
     }
     out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (SA[sgm] && SL[sgm] >= 0) {\n");
     for (int i = 0; i < n_live; ++i) {
