@@ -1,0 +1,459 @@
+// Tests of the C++ operator shim (velox-1_b200/host), written the way the reference tests its operators:
+// build a plan with PlanBuilder, run it, compare the result vectors with an independent answer
+// (velox/exec/tests/FilterProjectTest.cpp, AggregationTest.cpp, OperatorExtensibility example).
+//   host_tests cpu   no device needed: parser, lowering, plan types, registration seams, decoding
+//   host_tests gpu   the GPU operators against oracle/liboracle.so (vcpu_run) and plain C++ answers
+#include <cmath>
+#include <cstdio>
+#include <map>
+#include <set>
+
+#include "../../oracle/velox_cpu.h"
+#include "../../velox-1_b200/host/GpuDevice.h"
+
+using namespace vb200;
+using namespace vb200::core;
+
+// HOST_TESTS_TRACE=1: print a backtrace where any exception is thrown (there is no debugger on the GPU box)
+#include <dlfcn.h>
+#include <execinfo.h>
+#include <typeinfo>
+#include <cxxabi.h>
+namespace __cxxabiv1 {
+extern "C" void __cxa_throw(void* ex, std::type_info* info, void (_GLIBCXX_CDTOR_CALLABI* dest)(void*)) {
+  static auto real = (void (*)(void*, std::type_info*, void (*)(void*)))dlsym(RTLD_NEXT, "__cxa_throw");
+  if (getenv("HOST_TESTS_TRACE")) {
+    void* frames[32];
+    const int n = backtrace(frames, 32);
+    fprintf(stderr, "throw %s\n", info->name());
+    backtrace_symbols_fd(frames, n, 2);
+  }
+  real(ex, info, dest);
+  __builtin_unreachable();
+}
+} // namespace __cxxabiv1
+
+static int g_failed = 0, g_checks = 0;
+#define EXPECT(cond) do { ++g_checks; if (!(cond)) { ++g_failed; printf("  FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); } } while (0)
+#define EXPECT_THROW(stmt, Ex) do { ++g_checks; bool t_ = false; try { stmt; } catch (const Ex&) { t_ = true; } catch (...) {} if (!t_) { ++g_failed; printf("  FAILED %s:%d: expected %s from %s\n", __FILE__, __LINE__, #Ex, #stmt); } } while (0)
+static void section(const char* name) { printf("[ RUN ] %s\n", name); }
+
+// ---- deterministic lineitem-shaped data (value domains of dbgen, velox/tpch/gen/dbgen/include/dbgen/dss.h:321-334)
+struct Lcg { uint64_t s; uint32_t next() { s = s * 6364136223846793005ull + 1442695040888963407ull; return (uint32_t)(s >> 33); } int range(int lo, int hi) { return lo + (int)(next() % (uint32_t)(hi - lo + 1)); } };
+struct Lineitem {
+  std::vector<int64_t> orderkey;
+  std::vector<double> quantity, extendedprice, discount, tax;
+  std::vector<int32_t> shipdate, flag, status, mode, instruct;
+};
+static Lineitem makeLineitem(size_t n, uint64_t seed, int64_t firstOrder = 0) {
+  Lineitem t;
+  Lcg r{seed};
+  int64_t order = firstOrder;
+  int left = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (left == 0) { ++order; left = r.range(1, 7); }
+    --left;
+    t.orderkey.push_back(((order >> 3) << 5) + (order & 7) + 1);
+    const int q = r.range(1, 50);
+    t.quantity.push_back(q * 0.01);
+    t.extendedprice.push_back((int64_t)(90000 + r.range(0, 110000)) * q * 0.01);
+    t.discount.push_back(r.range(0, 10) * 0.01);
+    t.tax.push_back(r.range(0, 8) * 0.01);
+    t.shipdate.push_back(r.range(8036, 10591));
+    t.flag.push_back(r.range(0, 2));
+    t.status.push_back(r.range(0, 1));
+    t.mode.push_back(r.range(0, 6));
+    t.instruct.push_back(r.range(0, 3));
+  }
+  return t;
+}
+static const char* kFlags[] = {"A", "N", "R"};
+static const char* kStatus[] = {"F", "O"};
+static const char* kModes[] = {"AIR", "FOB", "MAIL", "RAIL", "REG AIR", "SHIP", "TRUCK"};
+static const char* kInstruct[] = {"COLLECT COD", "DELIVER IN PERSON", "NONE", "TAKE BACK RETURN"};
+
+static VectorPtr stringDictionary(const std::vector<int32_t>& ids, const char* const* names, int n) {
+  std::vector<std::string> base(names, names + n);
+  return wrapInDictionary(ids, makeFlatVector<std::string>(VARCHAR(), base));
+}
+static RowVectorPtr lineitemVector(const Lineitem& t, size_t from, size_t to) {
+  auto sl = [&](auto& v) { return std::decay_t<decltype(v)>(v.begin() + from, v.begin() + to); };
+  return makeRowVector(
+      {"l_orderkey", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate", "l_returnflag", "l_linestatus"},
+      {makeFlatVector<int64_t>(BIGINT(), sl(t.orderkey)), makeFlatVector<double>(DOUBLE(), sl(t.quantity)),
+       makeFlatVector<double>(DOUBLE(), sl(t.extendedprice)), makeFlatVector<double>(DOUBLE(), sl(t.discount)),
+       makeFlatVector<double>(DOUBLE(), sl(t.tax)), makeFlatVector<int32_t>(DATE(), sl(t.shipdate)),
+       stringDictionary(sl(t.flag), kFlags, 3), stringDictionary(sl(t.status), kStatus, 2)});
+}
+static std::vector<RowVectorPtr> batches(const Lineitem& t, size_t batchRows) {
+  std::vector<RowVectorPtr> out;
+  for (size_t at = 0; at < t.orderkey.size(); at += batchRows) out.push_back(lineitemVector(t, at, std::min(t.orderkey.size(), at + batchRows)));
+  return out;
+}
+
+// ---- reading result vectors ---------------------------------------------------------------------------
+static bool isNullAt(const VectorPtr& v, size_t i) { return v->mayHaveNulls() && !bits::isBitSet(v->nulls().data(), i); }
+template <typename T> static T at(const VectorPtr& v, size_t i) {
+  gpu::Decoded d = gpu::decode(v);
+  const size_t r = d.constant ? 0 : d.indices.empty() ? i : (size_t)d.indices[i];
+  return static_cast<const FlatVector<T>*>(d.base)->valueAt(r);
+}
+static bool close(double a, double b, double rtol = 1e-9) { return std::fabs(a - b) <= rtol * std::max(std::fabs(b), 1e-300); }
+
+static const char* kQ6Filter = "l_shipdate >= '1994-01-01'::DATE and l_shipdate < '1995-01-01'::DATE and l_discount between 0.05 and 0.07 and l_quantity < 0.24";
+
+// =========================================================================================================
+// cpu: everything that needs no device
+// =========================================================================================================
+struct PassThrough : exec::Operator { // a CPU operator for a custom plan node (OperatorExtensibility example)
+  PassThrough(exec::DriverCtx* c, int32_t id, const PlanNodePtr& n) : Operator(c, n->outputType(), id, n->id(), "PassThrough") {}
+  bool needsInput() const override { return !input_ && !noMoreInput_; }
+  void addInput(RowVectorPtr in) override { input_ = std::move(in); ++batches; }
+  RowVectorPtr getOutput() override { auto r = std::move(input_); input_ = nullptr; return r; }
+  bool isFinished() override { return noMoreInput_ && !input_; }
+  static int batches;
+};
+int PassThrough::batches = 0;
+struct CustomNode : PlanNode {
+  CustomNode(PlanNodeId id, PlanNodePtr src) : PlanNode(std::move(id), {src}) {}
+  const RowTypePtr& outputType() const override { return sources()[0]->outputType(); }
+  std::string name() const override { return "Custom"; }
+};
+struct CustomTranslator : exec::PlanNodeTranslator {
+  std::unique_ptr<exec::Operator> toOperator(exec::DriverCtx* c, int32_t id, const PlanNodePtr& n) override {
+    if (std::dynamic_pointer_cast<const CustomNode>(n)) return std::make_unique<PassThrough>(c, id, n);
+    return nullptr;
+  }
+};
+
+static void cpuTests() {
+  auto t = makeLineitem(1000, 1);
+  auto rv = lineitemVector(t, 0, 1000);
+  const auto& row = rv->rowType();
+
+  section("parser: dates, literal typing, operator names (DuckParser.cpp:53-110)");
+  EXPECT(parse::parseDate("1970-01-01") == 0);
+  EXPECT(parse::parseDate("1994-01-01") == 8766);
+  EXPECT(parse::parseDate("1998-09-02") == 10471);
+  auto f = parse::parseExpr(kQ6Filter, row);
+  EXPECT(f->toString() == "and(gte(l_shipdate,8766),lt(l_shipdate,9131),between(l_discount,0.050000,0.070000),lt(l_quantity,0.240000))");
+  EXPECT(f->inputs().size() == 4); // nested ANDs flattened (ExprCompiler.cpp:131-158)
+  std::string alias;
+  auto p = parse::parseExpr("l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax) as charge", row, &alias);
+  EXPECT(alias == "charge" && p->type()->kind() == TypeKind::DOUBLE);
+  EXPECT(p->toString() == "multiply(multiply(l_extendedprice,minus(1.000000,l_discount)),plus(1.000000,l_tax))");
+  EXPECT(parse::parseExpr("l_orderkey + 1", row)->type()->kind() == TypeKind::BIGINT);
+  EXPECT(parse::parseExpr("cast(l_orderkey as double) / 2.0", row)->toString() == "divide(cast(l_orderkey as DOUBLE),2.000000)");
+  EXPECT(parse::parseExpr("l_quantity is not null or not (l_tax <> 0.0)", row)->toString() == "or(not(is_null(l_quantity)),not(neq(l_tax,0.000000)))");
+  EXPECT(parse::parseExpr("1 + 2 * 3", row)->toString() == "7"); // constant folding (ExprCompiler.cpp:302-335)
+  EXPECT_THROW(parse::parseExpr("no_such_column > 1", row), VeloxUserError);
+  EXPECT_THROW(parse::parseExpr("l_quantity > l_orderkey", row), VeloxUserError); // no implicit casts between columns
+  EXPECT_THROW(parse::parseExpr("l_quantity >", row), VeloxUserError);
+  EXPECT_THROW(parse::parseExpr("'1994-13-01'::DATE", row), VeloxUserError);
+
+  section("lowering: common sub-expressions once, program shape");
+  {
+    auto dp = parse::parseExpr("l_extendedprice * (1.0 - l_discount)", row);
+    auto ch = parse::parseExpr("l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax)", row);
+    auto lp = lowerExpressions(parse::parseExpr("l_shipdate <= '1998-09-02'::DATE", row), {dp, ch});
+    int muls = 0, subs = 0;
+    for (auto& op : lp.ops) { muls += op.opcode == VGPU_OP_MUL; subs += op.opcode == VGPU_OP_SUB; }
+    EXPECT(subs == 1 && muls == 2); // disc_price is shared between the two outputs
+    EXPECT(lp.columns.size() == 4 && lp.columns[0] == "l_shipdate");
+    EXPECT(lp.filter.kind == VGPU_OPND_SLOT && lp.filter.type == VGPU_BOOLEAN);
+    EXPECT(lp.outputs.size() == 2 && lp.outputs[0].kind == VGPU_OPND_SLOT && lp.outputs[1].kind == VGPU_OPND_SLOT);
+    auto q6 = lowerExpressions(parse::parseExpr(kQ6Filter, row), {parse::parseExpr("l_extendedprice * l_discount", row)});
+    int ands = 0, betweens = 0;
+    for (auto& op : q6.ops) { ands += op.opcode == VGPU_OP_AND; betweens += op.opcode == VGPU_OP_BETWEEN; }
+    EXPECT(ands == 3 && betweens == 1);
+    for (auto& op : q6.ops) if (op.opcode == VGPU_OP_BETWEEN) EXPECT(op.imm.d == 0.05 && op.imm2.d == 0.07);
+    auto id = lowerExpressions(nullptr, {parse::parseExpr("l_orderkey", row)});
+    EXPECT(id.ops.empty() && id.filter.kind == VGPU_OPND_NONE && id.outputs[0].kind == VGPU_OPND_COL);
+  }
+
+  section("PlanBuilder: node types of partial / final aggregation (Aggregate.h:35-41)");
+  {
+    auto plan = PlanBuilder().values({rv}).filter("l_quantity < 0.3").project({"l_returnflag", "l_quantity", "l_extendedprice * l_discount as rev"})
+                    .partialAggregation({"l_returnflag"}, {"sum(rev) as s", "avg(l_quantity) as a", "count(*) as c", "min(l_quantity)"}).planNode();
+    EXPECT(plan->outputType()->toString() == "ROW<l_returnflag:VARCHAR,s:DOUBLE,a:ROW<sum:DOUBLE,count:BIGINT>,c:BIGINT,a3:DOUBLE>");
+    auto fin = PlanBuilder().values({rv}).partialAggregation({"l_linestatus"}, {"avg(l_quantity) as a", "sum(l_orderkey) as s"}).finalAggregation().planNode();
+    EXPECT(fin->outputType()->toString() == "ROW<l_linestatus:VARCHAR,a:DOUBLE,s:BIGINT>");
+    EXPECT_THROW(PlanBuilder().values({rv}).singleAggregation({}, {"median(l_quantity)"}), VeloxUserError);
+    EXPECT_THROW(PlanBuilder().values({rv}).singleAggregation({}, {"sum(l_returnflag)"}), VeloxUserError);
+    EXPECT_THROW(PlanBuilder().values({rv}).filter("l_quantity + 1.0"), VeloxUserError);
+  }
+
+  section("registration: translators in order, custom node, no silent fallback (Operator.h:256-297,507)");
+  {
+    exec::Operator::unregisterAllOperators();
+    auto plan = PlanBuilder().values({rv, rv}).addNode([](std::string id, PlanNodePtr src) { return std::make_shared<CustomNode>(id, src); }).planNode();
+    EXPECT_THROW(exec::runPlan(plan), VeloxRuntimeError); // nothing claims the node
+    exec::Operator::registerOperator(std::make_unique<CustomTranslator>());
+    auto out = exec::runPlan(plan);
+    EXPECT(out.size() == 2 && out[0]->size() == 1000 && PassThrough::batches == 2);
+    auto filterPlan = PlanBuilder().values({rv}).filter("l_quantity < 0.3").planNode();
+    EXPECT_THROW(exec::runPlan(filterPlan), VeloxRuntimeError); // FilterNode has no operator until the GPU ones are registered
+    exec::Operator::unregisterAllOperators();
+  }
+
+  section("DecodedVector: nested dictionaries and extra nulls (DecodedVector.cpp:135-187)");
+  {
+    auto base = makeFlatVector<int64_t>(BIGINT(), {10, 20, 30, 40});
+    base->setNull(3, true);
+    Nulls extra(1, ~0ull);
+    bits::setBit(extra.data(), 1, false);
+    auto inner = wrapInDictionary({3, 2, 1, 0}, base);
+    auto outer = wrapInDictionary({0, 1, 2, 3, 3}, inner, extra);
+    auto d = gpu::decode(outer);
+    EXPECT((d.indices == std::vector<int32_t>{3, 2, 1, 0, 0}) && d.base == base.get());
+    EXPECT(!bits::isBitSet(d.nulls.data(), 1) && bits::isBitSet(d.nulls.data(), 0));
+    auto c = std::make_shared<ConstantVector>(makeFlatVector<double>(DOUBLE(), {2.5}), 7);
+    auto dc = gpu::decode(c);
+    EXPECT(dc.constant && !dc.constantNull && dc.size == 7);
+  }
+}
+
+// =========================================================================================================
+// gpu: operators against the oracle
+// =========================================================================================================
+static std::string typeSuffix(const TypePtr& t) {
+  switch (t->kind()) { case TypeKind::BOOLEAN: return "b"; case TypeKind::INTEGER: return "i32"; case TypeKind::BIGINT: return "i64"; case TypeKind::DOUBLE: return "f64"; default: throw VeloxRuntimeError("oracle type"); }
+}
+// typed expression -> the s-expression text oracle/velox_cpu.cpp parses
+static std::string toSexpr(const TypedExprPtr& e, const std::vector<std::string>& cols) {
+  char buf[64];
+  if (e->kind() == ITypedExpr::Kind::kFieldAccess) {
+    const auto& n = static_cast<const FieldAccessTypedExpr*>(e.get())->name();
+    for (size_t i = 0; i < cols.size(); ++i) if (cols[i] == n) return "c" + std::to_string(i) + ":" + typeSuffix(e->type());
+    throw VeloxRuntimeError("oracle column " + n);
+  }
+  if (e->kind() == ITypedExpr::Kind::kConstant) {
+    auto c = static_cast<const ConstantTypedExpr*>(e.get());
+    if (c->isNull()) return "null:" + typeSuffix(e->type());
+    if (e->type()->isFloating()) { snprintf(buf, sizeof buf, "%.17g", c->doubleValue()); return std::string(buf) + ":f64"; }
+    return std::to_string(c->intValue()) + ":" + typeSuffix(e->type());
+  }
+  std::string s = "(" + static_cast<const CallTypedExpr*>(e.get())->name();
+  for (auto& a : e->inputs()) s += " " + toSexpr(a, cols);
+  return s + ")";
+}
+
+struct OracleResult { std::map<std::vector<int64_t>, std::vector<std::pair<int64_t, int64_t>>> groups; }; // key values -> (value bits, non-null count)
+static OracleResult runOracle(const Lineitem& t, const char* filter, const std::vector<std::string>& outputs, const std::vector<int32_t>& keyOutputs,
+                              const std::vector<vcpu_acc>& accs, const RowTypePtr& row) {
+  const std::vector<std::string> names = {"l_orderkey", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate", "l_returnflag", "l_linestatus"};
+  // the oracle sees VARCHAR keys as their int32 ids, like the device does
+  auto orow = ROW(names, {BIGINT(), DOUBLE(), DOUBLE(), DOUBLE(), DOUBLE(), INTEGER(), INTEGER(), INTEGER()});
+  (void)row;
+  vcpu_column cols[8] = {{4, 0, t.orderkey.data(), nullptr}, {6, 0, t.quantity.data(), nullptr}, {6, 0, t.extendedprice.data(), nullptr},
+                         {6, 0, t.discount.data(), nullptr}, {6, 0, t.tax.data(), nullptr}, {3, 0, t.shipdate.data(), nullptr},
+                         {3, 0, t.flag.data(), nullptr}, {3, 0, t.status.data(), nullptr}};
+  std::string f = filter ? toSexpr(parse::parseExpr(filter, orow), names) : "";
+  std::vector<std::string> outs;
+  for (auto& o : outputs) outs.push_back(toSexpr(parse::parseExpr(o, orow), names));
+  std::vector<const char*> outp;
+  for (auto& o : outs) outp.push_back(o.c_str());
+  const int64_t cap = (int64_t)t.orderkey.size() + 16;
+  const int words = 2 * (int)keyOutputs.size() + 2 * (int)accs.size();
+  std::vector<int64_t> buf((size_t)cap * words);
+  double secs = 0;
+  const int64_t n = vcpu_run(f.c_str(), outp.data(), (int32_t)outp.size(), cols, 8, (int64_t)t.orderkey.size(), keyOutputs.data(), (int32_t)keyOutputs.size(),
+                             accs.data(), (int32_t)accs.size(), 0, 2, 4096, buf.data(), cap, &secs);
+  if (n < 0) throw VeloxRuntimeError(std::string("oracle: ") + vcpu_error());
+  OracleResult r;
+  const int nk = (int)keyOutputs.size();
+  for (int64_t g = 0; g < n; ++g) {
+    const int64_t* w = buf.data() + g * words;
+    std::vector<int64_t> key(w, w + nk);
+    std::vector<std::pair<int64_t, int64_t>> vals;
+    for (size_t a = 0; a < accs.size(); ++a) vals.push_back({w[2 * nk + 2 * a], w[2 * nk + 2 * a + 1]});
+    r.groups[key] = vals;
+  }
+  return r;
+}
+static double bitsToDouble(int64_t b) { double d; memcpy(&d, &b, 8); return d; }
+
+static void gpuTests() {
+  gpu::registerGpuOperators();
+  auto t = makeLineitem(300007, 7);
+  auto in = batches(t, 65536);
+  const auto& row = in[0]->rowType();
+
+  section("FilterProject: selection, projection values, dictionary-wrapped output (FilterProject.cpp:125-174)");
+  {
+    auto plan = PlanBuilder().values(in).filter(kQ6Filter).project({"l_orderkey", "l_extendedprice * l_discount as rev", "l_shipdate"}).planNode();
+    auto out = exec::runPlan(plan);
+    size_t total = 0, pos = 0, b = 0;
+    bool same = true, wrapped = true;
+    for (size_t i = 0; i < t.orderkey.size(); ++i) {
+      const bool pass = t.shipdate[i] >= 8766 && t.shipdate[i] < 9131 && t.discount[i] >= 0.05 && t.discount[i] <= 0.07 && t.quantity[i] < 0.24;
+      if (!pass) continue;
+      while (b < out.size() && pos == out[b]->size()) { ++b; pos = 0; }
+      if (b == out.size()) { same = false; break; }
+      same = same && at<int64_t>(out[b]->childAt(0), pos) == t.orderkey[i] && at<int32_t>(out[b]->childAt(2), pos) == t.shipdate[i];
+      const double rev = at<double>(out[b]->childAt(1), pos), want = t.extendedprice[i] * t.discount[i];
+      same = same && memcmp(&rev, &want, 8) == 0; // IEEE multiply: bit-exact
+      wrapped = wrapped && out[b]->childAt(0)->encoding() == VectorEncoding::DICTIONARY;
+      ++pos; ++total;
+    }
+    for (auto& o : out) total -= o->size();
+    EXPECT(same && total == 0 && wrapped && !out.empty());
+    // all rows pass -> no wrapping (Operator.cpp:195-228)
+    auto all = exec::runPlan(PlanBuilder().values({in[0]}).filter("l_quantity > 0.0").planNode());
+    EXPECT(all.size() == 1 && all[0]->size() == in[0]->size() && all[0]->childAt(0)->encoding() == VectorEncoding::FLAT);
+    // no row passes -> no output vector at all (Driver.cpp:550-556)
+    EXPECT(exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").planNode()).empty());
+  }
+
+  section("Q6: filter -> project -> partial -> final sum (TpchQueryBuilder.cpp:461-486)");
+  {
+    auto plan = PlanBuilder().values(in).filter(kQ6Filter).project({"l_extendedprice * l_discount as rev"})
+                    .partialAggregation({}, {"sum(rev) as revenue", "count(*) as n"}).finalAggregation().planNode();
+    auto driver = exec::createDriver(plan);
+    EXPECT(driver->operators().size() == 3 && driver->operators()[1]->operatorType() == "GpuFilterProjectAggregation"); // adapter fused the pair
+    auto out = driver->run();
+    auto want = runOracle(t, kQ6Filter, {"l_extendedprice * l_discount"}, {}, {{0, 0}, {2, -1}}, row);
+    EXPECT(out.size() == 1 && out[0]->size() == 1 && want.groups.size() == 1);
+    const auto& w = want.groups.begin()->second;
+    EXPECT(at<int64_t>(out[0]->childAt(1), 0) == w[1].first);
+    EXPECT(close(at<double>(out[0]->childAt(0), 0), bitsToDouble(w[0].first)));
+  }
+
+  section("Q1: VARCHAR keys, sum / avg / count, fused and unfused (TpchQueryBuilder.cpp:189-244)");
+  for (int fused = 1; fused >= 0; --fused) {
+    if (!fused) { exec::Operator::unregisterAllOperators(); gpu::registerGpuOperators(); exec::DriverFactory::adapters().clear(); }
+    auto plan = PlanBuilder().values(in).filter("l_shipdate <= '1998-09-02'::DATE")
+                    .project({"l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_extendedprice * (1.0 - l_discount) as disc_price",
+                              "l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax) as charge", "l_discount"})
+                    .partialAggregation({"l_returnflag", "l_linestatus"}, {"sum(l_quantity)", "sum(l_extendedprice)", "sum(disc_price)", "sum(charge)",
+                                                                             "avg(l_quantity)", "avg(l_extendedprice)", "avg(l_discount)", "count(*)"})
+                    .finalAggregation().planNode();
+    auto driver = exec::createDriver(plan);
+    EXPECT(driver->operators().size() == (fused ? 3u : 4u));
+    auto out = driver->run();
+    auto want = runOracle(t, "l_shipdate <= '1998-09-02'::DATE",
+                          {"l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_extendedprice * (1.0 - l_discount)",
+                           "l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax)", "l_discount"},
+                          {0, 1}, {{0, 2}, {0, 3}, {0, 4}, {0, 5}, {0, 2}, {2, 2}, {0, 3}, {2, 3}, {0, 6}, {2, 6}, {2, -1}}, row);
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      const std::string fl = at<std::string>(o->childAt(0), g), st = at<std::string>(o->childAt(1), g);
+      std::vector<int64_t> key = {fl == "A" ? 0 : fl == "N" ? 1 : 2, st == "F" ? 0 : 1};
+      auto it = want.groups.find(key);
+      if (it == want.groups.end()) { ok = false; continue; }
+      const auto& w = it->second;
+      for (int s = 0; s < 4; ++s) ok = ok && close(at<double>(o->childAt(2 + s), g), bitsToDouble(w[s].first));
+      for (int a = 0; a < 3; ++a) ok = ok && close(at<double>(o->childAt(6 + a), g), bitsToDouble(w[4 + 2 * a].first) / (double)w[5 + 2 * a].first);
+      ok = ok && at<int64_t>(o->childAt(9), g) == w[10].first;
+    }
+    EXPECT(ok && groups == want.groups.size() && groups == 6);
+  }
+  exec::Operator::unregisterAllOperators();
+  gpu::registerGpuOperators();
+
+  section("high cardinality: GROUP BY l_orderkey, single vs partial+final, output batches (HashAggregation.cpp:388-464)");
+  {
+    std::map<int64_t, std::pair<double, int64_t>> want;
+    for (size_t i = 0; i < t.orderkey.size(); ++i) { auto& w = want[t.orderkey[i]]; w.first += t.extendedprice[i]; ++w.second; }
+    for (int twoStage = 0; twoStage < 2; ++twoStage) {
+      PlanBuilder b;
+      b.values(in);
+      if (twoStage) b.partialAggregation({"l_orderkey"}, {"sum(l_extendedprice) as s", "count(*) as c"}).finalAggregation();
+      else b.singleAggregation({"l_orderkey"}, {"sum(l_extendedprice) as s", "count(*) as c"});
+      auto out = exec::runPlan(b.planNode());
+      size_t groups = 0;
+      bool ok = true, batchOk = true;
+      std::set<int64_t> seen;
+      for (auto& o : out) {
+        batchOk = batchOk && o->size() <= 1024; // preferredOutputBatchRows
+        for (size_t g = 0; g < o->size(); ++g, ++groups) {
+          const int64_t k = at<int64_t>(o->childAt(0), g);
+          auto it = want.find(k);
+          ok = ok && it != want.end() && seen.insert(k).second && close(at<double>(o->childAt(1), g), it->second.first) && at<int64_t>(o->childAt(2), g) == it->second.second;
+        }
+      }
+      EXPECT(ok && batchOk && groups == want.size());
+    }
+  }
+
+  section("dictionary VARCHAR keys with nulls: min / max / count, NULL is a key value (GroupingSet.cpp:240-307)");
+  {
+    const size_t n = t.orderkey.size();
+    Nulls modeNulls(bits::nwords(n), ~0ull), instrNulls(bits::nwords(n), ~0ull);
+    auto qty = makeFlatVector<double>(DOUBLE(), t.quantity);
+    for (size_t i = 0; i < n; ++i) {
+      if (i % 11 == 0) bits::setBit(modeNulls.data(), i, false);
+      if (i % 13 == 0) bits::setBit(instrNulls.data(), i, false);
+      if (i % 7 == 0) qty->setNull(i, true);
+    }
+    std::vector<std::string> mb(kModes, kModes + 7), ib(kInstruct, kInstruct + 4);
+    auto rv = makeRowVector({"l_shipmode", "l_shipinstruct", "l_extendedprice", "l_shipdate", "l_quantity"},
+                            {wrapInDictionary(t.mode, makeFlatVector<std::string>(VARCHAR(), mb), modeNulls),
+                             wrapInDictionary(t.instruct, makeFlatVector<std::string>(VARCHAR(), ib), instrNulls),
+                             makeFlatVector<double>(DOUBLE(), t.extendedprice), makeFlatVector<int32_t>(DATE(), t.shipdate), qty});
+    struct W { double mn = 1e300, mx = -1e300; int32_t dmn = INT32_MAX, dmx = INT32_MIN; int64_t cq = 0, c = 0; };
+    std::map<std::pair<std::string, std::string>, W> want;
+    for (size_t i = 0; i < n; ++i) {
+      auto& w = want[{i % 11 == 0 ? "<null>" : kModes[t.mode[i]], i % 13 == 0 ? "<null>" : kInstruct[t.instruct[i]]}];
+      w.mn = std::min(w.mn, t.extendedprice[i]); w.mx = std::max(w.mx, t.extendedprice[i]);
+      w.dmn = std::min(w.dmn, t.shipdate[i]); w.dmx = std::max(w.dmx, t.shipdate[i]);
+      w.cq += i % 7 != 0; ++w.c;
+    }
+    for (int ignoreNullKeys = 0; ignoreNullKeys < 2; ++ignoreNullKeys) {
+      auto plan = PlanBuilder().values({rv}).aggregation({"l_shipmode", "l_shipinstruct"},
+                      {"min(l_extendedprice)", "max(l_extendedprice)", "min(l_shipdate)", "max(l_shipdate)", "count(l_quantity)", "count(*)"},
+                      AggregationNode::Step::kSingle, ignoreNullKeys != 0).planNode();
+      auto out = exec::runPlan(plan);
+      size_t groups = 0;
+      bool ok = true;
+      for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+        const std::string m = isNullAt(o->childAt(0), g) ? "<null>" : at<std::string>(o->childAt(0), g);
+        const std::string s = isNullAt(o->childAt(1), g) ? "<null>" : at<std::string>(o->childAt(1), g);
+        auto it = want.find({m, s});
+        if (it == want.end()) { ok = false; continue; }
+        const W& w = it->second;
+        ok = ok && at<double>(o->childAt(2), g) == w.mn && at<double>(o->childAt(3), g) == w.mx && at<int32_t>(o->childAt(4), g) == w.dmn &&
+             at<int32_t>(o->childAt(5), g) == w.dmx && at<int64_t>(o->childAt(6), g) == w.cq && at<int64_t>(o->childAt(7), g) == w.c;
+        if (ignoreNullKeys) ok = ok && m != "<null>" && s != "<null>";
+      }
+      EXPECT(ok && groups == (ignoreNullKeys ? 28u : 40u));
+    }
+  }
+
+  section("edge cases: empty input, all-null input, integer overflow (SumTest.cpp:509-538,610-620)");
+  {
+    auto none = exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").singleAggregation({"l_orderkey"}, {"sum(l_quantity)"}).planNode());
+    EXPECT(none.empty()); // grouped aggregation over no rows: no output
+    auto global = exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").singleAggregation({}, {"sum(l_quantity)", "count(*)", "avg(l_tax)", "max(l_shipdate)"}).planNode());
+    EXPECT(global.size() == 1 && global[0]->size() == 1 && isNullAt(global[0]->childAt(0), 0) && at<int64_t>(global[0]->childAt(1), 0) == 0 &&
+           isNullAt(global[0]->childAt(2), 0) && isNullAt(global[0]->childAt(3), 0)); // global: one row, NULL sums, zero count
+    auto big = makeFlatVector<int64_t>(BIGINT(), {INT64_MAX - 1, 1, 1});
+    auto k = makeFlatVector<int32_t>(INTEGER(), {1, 1, 2});
+    auto rv = makeRowVector({"k", "v"}, {k, big});
+    EXPECT_THROW(exec::runPlan(PlanBuilder().values({rv}).singleAggregation({}, {"sum(v)"}).planNode()), VeloxUserError);
+    auto fine = exec::runPlan(PlanBuilder().values({rv}).singleAggregation({"k"}, {"sum(v)", "min(v)"}).planNode());
+    EXPECT(fine.size() == 1 && fine[0]->size() == 2);
+    EXPECT_THROW(exec::runPlan(PlanBuilder().values({rv}).project({"k", "v * 4 as w"}).singleAggregation({"k"}, {"max(w)"}).planNode()), VeloxUserError); // checked multiply
+    auto nulls = makeFlatVector<double>(DOUBLE(), {1.0, 2.0, 3.0});
+    for (int i = 0; i < 3; ++i) nulls->setNull(i, true);
+    auto an = exec::runPlan(PlanBuilder().values({makeRowVector({"k", "v"}, {k, nulls})}).partialAggregation({"k"}, {"sum(v)", "avg(v)", "count(v)"}).finalAggregation().planNode());
+    bool ok = an.size() == 1 && an[0]->size() == 2;
+    for (size_t g = 0; ok && g < 2; ++g) ok = isNullAt(an[0]->childAt(1), g) && isNullAt(an[0]->childAt(2), g) && at<int64_t>(an[0]->childAt(3), g) == 0;
+    EXPECT(ok);
+  }
+}
+
+int main(int argc, char** argv) {
+  const std::string mode = argc > 1 ? argv[1] : "cpu";
+  try {
+    if (mode == "cpu") cpuTests();
+    else if (mode == "gpu") gpuTests();
+    else { printf("usage: host_tests cpu|gpu\n"); return 2; }
+  } catch (const std::exception& e) {
+    printf("  FAILED: uncaught exception: %s\n", e.what());
+    ++g_failed;
+  }
+  printf("%s: %d checks, %d failed\n", mode.c_str(), g_checks, g_failed);
+  return g_failed ? 1 : 0;
+}

@@ -1,0 +1,433 @@
+// GpuHashAggregation: exec::HashAggregation + GroupingSet on the GPU (velox/exec/HashAggregation.cpp:97-472,
+// velox/exec/GroupingSet.cpp:177-307,513-712).  Per batch: bind the input columns (VARCHAR keys become int32
+// value ids, VectorHasher::makeValueIds analogue, velox/exec/VectorHasher.cpp:110-143), one
+// vgpu_agg_add_input call (filter + projections + find-or-insert + accumulate in one kernel).  After
+// noMoreInput: vgpu_agg_extract, then output batches of preferredOutputBatchRows groups.
+// Not restated: partial-aggregation flushing / abandoning (HashAggregation.cpp:229-233,326-386) — partial
+// output is produced once, at end of input — spilling, sorted / distinct / masked aggregates.
+#include <cmath>
+#include <unordered_map>
+
+#include "GpuDevice.h"
+
+namespace vb200 {
+namespace gpu {
+using namespace core;
+using Step = AggregationNode::Step;
+
+namespace {
+struct KeyInfo {
+  std::string name;
+  TypePtr type;
+  bool varchar = false;
+  int64_t lo = 0, hi = 0;
+  int bits = 0;
+  std::vector<std::string> strings;                 // id -> string
+  std::unordered_map<std::string, int32_t> idOf;
+};
+struct AggInfo {
+  std::string fn;
+  TypePtr rawType, outType;
+  int acc0 = -1, acc1 = -1;
+};
+TypedExprPtr castTo(const TypedExprPtr& e, const TypePtr& t) { return e->type()->equals(*t) ? e : std::make_shared<CastTypedExpr>(t, e); }
+int64_t typeLo(TypeKind k) { return k == TypeKind::TINYINT ? -128 : k == TypeKind::SMALLINT ? -32768 : -2147483648ll; }
+int64_t typeHi(TypeKind k) { return k == TypeKind::TINYINT ? 127 : k == TypeKind::SMALLINT ? 32767 : 2147483647ll; }
+} // namespace
+
+struct GpuHashAggregation::Impl {
+  std::shared_ptr<const AggregationNode> node;
+  RowTypePtr inputType;       // what addInput receives
+  FilterProjectExprs fused;
+  bool hasFused = false;
+  exec::DriverCtx* ctx = nullptr;
+
+  std::vector<KeyInfo> keys;
+  std::vector<AggInfo> aggs;
+  std::vector<vgpu_acc_spec> accs;
+  std::vector<TypedExprPtr> outputs; // program outputs: keys, then accumulator inputs
+  LoweredProgram lowered;
+  vgpu_program_t program = nullptr;
+  vgpu_agg_t agg = nullptr;
+  void* stream = nullptr;
+  int mode = VGPU_AGG_GLOBAL;
+  bool sawInput = false;
+
+  std::vector<int64_t> rows; // extracted packed groups
+  int64_t nGroups = -1;
+  int64_t cursor = 0;
+  int rowWords() const { return 3 + 2 * (int)accs.size(); }
+  // ids per key in the device's numbering: [lo, hi] plus one id for NULL unless NULL keys are dropped
+  int64_t nullIds() const { return node->ignoreNullKeys() ? 0 : 1; }
+  int64_t cardOf(const KeyInfo& k) const { return k.hi - k.lo + 1 + nullIds(); }
+
+  // expression a name refers to on the operator's input (through the fused projections, if any)
+  TypedExprPtr exprOf(const std::string& name) const {
+    if (hasFused && !fused.names.empty()) {
+      for (size_t i = 0; i < fused.names.size(); ++i) if (fused.names[i] == name) return fused.projections[i];
+      throw VeloxUserError("Field not found: " + name);
+    }
+    const size_t dot = name.find('.');
+    if (dot != std::string::npos) { // child of a ROW-typed intermediate column (avg)
+      const int idx = inputType->getChildIdx(name.substr(0, dot));
+      auto row = std::dynamic_pointer_cast<const RowType>(inputType->childAt(idx));
+      return std::make_shared<FieldAccessTypedExpr>(row->childAt(row->getChildIdx(name.substr(dot + 1))), name);
+    }
+    return std::make_shared<FieldAccessTypedExpr>(inputType->childAt(inputType->getChildIdx(name)), name);
+  }
+  int addOutput(const TypedExprPtr& e) {
+    for (size_t i = keys.size(); i < outputs.size(); ++i) if (outputs[i]->toString() == e->toString() && outputs[i]->type()->equals(*e->type())) return (int)i;
+    outputs.push_back(e);
+    return (int)outputs.size() - 1;
+  }
+  int addAcc(int kind, int input) { accs.push_back(vgpu_acc_spec{kind, input}); return (int)accs.size() - 1; }
+
+  void planAccumulators() {
+    const bool raw = AggregationNode::isRawInput(node->step());
+    for (size_t i = 0; i < node->aggregates().size(); ++i) {
+      const auto& a = node->aggregates()[i];
+      AggInfo info;
+      info.fn = a.function;
+      info.rawType = a.rawInputType ? a.rawInputType : BIGINT();
+      info.outType = node->outputType()->childAt(keys.size() + i);
+      const bool hasColumn = !a.args.empty() && a.args[0]->kind() == ITypedExpr::Kind::kFieldAccess;
+      TypedExprPtr x = hasColumn ? exprOf(static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name()) : nullptr;
+      const std::string col = hasColumn ? static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name() : "";
+      if (a.function == "count") {
+        if (raw) info.acc0 = addAcc(VGPU_ACC_COUNT, hasColumn ? addOutput(x) : -1);
+        else info.acc0 = addAcc(VGPU_ACC_SUM_I64, addOutput(x)); // final count = sum of partial counts (CountAggregate.cpp:81-90)
+      } else if (a.function == "sum") {
+        const bool fp = raw ? x->type()->isFloating() : info.rawType->isFloating();
+        info.acc0 = addAcc(fp ? VGPU_ACC_SUM_F64 : VGPU_ACC_SUM_I64, addOutput(castTo(x, fp ? DOUBLE() : BIGINT())));
+      } else if (a.function == "avg") {
+        if (raw) {
+          const int in = addOutput(castTo(x, DOUBLE()));
+          info.acc0 = addAcc(VGPU_ACC_SUM_F64, in);
+          info.acc1 = addAcc(VGPU_ACC_COUNT, in);
+        } else { // intermediate ROW(sum DOUBLE, count BIGINT) (AverageAggregateBase.h:36-41)
+          info.acc0 = addAcc(VGPU_ACC_SUM_F64, addOutput(exprOf(col + ".sum")));
+          info.acc1 = addAcc(VGPU_ACC_SUM_I64, addOutput(exprOf(col + ".count")));
+        }
+      } else if (a.function == "min" || a.function == "max") {
+        VB_USER_CHECK(x->type()->kind() != TypeKind::VARCHAR && x->type()->kind() != TypeKind::BOOLEAN, a.function + " over " + x->type()->toString() + " is not supported on the GPU");
+        info.acc0 = addAcc(a.function == "min" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(x->type()->kind() == TypeKind::REAL ? castTo(x, DOUBLE()) : x));
+      } else {
+        throw VeloxUserError("Aggregate function not registered: " + a.function);
+      }
+      aggs.push_back(info);
+    }
+  }
+
+  // Decides the table mode and key packing once the first batch's VARCHAR dictionaries are known.
+  void create() {
+    mode = keys.empty() ? VGPU_AGG_GLOBAL : VGPU_AGG_HASH;
+    bool small = !keys.empty();
+    int64_t product = 1;
+    for (auto& k : keys) {
+      if (k.varchar) { k.lo = 0; k.hi = std::max<int64_t>(7, 2 * (int64_t)k.strings.size() - 1); }
+      else if (k.type->kind() == TypeKind::TINYINT) { k.lo = -128; k.hi = 127; }
+      else small = false;
+      product *= cardOf(k);
+      if (product > 4096) small = false;
+    }
+    if (small) mode = VGPU_AGG_ARRAY;
+    std::vector<vgpu_key_spec> specs(keys.size());
+    if (mode == VGPU_AGG_HASH) {
+      if (keys.size() == 1 && !keys[0].varchar) {
+        keys[0].bits = 64;
+        outputs[0] = castTo(outputs[0], BIGINT());
+      } else {
+        int total = 0;
+        for (auto& k : keys) {
+          if (k.varchar) { k.lo = 0; k.hi = (1 << 20) - 2; k.bits = 20; }
+          else {
+            VB_CHECK(k.type->kind() != TypeKind::BIGINT && k.type->isInteger(), "multi-key grouping on " + k.type->toString() + " needs key statistics (not supported yet)");
+            k.lo = typeLo(k.type->kind()); k.hi = typeHi(k.type->kind());
+            k.bits = k.type->kind() == TypeKind::TINYINT ? 9 : k.type->kind() == TypeKind::SMALLINT ? 17 : 33;
+          }
+          total += k.bits;
+        }
+        VB_CHECK(total <= 64, "grouping keys do not fit the 64-bit normalized key");
+      }
+    }
+    for (size_t i = 0; i < keys.size(); ++i) specs[i] = vgpu_key_spec{(int32_t)i, mode == VGPU_AGG_HASH ? keys[i].bits : 0, keys[i].lo, keys[i].hi};
+    lowered = lowerExpressions(hasFused ? fused.filter : nullptr, outputs);
+    const auto pdesc = lowered.desc();
+    check(vgpu_program_create(&pdesc, &program), "vgpu_program_create");
+    vgpu_agg_desc d{};
+    d.mode = mode; d.n_keys = (int32_t)keys.size(); d.keys = specs.data();
+    d.n_accs = (int32_t)accs.size(); d.accs = accs.data();
+    d.ignore_null_keys = node->ignoreNullKeys() ? 1 : 0;
+    check(vgpu_agg_create(&d, &agg), "vgpu_agg_create");
+  }
+
+  // ARRAY mode only: a VARCHAR key outgrew its id range.  Move the groups into a table with wider ranges.
+  void regrow() {
+    std::vector<int64_t> old = extractAll();
+    std::vector<int64_t> card(keys.size());
+    for (size_t i = 0; i < keys.size(); ++i) card[i] = cardOf(keys[i]);
+    vgpu_agg_destroy(agg); agg = nullptr;
+    vgpu_program_destroy(program); program = nullptr;
+    create();
+    VB_CHECK(mode == VGPU_AGG_ARRAY, "VARCHAR grouping keys outgrew the small-domain table (more than 4096 key combinations)");
+    const int rw = rowWords();
+    for (size_t g = 0; g * rw < old.size(); ++g) { // re-number the mixed-radix group ids
+      int64_t id = old[g * rw], fresh = 0, mul = 1;
+      for (size_t i = 0; i < keys.size(); ++i) { fresh += (id % card[i]) * mul; id /= card[i]; mul *= cardOf(keys[i]); }
+      old[g * rw] = fresh;
+    }
+    addEmpty();
+    if (!old.empty()) {
+      DeviceBatch b; b.stream = stream;
+      void* d = b.upload(old.data(), old.size() * 8);
+      check(vgpu_agg_merge_rows(agg, d, (int64_t)(old.size() / rw), stream), "vgpu_agg_merge_rows");
+      check(vgpu_stream_sync(stream), "vgpu_stream_sync");
+    }
+  }
+
+  void addEmpty() {
+    std::vector<vgpu_column> cols(std::max<size_t>(1, lowered.columns.size()));
+    for (size_t i = 0; i < lowered.columns.size(); ++i) cols[i].type = deviceType(exprOf(lowered.columns[i])->type());
+    check(vgpu_agg_add_input(agg, program, cols.data(), (int32_t)lowered.columns.size(), 0, nullptr, 0, stream), "vgpu_agg_add_input");
+  }
+
+  std::vector<int64_t> extractAll() {
+    int64_t n = 0;
+    check(vgpu_agg_num_groups(agg, stream, &n), "vgpu_agg_num_groups");
+    std::vector<int64_t> out((size_t)n * rowWords());
+    if (n == 0) return out;
+    void* d = nullptr;
+    check(vgpu_alloc(out.size() * 8, &d), "vgpu_alloc");
+    int64_t got = 0;
+    int rc = vgpu_agg_extract(agg, 0, n, d, &got, stream);
+    if (rc == VGPU_OK) rc = vgpu_d2h_async(out.data(), d, (size_t)got * rowWords() * 8, stream);
+    if (rc == VGPU_OK) rc = vgpu_stream_sync(stream);
+    vgpu_free(d);
+    check(rc, "vgpu_agg_extract");
+    out.resize((size_t)got * rowWords());
+    return out;
+  }
+
+  // VARCHAR key column -> ids of its base strings (new strings get the next id)
+  std::vector<int32_t> idsOf(KeyInfo& k, const VectorPtr& v) {
+    Decoded d = decode(v);
+    auto strs = static_cast<const FlatVector<std::string>*>(d.base);
+    std::vector<int32_t> ids(d.base->size());
+    for (size_t i = 0; i < ids.size(); ++i) {
+      if (d.base->mayHaveNulls() && !bits::isBitSet(d.base->nulls().data(), i)) { ids[i] = 0; continue; }
+      auto it = k.idOf.find(strs->valueAt(i));
+      if (it == k.idOf.end()) { it = k.idOf.emplace(strs->valueAt(i), (int32_t)k.strings.size()).first; k.strings.push_back(strs->valueAt(i)); }
+      ids[i] = it->second;
+    }
+    return ids;
+  }
+
+  VectorPtr columnByName(const RowVectorPtr& in, const std::string& name, std::vector<VectorPtr>& keepAlive) {
+    const size_t dot = name.find('.');
+    if (dot == std::string::npos) return in->childAt(inputType->getChildIdx(name));
+    auto parent = in->childAt(inputType->getChildIdx(name.substr(0, dot)));
+    auto row = std::dynamic_pointer_cast<RowVector>(parent);
+    VB_CHECK(row != nullptr, "intermediate avg column must be a flat ROW vector");
+    auto child = row->childAt(row->rowType()->getChildIdx(name.substr(dot + 1)));
+    if (!row->mayHaveNulls()) return child;
+    // a NULL row hides its fields: fold the row's nulls into a copy of the child
+    VB_CHECK(child->encoding() == VectorEncoding::FLAT, "intermediate avg fields must be flat");
+    VectorPtr copy;
+    if (child->type()->kind() == TypeKind::DOUBLE) copy = std::make_shared<FlatVector<double>>(*static_cast<FlatVector<double>*>(child.get()));
+    else copy = std::make_shared<FlatVector<int64_t>>(*static_cast<FlatVector<int64_t>*>(child.get()));
+    auto& nl = copy->mutableNulls();
+    for (size_t w = 0; w < nl.size(); ++w) nl[w] &= row->nulls()[w];
+    keepAlive.push_back(copy);
+    return copy;
+  }
+
+  void addBatch(const RowVectorPtr& in) {
+    std::vector<std::vector<int32_t>> keyIds(keys.size());
+    std::vector<VectorPtr> keyVecs(keys.size());
+    bool grew = false;
+    for (size_t i = 0; i < keys.size(); ++i) {
+      if (!keys[i].varchar) continue;
+      auto fa = static_cast<const FieldAccessTypedExpr*>(outputs[i].get());
+      keyVecs[i] = in->childAt(inputType->getChildIdx(fa->name()));
+      keyIds[i] = idsOf(keys[i], keyVecs[i]);
+      if (agg && (int64_t)keys[i].strings.size() - 1 > keys[i].hi) grew = true;
+    }
+    if (!agg) { create(); }
+    else if (grew) {
+      if (mode == VGPU_AGG_ARRAY) regrow();
+      else throw VeloxRuntimeError("more than 2^20 distinct strings in a grouping key");
+    }
+    DeviceBatch batch;
+    batch.stream = stream;
+    std::vector<VectorPtr> keepAlive;
+    for (auto& name : lowered.columns) {
+      int varcharKey = -1;
+      for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name() == name) varcharKey = (int)i;
+      if (varcharKey >= 0) bindColumn(batch, keyVecs[varcharKey], &keyIds[varcharKey]);
+      else bindColumn(batch, columnByName(in, name, keepAlive));
+    }
+    check(vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream), "vgpu_agg_add_input");
+    // data errors (sum overflow, checked arithmetic in fused projections) surface here, like the exception
+    // thrown out of HashAggregation::addInput; this also makes the batch's device copies safe to free
+    check(vgpu_check_errors(stream), "HashAggregation");
+    sawInput = true;
+  }
+};
+
+GpuHashAggregation::GpuHashAggregation(exec::DriverCtx* ctx, int32_t id, std::shared_ptr<const AggregationNode> node,
+                                       const FilterProjectExprs* fused, RowTypePtr fusedInputType)
+    : Operator(ctx, node->outputType(), id, node->id(), fused ? "GpuFilterProjectAggregation" : "GpuHashAggregation"), impl_(new Impl) {
+  auto& m = *impl_;
+  m.node = node;
+  m.ctx = ctx;
+  m.hasFused = fused != nullptr;
+  if (fused) { m.fused = *fused; VB_CHECK(AggregationNode::isRawInput(node->step()), "only raw-input aggregations can absorb a FilterProject"); }
+  m.inputType = fused ? fusedInputType : node->sources()[0]->outputType();
+  check(vgpu_init(ctx->queryConfig.device), "vgpu_init");
+  check(vgpu_stream_create(&m.stream), "vgpu_stream_create");
+  for (auto& name : node->groupingKeys()) {
+    KeyInfo k;
+    k.name = name;
+    auto e = m.exprOf(name);
+    k.type = e->type();
+    k.varchar = k.type->kind() == TypeKind::VARCHAR;
+    VB_USER_CHECK(!k.varchar || e->kind() == ITypedExpr::Kind::kFieldAccess, "VARCHAR grouping keys must be plain columns");
+    VB_USER_CHECK(k.varchar || k.type->isInteger(), "grouping on " + k.type->toString() + " is not supported on the GPU");
+    m.keys.push_back(std::move(k));
+    m.outputs.push_back(e);
+  }
+  m.planAccumulators();
+}
+
+GpuHashAggregation::~GpuHashAggregation() { close(); }
+
+void GpuHashAggregation::close() {
+  auto& m = *impl_;
+  if (m.agg) { vgpu_agg_destroy(m.agg); m.agg = nullptr; }
+  if (m.program) { vgpu_program_destroy(m.program); m.program = nullptr; }
+  if (m.stream) { vgpu_stream_destroy(m.stream); m.stream = nullptr; }
+  Operator::close();
+}
+
+void GpuHashAggregation::addInput(RowVectorPtr input) {
+  VB_CHECK(!noMoreInput_, "addInput after noMoreInput");
+  impl_->addBatch(input);
+}
+
+void GpuHashAggregation::noMoreInput() {
+  Operator::noMoreInput();
+  auto& m = *impl_;
+  if (!m.sawInput) {
+    if (!m.keys.empty()) { finished_ = true; return; } // grouped aggregation over no input: no rows (SumTest.cpp:509-516)
+    m.create();                                        // global: exactly one row, even on empty input
+    m.addEmpty();
+  }
+  m.rows = m.extractAll();
+  m.nGroups = (int64_t)(m.rows.size() / m.rowWords());
+  if (m.nGroups == 0) finished_ = true;
+}
+
+namespace {
+template <typename T>
+std::shared_ptr<FlatVector<T>> flatOf(const TypePtr& t, size_t n) { return std::make_shared<FlatVector<T>>(t, n); }
+double asDouble(int64_t bitsValue) { double d; memcpy(&d, &bitsValue, 8); return d; }
+} // namespace
+
+RowVectorPtr GpuHashAggregation::getOutput() {
+  auto& m = *impl_;
+  if (!noMoreInput_ || finished_ || m.nGroups < 0) return nullptr;
+  const int64_t n = std::min<int64_t>(m.ctx->queryConfig.preferredOutputBatchRows, m.nGroups - m.cursor);
+  const int rw = m.rowWords(), na = (int)m.accs.size();
+  const int64_t* base = m.rows.data() + m.cursor * rw;
+  std::vector<VectorPtr> children;
+  // ---- grouping keys (normalized key -> values; NULL is a key value of its own, GroupingSet.cpp:240-307)
+  std::vector<std::vector<int64_t>> kv(m.keys.size(), std::vector<int64_t>((size_t)n));
+  std::vector<std::vector<bool>> kn(m.keys.size(), std::vector<bool>((size_t)n, false));
+  const int64_t nullIds = m.nullIds();
+  for (int64_t g = 0; g < n; ++g) {
+    const int64_t key = base[g * rw], flags = base[g * rw + 1];
+    if (m.mode == VGPU_AGG_ARRAY) {
+      int64_t id = key;
+      for (size_t i = 0; i < m.keys.size(); ++i) {
+        const int64_t card = m.cardOf(m.keys[i]), d = id % card;
+        id /= card;
+        kn[i][g] = nullIds && d == 0;
+        kv[i][g] = d - nullIds + m.keys[i].lo;
+      }
+    } else if (m.mode == VGPU_AGG_HASH) {
+      int shift = 0;
+      for (size_t i = 0; i < m.keys.size(); ++i) {
+        if (m.keys[i].bits == 64) { kn[i][g] = flags & 1; kv[i][g] = key; continue; }
+        const int64_t d = (int64_t)(((uint64_t)key >> shift) & ((1ull << m.keys[i].bits) - 1));
+        shift += m.keys[i].bits;
+        kn[i][g] = nullIds && d == 0;
+        kv[i][g] = d - nullIds + m.keys[i].lo;
+      }
+    }
+  }
+  for (size_t i = 0; i < m.keys.size(); ++i) {
+    const auto& k = m.keys[i];
+    VectorPtr v;
+    if (k.varchar) { auto f = flatOf<std::string>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) if (!kn[i][g]) { VB_CHECK(kv[i][g] >= 0 && (size_t)kv[i][g] < k.strings.size(), "group key id outside the VARCHAR dictionary"); f->set(g, k.strings[(size_t)kv[i][g]]); } v = f; }
+    else if (k.type->kind() == TypeKind::BIGINT) { auto f = flatOf<int64_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, kv[i][g]); v = f; }
+    else if (k.type->kind() == TypeKind::INTEGER) { auto f = flatOf<int32_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int32_t)kv[i][g]); v = f; }
+    else if (k.type->kind() == TypeKind::SMALLINT) { auto f = flatOf<int16_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int16_t)kv[i][g]); v = f; }
+    else { auto f = flatOf<int8_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int8_t)kv[i][g]); v = f; }
+    for (int64_t g = 0; g < n; ++g) if (kn[i][g]) v->setNull(g, true);
+    children.push_back(v);
+  }
+  // ---- aggregates: accumulators (partial / intermediate steps) or final values (Aggregate.h:35-41)
+  const bool partialOut = AggregationNode::isPartialOutput(m.node->step());
+  for (auto& a : m.aggs) {
+    auto value = [&](int64_t g, int acc) { return base[g * rw + 3 + acc]; };
+    auto nonNull = [&](int64_t g, int acc) { return base[g * rw + 3 + na + acc]; };
+    VectorPtr v;
+    if (a.fn == "count") {
+      auto f = flatOf<int64_t>(BIGINT(), (size_t)n);
+      for (int64_t g = 0; g < n; ++g) f->set(g, value(g, a.acc0)); // never NULL (CountAggregate.cpp:37-44)
+      v = f;
+    } else if (a.fn == "avg") {
+      if (partialOut) {
+        auto s = flatOf<double>(DOUBLE(), (size_t)n);
+        auto c = flatOf<int64_t>(BIGINT(), (size_t)n);
+        for (int64_t g = 0; g < n; ++g) { s->set(g, asDouble(value(g, a.acc0))); c->set(g, value(g, a.acc1)); }
+        auto row = std::make_shared<RowVector>(std::dynamic_pointer_cast<const RowType>(a.outType), (size_t)n, std::vector<VectorPtr>{s, c});
+        for (int64_t g = 0; g < n; ++g) if (value(g, a.acc1) == 0) row->setNull(g, true);
+        v = row;
+      } else {
+        const bool real = a.outType->kind() == TypeKind::REAL;
+        auto fd = real ? nullptr : flatOf<double>(a.outType, (size_t)n);
+        auto ff = real ? flatOf<float>(a.outType, (size_t)n) : nullptr;
+        for (int64_t g = 0; g < n; ++g) {
+          const int64_t cnt = value(g, a.acc1);
+          const double avg = cnt ? asDouble(value(g, a.acc0)) / (double)cnt : 0.0; // AverageAggregateBase.h:110
+          if (real) ff->set(g, (float)avg); else fd->set(g, avg);
+        }
+        v = real ? VectorPtr(ff) : VectorPtr(fd);
+        for (int64_t g = 0; g < n; ++g) if (value(g, a.acc1) == 0) v->setNull(g, true);
+      }
+    } else { // sum / min / max: NULL until a non-null input arrived (Aggregate.h:305-337)
+      const int kind = m.accs[a.acc0].kind;
+      const auto outKind = a.outType->kind();
+      const bool accIsDouble = kind == VGPU_ACC_SUM_F64 || ((kind == VGPU_ACC_MIN || kind == VGPU_ACC_MAX) && m.outputs[m.accs[a.acc0].input]->type()->isFloating());
+      switch (outKind) {
+        case TypeKind::DOUBLE: { auto f = flatOf<double>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, asDouble(value(g, a.acc0))); v = f; break; }
+        case TypeKind::REAL: { auto f = flatOf<float>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (float)asDouble(value(g, a.acc0))); v = f; break; }
+        case TypeKind::BIGINT: { auto f = flatOf<int64_t>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, value(g, a.acc0)); v = f; break; }
+        case TypeKind::INTEGER: { auto f = flatOf<int32_t>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int32_t)value(g, a.acc0)); v = f; break; }
+        case TypeKind::SMALLINT: { auto f = flatOf<int16_t>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int16_t)value(g, a.acc0)); v = f; break; }
+        case TypeKind::TINYINT: { auto f = flatOf<int8_t>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int8_t)value(g, a.acc0)); v = f; break; }
+        default: throw VeloxRuntimeError("aggregate result type " + a.outType->toString() + " is not supported");
+      }
+      VB_CHECK(accIsDouble == a.outType->isFloating(), "accumulator / result type mismatch for " + a.fn);
+      for (int64_t g = 0; g < n; ++g) if (nonNull(g, a.acc0) == 0) v->setNull(g, true);
+    }
+    children.push_back(v);
+  }
+  m.cursor += n;
+  if (m.cursor >= m.nGroups) finished_ = true;
+  return std::make_shared<RowVector>(outputType_, (size_t)n, std::move(children));
+}
+
+} // namespace gpu
+} // namespace vb200

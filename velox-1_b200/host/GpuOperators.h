@@ -1,0 +1,74 @@
+// The B200 operators behind Velox's Operator API and their registration.
+//   GpuFilterProject     replaces exec::FilterProject   (velox/exec/FilterProject.cpp:44-191)
+//   GpuHashAggregation   replaces exec::HashAggregation (velox/exec/HashAggregation.cpp:97-472), optionally with
+//                        the FilterProject below it fused in (vgpu_agg_add_input evaluates filter + projections
+//                        + accumulation in one kernel, the shape of experimental/wave/exec/ToWave.cpp:346-413)
+// Both talk to the CUDA side only through include/vgpu.h; a non-zero status becomes VeloxUserError
+// (VGPU_ERR_USER: data errors) or VeloxRuntimeError.  There is no CPU path: if libvgpu.so or the GPU is
+// missing, construction throws.
+#pragma once
+#include "../../include/vgpu.h"
+#include "Lowering.h"
+#include "Operator.h"
+
+namespace vb200 {
+namespace gpu {
+
+void check(int status, const char* what);           // throws on non-zero vgpu_status
+struct DeviceBatch;                                 // device copies of the columns a program reads
+
+// What a FilterNode / ProjectNode pair contributes when fused into the aggregation above it.
+struct FilterProjectExprs {
+  core::TypedExprPtr filter;                                   // may be null
+  std::vector<std::string> names;                              // projection names (empty = identity over the input)
+  std::vector<core::TypedExprPtr> projections;
+};
+
+class GpuFilterProject : public exec::Operator {
+ public:
+  GpuFilterProject(exec::DriverCtx* ctx, int32_t id, std::shared_ptr<const core::FilterNode> filter,
+                   std::shared_ptr<const core::ProjectNode> project);
+  ~GpuFilterProject() override;
+  bool needsInput() const override { return input_ == nullptr && !noMoreInput_; }
+  void addInput(RowVectorPtr input) override { input_ = std::move(input); }
+  RowVectorPtr getOutput() override;
+  bool isFinished() override { return noMoreInput_ && input_ == nullptr; }
+  bool isFilter() const override { return exprs_.filter != nullptr; }
+  bool preservesOrder() const override { return true; }
+  // "for accelerator conversion" (velox/exec/FilterProject.h:63-72)
+  const FilterProjectExprs& exprsAndProjection() const { return exprs_; }
+  const RowTypePtr& inputType() const { return inputType_; }
+ private:
+  FilterProjectExprs exprs_;
+  RowTypePtr inputType_;
+  std::vector<int> identity_;        // per output: input child index for identity projections, else -1
+  std::vector<int> programOutput_;   // per output: index into the program's outputs, else -1
+  LoweredProgram lowered_;
+  vgpu_program_t program_ = nullptr;
+  void* stream_ = nullptr;
+};
+
+class GpuHashAggregation : public exec::Operator {
+ public:
+  // `fused` (optional): evaluate this filter + projections on the raw input inside the aggregation kernel.
+  GpuHashAggregation(exec::DriverCtx* ctx, int32_t id, std::shared_ptr<const core::AggregationNode> node,
+                     const FilterProjectExprs* fused = nullptr, RowTypePtr fusedInputType = nullptr);
+  ~GpuHashAggregation() override;
+  bool needsInput() const override { return !noMoreInput_; }
+  void addInput(RowVectorPtr input) override;
+  void noMoreInput() override;
+  RowVectorPtr getOutput() override;
+  bool isFinished() override { return finished_; }
+  void close() override;
+  struct Impl;
+ private:
+  std::unique_ptr<Impl> impl_;
+  bool finished_ = false;
+};
+
+// Registers the PlanNodeTranslator (FilterNode / ProjectNode / AggregationNode -> GPU operators) and the
+// DriverAdapter that fuses [GpuFilterProject, GpuHashAggregation(raw input)] into one operator.
+void registerGpuOperators();
+
+} // namespace gpu
+} // namespace vb200

@@ -1,0 +1,31 @@
+// Typed expressions -> one vgpu program (include/vgpu.h): the ExprSet compile step of the GPU
+// operators (velox/exec/FilterProject.cpp:59-103 builds an ExprSet; velox/expression/ExprCompiler.cpp
+// :54-58,160-163 shares common sub-expressions, :131-158 flattens AND/OR — both are kept here).
+#pragma once
+#include <map>
+
+#include "../../include/vgpu.h"
+#include "Plan.h"
+
+namespace vb200 {
+
+struct LoweredProgram {
+  std::vector<vgpu_op> ops;
+  vgpu_operand filter{};                // kind NONE when there is no filter
+  std::vector<vgpu_operand> outputs;
+  std::vector<std::string> columns;     // input column names, in program column order
+  vgpu_program_desc desc() const {
+    vgpu_program_desc d{};
+    d.ops = ops.data(); d.n_ops = (int32_t)ops.size(); d.filter = filter;
+    d.outputs = outputs.data(); d.n_outputs = (int32_t)outputs.size(); d.n_columns = (int32_t)columns.size();
+    return d;
+  }
+};
+
+// vgpu_type of a Velox type on the device (DATE = INTEGER; VARCHAR travels as INTEGER value ids).
+int deviceType(const TypePtr& t);
+
+// Lowers `filter` (may be null) and `outputs`.  Columns are numbered in order of first use.
+LoweredProgram lowerExpressions(const core::TypedExprPtr& filter, const std::vector<core::TypedExprPtr>& outputs);
+
+} // namespace vb200
