@@ -1,0 +1,92 @@
+"""Parity of the multi-GPU path (SURVEY.md section 8(e), config C5's shape at test size), run as
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/multi_gpu_check.py
+One process per GPU: scan + partial aggregation of this rank's order range, vgpu_agg_partition,
+NCCL all-to-all of the packed partial groups (vgpu_comm_alltoallv), vgpu_agg_merge_rows into the final
+aggregation; rank 0 compares the union of all ranks' final groups with the numpy oracle over the whole
+table.  Q1 (ARRAY sink, groups present on every rank) and GROUP BY l_partkey (HASH sink, groups spread
+over ranks) and GROUP BY l_orderkey (HASH, disjoint per rank)."""
+import importlib
+import os
+import pickle
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (ROOT, os.path.join(ROOT, "oracle"), HERE):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = importlib.import_module("velox-1_b200")
+    abi, ex = pkg.abi, pkg.expr
+    abi.check(abi.lib().vgpu_init(local))
+    engine = importlib.import_module("velox-1_b200.engine")
+    import helpers as H
+    import lineitem
+    ids = [engine.Exchange.make_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    exchange = engine.Exchange(rank, world, ids[0])
+
+    sf = 0.1
+    orders = 150000
+    per = (orders + world - 1) // world
+    mine = lineitem.gen_range(sf, rank * per, min(per, orders - rank * per))
+    n = len(mine["l_orderkey"])
+    scratch = f"/tmp/vgpu_mgpu_{os.environ.get('MASTER_PORT', '0')}"
+    os.makedirs(scratch, exist_ok=True)
+    results = {}
+
+    def run(name, mode, filt, outs, col_names, types, keys, accs):
+        cols = [engine.flat_column(t, mine[c]) for c, t in zip(col_names, types)]
+        prog = engine.Program(filt, outs)
+        empty = [engine.flat_column(t, mine[c][:0]) for c, t in zip(col_names, types)]
+        partial = engine.Aggregation(mode, keys, accs)
+        final = engine.Aggregation(mode, keys, accs)
+        partial.add_input(prog, cols, n)
+        final.add_input(prog, empty, 0)
+        exchange.shuffle(partial, final)
+        results[name] = H.decode_rows(final.extract(), keys, accs, [o.type for o in outs], mode)
+
+    f, outs = H.q1_exprs()
+    I32, I64, D = abi.INTEGER, abi.BIGINT, abi.DOUBLE
+    run("q1", abi.AGG_ARRAY, f, outs, H.Q1_COLS, [I32, I32, D, D, D, D, I32], H.Q1_KEYS, H.Q1_ACCS)
+    gb_accs = [(abi.ACC_SUM_F64, 1), (abi.ACC_COUNT, -1), (abi.ACC_MIN, 1), (abi.ACC_MAX, 1)]
+    for key in ("l_partkey", "l_orderkey"):
+        run(key, abi.AGG_HASH, None, [ex.col(0, I64), ex.col(1, D)], [key, "l_extendedprice"], [I64, D], [(0, 64, 0, 0)], gb_accs)
+    with open(os.path.join(scratch, f"rank{rank}.pkl"), "wb") as fh:
+        pickle.dump(results, fh)
+    dist.barrier()
+    ok = True
+    if rank == 0:
+        whole = lineitem.gen_range(sf, 0, orders)
+        total = len(whole["l_orderkey"])
+        parts = [pickle.load(open(os.path.join(scratch, f"rank{r}.pkl"), "rb")) for r in range(world)]
+        for name in results:
+            union = {}
+            for p in parts:
+                assert not (union.keys() & p[name].keys()), f"{name}: a group is final on two ranks"
+                union.update(p[name])
+            if name == "q1":
+                want = H.run_oracle_agg(f, outs, [(whole[c], None) for c in H.Q1_COLS], total, H.Q1_KEYS, H.Q1_ACCS)
+                H.assert_groups_equal(union, want, H.Q1_ACCS)
+            else:
+                want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(whole[name], None), (whole["l_extendedprice"], None)], total,
+                                        [(0, 64, 0, 0)], gb_accs)
+                H.assert_groups_equal(union, want, gb_accs)
+            spread = [len(p[name]) for p in parts]
+            print(f"multi-gpu parity ok: {name}: {len(union)} groups over {total} rows, final groups per rank {spread}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
