@@ -333,6 +333,17 @@ int vgpu_comm_alltoallv(vgpu_comm_t comm, const void* send, const int64_t* send_
 int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t bytes,
                         void* stream);
 
+/* The whole exchange step between a partial and a final aggregation of the same description
+ * (partialAggregation -> partitionedOutput -> exchange -> finalAggregation,
+ * velox/exec/tests/MultiFragmentTest.cpp:180-212): group g goes to rank mix64(key) % world.
+ *   GLOBAL / ARRAY aggregations (small key domains): every rank all-gathers its dense group state
+ *     (fixed size, no counts) and folds the groups it owns — no host synchronisation at all.
+ *   HASH aggregations: vgpu_agg_partition, counts all-gather, vgpu_comm_alltoallv, vgpu_agg_merge_rows.
+ * `final_agg` must have seen an (empty) vgpu_agg_add_input.  *bytes_sent (host, may be NULL) receives
+ * the payload bytes this rank sent to other ranks. */
+int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg_t final_agg, void* stream,
+                              int64_t* bytes_sent);
+
 /* ---- statistics -------------------------------------------------------------------------- */
 
 typedef struct {

@@ -52,8 +52,14 @@ def main():
         final = engine.Aggregation(mode, keys, accs)
         partial.add_input(prog, cols, n)
         final.add_input(prog, empty, 0)
-        exchange.shuffle(partial, final)
+        exchange.shuffle(partial, final)                       # vgpu_comm_exchange_groups
         results[name] = H.decode_rows(final.extract(), keys, accs, [o.type for o in outs], mode)
+        again = engine.Aggregation(mode, keys, accs)
+        again.add_input(prog, empty, 0)
+        exchange.shuffle_stepwise(partial, again)              # partition / all-to-all / merge, step by step
+        stepwise = H.decode_rows(again.extract(), keys, accs, [o.type for o in outs], mode)
+        assert stepwise.keys() == results[name].keys(), f"{name}: the two exchange paths own different groups"
+        H.assert_groups_equal(stepwise, results[name], accs, rtol=1e-12)
 
     f, outs = H.q1_exprs()
     I32, I64, D = abi.INTEGER, abi.BIGINT, abi.DOUBLE

@@ -121,6 +121,7 @@ PROTOTYPES = {
     "vgpu_comm_alltoallv": [_P, _P, C.POINTER(_I64), C.POINTER(_I64), _P, C.POINTER(_I64),
                             C.POINTER(_I64), _P],
     "vgpu_comm_allgather": [_P, _P, _P, _SZ, _P],
+    "vgpu_comm_exchange_groups": [_P, _P, _P, _P, C.POINTER(_I64)],
     "vgpu_get_stats": [C.POINTER(Stats)],
     "vgpu_reset_stats": [],
     "vgpu_debug_set_dry_run": [C.c_int],

@@ -96,6 +96,14 @@ __device__ __forceinline__ void write_packed(uint64_t* out, uint64_t key, uint64
   }
 }
 
+// Every group at its own position (absent groups have rows == 0): the fixed-size image of the state
+// that the small-domain exchange all-gathers.
+__global__ void dense_rows_kernel(const uint64_t* state, int G, RowMap rm, uint64_t* rows_out) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  write_packed(rows_out + (size_t)g * rm.row_words_out, (uint64_t)g, 0, state[(size_t)rm.rows_cell * G + g], rm, state + g, (size_t)G, false);
+}
+
 __global__ void extract_array_kernel(const uint64_t* state, int G, RowMap rm, int always,
                                      uint64_t* rows_out, unsigned long long* counter) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -215,11 +223,15 @@ __device__ __forceinline__ void merge_packed(const uint64_t* row, const RowMap& 
 
 struct DoneMap { uint8_t d[2 * kMaxOutputs]; }; // 1 = an earlier accumulator already covers the cell
 
+__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts);
+// n_parts > 0: rows of every rank's dense state arrive here (fixed-size all-gather); a rank folds the
+// groups it owns (part_of == my_part) and skips groups that saw no row.
 __global__ void merge_rows_array_kernel(const uint64_t* rows, int64_t n, RowMap rm, DoneMap dm,
-                                        uint64_t* state, int G, uint32_t* err_word) {
+                                        uint64_t* state, int G, uint32_t* err_word, int n_parts, int my_part) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t* row = rows + i * rm.row_words_out;
+  if (n_parts > 0 && (row[2] == 0 || part_of(row, n_parts) != my_part)) return;
   uint32_t err = 0;
   if (row[0] >= (uint64_t)G) { atomicOr(err_word, kErrKeyRange); return; }
   merge_packed(row, rm, state + row[0], (size_t)G, false, dm.d, err);
@@ -388,6 +400,7 @@ int agg_resolve(Agg& a, const Program& prog) {
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
+constexpr int kOvfCursor = 40; // a.ctr: [0] groups, [1] scratch, [2..33] partition counts, [40] parked-segment cursor
 constexpr int kDefaultBucketBits = 6; // profiles/r01_c3_experiments.md: 3..7 measured within 4 % of each other
 static KeyMap key_map_of(const Agg& a) {
   KeyMap m{};
@@ -660,13 +673,13 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
         VG_CUDA(cudaMalloc(&a.ovf, want * a.row_words * 8));
         a.ovf_cap = want;
       }
-      VG_CUDA(cudaMemsetAsync(a.ctr + 2, 0, sizeof(unsigned long long), stream));
-      p.ovf = a.ovf; p.ovf_cap = a.ovf_cap; p.ovf_cursor = a.ctr + 2;
+      VG_CUDA(cudaMemsetAsync(a.ctr + kOvfCursor, 0, sizeof(unsigned long long), stream));
+      p.ovf = a.ovf; p.ovf_cap = a.ovf_cap; p.ovf_cursor = a.ctr + kOvfCursor;
     }
     rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
     if (rc) return rc;
     if (p.ovf) {
-      drain_overflow_kernel<<<num_sms() * 8, 256, 0, stream>>>(a.ovf, a.ctr + 2, a.ovf_cap, href_of(a), cell_meta(a), device_err_word());
+      drain_overflow_kernel<<<num_sms() * 8, 256, 0, stream>>>(a.ovf, a.ctr + kOvfCursor, a.ovf_cap, href_of(a), cell_meta(a), device_err_word());
       VG_CUDA(cudaGetLastError());
       count_launch();
     }
@@ -734,7 +747,7 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
   if (n <= 0) return VGPU_OK;
   const DoneMap dm = done_map(a.rm);
   if (a.mode != VGPU_AGG_HASH) {
-    merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, a.state, a.n_groups, device_err_word());
+    merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, a.state, a.n_groups, device_err_word(), 0, 0);
     VG_CUDA(cudaGetLastError());
     count_launch();
     return VGPU_OK;
@@ -749,6 +762,24 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
     if (a.cells[c].kind == kCellCount && a.hash_aliased[c]) { int rc = hash_materialize(a, c, stream); if (rc) return rc; }
   }
   merge_rows_hash_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), device_err_word());
+  VG_CUDA(cudaGetLastError());
+  count_launch();
+  return VGPU_OK;
+}
+
+// Small-domain (ARRAY / GLOBAL) exchange helpers: no host synchronisation.
+int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream) {
+  if (a.mode == VGPU_AGG_HASH || !a.resolved) { set_error("dense rows need a resolved ARRAY / GLOBAL aggregation"); return VGPU_ERR_INVALID; }
+  dense_rows_kernel<<<(a.n_groups + 255) / 256, 256, 0, stream>>>(a.state, a.n_groups, a.rm, (uint64_t*)rows_out);
+  VG_CUDA(cudaGetLastError());
+  count_launch();
+  return VGPU_OK;
+}
+int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int my_part, cudaStream_t stream) {
+  if (a.mode == VGPU_AGG_HASH || !a.resolved) { set_error("owned-row merge needs a resolved ARRAY / GLOBAL aggregation"); return VGPU_ERR_INVALID; }
+  a.packed_rows = -1;
+  if (n <= 0) return VGPU_OK;
+  merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, done_map(a.rm), a.state, a.n_groups, device_err_word(), n_parts, my_part);
   VG_CUDA(cudaGetLastError());
   count_launch();
   return VGPU_OK;

@@ -56,6 +56,8 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
 int agg_extract_all(Agg& a, cudaStream_t stream); // fills the packed cache
 int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream);
 int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cudaStream_t stream);
+int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream);
+int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int my_part, cudaStream_t stream);
 int agg_reset(Agg& a, cudaStream_t stream);
 void agg_free(Agg& a);
 

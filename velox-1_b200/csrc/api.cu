@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <new>
 #include <utility>
@@ -453,7 +454,21 @@ int nccl_fail(int rc, const char* what) { set_error("NCCL error %d (%s) in %s", 
 #define VG_NCCL(x) do { int r_ = (x); if (r_ != 0) return nccl_fail(r_, #x); } while (0)
 } // namespace
 
-struct vgpu_comm_s { nccl_comm comm; int rank, world; };
+struct vgpu_comm_s {
+  nccl_comm comm; int rank, world;
+  // grow-only device scratch of vgpu_comm_exchange_groups
+  void* send = nullptr; size_t send_cap = 0;
+  void* recv = nullptr; size_t recv_cap = 0;
+  int64_t* dcounts = nullptr; // [world] + [world * world]
+};
+static int comm_reserve(void** p, size_t* cap, size_t want) {
+  if (*cap >= want) return VGPU_OK;
+  if (*p) { VG_CUDA(cudaDeviceSynchronize()); VG_CUDA(cudaFree(*p)); *p = nullptr; *cap = 0; }
+  want = std::max<size_t>(want + want / 4, 1 << 16);
+  VG_CUDA(cudaMalloc(p, want));
+  *cap = want;
+  return VGPU_OK;
+}
 
 int vgpu_comm_unique_id(uint8_t id[VGPU_COMM_ID_BYTES]) {
   int rc = load_nccl();
@@ -477,7 +492,7 @@ int vgpu_comm_create(const uint8_t id[VGPU_COMM_ID_BYTES], int32_t rank, int32_t
   return VGPU_OK;
 }
 int vgpu_comm_destroy(vgpu_comm_t comm) {
-  if (comm) { g_nccl.comm_destroy(comm->comm); delete comm; }
+  if (comm) { g_nccl.comm_destroy(comm->comm); cudaFree(comm->send); cudaFree(comm->recv); cudaFree(comm->dcounts); delete comm; }
   return VGPU_OK;
 }
 int vgpu_comm_alltoallv(vgpu_comm_t comm, const void* send, const int64_t* send_counts, const int64_t* send_offsets,
@@ -495,6 +510,46 @@ int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t b
   if (!comm) return VGPU_ERR_INVALID;
   VG_NCCL(g_nccl.allgather(send, recv, bytes, kNcclUint8, comm->comm, (cudaStream_t)stream));
   return VGPU_OK;
+}
+
+int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg_t final_agg, void* stream_, int64_t* bytes_sent) {
+  if (!comm || !partial_agg || !final_agg) return VGPU_ERR_INVALID;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Agg& pa = partial_agg->agg;
+  Agg& fa = final_agg->agg;
+  if (pa.mode != fa.mode || pa.accs.size() != fa.accs.size()) { set_error("partial and final aggregations differ"); return VGPU_ERR_INVALID; }
+  const size_t row_bytes = (3 + 2 * pa.accs.size()) * 8;
+  const int W = comm->world;
+  int rc;
+  if (pa.mode != VGPU_AGG_HASH) {
+    if (pa.n_groups != fa.n_groups) { set_error("partial and final aggregations differ in their key domains"); return VGPU_ERR_INVALID; }
+    const size_t mine = (size_t)pa.n_groups * row_bytes;
+    if ((rc = comm_reserve(&comm->send, &comm->send_cap, mine))) return rc;
+    if ((rc = comm_reserve(&comm->recv, &comm->recv_cap, mine * W))) return rc;
+    if ((rc = agg_dense_rows(pa, comm->send, stream))) return rc;
+    VG_NCCL(g_nccl.allgather(comm->send, comm->recv, mine, kNcclUint8, comm->comm, stream));
+    if (bytes_sent) *bytes_sent = (int64_t)(mine * (W - 1));
+    return agg_merge_owned_rows(fa, comm->recv, (int64_t)pa.n_groups * W, W, comm->rank, stream);
+  }
+  if ((rc = agg_extract_all(pa, stream))) return rc;
+  const int64_t n = pa.packed_rows;
+  if ((rc = comm_reserve(&comm->send, &comm->send_cap, (size_t)std::max<int64_t>(n, 1) * row_bytes))) return rc;
+  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * (32 + 32 * 32)));
+  int64_t counts[32] = {0}, matrix[32 * 32];
+  if ((rc = agg_partition(pa, W, comm->send, counts, stream))) return rc;
+  VG_CUDA(cudaMemcpyAsync(comm->dcounts, counts, sizeof(int64_t) * W, cudaMemcpyHostToDevice, stream));
+  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + 32, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
+  VG_CUDA(cudaMemcpyAsync(matrix, comm->dcounts + 32, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, stream));
+  VG_CUDA(cudaStreamSynchronize(stream));
+  int64_t sc[32], so[32], rcv[32], ro[32], srun = 0, rrun = 0;
+  for (int r = 0; r < W; ++r) { // matrix[src][dst]
+    sc[r] = counts[r] * (int64_t)row_bytes; so[r] = srun; srun += sc[r];
+    rcv[r] = matrix[r * W + comm->rank] * (int64_t)row_bytes; ro[r] = rrun; rrun += rcv[r];
+  }
+  if ((rc = comm_reserve(&comm->recv, &comm->recv_cap, (size_t)std::max<int64_t>(rrun, 8)))) return rc;
+  if ((rc = vgpu_comm_alltoallv(comm, comm->send, sc, so, comm->recv, rcv, ro, stream_))) return rc;
+  if (bytes_sent) *bytes_sent = srun - sc[comm->rank];
+  return agg_merge_rows(fa, comm->recv, rrun / (int64_t)row_bytes, stream);
 }
 
 } // extern "C"

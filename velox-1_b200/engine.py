@@ -286,6 +286,15 @@ class Exchange:
         return bytes(idbuf)
 
     def shuffle(self, partial: "Aggregation", final: "Aggregation"):
+        """One call: vgpu_comm_exchange_groups (dense all-gather for ARRAY / GLOBAL aggregations, partition +
+        counts + all-to-all for HASH ones).  `final` must have seen an (empty) add_input."""
+        sent = C.c_int64()
+        abi.check(abi.lib().vgpu_comm_exchange_groups(self.handle, partial.handle, final.handle, stream_ptr(), C.byref(sent)))
+        self.bytes_sent = sent.value
+
+    def shuffle_stepwise(self, partial: "Aggregation", final: "Aggregation"):
+        """The same exchange spelled out with the individual entry points (partition, counts all-gather,
+        all-to-all, merge); kept as the reference for vgpu_comm_exchange_groups in the multi-GPU test."""
         W = self.world
         rows, counts = partial.partition(W)
         row_bytes = partial.row_words * 8
