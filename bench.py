@@ -38,37 +38,48 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled during the timed region."""
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region: one long-running
+    `nvidia-smi -lms 20` process (started before the warm-up, so it is already streaming), a reader
+    thread that stamps every line, and mark_begin()/mark_end() around the timed steps."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
-        self.samples, self.stop_flag, self.index = [], False, index
+        self.samples, self.index, self.proc = [], index, None
+        self.t_begin = self.t_end = None
         self.thread = threading.Thread(target=self.run, daemon=True)
 
     def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            time.sleep(0.05)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                          str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.samples.append((time.time(), [x.strip() for x in line.split(",")]))
+        except Exception:
+            pass
 
     def start(self):
         self.thread.start()
 
+    def mark_begin(self):
+        self.t_begin = time.time()
+
+    def mark_end(self):
+        self.t_end = time.time()
+
     def stop(self):
-        self.stop_flag = True
+        time.sleep(0.05)
+        if self.proc is not None:
+            self.proc.terminate()
         self.thread.join(timeout=6)
-        sm = [int(s[0]) for s in self.samples if s[0].isdigit()]
-        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        inside = [f for t, f in self.samples if self.t_begin is not None and self.t_begin <= t <= (self.t_end or t) + 0.03]
+        use = inside if inside else [f for _, f in self.samples[-3:]]
+        sm = [int(s[0]) for s in use if s and s[0].isdigit()]
+        mx = [int(s[1]) for s in use if len(s) > 1 and s[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        reasons = sorted({n for s in use for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+                "reasons": reasons, "samples": len(inside), "samples_total": len(self.samples)}
 
 
 def ncu_traffic():
@@ -170,21 +181,23 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
             torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
     stats0 = abi.Stats()
     lib.vgpu_get_stats(stats0)
     abi.check(lib.vgpu_debug_kernel_timing(1))  # events around the scan kernel, on its own stream
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     barrier()
+    sampler.mark_begin()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for _ in range(args.steps):
         step()
     t1.record()
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     stats1 = abi.Stats()
     lib.vgpu_get_stats(stats1)

@@ -52,6 +52,7 @@ struct GpuHashAggregation::Impl {
   void* stream = nullptr;
   int mode = VGPU_AGG_GLOBAL;
   bool sawInput = false;
+  bool forceHash = false;     // the small-domain table was declined for this shape: group through the HBM table
 
   std::vector<int64_t> rows; // extracted packed groups
   int64_t nGroups = -1;
@@ -130,7 +131,7 @@ struct GpuHashAggregation::Impl {
       product *= cardOf(k);
       if (product > 4096) small = false;
     }
-    if (small) mode = VGPU_AGG_ARRAY;
+    if (small && !forceHash) mode = VGPU_AGG_ARRAY;
     std::vector<vgpu_key_spec> specs(keys.size());
     if (mode == VGPU_AGG_HASH) {
       if (keys.size() == 1 && !keys[0].varchar) {
@@ -266,7 +267,16 @@ struct GpuHashAggregation::Impl {
       if (varcharKey >= 0) bindColumn(batch, keyVecs[varcharKey], &keyIds[varcharKey]);
       else bindColumn(batch, columnByName(in, name, keepAlive));
     }
-    check(vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream), "vgpu_agg_add_input");
+    int rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream);
+    if (rc == VGPU_ERR_UNSUPPORTED && mode == VGPU_AGG_ARRAY && !sawInput) {
+      // HashTable::decideHashMode analogue: fall from the array mode to the hash mode (never to a CPU path)
+      vgpu_agg_destroy(agg); agg = nullptr;
+      vgpu_program_destroy(program); program = nullptr;
+      forceHash = true;
+      create();
+      rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream);
+    }
+    check(rc, "vgpu_agg_add_input");
     // data errors (sum overflow, checked arithmetic in fused projections) surface here, like the exception
     // thrown out of HashAggregation::addInput; this also makes the batch's device copies safe to free
     check(vgpu_check_errors(stream), "HashAggregation");
