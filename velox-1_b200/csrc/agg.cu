@@ -110,7 +110,7 @@ __global__ void extract_array_kernel(const uint64_t* state, int G, RowMap rm, in
   if (g >= G) return;
   const uint64_t rows = state[(size_t)rm.rows_cell * G + g];
   if (rows == 0 && !always) return;
-  const unsigned long long pos = atomicAdd(counter, 1ull);
+  const unsigned long long pos = take_one(counter);
   write_packed(rows_out + pos * rm.row_words_out, (uint64_t)g, 0, rows, rm, state + g, (size_t)G, false);
 }
 
@@ -143,7 +143,7 @@ __global__ void rehash_kernel(const uint64_t* from, uint64_t from_slots, HashRef
   if (special) {
     slot = (int64_t)to.cap_mask + 1 + (int64_t)(i - (from_slots - 2));
     to.table[slot * to.row_words] = 0;
-    atomicAdd(to.n_groups_ctr, 1ull);
+    count_one(to.n_groups_ctr);
   } else {
     slot = hash_find_or_insert(to, src[0], false, err);
   }
@@ -158,7 +158,7 @@ __global__ void extract_hash_kernel(const uint64_t* table, uint64_t n_slots, int
   if (i >= n_slots) return;
   const uint64_t* src = table + i * row_words;
   if (src[0] == kEmptyKey) return;
-  const unsigned long long pos = atomicAdd(counter, 1ull);
+  const unsigned long long pos = take_one(counter);
   uint64_t key = src[0], flags = 0;
   if (i == n_slots - 2) { key = 0; flags = 1; }      // NULL key group
   if (i == n_slots - 1) { key = kEmptyKey; }         // the key that equals the empty marker
@@ -287,17 +287,28 @@ __device__ __forceinline__ int part_of(const uint64_t* row, int n_parts) {
 }
 __global__ void partition_count_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
                                        unsigned long long* counts) {
+  __shared__ unsigned int hist[32];
+  if (threadIdx.x < 32) hist[threadIdx.x] = 0;
+  __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  atomicAdd(&counts[part_of(rows + i * row_words, n_parts)], 1ull);
+  if (i < n) atomicAdd(&hist[part_of(rows + i * row_words, n_parts)], 1u);
+  __syncthreads();
+  if (threadIdx.x < n_parts && hist[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)hist[threadIdx.x]);
 }
 __global__ void partition_scatter_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
                                          unsigned long long* cursors, uint64_t* out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t* row = rows + i * row_words;
-  const unsigned long long pos = atomicAdd(&cursors[part_of(row, n_parts)], 1ull);
-  uint64_t* dst = out + pos * row_words;
+  // lanes of the warp bound for the same part take their positions with one atomic
+  const int part = part_of(row, n_parts);
+  const unsigned active = __activemask();
+  const unsigned peers = __match_any_sync(active, part);
+  const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(&cursors[part], (unsigned long long)__popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  uint64_t* dst = out + (base + __popc(peers & ((1u << lane) - 1u))) * row_words;
   for (int w = 0; w < row_words; ++w) dst[w] = row[w];
 }
 

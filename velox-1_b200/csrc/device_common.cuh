@@ -26,6 +26,23 @@ __device__ __forceinline__ uint64_t mix64(uint64_t k) { // splitmix64 finaliser
 }
 constexpr uint64_t kEmptyKey = 0xffffffffffffffffull;
 
+// Warp-aggregated atomics.  Millions of threads bumping ONE counter serialise in the L2 atomic unit
+// (15 M increments ~ 7 ms on B200); the lanes that reach the call together elect a leader that adds
+// their count once.  Each lane is in exactly one such group, so the total is exact.
+__device__ __forceinline__ void count_one(unsigned long long* ctr) {
+  const unsigned m = __activemask();
+  if ((int)(threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(ctr, (unsigned long long)__popc(m));
+}
+// Same, returning this lane's own position in the sequence the counter hands out.
+__device__ __forceinline__ unsigned long long take_one(unsigned long long* ctr) {
+  const unsigned m = __activemask();
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(ctr, (unsigned long long)__popc(m));
+  base = __shfl_sync(m, base, leader);
+  return base + __popc(m & ((1u << lane) - 1u));
+}
+
 __device__ __forceinline__ uint64_t home_slot(const KeyMap& m, uint64_t cap_mask, uint64_t key) {
   if (m.mode == 3) {
     const uint32_t b = m.pad;
@@ -89,7 +106,7 @@ __device__ __forceinline__ int64_t hash_find_or_insert(const HashRef& p, uint64_
     const int64_t slot = (int64_t)p.cap_mask + (isnull ? 1 : 2);
     unsigned long long* kp = reinterpret_cast<unsigned long long*>(table + slot * rw);
     if (*reinterpret_cast<volatile unsigned long long*>(kp) == kEmptyKey) {
-      if (atomicCAS(kp, kEmptyKey, 0ull) == kEmptyKey) atomicAdd(p.n_groups_ctr, 1ull);
+      if (atomicCAS(kp, kEmptyKey, 0ull) == kEmptyKey) count_one(p.n_groups_ctr);
     }
     return slot;
   }
@@ -101,7 +118,7 @@ __device__ __forceinline__ int64_t hash_find_or_insert(const HashRef& p, uint64_
     if (cur == kEmptyKey) {
       cur = atomicCAS(kp, kEmptyKey, (unsigned long long)key);
       if (cur == kEmptyKey) {
-        atomicAdd(p.n_groups_ctr, 1ull);
+        count_one(p.n_groups_ctr);
         return (int64_t)h;
       }
       if (cur == key) return (int64_t)h;
