@@ -152,17 +152,44 @@ __global__ void rehash_kernel(const uint64_t* from, uint64_t from_slots, HashRef
   for (int w = 1; w < to.row_words; ++w) dst[w] = src[w];
 }
 
+// One block walks 1024 consecutive slots; the block takes its output range with ONE atomic (a per-warp
+// atomic on a single counter was half of this kernel's time at 32 M slots).
+constexpr int kExtractPerThread = 4;
 __global__ void extract_hash_kernel(const uint64_t* table, uint64_t n_slots, int row_words, RowMap rm,
                                     uint64_t* rows_out, unsigned long long* counter) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_slots) return;
-  const uint64_t* src = table + i * row_words;
-  if (src[0] == kEmptyKey) return;
-  const unsigned long long pos = take_one(counter);
-  uint64_t key = src[0], flags = 0;
-  if (i == n_slots - 2) { key = 0; flags = 1; }      // NULL key group
-  if (i == n_slots - 1) { key = kEmptyKey; }         // the key that equals the empty marker
-  write_packed(rows_out + pos * rm.row_words_out, key, flags, src[1 + rm.rows_cell], rm, src + 1, 1, true);
+  __shared__ unsigned int warp_count[8];
+  __shared__ unsigned long long block_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint64_t first = (uint64_t)blockIdx.x * (256 * kExtractPerThread);
+  bool occ[kExtractPerThread];
+  unsigned int mine = 0, before[kExtractPerThread];
+#pragma unroll
+  for (int k = 0; k < kExtractPerThread; ++k) {
+    const uint64_t i = first + (uint64_t)k * 256 + threadIdx.x;
+    occ[k] = i < n_slots && table[i * row_words] != kEmptyKey;
+    const unsigned m = __ballot_sync(0xffffffffu, occ[k]);
+    before[k] = mine + __popc(m & ((1u << lane) - 1u));   // rank inside the warp, pass k after passes < k
+    mine += __popc(m);                                      // warp total so far (same in every lane)
+  }
+  if (lane == 0) warp_count[warp] = mine;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int total = 0;
+    for (int w = 0; w < 8; ++w) { const unsigned int c = warp_count[w]; warp_count[w] = total; total += c; }
+    block_base = total ? atomicAdd(counter, (unsigned long long)total) : 0ull;
+  }
+  __syncthreads();
+  const unsigned long long base = block_base + warp_count[warp];
+#pragma unroll
+  for (int k = 0; k < kExtractPerThread; ++k) {
+    if (!occ[k]) continue;
+    const uint64_t i = first + (uint64_t)k * 256 + threadIdx.x;
+    const uint64_t* src = table + i * row_words;
+    uint64_t key = src[0], flags = 0;
+    if (i == n_slots - 2) { key = 0; flags = 1; }      // NULL key group
+    if (i == n_slots - 1) { key = kEmptyKey; }         // the key that equals the empty marker
+    write_packed(rows_out + (base + before[k]) * rm.row_words_out, key, flags, src[1 + rm.rows_cell], rm, src + 1, 1, true);
+  }
 }
 
 // ---- merging packed rows ---------------------------------------------------------------------
@@ -240,12 +267,29 @@ __global__ void merge_rows_array_kernel(const uint64_t* rows, int64_t n, RowMap 
 
 __global__ void merge_rows_hash_kernel(const uint64_t* rows, int64_t n, RowMap rm, DoneMap dm, HashRef h,
                                        uint32_t* err_word) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint64_t* row = rows + i * rm.row_words_out;
-  uint32_t err = 0;
-  const int64_t slot = hash_find_or_insert(h, row[0], (row[1] & 1ull) != 0, err);
-  if (slot >= 0) merge_packed(row, rm, h.table + slot * h.row_words + 1, 1, true, dm.d, err);
+  const int rw = h.row_words;
+  uint32_t err = 0, inserted = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t* row = rows + i * rm.row_words_out;
+    const uint64_t key = row[0];
+    const bool isnull = (row[1] & 1ull) != 0;
+    int64_t slot = -1;
+    if (isnull || key == kEmptyKey) {
+      slot = hash_find_or_insert(h, key, isnull, err); // the two dedicated slots
+    } else { // claim first: one atomic round trip settles a new group and a present one alike
+      uint64_t at = home_slot(h.key_map, h.cap_mask, key);
+      for (uint64_t probes = 0; probes <= h.cap_mask + kBucketSteps; ++probes) {
+        const unsigned long long seen = atomicCAS(reinterpret_cast<unsigned long long*>(h.table + at * rw), kEmptyKey, (unsigned long long)key);
+        if (seen == kEmptyKey) { ++inserted; slot = (int64_t)at; break; }
+        if (seen == key) { slot = (int64_t)at; break; }
+        at = next_slot(h.key_map, h.cap_mask, at, probes);
+      }
+      if (slot < 0) err |= kErrTableFull;
+    }
+    if (slot >= 0) merge_packed(row, rm, h.table + slot * rw + 1, 1, true, dm.d, err);
+  }
+  for (int o = 16; o > 0; o >>= 1) inserted += __shfl_xor_sync(0xffffffffu, inserted, o);
+  if ((threadIdx.x & 31) == 0 && inserted) atomicAdd(h.n_groups_ctr, (unsigned long long)inserted);
   if (err) atomicOr(err_word, err);
 }
 
@@ -297,18 +341,21 @@ __global__ void partition_count_kernel(const uint64_t* rows, int64_t n, int row_
 }
 __global__ void partition_scatter_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
                                          unsigned long long* cursors, uint64_t* out) {
+  // positions inside the block from a shared-memory histogram; one global atomic per part and block
+  __shared__ unsigned int hist[32];
+  __shared__ unsigned long long base[32];
+  if (threadIdx.x < 32) hist[threadIdx.x] = 0;
+  __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
   const uint64_t* row = rows + i * row_words;
-  // lanes of the warp bound for the same part take their positions with one atomic
-  const int part = part_of(row, n_parts);
-  const unsigned active = __activemask();
-  const unsigned peers = __match_any_sync(active, part);
-  const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
-  unsigned long long base = 0;
-  if (lane == leader) base = atomicAdd(&cursors[part], (unsigned long long)__popc(peers));
-  base = __shfl_sync(peers, base, leader);
-  uint64_t* dst = out + (base + __popc(peers & ((1u << lane) - 1u))) * row_words;
+  int part = 0;
+  unsigned int local = 0;
+  if (i < n) { part = part_of(row, n_parts); local = atomicAdd(&hist[part], 1u); }
+  __syncthreads();
+  if (threadIdx.x < n_parts && hist[threadIdx.x]) base[threadIdx.x] = atomicAdd(&cursors[threadIdx.x], (unsigned long long)hist[threadIdx.x]);
+  __syncthreads();
+  if (i >= n) return;
+  uint64_t* dst = out + (base[part] + local) * row_words;
   for (int w = 0; w < row_words; ++w) dst[w] = row[w];
 }
 
@@ -724,7 +771,7 @@ int agg_extract_all(Agg& a, cudaStream_t stream) {
         if (rm.value_kind[i] == kCellCount && a.hash_aliased[rm.value_cell[i]]) rm.value_cell[i] = (int16_t)rm.rows_cell;
       }
       const uint64_t slots = a.capacity + 2;
-      extract_hash_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, stream>>>(a.table, slots, a.row_words, rm, a.packed, a.ctr + 1);
+      extract_hash_kernel<<<(unsigned)((slots + 256 * kExtractPerThread - 1) / (256 * kExtractPerThread)), 256, 0, stream>>>(a.table, slots, a.row_words, rm, a.packed, a.ctr + 1);
       VG_CUDA(cudaGetLastError());
       count_launch();
     }
@@ -772,7 +819,7 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
   for (int c = 1; c < a.n_cells; ++c) {
     if (a.cells[c].kind == kCellCount && a.hash_aliased[c]) { int rc = hash_materialize(a, c, stream); if (rc) return rc; }
   }
-  merge_rows_hash_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), device_err_word());
+  merge_rows_hash_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), device_err_word());
   VG_CUDA(cudaGetLastError());
   count_launch();
   return VGPU_OK;
