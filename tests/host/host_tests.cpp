@@ -145,6 +145,8 @@ static void cpuTests() {
   EXPECT(parse::parseExpr("l_orderkey + 1", row)->type()->kind() == TypeKind::BIGINT);
   EXPECT(parse::parseExpr("cast(l_orderkey as double) / 2.0", row)->toString() == "divide(cast(l_orderkey as DOUBLE),2.000000)");
   EXPECT(parse::parseExpr("l_quantity is not null or not (l_tax <> 0.0)", row)->toString() == "or(not(is_null(l_quantity)),not(neq(l_tax,0.000000)))");
+  EXPECT(parse::parseExpr("l_shipdate in (8766, 9131) and l_quantity not in (0.5)", row)->toString() ==
+         "and(or(eq(l_shipdate,8766),eq(l_shipdate,9131)),not(eq(l_quantity,0.500000)))");
   EXPECT(parse::parseExpr("1 + 2 * 3", row)->toString() == "7"); // constant folding (ExprCompiler.cpp:302-335)
   EXPECT_THROW(parse::parseExpr("no_such_column > 1", row), VeloxUserError);
   EXPECT_THROW(parse::parseExpr("l_quantity > l_orderkey", row), VeloxUserError); // no implicit casts between columns
@@ -301,6 +303,12 @@ static void gpuTests() {
     // all rows pass -> no wrapping (Operator.cpp:195-228)
     auto all = exec::runPlan(PlanBuilder().values({in[0]}).filter("l_quantity > 0.0").planNode());
     EXPECT(all.size() == 1 && all[0]->size() == in[0]->size() && all[0]->childAt(0)->encoding() == VectorEncoding::FLAT);
+    // IN list (OR of eq on the device)
+    auto inl = exec::runPlan(PlanBuilder().values({in[0]}).filter("l_tax in (0.02, 0.05) and l_returnflag is not null").project({"l_tax"}).planNode());
+    size_t wantIn = 0, gotIn = 0;
+    for (size_t i = 0; i < in[0]->size(); ++i) wantIn += t.tax[i] == 0.02 || t.tax[i] == 0.05;
+    for (auto& o : inl) gotIn += o->size();
+    EXPECT(gotIn == wantIn && wantIn > 0);
     // no row passes -> no output vector at all (Driver.cpp:550-556)
     EXPECT(exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").planNode()).empty());
   }

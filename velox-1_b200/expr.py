@@ -84,6 +84,13 @@ def call(fn, *args):
     raise ValueError(f"unknown function {fn}")
 
 
+def in_list(x, values):
+    """x IN (v1, v2, ...) over literals: OR of eq, the form the device evaluates
+    (velox/functions/prestosql/InPredicate.cpp; same three-valued result)."""
+    terms = [call("eq", x, lit(v, x.type)) for v in values]
+    return terms[0] if len(terms) == 1 else call("or", *terms)
+
+
 def cast(x, to_type):
     return x if x.type == to_type else Call(to_type, "cast", (x,))
 

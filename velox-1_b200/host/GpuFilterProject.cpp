@@ -182,7 +182,16 @@ RowVectorPtr GpuFilterProject::getOutput() {
   const size_t n = in->size();
   DeviceBatch batch;
   batch.stream = stream_;
-  for (auto& name : lowered_.columns) bindColumn(batch, in->childAt(inputType_->getChildIdx(name)));
+  for (auto& name : lowered_.columns) {
+    const auto& child = in->childAt(inputType_->getChildIdx(name));
+    if (child->type()->kind() == TypeKind::VARCHAR) {
+      // only the null flags of a VARCHAR column can matter to a device expression (is_null); values travel as ids
+      const std::vector<int32_t> zeros(decode(child).base->size(), 0);
+      bindColumn(batch, child, &zeros);
+    } else {
+      bindColumn(batch, child);
+    }
+  }
   const size_t words = bits::nwords(n);
   auto* selBits = (uint64_t*)batch.scratch(words * 8, true);
   auto* selIdx = (int32_t*)batch.scratch(n * 4, false);

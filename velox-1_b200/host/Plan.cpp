@@ -192,6 +192,23 @@ class Parser {
       hi = makeCast(hi, a->type());
       return std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{a, lo, hi}, "between");
     }
+    {
+      // x [NOT] IN (v1, v2, ...): a literal list becomes OR of eq — what the device evaluates
+      // (velox/functions/prestosql/InPredicate.cpp builds a set; same three-valued result)
+      const size_t save = pos_;
+      const bool negated = acceptWord("not");
+      if (acceptWord("in")) {
+        VB_USER_CHECK(accept("("), "IN: '(' expected");
+        TypedExprPtr any;
+        do {
+          auto eq = binary("eq", a, parseAdd(), true);
+          any = any ? conjunct("or", any, eq) : eq;
+        } while (accept(","));
+        VB_USER_CHECK(accept(")"), "IN: ')' expected");
+        return negated ? std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{any}, "not") : any;
+      }
+      pos_ = save;
+    }
     if (acceptWord("is")) {
       const bool neg = acceptWord("not");
       VB_USER_CHECK(acceptWord("null"), "IS [NOT] NULL expected");
