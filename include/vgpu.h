@@ -23,8 +23,8 @@
  *                          <- velox/exec/HashPartitionFunction.cpp:59-92 + PartitionedOutput/Exchange
  *                             (partial -> repartition by key -> final,
  *                             velox/exec/tests/MultiFragmentTest.cpp:180-212)
- *   vgpu_tpch_lineitem     <- velox/tpch/gen/TpchGen.cpp:401-489 (genTpchLineItem),
- *                             velox/connectors/tpch/TpchConnector.cpp:139-163
+ *   (input data: velox/tpch/gen/TpchGen.cpp:401-489 is restated for tests in oracle/ref_dbgen_shim.cpp,
+ *    not part of this ABI)
  *
  * Bitmaps follow velox/common/base/Nulls.h:26-35: uint64 little-endian words, bit i of a nulls
  * bitmap is 1 when row i is NOT null; a NULL bitmap pointer means "no nulls".
