@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <map>
 #include <set>
+#include <thread>
 
 #include "../../oracle/velox_cpu.h"
 #include "../../velox-1_b200/host/GpuDevice.h"
@@ -427,6 +428,39 @@ static void gpuTests() {
       }
       EXPECT(ok && groups == (ignoreNullKeys ? 28u : 40u));
     }
+  }
+
+  section("four drivers in parallel: one operator instance per thread, one GPU (Operator.h threading contract)");
+  {
+    auto makePlan = [&] {
+      return PlanBuilder().values(in).filter("l_shipdate <= '1998-09-02'::DATE")
+          .project({"l_returnflag", "l_linestatus", "l_extendedprice * (1.0 - l_discount) as disc_price", "l_orderkey"})
+          .partialAggregation({"l_returnflag", "l_linestatus"}, {"sum(disc_price) as s", "count(*) as c", "max(l_orderkey) as m"}).finalAggregation().planNode();
+    };
+    auto flatten = [](const std::vector<RowVectorPtr>& out) {
+      std::map<std::string, std::tuple<double, int64_t, int64_t>> r;
+      for (auto& o : out) for (size_t g = 0; g < o->size(); ++g)
+        r[at<std::string>(o->childAt(0), g) + at<std::string>(o->childAt(1), g)] = {at<double>(o->childAt(2), g), at<int64_t>(o->childAt(3), g), at<int64_t>(o->childAt(4), g)};
+      return r;
+    };
+    const auto want = flatten(exec::runPlan(makePlan()));
+    std::vector<std::map<std::string, std::tuple<double, int64_t, int64_t>>> got(4);
+    std::vector<std::string> errors(4);
+    std::vector<std::thread> threads;
+    for (int d = 0; d < 4; ++d) threads.emplace_back([&, d] {
+      try { for (int rep = 0; rep < 3; ++rep) got[d] = flatten(exec::runPlan(makePlan())); } catch (const std::exception& e) { errors[d] = e.what(); }
+    });
+    for (auto& th : threads) th.join();
+    bool ok = want.size() == 6;
+    for (int d = 0; d < 4; ++d) {
+      ok = ok && errors[d].empty() && got[d].size() == want.size();
+      for (auto& [k, w] : want) {
+        auto it = got[d].find(k);
+        ok = ok && it != got[d].end() && std::get<1>(it->second) == std::get<1>(w) && std::get<2>(it->second) == std::get<2>(w) && close(std::get<0>(it->second), std::get<0>(w));
+      }
+      if (!errors[d].empty()) printf("  driver %d: %s\n", d, errors[d].c_str());
+    }
+    EXPECT(ok);
   }
 
   section("edge cases: empty input, all-null input, integer overflow (SumTest.cpp:509-538,610-620)");

@@ -737,7 +737,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     FusedKernel* fk = fused_prepare(p, &fgrid);
     static const bool parking = !(getenv("VGPU_NO_PARKING") && getenv("VGPU_NO_PARKING")[0] == '1');
     if (fk && parking) {
-      const uint64_t want = std::max<uint64_t>(1u << 20, a.capacity / 8);
+      const uint64_t want = std::max<uint64_t>(1u << 16, a.capacity / 8); // a full buffer only means the scan warp walks the table itself
       if (a.ovf_cap < want) {
         if (a.ovf) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(a.ovf)); a.ovf = nullptr; }
         VG_CUDA(cudaMalloc(&a.ovf, want * a.row_words * 8));
