@@ -182,7 +182,8 @@ def run_ours(args, rank, world, local_rank):
             torch.cuda.synchronize()
 
     sampler = ClockSampler(local_rank)
-    sampler.start()
+    if rank == 0:  # one nvidia-smi stream is enough; the other ranks' GPUs run the same kernels
+        sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
@@ -198,7 +199,7 @@ def run_ours(args, rank, world, local_rank):
     t1.record()
     barrier()
     sampler.mark_end()
-    clocks = sampler.stop()
+    clocks = sampler.stop() if rank == 0 else None
     stats1 = abi.Stats()
     lib.vgpu_get_stats(stats1)
     ms = t0.elapsed_time(t1)
