@@ -147,7 +147,10 @@ def main():
         prog = engine.Program(None, outs)
         agg = engine.Aggregation(abi.AGG_ARRAY, keys, accs)
         med, best = timed(lambda: agg.add_input(prog, cols, n), agg.reset)
-        report("C4 dictionary keys with nulls (ARRAY sink, 40 groups)", 28.375, med, best, {"groups": agg.num_groups()})
+        # bytes actually read: 2 x int32 indices + price 8 + date 4 + three null bitmaps; count(l_quantity) needs
+        # only l_quantity's null bits, so its 8-byte values are never loaded (ncu: 1.22 GB = 20.4 B/row)
+        report("C4 dictionary keys with nulls (ARRAY sink, 40 groups)", 20.375, med, best,
+               {"groups": agg.num_groups(), "bytes_per_row_if_quantity_values_were_read": 28.375})
 
 
 if __name__ == "__main__":
