@@ -60,6 +60,9 @@ class ClockSampler:
 
     def start(self):
         self.thread.start()
+        deadline = time.time() + 3.0   # nvidia-smi needs a moment before its first line
+        while not self.samples and time.time() < deadline:
+            time.sleep(0.01)
 
     def mark_begin(self):
         self.t_begin = time.time()
