@@ -430,6 +430,33 @@ static void gpuTests() {
     }
   }
 
+  section("VARCHAR key dictionary grows across batches: small-domain table regrown, groups kept (VectorHasher value ids)");
+  {
+    std::vector<RowVectorPtr> grow;
+    std::map<std::string, std::pair<int64_t, int64_t>> want; // name -> (count, sum)
+    Lcg r{99};
+    for (int b = 0; b < 6; ++b) {
+      const int distinct = b == 0 ? 2 : b < 3 ? 9 : 40;  // 2 -> 9 -> 40 distinct strings
+      std::vector<std::string> names;
+      std::vector<int64_t> vals;
+      for (int i = 0; i < 5000; ++i) {
+        names.push_back("city_" + std::to_string(r.range(0, distinct - 1)));
+        vals.push_back(r.range(-1000, 1000));
+        auto& w = want[names.back()];
+        ++w.first; w.second += vals.back();
+      }
+      grow.push_back(makeRowVector({"name", "v"}, {makeFlatVector<std::string>(VARCHAR(), names), makeFlatVector<int64_t>(BIGINT(), vals)}));
+    }
+    auto out = exec::runPlan(PlanBuilder().values(grow).partialAggregation({"name"}, {"count(*) as c", "sum(v) as s", "min(v) as lo"}).finalAggregation().planNode());
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      auto it = want.find(at<std::string>(o->childAt(0), g));
+      ok = ok && it != want.end() && at<int64_t>(o->childAt(1), g) == it->second.first && at<int64_t>(o->childAt(2), g) == it->second.second;
+    }
+    EXPECT(ok && groups == want.size() && groups == 40);
+  }
+
   section("four drivers in parallel: one operator instance per thread, one GPU (Operator.h threading contract)");
   {
     auto makePlan = [&] {
