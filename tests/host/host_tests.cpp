@@ -457,6 +457,43 @@ static void gpuTests() {
     EXPECT(ok && groups == want.size() && groups == 40);
   }
 
+  section("multi-key HASH grouping (SMALLINT + INTEGER with NULLs), REAL inputs, partial -> intermediate -> final");
+  {
+    const size_t n = 40000;
+    Lcg r{5};
+    std::vector<int16_t> k1(n);
+    std::vector<int32_t> k2(n), w(n);
+    std::vector<float> v(n);
+    for (size_t i = 0; i < n; ++i) { k1[i] = (int16_t)r.range(-3, 3); k2[i] = r.range(-20, 2000000000 / 40000 * 0 + 50); w[i] = r.range(-100000, 100000); v[i] = (float)r.range(-5000, 5000) * 0.125f; }
+    auto k2v = makeFlatVector<int32_t>(INTEGER(), k2);
+    auto vv = makeFlatVector<float>(REAL(), v);
+    for (size_t i = 0; i < n; ++i) { if (i % 17 == 0) k2v->setNull(i, true); if (i % 5 == 0) vv->setNull(i, true); }
+    std::vector<RowVectorPtr> parts;
+    auto whole = makeRowVector({"k1", "k2", "v", "w"}, {makeFlatVector<int16_t>(SMALLINT(), k1), k2v, vv, makeFlatVector<int32_t>(INTEGER(), w)});
+    struct W { double sum = 0; int64_t cnt = 0, sw = 0, rows = 0; float mn = 1e30f; int32_t mx = INT32_MIN; };
+    std::map<std::pair<int, int64_t>, W> want; // k2 NULL -> INT64_MIN
+    for (size_t i = 0; i < n; ++i) {
+      auto& x = want[{k1[i], i % 17 == 0 ? INT64_MIN : (int64_t)k2[i]}];
+      ++x.rows; x.sw += w[i]; x.mx = std::max(x.mx, w[i]);
+      if (i % 5 != 0) { x.sum += v[i]; ++x.cnt; x.mn = std::min(x.mn, v[i]); }
+    }
+    auto out = exec::runPlan(PlanBuilder().values({whole}).partialAggregation({"k1", "k2"}, {"sum(v) as s", "avg(v) as a", "min(v) as lo", "max(w) as hi", "sum(w) as sw", "count(v) as c", "count(*) as r"})
+                                 .intermediateAggregation().finalAggregation().planNode());
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      const int64_t key2 = isNullAt(o->childAt(1), g) ? INT64_MIN : (int64_t)at<int32_t>(o->childAt(1), g);
+      auto it = want.find({at<int16_t>(o->childAt(0), g), key2});
+      if (it == want.end()) { ok = false; continue; }
+      const W& x = it->second;
+      ok = ok && at<int64_t>(o->childAt(7), g) == x.cnt && at<int64_t>(o->childAt(8), g) == x.rows && at<int64_t>(o->childAt(6), g) == x.sw && at<int32_t>(o->childAt(5), g) == x.mx;
+      if (x.cnt == 0) { ok = ok && isNullAt(o->childAt(2), g) && isNullAt(o->childAt(3), g) && isNullAt(o->childAt(4), g); continue; }
+      ok = ok && at<float>(o->childAt(2), g) == (float)x.sum && at<float>(o->childAt(3), g) == (float)(x.sum / (double)x.cnt) && at<float>(o->childAt(4), g) == x.mn; // multiples of 1/8: exact in double
+    }
+    EXPECT(ok && groups == want.size());
+    EXPECT(out.empty() || out[0]->rowType()->toString() == "ROW<k1:SMALLINT,k2:INTEGER,s:REAL,a:REAL,lo:REAL,hi:INTEGER,sw:BIGINT,c:BIGINT,r:BIGINT>");
+  }
+
   section("four drivers in parallel: one operator instance per thread, one GPU (Operator.h threading contract)");
   {
     auto makePlan = [&] {
