@@ -307,8 +307,45 @@ def cpu_baseline(args, H, f, outs, data, types):
     for _ in range(2):
         _, secs = cpu.run(f, outs, sc, sample, [0, 1], accs, threads=threads, max_groups=64)
         best = secs if best is None else min(best, secs)
-    return {"value": sample / best, "unit": "rows/s", "cores": threads, "kind": "port",
-            "sample": f"first {sample} rows of the workload, {threads} driver threads, batches of 4096 rows"}
+    out = {"value": sample / best, "unit": "rows/s", "cores": threads, "kind": "port",
+           "sample": f"first {sample} rows of the workload, {threads} driver threads, batches of 4096 rows"}
+    duck = duckdb_baseline(data, threads)
+    if duck is not None:
+        out["duckdb"] = duck
+    return out
+
+
+Q1_SQL = ("select l_returnflag, l_linestatus, sum(l_quantity), sum(l_extendedprice), "
+          "sum(l_extendedprice * (1 - l_discount)), sum(l_extendedprice * (1 - l_discount) * (1 + l_tax)), "
+          "avg(l_quantity), avg(l_extendedprice), avg(l_discount), count(*) from lineitem "
+          "where l_shipdate <= date '1998-09-02' group by l_returnflag, l_linestatus order by 1, 2")
+
+
+def duckdb_baseline(data, threads, rows=6_000_000):
+    """Second CPU baseline: the reference's vendored DuckDB v0.4.1 (oracle/_ref/
+    libduckdb_ref.so) running TPC-H Q1 as SQL over the first `rows` rows, PRAGMA threads = host cores.  The table
+    load (row-at-a-time Appender, like the reference's DuckDbQueryRunner) is outside the timed region."""
+    import duck_ref as D
+    if not D.available():
+        return None
+    rows = min(rows, len(data[Q1_COLS[0]]))
+    host = {c: data[c][:rows].cpu().numpy() for c in Q1_COLS}
+    with D.Session(threads=threads) as s:
+        s.create_table("lineitem", [
+            ("l_returnflag", D.VARCHAR_CODES, host["l_returnflag"], ["A", "N", "R"]),
+            ("l_linestatus", D.VARCHAR_CODES, host["l_linestatus"], ["F", "O"]),
+            ("l_quantity", D.DOUBLE, host["l_quantity"]), ("l_extendedprice", D.DOUBLE, host["l_extendedprice"]),
+            ("l_discount", D.DOUBLE, host["l_discount"]), ("l_tax", D.DOUBLE, host["l_tax"]),
+            ("l_shipdate", D.DATE, host["l_shipdate"])])
+        best = None
+        for _ in range(4):
+            t0 = time.perf_counter()
+            vals, _, _ = s.query(Q1_SQL)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+    return {"value": rows / best, "unit": "rows/s", "cores": threads, "kind": "reference-test-oracle",
+            "groups": int(len(vals)),
+            "sample": f"first {rows} rows, vendored DuckDB v0.4.1 (-O2), Q1 as SQL, PRAGMA threads={threads}, best of 4"}
 
 
 def main():
