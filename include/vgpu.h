@@ -125,6 +125,16 @@ typedef enum {
   VGPU_OP_CAST = 8,
   /* move a value operand into ACC (and optionally a slot) — FieldReference / ConstantExpr. */
   VGPU_OP_MOV = 9,
+  /* special forms over values (not default null).  Like the reference, a branch is only "evaluated"
+   * on the rows that take it: an error latched in the branch a row does not take is dropped.
+   *   SELECT  : if(a, b, c) — a is a BOOLEAN operand; rows where a is TRUE take b, rows where a is
+   *             FALSE or NULL take c (c of kind VGPU_OPND_NULL = no ELSE branch); an error in a is
+   *             kept (velox/expression/SwitchExpr.cpp:64-160; CASE WHEN chains nest in c).
+   *   COALESCE: coalesce(a, b) — a where it is not NULL, else b; b's errors only count on rows
+   *             where a is NULL (velox/expression/CoalesceExpr.cpp:39-81; n-ary nests in b).
+   * b is read with `imm`, c with `imm2`.  Result type = op.type, never BOOLEAN. */
+  VGPU_OP_SELECT = 10,
+  VGPU_OP_COALESCE = 11,
   /* comparisons a ? b on op.type, default null, boolean result
    * (velox/functions/prestosql/Comparisons.h:43-80; NaN compares false except NE). */
   VGPU_OP_EQ = 16,

@@ -127,14 +127,36 @@ def eval_expr(e, cols, n):
         null = ~decided & ~err & any_null
         val = ~decided & ~err & ~null if fn == "and" else decided
         return val, null, err
+    if fn == "if":
+        # SwitchExpr.cpp:64-160: THEN is evaluated on the rows whose condition is TRUE, ELSE on the rest
+        # (FALSE or NULL), so an error in the branch a row does not take never surfaces.
+        (cv, cn, ce), (av, an, ae), (bv, bn, be) = [eval_expr(a, cols, n) for a in e.args]
+        take = cv & ~cn & ~ce
+        err = ce | (take & ae) | (~take & ~ce & be)
+        null = np.where(take, an, bn) & ~err
+        return np.where(take, av, bv).astype(NP[t]), null, err
+    if fn == "coalesce":
+        # CoalesceExpr.cpp:39-81: argument k is evaluated only where arguments 0..k-1 were NULL.
+        v, null, err = eval_expr(e.args[0], cols, n)
+        v = np.asarray(v).astype(NP[t])
+        for a in e.args[1:]:
+            bv, bn, be = eval_expr(a, cols, n)
+            need = null & ~err
+            v = np.where(need, bv, v).astype(NP[t])
+            err = err | (need & be)
+            null = np.where(need, bn, null) & ~err
+        return v, null, err
     args = [eval_expr(a, cols, n) for a in e.args]
     if fn == "is_null":
         return args[0][1].copy(), np.zeros(n, dtype=bool), args[0][2].copy()
+    # Expr::evalArgsDefaultNulls (Expr.cpp:371-441): arguments are evaluated left to right and a row whose
+    # argument k is NULL (without an error) is deselected before argument k+1 is evaluated, so an error in a
+    # later argument does not surface on it.
     null = np.zeros(n, dtype=bool)
     err = np.zeros(n, dtype=bool)
     for _, nl, er in args:
-        null |= nl
-        err |= er
+        err |= er & ~null
+        null |= nl & ~err
     live = ~null
     a = args[0][0]
     b = args[1][0] if len(args) > 1 else None

@@ -180,6 +180,11 @@ struct Parser {
       e.type = kBool;
     } else if (f == "plus" || f == "minus" || f == "multiply" || f == "divide" || f == "negate") {
       e.type = e.args.at(0)->type;
+    } else if (f == "if" || f == "switch") {
+      if (e.args.size() < 2) throw std::runtime_error("if / switch takes at least (condition, value)");
+      e.type = e.args.at(1)->type;
+    } else if (f == "coalesce") {
+      e.type = e.args.at(0)->type;
     } else if (f == "eq" || f == "neq" || f == "lt" || f == "lte" || f == "gt" || f == "gte" || f == "between" ||
                f == "not" || f == "is_null") {
       e.type = kBool;
@@ -273,29 +278,33 @@ struct Evaluator {
         return;
       default: break;
     }
+    if (e.fn == "if" || e.fn == "switch") { switchExpr(e, rows, out); return; }
+    if (e.fn == "coalesce") { coalesce(e, rows, out); return; }
     // default-null call: evaluate inputs, drop rows with a NULL input (Expr.cpp:371-441)
     std::vector<Vec> in(e.args.size());
-    for (size_t k = 0; k < e.args.size(); ++k) eval(*e.args[k], rows, in[k]);
     if (e.fn == "is_null") {
+      eval(*e.args[0], rows, in[0]);
       uint8_t* o = (uint8_t*)out.alloc(b.size, 1);
       rows.forEach([&](int32_t i) { o[i] = in[0].isNullAt(i); });
       return;
     }
+    // evalArgsDefaultNulls: argument k+1 is only evaluated on the rows where arguments 0..k are not NULL
     const Selectivity* active = &rows;
     Selectivity narrowed;
-    bool any_nulls = false;
-    for (auto& v : in) any_nulls |= v.constant ? v.const_null : v.nulls != nullptr;
-    if (any_nulls) {
-      narrowed = rows;
-      uint8_t* on = out.allocNulls(b.size);
-      rows.forEach([&](int32_t i) {
-        bool n = false;
-        for (auto& v : in) n |= v.isNullAt(i);
-        if (n) { narrowed.clear(i); on[i] = 1; }
-      });
-      narrowed.updateBounds();
-      active = &narrowed;
+    uint8_t* on = nullptr;
+    for (size_t k = 0; k < e.args.size(); ++k) {
+      if (!active->hasSelections()) break;
+      eval(*e.args[k], *active, in[k]);
+      const Vec& v = in[k];
+      if (!(v.constant ? v.const_null : v.nulls != nullptr)) continue;
+      if (active == &rows) { narrowed = rows; active = &narrowed; }
+      if (!on) on = out.allocNulls(b.size);
+      bool changed = false;
+      Selectivity pass = narrowed;
+      pass.forEach([&](int32_t i) { if (v.isNullAt(i)) { narrowed.clear(i); on[i] = 1; changed = true; } });
+      if (changed) narrowed.updateBounds();
     }
+    if (!active->hasSelections()) { out.alloc(b.size, widthOf(e.type)); return; }
     const int at = e.args[0]->type;
     if (e.type != kBool) {
       if (e.fn == "negate") {
@@ -321,6 +330,84 @@ struct Evaluator {
     else if (at == kBigint) comparison<int64_t>(e.fn, *active, in[0], in[1], o);
     else if (at == kInt) comparison<int32_t>(e.fn, *active, in[0], in[1], o);
     else comparison<uint8_t>(e.fn, *active, in[0], in[1], o);
+  }
+
+  // Copies the non-null values of `v` on `rows` into out's buffer; NULL rows set out's null byte.
+  void copyRows(const Selectivity& rows, const Vec& v, int type, char* o, uint8_t*& on, Vec& out) {
+    rows.forEach([&](int32_t i) {
+      if (v.isNullAt(i)) {
+        if (!on) on = out.allocNulls(b.size);
+        on[i] = 1;
+        return;
+      }
+      if (type == kInt) ((int32_t*)o)[i] = v.at<int32_t>(i);
+      else if (type == kBigint) ((int64_t*)o)[i] = v.at<int64_t>(i);
+      else if (type == kDouble) ((double*)o)[i] = v.at<double>(i);
+      else ((uint8_t*)o)[i] = v.at<uint8_t>(i);
+    });
+  }
+
+  // SwitchExpr::evalSpecialForm (SwitchExpr.cpp:64-160): args = (c1, v1, c2, v2, ..., [else]).  Condition k is
+  // evaluated on the rows no earlier condition took; its THEN clause only on the rows where it is TRUE; the ELSE
+  // clause on what remains (FALSE or NULL everywhere); without ELSE those rows are NULL (:143-156).
+  void switchExpr(const Expr& e, const Selectivity& rows, Vec& out) {
+    char* o = (char*)out.alloc(b.size, widthOf(e.type));
+    uint8_t* on = nullptr;
+    Selectivity remaining = rows;
+    const size_t cases = e.args.size() / 2;
+    for (size_t k = 0; k < cases && remaining.hasSelections(); ++k) {
+      Vec cond;
+      eval(*e.args[2 * k], remaining, cond);
+      Selectivity thenRows = remaining;
+      bool any = false;
+      remaining.forEach([&](int32_t i) {
+        const bool t = !cond.isNullAt(i) && cond.at<uint8_t>(i);
+        if (t) any = true; else thenRows.clear(i);
+      });
+      if (!any) continue;
+      thenRows.updateBounds();
+      Vec v;
+      eval(*e.args[2 * k + 1], thenRows, v);
+      copyRows(thenRows, v, e.type, o, on, out);
+      thenRows.forEach([&](int32_t i) { remaining.clear(i); });
+      remaining.updateBounds();
+    }
+    if (!remaining.hasSelections()) return;
+    if (e.args.size() % 2 == 1) {
+      Vec v;
+      eval(*e.args.back(), remaining, v);
+      copyRows(remaining, v, e.type, o, on, out);
+    } else {
+      if (!on) on = out.allocNulls(b.size);
+      remaining.forEach([&](int32_t i) { on[i] = 1; });
+    }
+  }
+
+  // CoalesceExpr::evalSpecialForm (CoalesceExpr.cpp:39-81): argument k is evaluated on the rows that
+  // are still NULL after arguments 0..k-1.
+  void coalesce(const Expr& e, const Selectivity& rows, Vec& out) {
+    char* o = (char*)out.alloc(b.size, widthOf(e.type));
+    uint8_t* on = nullptr;
+    Selectivity active = rows;
+    for (auto& arg : e.args) {
+      if (!active.hasSelections()) break;
+      Vec v;
+      eval(*arg, active, v);
+      uint8_t* ignored = nullptr;
+      bool any = false;
+      Selectivity found = active;
+      active.forEach([&](int32_t i) { if (v.isNullAt(i)) found.clear(i); else any = true; });
+      if (!any) continue;
+      found.updateBounds();
+      Vec sink; // null marks are not taken from this pass
+      copyRows(found, v, e.type, o, ignored, sink);
+      found.forEach([&](int32_t i) { active.clear(i); });
+      active.updateBounds();
+    }
+    if (active.hasSelections()) {
+      on = out.allocNulls(b.size);
+      active.forEach([&](int32_t i) { on[i] = 1; });
+    }
   }
 
   // ConjunctExpr::evalSpecialForm (ConjunctExpr.cpp:96-174): each conjunct is evaluated only on the

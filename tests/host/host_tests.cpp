@@ -148,6 +148,14 @@ static void cpuTests() {
   EXPECT(parse::parseExpr("l_quantity is not null or not (l_tax <> 0.0)", row)->toString() == "or(not(is_null(l_quantity)),not(neq(l_tax,0.000000)))");
   EXPECT(parse::parseExpr("l_shipdate in (8766, 9131) and l_quantity not in (0.5)", row)->toString() ==
          "and(or(eq(l_shipdate,8766),eq(l_shipdate,9131)),not(eq(l_quantity,0.500000)))");
+  // CASE -> if / switch, the names DuckParser.cpp gives them; literal branches take the column branch's type
+  EXPECT(parse::parseExpr("case when l_tax < 0.03 then l_extendedprice else 0 end", row)->toString() == "if(lt(l_tax,0.030000),l_extendedprice,0.000000)");
+  EXPECT(parse::parseExpr("case when l_tax < 0.03 then 1 when l_tax < 0.06 then l_orderkey end", row)->toString() ==
+         "switch(lt(l_tax,0.030000),1,lt(l_tax,0.060000),l_orderkey)");
+  EXPECT(parse::parseExpr("coalesce(l_quantity, 0)", row)->type()->kind() == TypeKind::DOUBLE);
+  EXPECT(parse::parseExpr("if(l_shipdate > 9131, l_orderkey)", row)->type()->kind() == TypeKind::BIGINT);
+  EXPECT_THROW(parse::parseExpr("if(l_orderkey, 1, 2)", row), VeloxUserError);                 // condition must be BOOLEAN
+  EXPECT_THROW(parse::parseExpr("case when l_tax < 0.03 then l_orderkey else l_tax end", row), VeloxUserError); // no implicit casts
   EXPECT(parse::parseExpr("1 + 2 * 3", row)->toString() == "7"); // constant folding (ExprCompiler.cpp:302-335)
   EXPECT_THROW(parse::parseExpr("no_such_column > 1", row), VeloxUserError);
   EXPECT_THROW(parse::parseExpr("l_quantity > l_orderkey", row), VeloxUserError); // no implicit casts between columns
@@ -310,6 +318,18 @@ static void gpuTests() {
     for (size_t i = 0; i < in[0]->size(); ++i) wantIn += t.tax[i] == 0.02 || t.tax[i] == 0.05;
     for (auto& o : inl) gotIn += o->size();
     EXPECT(gotIn == wantIn && wantIn > 0);
+    // CASE WHEN / if / coalesce: special forms evaluated per row on the device (SwitchExpr.cpp, CoalesceExpr.cpp)
+    auto cs = exec::runPlan(PlanBuilder().values({in[0]}).project({"case when l_tax < 0.03 then l_extendedprice when l_tax < 0.06 then l_extendedprice * 0.5 else 0.0 end as x",
+                                                                   "if(l_shipdate > 9131, l_orderkey) as k", "coalesce(if(l_tax > 0.04, l_quantity), -1.0) as q"}).planNode());
+    bool caseOk = cs.size() == 1 && cs[0]->size() == in[0]->size();
+    for (size_t i = 0; caseOk && i < in[0]->size(); ++i) {
+      const double wx = t.tax[i] < 0.03 ? t.extendedprice[i] : t.tax[i] < 0.06 ? t.extendedprice[i] * 0.5 : 0.0;
+      caseOk = caseOk && at<double>(cs[0]->childAt(0), i) == wx;
+      const bool hasK = t.shipdate[i] > 9131;
+      caseOk = caseOk && isNullAt(cs[0]->childAt(1), i) == !hasK && (!hasK || at<int64_t>(cs[0]->childAt(1), i) == t.orderkey[i]);
+      caseOk = caseOk && !isNullAt(cs[0]->childAt(2), i) && at<double>(cs[0]->childAt(2), i) == (t.tax[i] > 0.04 ? t.quantity[i] : -1.0);
+    }
+    EXPECT(caseOk);
     // no row passes -> no output vector at all (Driver.cpp:550-556)
     EXPECT(exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").planNode()).empty());
   }
@@ -326,6 +346,30 @@ static void gpuTests() {
     const auto& w = want.groups.begin()->second;
     EXPECT(at<int64_t>(out[0]->childAt(1), 0) == w[1].first);
     EXPECT(close(at<double>(out[0]->childAt(0), 0), bitsToDouble(w[0].first)));
+  }
+
+  section("sum(CASE WHEN ...) grouped (TPC-H Q12 / Q14 shape) vs the oracle's SwitchExpr");
+  {
+    const char* promo = "case when l_tax < 0.03 then l_extendedprice * (1.0 - l_discount) else 0.0 end";
+    const char* high = "case when l_shipdate < 9131 then 1 when l_shipdate < 10000 then 2 else 0 end";
+    auto plan = PlanBuilder().values(in).project({"l_linestatus", std::string(promo) + " as promo", std::string(high) + " as high"})
+                    .singleAggregation({"l_linestatus"}, {"sum(promo) as p", "sum(high) as h", "count(*) as n"}).planNode();
+    auto out = exec::runPlan(plan);
+    auto want = runOracle(t, nullptr, {"l_linestatus", promo, high}, {0}, {{0, 1}, {1, 2}, {2, -1}}, row);
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) {
+      for (size_t i = 0; i < o->size(); ++i, ++groups) {
+        const std::string key = at<std::string>(o->childAt(0), i);
+        const int64_t id = key == "F" ? 0 : 1;
+        auto it = want.groups.find({id});
+        ok = ok && it != want.groups.end();
+        if (!ok) break;
+        ok = ok && close(at<double>(o->childAt(1), i), bitsToDouble(it->second[0].first)) && at<int64_t>(o->childAt(2), i) == it->second[1].first &&
+             at<int64_t>(o->childAt(3), i) == it->second[2].first;
+      }
+    }
+    EXPECT(ok && groups == want.groups.size() && groups == 2);
   }
 
   section("Q1: VARCHAR keys, sum / avg / count, fused and unfused (TpchQueryBuilder.cpp:189-244)");

@@ -224,3 +224,90 @@ def test_all_pass_all_fail(engine):
         prog = engine.Program(ex.call("gt", ex.col(0, I32), ex.lit(lo, I32)), [ex.col(0, I32)])
         res = engine.filter_project(prog, [engine.flat_column(I32, a)], n)
         assert res.num_selected == expect
+
+
+def _switch_inputs(n=4099, seed=3):
+    rng = np.random.default_rng(seed)
+    a = rng.integers(-50, 50, n).astype(np.int64)
+    b = rng.integers(-3, 4, n).astype(np.int64)          # many zeros: a / b raises where b == 0
+    d = np.round(rng.normal(0, 10, n), 2)
+    a_nn, b_nn, d_nn = rng.random(n) > 0.2, rng.random(n) > 0.2, rng.random(n) > 0.3
+    return n, [(I64, a, a_nn), (I64, b, b_nn), (D, d, d_nn)]
+
+
+def test_if_takes_branch_per_row_and_drops_untaken_errors(engine):
+    """if(b <> 0, a / b, -1): the division error on b == 0 is in the branch those rows do not take
+    (SwitchExpr.cpp:64-160); a NULL condition takes ELSE; no ELSE gives NULL."""
+    n, spec = _switch_inputs()
+    a, b, d = ex.col(0, I64), ex.col(1, I64), ex.col(2, D)
+    nz = ex.call("neq", b, ex.lit(0, I64))
+    outs = [ex.call("if", nz, ex.call("divide", a, b), ex.lit(-1, I64)),
+            ex.call("if", nz, ex.call("divide", a, b)),                                  # no ELSE
+            ex.call("if", ex.call("gt", d, ex.lit(0.0, D)), d, ex.call("negate", d)),      # abs()
+            ex.call("if", ex.call("is_null", a), ex.lit(0, I64), a),
+            ex.call("if", ex.call("lt", a, b), ex.lit(1.5, D), ex.lit(-2.5, D))]           # two literals
+    res = check(engine, None, outs, spec, n)
+    # the same division outside the if raises
+    with pytest.raises(abi.VgpuError):
+        cols = [engine.flat_column(t, v, nn) for t, v, nn in spec]
+        engine.filter_project(engine.Program(None, [ex.call("divide", a, b)], n_columns=3), cols, n)
+    # an error in the condition itself is kept
+    with pytest.raises(abi.VgpuError):
+        bad = ex.call("if", ex.call("gt", ex.call("divide", a, b), ex.lit(0, I64)), a, b)
+        engine.filter_project(engine.Program(None, [bad], n_columns=3), cols, n)
+    # ... unless a conjunct decides the row first
+    guarded = ex.call("if", ex.call("and", nz, ex.call("gt", ex.call("divide", a, b), ex.lit(0, I64))), a, b)
+    check(engine, None, [guarded], spec, n)
+    assert res.num_selected == n
+
+
+def test_case_when_chain_and_coalesce(engine):
+    n, spec = _switch_inputs(seed=11)
+    a, b, d = ex.col(0, I64), ex.col(1, I64), ex.col(2, D)
+    case = ex.switch([(ex.call("lt", a, ex.lit(-10, I64)), ex.lit(0, I64)),
+                      (ex.call("lt", a, ex.lit(10, I64)), ex.call("plus", a, ex.lit(100, I64))),
+                      (ex.call("eq", b, ex.lit(0, I64)), b)], default=ex.call("multiply", a, b))
+    case_no_else = ex.switch([(ex.call("gt", d, ex.lit(5.0, D)), d), (ex.call("lt", d, ex.lit(-5.0, D)), ex.lit(0.0, D))])
+    outs = [case, case_no_else,
+            ex.call("coalesce", a, b), ex.call("coalesce", a, b, ex.lit(7, I64)),
+            ex.call("coalesce", d, ex.lit(0.0, D)),
+            # b's error (division by zero) only counts where a is NULL
+            ex.call("coalesce", a, ex.call("if", ex.call("neq", b, ex.lit(0, I64)), ex.call("divide", ex.lit(100, I64), b), ex.lit(0, I64)))]
+    filt = ex.call("gte", ex.call("coalesce", d, ex.lit(-1.0, D)), ex.lit(-1.0, D))
+    check(engine, filt, outs, spec, n)
+
+
+def test_null_argument_hides_later_argument_error(engine):
+    """Default-null calls evaluate arguments left to right and drop a row at its first NULL argument, so an
+    error in a LATER argument does not surface on it (Expr.cpp:371-441 evalArgsDefaultNulls)."""
+    a = np.array([1, 2, 3, 4], dtype=np.int64); a_nn = np.array([False, True, False, True])
+    b = np.array([0, 1, 0, 2], dtype=np.int64)
+    x, y = ex.col(0, I64), ex.col(1, I64)
+    spec = [(I64, a, a_nn), (I64, b, None)]
+    e = ex.call("plus", x, ex.call("divide", ex.lit(10, I64), y))   # rows 0 and 2: x NULL, 10 / 0
+    res = check(engine, None, [e, ex.call("lt", x, ex.call("divide", ex.lit(10, I64), y))], spec, 4)
+    assert res.num_selected == 4
+    # with the error in the FIRST argument the row raises although the second is NULL
+    with pytest.raises(abi.VgpuError):
+        cols = [engine.flat_column(t, v, nn) for t, v, nn in spec]
+        engine.filter_project(engine.Program(None, [ex.call("plus", ex.call("divide", ex.lit(10, I64), y), x)], n_columns=2), cols, 4)
+
+
+def test_sum_of_case_when_aggregation(engine):
+    """TPC-H Q12 / Q14 shape: sum(case when ... then x else 0 end) grouped by a small key."""
+    rng = np.random.default_rng(5)
+    n = 200_003
+    k = rng.integers(0, 7, n).astype(np.int32)
+    pri = rng.integers(0, 5, n).astype(np.int32)
+    ep = np.round(rng.uniform(900, 100000, n), 2)
+    disc = rng.integers(0, 11, n) / 100.0
+    import importlib
+    plan = importlib.import_module("velox-1_b200.aot_plans").case_when()   # the shape build() prebuilds a kernel for
+    outs, keys, accs = plan["outputs"], plan["keys"], plan["accs"]
+    cols = [engine.flat_column(I32, k), engine.flat_column(I32, pri), engine.flat_column(D, ep), engine.flat_column(D, disc)]
+    prog = engine.Program(None, outs)
+    agg = engine.Aggregation(abi.AGG_ARRAY, keys, accs)
+    agg.add_input(prog, cols, n)
+    got = H.decode_rows(agg.extract(), keys, accs, [o.type for o in outs], abi.AGG_ARRAY)
+    want = H.run_oracle_agg(None, outs, [(k, None), (pri, None), (ep, None), (disc, None)], n, keys, accs)
+    H.assert_groups_equal(got, want, accs)

@@ -16,6 +16,7 @@ FLAT, DICTIONARY, CONSTANT = range(3)
 OPND_NONE, OPND_ACC, OPND_SLOT, OPND_COL, OPND_IMM, OPND_NULL = range(6)
 OP_NOP, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG, OP_MOD = range(7)
 OP_CAST, OP_MOV = 8, 9
+OP_SELECT, OP_COALESCE = 10, 11
 OP_EQ, OP_NE, OP_LT, OP_LE, OP_GT, OP_GE, OP_BETWEEN = range(16, 23)
 OP_AND, OP_OR, OP_NOT, OP_IS_NULL = range(24, 28)
 ACC_SUM_F64, ACC_SUM_I64, ACC_COUNT, ACC_MIN, ACC_MAX = range(5)

@@ -96,8 +96,23 @@ def c4():
                 keys=keys, accs=accs)
 
 
+def case_when():
+    """TPC-H Q12 / Q14 shape: sums of CASE WHEN expressions grouped by a small key (special forms SELECT / COALESCE)."""
+    kk, p, e, dd = ex.col(0, I32), ex.col(1, I32), ex.col(2, D), ex.col(3, D)
+    rev = ex.call("multiply", e, ex.call("minus", ex.lit(1.0, D), dd))
+    high = ex.call("if", ex.call("or", ex.call("eq", p, ex.lit(0, I32)), ex.call("eq", p, ex.lit(1, I32))),
+                   ex.lit(1, I64), ex.lit(0, I64))
+    promo = ex.call("if", ex.call("lt", p, ex.lit(2, I32)), rev, ex.lit(0.0, D))
+    outs = [kk, high, promo, rev, ex.call("coalesce", ex.call("if", ex.call("gt", dd, ex.lit(0.05, D)), e), ex.lit(0.0, D))]
+    keys = [(0, 0, 0, 6)]
+    accs = [(abi.ACC_SUM_I64, 1), (abi.ACC_SUM_F64, 2), (abi.ACC_SUM_F64, 3), (abi.ACC_SUM_F64, 4), (abi.ACC_COUNT, -1)]
+    cols = [_fake_column(t) for t in (I32, I32, D, D)]
+    return dict(name="N3 sum(case when)", filter=None, outputs=outs, cols=cols, mode=abi.AGG_ARRAY, keys=keys, accs=accs)
+
+
 def plans():
-    return [q1(), q6_global(), q6_filter_project(False), q6_filter_project(True), orderkey(False), orderkey(True), c4()]
+    return [q1(), q6_global(), q6_filter_project(False), q6_filter_project(True), orderkey(False), orderkey(True), c4(),
+            case_when()]
 
 
 def generate(plan):

@@ -205,7 +205,7 @@ int vgpu_program_create(const vgpu_program_desc* desc, vgpu_program_t* out) {
     const vgpu_op& op = desc->ops[i];
     const int oc = op.opcode;
     const bool is_bool = oc >= VGPU_OP_EQ && oc <= VGPU_OP_IS_NULL;
-    const bool known = (oc >= VGPU_OP_ADD && oc <= VGPU_OP_MOD) || oc == VGPU_OP_CAST || oc == VGPU_OP_MOV ||
+    const bool known = (oc >= VGPU_OP_ADD && oc <= VGPU_OP_MOD) || oc == VGPU_OP_CAST || oc == VGPU_OP_MOV || oc == VGPU_OP_SELECT || oc == VGPU_OP_COALESCE ||
         (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) || (oc >= VGPU_OP_AND && oc <= VGPU_OP_IS_NULL);
     if (!known) { set_error("op %d: unknown opcode %d", i, oc); return VGPU_ERR_INVALID; }
     const bool unary = oc == VGPU_OP_NEG || oc == VGPU_OP_CAST || oc == VGPU_OP_MOV || oc == VGPU_OP_NOT || oc == VGPU_OP_IS_NULL;
@@ -213,13 +213,23 @@ int vgpu_program_create(const vgpu_program_desc* desc, vgpu_program_t* out) {
     if (rc) return rc;
     rc = validate_operand(op.b, unary, desc->n_columns, max_slot, max_bslot, max_col, "b", i);
     if (rc) return rc;
-    rc = validate_operand(op.c, oc != VGPU_OP_BETWEEN, desc->n_columns, max_slot, max_bslot, max_col, "c", i);
+    rc = validate_operand(op.c, oc != VGPU_OP_BETWEEN && oc != VGPU_OP_SELECT, desc->n_columns, max_slot, max_bslot, max_col, "c", i);
     if (rc) return rc;
+    if (oc == VGPU_OP_SELECT || oc == VGPU_OP_COALESCE) {
+      const vgpu_operand& first = oc == VGPU_OP_SELECT ? op.b : op.a;
+      const vgpu_operand& second = oc == VGPU_OP_SELECT ? op.c : op.b;
+      if (oc == VGPU_OP_SELECT && op.a.type != VGPU_BOOLEAN) { set_error("op %d: SELECT condition must be BOOLEAN", i); return VGPU_ERR_INVALID; }
+      if (oc == VGPU_OP_SELECT && (op.a.kind == VGPU_OPND_IMM || op.a.kind == VGPU_OPND_NULL)) { set_error("op %d: constant SELECT condition; fold it on the host", i); return VGPU_ERR_INVALID; }
+      if (op.type == VGPU_BOOLEAN) { set_error("op %d: BOOLEAN-valued SELECT / COALESCE is not supported", i); return VGPU_ERR_UNSUPPORTED; }
+      if (first.type != op.type || second.type != op.type) { set_error("op %d: branch types differ from op type %d (insert a CAST)", i, op.type); return VGPU_ERR_INVALID; }
+    }
     for (const vgpu_operand* o : {&op.a, &op.b, &op.c}) {
       if (o->kind == VGPU_OPND_ACC && !(o->type == VGPU_BOOLEAN ? have_bacc : have_acc)) { set_error("op %d reads ACC before any op wrote it", i); return VGPU_ERR_INVALID; }
     }
     if (oc >= VGPU_OP_AND && oc <= VGPU_OP_NOT) {
       if (op.a.type != VGPU_BOOLEAN || (oc != VGPU_OP_NOT && op.b.type != VGPU_BOOLEAN)) { set_error("op %d: boolean op over non-boolean operands", i); return VGPU_ERR_INVALID; }
+    } else if (oc == VGPU_OP_SELECT || oc == VGPU_OP_COALESCE) {
+      // checked above
     } else if (!is_bool || (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN)) {
       if (oc != VGPU_OP_CAST && op.type != VGPU_BOOLEAN && oc != VGPU_OP_MOV) {
         for (const vgpu_operand* o : {&op.a, &op.b, &op.c}) {

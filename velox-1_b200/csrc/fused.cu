@@ -164,7 +164,7 @@ struct Gen {
         out("        const V a = %s;\n", val(op.a, imm).c_str());
         if (oc == VGPU_OP_NEG) out("        const V b = {0ull, false, false};\n");
         else out("        const V b = %s;\n", val(op.b, imm).c_str());
-        out("        V r; r.n = a.n || b.n; r.e = a.e || b.e;\n");
+        out("        V r; r.n = a.n || b.n; r.e = a.e || (!a.n && b.e);\n");
         out("        const u32 er = arith(%d, %d, a.v, b.v, r.v);\n", oc, op.type);
         out("        if (er && !r.n && valid) { r.e = true; ec |= er; }\n");
         out("        acc = r;\n");
@@ -179,17 +179,27 @@ struct Gen {
       } else if (oc == VGPU_OP_MOV) {
         out("        acc = %s;\n", val(op.a, imm).c_str());
         if (op.dst_slot >= 0) out("        s%d = acc;\n", op.dst_slot);
+      } else if (oc == VGPU_OP_SELECT) {
+        out("        const B a = %s; const V b = %s, c = %s;\n", bval(op.a, imm).c_str(), val(op.b, imm).c_str(), val(op.c, imm2).c_str());
+        out("        V r = (a.v && !a.n) ? b : c; if (a.e) r = V{0ull, false, true};\n");
+        out("        acc = r;\n");
+        if (op.dst_slot >= 0) out("        s%d = r;\n", op.dst_slot);
+      } else if (oc == VGPU_OP_COALESCE) {
+        out("        const V a = %s, b = %s;\n", val(op.a, imm).c_str(), val(op.b, imm).c_str());
+        out("        const V r = (a.e || !a.n) ? a : b;\n");
+        out("        acc = r;\n");
+        if (op.dst_slot >= 0) out("        s%d = r;\n", op.dst_slot);
       } else if (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) {
         if (op.type == VGPU_BOOLEAN) {
           out("        const B a = %s, b = %s;\n", bval(op.a, imm).c_str(), bval(op.b, imm).c_str());
-          out("        B r; r.n = a.n || b.n; r.e = a.e || b.e; r.v = (a.v %s b.v) && !r.n;\n", oc == VGPU_OP_EQ ? "==" : "!=");
+          out("        B r; r.n = a.n || b.n; r.e = a.e || (!a.n && b.e); r.v = (a.v %s b.v) && !r.n;\n", oc == VGPU_OP_EQ ? "==" : "!=");
         } else if (oc == VGPU_OP_BETWEEN) {
           out("        const V a = %s, b = %s, c = %s;\n", val(op.a, imm).c_str(), val(op.b, imm).c_str(), val(op.c, imm2).c_str());
-          out("        B r; r.n = a.n || b.n || c.n; r.e = a.e || b.e || c.e;\n");
+          out("        B r; r.n = a.n || b.n || c.n; r.e = a.e || (!a.n && (b.e || (!b.n && c.e)));\n");
           out("        r.v = compare(%d, %d, a.v, b.v) && compare(%d, %d, a.v, c.v) && !r.n;\n", VGPU_OP_GE, op.type, VGPU_OP_LE, op.type);
         } else {
           out("        const V a = %s, b = %s;\n", val(op.a, imm).c_str(), val(op.b, imm).c_str());
-          out("        B r; r.n = a.n || b.n; r.e = a.e || b.e; r.v = compare(%d, %d, a.v, b.v) && !r.n;\n", oc, op.type);
+          out("        B r; r.n = a.n || b.n; r.e = a.e || (!a.n && b.e); r.v = compare(%d, %d, a.v, b.v) && !r.n;\n", oc, op.type);
         }
         out("        bacc = r;\n");
         if (op.dst_slot >= 0) out("        bs%d = r;\n", op.dst_slot);

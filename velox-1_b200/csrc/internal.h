@@ -143,6 +143,7 @@ enum Handler : uint8_t {
   H_CAST,    // acc = cast(x) to `type`
   H_CMP,     // bacc = combine(bacc, x (sub) y [, z for BETWEEN])
   H_BOOL,    // bacc = x AND/OR y, NOT x, IS_NULL x
+  H_SELECT,  // acc = if(x, y, z) (sub = VGPU_OP_SELECT) or coalesce(x, y) (sub = VGPU_OP_COALESCE)
   H_FILTER,  // pass = x is TRUE
   H_KEY,     // fold value x into the group number / normalized key (dst = key index)
   H_KEYEND,  // ARRAY: table offsets + in-thread duplicate plan; HASH: find-or-insert

@@ -748,7 +748,7 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
           Val b;
           fetch(cx, op.y, b);
           r.n = a.n | b.n;
-          r.e = a.e | b.e;
+          r.e = a.e | (~a.n & b.e); // a row whose first argument is NULL never evaluates the second (Expr.cpp:371-441)
           if (type == VGPU_DOUBLE && oc <= VGPU_OP_MUL) {
             // hot path of Q1/Q6: plain IEEE double ops, dispatch hoisted out of the row loop
             if (oc == VGPU_OP_MUL) {
@@ -802,7 +802,7 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
           const uint32_t x = a.v ^ b.v;
           r.v = (oc == VGPU_OP_EQ ? ~x : x) & 0xFu;
           r.n = a.n | b.n;
-          r.e = a.e | b.e;
+          r.e = a.e | (~a.n & b.e); // a row whose first argument is NULL never evaluates the second (Expr.cpp:371-441)
         } else if (op.x.kind == XK_COL4I && op.y.kind == XK_IMM && (oc != VGPU_OP_BETWEEN || op.z.kind == XK_IMM)) {
           // INTEGER / DATE column against literals: 32-bit compares straight off the staged tile
           const uint2* s = reinterpret_cast<const uint2*>(cx.stage + op.x.off);
@@ -818,12 +818,12 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
           fetch(cx, op.x, a);
           fetch(cx, op.y, b);
           r.n = a.n | b.n;
-          r.e = a.e | b.e;
+          r.e = a.e | (~a.n & b.e); // a row whose first argument is NULL never evaluates the second (Expr.cpp:371-441)
           if (oc == VGPU_OP_BETWEEN) {
             Val c;
             fetch(cx, op.z, c);
+            r.e |= ~r.n & c.e;
             r.n |= c.n;
-            r.e |= c.e;
             r.v = cmp4(VGPU_OP_GE, op.type, a.v, b.v) & cmp4(VGPU_OP_LE, op.type, a.v, c.v);
           } else {
             r.v = cmp4(oc, op.type, a.v, b.v);
@@ -863,6 +863,29 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
         }
         cx.bacc = r;
         if (op.flags & MF_STORE) reinterpret_cast<uint32_t*>(cx.smem + op.dst)[threadIdx.x] = r.v | (r.n << 8) | (r.e << 16);
+        break;
+      }
+      case H_SELECT: {
+        Val b, c, r;
+        uint32_t take; // rows that read the first value
+        if (op.sub == VGPU_OP_SELECT) {
+          BoolVal a;
+          fetchb(cx, op.x, a);
+          fetch(cx, op.y, b);
+          fetch(cx, op.z, c);
+          take = a.v & ~a.n & ~a.e & 0xFu;
+          r.e = (a.e | (take & b.e) | (~take & ~a.e & c.e)) & 0xFu;
+        } else {
+          fetch(cx, op.x, b);
+          fetch(cx, op.y, c);
+          take = (~b.n | b.e) & 0xFu;
+          r.e = (b.e | (~take & c.e)) & 0xFu;
+        }
+        r.n = ((take & b.n) | (~take & c.n)) & ~r.e & 0xFu;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) r.v[j] = ((take >> j) & 1u) ? b.v[j] : c.v[j];
+        cx.acc = r;
+        if (op.flags & MF_STORE) store_slot(cx, op, r);
         break;
       }
       case H_FILTER: {
@@ -1536,6 +1559,12 @@ struct Lowerer {
       m = emit(H_LD);
       m->type = op.type;
       m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+    } else if (oc == VGPU_OP_SELECT || oc == VGPU_OP_COALESCE) {
+      m = emit(H_SELECT);
+      m->sub = (uint8_t)oc; m->type = op.type;
+      m->x = opnd(op.a, (uint64_t)op.imm.i, 0);
+      m->y = opnd(op.b, (uint64_t)op.imm.i, 1);
+      if (oc == VGPU_OP_SELECT) m->z = opnd(op.c, (uint64_t)op.imm2.i, 2);
     } else if (oc >= VGPU_OP_EQ && oc <= VGPU_OP_BETWEEN) {
       m = emit(H_CMP);
       m->sub = (uint8_t)oc; m->type = op.type;

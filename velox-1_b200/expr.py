@@ -81,7 +81,26 @@ def call(fn, *args):
         return Call(abi.BOOLEAN, fn, tuple(args))
     if fn == "is_null":
         return Call(abi.BOOLEAN, fn, tuple(args))
+    if fn == "if":
+        # if(condition, then[, else]) — SwitchExpr.cpp:64-160; no ELSE = NULL for the remaining rows
+        cond, then = args[0], args[1]
+        other = args[2] if len(args) > 2 else null(then.type)
+        assert cond.type == abi.BOOLEAN and then.type == other.type, "if: condition must be boolean, branches of one type"
+        assert then.type != abi.BOOLEAN, "boolean-valued if is not supported on the device"
+        return Call(then.type, fn, (cond, then, other))
+    if fn == "coalesce":
+        assert len(args) >= 2 and all(a.type == args[0].type for a in args) and args[0].type != abi.BOOLEAN
+        return Call(args[0].type, fn, tuple(args))
     raise ValueError(f"unknown function {fn}")
+
+
+def switch(cases, default=None):
+    """CASE WHEN c1 THEN v1 WHEN c2 THEN v2 ... [ELSE default] END as nested if (SwitchExpr.cpp evaluates the
+    conditions in order on the rows no earlier condition took — exactly what the nesting does)."""
+    out = default if default is not None else null(cases[0][1].type)
+    for cond, value in reversed(cases):
+        out = call("if", cond, value, out)
+    return out
 
 
 def in_list(x, values):
@@ -224,6 +243,20 @@ class _Lowerer:
             res = self._emit(abi.OP_NOT, abi.BOOLEAN, ops[0], imm=imms[0])
         elif fn == "is_null":
             res = self._emit(abi.OP_IS_NULL, abi.BOOLEAN, ops[0], imm=imms[0])
+        elif fn == "if":
+            if imms[0] is not None or ops[0].kind == abi.OPND_NULL:
+                raise ValueError("if: constant condition; fold before lowering")
+            res = self._emit(abi.OP_SELECT, e.type, ops[0], ops[1], ops[2], imm=imms[1], imm2=imms[2])
+        elif fn == "coalesce":
+            res = None
+            # coalesce(a, b, c) = coalesce(a, coalesce(b, c)); arguments were evaluated left to right above
+            # and stay in slots / leaves, so fold from the right
+            acc_o, acc_imm = ops[-1], imms[-1]
+            for k in range(len(ops) - 2, -1, -1):
+                if imms[k] is not None:
+                    raise ValueError("coalesce: literal before the last argument; fold before lowering")
+                res = self._emit(abi.OP_COALESCE, e.type, ops[k], acc_o, imm=acc_imm)
+                acc_o, acc_imm = res, None
         else:
             raise ValueError(fn)
         for o in ops:

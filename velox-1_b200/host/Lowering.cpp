@@ -161,6 +161,26 @@ class Lowerer {
       res = emit(VGPU_OP_NOT, VGPU_BOOLEAN, args[0].opnd, none, none, &args[0], nullptr);
     } else if (fn == "is_null") {
       res = emit(VGPU_OP_IS_NULL, VGPU_BOOLEAN, args[0].opnd, none, none, &args[0], nullptr);
+    } else if (fn == "if") { // switch arrives here as nested ifs (desugarSwitch)
+      VB_CHECK(args.size() == 2 || args.size() == 3, "if takes (condition, then[, else])");
+      VB_CHECK(!args[0].hasImm && args[0].opnd.kind != VGPU_OPND_NULL, "if over a constant condition must be folded before lowering");
+      if (isBool(e)) throw VeloxUserError("BOOLEAN-valued if / switch is not supported on the device");
+      const int t = deviceType(e->type());
+      const vgpu_operand other = args.size() > 2 ? args[2].opnd : opnd(VGPU_OPND_NULL, t, 0);
+      res = emit(VGPU_OP_SELECT, t, args[0].opnd, args[1].opnd, other, &args[1], args.size() > 2 ? &args[2] : nullptr);
+    } else if (fn == "coalesce") {
+      // coalesce(a, b, c) = coalesce(a, coalesce(b, c)): the arguments are already evaluated (slots / leaves),
+      // the fold runs from the right with the running value in the accumulator
+      if (isBool(e)) throw VeloxUserError("BOOLEAN-valued coalesce is not supported on the device");
+      const int t = deviceType(e->type());
+      vgpu_operand running = args.back().opnd;
+      const Value* runningImm = &args.back();
+      for (int k = (int)args.size() - 2; k >= 0; --k) {
+        VB_CHECK(!args[k].hasImm, "coalesce with a literal before its last argument must be folded before lowering");
+        running = emit(VGPU_OP_COALESCE, t, args[k].opnd, running, none, runningImm, nullptr);
+        runningImm = nullptr;
+      }
+      res = running;
     } else {
       throw VeloxUserError("Scalar function is not supported on the device: " + fn);
     }
@@ -199,8 +219,31 @@ class Lowerer {
 
 } // namespace
 
-LoweredProgram lowerExpressions(const TypedExprPtr& filter, const std::vector<TypedExprPtr>& outputs) {
+// switch(c1, v1, c2, v2, ..., [else]) -> if(c1, v1, if(c2, v2, ... else)): SwitchExpr.cpp evaluates condition k on
+// the rows no earlier condition took, which is what the nesting does.  Applied to the whole tree before lowering.
+static TypedExprPtr desugarSwitch(const TypedExprPtr& e) {
+  if (e->kind() != ITypedExpr::Kind::kCall && e->kind() != ITypedExpr::Kind::kCast) return e;
+  std::vector<TypedExprPtr> in;
+  bool changed = false;
+  for (auto& x : e->inputs()) { in.push_back(desugarSwitch(x)); changed = changed || in.back() != x; }
+  if (e->kind() == ITypedExpr::Kind::kCast) return changed ? std::make_shared<CastTypedExpr>(e->type(), in[0]) : e;
+  const auto& name = static_cast<const CallTypedExpr*>(e.get())->name();
+  if (name != "switch") return changed ? std::make_shared<CallTypedExpr>(e->type(), std::move(in), name) : e;
+  VB_USER_CHECK(in.size() >= 2, "switch takes at least a condition and a value");
+  TypedExprPtr tail = in.size() % 2 == 1 ? in.back() : nullptr;
+  for (int k = (int)(in.size() / 2) - 1; k >= 0; --k) {
+    std::vector<TypedExprPtr> args{in[2 * k], in[2 * k + 1]};
+    if (tail) args.push_back(tail);
+    tail = std::make_shared<CallTypedExpr>(e->type(), std::move(args), "if");
+  }
+  return tail;
+}
+
+LoweredProgram lowerExpressions(const TypedExprPtr& filterIn, const std::vector<TypedExprPtr>& outputsIn) {
   Lowerer lw;
+  const TypedExprPtr filter = filterIn ? desugarSwitch(filterIn) : filterIn;
+  std::vector<TypedExprPtr> outputs;
+  for (auto& o : outputsIn) outputs.push_back(desugarSwitch(o));
   if (filter) {
     VB_USER_CHECK(filter->type()->kind() == TypeKind::BOOLEAN, "Filter expression must be of type BOOLEAN");
     lw.count(filter);

@@ -164,6 +164,44 @@ class Parser {
     return std::make_shared<CallTypedExpr>(BOOLEAN(), std::move(args), fn);
   }
 
+  // Brings the value branches of if / switch / coalesce to one type: literals (and the untyped NULL) take the type
+  // of the first non-literal branch, or of the first typed literal.
+  static void unifyBranches(std::vector<TypedExprPtr*> branches, const std::string& what) {
+    TypePtr t;
+    for (auto* b : branches) if (!asConst(*b)) { t = (*b)->type(); break; }
+    if (!t) for (auto* b : branches) { auto c = asConst(*b); if (c && !c->isNull()) { t = (*b)->type(); break; } }
+    if (!t) t = (*branches[0])->type();
+    for (auto* b : branches) {
+      if (!(*b)->type()->equals(*t)) {
+        VB_USER_CHECK(asConst(*b) != nullptr, "Scalar function signature is not supported: " + what + " with branches of " + t->toString() + " and " + (*b)->type()->toString());
+        *b = asConst(*b)->isNull() ? constNull(t) : makeCast(*b, t);
+      }
+    }
+  }
+  // if(c, a[, b]) / switch(c1, v1, c2, v2, ...[, else]) — the names DuckParser.cpp gives CASE expressions
+  // (special forms of velox/expression/SwitchExpr.cpp).
+  static TypedExprPtr makeSwitch(std::vector<TypedExprPtr> args) {
+    VB_USER_CHECK(args.size() >= 2, "if / switch takes at least a condition and a value");
+    std::vector<TypedExprPtr*> values;
+    for (size_t i = 0; i + 1 < args.size(); i += 2) {
+      VB_USER_CHECK(args[i]->type()->kind() == TypeKind::BOOLEAN, "Condition of if / switch must be BOOLEAN");
+      values.push_back(&args[i + 1]);
+    }
+    if (args.size() % 2 == 1) values.push_back(&args.back());
+    unifyBranches(values, "switch");
+    const TypePtr t = (*values[0])->type();
+    const std::string name = args.size() <= 3 ? "if" : "switch";
+    return std::make_shared<CallTypedExpr>(t, std::move(args), name);
+  }
+  static TypedExprPtr makeCoalesce(std::vector<TypedExprPtr> args) {
+    VB_USER_CHECK(args.size() >= 2, "coalesce takes at least 2 arguments");
+    std::vector<TypedExprPtr*> values;
+    for (auto& a : args) values.push_back(&a);
+    unifyBranches(values, "coalesce");
+    const TypePtr t = args[0]->type();
+    return std::make_shared<CallTypedExpr>(t, std::move(args), "coalesce");
+  }
+
   TypedExprPtr parseOr() {
     auto e = parseAnd();
     while (acceptWord("or")) e = conjunct("or", e, parseAnd());
@@ -283,6 +321,18 @@ class Parser {
       VB_USER_CHECK(accept(")"), "cast: ')' expected");
       return makeCast(e, t);
     }
+    if (acceptWord("case")) { // CASE WHEN c THEN v ... [ELSE v] END
+      std::vector<TypedExprPtr> args;
+      while (acceptWord("when")) {
+        args.push_back(parseOr());
+        VB_USER_CHECK(acceptWord("then"), "case: THEN expected in " + s_);
+        args.push_back(parseOr());
+      }
+      VB_USER_CHECK(!args.empty(), "case: WHEN expected in " + s_);
+      if (acceptWord("else")) args.push_back(parseOr());
+      VB_USER_CHECK(acceptWord("end"), "case: END expected in " + s_);
+      return makeSwitch(std::move(args));
+    }
     if (acceptWord("date")) { // DATE 'yyyy-mm-dd'
       auto lit = parsePrimary();
       return makeCast(lit, DATE());
@@ -298,6 +348,8 @@ class Parser {
       if (name == "negate" && args.size() == 1) return std::make_shared<CallTypedExpr>(args[0]->type(), args, "negate");
       if ((name == "not" || name == "is_null") && args.size() == 1) return std::make_shared<CallTypedExpr>(BOOLEAN(), args, name);
       if (name == "between" && args.size() == 3) return std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{args[0], makeCast(args[1], args[0]->type()), makeCast(args[2], args[0]->type())}, "between");
+      if (name == "if" || name == "switch") return makeSwitch(std::move(args));
+      if (name == "coalesce") return makeCoalesce(std::move(args));
       throw VeloxUserError("Scalar function doesn't exist: " + name);
     }
     const int idx = row_->getChildIdx(name);
