@@ -182,6 +182,17 @@ static void cpuTests() {
     EXPECT(id.ops.empty() && id.filter.kind == VGPU_OPND_NONE && id.outputs[0].kind == VGPU_OPND_COL);
   }
 
+  section("PlanBuilder: aggregation masks");
+  {
+    auto masked = PlanBuilder().values({rv}).project({"l_linestatus", "l_tax < 0.03 as m", "l_extendedprice"})
+                      .partialAggregation({"l_linestatus"}, {"sum(l_extendedprice)", "count(*)"}, {"m", ""}).finalAggregation().planNode();
+    auto fin = std::dynamic_pointer_cast<const AggregationNode>(masked);
+    auto par = std::dynamic_pointer_cast<const AggregationNode>(masked->sources()[0]);
+    EXPECT(par && par->aggregates()[0].mask && !par->aggregates()[1].mask && fin && !fin->aggregates()[0].mask); // masks apply to raw input only
+    EXPECT_THROW(PlanBuilder().values({rv}).partialAggregation({}, {"count(*)"}, {"l_tax"}), VeloxUserError);      // mask must be BOOLEAN
+    EXPECT_THROW(PlanBuilder().values({rv}).partialAggregation({}, {"count(*)", "sum(l_tax)"}, {"l_tax"}), VeloxUserError);
+  }
+
   section("PlanBuilder: node types of partial / final aggregation (Aggregate.h:35-41)");
   {
     auto plan = PlanBuilder().values({rv}).filter("l_quantity < 0.3").project({"l_returnflag", "l_quantity", "l_extendedprice * l_discount as rev"})
@@ -401,6 +412,26 @@ static void gpuTests() {
       ok = ok && at<int64_t>(o->childAt(9), g) == w[10].first;
     }
     EXPECT(ok && groups == want.groups.size() && groups == 6);
+    { // aggregation masks (core::AggregationNode::aggregateMasks, AggregationMasks.cpp): only rows whose mask is TRUE feed
+      // the aggregate; fused the mask is an expression, unfused a BOOLEAN column produced by the FilterProject below
+      auto mplan = PlanBuilder().values(in).project({"l_linestatus", "l_tax < 0.03 as m", "l_extendedprice", "l_shipdate > 9131 as late"})
+                       .singleAggregation({"l_linestatus"}, {"sum(l_extendedprice) as s", "count(*) as n", "min(l_extendedprice) as lo", "count(*) as all_rows"},
+                                          {"m", "late", "m", ""}).planNode();
+      auto mout = exec::runPlan(mplan);
+      auto mwant = runOracle(t, nullptr, {"l_linestatus", "case when l_tax < 0.03 then l_extendedprice end", "case when l_shipdate > 9131 then 1 end"},
+                             {0}, {{0, 1}, {2, 2}, {3, 1}, {2, -1}}, row);
+      size_t mg = 0;
+      bool mok = true;
+      for (auto& o : mout) for (size_t g = 0; g < o->size(); ++g, ++mg) {
+        auto it = mwant.groups.find({at<std::string>(o->childAt(0), g) == "F" ? 0 : 1});
+        if (it == mwant.groups.end()) { mok = false; continue; }
+        const auto& w = it->second;
+        mok = mok && close(at<double>(o->childAt(1), g), bitsToDouble(w[0].first)) && at<int64_t>(o->childAt(2), g) == w[1].first &&
+              at<double>(o->childAt(3), g) == bitsToDouble(w[2].first) && at<int64_t>(o->childAt(4), g) == w[3].first;
+        mok = mok && w[1].first > 0 && w[1].first < w[3].first; // the masks really select a strict subset
+      }
+      EXPECT(mok && mg == 2);
+    }
   }
   exec::Operator::unregisterAllOperators();
   gpu::registerGpuOperators();

@@ -94,8 +94,17 @@ struct GpuHashAggregation::Impl {
       const bool hasColumn = !a.args.empty() && a.args[0]->kind() == ITypedExpr::Kind::kFieldAccess;
       TypedExprPtr x = hasColumn ? exprOf(static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name()) : nullptr;
       const std::string col = hasColumn ? static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name() : "";
+      // Aggregation mask: only rows whose mask is TRUE feed the aggregate (AggregationMasks.cpp) == the aggregate over
+      // if(mask, x) with no ELSE, since every aggregate here skips NULL inputs; count(*) counts if(mask, 1).
+      if (raw && a.mask) {
+        TypedExprPtr m = exprOf(static_cast<const FieldAccessTypedExpr*>(a.mask.get())->name());
+        TypedExprPtr v = x ? x : TypedExprPtr(std::make_shared<ConstantTypedExpr>(BIGINT(), false, 1, 0.0));
+        VB_USER_CHECK(v->type()->kind() != TypeKind::VARCHAR && v->type()->kind() != TypeKind::BOOLEAN, "masked " + a.function + " over " + v->type()->toString() + " is not supported on the GPU");
+        x = std::make_shared<CallTypedExpr>(v->type(), std::vector<TypedExprPtr>{m, v}, "if");
+      }
+      const bool countsColumn = hasColumn || (raw && a.mask);
       if (a.function == "count") {
-        if (raw) info.acc0 = addAcc(VGPU_ACC_COUNT, hasColumn ? addOutput(x) : -1);
+        if (raw) info.acc0 = addAcc(VGPU_ACC_COUNT, countsColumn ? addOutput(x) : -1);
         else info.acc0 = addAcc(VGPU_ACC_SUM_I64, addOutput(x)); // final count = sum of partial counts (CountAggregate.cpp:81-90)
       } else if (a.function == "sum") {
         const bool fp = raw ? x->type()->isFloating() : info.rawType->isFloating();

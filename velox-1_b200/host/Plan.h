@@ -156,6 +156,9 @@ class AggregationNode : public PlanNode {
     std::string function;                 // sum count avg min max
     std::vector<TypedExprPtr> args;       // field accesses (or one constant for count(1)); empty = count(*)
     TypePtr rawInputType;                 // type of the ORIGINAL argument (final steps resolve result types from it)
+    // Optional BOOLEAN input column: only rows where it is TRUE feed this aggregate (raw-input steps only;
+    // core::AggregationNode::aggregateMasks, velox/exec/AggregationMasks.cpp).  nullptr = no mask.
+    TypedExprPtr mask;
   };
   AggregationNode(PlanNodeId id, Step step, std::vector<std::string> groupingKeys, std::vector<std::string> aggregateNames,
                   std::vector<Aggregate> aggregates, bool ignoreNullKeys, PlanNodePtr source);
@@ -196,16 +199,19 @@ class PlanBuilder {
   PlanBuilder& values(std::vector<RowVectorPtr> vectors);
   PlanBuilder& filter(const std::string& expr);
   PlanBuilder& project(const std::vector<std::string>& exprs);
-  PlanBuilder& partialAggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates) {
-    return aggregation(keys, aggregates, core::AggregationNode::Step::kPartial, false);
+  // masks: per aggregate, the name of a BOOLEAN column or "" (PlanBuilder::partialAggregation(keys, aggregates, masks))
+  PlanBuilder& partialAggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates,
+                                  const std::vector<std::string>& masks = {}) {
+    return aggregation(keys, aggregates, core::AggregationNode::Step::kPartial, false, masks);
   }
-  PlanBuilder& singleAggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates) {
-    return aggregation(keys, aggregates, core::AggregationNode::Step::kSingle, false);
+  PlanBuilder& singleAggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates,
+                                 const std::vector<std::string>& masks = {}) {
+    return aggregation(keys, aggregates, core::AggregationNode::Step::kSingle, false, masks);
   }
   PlanBuilder& intermediateAggregation();
   PlanBuilder& finalAggregation();
   PlanBuilder& aggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates,
-                           core::AggregationNode::Step step, bool ignoreNullKeys);
+                           core::AggregationNode::Step step, bool ignoreNullKeys, const std::vector<std::string>& masks = {});
   // custom nodes (PlanBuilder::addNode, velox/exec/tests/utils/PlanBuilder.h:787-792)
   PlanBuilder& addNode(std::function<core::PlanNodePtr(std::string nodeId, core::PlanNodePtr source)> make);
   core::PlanNodePtr planNode() const { return node_; }

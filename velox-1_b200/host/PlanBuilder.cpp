@@ -75,12 +75,20 @@ void parseAggregate(const std::string& text, const RowTypePtr& in, size_t ordina
 } // namespace
 
 PlanBuilder& PlanBuilder::aggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates,
-                                      AggregationNode::Step step, bool ignoreNullKeys) {
+                                      AggregationNode::Step step, bool ignoreNullKeys, const std::vector<std::string>& masks) {
   VB_CHECK(node_ != nullptr, "aggregation needs a source node");
   VB_CHECK(AggregationNode::isRawInput(step), "use intermediateAggregation()/finalAggregation() after a partial aggregation");
   std::vector<AggregationNode::Aggregate> aggs(aggregates.size());
   std::vector<std::string> names(aggregates.size());
   for (size_t i = 0; i < aggregates.size(); ++i) parseAggregate(aggregates[i], node_->outputType(), i, aggs[i], names[i]);
+  VB_USER_CHECK(masks.empty() || masks.size() == aggregates.size(), "one mask (or \"\") per aggregate expected");
+  for (size_t i = 0; i < masks.size(); ++i) {
+    if (masks[i].empty()) continue;
+    const auto& in = node_->outputType();
+    const TypePtr t = in->childAt(in->getChildIdx(masks[i]));
+    VB_USER_CHECK(t->kind() == TypeKind::BOOLEAN, "aggregation mask " + masks[i] + " must be a BOOLEAN column");
+    aggs[i].mask = std::make_shared<FieldAccessTypedExpr>(t, masks[i]);
+  }
   node_ = std::make_shared<AggregationNode>(nextId(), step, keys, std::move(names), std::move(aggs), ignoreNullKeys, node_);
   return *this;
 }
@@ -94,6 +102,7 @@ PlanBuilder& PlanBuilder::followUp(AggregationNode::Step step) {
   const auto& in = partial->outputType();
   for (size_t i = 0; i < partial->aggregates().size(); ++i) {
     AggregationNode::Aggregate a = partial->aggregates()[i];
+    a.mask = nullptr; // masks apply to raw input only
     const std::string& col = partial->aggregateNames()[i];
     a.args = {std::make_shared<FieldAccessTypedExpr>(in->childAt(in->getChildIdx(col)), col)};
     aggs.push_back(std::move(a));
