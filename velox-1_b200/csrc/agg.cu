@@ -713,7 +713,13 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     if (room < (uint64_t)std::min<int64_t>(rem, kTile)) {
       uint64_t want = known + (uint64_t)std::min<int64_t>(rem, std::max<int64_t>(4 << 20, (int64_t)known));
       if (a.expected_groups > 0) want = std::max<uint64_t>(want, (uint64_t)a.expected_groups);
-      rc = hash_resize(a, next_pow2(2 * want), stream);
+      // Slots per expected group.  4 (load <= 25 %) parks half as many segments as 2 did: C3 SF10 1.20 -> 0.93 ms per
+      // batch; the price is a table init twice as long (0.34 -> 0.68 ms, once per aggregation) and twice the HBM, so
+      // tables that would pass 8 GB keep the factor 2 (profiles/r01_c3_experiments.md).  VGPU_TABLE_FACTOR overrides.
+      static const uint64_t env_factor = getenv("VGPU_TABLE_FACTOR") ? std::max(2, atoi(getenv("VGPU_TABLE_FACTOR"))) : 0;
+      uint64_t table_factor = env_factor ? env_factor : 4;
+      if (!env_factor && next_pow2(table_factor * want) * (uint64_t)a.row_words * 8 > (8ull << 30)) table_factor = 2;
+      rc = hash_resize(a, next_pow2(table_factor * want), stream);
       if (rc) return rc;
       room = a.capacity - a.capacity / 8 - known;
     }
