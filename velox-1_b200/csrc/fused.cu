@@ -117,6 +117,23 @@ struct Gen {
     }
   }
 
+  bool small_dict(int c) const { return p.cols[c].small_dict != 0 && fused_small_dict_enabled(); }
+
+  // Kernel prologue: lane L keeps base value L of every small dictionary (and all lanes its null bits).
+  void gen_small_dict_registers() {
+    for (int c = 0; c < p.n_cols; ++c) {
+      if (!col_used[c] || p.cols[c].encoding != VGPU_DICTIONARY || !small_dict(c)) continue;
+      const DevCol& d = p.cols[c];
+      const char* ty = d.type == VGPU_TINYINT ? "signed char" : d.type == VGPU_SMALLINT ? "short" : d.type == VGPU_INTEGER ? "int" : d.type == VGPU_REAL ? "float" : "u64";
+      out("  u64 DB%d = 0ull;\n  if (lane < p.base_len[%d]) {\n", c, c);
+      if (d.type == VGPU_REAL) out("    DB%d = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + lane));\n", c, c);
+      else if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) out("    DB%d = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + lane);\n", c, c);
+      else out("    DB%d = (u64)(i64)__ldg(reinterpret_cast<const %s*>(p.values[%d]) + lane);\n", c, ty, c);
+      out("  }\n");
+      if (d.base_nulls) out("  const u32 DBN%d = (u32)__ldg(p.base_nulls[%d]);\n", c, c);
+    }
+  }
+
   // Per-row decoded column values (inside the row loop).
   void gen_row_columns() {
     for (int c = 0; c < p.n_cols; ++c) {
@@ -129,6 +146,20 @@ struct Gen {
         continue;
       }
       std::string nn = d.nulls ? "!((N" + std::to_string(c) + " >> j) & 1u)" : "false";
+      if (d.encoding == VGPU_DICTIONARY && small_dict(c)) {
+        // base value from the lane that holds it: no second, dependent memory round trip after the index load
+        // (every lane executes the shuffle; rows that are invalid or NULL just drop what they read)
+        out("      V c%d_; {\n", c);
+        out("        bool isn = %s;\n", nn.c_str());
+        out("        const u32 ix = (u32)Q%d[j] & 31u;\n", c);
+        if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE || d.type == VGPU_REAL) out("        const u64 got = __shfl_sync(0xffffffffu, DB%d, (int)ix);\n", c);
+        else out("        const u64 got = (u64)(i64)__shfl_sync(0xffffffffu, (int)DB%d, (int)ix);\n", c); // one 32-bit shuffle
+        if (d.base_nulls) out("        isn = isn || !((DBN%d >> ix) & 1u);\n", c);
+        out("        isn = isn || !valid;\n");
+        out("        c%d_ = V{isn ? 0ull : got, isn, false};\n      }\n", c);
+        out("      const V c%d = c%d_;\n", c, c);
+        continue;
+      }
       if (d.encoding == VGPU_DICTIONARY) {
         out("      V c%d_; bool cv%d_ = false; {\n", c, c);
         out("        bool isn = %s; u64 raw = 0;\n", nn.c_str());
@@ -580,6 +611,7 @@ struct Gen {
     out("  const i64 n_blocks = (n + 127) >> 7, n_full = n >> 7;\n");
     out("  const i64 wid = (i64)blockIdx.x * (NT / 32) + (threadIdx.x >> 5), nwarps = (i64)gridDim.x * (NT / 32);\n");
     out("  u32 accerr = 0;\n");
+    gen_small_dict_registers();
     if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
     if (p.mode == kSinkArray) {
       if (st == AS_REGS) {

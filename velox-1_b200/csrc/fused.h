@@ -28,6 +28,8 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
 // fused_last_source() returns.  Used by build() to prebuild the cubins of aot_plans.py.
 void fused_set_dry_run(bool on);
 bool fused_dry_run();
+// Small dictionaries (<= 32 base values) looked up with a warp shuffle instead of a gather (VGPU_SMALL_DICT=0 disables).
+bool fused_small_dict_enabled();
 const std::string& fused_last_source();
 const std::string& fused_last_note(); // why the last shape was declined / how it was built
 uint64_t fused_source_hash(const std::string& source);

@@ -62,6 +62,7 @@ struct FusedParams {
   const i32* indices[16];
   const u64* nulls[16];
   const u64* base_nulls[16];
+  i32 base_len[16]; // DICTIONARY columns with <= 32 base values (else 0): the base lives in one register per lane
   i64 n_rows;
   u32* err_word;
   // ARRAY / GLOBAL sink: per-CTA partials [gridDim][n_cells][n_groups]

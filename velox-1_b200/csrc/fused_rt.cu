@@ -196,6 +196,8 @@ std::string signature(const PipelineParams& p) {
     const uint8_t f[6] = {d.type, d.encoding, (uint8_t)(d.nulls != nullptr), (uint8_t)(d.base_nulls != nullptr), d.const_null,
                           (uint8_t)(((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) | (((reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) << 1))};
     put(f, 6);
+    const uint8_t sd = d.small_dict != 0 && fused_small_dict_enabled();
+    put(&sd, 1);
     if (d.encoding == VGPU_CONSTANT) put(&d.constant, 8);
   }
   const uint8_t ind = p.in_rows != nullptr;
@@ -220,6 +222,10 @@ std::string signature(const PipelineParams& p) {
 
 void fused_set_dry_run(bool on) { g_dry = on; }
 bool fused_dry_run() { return g_dry; }
+bool fused_small_dict_enabled() {
+  static const bool on = !(getenv("VGPU_SMALL_DICT") && getenv("VGPU_SMALL_DICT")[0] == '0');
+  return on;
+}
 const std::string& fused_last_source() { return g_last_source; }
 const std::string& fused_last_note() { return g_last_note; }
 uint64_t fused_source_hash(const std::string& source) {
@@ -309,6 +315,7 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
     fp.indices[c] = p.cols[c].indices;
     fp.nulls[c] = (const vgf::u64*)p.cols[c].nulls;
     fp.base_nulls[c] = (const vgf::u64*)p.cols[c].base_nulls;
+    fp.base_len[c] = p.cols[c].small_dict;
   }
   fp.n_rows = p.n_rows;
   fp.err_word = p.err_word;

@@ -49,7 +49,8 @@ struct DevCol {
   uint8_t const_null;
   uint8_t elem_log2; // log2 bytes of a staged element (BOOLEAN flat: bits, marked 255)
   uint8_t bulk_ok;   // staged tile may be fetched with cp.async.bulk (16 B aligned, flat walk)
-  uint8_t pad[3];
+  uint8_t small_dict; // DICTIONARY with 1..32 base values: base_len; the generated kernels keep the base in one register per lane
+  uint8_t pad[2];
 };
 
 // Cell = one 8-byte lane of group state.  An accumulator maps to a value cell and (for

@@ -1372,6 +1372,7 @@ int plan_pipeline(const Program& prog, const vgpu_column* cols, int32_t ncols, i
     d.constant = in.constant.i;
     d.type = (uint8_t)in.type; d.encoding = (uint8_t)in.encoding; d.const_null = (uint8_t)(in.constant_is_null != 0);
     d.stage_off = -1; d.nulls_off = -1; d.bulk_ok = 0;
+    d.small_dict = (in.encoding == VGPU_DICTIONARY && in.type != VGPU_BOOLEAN && in.base_length >= 1 && in.base_length <= 32) ? (uint8_t)in.base_length : 0;
     if (in.type < VGPU_BOOLEAN || in.type > VGPU_DOUBLE) { set_error("column %d: bad type %d", c, in.type); return VGPU_ERR_INVALID; }
     d.elem_log2 = (uint8_t)(in.encoding == VGPU_DICTIONARY ? 2 : host_elem_log2(in.type));
     if (!used[c] || in.encoding == VGPU_CONSTANT) continue;
