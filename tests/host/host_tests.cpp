@@ -182,6 +182,15 @@ static void cpuTests() {
     EXPECT(id.ops.empty() && id.filter.kind == VGPU_OPND_NONE && id.outputs[0].kind == VGPU_OPND_COL);
   }
 
+  section("lowering: VARCHAR equality on value ids");
+  {
+    auto lp = lowerExpressions(parse::parseExpr("l_returnflag = 'R' or l_linestatus in ('O', 'R') or l_returnflag <> 'N'", row), {});
+    EXPECT(lp.stringLiterals == (std::vector<std::string>{"R", "O", "N"}));              // 'R' shared: one id per distinct literal
+    EXPECT(lp.stringColumns == (std::set<std::string>{"l_returnflag", "l_linestatus"}));
+    EXPECT(lowerExpressions(parse::parseExpr("l_returnflag is null", row), {}).stringColumns.empty()); // null flags only
+    EXPECT_THROW(lowerExpressions(parse::parseExpr("l_returnflag < 'R'", row), {}), VeloxUserError);   // ids do not preserve order
+  }
+
   section("PlanBuilder: aggregation masks");
   {
     auto masked = PlanBuilder().values({rv}).project({"l_linestatus", "l_tax < 0.03 as m", "l_extendedprice"})
@@ -341,6 +350,23 @@ static void gpuTests() {
       caseOk = caseOk && !isNullAt(cs[0]->childAt(2), i) && at<double>(cs[0]->childAt(2), i) == (t.tax[i] > 0.04 ? t.quantity[i] : -1.0);
     }
     EXPECT(caseOk);
+    // VARCHAR =, <>, IN on dictionary-encoded strings (TPC-H Q12 / Q19 predicates): value ids on the device
+    auto sv = exec::runPlan(PlanBuilder().values(in).filter("l_returnflag = 'R' or (l_linestatus in ('O', 'X') and l_returnflag <> 'N')").project({"l_orderkey"}).planNode());
+    size_t wantS = 0, gotS = 0;
+    for (size_t i = 0; i < t.orderkey.size(); ++i) wantS += t.flag[i] == 2 || (t.status[i] == 1 && t.flag[i] != 1);
+    for (auto& o : sv) gotS += o->size();
+    EXPECT(gotS == wantS && wantS > 0 && wantS < t.orderkey.size());
+    { // below an aggregation the string predicate stays in its own GpuFilterProject (not fused), results unchanged
+      auto splan = PlanBuilder().values(in).filter("l_returnflag in ('A', 'R')").project({"l_linestatus", "l_extendedprice"})
+                       .singleAggregation({"l_linestatus"}, {"count(*) as n"}).planNode();
+      auto sdriver = exec::createDriver(splan);
+      EXPECT(sdriver->operators().size() == 3 && sdriver->operators()[1]->operatorType() == "GpuFilterProject");
+      auto sout = sdriver->run();
+      int64_t cnt = 0, wantCnt = 0;
+      for (auto& o : sout) for (size_t g = 0; g < o->size(); ++g) cnt += at<int64_t>(o->childAt(1), g);
+      for (size_t i = 0; i < t.orderkey.size(); ++i) wantCnt += t.flag[i] != 1;
+      EXPECT(cnt == wantCnt);
+    }
     // no row passes -> no output vector at all (Driver.cpp:550-556)
     EXPECT(exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").planNode()).empty());
   }

@@ -142,6 +142,7 @@ GpuFilterProject::GpuFilterProject(exec::DriverCtx* ctx, int32_t id, std::shared
     }
   }
   lowered_ = lowerExpressions(exprs_.filter, computed);
+  for (size_t k = 0; k < lowered_.stringLiterals.size(); ++k) stringIds_.emplace(lowered_.stringLiterals[k], (int32_t)k);
   check(vgpu_init(ctx->queryConfig.device), "vgpu_init");
   const auto desc = lowered_.desc();
   check(vgpu_program_create(&desc, &program_), "vgpu_program_create");
@@ -184,7 +185,18 @@ RowVectorPtr GpuFilterProject::getOutput() {
   batch.stream = stream_;
   for (auto& name : lowered_.columns) {
     const auto& child = in->childAt(inputType_->getChildIdx(name));
-    if (child->type()->kind() == TypeKind::VARCHAR) {
+    if (child->type()->kind() == TypeKind::VARCHAR && lowered_.stringColumns.count(name)) {
+      // compared with =, <>, IN: the base strings become value ids of the operator's dictionary (one lookup per BASE
+      // value: a dictionary-encoded column costs nothing per row and keeps its indices / nulls as they are)
+      const auto* base = static_cast<const FlatVector<std::string>*>(decode(child).base);
+      std::vector<int32_t> ids(base->size());
+      for (size_t i = 0; i < ids.size(); ++i) {
+        auto it = stringIds_.find(base->valueAt(i));
+        if (it == stringIds_.end()) it = stringIds_.emplace(base->valueAt(i), (int32_t)stringIds_.size()).first;
+        ids[i] = it->second;
+      }
+      bindColumn(batch, child, &ids);
+    } else if (child->type()->kind() == TypeKind::VARCHAR) {
       // only the null flags of a VARCHAR column can matter to a device expression (is_null); values travel as ids
       const std::vector<int32_t> zeros(decode(child).base->size(), 0);
       bindColumn(batch, child, &zeros);

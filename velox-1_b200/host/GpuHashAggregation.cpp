@@ -162,6 +162,8 @@ struct GpuHashAggregation::Impl {
     }
     for (size_t i = 0; i < keys.size(); ++i) specs[i] = vgpu_key_spec{(int32_t)i, mode == VGPU_AGG_HASH ? keys[i].bits : 0, keys[i].lo, keys[i].hi};
     lowered = lowerExpressions(hasFused ? fused.filter : nullptr, outputs);
+    // string comparisons need the FilterProject operator's value-id dictionary: the adapter keeps the two operators
+    if (!lowered.stringColumns.empty() || !lowered.stringLiterals.empty()) throw VeloxUserError("VARCHAR comparisons are evaluated by GpuFilterProject, not inside the fused aggregation");
     const auto pdesc = lowered.desc();
     check(vgpu_program_create(&pdesc, &program), "vgpu_program_create");
     vgpu_agg_desc d{};

@@ -7,6 +7,7 @@
 // (VGPU_ERR_USER: data errors) or VeloxRuntimeError.  There is no CPU path: if libvgpu.so or the GPU is
 // missing, construction throws.
 #pragma once
+#include <unordered_map>
 #include "../../include/vgpu.h"
 #include "Lowering.h"
 #include "Operator.h"
@@ -38,12 +39,17 @@ class GpuFilterProject : public exec::Operator {
   // "for accelerator conversion" (velox/exec/FilterProject.h:63-72)
   const FilterProjectExprs& exprsAndProjection() const { return exprs_; }
   const RowTypePtr& inputType() const { return inputType_; }
+  // VARCHAR =, <>, IN run on this operator's value-id dictionary; such a FilterProject is not fused into an aggregation
+  bool comparesStrings() const { return !lowered_.stringColumns.empty() || !lowered_.stringLiterals.empty(); }
  private:
   FilterProjectExprs exprs_;
   RowTypePtr inputType_;
   std::vector<int> identity_;        // per output: input child index for identity projections, else -1
   std::vector<int> programOutput_;   // per output: index into the program's outputs, else -1
   LoweredProgram lowered_;
+  // value ids of the strings compared by the program: the literals first (id = position in lowered_.stringLiterals),
+  // then every distinct string of the compared columns in order of first appearance
+  std::unordered_map<std::string, int32_t> stringIds_;
   vgpu_program_t program_ = nullptr;
   void* stream_ = nullptr;
 };

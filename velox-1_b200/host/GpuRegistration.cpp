@@ -29,7 +29,7 @@ bool fuseFilterProjectIntoAggregation(const exec::DriverFactory& factory, exec::
   for (size_t i = 0; i + 1 < ops.size(); ++i) {
     auto fp = dynamic_cast<GpuFilterProject*>(ops[i].get());
     auto ha = dynamic_cast<GpuHashAggregation*>(ops[i + 1].get());
-    if (!fp || !ha) continue;
+    if (!fp || !ha || fp->comparesStrings()) continue;
     std::shared_ptr<const AggregationNode> node;
     for (auto& n : factory.planNodes) if (n->id() == ha->planNodeId()) node = std::dynamic_pointer_cast<const AggregationNode>(n);
     if (!node || !AggregationNode::isRawInput(node->step())) continue;

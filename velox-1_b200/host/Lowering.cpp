@@ -117,8 +117,17 @@ class Lowerer {
       return v;
     }
     auto c = static_cast<const ConstantTypedExpr*>(e.get());
-    VB_CHECK(e->type()->kind() != TypeKind::VARCHAR, "VARCHAR literals cannot be evaluated on the device");
     if (c->isNull()) { v.opnd = opnd(VGPU_OPND_NULL, t, 0); return v; }
+    if (e->type()->kind() == TypeKind::VARCHAR) { // the literal's value id (see LoweredProgram::stringLiterals)
+      const std::string& sv = c->stringValue();
+      size_t id = 0;
+      while (id < out.stringLiterals.size() && out.stringLiterals[id] != sv) ++id;
+      if (id == out.stringLiterals.size()) out.stringLiterals.push_back(sv);
+      v.opnd = opnd(VGPU_OPND_IMM, t, 0);
+      v.hasImm = true;
+      v.imm.i = (int64_t)id;
+      return v;
+    }
     v.opnd = opnd(VGPU_OPND_IMM, t, 0);
     v.hasImm = true;
     if (e->type()->isFloating()) v.imm.d = c->doubleValue(); else v.imm.i = c->intValue();
@@ -146,6 +155,13 @@ class Lowerer {
     const vgpu_operand none = opnd(VGPU_OPND_NONE, 0, 0);
     vgpu_operand res;
     const int code = opcodeOf(fn);
+    for (auto& in : e->inputs()) {
+      if (in->type()->kind() != TypeKind::VARCHAR || fn == "is_null") continue;
+      // strings travel as value ids: equality is all that ids preserve
+      if (fn != "eq" && fn != "neq") throw VeloxUserError("Scalar function " + fn + " over VARCHAR is not supported on the device (only =, <>, IN, IS NULL)");
+      if (in->kind() == ITypedExpr::Kind::kFieldAccess) out.stringColumns.insert(static_cast<const FieldAccessTypedExpr*>(in.get())->name());
+      else if (in->kind() != ITypedExpr::Kind::kConstant) throw VeloxUserError("computed VARCHAR values cannot be compared on the device");
+    }
     if (code >= 0) {
       VB_CHECK(!(args[0].hasImm && args[1].hasImm), fn + " of two literals must be folded before lowering");
       const int t = deviceType(e->inputs()[0]->type());

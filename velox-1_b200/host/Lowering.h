@@ -3,6 +3,7 @@
 // :54-58,160-163 shares common sub-expressions, :131-158 flattens AND/OR — both are kept here).
 #pragma once
 #include <map>
+#include <set>
 
 #include "../../include/vgpu.h"
 #include "Plan.h"
@@ -14,6 +15,10 @@ struct LoweredProgram {
   vgpu_operand filter{};                // kind NONE when there is no filter
   std::vector<vgpu_operand> outputs;
   std::vector<std::string> columns;     // input column names, in program column order
+  // VARCHAR equality (eq / neq / IN) runs on value ids: literal k of this list has id k, and the operator must bind the
+  // columns named in stringColumns through ONE string -> id dictionary that starts with these literals.
+  std::vector<std::string> stringLiterals;
+  std::set<std::string> stringColumns;
   vgpu_program_desc desc() const {
     vgpu_program_desc d{};
     d.ops = ops.data(); d.n_ops = (int32_t)ops.size(); d.filter = filter;
