@@ -441,9 +441,14 @@ static void gpuTests() {
     { // aggregation masks (core::AggregationNode::aggregateMasks, AggregationMasks.cpp): only rows whose mask is TRUE feed
       // the aggregate; fused the mask is an expression, unfused a BOOLEAN column produced by the FilterProject below
       auto mplan = PlanBuilder().values(in).project({"l_linestatus", "l_tax < 0.03 as m", "l_extendedprice", "l_shipdate > 9131 as late"})
-                       .singleAggregation({"l_linestatus"}, {"sum(l_extendedprice) as s", "count(*) as n", "min(l_extendedprice) as lo", "count(*) as all_rows"},
-                                          {"m", "late", "m", ""}).planNode();
+                       .singleAggregation({"l_linestatus"}, {"sum(l_extendedprice) as s", "count(*) as n", "min(l_extendedprice) as lo", "count(*) as all_rows", "count_if(late) as n2"},
+                                          {"m", "late", "m", "", ""}).planNode();
       auto mout = exec::runPlan(mplan);
+      // count_if(late) == count(*) masked by late; and through partial -> final
+      auto cif = exec::runPlan(PlanBuilder().values(in).project({"l_linestatus", "l_shipdate > 9131 as late"})
+                                   .partialAggregation({"l_linestatus"}, {"count_if(late) as n2"}).finalAggregation().planNode());
+      std::map<std::string, int64_t> cifBy;
+      for (auto& o : cif) for (size_t g = 0; g < o->size(); ++g) cifBy[at<std::string>(o->childAt(0), g)] = at<int64_t>(o->childAt(1), g);
       auto mwant = runOracle(t, nullptr, {"l_linestatus", "case when l_tax < 0.03 then l_extendedprice end", "case when l_shipdate > 9131 then 1 end"},
                              {0}, {{0, 1}, {2, 2}, {3, 1}, {2, -1}}, row);
       size_t mg = 0;
@@ -455,6 +460,7 @@ static void gpuTests() {
         mok = mok && close(at<double>(o->childAt(1), g), bitsToDouble(w[0].first)) && at<int64_t>(o->childAt(2), g) == w[1].first &&
               at<double>(o->childAt(3), g) == bitsToDouble(w[2].first) && at<int64_t>(o->childAt(4), g) == w[3].first;
         mok = mok && w[1].first > 0 && w[1].first < w[3].first; // the masks really select a strict subset
+        mok = mok && at<int64_t>(o->childAt(5), g) == w[1].first && cifBy[at<std::string>(o->childAt(0), g)] == w[1].first;
       }
       EXPECT(mok && mg == 2);
     }

@@ -345,6 +345,22 @@ __device__ __forceinline__ void smem_update(u64* cell, u64 v, u32& err) {
   }
 }
 
+// Claim of an empty slot, executed only when `pred`: CAS(addr, EMPTY -> desired).  `seen` must hold VGF_EMPTY_KEY on
+// entry (from empty_marker(), a register of its own) and holds the slot's previous key afterwards.  The register is both
+// the compare operand and the result, which is the form the hardware instruction has: no copy after the atomic, so
+// several claims issue back to back and their round trips overlap.
+__device__ __forceinline__ u64 empty_marker() {
+  u64 e;
+  asm volatile("mov.b64 %0, 0xFFFFFFFFFFFFFFFF;" : "=l"(e));
+  return e;
+}
+__device__ __forceinline__ void claim_if(bool pred, u64* addr, u64 desired, u64& seen) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p atom.global.cas.b64 %0, [%1], %0, %2;\n\t}"
+      : "+l"(seen)
+      : "l"(addr), "l"(desired), "r"((u32)pred));
+}
+
 // ---- HBM hash table (same layout as device_common.cuh) -------------------------------------------
 __device__ __forceinline__ u64 mix64(u64 k) {
   k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
@@ -438,11 +454,12 @@ __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[
   // the caller prefetched the lines into L2 while the run aggregation was computing).  The CAS
   // returns the resident key when the slot is taken, which is all a lookup needs: keys never
   // change once set.
+  // (predicated PTX, not `if (pend) atomicCAS`: with branches the compiler gave all four CAS the same result
+  //  register and each one waited for the previous round trip — 28 % of the kernel's stall samples)
 #pragma unroll
-  for (int s = 0; s < 4; ++s) {
-    seen[s] = VGF_EMPTY_KEY;
-    if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
-  }
+  for (int s = 0; s < 4; ++s) seen[s] = empty_marker();
+#pragma unroll
+  for (int s = 0; s < 4; ++s) claim_if(pend[s], table + h[s] * ROW_WORDS, key[s], seen[s]);
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     if (!pend[s]) continue;
@@ -472,9 +489,9 @@ __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[
   u64 steps = 1;
   while (pend[0] || pend[1] || pend[2] || pend[3]) {
 #pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      if (pend[s]) seen[s] = atomicCAS(table + h[s] * ROW_WORDS, VGF_EMPTY_KEY, key[s]);
-    }
+    for (int s = 0; s < 4; ++s) seen[s] = empty_marker();
+#pragma unroll
+    for (int s = 0; s < 4; ++s) claim_if(pend[s], table + h[s] * ROW_WORDS, key[s], seen[s]);
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       if (!pend[s]) continue;

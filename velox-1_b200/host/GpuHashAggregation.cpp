@@ -94,6 +94,15 @@ struct GpuHashAggregation::Impl {
       const bool hasColumn = !a.args.empty() && a.args[0]->kind() == ITypedExpr::Kind::kFieldAccess;
       TypedExprPtr x = hasColumn ? exprOf(static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name()) : nullptr;
       const std::string col = hasColumn ? static_cast<const FieldAccessTypedExpr*>(a.args[0].get())->name() : "";
+      bool isCountIf = false;
+      if (a.function == "count_if") { // count_if(b) = count(if(b, 1)): TRUE rows only (CountIfAggregate.cpp); final = sum of partials
+        isCountIf = true;
+        info.fn = "count";
+        if (raw) {
+          VB_USER_CHECK(x && x->type()->kind() == TypeKind::BOOLEAN, "count_if takes one BOOLEAN argument");
+          x = std::make_shared<CallTypedExpr>(BIGINT(), std::vector<TypedExprPtr>{x, std::make_shared<ConstantTypedExpr>(BIGINT(), false, 1, 0.0)}, "if");
+        }
+      }
       // Aggregation mask: only rows whose mask is TRUE feed the aggregate (AggregationMasks.cpp) == the aggregate over
       // if(mask, x) with no ELSE, since every aggregate here skips NULL inputs; count(*) counts if(mask, 1).
       if (raw && a.mask) {
@@ -103,7 +112,7 @@ struct GpuHashAggregation::Impl {
         x = std::make_shared<CallTypedExpr>(v->type(), std::vector<TypedExprPtr>{m, v}, "if");
       }
       const bool countsColumn = hasColumn || (raw && a.mask);
-      if (a.function == "count") {
+      if (a.function == "count" || isCountIf) {
         if (raw) info.acc0 = addAcc(VGPU_ACC_COUNT, countsColumn ? addOutput(x) : -1);
         else info.acc0 = addAcc(VGPU_ACC_SUM_I64, addOutput(x)); // final count = sum of partial counts (CountAggregate.cpp:81-90)
       } else if (a.function == "sum") {

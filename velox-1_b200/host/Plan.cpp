@@ -7,14 +7,14 @@ namespace vb200 {
 namespace core {
 
 TypePtr AggregationNode::intermediateType(const std::string& fn, const TypePtr& raw) {
-  if (fn == "count") return BIGINT();
+  if (fn == "count" || fn == "count_if") return BIGINT(); // CountIfAggregate.cpp: BIGINT accumulator, never NULL
   if (fn == "sum") return raw->isFloating() ? DOUBLE() : BIGINT(); // sum(real) keeps a double accumulator
   if (fn == "avg") return ROW({"sum", "count"}, {DOUBLE(), BIGINT()});
   if (fn == "min" || fn == "max") return raw;
   throw VeloxUserError("Aggregate function not registered: " + fn);
 }
 TypePtr AggregationNode::finalType(const std::string& fn, const TypePtr& raw) {
-  if (fn == "count") return BIGINT();
+  if (fn == "count" || fn == "count_if") return BIGINT(); // CountIfAggregate.cpp: BIGINT accumulator, never NULL
   if (fn == "sum") return raw->kind() == TypeKind::REAL ? REAL() : raw->isFloating() ? DOUBLE() : BIGINT();
   if (fn == "avg") return raw->kind() == TypeKind::REAL ? REAL() : DOUBLE();
   if (fn == "min" || fn == "max") return raw;
