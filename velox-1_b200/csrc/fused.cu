@@ -343,7 +343,8 @@ struct Gen {
     // Thread-private tables turn every row into dependent shared-memory read-modify-writes; the warps
     // left to cover HBM latency are too few, so the warp's NEXT block is pulled into L2 one iteration
     // early (Q1 SF10: 0.49 -> 0.39 ms).  Register / atomic strategies measured 1-5 % slower with it.
-    if (full && st == AS_THREAD) gen_input_prefetch();
+    static const bool prefetch_all = getenv("VGPU_PREFETCH_ALL") && getenv("VGPU_PREFETCH_ALL")[0] == '1'; // tuning aid
+    if (full && (st == AS_THREAD || prefetch_all)) gen_input_prefetch();
     gen_block_header(full);
     gen_row_begin(full);
     gen_keys(false);
@@ -369,7 +370,8 @@ struct Gen {
   // Next block's input lines -> L2 (no registers held): the warp's following iteration then starts
   // from L2 latency instead of HBM latency.  One 128-byte line per lane per column.
   void gen_input_prefetch() {
-    out("    if (blk + nwarps < n_full) {\n");
+    static const int dist = getenv("VGPU_PREFETCH_DIST") ? std::max(1, atoi(getenv("VGPU_PREFETCH_DIST"))) : 1; // blocks ahead (tuning aid)
+    out("    if (blk + %d * nwarps < n_full) {\n", dist);
     for (int c = 0; c < p.n_cols; ++c) {
       if (!col_used[c]) continue;
       const DevCol& d = p.cols[c];
@@ -377,8 +379,8 @@ struct Gen {
       const bool dict = d.encoding == VGPU_DICTIONARY;
       const int w = dict ? 4 : (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) ? 8 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 4 : 0;
       if (!w) continue;
-      out("      if (lane < %d) prefetch_l2(reinterpret_cast<const char*>(p.%s[%d]) + (blk + nwarps) * %d + lane * 128);\n",
-          w, dict ? "indices" : "values", c, 128 * w);
+      out("      if (lane < %d) prefetch_l2(reinterpret_cast<const char*>(p.%s[%d]) + (blk + %d * nwarps) * %d + lane * 128);\n",
+          w, dict ? "indices" : "values", c, dist, 128 * w);
     }
     out("    }\n");
   }
