@@ -401,8 +401,11 @@ struct Gen {
     gen_raise();
     out("    }\n");
     // home slots of the rows' keys -> L2 while the run aggregation below computes
+    // (computed once per row and handed to the probe below: the hash is ~25 instructions)
+    out("    u64 HOME[4];\n");
     out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
-    out("      if (PASS[j] && !KN[j] && (j == 0 || KEY[j] != KEY[j - 1])) prefetch_l2(p.table + home_slot(p, KEY[j]) * %d);\n", p.row_words);
+    out("      HOME[j] = home_slot(p, KEY[j]);\n");
+    out("      if (PASS[j] && !KN[j] && (j == 0 || KEY[j] != KEY[j - 1])) prefetch_l2(p.table + HOME[j] * %d);\n", p.row_words);
     out("    }\n");
     // Run aggregation before the table is touched.  Equal keys tend to arrive together (sorted or
     // clustered inputs such as l_orderkey), so per 64-row half block: (1) a thread folds its two
@@ -410,7 +413,7 @@ struct Gen {
     // from lane to lane, (3) only the last lane of a run probes the table and issues the
     // atomics.  Any two rows with equal keys may be folded, so this is exact for every input;
     // it just saves nothing when neighbours differ.
-    out("    u64 SK[4]; bool SN[4], SA[4];\n");
+    out("    u64 SK[4], SH[4]; bool SN[4], SA[4];\n");
     for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4];\n", live_cells[i]);
     out("    _Pragma(\"unroll\") for (int pr = 0; pr < 2; ++pr) {\n");
     out("      const int j0 = 2 * pr, j1 = j0 + 1;\n");
@@ -444,13 +447,14 @@ struct Gen {
     }
     out("      const bool next_link = __shfl_down_sync(0xffffffffu, (u32)link, 1) != 0u && lane < 31;\n");
     out("      SK[j0] = hk; SN[j0] = hn; SA[j0] = hasH;\n");
+    out("      SH[j0] = HOME[j0]; SH[j1] = p1 ? HOME[j1] : HOME[j0];\n");
     out("      SK[j1] = tk; SN[j1] = tn; SA[j1] = hasT && !next_link;\n");
     for (int i = 0; i < n_live; ++i) out("      SV%d[j0] = h%d; SV%d[j1] = t%d;\n", live_cells[i], live_cells[i], live_cells[i], live_cells[i]);
     out("    }\n");
     // the (up to) four segments of the thread probe the table together: their first reads and
     // their claims overlap instead of forming four dependent round trips to HBM
     {
-      out("    i64 SL[4]; bool PK[4];\n    hash_probe4<%d>(p, SK, SN, SA, SL, PK, inserted, accerr);\n", p.row_words);
+      out("    i64 SL[4]; bool PK[4];\n    hash_probe4<%d>(p, SK, SN, SA, SH, SL, PK, inserted, accerr);\n", p.row_words);
       // park what the first claim did not settle (or, buffer full, walk the table here)
       out("    if (p.ovf != nullptr) {\n      i64 OE[4]; ovf_reserve(p, PK, OE);\n");
       out("      _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n        if (!PK[sgm]) continue;\n");

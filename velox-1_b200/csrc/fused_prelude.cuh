@@ -440,14 +440,15 @@ __device__ __forceinline__ i64 hash_walk(const FusedParams& p, u64 key, u64 h, u
 }
 template <int ROW_WORDS>
 __device__ __forceinline__ void hash_probe4(const FusedParams& p, const u64 key[4], const bool isnull[4],
-                                            const bool active[4], i64 slot[4], bool parked[4], u32& inserted, u32& err) {
+                                            const bool active[4], const u64 home[4], i64 slot[4], bool parked[4],
+                                            u32& inserted, u32& err) {
   u64* table = p.table;
   u64 h[4], seen[4];
   bool pend[4];
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     pend[s] = active[s] && !isnull[s] && key[s] != VGF_EMPTY_KEY;
-    h[s] = pend[s] ? home_slot(p, key[s]) : 0ull;
+    h[s] = pend[s] ? home[s] : 0ull; // home_slot(p, key[s]), computed by the caller (it also prefetched that line)
     slot[s] = -1;
   }
   // Round 1 claims the home slots directly (one atomic round trip, all four in flight together;
