@@ -705,10 +705,12 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     uint64_t known = 0;
     if (a.table) { rc = read_group_count(a, stream, &known); if (rc) return rc; }
     const int64_t rem = total - done;
-    // every row of a piece may start a group: a piece may take the table to 7/8 full at worst
-    // (the reference rehashes at the same load, velox/exec/HashTable.h:562-565); tables are sized
-    // for <= 50 % load, so real inputs with repeated keys stay far below that
-    const uint64_t limit = a.capacity - a.capacity / 8;
+    // every row of a piece may start a group: a piece may take the table to 15/16 full at worst (still
+    // terminating; the reference rehashes at 7/8, velox/exec/HashTable.h:562-565).  Tables are sized for <= 25-50 %
+    // load from the group-count hint, so real inputs with repeated keys stay far below that; the looser bound only
+    // keeps a batch that is slightly larger than 7/8 of the table from being split into a second, tiny piece
+    // (one more host read of the group count and two more launches: ~0.04 ms of C3's 0.74).
+    const uint64_t limit = a.capacity - a.capacity / 16;
     uint64_t room = limit > known ? limit - known : 0;
     if (room < (uint64_t)std::min<int64_t>(rem, kTile)) {
       uint64_t want = known + (uint64_t)std::min<int64_t>(rem, std::max<int64_t>(4 << 20, (int64_t)known));
@@ -721,7 +723,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       if (!env_factor && next_pow2(table_factor * want) * (uint64_t)a.row_words * 8 > (8ull << 30)) table_factor = 2;
       rc = hash_resize(a, next_pow2(table_factor * want), stream);
       if (rc) return rc;
-      room = a.capacity - a.capacity / 8 - known;
+      room = a.capacity - a.capacity / 16 - known;
     }
     int64_t piece = std::min<int64_t>(rem, (int64_t)room);
     if (piece < rem) piece = std::max<int64_t>(kTile, piece / kTile * kTile); // keep slices tile aligned
