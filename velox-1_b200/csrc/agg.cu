@@ -702,9 +702,13 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
   int64_t done = 0;
   std::vector<vgpu_column> sliced(ncols);
   while (done < total) {
-    uint64_t known = 0;
-    if (a.table) { rc = read_group_count(a, stream, &known); if (rc) return rc; }
     const int64_t rem = total - done;
+    uint64_t known = 0;
+    if (a.table) {
+      // the exact count costs a stream synchronise: skip it while even "every row so far was a new group" fits
+      if (a.groups_bound + (uint64_t)rem <= a.capacity - a.capacity / 16) known = a.groups_bound;
+      else { rc = read_group_count(a, stream, &known); if (rc) return rc; a.groups_bound = known; }
+    }
     // every row of a piece may start a group: a piece may take the table to 15/16 full at worst (still
     // terminating; the reference rehashes at 7/8, velox/exec/HashTable.h:562-565).  Tables are sized for <= 25-50 %
     // load from the group-count hint, so real inputs with repeated keys stay far below that; the looser bound only
@@ -762,6 +766,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       count_launch();
     }
     done += piece;
+    a.groups_bound += (uint64_t)piece;
   }
   return VGPU_OK;
 }
@@ -836,6 +841,7 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
     int rc = hash_resize(a, next_pow2(2 * (known + (uint64_t)n)), stream);
     if (rc) return rc;
   }
+  a.groups_bound = known + (uint64_t)n;
   for (int c = 1; c < a.n_cells; ++c) {
     if (a.cells[c].kind == kCellCount && a.hash_aliased[c]) { int rc = hash_materialize(a, c, stream); if (rc) return rc; }
   }
@@ -902,6 +908,7 @@ int agg_reset(Agg& a, cudaStream_t stream) {
     }
     for (int c = 0; c < kMaxCells; ++c) a.hash_aliased[c] = true;
     VG_CUDA(cudaMemsetAsync(a.ctr, 0, sizeof(unsigned long long), stream));
+    a.groups_bound = 0;
   } else {
     const size_t words = (size_t)a.n_cells * a.n_groups;
     init_state_kernel<<<(int)((words + 255) / 256), 256, 0, stream>>>(a.state, cell_meta(a), a.n_groups);

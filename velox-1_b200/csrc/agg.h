@@ -36,6 +36,8 @@ struct Agg {
   // HASH
   uint64_t* table = nullptr;
   uint64_t capacity = 0;       // power of two; table has capacity + 2 rows
+  uint64_t groups_bound = 0;   // host-side upper bound of the groups in the table (rows added so far): lets add_input
+                               // skip the device read of the exact count while the bound still fits the table
   int row_words = 0;
   uint8_t shifts[kMaxKeys] = {0};
   bool hash_aliased[kMaxCells]; // count cell still equals the rows cell (never updated on its own)
