@@ -4,8 +4,6 @@ import importlib
 
 import numpy as np
 
-import np_oracle as orc
-
 pkg = importlib.import_module("velox-1_b200")
 abi, ex = pkg.abi, pkg.expr
 
@@ -57,6 +55,7 @@ def oracle_cols(cols):
 
 def run_oracle_agg(filter_expr, outputs, cols, n, keys, accs, ignore_null_keys=False):
     """Oracle result {key tuple: [(value, nn)]} for accumulators given as (kind, output index)."""
+    import np_oracle as orc  # imported here so that bench.py / tools can use the query shapes without loading the oracle
     sel, outs = orc.filter_project(filter_expr, outputs, cols, n)
     key_cols = [outs[k[0]] for k in keys]
     acc_in = [(KIND_NAME[kind], None if idx < 0 else outs[idx]) for kind, idx in accs]
