@@ -233,7 +233,8 @@ int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t
                         const vgpu_out_column* outs, void* stream);
 
 /* Synchronises `stream` and returns VGPU_ERR_USER (with the Velox-style message) when a kernel
- * launched through this library latched a data error since the last check. */
+ * launched through this library on the current device latched a data error since the last check
+ * (FilterProject calls and every aggregation; see vgpu_agg_check_errors for one aggregation). */
 int vgpu_check_errors(void* stream);
 
 /* ---- HashAggregation ---------------------------------------------------------------------- */
@@ -301,6 +302,17 @@ int vgpu_agg_add_input(vgpu_agg_t agg, vgpu_program_t program, const vgpu_column
                        int32_t ncols, int64_t nrows, const int32_t* in_rows, int64_t n_in_rows,
                        void* stream);
 
+/* End of input (HashAggregation::noMoreInput, velox/exec/HashAggregation.cpp:466-472): completes the device-side
+ * aggregation asynchronously on `stream`.  HASH aggregations log run-aggregated {key, accumulators} entries while
+ * scanning and deduplicate them here (radix partition + shared-memory tables); the other modes have nothing left to
+ * do.  Implied by vgpu_agg_num_groups / vgpu_agg_extract / vgpu_agg_partition; more input may follow. */
+int vgpu_agg_finalize(vgpu_agg_t agg, void* stream);
+
+/* Like vgpu_check_errors, for the data errors (sum overflow, checked arithmetic in fused projections, key domain)
+ * latched by this aggregation's kernels only: with N drivers per device every operator instance raises its own
+ * errors, as exceptions thrown out of HashAggregation::addInput do (velox/exec/Driver.cpp:536-586). */
+int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream);
+
 /* Number of groups so far (synchronises the stream). */
 int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* num_groups);
 
@@ -343,14 +355,33 @@ int vgpu_comm_alltoallv(vgpu_comm_t comm, const void* send, const int64_t* send_
 int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t bytes,
                         void* stream);
 
+/* Peer-mapped window (collective; every rank passes the same size): each rank allocates `bytes` of device memory,
+ * publishes a CUDA IPC handle and maps every peer's window, so that exchange kernels store their output straight into
+ * the destination GPU's memory over NVLink / NVSwitch.  Two halves serve alternate exchanges; each half holds one
+ * region per source rank.  For a HASH exchange of E entries of w words per rank, 2 * 1.3 * E * w * 8 bytes is ample.
+ * *mapped (may be NULL) = 1 when every rank mapped every peer; otherwise the window is dropped on all ranks and
+ * vgpu_comm_exchange_groups moves the payload with NCCL (the same result). */
+int vgpu_comm_reserve_window(vgpu_comm_t comm, size_t bytes, int32_t* mapped);
+
+/* Count matrix of the last window exchange of a HASH aggregation: matrix[src * world + dst] = entries src stored into
+ * dst's window (HOST array of world * world int64).  Synchronises the stream. */
+int vgpu_comm_last_counts(vgpu_comm_t comm, int64_t* matrix, void* stream);
+
 /* The whole exchange step between a partial and a final aggregation of the same description
  * (partialAggregation -> partitionedOutput -> exchange -> finalAggregation,
  * velox/exec/tests/MultiFragmentTest.cpp:180-212): group g goes to rank mix64(key) % world.
- *   GLOBAL / ARRAY aggregations (small key domains): every rank all-gathers its dense group state
- *     (fixed size, no counts) and folds the groups it owns — no host synchronisation at all.
- *   HASH aggregations: vgpu_agg_partition, counts all-gather, vgpu_comm_alltoallv, vgpu_agg_merge_rows.
- * `final_agg` must have seen an (empty) vgpu_agg_add_input.  *bytes_sent (host, may be NULL) receives
- * the payload bytes this rank sent to other ranks. */
+ * With a mapped window (vgpu_comm_reserve_window) and no host synchronisation anywhere:
+ *   GLOBAL / ARRAY aggregations (small key domains): one kernel stores this rank's dense group state into every
+ *     peer's window, raises an epoch flag, waits for the peers' flags and folds the groups this rank owns.
+ *   HASH aggregations (log engine): one kernel hash-partitions the partial stage's logged {key, accumulators}
+ *     entries and stores each destination's share into that peer's window; the per-destination counts travel in one
+ *     small ncclAllGather (the only inter-rank synchronisation); the final aggregation deduplicates what it received
+ *     (and is finalized on return, asynchronously).
+ * Without a window: dense ncclAllGather / vgpu_agg_partition + counts all-gather + vgpu_comm_alltoallv +
+ * vgpu_agg_merge_rows (one host synchronisation for the counts).
+ * `final_agg` must have seen an (empty) vgpu_agg_add_input and be reset before the exchange after next.
+ * *bytes_sent (host, may be NULL) receives the payload bytes this rank sent to other ranks, or -1 when only the
+ * device knows (HASH through the window: see vgpu_comm_last_counts). */
 int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg_t final_agg, void* stream,
                               int64_t* bytes_sent);
 
@@ -377,6 +408,18 @@ int vgpu_debug_last_kernel_source(char* buf, size_t cap, uint64_t* hash);
 /* How the last shape was handled on this thread: "built from aot|disk|nvrtc", "declined: ...",
  * "nvrtc failed: ...". */
 int vgpu_debug_last_kernel_note(char* buf, size_t cap);
+
+/* State of a HASH aggregation's engine, for tests and bench lines: info[0] engine (0 undecided, 1 log, 2 table),
+ * and for a finalized log engine [1] sorted input detected, [2] front entries (whole groups when sorted),
+ * [3] entries deduplicated, [4] groups the deduplication produced, [5] hash partitions, [6] 8-byte words per entry,
+ * [7] host-side upper bound of the logged entries.  Synchronises the stream. */
+int vgpu_debug_agg_info(vgpu_agg_t agg, void* stream, int64_t info[8]);
+
+/* Every rank of a `world`-rank window exchange emulated on the CURRENT device (rank r: partials[r] -> finals[r]); for
+ * boxes with fewer GPUs than ranks.  Runs the kernels of vgpu_comm_exchange_groups' window path (partition + store,
+ * dedicated-group slots, receiver-side deduplication; dense store / fold for GLOBAL and ARRAY) with local buffers as
+ * windows and a device copy in place of the count all-gather.  The finals hold extracted groups on return. */
+int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t world, size_t window_bytes, void* stream);
 
 /* Timing of the scan kernels (the fused / interpreter kernel of vgpu_agg_add_input and
  * vgpu_filter_project, not the small bookkeeping kernels): while on, CUDA events are recorded on

@@ -34,6 +34,9 @@ def main():
     ids = [engine.Exchange.make_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     exchange = engine.Exchange(rank, world, ids[0])
+    mapped = exchange.reserve_window(512 << 20)   # peer-mapped window: the fused partition + NVLink store path
+    if os.environ.get("VGPU_EXCHANGE") != "nccl":
+        assert mapped, "CUDA IPC window not mapped: the P2P exchange path was not exercised"
 
     sf = 0.1
     orders = 150000
@@ -63,10 +66,30 @@ def main():
 
     f, outs = H.q1_exprs()
     I32, I64, D = abi.INTEGER, abi.BIGINT, abi.DOUBLE
-    run("q1", abi.AGG_ARRAY, f, outs, H.Q1_COLS, [I32, I32, D, D, D, D, I32], H.Q1_KEYS, H.Q1_ACCS)
+    for rep in range(3):  # repeated exchanges alternate the window halves
+        run("q1", abi.AGG_ARRAY, f, outs, H.Q1_COLS, [I32, I32, D, D, D, D, I32], H.Q1_KEYS, H.Q1_ACCS)
+    f6, outs6 = H.q6_exprs()
+    q6_accs = [(abi.ACC_SUM_F64, 0), (abi.ACC_COUNT, -1)]
+    run("q6", abi.AGG_GLOBAL, f6, outs6, H.Q6_COLS, [I32, D, D, D], [], q6_accs)
     gb_accs = [(abi.ACC_SUM_F64, 1), (abi.ACC_COUNT, -1), (abi.ACC_MIN, 1), (abi.ACC_MAX, 1)]
-    for key in ("l_partkey", "l_orderkey"):
+    for key in ("l_partkey", "l_orderkey", "l_orderkey"):
         run(key, abi.AGG_HASH, None, [ex.col(0, I64), ex.col(1, D)], [key, "l_extendedprice"], [I64, D], [(0, 64, 0, 0)], gb_accs)
+    # NULL keys and the key equal to the tables' empty marker travel in the regions' dedicated slots
+    mine["k_special"] = np.where(mine["l_orderkey"] % 7 == 0, -1, mine["l_orderkey"] % 1000).astype(np.int64)
+    special_nn = (mine["l_orderkey"] % 5) != 0
+
+    def run_special():
+        cols = [engine.flat_column(I64, mine["k_special"], special_nn), engine.flat_column(D, mine["l_extendedprice"])]
+        outs_s = [ex.col(0, I64), ex.col(1, D)]
+        prog = engine.Program(None, outs_s)
+        empty = [engine.flat_column(I64, mine["k_special"][:0]), engine.flat_column(D, mine["l_extendedprice"][:0])]
+        partial = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], gb_accs)
+        final = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], gb_accs)
+        partial.add_input(prog, cols, n)
+        final.add_input(prog, empty, 0)
+        exchange.shuffle(partial, final)
+        results["special"] = H.decode_rows(final.extract(), [(0, 64, 0, 0)], gb_accs, [I64, D], abi.AGG_HASH)
+    run_special()
     with open(os.path.join(scratch, f"rank{rank}.pkl"), "wb") as fh:
         pickle.dump(results, fh)
     dist.barrier()
@@ -83,6 +106,17 @@ def main():
             if name == "q1":
                 want = H.run_oracle_agg(f, outs, [(whole[c], None) for c in H.Q1_COLS], total, H.Q1_KEYS, H.Q1_ACCS)
                 H.assert_groups_equal(union, want, H.Q1_ACCS)
+            elif name == "q6":
+                want = H.run_oracle_agg(f6, outs6, [(whole[c], None) for c in H.Q6_COLS], total, [], q6_accs)
+                assert sum(len(p[name]) for p in parts) == 1, "a global aggregation reports one row over all ranks"
+                H.assert_groups_equal(union, want, q6_accs)
+            elif name == "special":
+                ks = np.where(whole["l_orderkey"] % 7 == 0, -1, whole["l_orderkey"] % 1000).astype(np.int64)
+                knn = (whole["l_orderkey"] % 5) != 0
+                want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(ks, knn), (whole["l_extendedprice"], None)], total,
+                                        [(0, 64, 0, 0)], gb_accs)
+                assert (None,) in union and (-1,) in union
+                H.assert_groups_equal(union, want, gb_accs)
             else:
                 want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(whole[name], None), (whole["l_extendedprice"], None)], total,
                                         [(0, 64, 0, 0)], gb_accs)

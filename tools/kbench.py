@@ -40,7 +40,7 @@ def main():
     ap.add_argument("--sf", type=float, default=10.0)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--only", default="q1,q6,q6fp,orderkey,c4")
+    ap.add_argument("--only", default="q1,q6,q6fp,orderkey,randkey,c4")
     args = ap.parse_args()
     pkg = importlib.import_module("velox-1_b200")
     abi = pkg.abi
@@ -110,26 +110,40 @@ def main():
         med, best = timed(lambda: engine.filter_project(prog, cols, n, want_nulls=False, sync=False), lambda: None)
         # reads 28 B/row, writes the projection (8 B/row), the bitmap and the selected row numbers
         report("C1 Q6 FilterProject (selection + projection)", 28 + 8 + 0.125, med, best)
-    if "orderkey" in want:
+    if "orderkey" in want or "randkey" in want:
         outs = [ex.col(0, I64), ex.col(1, D)]
-        cols = [flat("l_orderkey"), flat("l_extendedprice")]
         prog = engine.Program(None, outs)
         accs = [(abi.ACC_SUM_F64, 1)]
         groups = int(torch.unique_consecutive(data["l_orderkey"]).numel())
-        kmin, kmax = int(data["l_orderkey"].min()), int(data["l_orderkey"].max())
-        for label, spec in (("hashed", (0, 64, 0, 0)), ("ranged", (0, 64, kmin, kmax))):
-            agg = engine.Aggregation(abi.AGG_HASH, [spec], accs, expected_groups=groups)
-            med, best = timed(lambda: agg.add_input(prog, cols, n), agg.reset)
-            ng = agg.num_groups()
-            gbs = (n * 16 + ng * 16) / (med * 1e-3) / 1e9
-            if label == "hashed":
-                report("C3 GROUP BY l_orderkey (HASH sink, no key statistics)", 16, med, best,
-                       {"groups": ng, "alg_gbs_incl_output": round(gbs, 1), "frac_incl_output": round(gbs / peak(), 4)})
-            del agg
-        # 16 B/row input + 16 B/group output
-        gbs = (n * 16 + ng * 16) / (med * 1e-3) / 1e9
-        report("C3 GROUP BY l_orderkey (HASH sink, key range known)", 16, med, best,
-               {"groups": ng, "alg_gbs_incl_output": round(gbs, 1), "frac_incl_output": round(gbs / peak(), 4)})
+        cases = []
+        if "orderkey" in want:
+            cases.append(("C3 GROUP BY l_orderkey (sorted runs of 1-7)", data["l_orderkey"]))
+        if "randkey" in want:  # the same keys in random order: no runs to fold, nothing sorted
+            perm = torch.randperm(n, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
+            cases.append(("high-cardinality GROUP BY, same keys shuffled", data["l_orderkey"][perm].contiguous()))
+            del perm
+        for label, keycol in cases:
+            cols = [engine.DeviceColumn(I64, abi.FLAT, keycol, length=n), flat("l_extendedprice")]
+            for eng in ("log", "table"):
+                os.environ["VGPU_HASH_ENGINE"] = eng
+                agg = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], accs, expected_groups=groups)
+
+                def step():
+                    agg.add_input(prog, cols, n)
+                    agg.finalize()
+
+                # the table engine's reset wipes the whole table (init_table_kernel): time it inside the step as well
+                med_in, best_in = timed(lambda: (agg.reset(), step()), lambda: None)
+                med, best = timed(step, agg.reset)
+                ng = agg.num_groups()
+                info = agg.info()
+                gbs = (n * 16 + ng * 16) / (med_in * 1e-3) / 1e9
+                report(f"{label} [{eng} engine]", 16, med_in, best_in,
+                       {"groups": ng, "ms_without_reset": round(med, 4), "alg_gbs_incl_output": round(gbs, 1),
+                        "frac_incl_output": round(gbs / peak(), 4), "engine_info": info,
+                        "note": "ms_median includes reset (table init for the table engine) + scan + finalize"})
+                del agg
+            os.environ.pop("VGPU_HASH_ENGINE", None)
     if "c4" in want:
         mode_base = torch.tensor([6, 5, 4, 3, 2, 1, 0, 3], dtype=torch.int32, device="cuda")
         mode_idx = (6 - data["l_shipmode"]).to(torch.int32)

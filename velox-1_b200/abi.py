@@ -111,6 +111,8 @@ PROTOTYPES = {
     "vgpu_agg_destroy": [_P],
     "vgpu_agg_reset": [_P, _P],
     "vgpu_agg_add_input": [_P, _P, C.POINTER(Column), _I32, _I64, _P, _I64, _P],
+    "vgpu_agg_finalize": [_P, _P],
+    "vgpu_agg_check_errors": [_P, _P],
     "vgpu_agg_num_groups": [_P, _P, C.POINTER(_I64)],
     "vgpu_agg_row_bytes": [_P, C.POINTER(_I32)],
     "vgpu_agg_extract": [_P, _I64, _I64, _P, C.POINTER(_I64), _P],
@@ -123,11 +125,15 @@ PROTOTYPES = {
                             C.POINTER(_I64), _P],
     "vgpu_comm_allgather": [_P, _P, _P, _SZ, _P],
     "vgpu_comm_exchange_groups": [_P, _P, _P, _P, C.POINTER(_I64)],
+    "vgpu_comm_reserve_window": [_P, _SZ, C.POINTER(_I32)],
+    "vgpu_comm_last_counts": [_P, C.POINTER(_I64), _P],
     "vgpu_get_stats": [C.POINTER(Stats)],
     "vgpu_reset_stats": [],
     "vgpu_debug_set_dry_run": [C.c_int],
     "vgpu_debug_last_kernel_source": [C.c_char_p, _SZ, C.POINTER(C.c_uint64)],
     "vgpu_debug_last_kernel_note": [C.c_char_p, _SZ],
+    "vgpu_debug_agg_info": [_P, _P, C.POINTER(_I64)],
+    "vgpu_debug_exchange_local": [C.POINTER(_P), C.POINTER(_P), _I32, _SZ, _P],
     "vgpu_debug_kernel_timing": [C.c_int],
     "vgpu_debug_kernel_time": [C.POINTER(C.c_double), C.POINTER(_I64)],
 }

@@ -10,6 +10,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <string.h>
+
 #include <algorithm>
 
 #include "agg.h"
@@ -118,8 +120,8 @@ __global__ void extract_array_kernel(const uint64_t* state, int G, RowMap rm, in
 // One thread writes whole rows (16-byte stores when the row is a multiple of two words), no division
 // per word: the wipe of a 1 GB table runs at store bandwidth instead of at the integer-divide rate.
 __global__ void init_table_kernel(uint64_t* table, uint64_t n_slots, int row_words, CellMeta m) {
-  __shared__ uint64_t image[2 + kMaxCells];
-  for (int w = threadIdx.x; w < row_words && w < 2 + kMaxCells; w += blockDim.x) {
+  __shared__ uint64_t image[(1 + kMaxCells + 3) & ~3];
+  for (int w = threadIdx.x; w < row_words && w < ((1 + kMaxCells + 3) & ~3); w += blockDim.x) {
     uint64_t v = kEmptyKey;
     if (w > m.n_cells) {
       v = 0; // padding
@@ -391,7 +393,7 @@ static int find_or_add_cell(Agg& a, uint8_t kind, int input) {
 }
 
 // Builds the cell plan from the accumulator list once operand types are known.
-int agg_resolve(Agg& a, const Program& prog) {
+int agg_resolve(Agg& a, const Program& prog, cudaStream_t stream) {
   if (a.resolved) return VGPU_OK;
   a.n_cells = 0;
   find_or_add_cell(a, kCellCount, -1); // cell 0: passing rows per group
@@ -438,7 +440,8 @@ int agg_resolve(Agg& a, const Program& prog) {
     const size_t words = (size_t)a.n_cells * a.n_groups;
     if (!fused_dry_run()) {
       VG_CUDA(cudaMalloc(&a.state, words * 8));
-      init_state_kernel<<<(int)((words + 255) / 256), 256>>>(a.state, cell_meta(a), a.n_groups);
+      // on the caller's stream: cudaStreamNonBlocking streams have no implicit ordering with stream 0
+      init_state_kernel<<<(int)((words + 255) / 256), 256, 0, stream>>>(a.state, cell_meta(a), a.n_groups);
       VG_CUDA(cudaGetLastError());
       count_launch();
     }
@@ -451,6 +454,9 @@ int agg_resolve(Agg& a, const Program& prog) {
         continue;
       }
       if (ks.bits < 1 || ks.bits > 63) { set_error("key %zu: bits %d", k, ks.bits); return VGPU_ERR_INVALID; }
+      // ids are value - min + 1 (0 = NULL unless NULL keys are dropped): the largest one must fit the field
+      const uint64_t top = (uint64_t)ks.max - (uint64_t)ks.min + (a.ignore_null_keys ? 0u : 1u);
+      if (ks.max < ks.min || top > ((1ull << ks.bits) - 1ull)) { set_error("key %zu: domain [%lld, %lld] does not fit %d bits", k, (long long)ks.min, (long long)ks.max, ks.bits); return VGPU_ERR_INVALID; }
       a.shifts[k] = (uint8_t)shift;
       shift += ks.bits;
       if (shift > 63) { set_error("normalized key wider than 63 bits"); return VGPU_ERR_UNSUPPORTED; }
@@ -461,8 +467,9 @@ int agg_resolve(Agg& a, const Program& prog) {
     a.row_words = rw;
   }
   if (!fused_dry_run()) {
-    VG_CUDA(cudaMalloc(&a.ctr, 64 * sizeof(unsigned long long)));
-    VG_CUDA(cudaMemset(a.ctr, 0, 64 * sizeof(unsigned long long)));
+    a.err = err_word_acquire();
+    VG_CUDA(cudaMalloc(&a.ctr, kCtrWords * sizeof(unsigned long long)));
+    VG_CUDA(cudaMemsetAsync(a.ctr, 0, kCtrWords * sizeof(unsigned long long), stream));
   }
   a.resolved = true;
   return VGPU_OK;
@@ -470,7 +477,7 @@ int agg_resolve(Agg& a, const Program& prog) {
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
-constexpr int kOvfCursor = 40; // a.ctr: [0] groups, [1] scratch, [2..33] partition counts, [40] parked-segment cursor
+constexpr int kOvfCursor = kCtrOvfCursor;
 constexpr int kDefaultBucketBits = 6; // profiles/r01_c3_experiments.md: 3..7 measured within 4 % of each other
 static KeyMap key_map_of(const Agg& a) {
   KeyMap m{};
@@ -521,7 +528,7 @@ static int hash_resize(Agg& a, uint64_t capacity, cudaStream_t stream) {
   a.capacity = capacity;
   if (old) {
     VG_CUDA(cudaMemsetAsync(a.ctr, 0, sizeof(unsigned long long), stream));
-    rehash_kernel<<<(unsigned)((old_slots + 255) / 256), 256, 0, stream>>>(old, old_slots, href_of(a), device_err_word());
+    rehash_kernel<<<(unsigned)((old_slots + 255) / 256), 256, 0, stream>>>(old, old_slots, href_of(a), a.err);
     VG_CUDA(cudaGetLastError());
     count_launch();
     VG_CUDA(cudaStreamSynchronize(stream));
@@ -608,9 +615,24 @@ static int hash_materialize(Agg& a, int cell, cudaStream_t stream) {
   return VGPU_OK;
 }
 
+// LOG -> TABLE: finalize, expand the groups to ABI rows and fold them into the HBM table.
+static int log_migrate_to_table(Agg& a, cudaStream_t stream) {
+  int rc = agg_extract_all(a, stream); // finalize + expand into a.packed
+  if (rc) return rc;
+  const int64_t n = a.packed_rows;
+  uint64_t* rows = a.packed;
+  a.packed = nullptr; a.packed_cap = 0; a.packed_rows = -1;
+  a.engine = kEngineTable;
+  log_reset(a, stream);
+  rc = n > 0 ? agg_merge_rows(a, rows, n, stream) : VGPU_OK;
+  cudaStreamSynchronize(stream);
+  cudaFree(rows);
+  return rc;
+}
+
 int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t ncols, int64_t nrows,
                   const int32_t* in_rows, int64_t n_in_rows, cudaStream_t stream) {
-  int rc = agg_resolve(a, prog);
+  int rc = agg_resolve(a, prog, stream);
   if (rc) return rc;
   a.packed_rows = -1;
   const int64_t total = in_rows ? n_in_rows : nrows;
@@ -620,6 +642,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
     if (rc) return rc;
     p.mode = kSinkArray;
+    p.err_word = a.err;
     GroupMap gm;
     rc = fill_sink(a, p, &gm);
     if (rc) return rc;
@@ -640,7 +663,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
         rc = fused_launch(fk, p, fgrid, stream);
         if (rc) return rc;
         const int cells = a.n_cells * Gc;
-        merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, fgrid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
+        merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, fgrid, cell_meta(a), Gc, a.n_groups, gm, a.err);
         VG_CUDA(cudaGetLastError());
         count_launch();
         return VGPU_OK;
@@ -682,10 +705,59 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = launch_pipeline(p, tab, grid, stream);
     if (rc) return rc;
     const int cells = a.n_cells * Gc;
-    merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), Gc, a.n_groups, gm, device_err_word());
+    merge_partials_kernel<<<(cells + 7) / 8, 256, 0, stream>>>(a.state, a.partials, grid, cell_meta(a), Gc, a.n_groups, gm, a.err);
     VG_CUDA(cudaGetLastError());
     count_launch();
     return VGPU_OK;
+  }
+  // LOG engine (hashagg.cu): the scan appends run-aggregated entries, finalize deduplicates them.  Used while
+  // every batch has a plan-specialised kernel and updates only cells the entry layout holds; the first batch that
+  // does not moves the groups into the HBM table (TABLE engine) for good.
+  // (the variable is read per call so that tools can compare the two engines in one process)
+  const bool log_enabled = !(getenv("VGPU_HASH_ENGINE") && strcmp(getenv("VGPU_HASH_ENGINE"), "table") == 0);
+  if ((log_enabled || a.engine == kEngineLog) && a.engine != kEngineTable) {
+    rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
+    if (rc) return rc;
+    p.err_word = a.err;
+    p.mode = kSinkLog;
+    rc = fill_sink(a, p);
+    if (rc) return rc;
+    bool ok = true;
+    if (a.engine == kEngineUndecided) { rc = log_setup(a, p, stream); if (rc) return rc; }
+    else ok = log_layout_covers(a, p);
+    FusedKernel* fk = nullptr;
+    int fgrid = 0;
+    if (ok) {
+      p.log_entry_words = a.ew;
+      p.log_n_cells = a.log_n_cells;
+      for (int i = 0; i < a.log_n_cells; ++i) p.log_cells[i] = a.log_cells[i];
+      // sorted-input probe: one raw 64-bit key read straight from a FLAT BIGINT column without NULLs, no filter
+      p.sorted_probe = 0;
+      if (prog.filter.kind == VGPU_OPND_NONE && a.keys.size() == 1 && a.keys[0].bits == 64 && in_rows == nullptr) {
+        const vgpu_operand& ko = p.outputs[a.keys[0].output];
+        if (ko.kind == VGPU_OPND_COL && p.cols[ko.index].encoding == VGPU_FLAT && p.cols[ko.index].type == VGPU_BIGINT && p.cols[ko.index].nulls == nullptr) {
+          p.sorted_probe = 1;
+          p.sorted_key_col = ko.index;
+        }
+      }
+      fk = fused_prepare(p, &fgrid);
+      if (fused_dry_run()) return VGPU_OK;
+    }
+    if (fk) {
+      a.engine = kEngineLog;
+      const int warps = fused_kernel_threads(fk) / 32;
+      const uint64_t n_blocks = ((uint64_t)p.n_rows + 127) / 128;
+      const uint64_t per_warp = (n_blocks + (uint64_t)fgrid * warps - 1) / ((uint64_t)fgrid * warps);
+      rc = log_begin_batch(a, p, fgrid, per_warp * warps * 128, stream);
+      if (rc) return rc;
+      a.log_bound += (uint64_t)p.n_rows;
+      a.finalized = false;
+      return fused_launch(fk, p, fgrid, stream);
+    }
+    if (fused_dry_run()) return VGPU_OK;
+    if (a.engine == kEngineLog) { rc = log_migrate_to_table(a, stream); if (rc) return rc; }
+    a.engine = kEngineTable;
+    p = PipelineParams{};
   }
   if (fused_dry_run()) {
     rc = plan_pipeline(prog, cols, ncols, nrows, in_rows, n_in_rows, p);
@@ -698,6 +770,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     fused_prepare(p, &fgrid);
     return VGPU_OK;
   }
+  a.engine = kEngineTable;
   // HASH: walk the batch in pieces small enough that the table cannot fill up.
   int64_t done = 0;
   std::vector<vgpu_column> sliced(ncols);
@@ -737,6 +810,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = plan_pipeline(prog, use, ncols, piece, in_rows ? in_rows + done : nullptr, piece, p);
     if (rc) return rc;
     p.mode = kSinkHash;
+    p.err_word = a.err;
     rc = fill_sink(a, p);
     if (rc) return rc;
     for (int c = 1; c < a.n_cells; ++c) {
@@ -761,7 +835,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
     if (rc) return rc;
     if (p.ovf) {
-      drain_overflow_kernel<<<num_sms() * 8, 256, 0, stream>>>(a.ovf, a.ctr + kOvfCursor, a.ovf_cap, href_of(a), cell_meta(a), device_err_word());
+      drain_overflow_kernel<<<num_sms() * 8, 256, 0, stream>>>(a.ovf, a.ctr + kOvfCursor, a.ovf_cap, href_of(a), cell_meta(a), a.err);
       VG_CUDA(cudaGetLastError());
       count_launch();
     }
@@ -775,6 +849,29 @@ int agg_extract_all(Agg& a, cudaStream_t stream) {
   if (a.packed_rows >= 0) return VGPU_OK;
   if (!a.resolved) { set_error("aggregation has seen no input; call add_input (an empty batch is fine) first"); return VGPU_ERR_INVALID; }
   size_t max_rows;
+  if (a.mode == VGPU_AGG_HASH && a.engine == kEngineLog) {
+    int rc = log_finalize(a, stream);
+    if (rc) return rc;
+    FinHeader h{};
+    uint64_t n_special = 0;
+    rc = log_read_header(a, stream, &h, &n_special);
+    if (rc) return rc;
+    if (h.overflow) { set_error("internal: a hash partition overflowed its shared-memory table"); return VGPU_ERR_INVALID; }
+    max_rows = (size_t)(h.n_groups + (h.sorted ? h.n_front : 0) + n_special);
+    if (max_rows > a.packed_cap || a.packed == nullptr) {
+      if (a.packed) VG_CUDA(cudaFree(a.packed));
+      a.packed_cap = std::max<size_t>(max_rows, 16);
+      VG_CUDA(cudaMalloc(&a.packed, a.packed_cap * a.rm.row_words_out * 8));
+    }
+    VG_CUDA(cudaMemsetAsync(a.ctr + 1, 0, sizeof(unsigned long long), stream));
+    rc = log_expand_rows(a, a.packed, a.ctr + 1, stream);
+    if (rc) return rc;
+    unsigned long long n = 0;
+    VG_CUDA(cudaMemcpyAsync(&n, a.ctr + 1, sizeof(n), cudaMemcpyDeviceToHost, stream));
+    VG_CUDA(cudaStreamSynchronize(stream));
+    a.packed_rows = (int64_t)n;
+    return VGPU_OK;
+  }
   if (a.mode == VGPU_AGG_HASH) {
     uint64_t known = 0;
     if (a.table) { int rc = read_group_count(a, stream, &known); if (rc) return rc; }
@@ -801,7 +898,7 @@ int agg_extract_all(Agg& a, cudaStream_t stream) {
       count_launch();
     }
   } else {
-    extract_array_kernel<<<(a.n_groups + 255) / 256, 256, 0, stream>>>(a.state, a.n_groups, a.rm, a.mode == VGPU_AGG_GLOBAL ? 1 : 0, a.packed, a.ctr + 1);
+    extract_array_kernel<<<(a.n_groups + 255) / 256, 256, 0, stream>>>(a.state, a.n_groups, a.rm, a.mode == VGPU_AGG_GLOBAL && a.emit_empty_global ? 1 : 0, a.packed, a.ctr + 1);
     VG_CUDA(cudaGetLastError());
     count_launch();
   }
@@ -830,11 +927,13 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
   if (n <= 0) return VGPU_OK;
   const DoneMap dm = done_map(a.rm);
   if (a.mode != VGPU_AGG_HASH) {
-    merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, a.state, a.n_groups, device_err_word(), 0, 0);
+    merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, a.state, a.n_groups, a.err, 0, 0);
     VG_CUDA(cudaGetLastError());
     count_launch();
     return VGPU_OK;
   }
+  if (a.engine == kEngineLog) { int rc = log_migrate_to_table(a, stream); if (rc) return rc; }
+  a.engine = kEngineTable;
   uint64_t known = 0;
   if (a.table) { int rc = read_group_count(a, stream, &known); if (rc) return rc; }
   if (a.capacity / 2 < known + (uint64_t)n) {
@@ -845,7 +944,7 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
   for (int c = 1; c < a.n_cells; ++c) {
     if (a.cells[c].kind == kCellCount && a.hash_aliased[c]) { int rc = hash_materialize(a, c, stream); if (rc) return rc; }
   }
-  merge_rows_hash_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), device_err_word());
+  merge_rows_hash_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, dm, href_of(a), a.err);
   VG_CUDA(cudaGetLastError());
   count_launch();
   return VGPU_OK;
@@ -863,7 +962,7 @@ int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int m
   if (a.mode == VGPU_AGG_HASH || !a.resolved) { set_error("owned-row merge needs a resolved ARRAY / GLOBAL aggregation"); return VGPU_ERR_INVALID; }
   a.packed_rows = -1;
   if (n <= 0) return VGPU_OK;
-  merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, done_map(a.rm), a.state, a.n_groups, device_err_word(), n_parts, my_part);
+  merge_rows_array_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>((const uint64_t*)rows, n, a.rm, done_map(a.rm), a.state, a.n_groups, a.err, n_parts, my_part);
   VG_CUDA(cudaGetLastError());
   count_launch();
   return VGPU_OK;
@@ -897,7 +996,12 @@ int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cuda
 
 int agg_reset(Agg& a, cudaStream_t stream) {
   a.packed_rows = -1;
+  a.emit_empty_global = true;
   if (!a.resolved) return VGPU_OK;
+  if (a.mode == VGPU_AGG_HASH && a.engine != kEngineTable) {
+    // the entry layout and the slabs stay; a later ineligible batch may still move to the TABLE engine
+    return log_reset(a, stream);
+  }
   if (a.mode == VGPU_AGG_HASH) {
     if (a.table) { // keep the allocation, wipe it in place
       const uint64_t slots = a.capacity + 2;
@@ -918,7 +1022,15 @@ int agg_reset(Agg& a, cudaStream_t stream) {
   return VGPU_OK;
 }
 
+int agg_finalize(Agg& a, cudaStream_t stream) {
+  if (a.mode == VGPU_AGG_HASH && a.engine == kEngineLog) return log_finalize(a, stream);
+  return VGPU_OK; // the other sinks keep their groups final after every batch
+}
+
 void agg_free(Agg& a) {
+  log_free(a);
+  err_word_release(a.err);
+  a.err = nullptr;
   cudaFree(a.state); cudaFree(a.partials); cudaFree(a.table); cudaFree(a.ctr); cudaFree(a.packed); cudaFree(a.ovf);
   a.ovf = nullptr; a.ovf_cap = 0;
   a.state = a.partials = a.table = a.packed = nullptr; a.ctr = nullptr;

@@ -32,19 +32,52 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 static std::mutex g_mu;
-static uint32_t* g_err_words[64] = {nullptr};
+// Error words: one slab of kErrSlots 32-bit words per device.  Slot 0 is the device-wide word (kernels that belong to
+// no aggregation, i.e. FilterProject); every aggregation takes a slot of its own, so with N drivers on a device an
+// overflow in one operator is raised by that operator (vgpu_agg_check_errors), not by whoever checks first.
+constexpr int kErrSlots = 4096;
+static uint32_t* g_err_slab[64] = {nullptr};
+static std::vector<bool> g_err_used[64];
 static int g_sms[64] = {0};
 static vgpu_stats g_stats = {0, 0, 0, 0};
 
+static uint32_t* err_slab_locked(int dev) {
+  if (!g_err_slab[dev]) {
+    cudaMalloc(&g_err_slab[dev], kErrSlots * sizeof(uint32_t));
+    cudaMemset(g_err_slab[dev], 0, kErrSlots * sizeof(uint32_t));
+    cudaDeviceSynchronize(); // streams created with cudaStreamNonBlocking are not ordered after the legacy stream
+    g_err_used[dev].assign(kErrSlots, false);
+    g_err_used[dev][0] = true;
+  }
+  return g_err_slab[dev];
+}
 uint32_t* device_err_word() {
   int dev = 0;
   cudaGetDevice(&dev);
   std::lock_guard<std::mutex> l(g_mu);
-  if (!g_err_words[dev]) {
-    cudaMalloc(&g_err_words[dev], 64);
-    cudaMemset(g_err_words[dev], 0, 64);
+  return err_slab_locked(dev);
+}
+uint32_t* err_word_acquire() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> l(g_mu);
+  uint32_t* base = err_slab_locked(dev);
+  if (!base) return nullptr;
+  for (int i = 1; i < kErrSlots; ++i) {
+    if (!g_err_used[dev][i]) { g_err_used[dev][i] = true; return base + i; }
   }
-  return g_err_words[dev];
+  return base; // out of slots: share the device-wide word
+}
+void err_word_release(uint32_t* w) {
+  if (!w) return;
+  std::lock_guard<std::mutex> l(g_mu);
+  for (int dev = 0; dev < 64; ++dev) {
+    if (g_err_slab[dev] && w > g_err_slab[dev] && w < g_err_slab[dev] + kErrSlots) {
+      // a latched error nobody collected must not leak into the slot's next owner
+      cudaMemset(w, 0, sizeof(uint32_t));
+      g_err_used[dev][w - g_err_slab[dev]] = false;
+    }
+  }
 }
 // ---- kernel timing (diagnostics) -------------------------------------------------------------
 static bool g_timing = false;
@@ -100,8 +133,6 @@ static int validate_operand(const vgpu_operand& o, bool allow_none, int n_cols, 
 
 using namespace vg;
 
-struct vgpu_program_s { Program prog; };
-struct vgpu_agg_s { Agg agg; };
 
 extern "C" {
 
@@ -178,19 +209,28 @@ int vgpu_get_stats(vgpu_stats* out) {
 }
 int vgpu_reset_stats(void) { g_stats = vgpu_stats{0, 0, 0, 0}; return VGPU_OK; }
 
-int vgpu_check_errors(void* stream) {
-  uint32_t* w = device_err_word();
-  uint32_t bits = 0;
-  VG_CUDA(cudaMemcpyAsync(&bits, w, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
-  VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+static int report_error_bits(uint32_t bits) {
   if (!bits) return VGPU_OK;
-  VG_CUDA(cudaMemsetAsync(w, 0, 4, (cudaStream_t)stream));
   if (bits & kErrDivZero) set_error("division by zero");
   else if (bits & kErrOverflow) set_error("integer overflow");
   else if (bits & kErrCastRange) set_error("Cannot cast value: out of range or NaN");
   else if (bits & kErrKeyRange) { set_error("grouping key outside the declared domain"); return VGPU_ERR_INVALID; }
   else { set_error("internal: hash table full"); return VGPU_ERR_INVALID; }
   return VGPU_ERR_USER;
+}
+
+// Every error word of the device (the device-wide one and those of all aggregations).
+int vgpu_check_errors(void* stream) {
+  uint32_t* slab = device_err_word();
+  static thread_local std::vector<uint32_t> host;
+  host.resize(kErrSlots);
+  VG_CUDA(cudaMemcpyAsync(host.data(), slab, kErrSlots * sizeof(uint32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  uint32_t bits = 0;
+  for (uint32_t w : host) bits |= w;
+  if (!bits) return VGPU_OK;
+  VG_CUDA(cudaMemsetAsync(slab, 0, kErrSlots * sizeof(uint32_t), (cudaStream_t)stream));
+  return report_error_bits(bits);
 }
 
 // ---- programs -------------------------------------------------------------------------------
@@ -348,6 +388,20 @@ int vgpu_agg_add_input(vgpu_agg_t agg, vgpu_program_t program, const vgpu_column
   __atomic_fetch_add(&g_stats.rows_in, in_rows ? n_in_rows : nrows, __ATOMIC_RELAXED);
   return agg_add_input(agg->agg, program->prog, cols, ncols, nrows, in_rows, n_in_rows, (cudaStream_t)stream);
 }
+int vgpu_agg_finalize(vgpu_agg_t agg, void* stream) {
+  if (!agg) return VGPU_ERR_INVALID;
+  return agg_finalize(agg->agg, (cudaStream_t)stream);
+}
+int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream) {
+  if (!agg) return VGPU_ERR_INVALID;
+  if (!agg->agg.err) return VGPU_OK; // no kernel ran yet
+  uint32_t bits = 0;
+  VG_CUDA(cudaMemcpyAsync(&bits, agg->agg.err, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  if (!bits) return VGPU_OK;
+  VG_CUDA(cudaMemsetAsync(agg->agg.err, 0, 4, (cudaStream_t)stream));
+  return report_error_bits(bits);
+}
 int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* n) {
   if (!agg || !n) return VGPU_ERR_INVALID;
   int rc = agg_extract_all(agg->agg, (cudaStream_t)stream);
@@ -399,6 +453,25 @@ int vgpu_debug_last_kernel_note(char* buf, size_t cap) {
   return VGPU_OK;
 }
 
+// info[0] = engine of a HASH aggregation (0 undecided, 1 log, 2 table), then — log engine, after finalize —
+// [1] sorted input detected, [2] front entries, [3] entries deduplicated, [4] groups the deduplication produced,
+// [5] hash partitions, [6] words per entry, [7] upper bound of the logged entries.  Synchronises the stream.
+int vgpu_debug_agg_info(vgpu_agg_t agg, void* stream, int64_t info[8]) {
+  if (!agg || !info) return VGPU_ERR_INVALID;
+  Agg& a = agg->agg;
+  for (int i = 0; i < 8; ++i) info[i] = 0;
+  info[0] = a.mode == VGPU_AGG_HASH ? a.engine : -1;
+  if (a.mode == VGPU_AGG_HASH && a.engine == kEngineLog && a.finalized) {
+    FinHeader h{};
+    uint64_t nsp = 0;
+    int rc = log_read_header(a, (cudaStream_t)stream, &h, &nsp);
+    if (rc) return rc;
+    info[1] = (int64_t)h.sorted; info[2] = (int64_t)h.n_front; info[3] = (int64_t)h.n_dedupe; info[4] = (int64_t)h.n_groups;
+    info[5] = (int64_t)1 << (int)h.log2p; info[6] = a.ew; info[7] = (int64_t)a.log_bound;
+  }
+  return VGPU_OK;
+}
+
 int vgpu_debug_kernel_timing(int on) {
   std::lock_guard<std::mutex> l(g_mu);
   g_timing = on != 0;
@@ -424,142 +497,6 @@ int vgpu_debug_kernel_time(double* ms_total, int64_t* launches) {
   *ms_total = sum;
   *launches = n;
   return VGPU_OK;
-}
-
-// ---- multi-GPU exchange over NCCL (dlopen'ed) -------------------------------------------------
-namespace {
-typedef struct { char internal[128]; } nccl_unique_id;
-typedef void* nccl_comm;
-typedef int (*fn_get_unique_id)(nccl_unique_id*);
-typedef int (*fn_comm_init_rank)(nccl_comm*, int, nccl_unique_id, int);
-typedef int (*fn_comm_destroy)(nccl_comm);
-typedef int (*fn_send)(const void*, size_t, int, int, nccl_comm, cudaStream_t);
-typedef int (*fn_recv)(void*, size_t, int, int, nccl_comm, cudaStream_t);
-typedef int (*fn_group)(void);
-typedef int (*fn_allgather)(const void*, void*, size_t, int, nccl_comm, cudaStream_t);
-typedef const char* (*fn_errstr)(int);
-struct NcclApi {
-  void* handle = nullptr;
-  fn_get_unique_id get_unique_id; fn_comm_init_rank comm_init_rank; fn_comm_destroy comm_destroy;
-  fn_send send; fn_recv recv; fn_group group_start, group_end; fn_allgather allgather; fn_errstr errstr;
-};
-NcclApi g_nccl;
-constexpr int kNcclUint8 = 1; // ncclUint8 in nccl.h's ncclDataType_t
-
-int load_nccl() {
-  if (g_nccl.handle) return VGPU_OK;
-  const char* names[] = {"libnccl.so.2", "libnccl.so"};
-  void* h = nullptr;
-  for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
-  if (!h) { set_error("cannot load libnccl.so.2: %s", dlerror()); return VGPU_ERR_NCCL; }
-#define VG_SYM(field, name) g_nccl.field = (decltype(g_nccl.field))dlsym(h, name); if (!g_nccl.field) { set_error("libnccl lacks %s", name); return VGPU_ERR_NCCL; }
-  VG_SYM(get_unique_id, "ncclGetUniqueId") VG_SYM(comm_init_rank, "ncclCommInitRank") VG_SYM(comm_destroy, "ncclCommDestroy")
-  VG_SYM(send, "ncclSend") VG_SYM(recv, "ncclRecv") VG_SYM(group_start, "ncclGroupStart") VG_SYM(group_end, "ncclGroupEnd")
-  VG_SYM(allgather, "ncclAllGather") VG_SYM(errstr, "ncclGetErrorString")
-#undef VG_SYM
-  g_nccl.handle = h;
-  return VGPU_OK;
-}
-int nccl_fail(int rc, const char* what) { set_error("NCCL error %d (%s) in %s", rc, g_nccl.errstr(rc), what); return VGPU_ERR_NCCL; }
-#define VG_NCCL(x) do { int r_ = (x); if (r_ != 0) return nccl_fail(r_, #x); } while (0)
-} // namespace
-
-struct vgpu_comm_s {
-  nccl_comm comm; int rank, world;
-  // grow-only device scratch of vgpu_comm_exchange_groups
-  void* send = nullptr; size_t send_cap = 0;
-  void* recv = nullptr; size_t recv_cap = 0;
-  int64_t* dcounts = nullptr; // [world] + [world * world]
-};
-static int comm_reserve(void** p, size_t* cap, size_t want) {
-  if (*cap >= want) return VGPU_OK;
-  if (*p) { VG_CUDA(cudaDeviceSynchronize()); VG_CUDA(cudaFree(*p)); *p = nullptr; *cap = 0; }
-  want = std::max<size_t>(want + want / 4, 1 << 16);
-  VG_CUDA(cudaMalloc(p, want));
-  *cap = want;
-  return VGPU_OK;
-}
-
-int vgpu_comm_unique_id(uint8_t id[VGPU_COMM_ID_BYTES]) {
-  int rc = load_nccl();
-  if (rc) return rc;
-  nccl_unique_id u;
-  VG_NCCL(g_nccl.get_unique_id(&u));
-  memcpy(id, &u, VGPU_COMM_ID_BYTES);
-  return VGPU_OK;
-}
-int vgpu_comm_create(const uint8_t id[VGPU_COMM_ID_BYTES], int32_t rank, int32_t world, vgpu_comm_t* out) {
-  if (!id || !out || rank < 0 || rank >= world) return VGPU_ERR_INVALID;
-  int rc = load_nccl();
-  if (rc) return rc;
-  nccl_unique_id u;
-  memcpy(&u, id, VGPU_COMM_ID_BYTES);
-  vgpu_comm_s* c = new vgpu_comm_s();
-  c->rank = rank; c->world = world;
-  int r = g_nccl.comm_init_rank(&c->comm, world, u, rank);
-  if (r != 0) { delete c; return nccl_fail(r, "ncclCommInitRank"); }
-  *out = c;
-  return VGPU_OK;
-}
-int vgpu_comm_destroy(vgpu_comm_t comm) {
-  if (comm) { g_nccl.comm_destroy(comm->comm); cudaFree(comm->send); cudaFree(comm->recv); cudaFree(comm->dcounts); delete comm; }
-  return VGPU_OK;
-}
-int vgpu_comm_alltoallv(vgpu_comm_t comm, const void* send, const int64_t* send_counts, const int64_t* send_offsets,
-                        void* recv, const int64_t* recv_counts, const int64_t* recv_offsets, void* stream) {
-  if (!comm || !send_counts || !recv_counts || !send_offsets || !recv_offsets) return VGPU_ERR_INVALID;
-  VG_NCCL(g_nccl.group_start());
-  for (int r = 0; r < comm->world; ++r) {
-    if (send_counts[r] > 0) VG_NCCL(g_nccl.send((const char*)send + send_offsets[r], (size_t)send_counts[r], kNcclUint8, r, comm->comm, (cudaStream_t)stream));
-    if (recv_counts[r] > 0) VG_NCCL(g_nccl.recv((char*)recv + recv_offsets[r], (size_t)recv_counts[r], kNcclUint8, r, comm->comm, (cudaStream_t)stream));
-  }
-  VG_NCCL(g_nccl.group_end());
-  return VGPU_OK;
-}
-int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t bytes, void* stream) {
-  if (!comm) return VGPU_ERR_INVALID;
-  VG_NCCL(g_nccl.allgather(send, recv, bytes, kNcclUint8, comm->comm, (cudaStream_t)stream));
-  return VGPU_OK;
-}
-
-int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg_t final_agg, void* stream_, int64_t* bytes_sent) {
-  if (!comm || !partial_agg || !final_agg) return VGPU_ERR_INVALID;
-  cudaStream_t stream = (cudaStream_t)stream_;
-  Agg& pa = partial_agg->agg;
-  Agg& fa = final_agg->agg;
-  if (pa.mode != fa.mode || pa.accs.size() != fa.accs.size()) { set_error("partial and final aggregations differ"); return VGPU_ERR_INVALID; }
-  const size_t row_bytes = (3 + 2 * pa.accs.size()) * 8;
-  const int W = comm->world;
-  int rc;
-  if (pa.mode != VGPU_AGG_HASH) {
-    if (pa.n_groups != fa.n_groups) { set_error("partial and final aggregations differ in their key domains"); return VGPU_ERR_INVALID; }
-    const size_t mine = (size_t)pa.n_groups * row_bytes;
-    if ((rc = comm_reserve(&comm->send, &comm->send_cap, mine))) return rc;
-    if ((rc = comm_reserve(&comm->recv, &comm->recv_cap, mine * W))) return rc;
-    if ((rc = agg_dense_rows(pa, comm->send, stream))) return rc;
-    VG_NCCL(g_nccl.allgather(comm->send, comm->recv, mine, kNcclUint8, comm->comm, stream));
-    if (bytes_sent) *bytes_sent = (int64_t)(mine * (W - 1));
-    return agg_merge_owned_rows(fa, comm->recv, (int64_t)pa.n_groups * W, W, comm->rank, stream);
-  }
-  if ((rc = agg_extract_all(pa, stream))) return rc;
-  const int64_t n = pa.packed_rows;
-  if ((rc = comm_reserve(&comm->send, &comm->send_cap, (size_t)std::max<int64_t>(n, 1) * row_bytes))) return rc;
-  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * (32 + 32 * 32)));
-  int64_t counts[32] = {0}, matrix[32 * 32];
-  if ((rc = agg_partition(pa, W, comm->send, counts, stream))) return rc;
-  VG_CUDA(cudaMemcpyAsync(comm->dcounts, counts, sizeof(int64_t) * W, cudaMemcpyHostToDevice, stream));
-  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + 32, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
-  VG_CUDA(cudaMemcpyAsync(matrix, comm->dcounts + 32, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, stream));
-  VG_CUDA(cudaStreamSynchronize(stream));
-  int64_t sc[32], so[32], rcv[32], ro[32], srun = 0, rrun = 0;
-  for (int r = 0; r < W; ++r) { // matrix[src][dst]
-    sc[r] = counts[r] * (int64_t)row_bytes; so[r] = srun; srun += sc[r];
-    rcv[r] = matrix[r * W + comm->rank] * (int64_t)row_bytes; ro[r] = rrun; rrun += rcv[r];
-  }
-  if ((rc = comm_reserve(&comm->recv, &comm->recv_cap, (size_t)std::max<int64_t>(rrun, 8)))) return rc;
-  if ((rc = vgpu_comm_alltoallv(comm, comm->send, sc, so, comm->recv, rcv, ro, stream_))) return rc;
-  if (bytes_sent) *bytes_sent = srun - sc[comm->rank];
-  return agg_merge_rows(fa, comm->recv, rrun / (int64_t)row_bytes, stream);
 }
 
 } // extern "C"

@@ -279,9 +279,10 @@ struct Gen {
       }
       out("        const u64 u = k.v - %s;\n", hex((uint64_t)ks.min).c_str());
       out("        const bool bad = k.n ? %s : u > %s;\n", ks.nullable ? "false" : "true", hex((uint64_t)(ks.max - ks.min)).c_str());
-      out("        const u32 id = k.n ? 0u : (u32)u + %uu;\n", ks.nullable ? 1u : 0u);
-      if (hash) out("        key += (u64)id << %d;\n", (int)ks.shift);
-      else out("        g += id * %uu;\n", (unsigned)ks.mult);
+      // 64-bit ids: a 33-bit INTEGER field must not wrap into the NULL id (id 0)
+      out("        const u64 id = k.n ? 0ull : u + %uull;\n", ks.nullable ? 1u : 0u);
+      if (hash) out("        key += id << %d;\n", (int)ks.shift);
+      else out("        g += (u32)id * %uu;\n", (unsigned)ks.mult);
       out("        if (bad && pass) { ec |= VGF_ERR_KEYRANGE; raise = true; pass = false; } }\n");
     }
   }
@@ -385,7 +386,8 @@ struct Gen {
     out("    }\n");
   }
 
-  void gen_hash_body(bool full) {
+  // Rows of the block -> KEY / KN / PASS and the per-cell X / L arrays (HASH and LOG sinks).
+  void gen_keyed_rows(bool full) {
     if (full) gen_input_prefetch();
     gen_block_header(full);
     out("    u64 KEY[4]; bool KN[4], PASS[4];\n");
@@ -398,22 +400,24 @@ struct Gen {
       out("      X%d[j] = x%d; L%d[j] = l%d;\n", c, c, c, c);
     }
     out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
+    if (p.mode == kSinkLog && p.sorted_probe) {
+      // the batch's last row is the "row before" of the next batch's first one
+      out("      if (((j < 2 ? r0 : r1) + (j & 1)) == n - 1) { p.sort_prev_out[0] = key; p.sort_prev_out[1] = 1ull; }\n");
+    }
     gen_raise();
     out("    }\n");
-    // home slots of the rows' keys -> L2 while the run aggregation below computes
-    // (computed once per row and handed to the probe below: the hash is ~25 instructions)
-    out("    u64 HOME[4];\n");
-    out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
-    out("      HOME[j] = home_slot(p, KEY[j]);\n");
-    out("      if (PASS[j] && !KN[j] && (j == 0 || KEY[j] != KEY[j - 1])) prefetch_l2(p.table + HOME[j] * %d);\n", p.row_words);
-    out("    }\n");
-    // Run aggregation before the table is touched.  Equal keys tend to arrive together (sorted or
-    // clustered inputs such as l_orderkey), so per 64-row half block: (1) a thread folds its two
-    // rows when their keys match, (2) a segmented scan over the lanes carries a run's partial
-    // from lane to lane, (3) only the last lane of a run probes the table and issues the
-    // atomics.  Any two rows with equal keys may be folded, so this is exact for every input;
-    // it just saves nothing when neighbours differ.
-    out("    u64 SK[4], SH[4]; bool SN[4], SA[4];\n");
+  }
+
+  // Run aggregation before any group state is touched.  Equal keys tend to arrive together (sorted or
+  // clustered inputs such as l_orderkey), so per 64-row half block: (1) a thread folds its two
+  // rows when their keys match, (2) a segmented scan over the lanes carries a run's partial
+  // from lane to lane, (3) only the last lane of a run owns the run's segment.  Any two rows with
+  // equal keys may be folded, so this is exact for every input; it just saves nothing when
+  // neighbours differ.  Leaves up to four segments per thread: SK / SN (key), SA (active), SV<c> (cells)
+  // and, with_home, SH (home slot of the key in the HBM table).
+  void gen_run_aggregation(bool with_home) {
+    out("    u64 SK[4]; bool SN[4], SA[4];\n");
+    if (with_home) out("    u64 SH[4];\n");
     for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4];\n", live_cells[i]);
     out("    _Pragma(\"unroll\") for (int pr = 0; pr < 2; ++pr) {\n");
     out("      const int j0 = 2 * pr, j1 = j0 + 1;\n");
@@ -447,10 +451,22 @@ struct Gen {
     }
     out("      const bool next_link = __shfl_down_sync(0xffffffffu, (u32)link, 1) != 0u && lane < 31;\n");
     out("      SK[j0] = hk; SN[j0] = hn; SA[j0] = hasH;\n");
-    out("      SH[j0] = HOME[j0]; SH[j1] = p1 ? HOME[j1] : HOME[j0];\n");
+    if (with_home) out("      SH[j0] = HOME[j0]; SH[j1] = p1 ? HOME[j1] : HOME[j0];\n");
     out("      SK[j1] = tk; SN[j1] = tn; SA[j1] = hasT && !next_link;\n");
     for (int i = 0; i < n_live; ++i) out("      SV%d[j0] = h%d; SV%d[j1] = t%d;\n", live_cells[i], live_cells[i], live_cells[i], live_cells[i]);
     out("    }\n");
+  }
+
+  void gen_hash_body(bool full) {
+    gen_keyed_rows(full);
+    // home slots of the rows' keys -> L2 while the run aggregation below computes
+    // (computed once per row and handed to the probe below: the hash is ~25 instructions)
+    out("    u64 HOME[4];\n");
+    out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
+    out("      HOME[j] = home_slot(p, KEY[j]);\n");
+    out("      if (PASS[j] && !KN[j] && (j == 0 || KEY[j] != KEY[j - 1])) prefetch_l2(p.table + HOME[j] * %d);\n", p.row_words);
+    out("    }\n");
+    gen_run_aggregation(true);
     // the (up to) four segments of the thread probe the table together: their first reads and
     // their claims overlap instead of forming four dependent round trips to HBM
     {
@@ -473,6 +489,69 @@ struct Gen {
       out("        if (SV%d[sgm] != cell_identity<%d>()) hbm_update<%d>(p.table + SL[sgm] * %d + %d, SV%d[sgm], accerr);\n", c, p.cells[c].kind, p.cells[c].kind, p.row_words, 1 + c, c);
     }
     out("      }\n    }\n");
+  }
+
+  // LOG sink: the run-aggregated segments are appended to the CTA's region of the log.  A segment whose run cannot
+  // continue in a neighbouring half block goes to the front of the region, one that touches a half-block edge to
+  // the back; when the whole input turns out to be sorted by key, the front entries are complete groups and only
+  // the back entries need deduplication (hashagg.cu).  NULL keys and the key equal to the empty marker are rare and
+  // go to two dedicated rows with atomics.
+  void gen_log_body(bool full) {
+    gen_keyed_rows(full);
+    const int EW = p.log_entry_words;
+    if (p.sorted_probe) {
+      // adjacent rows must be in non-decreasing (unsigned) key order: inside the thread, lane to lane, half block to
+      // half block, and against the row before the block (the previous batch's last row for block 0)
+      out("    {\n");
+      if (full) out("      const bool ok1 = true, ok2 = true, ok3 = true, ok0 = true;\n");
+      else out("      const bool ok0 = r0 < n, ok1 = r0 + 1 < n, ok2 = r1 < n, ok3 = r1 + 1 < n;\n");
+      out("      bool bad = (ok1 && KEY[0] > KEY[1]) || (ok3 && KEY[2] > KEY[3]);\n");
+      out("      const u64 pk0 = __shfl_up_sync(0xffffffffu, KEY[1], 1), pk1 = __shfl_up_sync(0xffffffffu, KEY[3], 1);\n");
+      out("      const u64 last0 = __shfl_sync(0xffffffffu, KEY[1], 31);\n");
+      out("      u64 before = 0ull; bool have = false;\n");
+      out("      if (lane == 0) {\n");
+      out("        if (blk > 0) { before = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + (blk * 128 - 1)); have = true; }\n", p.sorted_key_col);
+      out("        else { before = p.sort_prev_in[0]; have = p.sort_prev_in[1] != 0ull; }\n");
+      out("      }\n");
+      out("      bad = bad || (ok0 && (lane > 0 ? pk0 > KEY[0] : (have && before > KEY[0])));\n");
+      out("      bad = bad || (ok2 && (lane > 0 ? pk1 > KEY[2] : last0 > KEY[2]));\n");
+      out("      viol = viol || bad;\n    }\n");
+    }
+    gen_run_aggregation(false);
+    out("    u32 KIND[4];\n");
+    if (p.sorted_probe && full) {
+      out("    const u64 KF0 = __shfl_sync(0xffffffffu, KEY[0], 0), KL0 = __shfl_sync(0xffffffffu, KEY[1], 31);\n");
+      out("    const u64 KF1 = __shfl_sync(0xffffffffu, KEY[2], 0), KL1 = __shfl_sync(0xffffffffu, KEY[3], 31);\n");
+    }
+    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n");
+    out("      const bool special = SN[sgm] || SK[sgm] == VGF_EMPTY_KEY;\n");
+    if (p.sorted_probe && full) out("      const bool edge = sgm < 2 ? (SK[sgm] == KF0 || SK[sgm] == KL0) : (SK[sgm] == KF1 || SK[sgm] == KL1);\n");
+    else if (p.sorted_probe) out("      const bool edge = true;\n");
+    else out("      const bool edge = false;\n");
+    out("      KIND[sgm] = !SA[sgm] || special ? 0u : (edge ? 2u : 1u);\n");
+    out("      if (SA[sgm] && special) {\n");
+    out("        u64* sp = p.log_special + (SN[sgm] ? 0 : %d);\n        sp[0] = 1ull;\n", 1 + p.log_n_cells);
+    for (int i = 0; i < p.log_n_cells; ++i) {
+      const int c = p.log_cells[i];
+      const int src = p.cells[c].skip ? 0 : c;
+      out("        hbm_update<%d>(sp + %d, SV%d[sgm], accerr);\n", p.cells[c].kind, 1 + i, src);
+    }
+    out("      }\n    }\n");
+    out("    u32 IDX[4]; log_reserve(logcur, KIND, IDX);\n");
+    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (KIND[sgm] == 0u) continue;\n");
+    out("      u64* e = KIND[sgm] == 1u ? region + (u64)IDX[sgm] * %d : region_end - ((u64)IDX[sgm] + 1ull) * %d;\n", EW, EW);
+    if (EW == 2) {
+      const int c = p.log_cells[0];
+      out("      *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(SK[sgm], SV%d[sgm]);\n", p.cells[c].skip ? 0 : c);
+    } else {
+      out("      e[0] = SK[sgm];\n");
+      for (int i = 0; i < p.log_n_cells; ++i) {
+        const int c = p.log_cells[i];
+        out("      e[%d] = SV%d[sgm];\n", 1 + i, p.cells[c].skip ? 0 : c);
+      }
+      for (int w = 1 + p.log_n_cells; w < EW; ++w) out("      e[%d] = 0ull;\n", w);
+    }
+    out("    }\n");
   }
 
   void gen_fp_body(bool full) {
@@ -540,7 +619,15 @@ struct Gen {
       if (d.nulls && (reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) { decline("unaligned nulls"); return; }
     }
     n_live = 0;
-    for (int c = 0; c < p.n_cells; ++c) if (!p.cells[c].skip) live_cells[n_live++] = c;
+    if (p.mode == kSinkLog) {
+      // only what an entry stores: its own cells, plus the rows cell when a stored count cell aliases it in this launch
+      bool need[kMaxCells] = {false};
+      for (int i = 0; i < p.log_n_cells; ++i) need[p.cells[p.log_cells[i]].skip ? 0 : p.log_cells[i]] = true;
+      for (int c = 0; c < p.n_cells; ++c) if (need[c]) live_cells[n_live++] = c;
+      if (p.log_n_cells < 1 || p.log_entry_words < 1 + p.log_n_cells) { decline("log entry layout"); return; }
+    } else {
+      for (int c = 0; c < p.n_cells; ++c) if (!p.cells[c].skip) live_cells[n_live++] = c;
+    }
 
     const int G = p.n_groups;
     int copies = 1;
@@ -554,6 +641,7 @@ struct Gen {
       if (d.encoding == VGPU_DICTIONARY) need += 4;
     }
     if (p.mode == kSinkHash) need += 8 + 3 * n_live * 4;
+    if (p.mode == kSinkLog) need += 4 + 3 * n_live * 4;
     int acc_regs = 0, group_bytes = 0; // per thread: accumulator registers / bytes of one thread table
     for (int i = 0; i < n_live; ++i) {
       const bool cnt = p.cells[live_cells[i]].kind == kCellCount;
@@ -619,6 +707,12 @@ struct Gen {
     out("  u32 accerr = 0;\n");
     gen_small_dict_registers();
     if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
+    if (p.mode == kSinkLog) {
+      out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
+      out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
+      out("  u64* const region_end = region + p.log_region_cap * %d;\n", p.log_entry_words);
+      if (p.sorted_probe) out("  bool viol = false;\n");
+    }
     if (p.mode == kSinkArray) {
       if (st == AS_REGS) {
         for (int i = 0; i < n_live; ++i) {
@@ -643,9 +737,9 @@ struct Gen {
       }
     }
     out("  for (i64 blk = wid; blk < n_blocks; blk += nwarps) {\n   if (blk < n_full) {\n");
-    if (p.mode == kSinkArray) gen_array_body(true, st, G); else if (p.mode == kSinkHash) gen_hash_body(true); else gen_fp_body(true);
+    if (p.mode == kSinkArray) gen_array_body(true, st, G); else if (p.mode == kSinkHash) gen_hash_body(true); else if (p.mode == kSinkLog) gen_log_body(true); else gen_fp_body(true);
     out("   } else {\n");
-    if (p.mode == kSinkArray) gen_array_body(false, st, G); else if (p.mode == kSinkHash) gen_hash_body(false); else gen_fp_body(false);
+    if (p.mode == kSinkArray) gen_array_body(false, st, G); else if (p.mode == kSinkHash) gen_hash_body(false); else if (p.mode == kSinkLog) gen_log_body(false); else gen_fp_body(false);
     out("   }\n  }\n");
     if (p.mode == kSinkArray) {
       if (st == AS_REGS || st == AS_THREAD) {
@@ -668,6 +762,10 @@ struct Gen {
         for (int i = 0; i < n_live; ++i) out("    if (ci == %d) c = %d;\n", i, live_cells[i]);
         out("    p.partials[((size_t)blockIdx.x * %d + c) * %d + gg] = acc;\n  }\n", p.n_cells, G);
       }
+    }
+    if (p.mode == kSinkLog) {
+      out("  __syncthreads();\n  if (threadIdx.x == 0) { p.log_counts[2 * blockIdx.x] = logcur[0]; p.log_counts[2 * blockIdx.x + 1] = logcur[1]; }\n");
+      if (p.sorted_probe) out("  if (__any_sync(0xffffffffu, viol) && lane == 0) atomicOr(p.sort_state, 1ull);\n");
     }
     if (p.mode == kSinkHash) {
       out("  _Pragma(\"unroll\") for (int o = 16; o > 0; o >>= 1) inserted += __shfl_xor_sync(0xffffffffu, inserted, o);\n");

@@ -23,6 +23,7 @@ struct FusedKernel;
 // width (CTAs), fixed per device and kernel so results are run-to-run deterministic.
 FusedKernel* fused_prepare(const PipelineParams& p, int* grid);
 int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t stream);
+int fused_kernel_threads(const FusedKernel* k);
 
 // Dry run (no device): vgpu_agg_add_input / vgpu_filter_project only generate the source, which
 // fused_last_source() returns.  Used by build() to prebuild the cubins of aot_plans.py.

@@ -82,6 +82,14 @@ struct FusedParams {
   u64* ovf;
   u64 ovf_cap;
   u64* ovf_cursor;
+  // LOG sink (internal.h PipelineParams::log...)
+  u64* log;
+  u64 log_region_cap;
+  u32* log_counts;
+  u64* log_special;
+  u64* sort_state;
+  const u64* sort_prev_in;
+  u64* sort_prev_out;
 };
 
 __device__ __forceinline__ u64 d2u(double d) { return (u64)__double_as_longlong(d); }
@@ -523,6 +531,35 @@ __device__ __forceinline__ void ovf_reserve(const FusedParams& p, const bool par
   for (int s = 0; s < 4; ++s) {
     if (parked[s]) entry[s] = (i64)(base + off + __popc(m[s] & lt));
     off += __popc(m[s]);
+  }
+}
+
+// ---- LOG sink ---------------------------------------------------------------------------------------
+// Positions of the warp's active segments inside the CTA's log region.  kind[s]: 0 = none, 1 = front (a run that
+// cannot continue in another block), 2 = back (a run touching a block edge).  One shared-memory atomic per warp and
+// side; returns the entry index (front: counted from the region start, back: from its end).
+__device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */, const u32 kind[4], u32 idx[4]) {
+  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  u32 mf[4], mb[4], nf = 0, nb = 0;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    mf[s] = __ballot_sync(0xffffffffu, kind[s] == 1u);
+    mb[s] = __ballot_sync(0xffffffffu, kind[s] == 2u);
+    nf += __popc(mf[s]);
+    nb += __popc(mb[s]);
+  }
+  u32 bf = 0, bb = 0;
+  if (lane == 0) {
+    if (nf) bf = atomicAdd(&cur[0], nf);
+    if (nb) bb = atomicAdd(&cur[1], nb);
+  }
+  bf = __shfl_sync(0xffffffffu, bf, 0);
+  bb = __shfl_sync(0xffffffffu, bb, 0);
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    idx[s] = kind[s] == 1u ? bf + __popc(mf[s] & lt) : bb + __popc(mb[s] & lt);
+    bf += __popc(mf[s]);
+    bb += __popc(mb[s]);
   }
 }
 

@@ -134,9 +134,21 @@ std::string lib_dir() {
   }
   return ".";
 }
+// Per-user cache directory (mode 0700): $VGPU_CACHE_DIR, else $XDG_CACHE_HOME/vgpu, else ~/.cache/vgpu, else
+// /tmp/vgpu_kernel_cache.<uid>.  A directory that is not ours or is writable by others is not used.
 std::string cache_dir() {
   const char* e = getenv("VGPU_CACHE_DIR");
-  return e && *e ? e : "/tmp/vgpu_kernel_cache";
+  if (e && *e) return e;
+  const char* x = getenv("XDG_CACHE_HOME");
+  if (x && *x) return std::string(x) + "/vgpu";
+  const char* h = getenv("HOME");
+  if (h && *h) return std::string(h) + "/.cache/vgpu";
+  return "/tmp/vgpu_kernel_cache." + std::to_string((long)getuid());
+}
+bool cache_dir_trusted(const std::string& dir) {
+  struct stat st;
+  if (stat(dir.c_str(), &st) != 0) return false;
+  return S_ISDIR(st.st_mode) && st.st_uid == getuid() && (st.st_mode & (S_IWGRP | S_IWOTH)) == 0;
 }
 
 bool read_file(const std::string& path, std::vector<char>& out) {
@@ -151,7 +163,10 @@ bool read_file(const std::string& path, std::vector<char>& out) {
   return ok;
 }
 void write_file(const std::string& dir, const std::string& name, const std::vector<char>& data) {
-  mkdir(dir.c_str(), 0777);
+  const size_t slash = dir.rfind('/');
+  if (slash != std::string::npos && slash > 0) mkdir(dir.substr(0, slash).c_str(), 0700); // e.g. ~/.cache
+  mkdir(dir.c_str(), 0700);
+  if (!cache_dir_trusted(dir)) return;
   const std::string tmp = dir + "/." + name + "." + std::to_string((long)getpid());
   FILE* f = fopen(tmp.c_str(), "wb");
   if (!f) return;
@@ -209,6 +224,10 @@ std::string signature(const PipelineParams& p) {
       put(&ks.min, 8); put(&ks.max, 8); put(&ks.mult, 8); put(&ks.output, 1); put(&ks.bits, 1); put(&ks.shift, 1); put(&ks.nullable, 1);
     }
     for (int c = 0; c < p.n_cells; ++c) { put(&p.cells[c].kind, 1); put(&p.cells[c].input, 1); put(&p.cells[c].skip, 1); }
+    if (p.mode == kSinkLog) {
+      put(&p.log_entry_words, 4); put(&p.log_n_cells, 4); put(p.log_cells, (size_t)p.log_n_cells);
+      put(&p.sorted_probe, 4); put(&p.sorted_key_col, 4);
+    }
   } else {
     for (int k = 0; k < p.n_outputs; ++k) {
       const uint8_t f[2] = {(uint8_t)(p.outs[k].values != nullptr), (uint8_t)(p.outs[k].nulls != nullptr)};
@@ -235,7 +254,9 @@ uint64_t fused_source_hash(const std::string& source) {
 FusedKernel* fused_prepare(const PipelineParams& p, int* grid) {
   const char* env = getenv("VGPU_FUSED");
   if (env && env[0] == '0') { g_last_note = "disabled by VGPU_FUSED=0"; return nullptr; }
-  const std::string sig = signature(p);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const std::string sig = std::string(1, (char)dev) + signature(p);
   FusedKernel* k = nullptr;
   {
     std::lock_guard<std::mutex> l(g_mu);
@@ -262,7 +283,7 @@ FusedKernel* fused_prepare(const PipelineParams& p, int* grid) {
     std::vector<char> cubin;
     std::string origin;
     if (read_file(lib_dir() + "/aot/" + name, cubin)) origin = "aot";
-    else if (read_file(cache_dir() + "/" + name, cubin)) origin = "disk";
+    else if (cache_dir_trusted(cache_dir()) && read_file(cache_dir() + "/" + name, cubin)) origin = "disk";
     else {
       std::string log;
       const std::string full = std::string(kFusedPrelude) + "\n" + body;
@@ -307,6 +328,8 @@ FusedKernel* fused_prepare(const PipelineParams& p, int* grid) {
   return k;
 }
 
+int fused_kernel_threads(const FusedKernel* k) { return k->threads; }
+
 int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t stream) {
   vgf::FusedParams fp;
   memset(&fp, 0, sizeof(fp));
@@ -325,6 +348,8 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
   fp.key_min = p.key_map.min; fp.key_span = p.key_map.span; fp.key_scale = p.key_map.scale; fp.key_mode = p.key_map.mode; fp.key_pad = p.key_map.pad;
   fp.n_groups_ctr = (vgf::u64*)p.n_groups_ctr;
   fp.ovf = (vgf::u64*)p.ovf; fp.ovf_cap = p.ovf_cap; fp.ovf_cursor = (vgf::u64*)p.ovf_cursor;
+  fp.log = (vgf::u64*)p.log; fp.log_region_cap = p.log_region_cap; fp.log_counts = p.log_counts; fp.log_special = (vgf::u64*)p.log_special;
+  fp.sort_state = (vgf::u64*)p.sort_state; fp.sort_prev_in = (const vgf::u64*)p.sort_prev_in; fp.sort_prev_out = (vgf::u64*)p.sort_prev_out;
   fp.sel_words = p.sel_words;
   fp.tile_counts = p.tile_counts;
   for (int i = 0; i < p.n_outputs && i < 24; ++i) { fp.out_values[i] = p.outs[i].values; fp.out_nulls[i] = (vgf::u64*)p.outs[i].nulls; }

@@ -98,7 +98,9 @@ struct KeyMap {
   uint32_t pad;
 };
 
-enum SinkMode : int32_t { kSinkFilterProject = 0, kSinkArray = 1, kSinkHash = 2 };
+// kSinkLog: HASH aggregation, log engine — the scan appends run-aggregated {key, cells...} entries to
+// per-CTA regions of a log (no table, no global atomics); hashagg.cu deduplicates them afterwards.
+enum SinkMode : int32_t { kSinkFilterProject = 0, kSinkArray = 1, kSinkHash = 2, kSinkLog = 3 };
 
 struct DevOut {
   void* values;
@@ -205,6 +207,23 @@ struct PipelineParams {
   uint64_t* ovf;
   uint64_t ovf_cap; // entries
   unsigned long long* ovf_cursor;
+  // LOG sink (fused kernels only): CTA c owns entries [c * log_region_cap, (c + 1) * log_region_cap) of `log`
+  // (log_entry_words 8-byte words each): runs that cannot continue into a neighbouring block grow from the front,
+  // runs touching a block edge from the back; log_counts[2c], [2c+1] receive the two counts.
+  uint64_t* log;
+  uint64_t log_region_cap;
+  uint32_t* log_counts;
+  int32_t log_entry_words;
+  int32_t log_n_cells;          // cells stored in an entry, in order: log_cells[0..n)
+  uint8_t log_cells[kMaxCells];
+  uint64_t* log_special;        // rows of the NULL-key group and of the key that equals the empty marker: {present, cells...}
+  // sorted-input probe (single raw 64-bit FLAT key column, no filter): sort_state[0] != 0 once any adjacent pair of
+  // rows was out of order; prev_in = {key, valid} of the row before this batch, prev_out receives this batch's last row
+  int32_t sorted_probe;
+  int32_t sorted_key_col;
+  unsigned long long* sort_state;
+  const unsigned long long* sort_prev_in;
+  unsigned long long* sort_prev_out;
   // FILTER_PROJECT sink
   uint32_t* sel_words;
   int32_t* tile_counts;
@@ -232,7 +251,11 @@ int cuda_fail(cudaError_t e, const char* what);
     if (e_ != cudaSuccess) return cuda_fail(e_, #x); \
   } while (0)
 
-uint32_t* device_err_word();  // per-device latched error bits
+uint32_t* device_err_word();  // latched error bits of kernels that belong to no aggregation (FilterProject)
+// Error words are slots of one per-device slab, so vgpu_check_errors can read them all with one copy while every
+// aggregation reports only its own data errors (N drivers = N operator instances per device).
+uint32_t* err_word_acquire();
+void err_word_release(uint32_t* w);
 // Optional timing of the scan kernels (vgpu_debug_kernel_timing): events on the launching stream
 // right before / after the kernel, summed by vgpu_debug_kernel_time.
 void kernel_timing_begin(cudaStream_t stream);

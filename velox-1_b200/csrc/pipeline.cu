@@ -918,9 +918,9 @@ __device__ __forceinline__ void run_mops(Ctx& cx, char* tab, int64_t tile, int c
           const uint64_t u = v.v[j] - (uint64_t)ks.min;
           const bool isnull = (v.n >> j) & 1u;
           if (isnull ? !ks.nullable : u > span) bad |= 1u << j;
-          const uint32_t id = isnull ? 0u : (uint32_t)u + ks.nullable;
-          if (MODE == kSinkHash) cx.key[j] += (uint64_t)id << ks.shift;
-          else cx.goff[j] += id * (uint32_t)ks.mult;
+          const uint64_t id = isnull ? 0ull : u + ks.nullable; // 64-bit: a 33-bit field must not wrap into the NULL id
+          if (MODE == kSinkHash) cx.key[j] += id << ks.shift;
+          else cx.goff[j] += (uint32_t)id * (uint32_t)ks.mult;
         }
         if (bad & cx.pass) {
           cx.ecode |= kErrKeyRange * 0x01010101u;

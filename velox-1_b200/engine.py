@@ -203,6 +203,19 @@ class Aggregation:
     def reset(self):
         abi.check(abi.lib().vgpu_agg_reset(self.handle, stream_ptr()))
 
+    def finalize(self):
+        """noMoreInput: completes the device-side aggregation (asynchronous; more input may still follow)."""
+        abi.check(abi.lib().vgpu_agg_finalize(self.handle, stream_ptr()))
+
+    def check_errors(self):
+        abi.check(abi.lib().vgpu_agg_check_errors(self.handle, stream_ptr()))
+
+    def info(self) -> dict:
+        out = (C.c_int64 * 8)()
+        abi.check(abi.lib().vgpu_debug_agg_info(self.handle, stream_ptr(), out))
+        names = ["engine", "sorted", "front_entries", "deduped_entries", "deduped_groups", "partitions", "entry_words", "entry_bound"]
+        return dict(zip(names, list(out)))
+
     def num_groups(self) -> int:
         n = C.c_int64()
         abi.check(abi.lib().vgpu_agg_num_groups(self.handle, stream_ptr(), C.byref(n)))
@@ -279,6 +292,17 @@ class Exchange:
         abi.check(abi.lib().vgpu_comm_create(idbuf, rank, world, C.byref(self.handle)))
         self.bytes_sent = 0
 
+    def reserve_window(self, nbytes: int) -> bool:
+        """Collective: peer-mapped exchange window of nbytes per rank (same value on every rank).  True when mapped."""
+        ok = C.c_int32()
+        abi.check(abi.lib().vgpu_comm_reserve_window(self.handle, nbytes, C.byref(ok)))
+        return bool(ok.value)
+
+    def last_counts(self) -> np.ndarray:
+        m = (C.c_int64 * (self.world * self.world))()
+        abi.check(abi.lib().vgpu_comm_last_counts(self.handle, m, stream_ptr()))
+        return np.array(list(m), dtype=np.int64).reshape(self.world, self.world)
+
     @staticmethod
     def make_unique_id() -> bytes:
         idbuf = (C.c_uint8 * abi.COMM_ID_BYTES)()
@@ -311,6 +335,15 @@ class Exchange:
                                                 arr(ro), stream_ptr()))
         self.bytes_sent = int(sum(sc)) - int(sc[self.rank])
         final.merge_rows(recv[: int(recv_counts.sum())])
+
+
+def exchange_local(partials, finals, window_bytes=256 << 20):
+    """All ranks of a window exchange emulated on this one GPU (vgpu_debug_exchange_local): rank r owns
+    partials[r] -> finals[r]."""
+    w = len(partials)
+    pa = (C.c_void_p * w)(*[p.handle for p in partials])
+    fa = (C.c_void_p * w)(*[f.handle for f in finals])
+    abi.check(abi.lib().vgpu_debug_exchange_local(pa, fa, w, window_bytes, stream_ptr()))
 
 
 def plan_alltoall(send_rows, recv_rows, row_bytes):
