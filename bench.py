@@ -5,8 +5,14 @@
   python bench.py --impl reference --gpus N ...            # the reference's CPU path (oracle/)
 
 A step is one pass of the hot path over one resident batch: reset groups, fused filter ->
-project -> partial aggregation over every row, (N > 1: hash-partition the partial groups,
-all-to-all over NCCL, final aggregation), extract the result rows.  Prints ONE JSON line.
+project -> partial aggregation over every row, (N > 1: exchange of the partial groups through the
+peer-mapped window, final aggregation).  Prints ONE JSON line.  The same line carries
+  config.c5_groupby   the all-to-all leg of config 5 (GROUP BY l_orderkey, hash partition + NVLink peer stores +
+                      final deduplication) at this N, with its own result check,
+  config.other_configs  kernel timings of configs C1 / C3 / C4 (N = 1),
+  result_check        the final groups of every rank against torch reductions over the same rows (every N).
+Input: the reference's own data — lineitem of the order range [rank * 15 M, (rank + 1) * 15 M) of TPC-H SF(10 N),
+generated on the device bit-identically to the reference's dbgen (csrc/tpchgen.cu, checked by tests/test_gpu_tpchgen.py).
 """
 import argparse
 import importlib
@@ -18,7 +24,7 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tools")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
@@ -27,6 +33,19 @@ import torch  # noqa: E402
 
 Q1_COLS = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate"]
 Q1_BYTES_PER_ROW = 4 + 4 + 8 + 8 + 8 + 8 + 4  # 44 B/row
+ROWS = {1: 6_001_215, 10: 59_986_052, 100: 600_037_902}  # velox/tpch/gen/TpchGen.cpp:30-41
+
+
+def nominal_rows(sf):
+    return ROWS.get(int(sf), int(6_001_215 * sf)) if sf >= 1 else int(6_001_215 * sf)
+
+
+def base_config(args):
+    """The workload description both arms print (identical, so that the driver can compare them)."""
+    return {"workload": f"TPC-H Q1 SF{args.sf:g} per GPU: filter + group-by (4 groups) sum/avg/count",
+            "rows_per_gpu": nominal_rows(args.sf), "sf": args.sf, "bytes_per_row": Q1_BYTES_PER_ROW, "groups": 4,
+            "l2": "input (2.6 GB per step) is larger than L2 (126 MB); no flush needed",
+            "generator": "the reference's dbgen streams (velox/tpch/gen/dbgen), order range [rank, rank + 1) * 1.5 M * sf of SF(sf * gpus)"}
 
 
 def load_peaks():
@@ -86,21 +105,35 @@ class ClockSampler:
 
 
 def ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the Q1 kernel, from the committed
-    ncu capture (profiles/r01_q1_ncu_summary.json); None when the summary is absent."""
-    path = os.path.join(ROOT, "profiles", "r01_q1_ncu_summary.json")
-    try:
-        with open(path) as f:
-            d = json.load(f)
-        return d["dram_bytes_read"] + d["dram_bytes_write"]
-    except Exception:
-        return None
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the Q1 kernel, from the newest committed
+    ncu capture (profiles/r0N_q1_ncu_summary.json); None when no summary exists."""
+    for name in ("r02_q1_ncu_summary.json", "r01_q1_ncu_summary.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                d = json.load(f)
+            return d["dram_bytes_read"] + d["dram_bytes_write"]
+        except Exception:
+            continue
+    return None
 
 
 def q1_plan():
     import helpers as H
     f, outs = H.q1_exprs()
     return H, f, outs
+
+
+def reference_sample(sf, rows_wanted, threads):
+    """First orders of TPC-H SF`sf` from the reference's own dbgen (oracle/_ref/libdbgen_ref.so), generated in
+    parallel by order ranges; about rows_wanted rows."""
+    import lineitem as ref
+    from concurrent.futures import ThreadPoolExecutor
+    orders = min(int(1500000 * sf), rows_wanted // 4 + 1)
+    parts = max(1, min(threads, 32))
+    per = (orders + parts - 1) // parts
+    with ThreadPoolExecutor(parts) as pool:
+        chunks = list(pool.map(lambda i: ref.gen_range(sf, i * per, min(per, max(orders - i * per, 0)), set(Q1_COLS)), range(parts)))
+    return {c: np.concatenate([ch[c] for ch in chunks]) for c in Q1_COLS}
 
 
 def run_reference(args, rank, world):
@@ -110,14 +143,12 @@ def run_reference(args, rank, world):
         return
     import cpu_oracle as cpu
     H, f, outs = q1_plan()
-    tpch = importlib.import_module("velox-1_b200.tpch_synth")
-    sample = min(tpch.row_count(args.sf), args.ref_rows)
-    dev = "cuda" if torch.cuda.is_available() else "cpu"
-    data = tpch.lineitem(args.sf, Q1_COLS, rows=sample, device=dev)
-    types = [3, 3, 6, 6, 6, 6, 3]
-    cols = [(t, data[c].cpu().numpy(), None) for c, t in zip(Q1_COLS, types)]
-    accs = [(H.KIND_NAME[k], i) for k, i in H.Q1_ACCS]
     threads = os.cpu_count() or 1
+    data = reference_sample(args.sf * world, args.ref_rows, threads)
+    sample = len(data[Q1_COLS[0]])
+    types = [3, 3, 6, 6, 6, 6, 3]
+    cols = [(t, data[c], None) for c, t in zip(Q1_COLS, types)]
+    accs = [(H.KIND_NAME[k], i) for k, i in H.Q1_ACCS]
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -131,45 +162,139 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "TPC-H Q1 lineitem rows/sec", "value": value, "unit": "rows/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"TPC-H Q1 SF{args.sf:g}: filter + group-by (4 groups) sum/avg/count", "sf": args.sf},
+        "config": base_config(args),
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port",
-                         "sample": f"first {sample} rows of the SF{args.sf:g} workload per step, {threads} driver threads"},
+                         "sample": f"first {sample} rows of the workload (the reference's dbgen) per step, {threads} driver threads, batches of 4096 rows"},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
 
 
+def q1_expected(data):
+    """Per-group count and sums of Q1 by torch reductions over the same rows: tensor [6 groups, 6] (float64)."""
+    keep = data["l_shipdate"] <= 10471
+    gid = (data["l_returnflag"] * 2 + data["l_linestatus"]).long()[keep]
+    qty, ep, disc, tax = (data[c][keep] for c in ("l_quantity", "l_extendedprice", "l_discount", "l_tax"))
+    dp = ep * (1.0 - disc)
+    cols = [torch.ones_like(qty), qty, ep, dp, dp * (1.0 + tax), disc]
+    out = torch.zeros(6, len(cols), dtype=torch.float64, device=qty.device)
+    for j, v in enumerate(cols):
+        out[:, j].index_add_(0, gid, v)
+    return out
+
+
+def check_q1(groups, expected):
+    """groups: {(rf, ls): [(value, nn)...]} over all ranks; expected: [6, 6] tensor.  Counts exact, sums 1e-9."""
+    exp = expected.cpu().numpy()
+    want_groups = {(g // 2, g % 2) for g in range(6) if exp[g, 0] > 0}
+    if set(groups.keys()) != want_groups:
+        return f"FAILED: groups {sorted(groups.keys())} != {sorted(want_groups)}"
+    for (rf, ls), vals in groups.items():
+        e = exp[rf * 2 + ls]
+        # accumulators (helpers.Q1_ACCS): sum qty, eprice, disc_price, charge, (sum, count) x qty / eprice / disc, count(*)
+        got = {"count": vals[10][0], "qty": vals[0][0], "ep": vals[1][0], "dp": vals[2][0], "charge": vals[3][0], "disc": vals[8][0]}
+        if got["count"] != int(e[0]) or vals[5][0] != int(e[0]):
+            return f"FAILED: count of group {(rf, ls)}: {got['count']} != {int(e[0])}"
+        for name, j in (("qty", 1), ("ep", 2), ("dp", 3), ("charge", 4), ("disc", 5)):
+            if abs(got[name] - e[j]) > 1e-9 * abs(e[j]):
+                return f"FAILED: sum {name} of group {(rf, ls)}: {got[name]} vs {e[j]}"
+    return f"ok: {len(groups)} groups over all ranks: count(*) exact, 5 sums within 1e-9 of torch reductions over the same rows"
+
+
+def other_configs(engine, abi, H, ex, sf, data, iters=5):
+    """Kernel timings (CUDA events, median) of the single-GPU configs that are not the headline: C1 Q6 (GLOBAL sink),
+    C4 dictionary keys with nulls (ARRAY sink).  C3 is config.c5_groupby at N = 1."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    n = len(data["l_shipdate"])
+    I32, D = abi.INTEGER, abi.DOUBLE
+    out = {}
+
+    def timed(fn, reset):
+        evs = []
+        for i in range(3 + iters):
+            reset()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            if i >= 3:
+                evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return float(np.median([a.elapsed_time(b) for a, b in evs]))
+
+    peak, _ = load_peaks()
+    f, outs = H.q6_exprs()
+    cols = [engine.DeviceColumn({"l_shipdate": I32}.get(c, D), abi.FLAT, data[c], length=n) for c in H.Q6_COLS]
+    prog = engine.Program(f, outs)
+    agg = engine.Aggregation(abi.AGG_GLOBAL, [], [(abi.ACC_SUM_F64, 0), (abi.ACC_COUNT, -1)])
+    ms = timed(lambda: agg.add_input(prog, cols, n), agg.reset)
+    got = H.decode_rows(agg.extract(), [], [(abi.ACC_SUM_F64, 0), (abi.ACC_COUNT, -1)], [D], abi.AGG_GLOBAL)[()]
+    keep = (data["l_shipdate"] >= 8766) & (data["l_shipdate"] < 9131) & (data["l_discount"] >= 0.05) & (data["l_discount"] <= 0.07) & (data["l_quantity"] < 24.0)
+    want_n, want_s = int(keep.sum()), float((data["l_extendedprice"][keep] * data["l_discount"][keep]).sum())
+    ok = got[1][0] == want_n and abs(got[0][0] - want_s) <= 1e-9 * abs(want_s)
+    out["C1 Q6 (GLOBAL sink)"] = {"rows": n, "ms": round(ms, 4), "bytes_per_row": 28, "gbs": round(n * 28 / ms / 1e6, 1),
+                                  "frac_of_measured_peak": round(n * 28 / ms / 1e6 / peak, 4),
+                                  "result_check": f"{'ok' if ok else 'FAILED'}: {got[1][0]} rows, sum {got[0][0]:.4f} vs torch {want_n}, {want_s:.4f}"}
+    import kbench
+    mode_base = torch.tensor([6, 5, 4, 3, 2, 1, 0, 3], dtype=torch.int32, device="cuda")
+    mode_idx = (6 - data["l_shipmode"]).to(torch.int32)
+    instr_base = torch.tensor([2, 0, 3, 1], dtype=torch.int32, device="cuda")
+    instr_idx = torch.tensor([1, 3, 0, 2], dtype=torch.int32, device="cuda")[data["l_shipinstruct"].long()]
+    c4cols = [engine.DeviceColumn(I32, abi.DICTIONARY, mode_base, mode_idx, nulls=kbench.bits_every(n, 11, "cuda"), length=n),
+              engine.DeviceColumn(I32, abi.DICTIONARY, instr_base, instr_idx, nulls=kbench.bits_every(n, 13, "cuda"), length=n),
+              engine.DeviceColumn(D, abi.FLAT, data["l_extendedprice"], length=n),
+              engine.DeviceColumn(I32, abi.FLAT, data["l_shipdate"], length=n),
+              engine.DeviceColumn(D, abi.FLAT, data["l_quantity"], nulls=kbench.bits_every(n, 7, "cuda"), length=n)]
+    c4outs = [ex.col(0, I32), ex.col(1, I32), ex.col(2, D), ex.col(3, I32), ex.col(4, D)]
+    c4accs = [(abi.ACC_MIN, 2), (abi.ACC_MAX, 2), (abi.ACC_MIN, 3), (abi.ACC_MAX, 3), (abi.ACC_COUNT, 4), (abi.ACC_COUNT, -1)]
+    c4prog = engine.Program(None, c4outs)
+    c4agg = engine.Aggregation(abi.AGG_ARRAY, [(0, 0, 0, 6), (1, 0, 0, 3)], c4accs)
+    ms = timed(lambda: c4agg.add_input(c4prog, c4cols, n), c4agg.reset)
+    g = c4agg.num_groups()
+    total = sum(v[5][0] for v in H.decode_rows(c4agg.extract(), [(0, 0, 0, 6), (1, 0, 0, 3)], c4accs, [I32, I32, D, I32, D], abi.AGG_ARRAY).values())
+    out["C4 dictionary keys with nulls (ARRAY sink)"] = {
+        "rows": n, "ms": round(ms, 4), "bytes_per_row": 20.375, "gbs": round(n * 20.375 / ms / 1e6, 1),
+        "frac_of_measured_peak": round(n * 20.375 / ms / 1e6 / peak, 4),
+        "result_check": f"{'ok' if g == 40 and total == n else 'FAILED'}: {g} groups (40 = (7+1) x (4+1) with NULL keys), count(*) sums to {total} of {n} rows"}
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     pkg = importlib.import_module("velox-1_b200")
-    abi = pkg.abi
+    abi, ex = pkg.abi, pkg.expr
     torch.cuda.set_device(local_rank)
     abi.check(abi.lib().vgpu_init(local_rank))
     engine = importlib.import_module("velox-1_b200.engine")
-    tpch = importlib.import_module("velox-1_b200.tpch_synth")
     H, f, outs = q1_plan()
     dist = None
     exchange = None
+    window = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         ids = [engine.Exchange.make_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         exchange = engine.Exchange(rank, world, ids[0])
+        # one peer-mapped window for the whole run: sized for the C5 leg's entries (two halves, 1.3 x slack)
+        window = exchange.reserve_window(int(2 * 1.3 * nominal_rows(args.sf) * 1.02 * 16) + (64 << 20))
 
-    n = tpch.row_count(args.sf)
-    data = tpch.lineitem(args.sf, Q1_COLS, order_offset=rank * (n // 4 + n // 50 + 16), seed=rank)
+    # ---- input: this rank's split of TPC-H SF(sf * world), generated on the device (the reference's dbgen streams) ----
+    orders_per_rank = int(1500000 * args.sf)
+    gen_cols = list(dict.fromkeys(Q1_COLS + ["l_orderkey", "l_shipmode", "l_shipinstruct"]))
+    t0 = time.perf_counter()
+    data = engine.tpch_lineitem(args.sf * world, gen_cols, order_offset=rank * orders_per_rank, max_orders=orders_per_rank)
+    torch.cuda.synchronize()
+    gen_s = time.perf_counter() - t0
+    n = len(data["l_shipdate"])
     types = [abi.INTEGER, abi.INTEGER, abi.DOUBLE, abi.DOUBLE, abi.DOUBLE, abi.DOUBLE, abi.INTEGER]
     cols = [engine.DeviceColumn(t, abi.FLAT, data[c], length=n) for c, t in zip(Q1_COLS, types)]
     prog = engine.Program(f, outs)
     partial = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS)
     final = engine.Aggregation(abi.AGG_ARRAY, H.Q1_KEYS, H.Q1_ACCS) if world > 1 else None
     empty = [engine.DeviceColumn(t, abi.FLAT, data[c][:0], length=0) for c, t in zip(Q1_COLS, types)]
-
     lib = abi.lib()
 
     def step():
         """One pass of the hot path over the resident batch: reset the groups, fused filter ->
-        project -> partial aggregation, (N > 1: partition, all-to-all, final aggregation).  The
+        project -> partial aggregation, (N > 1: exchange, final aggregation).  The
         result (the group state) stays on the device; it is extracted and checked after the loop."""
         partial.reset()
         partial.add_input(prog, cols, n)
@@ -213,15 +338,24 @@ def run_ours(args, rank, world, local_rank):
     kms = k_total.value / max(1, k_n.value)
     kernel_note = abi.last_kernel_note()
     engine.check_errors()
-    groups = (final if world > 1 else partial).num_groups()
-    checked = None
-    if world == 1:  # the resident result against an independent count of the rows the filter keeps
-        got = H.decode_rows(partial.extract(), H.Q1_KEYS, H.Q1_ACCS, [o.type for o in outs], abi.AGG_ARRAY)
-        want_rows = int((data["l_shipdate"] <= H.DATE_1998_09_02).sum())
-        have_rows = sum(v[-1][0] for v in got.values())
-        if have_rows != want_rows:
-            raise RuntimeError(f"result check failed: count(*) over groups {have_rows} != {want_rows}")
-        checked = f"sum of count(*) over {len(got)} groups == {want_rows} rows passing the filter"
+
+    # ---- result check at every N: the final groups of all ranks against torch reductions over all ranks' rows --------
+    mine = H.decode_rows((final if world > 1 else partial).extract(), H.Q1_KEYS, H.Q1_ACCS, [o.type for o in outs], abi.AGG_ARRAY)
+    expected = q1_expected(data)
+    rows_all = torch.tensor([n], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(expected)
+        dist.all_reduce(rows_all)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+        groups = {}
+        dup = False
+        for g in gathered:
+            dup = dup or bool(groups.keys() & g.keys())
+            groups.update(g)
+        checked = "FAILED: a group is final on two ranks" if dup else check_q1(groups, expected)
+    else:
+        checked = check_q1(mine, expected)
 
     # ---- end to end: HOST batches through the public API (H2D inside the timed region) ----------
     host = [data[c].cpu().pin_memory() for c in Q1_COLS]
@@ -240,7 +374,7 @@ def run_ours(args, rank, world, local_rank):
             rows = final.extract()
         else:
             rows = e2e_agg.extract()  # device -> host read of the result rows
-        result_bytes = rows.nbytes
+        result_bytes = max(result_bytes, rows.nbytes)
         return rows
 
     for _ in range(max(1, min(args.warmup, 2))):
@@ -249,28 +383,66 @@ def run_ours(args, rank, world, local_rank):
     w0 = time.perf_counter()
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(e2e_steps):
-        e2e_rows = e2e_step()
+        e2e_step()
     barrier()
     e2e_s = time.perf_counter() - w0
+    del host, runner
+
+    # ---- the same query with the TableScan on the device: generate this rank's split + aggregate, every step --------
+    scan_cols = {c: data[c] for c in Q1_COLS}   # generated in place, over the resident columns
+    desc = abi.LineitemColumns()
+    for c, t in scan_cols.items():
+        setattr(desc, c, t.data_ptr())
+
+    def scan_step():
+        abi.check(lib.vgpu_tpch_gen_lineitem(float(args.sf * world), rank * orders_per_rank, orders_per_rank, C.byref(desc), n, None, engine.stream_ptr()))
+        step()
+        return (final if world > 1 else partial).extract()
+
+    scan_step()
+    barrier()
+    w0 = time.perf_counter()
+    scan_steps = max(1, min(args.steps, 5))
+    for _ in range(scan_steps):
+        scan_step()
+    barrier()
+    scan_s = time.perf_counter() - w0
+
+    # ---- config 5's all-to-all leg at this N (and C3 at N = 1) ----------------------------------------------------
+    import mgpu_bench
+    c5 = mgpu_bench.groupby_leg(engine, abi, ex, exchange, dist, rank, world, data["l_orderkey"], data["l_extendedprice"],
+                                steps=max(3, min(args.steps, 10)), warmup=3)
+    others = other_configs(engine, abi, H, ex, args.sf, data) if world == 1 and not args.no_other_configs else None
 
     # max over ranks
+    d2h = torch.tensor([result_bytes], dtype=torch.int64, device="cuda")
     if world > 1:
-        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms, e2e_s, scan_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = float(t[0]), float(t[1])
+        ms, e2e_s, scan_s = float(t[0]), float(t[1]), float(t[2])
+        dist.all_reduce(d2h, op=dist.ReduceOp.MAX)
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
+    total_rows = int(rows_all[0])
     peak, peak_src = load_peaks()
-    value = n * world * args.steps / (ms * 1e-3)
+    value = total_rows * args.steps / (ms * 1e-3)
     achieved = n * Q1_BYTES_PER_ROW / (kms * 1e-3) / 1e9
+    config = base_config(args)
+    config.update({
+        "rows_processed_per_step": total_rows, "generate_ms_per_gpu": round(gen_s * 1e3, 1),
+        "exchange": ("peer-mapped window (CUDA IPC): dense store + epoch flags + fold in one kernel" if window else
+                     ("NCCL all-gather of the dense group state" if world > 1 else "none (1 GPU)")),
+        "c5_groupby": c5,
+    })
+    if others is not None:
+        config["other_configs"] = others
     line = {
         "metric": "TPC-H Q1 lineitem rows/sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"TPC-H Q1 SF{args.sf:g}: filter + group-by (4 groups) sum/avg/count",
-                   "rows_per_gpu": n, "sf": args.sf, "bytes_per_row": Q1_BYTES_PER_ROW, "groups": int(groups),
-                   "l2": "input (2.6 GB per step) is larger than L2 (126 MB); no flush needed",
-                   "generator": "velox-1_b200/tpch_synth.py (lineitem-shaped, dbgen value domains)"},
+        "config": config,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(), "kernel": "vgpu_fused (plan-specialised Q1 scan: filter + project + "
                      "per-thread shared-memory partial aggregation)", "kernel_ms": kms, "kernel_launches": int(k_n.value),
@@ -278,8 +450,13 @@ def run_ours(args, rank, world, local_rank):
                      "peak_source": peak_src, "nominal_peak": 8000.0, "frac_of_nominal": achieved / 8000.0,
                      "note": "peak is the driver's copy (read+write) bandwidth; a read-only stream can exceed it "
                              "(ncu: 84 % of its DRAM peak for this kernel, profiles/r01_q1_ncu_summary.json)"},
-        "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": runner.h2d_bytes,
-                "d2h_bytes_per_step": int(result_bytes), "steps": e2e_steps, "chunk_rows": args.chunk_rows},
+        "e2e": {"value": total_rows * e2e_steps / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": n * Q1_BYTES_PER_ROW,
+                "d2h_bytes_per_step": int(d2h[0]), "steps": e2e_steps, "chunk_rows": args.chunk_rows,
+                "note": "host RowVector-style pinned columns -> HBM in chunks on a copy stream, double-buffered against the scan"},
+        "e2e_device_tablescan": {"value": total_rows * scan_steps / scan_s, "unit": "rows/s", "steps": scan_steps,
+                                 "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h[0]),
+                                 "note": "TableScan(tpch connector) on the device: this rank's split generated into HBM "
+                                         "(vgpu_tpch_gen_lineitem) + the Q1 step + result read-back, every step"},
         "gpu_launches": int(stats1.kernel_launches - stats0.kernel_launches),
         "result_check": checked,
         "clocks": clocks,
@@ -358,6 +535,7 @@ def main():
     ap.add_argument("--chunk-rows", type=int, default=4 << 20)
     ap.add_argument("--ref-rows", type=int, default=20_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

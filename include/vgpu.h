@@ -316,10 +316,11 @@ int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream);
 /* Number of groups so far (synchronises the stream). */
 int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* num_groups);
 
-/* Row width of vgpu_agg_extract output: 8 bytes normalized key, then 8 bytes per accumulator
- * (SUM_F64 as double; everything else int64, MIN/MAX of doubles as double), then 8 bytes per
+/* Row width of vgpu_agg_extract output: 8 bytes normalized key, 8 bytes flags (bit 0: NULL key), 8 bytes rows, then
+ * 8 bytes per accumulator (SUM_F64 as double; everything else int64, MIN/MAX of doubles as double), then 8 bytes per
  * accumulator of "non-null input count" — a group's SUM/MIN/MAX is NULL when that count is 0
- * (velox/exec/Aggregate.h:305-337). */
+ * (velox/exec/Aggregate.h:305-337).  Only zero / non-zero of that count (and of `rows`) is specified: the engines
+ * count exactly where a COUNT accumulator needs the number and otherwise may report 1 for "some". */
 int vgpu_agg_row_bytes(vgpu_agg_t agg, int32_t* bytes);
 
 /* Writes up to max_groups packed group rows into device memory `rows`, starting at group number
@@ -384,6 +385,45 @@ int vgpu_comm_last_counts(vgpu_comm_t comm, int64_t* matrix, void* stream);
  * device knows (HASH through the window: see vgpu_comm_last_counts). */
 int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg_t final_agg, void* stream,
                               int64_t* bytes_sent);
+
+/* ---- TableScan over the TPC-H connector, on the device -------------------------------------- */
+
+/* lineitem columns in HBM (device pointers; any may be NULL = not wanted).  Widths are Velox's: BIGINT / DOUBLE 8 bytes,
+ * INTEGER / DATE 4 bytes.  The four VARCHAR columns are produced as int32 ids into the sorted dictionaries that
+ * vgpu_tpch_dictionary returns (what a DictionaryVector<StringView> over those bases carries). */
+typedef struct {
+  int64_t* l_orderkey;
+  int64_t* l_partkey;
+  int64_t* l_suppkey;
+  int32_t* l_linenumber;
+  double* l_quantity;
+  double* l_extendedprice;
+  double* l_discount;
+  double* l_tax;
+  int32_t* l_returnflag;   /* ids of {"A","N","R"} */
+  int32_t* l_linestatus;   /* ids of {"F","O"} */
+  int32_t* l_shipdate;
+  int32_t* l_commitdate;
+  int32_t* l_receiptdate;
+  int32_t* l_shipinstruct; /* ids of {"COLLECT COD","DELIVER IN PERSON","NONE","TAKE BACK RETURN"} */
+  int32_t* l_shipmode;     /* ids of {"AIR","FOB","MAIL","RAIL","REG AIR","SHIP","TRUCK"} */
+} vgpu_lineitem_columns;
+
+/* Lineitem rows of the orders [order_offset, order_offset + max_orders) at scale factor sf — the split arithmetic of
+ * TpchDataSource::next / genTpchLineItem (velox/connectors/tpch/TpchConnector.cpp:139-163,
+ * velox/tpch/gen/TpchGen.cpp:401-489: offsets and sizes count ORDERS).  Synchronises the stream. */
+int vgpu_tpch_lineitem_rows(double sf, int64_t order_offset, int64_t max_orders, int64_t* rows, void* stream);
+
+/* Generates those rows straight into HBM, bit-identical to the reference's dbgen (velox/tpch/gen/dbgen/build.cpp:110-223
+ * mk_order with the seeds of dss.h:491-540; DOUBLE columns are integer * 0.01 like TpchGen.cpp:79-81; dates are days
+ * since the epoch).  `capacity_rows`: rows the output arrays hold (7 * max_orders always suffices).  *rows (host, may
+ * be NULL) receives the row count; passing it synchronises the stream, NULL keeps the call asynchronous. */
+int vgpu_tpch_gen_lineitem(double sf, int64_t order_offset, int64_t max_orders, const vgpu_lineitem_columns* out,
+                           int64_t capacity_rows, int64_t* rows, void* stream);
+
+/* Dictionary of a VARCHAR column: which = 0 l_returnflag, 1 l_linestatus, 2 l_shipinstruct, 3 l_shipmode.
+ * Returns the number of entries (-1: bad argument) and stores up to `cap` static strings in out (may be NULL). */
+int vgpu_tpch_dictionary(int32_t which, const char** out, int32_t cap);
 
 /* ---- statistics -------------------------------------------------------------------------- */
 

@@ -120,7 +120,9 @@ def assert_groups_equal(got, want, accs, rtol=1e-9):
             if kind == abi.ACC_COUNT:
                 assert gv == wv, (k, a, gv, wv)
                 continue
-            assert gn == wn, (k, a, "non-null count", gn, wn)
+            # the ABI's "non-null input count" of SUM / MIN / MAX only says NULL (0) or not (> 0): the log engine
+            # does not count rows unless a COUNT accumulator asks for it
+            assert (gn > 0) == (wn > 0), (k, a, "non-null count", gn, wn)
             if wn == 0:
                 continue  # NULL result: value is unspecified
             if kind == abi.ACC_SUM_F64:

@@ -57,6 +57,8 @@ def main():
         final.add_input(prog, empty, 0)
         exchange.shuffle(partial, final)                       # vgpu_comm_exchange_groups
         results[name] = H.decode_rows(final.extract(), keys, accs, [o.type for o in outs], mode)
+        if mode == abi.AGG_GLOBAL:
+            return  # vgpu_agg_merge_rows has no notion of the owning rank of the single global row
         again = engine.Aggregation(mode, keys, accs)
         again.add_input(prog, empty, 0)
         exchange.shuffle_stepwise(partial, again)              # partition / all-to-all / merge, step by step

@@ -77,6 +77,15 @@ class AggDesc(C.Structure):
     ]
 
 
+LINEITEM_COLUMNS = ["l_orderkey", "l_partkey", "l_suppkey", "l_linenumber", "l_quantity", "l_extendedprice", "l_discount",
+                    "l_tax", "l_returnflag", "l_linestatus", "l_shipdate", "l_commitdate", "l_receiptdate", "l_shipinstruct",
+                    "l_shipmode"]
+
+
+class LineitemColumns(C.Structure):
+    _fields_ = [(name, C.c_void_p) for name in LINEITEM_COLUMNS]
+
+
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_int64), ("rows_in", C.c_int64),
                 ("bytes_h2d", C.c_int64), ("bytes_d2h", C.c_int64)]
@@ -127,6 +136,8 @@ PROTOTYPES = {
     "vgpu_comm_exchange_groups": [_P, _P, _P, _P, C.POINTER(_I64)],
     "vgpu_comm_reserve_window": [_P, _SZ, C.POINTER(_I32)],
     "vgpu_comm_last_counts": [_P, C.POINTER(_I64), _P],
+    "vgpu_tpch_lineitem_rows": [C.c_double, _I64, _I64, C.POINTER(_I64), _P],
+    "vgpu_tpch_gen_lineitem": [C.c_double, _I64, _I64, C.POINTER(LineitemColumns), _I64, C.POINTER(_I64), _P],
     "vgpu_get_stats": [C.POINTER(Stats)],
     "vgpu_reset_stats": [],
     "vgpu_debug_set_dry_run": [C.c_int],

@@ -752,6 +752,8 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       if (rc) return rc;
       a.log_bound += (uint64_t)p.n_rows;
       a.finalized = false;
+      if (p.sorted_probe && a.log_batches == 1) // the stream's first key, for the exchange's "sources are disjoint" test
+        VG_CUDA(cudaMemcpyAsync(a.ctr + kCtrFirstKey, p.cols[p.sorted_key_col].values, 8, cudaMemcpyDeviceToDevice, stream));
       return fused_launch(fk, p, fgrid, stream);
     }
     if (fused_dry_run()) return VGPU_OK;

@@ -26,6 +26,7 @@ enum : int {
   kCtrSortState = 48,  // != 0: some adjacent rows were out of key order (the front entries are not unique)
   kCtrPrevKey = 49,    // [2][2]: {key, valid} of the last row of the previous batch, double-buffered by batch parity
   kCtrFin = 53,        // finalize header: see FinHeader (6 words)
+  kCtrFirstKey = 59,   // key of the very first logged row (meaningful while the input is sorted)
   kCtrWords = 64
 };
 
@@ -60,6 +61,7 @@ struct FinHeader {
   unsigned long long log2p;     // hash partitions used (chosen on the device from n_dedupe)
 };
 
+constexpr int kSrcMetaWords = 4;
 enum HashEngine : int { kEngineUndecided = 0, kEngineLog = 1, kEngineTable = 2 };
 
 struct Agg {
@@ -99,6 +101,11 @@ struct Agg {
   std::vector<LogSlab> free_slabs;   // kept across reset()
   std::vector<LogRange> ext_ranges;  // entries in foreign buffers (received from other GPUs), deduplicated with the slabs'
   uint64_t ext_bound = 0;            // upper bound of the entries in ext_ranges
+  // what the senders said about their streams: per source kSrcMetaWords words {sorted, first key, last key, entries}
+  // at ext_meta + s * ext_meta_stride (device).  When every source was sorted and their key ranges are disjoint, the
+  // received front entries are whole groups and skip the deduplication like a local sorted stream's.
+  const unsigned long long* ext_meta = nullptr;
+  int ext_sources = 0, ext_meta_stride = 0;
   uint64_t log_bound = 0;            // upper bound of the entries in the slabs
   bool log_probed = true;            // every batch so far ran the sorted-input probe
   int log_batches = 0;

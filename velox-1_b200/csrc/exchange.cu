@@ -67,6 +67,7 @@ int nccl_fail(int rc, const char* what) { set_error("NCCL error %d (%s) in %s", 
 #define VG_NCCL(x) do { int r_ = (x); if (r_ != 0) return nccl_fail(r_, #x); } while (0)
 
 constexpr int kMaxWorld = 32;
+constexpr int kMsgWords = kMaxWorld + 8;  // one rank's count message
 constexpr size_t kWinHeader = 4096;   // per half: epoch flags of the dense exchange, one 64-byte line per source
 } // namespace
 
@@ -79,7 +80,8 @@ struct vgpu_comm_s {
   // grow-only device scratch of the NCCL payload path
   void* send = nullptr; size_t send_cap = 0;
   void* recv = nullptr; size_t recv_cap = 0;
-  int64_t* dcounts = nullptr;          // [32] counts this rank sends + [32 * 32] all-gathered matrix [src][dst]
+  int64_t* dcounts = nullptr;          // [kMsgWords] this rank's message + [32 * kMsgWords] the all-gathered messages [src]
+                                       // message: [world] entries per destination (low 32 bits front, high 32 back), then kSrcMetaWords of stream facts
   // peer-mapped window
   char* win = nullptr;                 // this rank's window
   size_t win_bytes = 0;                // both halves
@@ -122,7 +124,7 @@ struct SendArgs {
   uint32_t world, rank;
   uint64_t* peer_region[kMaxWorld]; // destination d: first entry of the region this rank owns in d's window
   uint64_t region_cap;            // entries
-  unsigned long long* cursor;     // [world]: entries sent to each destination so far (device)
+  unsigned long long* cursor;     // [world]: entries stored per destination so far: low 32 bits front, high 32 bits back
   uint32_t* err;
 };
 
@@ -167,7 +169,10 @@ __global__ void __launch_bounds__(kSendThreads) xchg_send_kernel(SendArgs a) {
       for (uint32_t d = 0; d < a.world; ++d) { off[d] = run; run += cnt[d]; }
       off[a.world] = run;
     }
-    if (threadIdx.x < a.world) base[threadIdx.x] = cnt[threadIdx.x] ? atomicAdd(&a.cursor[threadIdx.x], (unsigned long long)cnt[threadIdx.x]) : 0ull;
+    // front entries (whole groups if the stream is sorted) fill a region from its start, back entries from its end;
+    // one packed cursor per destination keeps "front + back <= capacity" checkable with a single atomic
+    const bool is_back = rg.back == 1;
+    if (threadIdx.x < a.world) base[threadIdx.x] = cnt[threadIdx.x] ? atomicAdd(&a.cursor[threadIdx.x], (unsigned long long)cnt[threadIdx.x] << (is_back ? 32 : 0)) : 0ull;
     __syncthreads();
     // pass 2: entries grouped by destination in shared memory
 #pragma unroll
@@ -184,9 +189,10 @@ __global__ void __launch_bounds__(kSendThreads) xchg_send_kernel(SendArgs a) {
     for (uint32_t i = threadIdx.x; i < n; i += kSendThreads) {
       uint32_t d = 0;
       while (d + 1 < a.world && off[d + 1] <= i) ++d;
-      const unsigned long long pos = base[d] + (i - off[d]);
-      if (pos >= a.region_cap) { overflow = true; continue; }
-      uint64_t* out = a.peer_region[d] + pos * ew;
+      const unsigned long long front = base[d] & 0xffffffffull, back = base[d] >> 32;
+      const unsigned long long j = i - off[d];
+      if (front + back + cnt[d] > a.region_cap) { overflow = true; continue; }
+      uint64_t* out = is_back ? a.peer_region[d] + (a.region_cap - 1ull - (back + j)) * ew : a.peer_region[d] + (front + j) * ew;
       const uint64_t* s = stage + (uint64_t)i * ew;
       if (ew == 2) *reinterpret_cast<ulonglong2*>(out) = *reinterpret_cast<const ulonglong2*>(s);
       else for (int w = 0; w < ew; ++w) out[w] = s[w];
@@ -194,6 +200,17 @@ __global__ void __launch_bounds__(kSendThreads) xchg_send_kernel(SendArgs a) {
     __syncthreads();
   }
   if (overflow) atomicOr(a.err, kErrTableFull);
+}
+
+// Facts about the sender's stream for the receivers' "all sources sorted and disjoint" shortcut.
+__global__ void xchg_meta_kernel(unsigned long long* msg, uint32_t world, const unsigned long long* ctr, int probed, int last_parity) {
+  if (threadIdx.x != 0) return;
+  unsigned long long n = 0;
+  for (uint32_t d = 0; d < world; ++d) n += (msg[d] & 0xffffffffull) + (msg[d] >> 32);
+  msg[kMaxWorld + 0] = probed && ctr[kCtrSortState] == 0ull ? 1ull : 0ull;
+  msg[kMaxWorld + 1] = ctr[kCtrFirstKey];
+  msg[kMaxWorld + 2] = ctr[kCtrPrevKey + 2 * last_parity];
+  msg[kMaxWorld + 3] = n;
 }
 
 // The two dedicated groups (NULL key, key equal to the empty marker) go to their owners' slots in front of the region;
@@ -450,8 +467,9 @@ static int exchange_nccl(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t strea
   int64_t counts[32] = {0}, matrix[32 * 32];
   if ((rc = agg_partition(pa, W, comm->send, counts, stream))) return rc;
   VG_CUDA(cudaMemcpyAsync(comm->dcounts, counts, sizeof(int64_t) * W, cudaMemcpyHostToDevice, stream));
-  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + 32, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
-  VG_CUDA(cudaMemcpyAsync(matrix, comm->dcounts + 32, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, stream));
+  int64_t* gathered = comm->dcounts + kMsgWords + 32 * kMsgWords;
+  VG_NCCL(g_nccl.allgather(comm->dcounts, gathered, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
+  VG_CUDA(cudaMemcpyAsync(matrix, gathered, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, stream));
   VG_CUDA(cudaStreamSynchronize(stream));
   int64_t sc[32], so[32], rcv[32], ro[32], srun = 0, rrun = 0;
   for (int r = 0; r < W; ++r) { // matrix[src][dst]
@@ -494,7 +512,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   }
   s.chunk_prefix = comm->chunk_prefix;
   if ((rc = log_chunk_prefix(ranges, n_ranges, chunk, comm->chunk_prefix, stream))) return rc;
-  VG_CUDA(cudaMemsetAsync(comm->dcounts, 0, sizeof(int64_t) * 32, stream));
+  VG_CUDA(cudaMemsetAsync(comm->dcounts, 0, sizeof(int64_t) * kMsgWords, stream));
   const size_t smem = (size_t)chunk * ew * 8;
   VG_CUDA(cudaFuncSetAttribute(xchg_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   xchg_send_kernel<<<num_sms() * 4, kSendThreads, smem, stream>>>(s);
@@ -502,8 +520,10 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew;
   for (int d = 0; d < W; ++d) sp.peer_slot[d] = (uint64_t*)region_of(comm, d, half, comm->rank);
   xchg_send_special_kernel<<<W, 64, 0, stream>>>(sp);
+  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)comm->dcounts, (uint32_t)W, pa.ctr, pa.log_probed && pa.ext_ranges.empty() ? 1 : 0,
+                                         (pa.log_batches + 1) & 1);
   VG_CUDA(cudaGetLastError());
-  count_launch(3);
+  count_launch(4);
   return VGPU_OK;
 }
 
@@ -522,12 +542,19 @@ static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t str
     LogRange r{};
     r.base = (const uint64_t*)(region_of(comm, comm->rank, half, src) + special_bytes);
     r.cap = region_cap;
-    r.count = comm->dcounts + 32 + (size_t)src * W + comm->rank; // matrix[src][dst = me]
-    r.count64 = 1;
-    r.back = 2;
+    const uint32_t* packed = reinterpret_cast<const uint32_t*>(comm->dcounts + kMsgWords + (size_t)src * kMsgWords + comm->rank); // message[src][dst = me]
+    r.count64 = 0;
+    r.count = packed;       // low half: front entries
+    r.back = 0;
+    fa.ext_ranges.push_back(r);
+    r.count = packed + 1;   // high half: back entries
+    r.back = 1;
     fa.ext_ranges.push_back(r);
   }
   fa.ext_bound += region_cap * (uint64_t)W;
+  fa.ext_meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fa.ext_sources = W;
+  fa.ext_meta_stride = kMsgWords;
   fa.finalized = false;
   fa.packed_rows = -1;
   xchg_fold_special_kernel<<<1, 32, 0, stream>>>(fs);
@@ -541,7 +568,7 @@ static int exchange_log_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t st
   int rc = log_p2p_send(comm, pa, stream);
   if (rc) return rc;
   // the counts, and the barrier between "everybody has stored" and "anybody reads"
-  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + 32, sizeof(int64_t) * comm->world, kNcclUint8, comm->comm, stream));
+  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, stream));
   if (bytes_sent) *bytes_sent = -1; // known on the device only; see vgpu_comm_last_counts
   return log_p2p_receive(comm, pa, fa, stream);
 }
@@ -589,7 +616,7 @@ int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg
   Agg& fa = final_agg->agg;
   if (pa.mode != fa.mode || pa.accs.size() != fa.accs.size()) { set_error("partial and final aggregations differ"); return VGPU_ERR_INVALID; }
   if (!pa.resolved || !fa.resolved) { set_error("both aggregations must have seen an (empty) vgpu_agg_add_input"); return VGPU_ERR_INVALID; }
-  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * (32 + 32 * 32)));
+  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)));
   const bool no_p2p = getenv("VGPU_EXCHANGE") && strcmp(getenv("VGPU_EXCHANGE"), "nccl") == 0;
   if (pa.mode != VGPU_AGG_HASH) {
     if (pa.n_groups != fa.n_groups || pa.n_cells != fa.n_cells) { set_error("partial and final aggregations differ in their key domains"); return VGPU_ERR_INVALID; }
@@ -615,7 +642,7 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
   for (int r = 0; r < world && rc == VGPU_OK; ++r) {
     comms[r].comm = nullptr; comms[r].rank = r; comms[r].world = world;
     if (cudaMalloc(&comms[r].win, window_bytes) != cudaSuccess || cudaMemset(comms[r].win, 0, window_bytes) != cudaSuccess ||
-        cudaMalloc(&comms[r].dcounts, sizeof(int64_t) * (32 + 32 * 32)) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
+        cudaMalloc(&comms[r].dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
     comms[r].win_bytes = window_bytes;
   }
   for (int r = 0; r < world; ++r) for (int q = 0; q < world; ++q) comms[r].peer[q] = comms[q].win;
@@ -633,7 +660,7 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
     }
     if (hash) { // the all-gather of the counts
       for (int r = 0; r < world; ++r) for (int src = 0; src < world; ++src)
-        VG_CUDA(cudaMemcpyAsync(comms[r].dcounts + 32 + (size_t)src * world, comms[src].dcounts, sizeof(int64_t) * world, cudaMemcpyDeviceToDevice, stream));
+        VG_CUDA(cudaMemcpyAsync(comms[r].dcounts + kMsgWords + (size_t)src * kMsgWords, comms[src].dcounts, sizeof(int64_t) * kMsgWords, cudaMemcpyDeviceToDevice, stream));
     }
     for (int r = 0; r < world; ++r) {
       Agg& fa = finals[r]->agg;
@@ -648,7 +675,7 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
   if (rc == VGPU_OK) rc = body();
   cudaStreamSynchronize(stream);
   for (int r = 0; r < world; ++r) {
-    if (partials[r] && finals[r]) { finals[r]->agg.ext_ranges.clear(); finals[r]->agg.ext_bound = 0; }
+    if (partials[r] && finals[r]) { Agg& fa = finals[r]->agg; fa.ext_ranges.clear(); fa.ext_bound = 0; fa.ext_meta = nullptr; fa.ext_sources = 0; }
     cudaFree(comms[r].win); cudaFree(comms[r].dcounts); cudaFree(comms[r].chunk_prefix);
   }
   return rc;
@@ -659,8 +686,13 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
 int vgpu_comm_last_counts(vgpu_comm_t comm, int64_t* matrix, void* stream) {
   if (!comm || !matrix || !comm->dcounts) return VGPU_ERR_INVALID;
   const int W = comm->world;
-  VG_CUDA(cudaMemcpyAsync(matrix, comm->dcounts + 32, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  std::vector<int64_t> msgs((size_t)W * kMsgWords);
+  VG_CUDA(cudaMemcpyAsync(msgs.data(), comm->dcounts + kMsgWords, sizeof(int64_t) * W * kMsgWords, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  for (int s = 0; s < W; ++s) for (int d = 0; d < W; ++d) {
+    const uint64_t w = (uint64_t)msgs[(size_t)s * kMsgWords + d];
+    matrix[s * W + d] = (int64_t)((w & 0xffffffffull) + (w >> 32));
+  }
   return VGPU_OK;
 }
 

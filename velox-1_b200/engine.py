@@ -337,6 +337,38 @@ class Exchange:
         final.merge_rows(recv[: int(recv_counts.sum())])
 
 
+TORCH_OF = {"l_orderkey": torch.int64, "l_partkey": torch.int64, "l_suppkey": torch.int64, "l_linenumber": torch.int32,
+            "l_quantity": torch.float64, "l_extendedprice": torch.float64, "l_discount": torch.float64, "l_tax": torch.float64,
+            "l_returnflag": torch.int32, "l_linestatus": torch.int32, "l_shipdate": torch.int32, "l_commitdate": torch.int32,
+            "l_receiptdate": torch.int32, "l_shipinstruct": torch.int32, "l_shipmode": torch.int32}
+
+
+def tpch_lineitem_rows(sf: float, order_offset: int, max_orders: int) -> int:
+    n = C.c_int64()
+    abi.check(abi.lib().vgpu_tpch_lineitem_rows(float(sf), order_offset, max_orders, C.byref(n), stream_ptr()))
+    return n.value
+
+
+def tpch_lineitem(sf: float, columns, order_offset: int = 0, max_orders: int = None, rows: int = None):
+    """TableScan over the TPC-H connector on the device: the lineitem rows of orders [order_offset, +max_orders) at
+    scale factor sf, generated straight into HBM bit-identically to the reference's dbgen (vgpu_tpch_gen_lineitem).
+    Returns dict name -> tensor (VARCHAR columns as int32 dictionary ids)."""
+    total_orders = int(1500000 * sf)
+    if max_orders is None:
+        max_orders = max(total_orders - order_offset, 0)
+    if rows is None:
+        rows = tpch_lineitem_rows(sf, order_offset, max_orders)
+    out = {c: torch.empty(max(rows, 1), dtype=TORCH_OF[c], device="cuda") for c in columns}
+    desc = abi.LineitemColumns()
+    for c, t in out.items():
+        setattr(desc, c, t.data_ptr())
+    got = C.c_int64()
+    abi.check(abi.lib().vgpu_tpch_gen_lineitem(float(sf), order_offset, max_orders, C.byref(desc), rows, C.byref(got), stream_ptr()))
+    check_errors()
+    assert got.value == rows, (got.value, rows)
+    return {c: t[:rows] for c, t in out.items()}
+
+
 def exchange_local(partials, finals, window_bytes=256 << 20):
     """All ranks of a window exchange emulated on this one GPU (vgpu_debug_exchange_local): rank r owns
     partials[r] -> finals[r]."""
