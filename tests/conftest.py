@@ -4,6 +4,9 @@ import sys
 
 import pytest
 
+# a plan-specialised kernel that fails to compile is a test failure, not a silent fall-back to the interpreter
+os.environ.setdefault("VGPU_STRICT", "1")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
     if p not in sys.path:

@@ -28,6 +28,8 @@ def run_hash(engine, filt, outs, spec, n, keys, accs, batches=1, ignore=False, h
         agg.add_input(prog, cols, hi - lo)
     agg.finalize()
     info = agg.info()
+    if os.environ.get("VGPU_HASH_ENGINE", "log") != "table" and os.environ.get("VGPU_FUSED", "1") != "0":
+        assert info["engine"] == 1, ("the log engine was expected", info, abi.last_kernel_note())
     got = H.decode_rows(agg.extract(), keys, accs, [o.type for o in outs], abi.AGG_HASH, nullable=not ignore)
     return got, info
 

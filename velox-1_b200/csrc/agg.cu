@@ -652,6 +652,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       int fgrid = 0;
       FusedKernel* fk = fused_prepare(p, &fgrid);
       if (fused_dry_run()) return VGPU_OK;
+      if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
       if (fk) {
         const size_t need = (size_t)fgrid * a.n_cells * Gc;
         if (need > a.partials_cap) {
@@ -742,6 +743,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       }
       fk = fused_prepare(p, &fgrid);
       if (fused_dry_run()) return VGPU_OK;
+      if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
     }
     if (fk) {
       a.engine = kEngineLog;
@@ -823,6 +825,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
     p.table = a.table; p.cap_mask = a.capacity - 1; p.key_map = key_map_of(a); p.row_words = a.row_words; p.n_groups_ctr = a.ctr;
     int fgrid = 0;
     FusedKernel* fk = fused_prepare(p, &fgrid);
+    if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
     static const bool parking = !(getenv("VGPU_NO_PARKING") && getenv("VGPU_NO_PARKING")[0] == '1');
     if (fk && parking) {
       const uint64_t want = std::max<uint64_t>(1u << 16, a.capacity / 8); // a full buffer only means the scan warp walks the table itself

@@ -349,6 +349,7 @@ int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t
     int fgrid = 0;
     FusedKernel* fk = fused_prepare(p, &fgrid);
     if (fused_dry_run()) return VGPU_OK;
+    if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
     rc = fk ? fused_launch(fk, p, fgrid, stream) : launch_pipeline(p, 0, pipeline_grid(p.n_rows), stream);
   }
   if (rc) return rc;

@@ -54,6 +54,11 @@ struct Gen {
     return b;
   }
 
+  // Row layout of a warp's 128-row block.  pair: thread rows 2l, 2l+1, 64+2l, 64+2l+1 (two 16-byte loads per 8-byte
+  // column).  quad (LOG sink): thread rows 4l .. 4l+3 (one 256-bit load per 8-byte column), so that runs of equal keys
+  // fold inside the thread first and one segmented scan covers the whole block.
+  bool quad = false;
+  std::string row_of_j() const { return quad ? "(r0 + j)" : "((j < 2 ? r0 : r1) + (j & 1))"; }
   bool col_used[kMaxCols] = {false};
   void mark(const vgpu_operand& o) { if (o.kind == VGPU_OPND_COL && o.index < kMaxCols) col_used[o.index] = true; }
 
@@ -88,19 +93,38 @@ struct Gen {
       const int lg = dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : 3));
       const char* src = dict ? "indices" : "values";
       if (d.nulls) {
-        if (full) out("    const u32 N%d = bits2(p.nulls[%d], r0) | (bits2(p.nulls[%d], r1) << 2);\n", c, c, c);
+        if (quad) {
+          if (full) out("    const u32 N%d = bits4(p.nulls[%d], r0);\n", c, c);
+          else out("    const u32 N%d = r0 < n ? bits4(p.nulls[%d], r0) : 0u;\n", c, c);
+        } else if (full) out("    const u32 N%d = bits2(p.nulls[%d], r0) | (bits2(p.nulls[%d], r1) << 2);\n", c, c, c);
         else out("    const u32 N%d = (r0 < n ? bits2(p.nulls[%d], r0) : 0u) | ((r1 < n ? bits2(p.nulls[%d], r1) : 0u) << 2);\n", c, c, c);
       }
       if (lg == -1) { // bit-packed BOOLEAN
-        if (full) out("    const u32 Q%d = bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) | (bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) << 2);\n", c, c, c);
+        if (quad) {
+          if (full) out("    const u32 Q%d = bits4(reinterpret_cast<const u64*>(p.values[%d]), r0);\n", c, c);
+          else out("    const u32 Q%d = r0 < n ? bits4(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u;\n", c, c);
+        } else if (full) out("    const u32 Q%d = bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) | (bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) << 2);\n", c, c, c);
         else out("    const u32 Q%d = (r0 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u) | ((r1 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) : 0u) << 2);\n", c, c, c);
         continue;
       }
       const bool real = !dict && d.type == VGPU_REAL;
-      if (full && lg == 3) {
+      if (full && quad && lg == 3) {
+        const void* walk = dict ? (const void*)d.indices : d.values;
+        if ((reinterpret_cast<uintptr_t>(walk) & 31u) == 0) {
+          out("    const u64x4 qq%d = ld32(p.%s[%d], r0 * 8);\n", c, src, c);
+          out("    const u64 Q%d[4] = {qq%d.x, qq%d.y, qq%d.z, qq%d.w};\n", c, c, c, c, c);
+        } else { // 16-byte aligned only
+          out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 8), qb%d = ld16(p.%s[%d], r0 * 8 + 16);\n", c, src, c, c, src, c);
+          out("    const u64 Q%d[4] = {pack64(qa%d.x, qa%d.y), pack64(qa%d.z, qa%d.w), pack64(qb%d.x, qb%d.y), pack64(qb%d.z, qb%d.w)};\n", c, c, c, c, c, c, c, c, c);
+        }
+      } else if (full && quad && lg == 2) {
+        out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 4);\n", c, src, c);
+        if (real) out("    const u64 Q%d[4] = {d2u((double)__uint_as_float(qa%d.x)), d2u((double)__uint_as_float(qa%d.y)), d2u((double)__uint_as_float(qa%d.z)), d2u((double)__uint_as_float(qa%d.w))};\n", c, c, c, c, c);
+        else out("    const u64 Q%d[4] = {sext32(qa%d.x), sext32(qa%d.y), sext32(qa%d.z), sext32(qa%d.w)};\n", c, c, c, c, c);
+      } else if (full && !quad && lg == 3) {
         out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 8), qb%d = ld16(p.%s[%d], r1 * 8);\n", c, src, c, c, src, c);
         out("    const u64 Q%d[4] = {pack64(qa%d.x, qa%d.y), pack64(qa%d.z, qa%d.w), pack64(qb%d.x, qb%d.y), pack64(qb%d.z, qb%d.w)};\n", c, c, c, c, c, c, c, c, c);
-      } else if (full && lg == 2) {
+      } else if (full && !quad && lg == 2) {
         out("    const uint2 qa%d = ld8(p.%s[%d], r0 * 4), qb%d = ld8(p.%s[%d], r1 * 4);\n", c, src, c, c, src, c);
         if (real) out("    const u64 Q%d[4] = {d2u((double)__uint_as_float(qa%d.x)), d2u((double)__uint_as_float(qa%d.y)), d2u((double)__uint_as_float(qb%d.x)), d2u((double)__uint_as_float(qb%d.y))};\n", c, c, c, c, c);
         else out("    const u64 Q%d[4] = {sext32(qa%d.x), sext32(qa%d.y), sext32(qb%d.x), sext32(qb%d.y)};\n", c, c, c, c, c);
@@ -108,7 +132,7 @@ struct Gen {
         const char* ty = lg == 0 ? "signed char" : lg == 1 ? "short" : lg == 2 ? (real ? "float" : "int") : "u64";
         out("    u64 Q%d[4];\n", c);
         out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
-        out("      const i64 r = (j < 2 ? r0 : r1) + (j & 1);\n");
+        out("      const i64 r = %s;\n", row_of_j().c_str());
         if (real) out("      Q%d[j] = r < n ? d2u((double)reinterpret_cast<const float*>(p.%s[%d])[r]) : 0ull;\n", c, src, c);
         else if (lg == 3) out("      Q%d[j] = r < n ? reinterpret_cast<const u64*>(p.%s[%d])[r] : 0ull;\n", c, src, c);
         else out("      Q%d[j] = r < n ? (u64)(i64)reinterpret_cast<const %s*>(p.%s[%d])[r] : 0ull;\n", c, ty, src, c);
@@ -316,13 +340,14 @@ struct Gen {
 
   // ---- whole kernels ----------------------------------------------------------------------------
   void gen_block_header(bool full) {
-    out("    const i64 r0 = blk * 128 + 2 * lane, r1 = r0 + 64;\n");
+    if (quad) out("    const i64 r0 = blk * 128 + 4 * lane;\n");
+    else out("    const i64 r0 = blk * 128 + 2 * lane, r1 = r0 + 64;\n");
     gen_loads(full);
   }
   void gen_row_begin(bool full) {
     out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
     if (full) out("      const bool valid = true;\n");
-    else out("      const bool valid = ((j < 2 ? r0 : r1) + (j & 1)) < n;\n");
+    else out("      const bool valid = %s < n;\n", row_of_j().c_str());
     out("      u32 ec = 0;\n");
     gen_row_columns();
     gen_ops();
@@ -402,7 +427,7 @@ struct Gen {
     out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
     if (p.mode == kSinkLog && p.sorted_probe) {
       // the batch's last row is the "row before" of the next batch's first one
-      out("      if (((j < 2 ? r0 : r1) + (j & 1)) == n - 1) { p.sort_prev_out[0] = key; p.sort_prev_out[1] = 1ull; }\n");
+      out("      if (%s == n - 1) { p.sort_prev_out[0] = key; p.sort_prev_out[1] = 1ull; }\n", row_of_j().c_str());
     }
     gen_raise();
     out("    }\n");
@@ -500,32 +525,70 @@ struct Gen {
     gen_keyed_rows(full);
     const int EW = p.log_entry_words;
     if (p.sorted_probe) {
-      // adjacent rows must be in non-decreasing (unsigned) key order: inside the thread, lane to lane, half block to
-      // half block, and against the row before the block (the previous batch's last row for block 0)
+      // adjacent rows must be in non-decreasing (unsigned) key order: inside the thread, lane to lane, and against the row
+      // before the block (the previous batch's last row for block 0)
       out("    {\n");
-      if (full) out("      const bool ok1 = true, ok2 = true, ok3 = true, ok0 = true;\n");
-      else out("      const bool ok0 = r0 < n, ok1 = r0 + 1 < n, ok2 = r1 < n, ok3 = r1 + 1 < n;\n");
-      out("      bool bad = (ok1 && KEY[0] > KEY[1]) || (ok3 && KEY[2] > KEY[3]);\n");
-      out("      const u64 pk0 = __shfl_up_sync(0xffffffffu, KEY[1], 1), pk1 = __shfl_up_sync(0xffffffffu, KEY[3], 1);\n");
-      out("      const u64 last0 = __shfl_sync(0xffffffffu, KEY[1], 31);\n");
+      if (full) out("      const bool ok0 = true, ok1 = true, ok2 = true, ok3 = true;\n");
+      else out("      const bool ok0 = r0 < n, ok1 = r0 + 1 < n, ok2 = r0 + 2 < n, ok3 = r0 + 3 < n;\n");
+      out("      bool bad = (ok1 && KEY[0] > KEY[1]) || (ok2 && KEY[1] > KEY[2]) || (ok3 && KEY[2] > KEY[3]);\n");
+      out("      const u64 pk = __shfl_up_sync(0xffffffffu, KEY[3], 1);\n");
       out("      u64 before = 0ull; bool have = false;\n");
       out("      if (lane == 0) {\n");
       out("        if (blk > 0) { before = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + (blk * 128 - 1)); have = true; }\n", p.sorted_key_col);
       out("        else { before = p.sort_prev_in[0]; have = p.sort_prev_in[1] != 0ull; }\n");
       out("      }\n");
-      out("      bad = bad || (ok0 && (lane > 0 ? pk0 > KEY[0] : (have && before > KEY[0])));\n");
-      out("      bad = bad || (ok2 && (lane > 0 ? pk1 > KEY[2] : last0 > KEY[2]));\n");
+      out("      bad = bad || (ok0 && (lane > 0 ? pk > KEY[0] : (have && before > KEY[0])));\n");
       out("      viol = viol || bad;\n    }\n");
     }
-    gen_run_aggregation(false);
-    out("    u32 KIND[4];\n");
-    if (p.sorted_probe && full) {
-      out("    const u64 KF0 = __shfl_sync(0xffffffffu, KEY[0], 0), KL0 = __shfl_sync(0xffffffffu, KEY[1], 31);\n");
-      out("    const u64 KF1 = __shfl_sync(0xffffffffu, KEY[2], 0), KL1 = __shfl_sync(0xffffffffu, KEY[3], 31);\n");
+    // Run aggregation over the thread's 4 consecutive rows, then across lanes.  r<c> is the running fold of the run
+    // that is open at row j; the run that ENDS at row j (the next passing row starts another one, or j is the
+    // thread's last row) leaves its key and value in slot j.  Slot 3 is the thread's tail run: it may continue in the
+    // next lane.  The thread's first run (its "head") may continue the previous lane's tail.
+    out("    u64 SK[4]; bool SN[4], SA[4];\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4];\n", live_cells[i]);
+    out("    u64 lastk = 0ull, firstk = 0ull; bool lastn = false, firstn = false, have = false;\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 rf%d = cell_identity<%d>();\n", live_cells[i], p.cells[live_cells[i]].kind);
+    out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
+    out("      const bool start = PASS[j] && !(have && lastk == KEY[j] && lastn == KN[j]);\n");
+    out("      if (j > 0) { SK[j - 1] = lastk; SN[j - 1] = lastn; SA[j - 1] = start && have;\n");
+    for (int i = 0; i < n_live; ++i) out("        SV%d[j - 1] = rf%d;\n", live_cells[i], live_cells[i]);
+    out("      }\n");
+    out("      if (PASS[j] && !have) { firstk = KEY[j]; firstn = KN[j]; }\n");
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      const int kind = p.cells[c].kind;
+      out("      { const u64 v = L%d[j] ? X%d[j] : cell_identity<%d>(); rf%d = start ? v : cell_comb<%d>(rf%d, v, accerr); }\n", c, c, kind, c, kind, c);
     }
+    out("      if (PASS[j]) { lastk = KEY[j]; lastn = KN[j]; have = true; }\n");
+    out("    }\n");
+    out("    SK[3] = lastk; SN[3] = lastn;\n");
+    out("    const bool hasT = have, single = have && !(SA[0] || SA[1] || SA[2]);\n");
+    out("    const u64 ptk = __shfl_up_sync(0xffffffffu, lastk, 1);\n");
+    out("    const u32 pfl = __shfl_up_sync(0xffffffffu, (u32)hasT | ((u32)lastn << 1), 1);\n");
+    out("    const bool link = lane > 0 && hasT && (pfl & 1u) && ptk == firstk && (bool)((pfl >> 1) & 1u) == firstn;\n");
+    out("    bool f = !(link && single); // the carry flows through this lane's tail only when the tail is its only run\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 t%d = rf%d;\n", live_cells[i], live_cells[i]);
+    out("    _Pragma(\"unroll\") for (int d = 1; d < 32; d <<= 1) {\n");
+    for (int i = 0; i < n_live; ++i) out("      const u64 u%d = __shfl_up_sync(0xffffffffu, t%d, d);\n", live_cells[i], live_cells[i]);
+    out("      const bool uf = __shfl_up_sync(0xffffffffu, (u32)f, d) != 0u;\n");
+    out("      if (lane >= d && !f) {\n");
+    for (int i = 0; i < n_live; ++i) out("        t%d = cell_comb<%d>(u%d, t%d, accerr);\n", live_cells[i], p.cells[live_cells[i]].kind, live_cells[i], live_cells[i]);
+    out("        f = uf;\n      }\n    }\n");
+    // the head of a lane with several runs takes the previous lane's (scanned) tail
+    for (int i = 0; i < n_live; ++i) {
+      const int c = live_cells[i];
+      out("    { const u64 carry = __shfl_up_sync(0xffffffffu, t%d, 1);\n", c);
+      out("      if (link && !single) { if (SA[0]) SV%d[0] = cell_comb<%d>(carry, SV%d[0], accerr); else if (SA[1]) SV%d[1] = cell_comb<%d>(carry, SV%d[1], accerr); else SV%d[2] = cell_comb<%d>(carry, SV%d[2], accerr); } }\n",
+          c, p.cells[c].kind, c, c, p.cells[c].kind, c, c, p.cells[c].kind, c);
+      out("    SV%d[3] = t%d;\n", c, c);
+    }
+    out("    const bool next_link = __shfl_down_sync(0xffffffffu, (u32)link, 1) != 0u && lane < 31;\n");
+    out("    SA[3] = hasT && !next_link;\n");
+    out("    u32 KIND[4];\n");
+    if (p.sorted_probe && full) out("    const u64 KF = __shfl_sync(0xffffffffu, KEY[0], 0), KL = __shfl_sync(0xffffffffu, KEY[3], 31);\n");
     out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n");
     out("      const bool special = SN[sgm] || SK[sgm] == VGF_EMPTY_KEY;\n");
-    if (p.sorted_probe && full) out("      const bool edge = sgm < 2 ? (SK[sgm] == KF0 || SK[sgm] == KL0) : (SK[sgm] == KF1 || SK[sgm] == KL1);\n");
+    if (p.sorted_probe && full) out("      const bool edge = SK[sgm] == KF || SK[sgm] == KL; // the run may continue in a neighbouring block\n");
     else if (p.sorted_probe) out("      const bool edge = true;\n");
     else out("      const bool edge = false;\n");
     out("      KIND[sgm] = !SA[sgm] || special ? 0u : (edge ? 2u : 1u);\n");
@@ -607,6 +670,7 @@ struct Gen {
   }
 
   void generate() {
+    quad = p.mode == kSinkLog;
     for (const auto& op : prog.ops) { mark(op.a); mark(op.b); mark(op.c); }
     for (const auto& o : prog.outputs) mark(o);
     mark(prog.filter);

@@ -31,6 +31,8 @@ void fused_set_dry_run(bool on);
 bool fused_dry_run();
 // Small dictionaries (<= 32 base values) looked up with a warp shuffle instead of a gather (VGPU_SMALL_DICT=0 disables).
 bool fused_small_dict_enabled();
+// True once after a kernel failed to compile under VGPU_STRICT=1 (the error text is in vgpu_last_error).
+bool fused_strict_failure();
 const std::string& fused_last_source();
 const std::string& fused_last_note(); // why the last shape was declined / how it was built
 uint64_t fused_source_hash(const std::string& source);

@@ -104,6 +104,27 @@ __device__ __forceinline__ uint4 ld16(const void* base, i64 byte_off) {
 __device__ __forceinline__ uint2 ld8(const void* base, i64 byte_off) {
   return __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(base) + byte_off));
 }
+// 256-bit load (sm_100+): four consecutive 8-byte values of one thread in one fully coalesced instruction
+struct u64x4 { u64 x, y, z, w; };
+__device__ __forceinline__ u64x4 ld32(const void* base, i64 byte_off) {
+  u64x4 r;
+#if defined(__CUDACC_VER_MAJOR__) && (__CUDACC_VER_MAJOR__ * 100 + __CUDACC_VER_MINOR__ >= 1209)
+  asm volatile("ld.global.cs.v4.u64 {%0, %1, %2, %3}, [%4];"
+               : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+               : "l"(reinterpret_cast<const char*>(base) + byte_off));
+#else // an NVRTC older than 12.9 (e.g. the one bundled with the framework): its ptxas has no 256-bit vector loads
+  const uint4 a = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(base) + byte_off));
+  const uint4 b = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(base) + byte_off + 16));
+  r.x = (u64)a.x | ((u64)a.y << 32); r.y = (u64)a.z | ((u64)a.w << 32);
+  r.z = (u64)b.x | ((u64)b.y << 32); r.w = (u64)b.z | ((u64)b.w << 32);
+#endif
+  return r;
+}
+// rows r .. r+3 of a bitmap (r a multiple of 4): 4 bits
+__device__ __forceinline__ u32 bits4(const u64* bits, i64 r) {
+  const u32 w = __ldg(reinterpret_cast<const u32*>(bits) + (r >> 5));
+  return (w >> (r & 31)) & 15u;
+}
 // pulls one 128-byte line into L2 without occupying a register (next block's input, a key's home slot)
 __device__ __forceinline__ void prefetch_l2(const void* ptr) {
   asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));

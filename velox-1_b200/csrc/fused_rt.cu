@@ -79,6 +79,7 @@ struct NvrtcApi {
 std::mutex g_mu;
 std::map<std::string, FusedKernel*> g_cache; // signature bytes -> kernel (nullptr = declined)
 thread_local std::string g_last_source, g_last_note;
+thread_local bool g_strict_failed = false;
 bool g_dry = false;
 
 bool load_cu() {
@@ -102,7 +103,8 @@ bool load_cu() {
 bool load_rtc() {
   if (g_rtc.tried) return g_rtc.ok;
   g_rtc.tried = true;
-  const char* names[] = {"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so"};
+  // the toolkit's own NVRTC first: the one a framework bundles may be older than the installed ptxas features
+  const char* names[] = {"/usr/local/cuda/lib64/libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so", "libnvrtc.so.12", "libnvrtc.so"};
   void* h = nullptr;
   for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
   if (!h) return false;
@@ -209,7 +211,8 @@ std::string signature(const PipelineParams& p) {
     const DevCol& d = p.cols[c];
     const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
     const uint8_t f[6] = {d.type, d.encoding, (uint8_t)(d.nulls != nullptr), (uint8_t)(d.base_nulls != nullptr), d.const_null,
-                          (uint8_t)(((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) | (((reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) << 1))};
+                          (uint8_t)(((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) | (((reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) << 1) |
+                                    ((p.mode == kSinkLog && (reinterpret_cast<uintptr_t>(walk) & 31u) != 0) << 2))};
     put(f, 6);
     const uint8_t sd = d.small_dict != 0 && fused_small_dict_enabled();
     put(&sd, 1);
@@ -245,6 +248,7 @@ bool fused_small_dict_enabled() {
   static const bool on = !(getenv("VGPU_SMALL_DICT") && getenv("VGPU_SMALL_DICT")[0] == '0');
   return on;
 }
+bool fused_strict_failure() { const bool f = g_strict_failed; g_strict_failed = false; return f; }
 const std::string& fused_last_source() { return g_last_source; }
 const std::string& fused_last_note() { return g_last_note; }
 uint64_t fused_source_hash(const std::string& source) {
@@ -289,6 +293,9 @@ FusedKernel* fused_prepare(const PipelineParams& p, int* grid) {
       const std::string full = std::string(kFusedPrelude) + "\n" + body;
       if (!nvrtc_compile(full, cubin, log)) {
         g_last_note = "nvrtc failed: " + log.substr(0, 2000);
+        // VGPU_STRICT=1 (the test suites): a generated kernel that does not compile is an error, not a reason to run the
+        // shape on the interpreter
+        if (getenv("VGPU_STRICT") && getenv("VGPU_STRICT")[0] == '1') { g_strict_failed = true; set_error("%s", g_last_note.c_str()); }
         if (getenv("VGPU_FUSED_VERBOSE")) fprintf(stderr, "[vgpu] %s\n", g_last_note.c_str());
         std::lock_guard<std::mutex> l(g_mu);
         g_cache[sig] = nullptr;
