@@ -204,6 +204,15 @@ int vgpu_memset_async(void* dst, int value, size_t bytes, void* stream);
 int vgpu_stream_create(void** stream);
 int vgpu_stream_destroy(void* stream);
 int vgpu_stream_sync(void* stream);
+/* Events order a copy stream against a compute stream without blocking the host (staging rings of the operators). */
+int vgpu_event_create(void** event);
+int vgpu_event_destroy(void* event);
+int vgpu_event_record(void* event, void* stream);
+int vgpu_stream_wait_event(void* stream, void* event);
+int vgpu_event_sync(void* event);
+/* *pinned = 1 when `hptr` is page-locked host memory (vgpu_alloc_host or registered): an async copy from it does
+ * not stage through the driver. */
+int vgpu_host_is_pinned(const void* hptr, int32_t* pinned);
 
 /* ---- FilterProject ----------------------------------------------------------------------- */
 

@@ -202,6 +202,26 @@ int vgpu_stream_create(void** stream) {
 int vgpu_stream_destroy(void* stream) { VG_CUDA(cudaStreamDestroy((cudaStream_t)stream)); return VGPU_OK; }
 int vgpu_stream_sync(void* stream) { VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); return VGPU_OK; }
 
+int vgpu_event_create(void** event) {
+  if (!event) return VGPU_ERR_INVALID;
+  cudaEvent_t e;
+  VG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  *event = (void*)e;
+  return VGPU_OK;
+}
+int vgpu_event_destroy(void* event) { VG_CUDA(cudaEventDestroy((cudaEvent_t)event)); return VGPU_OK; }
+int vgpu_event_record(void* event, void* stream) { VG_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream)); return VGPU_OK; }
+int vgpu_stream_wait_event(void* stream, void* event) { VG_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0)); return VGPU_OK; }
+int vgpu_event_sync(void* event) { VG_CUDA(cudaEventSynchronize((cudaEvent_t)event)); return VGPU_OK; }
+int vgpu_host_is_pinned(const void* hptr, int32_t* pinned) {
+  if (!pinned) return VGPU_ERR_INVALID;
+  cudaPointerAttributes a;
+  const cudaError_t e = cudaPointerGetAttributes(&a, hptr);
+  if (e != cudaSuccess) { cudaGetLastError(); *pinned = 0; return VGPU_OK; }
+  *pinned = a.type == cudaMemoryTypeHost ? 1 : 0;
+  return VGPU_OK;
+}
+
 int vgpu_get_stats(vgpu_stats* out) {
   if (!out) return VGPU_ERR_INVALID;
   *out = g_stats;

@@ -83,24 +83,47 @@ struct Gen {
   }
 
   // ---- column loads -------------------------------------------------------------------------
-  // full: whole 128-row block (vector loads); else per-row guarded loads.
+  // Alignment a column's walked array (values, or indices of a dictionary) needs for the block-wide vector loads.
+  static int walk_log2(const DevCol& d) {
+    const bool dict = d.encoding == VGPU_DICTIONARY;
+    return dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : 3));
+  }
+  bool vector_loads_ok(const DevCol& d) const {
+    if (p.in_rows) return false;
+    const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
+    const int lg = walk_log2(d);
+    const uintptr_t need = lg == 3 ? 16 : lg == 2 ? (quad ? 16 : 8) : 1;
+    return (reinterpret_cast<uintptr_t>(walk) & (need - 1)) == 0;
+  }
+
+  // full: whole 128-row block (vector loads where the column's alignment allows); else per-row guarded loads.
+  // With a row selection (in_rows, the batch's SelectivityVector as an index list) every column is gathered
+  // through RR[j] = in_rows[row]; a sliced column whose base is not vector-aligned is read row by row.
   void gen_loads(bool full) {
+    if (p.in_rows) {
+      out("    i64 RR[4];\n    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) { const i64 r = %s; RR[j] = r < n ? (i64)__ldg(p.in_rows + r) : 0; }\n", row_of_j().c_str());
+    }
     for (int c = 0; c < p.n_cols; ++c) {
       if (!col_used[c]) continue;
       const DevCol& d = p.cols[c];
       if (d.encoding == VGPU_CONSTANT) continue;
       const bool dict = d.encoding == VGPU_DICTIONARY;
-      const int lg = dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : 3));
+      const int lg = walk_log2(d);
       const char* src = dict ? "indices" : "values";
+      const bool vec = full && vector_loads_ok(d);
       if (d.nulls) {
-        if (quad) {
+        if (p.in_rows) {
+          out("    u32 N%d = 0u;\n    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) if (%s < n && bit1(p.nulls[%d], RR[j])) N%d |= 1u << j;\n", c, row_of_j().c_str(), c, c);
+        } else if (quad) {
           if (full) out("    const u32 N%d = bits4(p.nulls[%d], r0);\n", c, c);
           else out("    const u32 N%d = r0 < n ? bits4(p.nulls[%d], r0) : 0u;\n", c, c);
         } else if (full) out("    const u32 N%d = bits2(p.nulls[%d], r0) | (bits2(p.nulls[%d], r1) << 2);\n", c, c, c);
         else out("    const u32 N%d = (r0 < n ? bits2(p.nulls[%d], r0) : 0u) | ((r1 < n ? bits2(p.nulls[%d], r1) : 0u) << 2);\n", c, c, c);
       }
       if (lg == -1) { // bit-packed BOOLEAN
-        if (quad) {
+        if (p.in_rows) {
+          out("    u32 Q%d = 0u;\n    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) if (%s < n && bit1(reinterpret_cast<const u64*>(p.values[%d]), RR[j])) Q%d |= 1u << j;\n", c, row_of_j().c_str(), c, c);
+        } else if (quad) {
           if (full) out("    const u32 Q%d = bits4(reinterpret_cast<const u64*>(p.values[%d]), r0);\n", c, c);
           else out("    const u32 Q%d = r0 < n ? bits4(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u;\n", c, c);
         } else if (full) out("    const u32 Q%d = bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) | (bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) << 2);\n", c, c, c);
@@ -108,7 +131,7 @@ struct Gen {
         continue;
       }
       const bool real = !dict && d.type == VGPU_REAL;
-      if (full && quad && lg == 3) {
+      if (vec && quad && lg == 3) {
         const void* walk = dict ? (const void*)d.indices : d.values;
         if ((reinterpret_cast<uintptr_t>(walk) & 31u) == 0) {
           out("    const u64x4 qq%d = ld32(p.%s[%d], r0 * 8);\n", c, src, c);
@@ -117,25 +140,26 @@ struct Gen {
           out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 8), qb%d = ld16(p.%s[%d], r0 * 8 + 16);\n", c, src, c, c, src, c);
           out("    const u64 Q%d[4] = {pack64(qa%d.x, qa%d.y), pack64(qa%d.z, qa%d.w), pack64(qb%d.x, qb%d.y), pack64(qb%d.z, qb%d.w)};\n", c, c, c, c, c, c, c, c, c);
         }
-      } else if (full && quad && lg == 2) {
+      } else if (vec && quad && lg == 2) {
         out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 4);\n", c, src, c);
         if (real) out("    const u64 Q%d[4] = {d2u((double)__uint_as_float(qa%d.x)), d2u((double)__uint_as_float(qa%d.y)), d2u((double)__uint_as_float(qa%d.z)), d2u((double)__uint_as_float(qa%d.w))};\n", c, c, c, c, c);
         else out("    const u64 Q%d[4] = {sext32(qa%d.x), sext32(qa%d.y), sext32(qa%d.z), sext32(qa%d.w)};\n", c, c, c, c, c);
-      } else if (full && !quad && lg == 3) {
+      } else if (vec && !quad && lg == 3) {
         out("    const uint4 qa%d = ld16(p.%s[%d], r0 * 8), qb%d = ld16(p.%s[%d], r1 * 8);\n", c, src, c, c, src, c);
         out("    const u64 Q%d[4] = {pack64(qa%d.x, qa%d.y), pack64(qa%d.z, qa%d.w), pack64(qb%d.x, qb%d.y), pack64(qb%d.z, qb%d.w)};\n", c, c, c, c, c, c, c, c, c);
-      } else if (full && !quad && lg == 2) {
+      } else if (vec && !quad && lg == 2) {
         out("    const uint2 qa%d = ld8(p.%s[%d], r0 * 4), qb%d = ld8(p.%s[%d], r1 * 4);\n", c, src, c, c, src, c);
         if (real) out("    const u64 Q%d[4] = {d2u((double)__uint_as_float(qa%d.x)), d2u((double)__uint_as_float(qa%d.y)), d2u((double)__uint_as_float(qb%d.x)), d2u((double)__uint_as_float(qb%d.y))};\n", c, c, c, c, c);
         else out("    const u64 Q%d[4] = {sext32(qa%d.x), sext32(qa%d.y), sext32(qb%d.x), sext32(qb%d.y)};\n", c, c, c, c, c);
       } else {
         const char* ty = lg == 0 ? "signed char" : lg == 1 ? "short" : lg == 2 ? (real ? "float" : "int") : "u64";
+        const char* at = p.in_rows ? "RR[j]" : "r";
         out("    u64 Q%d[4];\n", c);
         out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
         out("      const i64 r = %s;\n", row_of_j().c_str());
-        if (real) out("      Q%d[j] = r < n ? d2u((double)reinterpret_cast<const float*>(p.%s[%d])[r]) : 0ull;\n", c, src, c);
-        else if (lg == 3) out("      Q%d[j] = r < n ? reinterpret_cast<const u64*>(p.%s[%d])[r] : 0ull;\n", c, src, c);
-        else out("      Q%d[j] = r < n ? (u64)(i64)reinterpret_cast<const %s*>(p.%s[%d])[r] : 0ull;\n", c, ty, src, c);
+        if (real) out("      Q%d[j] = r < n ? d2u((double)reinterpret_cast<const float*>(p.%s[%d])[%s]) : 0ull;\n", c, src, c, at);
+        else if (lg == 3) out("      Q%d[j] = r < n ? reinterpret_cast<const u64*>(p.%s[%d])[%s] : 0ull;\n", c, src, c, at);
+        else out("      Q%d[j] = r < n ? (u64)(i64)reinterpret_cast<const %s*>(p.%s[%d])[%s] : 0ull;\n", c, ty, src, c, at);
         out("    }\n");
       }
     }
@@ -396,6 +420,7 @@ struct Gen {
   // Next block's input lines -> L2 (no registers held): the warp's following iteration then starts
   // from L2 latency instead of HBM latency.  One 128-byte line per lane per column.
   void gen_input_prefetch() {
+    if (p.in_rows) return;
     static const int dist = getenv("VGPU_PREFETCH_DIST") ? std::max(1, atoi(getenv("VGPU_PREFETCH_DIST"))) : 1; // blocks ahead (tuning aid)
     out("    if (blk + %d * nwarps < n_full) {\n", dist);
     for (int c = 0; c < p.n_cols; ++c) {
@@ -674,14 +699,17 @@ struct Gen {
     for (const auto& op : prog.ops) { mark(op.a); mark(op.b); mark(op.c); }
     for (const auto& o : prog.outputs) mark(o);
     mark(prog.filter);
-    if (p.in_rows) { decline("row indirection"); return; }
     for (int c = 0; c < p.n_cols; ++c) {
       if (!col_used[c] || p.cols[c].encoding == VGPU_CONSTANT) continue;
       const DevCol& d = p.cols[c];
       const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
-      if ((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) { decline("unaligned column"); return; }
+      const int lg = walk_log2(d);
+      // element alignment is all a column needs (a sliced vector's base is rarely 16-byte aligned); bitmaps are read as 32-bit words
+      if (lg > 0 && (reinterpret_cast<uintptr_t>(walk) & ((1u << lg) - 1u)) != 0) { decline("column not aligned to its element size"); return; }
+      if (lg < 0 && (reinterpret_cast<uintptr_t>(walk) & 7u) != 0) { decline("unaligned bitmap"); return; }
       if (d.nulls && (reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) { decline("unaligned nulls"); return; }
     }
+    if (p.in_rows && p.mode == kSinkFilterProject) { decline("row selection with the FilterProject sink"); return; }
     n_live = 0;
     if (p.mode == kSinkLog) {
       // only what an entry stores: its own cells, plus the rows cell when a stored count cell aliases it in this launch

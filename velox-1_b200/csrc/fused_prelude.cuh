@@ -64,6 +64,7 @@ struct FusedParams {
   const u64* base_nulls[16];
   i32 base_len[16]; // DICTIONARY columns with <= 32 base values (else 0): the base lives in one register per lane
   i64 n_rows;
+  const i32* in_rows; // optional row selection: the kernel walks in_rows[0 .. n_rows)
   u32* err_word;
   // ARRAY / GLOBAL sink: per-CTA partials [gridDim][n_cells][n_groups]
   u64* partials;

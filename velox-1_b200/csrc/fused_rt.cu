@@ -212,7 +212,8 @@ std::string signature(const PipelineParams& p) {
     const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
     const uint8_t f[6] = {d.type, d.encoding, (uint8_t)(d.nulls != nullptr), (uint8_t)(d.base_nulls != nullptr), d.const_null,
                           (uint8_t)(((reinterpret_cast<uintptr_t>(walk) & 15u) != 0) | (((reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) << 1) |
-                                    ((p.mode == kSinkLog && (reinterpret_cast<uintptr_t>(walk) & 31u) != 0) << 2))};
+                                    (((reinterpret_cast<uintptr_t>(walk) & 31u) != 0) << 2) | (((reinterpret_cast<uintptr_t>(walk) & 7u) != 0) << 3) |
+                                    (((reinterpret_cast<uintptr_t>(walk) & 3u) != 0) << 4) | (((reinterpret_cast<uintptr_t>(walk) & 1u) != 0) << 5))};
     put(f, 6);
     const uint8_t sd = d.small_dict != 0 && fused_small_dict_enabled();
     put(&sd, 1);
@@ -348,6 +349,7 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
     fp.base_len[c] = p.cols[c].small_dict;
   }
   fp.n_rows = p.n_rows;
+  fp.in_rows = p.in_rows;
   fp.err_word = p.err_word;
   fp.partials = (vgf::u64*)p.partials;
   fp.table = (vgf::u64*)p.table;
