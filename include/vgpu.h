@@ -214,6 +214,11 @@ int vgpu_event_sync(void* event);
  * not stage through the driver. */
 int vgpu_host_is_pinned(const void* hptr, int32_t* pinned);
 
+/* dst[i] = table[src[i]] for i < n, all device arrays: turns the int32 dictionary indices of a VARCHAR key batch into
+ * the operator-wide value ids of the batch's base strings (VectorHasher::makeValueIds per BASE value on the host,
+ * velox/exec/VectorHasher.cpp:241-289, the per-row step here).  An index outside [0, table_len) latches an error. */
+int vgpu_translate_i32(int32_t* dst, const int32_t* src, const int32_t* table, int32_t table_len, int64_t n, void* stream);
+
 /* ---- FilterProject ----------------------------------------------------------------------- */
 
 /* Validates and uploads a program (ExprSet construction; velox/exec/FilterProject.cpp:59-103). */

@@ -3,6 +3,7 @@
 // (velox/exec/tests/FilterProjectTest.cpp, AggregationTest.cpp, OperatorExtensibility example).
 //   host_tests cpu   no device needed: parser, lowering, plan types, registration seams, decoding
 //   host_tests gpu   the GPU operators against oracle/liboracle.so (vcpu_run) and plain C++ answers
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <map>
@@ -112,6 +113,7 @@ struct PassThrough : exec::Operator { // a CPU operator for a custom plan node (
   void addInput(RowVectorPtr in) override { input_ = std::move(in); ++batches; }
   RowVectorPtr getOutput() override { auto r = std::move(input_); input_ = nullptr; return r; }
   bool isFinished() override { return noMoreInput_ && !input_; }
+  exec::BlockingReason isBlocked(exec::ContinueFuture*) override { return exec::BlockingReason::kNotBlocked; }
   static int batches;
 };
 int PassThrough::batches = 0;
@@ -657,12 +659,65 @@ static void gpuTests() {
   }
 }
 
+// =========================================================================================================
+// bench: TPC-H Q1 through runPlan(PlanBuilder...) — the plugin as a Velox driver would run it — over HOST RowVectors of
+// `batchRows` rows each (4096 = the reference's default scan batch, 1 M = a large batch), with pageable and with pinned
+// vector memory.  Prints one JSON line per configuration: rows/s end to end (H2D, kernels, result read-back inside the
+// timed region; building the input vectors outside), and the operator's own counters.
+// =========================================================================================================
+static void benchQ1(size_t rows, size_t batchRows, bool pinned, int reps) {
+  gpu::usePinnedHostMemory(pinned);
+  const Lineitem t = makeLineitem(rows, 42);
+  std::vector<RowVectorPtr> input = batches(t, batchRows);
+  gpu::usePinnedHostMemory(false);
+  auto plan = PlanBuilder()
+                  .values(input)
+                  .filter("l_shipdate <= '1998-09-02'::DATE")
+                  .project({"l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_extendedprice * (1.0 - l_discount) AS disc_price",
+                            "l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax) AS charge", "l_discount"})
+                  .singleAggregation({"l_returnflag", "l_linestatus"},
+                                     {"sum(l_quantity)", "sum(l_extendedprice)", "sum(disc_price)", "sum(charge)", "avg(l_quantity)", "avg(l_extendedprice)",
+                                      "avg(l_discount)", "count(0)"})
+                  .planNode();
+  double best = 1e30;
+  int64_t groups = 0, countStar = 0;
+  gpu::GpuHashAggregation::Stats st{};
+  for (int r = 0; r < reps + 1; ++r) {
+    auto driver = exec::createDriver(plan);
+    const auto t0 = std::chrono::steady_clock::now();
+    auto out = driver->run();
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    groups = 0; countStar = 0;
+    for (auto& b : out) { groups += (int64_t)b->size(); for (size_t g = 0; g < b->size(); ++g) countStar += at<int64_t>(b->childAt(9), g); }
+    if (r > 0) best = std::min(best, ms); // the first run pays kernel loading
+  }
+  int64_t want = 0;
+  for (size_t i = 0; i < rows; ++i) want += t.shipdate[i] <= 10471;
+  printf("{\"case\": \"Q1 through runPlan(PlanBuilder) over host RowVectors\", \"rows\": %zu, \"batch_rows\": %zu, \"host_memory\": \"%s\", "
+         "\"ms\": %.3f, \"rows_per_s\": %.4g, \"groups\": %lld, \"result_check\": \"%s: count(*) over groups %lld vs %lld rows passing the filter\"}\n",
+         rows, batchRows, pinned ? "pinned" : "pageable", best, rows / (best * 1e-3), (long long)groups, countStar == want ? "ok" : "FAILED",
+         (long long)countStar, (long long)want);
+  fflush(stdout);
+  if (countStar != want) ++g_failed;
+  (void)st;
+}
+
+static void benchMode(int argc, char** argv) {
+  gpu::registerGpuOperators();
+  const size_t rows = argc > 2 ? (size_t)atoll(argv[2]) : 20000000;
+  for (const bool pinned : {false, true}) {
+    benchQ1(rows, 4096, pinned, 2);
+    benchQ1(rows, 1 << 20, pinned, 2);
+  }
+}
+
 int main(int argc, char** argv) {
   const std::string mode = argc > 1 ? argv[1] : "cpu";
   try {
     if (mode == "cpu") cpuTests();
     else if (mode == "gpu") gpuTests();
-    else { printf("usage: host_tests cpu|gpu\n"); return 2; }
+    else if (mode == "bench") benchMode(argc, argv);
+    else { printf("usage: host_tests cpu|gpu|bench [rows]\n"); return 2; }
   } catch (const std::exception& e) {
     printf("  FAILED: uncaught exception: %s\n", e.what());
     ++g_failed;

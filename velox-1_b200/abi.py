@@ -117,6 +117,7 @@ PROTOTYPES = {
     "vgpu_stream_wait_event": [_P, _P],
     "vgpu_event_sync": [_P],
     "vgpu_host_is_pinned": [_P, C.POINTER(_I32)],
+    "vgpu_translate_i32": [_P, _P, _P, _I32, _I64, _P],
     "vgpu_program_create": [C.POINTER(ProgramDesc), C.POINTER(_P)],
     "vgpu_program_destroy": [_P],
     "vgpu_filter_project": [_P, C.POINTER(Column), _I32, _I64, _P, _I64, _P, _P, _P,

@@ -131,6 +131,19 @@ static int validate_operand(const vgpu_operand& o, bool allow_none, int n_cols, 
 
 } // namespace vg
 
+namespace vg {
+// dst[i] = table[src[i]]: a dictionary-encoded VARCHAR key column (int32 indices into a batch's base strings) becomes
+// the operator-wide value ids of those strings while the batch is gathered on the device (VectorHasher::makeValueIds
+// per base value, velox/exec/VectorHasher.cpp:241-289, then one gather per row — on the GPU instead of the host).
+__global__ void translate_i32_kernel(int32_t* dst, const int32_t* src, const int32_t* table, int32_t table_len, int64_t n, uint32_t* err) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t ix = src[i];
+  if (ix < 0 || ix >= table_len) { atomicOr(err, kErrKeyRange); dst[i] = 0; return; }
+  dst[i] = __ldg(table + ix);
+}
+} // namespace vg
+
 using namespace vg;
 
 
@@ -219,6 +232,15 @@ int vgpu_host_is_pinned(const void* hptr, int32_t* pinned) {
   const cudaError_t e = cudaPointerGetAttributes(&a, hptr);
   if (e != cudaSuccess) { cudaGetLastError(); *pinned = 0; return VGPU_OK; }
   *pinned = a.type == cudaMemoryTypeHost ? 1 : 0;
+  return VGPU_OK;
+}
+
+int vgpu_translate_i32(int32_t* dst, const int32_t* src, const int32_t* table, int32_t table_len, int64_t n, void* stream) {
+  if (n <= 0) return VGPU_OK;
+  if (!dst || !src || !table) return VGPU_ERR_INVALID;
+  translate_i32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dst, src, table, table_len, n, device_err_word());
+  VG_CUDA(cudaGetLastError());
+  count_launch();
   return VGPU_OK;
 }
 

@@ -1,0 +1,126 @@
+// Host -> device staging ring and the pinned host allocator of the GPU operators (GpuDevice.h).
+#include <cstdlib>
+#include <cstring>
+
+#include "GpuDevice.h"
+
+namespace vb200 {
+
+namespace memory {
+namespace {
+void* mallocAlloc(size_t bytes) { return std::malloc(bytes ? bytes : 1); }
+void mallocFree(void* p) { std::free(p); }
+void* pinnedAlloc(size_t bytes) {
+  void* p = nullptr;
+  return vgpu_alloc_host(bytes ? bytes : 16, &p) == VGPU_OK ? p : nullptr;
+}
+void pinnedFree(void* p) { vgpu_free_host(p); }
+HostAllocator g_allocator{mallocAlloc, mallocFree};
+} // namespace
+HostAllocator& hostAllocator() { return g_allocator; }
+} // namespace memory
+
+namespace gpu {
+
+void usePinnedHostMemory(bool on) {
+  memory::hostAllocator() = on ? memory::HostAllocator{memory::pinnedAlloc, memory::pinnedFree} : memory::HostAllocator{memory::mallocAlloc, memory::mallocFree};
+}
+
+Staging::Staging(void* computeStream) : compute_(computeStream) {
+  check(vgpu_stream_create(&copy_), "vgpu_stream_create");
+  for (auto& s : slots_) {
+    check(vgpu_event_create(&s.freeEv), "vgpu_event_create");
+    check(vgpu_event_create(&s.readyEv), "vgpu_event_create");
+  }
+}
+
+Staging::~Staging() {
+  for (auto& s : slots_) {
+    if (s.inFlight) vgpu_event_sync(s.freeEv);
+    if (s.dev) vgpu_free(s.dev);
+    if (s.pin) vgpu_free_host(s.pin);
+    if (s.freeEv) vgpu_event_destroy(s.freeEv);
+    if (s.readyEv) vgpu_event_destroy(s.readyEv);
+  }
+  if (copy_) vgpu_stream_destroy(copy_);
+}
+
+void Staging::begin(size_t bytes) {
+  VB_CHECK(!active_, "Staging::begin while a slot is open");
+  cur_ = (cur_ + 1) % kSlots;
+  Slot& s = slots_[cur_];
+  if (s.inFlight) { // the only place the host waits: a full ring ahead of the GPU
+    check(vgpu_event_sync(s.freeEv), "vgpu_event_sync");
+    s.inFlight = false;
+  }
+  s.keep.clear();
+  bytes = (bytes + 4095) & ~(size_t)4095;
+  if (bytes > s.cap) {
+    if (s.dev) check(vgpu_free(s.dev), "vgpu_free");
+    if (s.pin) check(vgpu_free_host(s.pin), "vgpu_free_host");
+    s.dev = s.pin = nullptr;
+    void* d = nullptr;
+    void* h = nullptr;
+    check(vgpu_alloc(bytes, &d), "vgpu_alloc");
+    check(vgpu_alloc_host(bytes, &h), "vgpu_alloc_host");
+    s.dev = (char*)d;
+    s.pin = (char*)h;
+    s.cap = bytes;
+  }
+  s.used = s.pinUsed = 0;
+  active_ = true;
+}
+
+void* Staging::reserve(size_t bytes) {
+  VB_CHECK(active_, "Staging::reserve without a slot");
+  Slot& s = slots_[cur_];
+  const size_t at = (s.used + 255) & ~(size_t)255;
+  VB_CHECK(at + bytes <= s.cap, "staging slot overflow (internal: the caller sized the slot too small)");
+  s.used = at + bytes;
+  return s.dev + at;
+}
+
+void Staging::copyIn(void* dst, const void* host, size_t bytes, const std::shared_ptr<const void>& owner) {
+  if (!bytes) return;
+  Slot& s = slots_[cur_];
+  int32_t pinned = 0;
+  if (owner) vgpu_host_is_pinned(host, &pinned);
+  if (pinned) {
+    s.keep.push_back(owner);
+    check(vgpu_h2d_async(dst, host, bytes, copy_), "vgpu_h2d_async");
+  } else {
+    const size_t at = (s.pinUsed + 63) & ~(size_t)63;
+    VB_CHECK(at + bytes <= s.cap, "staging slot overflow (pinned area)");
+    std::memcpy(s.pin + at, host, bytes);
+    s.pinUsed = at + bytes;
+    check(vgpu_h2d_async(dst, s.pin + at, bytes, copy_), "vgpu_h2d_async");
+    stagedBytes += (int64_t)bytes;
+  }
+  h2dBytes += (int64_t)bytes;
+}
+
+void* Staging::scratch(size_t bytes, bool zero) {
+  void* d = reserve(bytes ? bytes : 8);
+  if (zero) check(vgpu_memset_async(d, 0, bytes ? bytes : 8, copy_), "vgpu_memset_async");
+  return d;
+}
+
+void Staging::ready() {
+  VB_CHECK(active_, "Staging::ready without a slot");
+  Slot& s = slots_[cur_];
+  check(vgpu_event_record(s.readyEv, copy_), "vgpu_event_record");
+  check(vgpu_stream_wait_event(compute_, s.readyEv), "vgpu_stream_wait_event");
+}
+
+void Staging::release() {
+  VB_CHECK(active_, "Staging::release without a slot");
+  Slot& s = slots_[cur_];
+  check(vgpu_event_record(s.freeEv, compute_), "vgpu_event_record");
+  // the slot's next copies must not overtake the kernels that still read it
+  check(vgpu_stream_wait_event(copy_, s.freeEv), "vgpu_stream_wait_event");
+  s.inFlight = true;
+  active_ = false;
+}
+
+} // namespace gpu
+} // namespace vb200

@@ -1,4 +1,4 @@
-// Small RAII layer over the C ABI for the operators: status -> exception, device buffers, and the
+// Small RAII layer over the C ABI for the operators: status -> exception, the host -> device staging ring, and the
 // device image of the input columns a program reads (the DecodedVector triple per column,
 // velox/vector/DecodedVector.cpp:60-187).
 #pragma once
@@ -7,10 +7,70 @@
 namespace vb200 {
 namespace gpu {
 
+// Vectors built after usePinnedHostMemory(true) keep their value arrays in page-locked memory (Vectors.h
+// memory::hostAllocator): the staging ring then copies them to HBM with one DMA per column, straight out of the vector.
+void usePinnedHostMemory(bool on);
+
+// Host -> device staging of one operator.  kSlots slots are used round-robin; a slot is a device arena plus a pinned host
+// area of the same size.  Uploads run on a copy stream of their own, so the copies of the batch being gathered overlap
+// the kernels of the previous one; events order the two streams without blocking the host:
+//   copy stream   waits for the slot's "free" event (recorded on the compute stream after the kernels that read it),
+//   compute stream waits for the slot's "ready" event (recorded on the copy stream after the batch's last copy).
+// The host only blocks when it is a full ring ahead of the GPU (back-pressure), never per batch — this replaces the
+// cudaMalloc / pageable cudaMemcpy / stream synchronise per addInput of round 1.
+class Staging {
+ public:
+  static constexpr int kSlots = 3;
+  explicit Staging(void* computeStream);
+  ~Staging();
+  Staging(const Staging&) = delete;
+  Staging& operator=(const Staging&) = delete;
+
+  // Starts the next slot with at least `bytes` of device (and pinned) room; waits until its previous user is done.
+  void begin(size_t bytes);
+  bool active() const { return active_; }
+  size_t room() const { return active_ ? slots_[cur_].cap - slots_[cur_].used : 0; }
+  // Device memory inside the current slot (256-byte aligned).  Throws when the slot is full.
+  void* reserve(size_t bytes);
+  // Copies host memory into slot memory.  Page-locked sources are copied directly (asynchronously: `owner` keeps the
+  // source alive until the slot is reused; without an owner the source is staged like pageable memory); pageable
+  // sources go through the slot's pinned area.
+  void copyIn(void* dst, const void* host, size_t bytes, const std::shared_ptr<const void>& owner = nullptr);
+  void* upload(const void* host, size_t bytes, const std::shared_ptr<const void>& owner = nullptr) {
+    void* d = reserve(bytes);
+    if (bytes) copyIn(d, host, bytes, owner);
+    return d;
+  }
+  void* scratch(size_t bytes, bool zero);
+  // All copies of the slot are issued: the compute stream will wait for them.
+  void ready();
+  // The kernels reading the slot are launched: the slot may be reused once they finish.
+  void release();
+  void* copyStream() const { return copy_; }
+  int64_t h2dBytes = 0, stagedBytes = 0;
+
+ private:
+  struct Slot {
+    char* dev = nullptr;
+    char* pin = nullptr;
+    size_t cap = 0, used = 0, pinUsed = 0;
+    void* freeEv = nullptr;
+    void* readyEv = nullptr;
+    bool inFlight = false;
+    std::vector<std::shared_ptr<const void>> keep;
+  };
+  Slot slots_[kSlots];
+  int cur_ = -1;
+  bool active_ = false;
+  void* compute_ = nullptr;
+  void* copy_ = nullptr;
+};
+
 struct DeviceBatch {
   std::vector<vgpu_column> cols;
   std::vector<void*> owned;
   void* stream = nullptr;
+  Staging* staging = nullptr; // when set, memory comes from the staging slot and copies run on its copy stream
   ~DeviceBatch() { release(); }
   void release() {
     for (void* p : owned) vgpu_free(p);
@@ -18,6 +78,7 @@ struct DeviceBatch {
     cols.clear();
   }
   void* upload(const void* host, size_t bytes) {
+    if (staging) return staging->upload(host, bytes);
     void* d = nullptr;
     check(vgpu_alloc(bytes ? bytes : 8, &d), "vgpu_alloc");
     owned.push_back(d);
@@ -25,6 +86,7 @@ struct DeviceBatch {
     return d;
   }
   void* scratch(size_t bytes, bool zero) {
+    if (staging) return staging->scratch(bytes, zero);
     void* d = nullptr;
     check(vgpu_alloc(bytes ? bytes : 8, &d), "vgpu_alloc");
     owned.push_back(d);
@@ -38,6 +100,8 @@ size_t deviceWidth(int vgpuType); // bytes per value (0 for bit-packed BOOLEAN)
 // Appends the device image of `v` (numeric / boolean, any stack of dictionary / constant wrappers) to `b`.
 // `idsOfBase` (optional): replaces the base values by these int32 value ids (VARCHAR keys).
 void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase = nullptr);
+// Upper bound of the device bytes bindColumn needs for `v`.
+size_t bindBytes(const VectorPtr& v);
 
 // Flattened view of a vector: base flat vector + per-row index (or -1 for "row itself") + null test.
 struct Decoded {
@@ -49,6 +113,8 @@ struct Decoded {
   size_t size = 0;
 };
 Decoded decode(const VectorPtr& v);
+// Raw value array of a flat vector (bit words for BOOLEAN).
+const void* rawValuesOf(const BaseVector* flat);
 
 } // namespace gpu
 } // namespace vb200

@@ -61,8 +61,7 @@ Decoded decode(const VectorPtr& v) {
   }
 }
 
-namespace {
-const void* rawOf(const BaseVector* flat, int t) {
+const void* rawValuesOf(const BaseVector* flat) {
   switch (flat->type()->kind()) {
     case TypeKind::BOOLEAN: return static_cast<const BoolVector*>(flat)->rawValues();
     case TypeKind::TINYINT: return static_cast<const FlatVector<int8_t>*>(flat)->rawValues();
@@ -73,9 +72,16 @@ const void* rawOf(const BaseVector* flat, int t) {
     case TypeKind::DOUBLE: return static_cast<const FlatVector<double>*>(flat)->rawValues();
     default: throw VeloxRuntimeError("no raw device image for " + flat->type()->toString());
   }
-  (void)t;
 }
-} // namespace
+
+size_t bindBytes(const VectorPtr& v) {
+  // values + indices + two bitmaps, each padded to the staging alignment
+  const BaseVector* cur = v.get();
+  size_t n = v->size(), base = n;
+  while (cur->encoding() == VectorEncoding::DICTIONARY) { cur = static_cast<const DictionaryVector*>(cur)->valueVector().get(); base = cur->size(); }
+  if (cur->encoding() == VectorEncoding::CONSTANT) { cur = static_cast<const ConstantVector*>(cur)->valueVector().get(); base = cur->size(); }
+  return base * 8 + n * 4 + 2 * (bits::nwords(std::max(n, base)) * 8) + 5 * 256;
+}
 
 void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase) {
   Decoded d = decode(v);
@@ -85,7 +91,7 @@ void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* 
   const size_t w = deviceWidth(t);
   const size_t baseN = d.base->size();
   auto baseBytes = [&](size_t n) { return w ? n * w : bits::nwords(n) * 8; };
-  const void* baseRaw = idsOfBase ? (const void*)idsOfBase->data() : rawOf(d.base, t);
+  const void* baseRaw = idsOfBase ? (const void*)idsOfBase->data() : rawValuesOf(d.base);
   if (d.constant) {
     c.encoding = VGPU_CONSTANT;
     c.constant_is_null = d.constantNull || (d.base->mayHaveNulls() && !bits::isBitSet(d.base->nulls().data(), 0));

@@ -1,10 +1,17 @@
 // GpuHashAggregation: exec::HashAggregation + GroupingSet on the GPU (velox/exec/HashAggregation.cpp:97-472,
-// velox/exec/GroupingSet.cpp:177-307,513-712).  Per batch: bind the input columns (VARCHAR keys become int32
-// value ids, VectorHasher::makeValueIds analogue, velox/exec/VectorHasher.cpp:110-143), one
-// vgpu_agg_add_input call (filter + projections + find-or-insert + accumulate in one kernel).  After
-// noMoreInput: vgpu_agg_extract, then output batches of preferredOutputBatchRows groups.
-// Not restated: partial-aggregation flushing / abandoning (HashAggregation.cpp:229-233,326-386) — partial
-// output is produced once, at end of input — spilling, sorted / distinct / masked aggregates.
+// velox/exec/GroupingSet.cpp:177-307,513-712).
+// addInput: the batch's columns are copied into the current slot of the staging ring (GpuDevice.h) on a copy stream —
+// VARCHAR keys as int32 value ids (VectorHasher::makeValueIds analogue, velox/exec/VectorHasher.cpp:110-143: one
+// dictionary lookup per BASE string on the host, the per-row gather on the device) — and small batches (Velox's
+// default scan batch is ~4 k rows) are gathered there until QueryConfig::coalesceRows rows are resident; then ONE
+// vgpu_agg_add_input call runs filter + projections + grouping + accumulation over all of them.  No device allocation,
+// no pageable copy and no stream synchronisation per batch; data errors (sum overflow, checked arithmetic) are
+// collected every QueryConfig::errorCheckEvery launches and at noMoreInput.
+// After noMoreInput: vgpu_agg_extract, then output batches of preferredOutputBatchRows groups.
+// A partial aggregation flushes (HashAggregation.cpp:326-348): when the device state passes
+// maxPartialAggregationMemory its groups are emitted downstream and the state is reset.
+// Not restated: abandoning partial aggregation (:350-366), spilling, sorted / distinct aggregates.
+#include <chrono>
 #include <cmath>
 #include <unordered_map>
 
@@ -57,6 +64,20 @@ struct GpuHashAggregation::Impl {
   std::vector<int64_t> rows; // extracted packed groups
   int64_t nGroups = -1;
   int64_t cursor = 0;
+  // ---- staging / coalescing (GpuDevice.h) ----
+  std::unique_ptr<Staging> staging;
+  struct PendingColumn {
+    int type = 0;            // vgpu_type on the device
+    size_t width = 0;        // bytes per value
+    char* dValues = nullptr; // device array of capacity pendingCap values
+    bool anyNulls = false;
+    std::vector<uint64_t> notNull; // host bitmap of the gathered rows (uploaded at launch when anyNulls)
+  };
+  std::vector<PendingColumn> pending;
+  int64_t pendingRows = 0, pendingCap = 0;
+  int64_t launchesSinceCheck = 0;
+  int64_t rowsSinceFlush = 0;
+  GpuHashAggregation::Stats stats;
   int rowWords() const { return 3 + 2 * (int)accs.size(); }
   // ids per key in the device's numbering: [lo, hi] plus one id for NULL unless NULL keys are dropped
   int64_t nullIds() const { return node->ignoreNullKeys() ? 0 : 1; }
@@ -262,7 +283,143 @@ struct GpuHashAggregation::Impl {
     return copy;
   }
 
+  // ---- one device launch over `batch` ----------------------------------------------------------------------------
+  void launch(DeviceBatch& batch, int64_t nrows) {
+    staging->ready();
+    int rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), nrows, nullptr, 0, stream);
+    if (rc == VGPU_ERR_UNSUPPORTED && mode == VGPU_AGG_ARRAY && !sawInput) {
+      // HashTable::decideHashMode analogue: fall from the array mode to the hash mode (never to a CPU path)
+      vgpu_agg_destroy(agg); agg = nullptr;
+      vgpu_program_destroy(program); program = nullptr;
+      forceHash = true;
+      create();
+      rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), nrows, nullptr, 0, stream);
+    }
+    staging->release();
+    check(rc, "vgpu_agg_add_input");
+    ++stats.deviceLaunches;
+    sawInput = true;
+    // data errors (sum overflow, checked arithmetic in fused projections) surface like the exception thrown out of
+    // HashAggregation::addInput, a few batches late at most
+    if (++launchesSinceCheck >= std::max(1, ctx->queryConfig.errorCheckEvery)) checkErrors();
+  }
+  void checkErrors() {
+    launchesSinceCheck = 0;
+    check(vgpu_agg_check_errors(agg, stream), "HashAggregation");
+  }
+
+  // ---- coalescing ----------------------------------------------------------------------------------------------
+  size_t pendingBytes(int64_t cap) const {
+    size_t bytes = 0;
+    for (auto& name : lowered.columns) {
+      const int t = deviceType(exprOf(name)->type());
+      bytes += (size_t)cap * std::max<size_t>(deviceWidth(t), 4) + bits::nwords((size_t)cap) * 8 + 1024;
+    }
+    return bytes + (1 << 16);
+  }
+  void openPending(int64_t atLeastRows) {
+    pendingCap = std::max<int64_t>(ctx->queryConfig.coalesceRows, atLeastRows);
+    // room for the gathered columns plus, per VARCHAR key batch, its raw indices and id table (transient)
+    staging->begin(pendingBytes(pendingCap) + (size_t)pendingCap * 4 * keys.size() + (1 << 20));
+    pending.assign(lowered.columns.size(), PendingColumn{});
+    for (size_t c = 0; c < lowered.columns.size(); ++c) {
+      auto& pc = pending[c];
+      pc.type = deviceType(exprOf(lowered.columns[c])->type());
+      pc.width = deviceWidth(pc.type);
+      pc.dValues = (char*)staging->reserve((size_t)pendingCap * pc.width);
+    }
+    pendingRows = 0;
+  }
+  // FLAT numeric columns and VARCHAR keys (flat or one dictionary over flat strings) can be gathered
+  bool canCoalesce(const RowVectorPtr& in, const std::vector<VectorPtr>& vecs) const {
+    for (size_t c = 0; c < vecs.size(); ++c) {
+      const auto& v = vecs[c];
+      const auto kind = v->type()->kind();
+      if (kind == TypeKind::BOOLEAN) return false; // bit-packed values: appended rarely enough to take the direct path
+      if (kind == TypeKind::VARCHAR) {
+        if (v->encoding() == VectorEncoding::FLAT) continue;
+        if (v->encoding() == VectorEncoding::DICTIONARY && static_cast<const DictionaryVector*>(v.get())->valueVector()->encoding() == VectorEncoding::FLAT) continue;
+        return false;
+      }
+      if (v->encoding() != VectorEncoding::FLAT) return false;
+    }
+    return in->size() > 0;
+  }
+  static void appendBits(std::vector<uint64_t>& dst, size_t at, const uint64_t* src, size_t n) {
+    dst.resize(bits::nwords(at + n), 0);
+    for (size_t i = 0; i < n; ++i) if (!src || bits::isBitSet(src, i)) bits::setBit(dst.data(), at + i, true);
+  }
+  void appendPending(const RowVectorPtr& in, const std::vector<VectorPtr>& vecs, const std::vector<int>& varcharKeyOf,
+                     const std::vector<std::vector<int32_t>>& keyIds) {
+    const size_t n = in->size();
+    if (pendingCap > 0 && pendingRows + (int64_t)n > pendingCap) flushPending();
+    if (pendingCap == 0) openPending((int64_t)n);
+    std::shared_ptr<const void> owner = in; // keeps pinned vector memory alive while the DMA is in flight
+    for (size_t c = 0; c < vecs.size(); ++c) {
+      auto& pc = pending[c];
+      const auto& v = vecs[c];
+      char* dst = pc.dValues + (size_t)pendingRows * pc.width;
+      const uint64_t* rowNulls = nullptr;
+      std::vector<uint64_t> merged;
+      if (varcharKeyOf[c] >= 0) {
+        const auto& ids = keyIds[varcharKeyOf[c]]; // id per BASE string of this batch
+        if (v->encoding() == VectorEncoding::FLAT) { // one id per row already
+          staging->copyIn(dst, ids.data(), n * 4);
+          if (v->mayHaveNulls()) rowNulls = v->nulls().data();
+        } else {
+          auto dict = static_cast<const DictionaryVector*>(v.get());
+          const BaseVector* base = dict->valueVector().get();
+          void* dIdx = staging->upload(dict->rawIndices(), n * 4, owner);
+          void* dTab = staging->upload(ids.data(), ids.size() * 4);
+          check(vgpu_translate_i32((int32_t*)dst, (const int32_t*)dIdx, (const int32_t*)dTab, (int32_t)ids.size(), (int64_t)n, staging->copyStream()), "vgpu_translate_i32");
+          if (v->mayHaveNulls() || base->mayHaveNulls()) { // NULL when the wrapper or the base string is NULL
+            merged.assign(bits::nwords(n), 0);
+            for (size_t i = 0; i < n; ++i) {
+              const bool ok = (!v->mayHaveNulls() || bits::isBitSet(v->nulls().data(), i)) &&
+                              (!base->mayHaveNulls() || bits::isBitSet(base->nulls().data(), (size_t)dict->rawIndices()[i]));
+              if (ok) bits::setBit(merged.data(), i, true);
+            }
+            rowNulls = merged.data();
+          }
+        }
+      } else {
+        staging->copyIn(dst, rawValuesOf(v.get()), n * pc.width, owner);
+        if (v->mayHaveNulls()) rowNulls = v->nulls().data();
+      }
+      if (rowNulls && !pc.anyNulls) { pc.anyNulls = true; pc.notNull.assign(bits::nwords((size_t)pendingRows), ~0ull); }
+      if (pc.anyNulls) appendBits(pc.notNull, (size_t)pendingRows, rowNulls, n);
+    }
+    pendingRows += (int64_t)n;
+    if (pendingRows >= pendingCap) flushPending();
+  }
+  void flushPending() {
+    if (pendingCap == 0) return;
+    if (pendingRows > 0) {
+      DeviceBatch batch;
+      batch.stream = stream;
+      batch.staging = staging.get();
+      for (auto& pc : pending) {
+        vgpu_column c{};
+        c.type = pc.type;
+        c.encoding = VGPU_FLAT;
+        c.values = pc.dValues;
+        if (pc.anyNulls) c.nulls = (const uint64_t*)staging->upload(pc.notNull.data(), bits::nwords((size_t)pendingRows) * 8);
+        batch.cols.push_back(c);
+      }
+      launch(batch, pendingRows);
+    } else {
+      staging->ready();
+      staging->release();
+    }
+    pendingCap = 0;
+    pendingRows = 0;
+    pending.clear();
+  }
+
   void addBatch(const RowVectorPtr& in) {
+    const auto t0 = std::chrono::steady_clock::now();
+    ++stats.inputVectors;
+    stats.inputRows += (int64_t)in->size();
     std::vector<std::vector<int32_t>> keyIds(keys.size());
     std::vector<VectorPtr> keyVecs(keys.size());
     bool grew = false;
@@ -273,34 +430,42 @@ struct GpuHashAggregation::Impl {
       keyIds[i] = idsOf(keys[i], keyVecs[i]);
       if (agg && (int64_t)keys[i].strings.size() - 1 > keys[i].hi) grew = true;
     }
+    if (!staging) staging.reset(new Staging(stream));
     if (!agg) { create(); }
     else if (grew) {
+      flushPending(); // rows gathered so far carry ids of the old range
       if (mode == VGPU_AGG_ARRAY) regrow();
       else throw VeloxRuntimeError("more than 2^20 distinct strings in a grouping key");
     }
-    DeviceBatch batch;
-    batch.stream = stream;
     std::vector<VectorPtr> keepAlive;
-    for (auto& name : lowered.columns) {
-      int varcharKey = -1;
-      for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name() == name) varcharKey = (int)i;
-      if (varcharKey >= 0) bindColumn(batch, keyVecs[varcharKey], &keyIds[varcharKey]);
-      else bindColumn(batch, columnByName(in, name, keepAlive));
+    std::vector<VectorPtr> vecs(lowered.columns.size());
+    std::vector<int> varcharKeyOf(lowered.columns.size(), -1);
+    for (size_t c = 0; c < lowered.columns.size(); ++c) {
+      const auto& name = lowered.columns[c];
+      for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name() == name) varcharKeyOf[c] = (int)i;
+      vecs[c] = varcharKeyOf[c] >= 0 ? keyVecs[varcharKeyOf[c]] : columnByName(in, name, keepAlive);
     }
-    int rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream);
-    if (rc == VGPU_ERR_UNSUPPORTED && mode == VGPU_AGG_ARRAY && !sawInput) {
-      // HashTable::decideHashMode analogue: fall from the array mode to the hash mode (never to a CPU path)
-      vgpu_agg_destroy(agg); agg = nullptr;
-      vgpu_program_destroy(program); program = nullptr;
-      forceHash = true;
-      create();
-      rc = vgpu_agg_add_input(agg, program, batch.cols.data(), (int32_t)batch.cols.size(), (int64_t)in->size(), nullptr, 0, stream);
+    if (keepAlive.empty() && canCoalesce(in, vecs)) {
+      appendPending(in, vecs, varcharKeyOf, keyIds);
+    } else {
+      // other encodings (dictionary / constant wrappers over numbers, booleans): this batch alone, through a slot of its own
+      flushPending();
+      size_t bytes = 1 << 16;
+      for (auto& v : vecs) bytes += bindBytes(v);
+      staging->begin(bytes);
+      DeviceBatch batch;
+      batch.stream = stream;
+      batch.staging = staging.get();
+      for (size_t c = 0; c < vecs.size(); ++c) {
+        if (varcharKeyOf[c] >= 0) bindColumn(batch, vecs[c], &keyIds[varcharKeyOf[c]]);
+        else bindColumn(batch, vecs[c]);
+      }
+      launch(batch, (int64_t)in->size());
     }
-    check(rc, "vgpu_agg_add_input");
-    // data errors (sum overflow, checked arithmetic in fused projections) surface here, like the exception
-    // thrown out of HashAggregation::addInput; this also makes the batch's device copies safe to free
-    check(vgpu_check_errors(stream), "HashAggregation");
-    sawInput = true;
+    rowsSinceFlush += (int64_t)in->size();
+    stats.h2dBytes = staging->h2dBytes;
+    stats.stagedBytes = staging->stagedBytes;
+    stats.addInputWallMs += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   }
 };
 
@@ -330,9 +495,11 @@ GpuHashAggregation::GpuHashAggregation(exec::DriverCtx* ctx, int32_t id, std::sh
 }
 
 GpuHashAggregation::~GpuHashAggregation() { close(); }
+const GpuHashAggregation::Stats& GpuHashAggregation::stats() const { return impl_->stats; }
 
 void GpuHashAggregation::close() {
   auto& m = *impl_;
+  m.staging.reset(); // waits for the copies / kernels still reading its slots
   if (m.agg) { vgpu_agg_destroy(m.agg); m.agg = nullptr; }
   if (m.program) { vgpu_program_destroy(m.program); m.program = nullptr; }
   if (m.stream) { vgpu_stream_destroy(m.stream); m.stream = nullptr; }
@@ -347,6 +514,7 @@ void GpuHashAggregation::addInput(RowVectorPtr input) {
 void GpuHashAggregation::noMoreInput() {
   Operator::noMoreInput();
   auto& m = *impl_;
+  if (m.agg) { m.flushPending(); if (m.sawInput) m.checkErrors(); }
   if (!m.sawInput) {
     if (!m.keys.empty()) { finished_ = true; return; } // grouped aggregation over no input: no rows (SumTest.cpp:509-516)
     m.create();                                        // global: exactly one row, even on empty input

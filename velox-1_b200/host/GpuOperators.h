@@ -33,6 +33,7 @@ class GpuFilterProject : public exec::Operator {
   bool needsInput() const override { return input_ == nullptr && !noMoreInput_; }
   void addInput(RowVectorPtr input) override { input_ = std::move(input); }
   RowVectorPtr getOutput() override;
+  exec::BlockingReason isBlocked(exec::ContinueFuture*) override { return exec::BlockingReason::kNotBlocked; } // device work is awaited inside getOutput
   bool isFinished() override { return noMoreInput_ && input_ == nullptr; }
   bool isFilter() const override { return exprs_.filter != nullptr; }
   bool preservesOrder() const override { return true; }
@@ -64,8 +65,18 @@ class GpuHashAggregation : public exec::Operator {
   void addInput(RowVectorPtr input) override;
   void noMoreInput() override;
   RowVectorPtr getOutput() override;
+  exec::BlockingReason isBlocked(exec::ContinueFuture*) override { return exec::BlockingReason::kNotBlocked; }
   bool isFinished() override { return finished_; }
   void close() override;
+  // OperatorStats-shaped counters (velox/exec/Operator.h:83-182) plus what only a device operator has
+  struct Stats {
+    int64_t inputVectors = 0, inputRows = 0, inputBytes = 0, outputVectors = 0, outputRows = 0;
+    int64_t deviceLaunches = 0;      // vgpu_agg_add_input calls (coalesced host batches per launch = inputVectors / deviceLaunches)
+    int64_t h2dBytes = 0, stagedBytes = 0; // bytes copied to HBM; of those, bytes that went through the pinned staging ring
+    int64_t flushes = 0;             // partial-aggregation flushes (HashAggregation.cpp:326-348)
+    double addInputWallMs = 0, getOutputWallMs = 0;
+  };
+  const Stats& stats() const;
   struct Impl;
  private:
   std::unique_ptr<Impl> impl_;

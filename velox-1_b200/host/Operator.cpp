@@ -79,8 +79,10 @@ std::unique_ptr<Driver> createDriver(const core::PlanNodePtr& plan, const QueryC
     VB_CHECK(op != nullptr, "No operator registered for plan node " + node->name() + " (id " + node->id() + "): call registerGpuOperators()");
     ops.push_back(std::move(op));
   }
+  core::PlanFragment fragment;
+  fragment.planNode = plan;
   for (auto& a : DriverFactory::adapters()) {
-    if (a.inspect) a.inspect(factory);
+    if (a.inspect) a.inspect(fragment);
     if (a.adapt && a.adapt(factory, *driver)) break; // first adapter that rewrites wins (LocalPlanner.cpp:582-588)
   }
   for (auto& op : ops) op->initialize();
@@ -92,6 +94,8 @@ void Driver::push(size_t from, RowVectorPtr batch, std::vector<RowVectorPtr>& re
   VB_CHECK(batch->size() > 0, "operators must not produce empty vectors");
   auto& op = *operators_[from];
   if (op.isFinished()) return;
+  ContinueFuture future;
+  VB_CHECK(op.isBlocked(&future) == BlockingReason::kNotBlocked, op.operatorType() + " blocked: this single-threaded driver has no one to wait for");
   VB_CHECK(op.needsInput(), op.operatorType() + " does not accept input");
   op.addInput(std::move(batch));
   while (auto out = op.getOutput()) push(from + 1, std::move(out), results);

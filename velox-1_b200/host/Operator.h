@@ -9,6 +9,8 @@
 // registered PlanNodeTranslator — this repository has no CPU operators to fall back to.
 #pragma once
 #include <functional>
+#include <future>
+#include <optional>
 
 #include "Plan.h"
 
@@ -16,8 +18,12 @@ namespace vb200 {
 namespace exec {
 
 struct QueryConfig {
-  int32_t preferredOutputBatchRows = 1024; // velox/core/QueryConfig.h kPreferredOutputBatchRows
-  int32_t device = 0;                      // CUDA device of this driver (one driver = one GPU stream)
+  int32_t preferredOutputBatchRows = 1024; // velox/core/QueryConfig.h kPreferredOutputBatchRows ("preferred_output_batch_rows")
+  // GPU knobs (the reference's QueryConfig is a string map; these would be its "gpu."-prefixed keys)
+  int32_t device = 0;                      // gpu.device: CUDA device of this driver (one driver = one GPU stream)
+  int64_t coalesceRows = 1 << 20;          // gpu.coalesce_rows: host batches are gathered on the device until this many rows before a kernel runs
+  int32_t errorCheckEvery = 16;            // gpu.error_check_every: device launches between two data-error checks (plus one at noMoreInput)
+  int64_t maxPartialAggregationMemory = 1ll << 34; // max_partial_aggregation_memory (device bytes of logged partial groups before a flush)
 };
 
 struct DriverCtx {
@@ -27,18 +33,22 @@ struct DriverCtx {
 };
 
 enum class BlockingReason { kNotBlocked };
+using ContinueFuture = std::future<void>;   // folly::SemiFuture<folly::Unit> in the reference (velox/exec/Driver.h)
+namespace common { struct SpillConfig {}; } // the path never spills; kept for the constructor's shape
 
 class Operator {
  public:
-  Operator(DriverCtx* ctx, RowTypePtr outputType, int32_t operatorId, std::string planNodeId, std::string operatorType)
-      : ctx_(ctx), outputType_(std::move(outputType)), operatorId_(operatorId), planNodeId_(std::move(planNodeId)), operatorType_(std::move(operatorType)) {}
+  // velox/exec/Operator.h:309-315
+  Operator(DriverCtx* ctx, RowTypePtr outputType, int32_t operatorId, std::string planNodeId, std::string operatorType,
+           std::optional<common::SpillConfig> spillConfig = std::nullopt)
+      : ctx_(ctx), outputType_(std::move(outputType)), operatorId_(operatorId), planNodeId_(std::move(planNodeId)), operatorType_(std::move(operatorType)) { (void)spillConfig; }
   virtual ~Operator() = default;
   virtual void initialize() {}
   virtual bool needsInput() const = 0;
   virtual void addInput(RowVectorPtr input) = 0;
   virtual void noMoreInput() { noMoreInput_ = true; }
   virtual RowVectorPtr getOutput() = 0; // nullptr or a NON-empty vector (velox/exec/Driver.cpp:550-556)
-  virtual BlockingReason isBlocked() { return BlockingReason::kNotBlocked; }
+  virtual BlockingReason isBlocked(ContinueFuture* future) = 0; // velox/exec/Operator.h:361 (pure virtual there, too)
   virtual bool isFinished() = 0;
   virtual void close() { input_ = nullptr; }
   virtual bool isFilter() const { return false; }
@@ -69,6 +79,7 @@ class SourceOperator : public Operator {
   using Operator::Operator;
   bool needsInput() const override { return false; }
   void addInput(RowVectorPtr) override { throw VeloxRuntimeError("SourceOperator does not support addInput()"); }
+  BlockingReason isBlocked(ContinueFuture*) override { return BlockingReason::kNotBlocked; }
 };
 
 class PlanNodeTranslator {
@@ -78,6 +89,15 @@ class PlanNodeTranslator {
   virtual std::unique_ptr<Operator> toOperator(DriverCtx* ctx, int32_t id, const core::PlanNodePtr& node) { return nullptr; }
 };
 
+} // namespace exec
+namespace core {
+// velox/core/PlanFragment.h:40-60 (the fields an adapter's inspect() can look at on this path)
+struct PlanFragment {
+  PlanNodePtr planNode; // top level (root) plan node
+};
+} // namespace core
+namespace exec {
+
 class Driver;
 struct DriverFactory {
   std::vector<core::PlanNodePtr> planNodes; // source first
@@ -86,7 +106,7 @@ struct DriverFactory {
                                                            std::vector<std::unique_ptr<Operator>> replaceWith) const;
   struct DriverAdapter {
     std::string label;
-    std::function<void(const DriverFactory&)> inspect;
+    std::function<void(const core::PlanFragment&)> inspect; // velox/exec/Driver.h:482-486
     std::function<bool(const DriverFactory&, Driver&)> adapt;
   };
   static void registerAdapter(DriverAdapter adapter);

@@ -91,6 +91,32 @@ inline RowTypePtr ROW(std::vector<std::string> names, std::vector<TypePtr> types
   return std::make_shared<RowType>(std::move(names), std::move(types));
 }
 
+// ---- host memory of flat buffers (velox/common/memory/MemoryPool.h analogue) ---------------------------------
+// Vectors allocate their value arrays through a process-wide hook.  gpu::usePinnedHostMemory(true) points it at
+// page-locked memory, which lets the GPU operators copy a batch with one asynchronous DMA straight out of the vector
+// (what a Velox deployment gets by giving the scan's MemoryPool a pinned allocator); the default is malloc.
+namespace memory {
+struct HostAllocator { void* (*alloc)(size_t bytes); void (*dealloc)(void* p); };
+HostAllocator& hostAllocator();
+template <typename T>
+struct PoolAllocator {
+  using value_type = T;
+  HostAllocator backing;
+  PoolAllocator() : backing(hostAllocator()) {}
+  template <typename U> PoolAllocator(const PoolAllocator<U>& o) : backing(o.backing) {}
+  T* allocate(size_t n) {
+    void* p = backing.alloc(n * sizeof(T));
+    if (!p) throw std::bad_alloc();
+    return static_cast<T*>(p);
+  }
+  void deallocate(T* p, size_t) { backing.dealloc(p); }
+  template <typename U> bool operator==(const PoolAllocator<U>& o) const { return backing.alloc == o.backing.alloc; }
+  template <typename U> bool operator!=(const PoolAllocator<U>& o) const { return !(*this == o); }
+};
+} // namespace memory
+template <typename T>
+using Buffer = std::vector<T, memory::PoolAllocator<T>>;
+
 // ---- null bitmaps ----------------------------------------------------------------------------------
 using Nulls = std::vector<uint64_t>; // empty = no nulls; bit i = 1 -> row i is NOT null
 namespace bits {
@@ -128,13 +154,13 @@ template <typename T>
 class FlatVector : public BaseVector {
  public:
   FlatVector(TypePtr type, size_t size) : BaseVector(std::move(type), VectorEncoding::FLAT, size), values_(size) {}
-  FlatVector(TypePtr type, std::vector<T> values) : BaseVector(std::move(type), VectorEncoding::FLAT, values.size()), values_(std::move(values)) {}
+  FlatVector(TypePtr type, const std::vector<T>& values) : BaseVector(std::move(type), VectorEncoding::FLAT, values.size()), values_(values.begin(), values.end()) {}
   const T* rawValues() const { return values_.data(); }
   T* mutableRawValues() { return values_.data(); }
   const T& valueAt(size_t i) const { return values_[i]; }
   void set(size_t i, T v) { values_[i] = std::move(v); }
  private:
-  std::vector<T> values_;
+  Buffer<T> values_;
 };
 
 // BOOLEAN flat vectors are bit-packed like the reference's FlatVector<bool>.
@@ -152,14 +178,14 @@ class BoolVector : public BaseVector {
 // wrapInfo = int32 indices into `base`; optional extra nulls on this layer (per OUTER row).
 class DictionaryVector : public BaseVector {
  public:
-  DictionaryVector(std::vector<int32_t> indices, VectorPtr base, Nulls extraNulls = {})
-      : BaseVector(base->type(), VectorEncoding::DICTIONARY, indices.size()), indices_(std::move(indices)), base_(std::move(base)) {
+  DictionaryVector(const std::vector<int32_t>& indices, VectorPtr base, Nulls extraNulls = {})
+      : BaseVector(base->type(), VectorEncoding::DICTIONARY, indices.size()), indices_(indices.begin(), indices.end()), base_(std::move(base)) {
     nulls_ = std::move(extraNulls);
   }
   const int32_t* rawIndices() const { return indices_.data(); }
   const VectorPtr& valueVector() const { return base_; }
  private:
-  std::vector<int32_t> indices_;
+  Buffer<int32_t> indices_;
   VectorPtr base_;
 };
 
