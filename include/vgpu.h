@@ -327,6 +327,11 @@ int vgpu_agg_finalize(vgpu_agg_t agg, void* stream);
  * errors, as exceptions thrown out of HashAggregation::addInput do (velox/exec/Driver.cpp:536-586). */
 int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream);
 
+/* Device bytes the aggregation's group state holds right now (a host-side upper bound: no synchronisation) — what a
+ * partial HashAggregation compares with max_partial_aggregation_memory before it flushes
+ * (velox/exec/HashAggregation.cpp:326-348). */
+int vgpu_agg_memory_bytes(vgpu_agg_t agg, int64_t* bytes);
+
 /* Number of groups so far (synchronises the stream). */
 int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* num_groups);
 
@@ -354,6 +359,14 @@ int vgpu_agg_partition(vgpu_agg_t agg, int32_t n_parts, void* rows_out, int64_t*
                        void* stream);
 
 /* ---- multi-GPU exchange (one process per GPU) ------------------------------------------- */
+
+/* Partition (destination rank) of a group between the partial and the final aggregation: hash % n_parts
+ * (velox/exec/HashPartitionFunction.cpp:59-92).  raw_bigint_key != 0 — the grouping key is ONE BIGINT column (bits = 64):
+ * the hash is VectorHasher::hash's, folly::hasher<int64_t> = twang_mix64 per value and kNullHash = 1 for NULL
+ * (velox/exec/VectorHasher.cpp:68-108, velox/vector/BaseVector.h:74), so a GPU partial stage routes every group where a
+ * CPU Velox PartitionedOutput would.  Otherwise `key` is a packed normalized key / dense group number, which the
+ * reference never hashes as such; a fixed splitmix64 is used.  Host function, no device needed. */
+int vgpu_partition_of(int64_t key, int32_t is_null, int32_t n_parts, int32_t raw_bigint_key, int32_t* part);
 
 #define VGPU_COMM_ID_BYTES 128
 typedef struct vgpu_comm_s* vgpu_comm_t;

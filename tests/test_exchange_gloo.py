@@ -120,3 +120,41 @@ def test_plan_alltoall_offsets():
     sc, so, rc, ro = engine.plan_alltoall([3, 0, 5], [1, 2, 0], 56)
     assert sc == [168, 0, 280] and so == [0, 168, 168]
     assert rc == [56, 112, 0] and ro == [0, 56, 168]
+
+
+def test_partition_of_matches_the_reference_hash():
+    """One raw BIGINT key: partition = folly::hasher<int64_t>(key) % n = twang_mix64(key) % n, NULL -> kNullHash = 1
+    (velox/exec/HashPartitionFunction.cpp:59-92, velox/exec/VectorHasher.cpp:68-108, velox/vector/BaseVector.h:74;
+    twang_mix64 as restated in the reference tree at velox/experimental/gpu/tests/HashTableTest.cu:51-60)."""
+    import ctypes as C
+    import importlib
+    import numpy as np
+    abi = importlib.import_module("velox-1_b200").abi
+    M = (1 << 64) - 1
+
+    def twang(k):
+        k &= M
+        k = ((~k) + (k << 21)) & M
+        k ^= k >> 24
+        k = (k + (k << 3) + (k << 8)) & M
+        k ^= k >> 14
+        k = (k + (k << 2) + (k << 4)) & M
+        k ^= k >> 28
+        k = (k + (k << 31)) & M
+        return k
+
+    rng = np.random.default_rng(3)
+    keys = [0, 1, -1, 2**63 - 1, -2**63, 6_000_000] + [int(x) for x in rng.integers(-2**62, 2**62, 200)]
+    out = C.c_int32()
+    for n in (1, 2, 3, 8, 31):
+        for k in keys:
+            abi.check(abi.lib().vgpu_partition_of(k, 0, n, 1, C.byref(out)))
+            assert out.value == twang(k) % n, (k, n)
+        abi.check(abi.lib().vgpu_partition_of(12345, 1, n, 1, C.byref(out)))
+        assert out.value == 1 % n
+    # the packed-key function is deterministic and spreads
+    seen = set()
+    for k in range(1000):
+        abi.check(abi.lib().vgpu_partition_of(k, 0, 8, 0, C.byref(out)))
+        seen.add(out.value)
+    assert seen == set(range(8))

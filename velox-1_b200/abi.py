@@ -129,11 +129,13 @@ PROTOTYPES = {
     "vgpu_agg_add_input": [_P, _P, C.POINTER(Column), _I32, _I64, _P, _I64, _P],
     "vgpu_agg_finalize": [_P, _P],
     "vgpu_agg_check_errors": [_P, _P],
+    "vgpu_agg_memory_bytes": [_P, C.POINTER(_I64)],
     "vgpu_agg_num_groups": [_P, _P, C.POINTER(_I64)],
     "vgpu_agg_row_bytes": [_P, C.POINTER(_I32)],
     "vgpu_agg_extract": [_P, _I64, _I64, _P, C.POINTER(_I64), _P],
     "vgpu_agg_merge_rows": [_P, _P, _I64, _P],
     "vgpu_agg_partition": [_P, _I32, _P, C.POINTER(_I64), _P],
+    "vgpu_partition_of": [_I64, _I32, _I32, _I32, C.POINTER(_I32)],
     "vgpu_comm_unique_id": [C.POINTER(C.c_uint8)],
     "vgpu_comm_create": [C.POINTER(C.c_uint8), _I32, _I32, C.POINTER(_P)],
     "vgpu_comm_destroy": [_P],

@@ -264,7 +264,7 @@ __device__ __forceinline__ void merge_packed(const uint64_t* row, const RowMap& 
 
 struct DoneMap { uint8_t d[2 * kMaxOutputs]; }; // 1 = an earlier accumulator already covers the cell
 
-__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts);
+__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts, bool velox_hash);
 // n_parts > 0: rows of every rank's dense state arrive here (fixed-size all-gather); a rank folds the
 // groups it owns (part_of == my_part) and skips groups that saw no row.
 __global__ void merge_rows_array_kernel(const uint64_t* rows, int64_t n, RowMap rm, DoneMap dm,
@@ -272,7 +272,7 @@ __global__ void merge_rows_array_kernel(const uint64_t* rows, int64_t n, RowMap 
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t* row = rows + i * rm.row_words_out;
-  if (n_parts > 0 && (row[2] == 0 || part_of(row, n_parts) != my_part)) return;
+  if (n_parts > 0 && (row[2] == 0 || part_of(row, n_parts, false) != my_part)) return;
   uint32_t err = 0;
   if (row[0] >= (uint64_t)G) { atomicOr(err_word, kErrKeyRange); return; }
   merge_packed(row, rm, state + row[0], (size_t)G, false, dm.d, err);
@@ -340,21 +340,21 @@ __global__ void drain_overflow_kernel(const uint64_t* ovf, const unsigned long l
 }
 
 // ---- partitioning packed rows ----------------------------------------------------------------
-__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts) {
-  return (int)(mix64(row[0] ^ (row[1] << 63)) % (uint64_t)n_parts);
+__device__ __forceinline__ int part_of(const uint64_t* row, int n_parts, bool velox_hash) {
+  return (int)partition_of(row[0], row[1] & 1ull, (uint32_t)n_parts, velox_hash);
 }
 __global__ void partition_count_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
-                                       unsigned long long* counts) {
+                                       unsigned long long* counts, bool velox_hash) {
   __shared__ unsigned int hist[32];
   if (threadIdx.x < 32) hist[threadIdx.x] = 0;
   __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) atomicAdd(&hist[part_of(rows + i * row_words, n_parts)], 1u);
+  if (i < n) atomicAdd(&hist[part_of(rows + i * row_words, n_parts, velox_hash)], 1u);
   __syncthreads();
   if (threadIdx.x < n_parts && hist[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)hist[threadIdx.x]);
 }
 __global__ void partition_scatter_kernel(const uint64_t* rows, int64_t n, int row_words, int n_parts,
-                                         unsigned long long* cursors, uint64_t* out) {
+                                         unsigned long long* cursors, uint64_t* out, bool velox_hash) {
   // positions inside the block from a shared-memory histogram; one global atomic per part and block
   __shared__ unsigned int hist[32];
   __shared__ unsigned long long base[32];
@@ -364,7 +364,7 @@ __global__ void partition_scatter_kernel(const uint64_t* rows, int64_t n, int ro
   const uint64_t* row = rows + i * row_words;
   int part = 0;
   unsigned int local = 0;
-  if (i < n) { part = part_of(row, n_parts); local = atomicAdd(&hist[part], 1u); }
+  if (i < n) { part = part_of(row, n_parts, velox_hash); local = atomicAdd(&hist[part], 1u); }
   __syncthreads();
   if (threadIdx.x < n_parts && hist[threadIdx.x]) base[threadIdx.x] = atomicAdd(&cursors[threadIdx.x], (unsigned long long)hist[threadIdx.x]);
   __syncthreads();
@@ -474,6 +474,8 @@ int agg_resolve(Agg& a, const Program& prog, cudaStream_t stream) {
   a.resolved = true;
   return VGPU_OK;
 }
+
+bool agg_raw_bigint_key(const Agg& a) { return a.mode == VGPU_AGG_HASH && a.keys.size() == 1 && a.keys[0].bits == 64; }
 
 static uint64_t next_pow2(uint64_t x) { uint64_t p = 1024; while (p < x) p <<= 1; return p; }
 
@@ -982,7 +984,8 @@ int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cuda
   VG_CUDA(cudaMemsetAsync(counts, 0, 32 * sizeof(unsigned long long), stream));
   unsigned long long h[32] = {0};
   if (n > 0) {
-    partition_count_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts);
+    const bool velox_hash = agg_raw_bigint_key(a);
+    partition_count_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts, velox_hash);
     VG_CUDA(cudaGetLastError());
     count_launch();
     VG_CUDA(cudaMemcpyAsync(h, counts, n_parts * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
@@ -990,7 +993,7 @@ int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cuda
     unsigned long long cur[32], run = 0;
     for (int i = 0; i < n_parts; ++i) { cur[i] = run; run += h[i]; }
     VG_CUDA(cudaMemcpyAsync(counts, cur, n_parts * sizeof(unsigned long long), cudaMemcpyHostToDevice, stream));
-    partition_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts, (uint64_t*)rows_out);
+    partition_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a.packed, n, a.rm.row_words_out, n_parts, counts, (uint64_t*)rows_out, velox_hash);
     VG_CUDA(cudaGetLastError());
     count_launch();
     VG_CUDA(cudaStreamSynchronize(stream));

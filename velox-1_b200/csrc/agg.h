@@ -138,6 +138,7 @@ int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream);
 int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int my_part, cudaStream_t stream);
 int agg_reset(Agg& a, cudaStream_t stream);
 void agg_free(Agg& a);
+bool agg_raw_bigint_key(const Agg& a); // one raw BIGINT key: partitions are assigned with the reference's own hash
 int agg_finalize(Agg& a, cudaStream_t stream);   // LOG engine: deduplicate what the scans logged (asynchronous)
 
 // ---- hashagg.cu --------------------------------------------------------------------------------

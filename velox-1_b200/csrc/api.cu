@@ -445,6 +445,19 @@ int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream) {
   VG_CUDA(cudaMemsetAsync(agg->agg.err, 0, 4, (cudaStream_t)stream));
   return report_error_bits(bits);
 }
+int vgpu_agg_memory_bytes(vgpu_agg_t agg, int64_t* bytes) {
+  if (!agg || !bytes) return VGPU_ERR_INVALID;
+  const Agg& a = agg->agg;
+  int64_t b = 0;
+  if (a.mode == VGPU_AGG_HASH) {
+    b += (int64_t)(a.capacity ? (a.capacity + 2) * a.row_words * 8 : 0);          // TABLE engine
+    b += (int64_t)(a.log_bound * (uint64_t)a.ew * 8);                               // LOG engine: entries logged so far (upper bound)
+  } else {
+    b += (int64_t)a.n_cells * a.n_groups * 8;
+  }
+  *bytes = b;
+  return VGPU_OK;
+}
 int vgpu_agg_num_groups(vgpu_agg_t agg, void* stream, int64_t* n) {
   if (!agg || !n) return VGPU_ERR_INVALID;
   int rc = agg_extract_all(agg->agg, (cudaStream_t)stream);

@@ -26,6 +26,33 @@ __device__ __forceinline__ uint64_t mix64(uint64_t k) { // splitmix64 finaliser
 }
 constexpr uint64_t kEmptyKey = 0xffffffffffffffffull;
 
+// folly::hasher<int64_t> = folly::hash::twang_mix64 (Thomas Wang's 64-bit mix; folly is not vendored in the reference
+// tree, the same function is restated in velox/experimental/gpu/tests/HashTableTest.cu:51-60).
+__host__ __device__ __forceinline__ uint64_t twang_mix64(uint64_t key) {
+  key = (~key) + (key << 21);
+  key = key ^ (key >> 24);
+  key = key + (key << 3) + (key << 8);
+  key = key ^ (key >> 14);
+  key = key + (key << 2) + (key << 4);
+  key = key ^ (key >> 28);
+  key = key + (key << 31);
+  return key;
+}
+// Destination of a group between a partial and a final aggregation: hash % partitions
+// (velox/exec/HashPartitionFunction.cpp:59-92).  velox_hash: the key is one raw BIGINT column, hashed exactly as
+// VectorHasher::hash does (velox/exec/VectorHasher.cpp:68-108: folly::hasher<int64_t> per value, NULL -> kNullHash = 1,
+// velox/vector/BaseVector.h:74) so that a GPU partial stage assigns every group to the partition a CPU Velox stage
+// would.  Otherwise the key is a packed normalized key / a dense group number, which the reference never hashes as
+// such: any deterministic function does, and splitmix64 is used.
+__host__ __device__ __forceinline__ uint32_t partition_of(uint64_t key, uint64_t null_flag, uint32_t n_parts, bool velox_hash) {
+  if (velox_hash) return (uint32_t)((null_flag ? 1ull : twang_mix64(key)) % (uint64_t)n_parts);
+  uint64_t k = key ^ (null_flag << 63);
+  k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
+  k ^= k >> 27; k *= 0x94d049bb133111ebull;
+  k ^= k >> 31;
+  return (uint32_t)(k % (uint64_t)n_parts);
+}
+
 // Warp-aggregated atomics.  Millions of threads bumping ONE counter serialise in the L2 atomic unit
 // (15 M increments ~ 7 ms on B200); the lanes that reach the call together elect a leader that adds
 // their count once.  Each lane is in exactly one such group, so the total is exact.

@@ -92,13 +92,6 @@ struct vgpu_comm_s {
 
 namespace vg {
 
-static uint64_t splitmix_host(uint64_t k) { // = device mix64
-  k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
-  k ^= k >> 27; k *= 0x94d049bb133111ebull;
-  k ^= k >> 31;
-  return k;
-}
-
 static int comm_reserve(void** p, size_t* cap, size_t want) {
   if (*cap >= want) return VGPU_OK;
   if (*p) { VG_CUDA(cudaDeviceSynchronize()); VG_CUDA(cudaFree(*p)); *p = nullptr; *cap = 0; }
@@ -109,10 +102,11 @@ static int comm_reserve(void** p, size_t* cap, size_t want) {
 }
 
 // ---- destination of a group ------------------------------------------------------------------------------------
-// part = mix64(normalized key ^ (null flag << 63)) % world, the same function as agg.cu's part_of (the stepwise
-// NCCL path and the fused path must give every group the same owner).
-__device__ __forceinline__ uint32_t dest_of(uint64_t key, uint64_t null_flag, uint32_t world) {
-  return (uint32_t)(mix64(key ^ (null_flag << 63)) % (uint64_t)world);
+// partition_of (device_common.cuh): the same function as agg.cu's part_of, so the stepwise NCCL path and the fused
+// path give every group the same owner — and, for one raw BIGINT key, the owner the reference's HashPartitionFunction
+// would pick.
+__device__ __forceinline__ uint32_t dest_of(uint64_t key, uint64_t null_flag, uint32_t world, bool velox_hash) {
+  return partition_of(key, null_flag, world, velox_hash);
 }
 
 // ---- HASH: partition + peer store ---------------------------------------------------------------------------------
@@ -122,6 +116,7 @@ struct SendArgs {
   int n_ranges, ew;
   uint32_t chunk;                 // entries per chunk (= what the shared-memory stage holds)
   uint32_t world, rank;
+  int velox_hash;                 // one raw BIGINT key: HashPartitionFunction's own hash
   uint64_t* peer_region[kMaxWorld]; // destination d: first entry of the region this rank owns in d's window
   uint64_t region_cap;            // entries
   unsigned long long* cursor;     // [world]: entries stored per destination so far: low 32 bits front, high 32 bits back
@@ -155,7 +150,7 @@ __global__ void __launch_bounds__(kSendThreads) xchg_send_kernel(SendArgs a) {
 #pragma unroll
     for (int k = 0; k < kSendPerThread; ++k) {
       const uint32_t i = k * kSendThreads + threadIdx.x;
-      dst[k] = i < n ? dest_of(first[(uint64_t)i * ew], 0ull, a.world) : 0xffffffffu;
+      dst[k] = i < n ? dest_of(first[(uint64_t)i * ew], 0ull, a.world, a.velox_hash != 0) : 0xffffffffu;
       const uint32_t m = __match_any_sync(0xffffffffu, dst[k]);
       const int leader = __ffs(m) - 1;
       uint32_t b = 0;
@@ -220,11 +215,12 @@ struct SpecialArgs {
   uint64_t* peer_slot[kMaxWorld];
   uint32_t world;
   int ew;
+  int velox_hash;
 };
 __global__ void xchg_send_special_kernel(SpecialArgs a) {
   const uint32_t d = blockIdx.x;
   if (d >= a.world) return;
-  const uint32_t owner[2] = {dest_of(0ull, 1ull, a.world), dest_of(kEmptyKey, 0ull, a.world)};
+  const uint32_t owner[2] = {dest_of(0ull, 1ull, a.world, a.velox_hash != 0), dest_of(kEmptyKey, 0ull, a.world, a.velox_hash != 0)};
   for (int i = threadIdx.x; i < 2 * a.ew; i += blockDim.x) {
     const int r = i / a.ew, w = i % a.ew;
     uint64_t v = a.special[i];
@@ -311,7 +307,7 @@ __global__ void xchg_dense_kernel(DenseArgs a) {
   __threadfence_system();
   // 3. fold the groups this rank owns, sources in rank order (deterministic)
   for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
-    if (dest_of((uint64_t)g, 0ull, a.world) != a.rank) continue;
+    if (dest_of((uint64_t)g, 0ull, a.world, false) != a.rank) continue;
     uint32_t err = 0;
     for (int c = 0; c < a.n_cells; ++c) {
       uint64_t acc = a.final_state[(size_t)c * a.G + g];
@@ -330,6 +326,12 @@ __global__ void xchg_dense_kernel(DenseArgs a) {
 } // namespace vg
 
 extern "C" {
+
+int vgpu_partition_of(int64_t key, int32_t is_null, int32_t n_parts, int32_t raw_bigint_key, int32_t* part) {
+  if (!part || n_parts < 1) return VGPU_ERR_INVALID;
+  *part = (int32_t)partition_of((uint64_t)key, is_null ? 1ull : 0ull, (uint32_t)n_parts, raw_bigint_key != 0);
+  return VGPU_OK;
+}
 
 int vgpu_comm_unique_id(uint8_t id[VGPU_COMM_ID_BYTES]) {
   int rc = load_nccl();
@@ -501,6 +503,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   while (chunk > kSendThreads && (size_t)chunk * ew * 8 > 64 * 1024) chunk -= kSendThreads;
   s.chunk = chunk;
   s.world = (uint32_t)W; s.rank = (uint32_t)comm->rank;
+  s.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
   for (int d = 0; d < W; ++d) s.peer_region[d] = (uint64_t*)(region_of(comm, d, half, comm->rank) + special_bytes);
   s.region_cap = region_cap_entries(comm, ew);
   s.cursor = (unsigned long long*)comm->dcounts;
@@ -517,7 +520,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   VG_CUDA(cudaFuncSetAttribute(xchg_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   xchg_send_kernel<<<num_sms() * 4, kSendThreads, smem, stream>>>(s);
   SpecialArgs sp{};
-  sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew;
+  sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew; sp.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
   for (int d = 0; d < W; ++d) sp.peer_slot[d] = (uint64_t*)region_of(comm, d, half, comm->rank);
   xchg_send_special_kernel<<<W, 64, 0, stream>>>(sp);
   xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)comm->dcounts, (uint32_t)W, pa.ctr, pa.log_probed && pa.ext_ranges.empty() ? 1 : 0,
@@ -621,7 +624,7 @@ int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg
   if (pa.mode != VGPU_AGG_HASH) {
     if (pa.n_groups != fa.n_groups || pa.n_cells != fa.n_cells) { set_error("partial and final aggregations differ in their key domains"); return VGPU_ERR_INVALID; }
     // a global aggregation's single row (present even without input) is reported by the rank that owns group 0 only
-    if (pa.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)(splitmix_host(0) % (uint64_t)comm->world) == comm->rank;
+    if (pa.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)partition_of(0, 0, (uint32_t)comm->world, false) == comm->rank;
     if (comm->win && !no_p2p && dense_fits(comm, pa)) return exchange_dense_p2p(comm, pa, fa, stream, bytes_sent);
     return exchange_nccl(comm, pa, fa, stream, bytes_sent);
   }
@@ -664,7 +667,7 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
     }
     for (int r = 0; r < world; ++r) {
       Agg& fa = finals[r]->agg;
-      if (partials[r]->agg.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)(splitmix_host(0) % (uint64_t)world) == r;
+      if (partials[r]->agg.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)partition_of(0, 0, (uint32_t)world, false) == r;
       int rc2 = hash ? log_p2p_receive(&comms[r], partials[r]->agg, fa, stream) : dense_p2p(&comms[r], partials[r]->agg, fa, stream, 2, true);
       if (rc2) return rc2;
       // the final aggregation must not keep pointers into the temporary windows: materialise its groups now

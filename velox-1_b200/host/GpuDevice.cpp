@@ -89,14 +89,27 @@ void Staging::copyIn(void* dst, const void* host, size_t bytes, const std::share
     s.keep.push_back(owner);
     check(vgpu_h2d_async(dst, host, bytes, copy_), "vgpu_h2d_async");
   } else {
-    const size_t at = (s.pinUsed + 63) & ~(size_t)63;
+    // the pinned area mirrors the device arena offset for offset: stage at the destination's own mirror
+    const size_t at = (size_t)((char*)dst - s.dev);
     VB_CHECK(at + bytes <= s.cap, "staging slot overflow (pinned area)");
     std::memcpy(s.pin + at, host, bytes);
-    s.pinUsed = at + bytes;
     check(vgpu_h2d_async(dst, s.pin + at, bytes, copy_), "vgpu_h2d_async");
     stagedBytes += (int64_t)bytes;
   }
   h2dBytes += (int64_t)bytes;
+}
+
+void* Staging::mirror(void* dev) {
+  Slot& s = slots_[cur_];
+  return s.pin + ((char*)dev - s.dev);
+}
+
+void Staging::copyMirror(void* dev, size_t bytes) {
+  if (!bytes) return;
+  Slot& s = slots_[cur_];
+  check(vgpu_h2d_async(dev, s.pin + ((char*)dev - s.dev), bytes, copy_), "vgpu_h2d_async");
+  h2dBytes += (int64_t)bytes;
+  stagedBytes += (int64_t)bytes;
 }
 
 void* Staging::scratch(size_t bytes, bool zero) {

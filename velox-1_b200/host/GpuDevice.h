@@ -42,6 +42,12 @@ class Staging {
     return d;
   }
   void* scratch(size_t bytes, bool zero);
+  // The pinned host address that mirrors device address `dev` of the current slot (same offset in the slot's pinned
+  // area), and the copy of `bytes` from there to `dev`: callers gather many small batches on the host, then move
+  // them with one DMA.  Mirror space and the staged copies of copyIn share the pinned area: copyIn stages behind
+  // everything reserved so far.
+  void* mirror(void* dev);
+  void copyMirror(void* dev, size_t bytes);
   // All copies of the slot are issued: the compute stream will wait for them.
   void ready();
   // The kernels reading the slot are launched: the slot may be reused once they finish.

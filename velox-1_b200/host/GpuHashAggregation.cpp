@@ -70,6 +70,8 @@ struct GpuHashAggregation::Impl {
     int type = 0;            // vgpu_type on the device
     size_t width = 0;        // bytes per value
     char* dValues = nullptr; // device array of capacity pendingCap values
+    char* hValues = nullptr; // pinned mirror of dValues: small batches are gathered here and copied once per flush
+    int64_t hostFrom = -1;   // first gathered row that still lives only in hValues (-1: none)
     bool anyNulls = false;
     std::vector<uint64_t> notNull; // host bitmap of the gathered rows (uploaded at launch when anyNulls)
   };
@@ -96,6 +98,14 @@ struct GpuHashAggregation::Impl {
       return std::make_shared<FieldAccessTypedExpr>(row->childAt(row->getChildIdx(name.substr(dot + 1))), name);
     }
     return std::make_shared<FieldAccessTypedExpr>(inputType->childAt(inputType->getChildIdx(name)), name);
+  }
+  // type of an INPUT column of the operator (what lowered.columns names; "col.field" = a child of a ROW-typed column)
+  TypePtr inputColumnType(const std::string& name) const {
+    const size_t dot = name.find('.');
+    if (dot == std::string::npos) return inputType->childAt(inputType->getChildIdx(name));
+    auto row = std::dynamic_pointer_cast<const RowType>(inputType->childAt(inputType->getChildIdx(name.substr(0, dot))));
+    VB_CHECK(row != nullptr, "not a ROW column: " + name);
+    return row->childAt(row->getChildIdx(name.substr(dot + 1)));
   }
   int addOutput(const TypedExprPtr& e) {
     for (size_t i = keys.size(); i < outputs.size(); ++i) if (outputs[i]->toString() == e->toString() && outputs[i]->type()->equals(*e->type())) return (int)i;
@@ -229,7 +239,7 @@ struct GpuHashAggregation::Impl {
 
   void addEmpty() {
     std::vector<vgpu_column> cols(std::max<size_t>(1, lowered.columns.size()));
-    for (size_t i = 0; i < lowered.columns.size(); ++i) cols[i].type = deviceType(exprOf(lowered.columns[i])->type());
+    for (size_t i = 0; i < lowered.columns.size(); ++i) cols[i].type = deviceType(inputColumnType(lowered.columns[i]));
     check(vgpu_agg_add_input(agg, program, cols.data(), (int32_t)lowered.columns.size(), 0, nullptr, 0, stream), "vgpu_agg_add_input");
   }
 
@@ -252,7 +262,12 @@ struct GpuHashAggregation::Impl {
 
   // VARCHAR key column -> ids of its base strings (new strings get the next id)
   std::vector<int32_t> idsOf(KeyInfo& k, const VectorPtr& v) {
-    Decoded d = decode(v);
+    // the flat vector of strings at the bottom of the wrappers (no per-row work for a dictionary: one lookup per base string)
+    const BaseVector* base = v.get();
+    while (base->encoding() == VectorEncoding::DICTIONARY) base = static_cast<const DictionaryVector*>(base)->valueVector().get();
+    if (base->encoding() == VectorEncoding::CONSTANT) base = static_cast<const ConstantVector*>(base)->valueVector().get();
+    VB_CHECK(base->encoding() == VectorEncoding::FLAT, "VARCHAR key over an unsupported encoding");
+    struct { const BaseVector* base; } d{base};
     auto strs = static_cast<const FlatVector<std::string>*>(d.base);
     std::vector<int32_t> ids(d.base->size());
     for (size_t i = 0; i < ids.size(); ++i) {
@@ -312,7 +327,7 @@ struct GpuHashAggregation::Impl {
   size_t pendingBytes(int64_t cap) const {
     size_t bytes = 0;
     for (auto& name : lowered.columns) {
-      const int t = deviceType(exprOf(name)->type());
+      const int t = deviceType(inputColumnType(name));
       bytes += (size_t)cap * std::max<size_t>(deviceWidth(t), 4) + bits::nwords((size_t)cap) * 8 + 1024;
     }
     return bytes + (1 << 16);
@@ -324,11 +339,18 @@ struct GpuHashAggregation::Impl {
     pending.assign(lowered.columns.size(), PendingColumn{});
     for (size_t c = 0; c < lowered.columns.size(); ++c) {
       auto& pc = pending[c];
-      pc.type = deviceType(exprOf(lowered.columns[c])->type());
+      pc.type = deviceType(inputColumnType(lowered.columns[c]));
       pc.width = deviceWidth(pc.type);
       pc.dValues = (char*)staging->reserve((size_t)pendingCap * pc.width);
+      pc.hValues = (char*)staging->mirror(pc.dValues);
     }
     pendingRows = 0;
+  }
+  // rows [pc.hostFrom, pendingRows) of a column wait in the pinned mirror: one DMA moves them
+  void pushMirror(PendingColumn& pc) {
+    if (pc.hostFrom < 0) return;
+    staging->copyMirror(pc.dValues + (size_t)pc.hostFrom * pc.width, (size_t)(pendingRows - pc.hostFrom) * pc.width);
+    pc.hostFrom = -1;
   }
   // FLAT numeric columns and VARCHAR keys (flat or one dictionary over flat strings) can be gathered
   bool canCoalesce(const RowVectorPtr& in, const std::vector<VectorPtr>& vecs) const {
@@ -355,23 +377,36 @@ struct GpuHashAggregation::Impl {
     if (pendingCap > 0 && pendingRows + (int64_t)n > pendingCap) flushPending();
     if (pendingCap == 0) openPending((int64_t)n);
     std::shared_ptr<const void> owner = in; // keeps pinned vector memory alive while the DMA is in flight
+    // Small batches (Velox's default scan batch is ~4 k rows) cost more in CUDA calls than in bytes: they are gathered
+    // on the HOST into the pinned mirror of the device arrays — no CUDA call per batch — and one DMA per column moves
+    // them at flush time.  Large batches are copied straight out of their vectors (page-locked) or through the ring.
+    const bool small = n < 32768;
     for (size_t c = 0; c < vecs.size(); ++c) {
       auto& pc = pending[c];
       const auto& v = vecs[c];
       char* dst = pc.dValues + (size_t)pendingRows * pc.width;
+      char* hdst = pc.hValues + (size_t)pendingRows * pc.width;
+      if (!small) pushMirror(pc); // keep the column's rows in order: earlier small batches go first
+      else if (pc.hostFrom < 0) pc.hostFrom = pendingRows;
       const uint64_t* rowNulls = nullptr;
       std::vector<uint64_t> merged;
       if (varcharKeyOf[c] >= 0) {
         const auto& ids = keyIds[varcharKeyOf[c]]; // id per BASE string of this batch
         if (v->encoding() == VectorEncoding::FLAT) { // one id per row already
-          staging->copyIn(dst, ids.data(), n * 4);
+          if (small) memcpy(hdst, ids.data(), n * 4); else staging->copyIn(dst, ids.data(), n * 4);
           if (v->mayHaveNulls()) rowNulls = v->nulls().data();
         } else {
           auto dict = static_cast<const DictionaryVector*>(v.get());
           const BaseVector* base = dict->valueVector().get();
-          void* dIdx = staging->upload(dict->rawIndices(), n * 4, owner);
-          void* dTab = staging->upload(ids.data(), ids.size() * 4);
-          check(vgpu_translate_i32((int32_t*)dst, (const int32_t*)dIdx, (const int32_t*)dTab, (int32_t)ids.size(), (int64_t)n, staging->copyStream()), "vgpu_translate_i32");
+          if (small) {
+            int32_t* out = (int32_t*)hdst;
+            const int32_t* ix = dict->rawIndices();
+            for (size_t i = 0; i < n; ++i) out[i] = ids[(size_t)ix[i]];
+          } else {
+            void* dIdx = staging->upload(dict->rawIndices(), n * 4, owner);
+            void* dTab = staging->upload(ids.data(), ids.size() * 4);
+            check(vgpu_translate_i32((int32_t*)dst, (const int32_t*)dIdx, (const int32_t*)dTab, (int32_t)ids.size(), (int64_t)n, staging->copyStream()), "vgpu_translate_i32");
+          }
           if (v->mayHaveNulls() || base->mayHaveNulls()) { // NULL when the wrapper or the base string is NULL
             merged.assign(bits::nwords(n), 0);
             for (size_t i = 0; i < n; ++i) {
@@ -383,7 +418,7 @@ struct GpuHashAggregation::Impl {
           }
         }
       } else {
-        staging->copyIn(dst, rawValuesOf(v.get()), n * pc.width, owner);
+        if (small) memcpy(hdst, rawValuesOf(v.get()), n * pc.width); else staging->copyIn(dst, rawValuesOf(v.get()), n * pc.width, owner);
         if (v->mayHaveNulls()) rowNulls = v->nulls().data();
       }
       if (rowNulls && !pc.anyNulls) { pc.anyNulls = true; pc.notNull.assign(bits::nwords((size_t)pendingRows), ~0ull); }
@@ -399,6 +434,7 @@ struct GpuHashAggregation::Impl {
       batch.stream = stream;
       batch.staging = staging.get();
       for (auto& pc : pending) {
+        pushMirror(pc);
         vgpu_column c{};
         c.type = pc.type;
         c.encoding = VGPU_FLAT;
@@ -508,7 +544,25 @@ void GpuHashAggregation::close() {
 
 void GpuHashAggregation::addInput(RowVectorPtr input) {
   VB_CHECK(!noMoreInput_, "addInput after noMoreInput");
-  impl_->addBatch(input);
+  VB_CHECK(!partialFull_, "addInput while the partial aggregation is flushing");
+  auto& m = *impl_;
+  m.addBatch(input);
+  // Partial aggregation flushes when its state passes max_partial_aggregation_memory (HashAggregation.cpp:326-348): the
+  // groups so far go downstream as partial results (the final aggregation merges duplicates) and the state starts over.
+  if (m.node->step() == Step::kPartial && !m.keys.empty() && m.agg) {
+    int64_t bytes = 0;
+    check(vgpu_agg_memory_bytes(m.agg, &bytes), "vgpu_agg_memory_bytes");
+    if (bytes > m.ctx->queryConfig.maxPartialAggregationMemory) {
+      m.flushPending();
+      m.checkErrors();
+      m.rows = m.extractAll();
+      m.nGroups = (int64_t)(m.rows.size() / m.rowWords());
+      m.cursor = 0;
+      partialFull_ = m.nGroups > 0;
+      if (!partialFull_) { check(vgpu_agg_reset(m.agg, m.stream), "vgpu_agg_reset"); m.nGroups = -1; }
+      ++m.stats.flushes;
+    }
+  }
 }
 
 void GpuHashAggregation::noMoreInput() {
@@ -533,7 +587,13 @@ double asDouble(int64_t bitsValue) { double d; memcpy(&d, &bitsValue, 8); return
 
 RowVectorPtr GpuHashAggregation::getOutput() {
   auto& m = *impl_;
-  if (!noMoreInput_ || finished_ || m.nGroups < 0) return nullptr;
+  if (partialFull_ && m.cursor >= m.nGroups) { // the flush is drained: start over
+    check(vgpu_agg_reset(m.agg, m.stream), "vgpu_agg_reset");
+    m.nGroups = -1; m.cursor = 0; m.rows.clear();
+    partialFull_ = false;
+    return nullptr;
+  }
+  if ((!noMoreInput_ && !partialFull_) || finished_ || m.nGroups < 0) return nullptr;
   const int64_t n = std::min<int64_t>(m.ctx->queryConfig.preferredOutputBatchRows, m.nGroups - m.cursor);
   const int rw = m.rowWords(), na = (int)m.accs.size();
   const int64_t* base = m.rows.data() + m.cursor * rw;
@@ -623,7 +683,9 @@ RowVectorPtr GpuHashAggregation::getOutput() {
     children.push_back(v);
   }
   m.cursor += n;
-  if (m.cursor >= m.nGroups) finished_ = true;
+  ++m.stats.outputVectors;
+  m.stats.outputRows += n;
+  if (m.cursor >= m.nGroups && !partialFull_) finished_ = true;
   return std::make_shared<RowVector>(outputType_, (size_t)n, std::move(children));
 }
 

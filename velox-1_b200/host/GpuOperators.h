@@ -61,7 +61,7 @@ class GpuHashAggregation : public exec::Operator {
   GpuHashAggregation(exec::DriverCtx* ctx, int32_t id, std::shared_ptr<const core::AggregationNode> node,
                      const FilterProjectExprs* fused = nullptr, RowTypePtr fusedInputType = nullptr);
   ~GpuHashAggregation() override;
-  bool needsInput() const override { return !noMoreInput_; }
+  bool needsInput() const override { return !noMoreInput_ && !partialFull_; }
   void addInput(RowVectorPtr input) override;
   void noMoreInput() override;
   RowVectorPtr getOutput() override;
@@ -81,6 +81,7 @@ class GpuHashAggregation : public exec::Operator {
  private:
   std::unique_ptr<Impl> impl_;
   bool finished_ = false;
+  bool partialFull_ = false; // a partial aggregation over its memory limit: getOutput drains the groups, then input resumes
 };
 
 // Registers the PlanNodeTranslator (FilterNode / ProjectNode / AggregationNode -> GPU operators) and the
