@@ -1,6 +1,7 @@
 // Host -> device staging ring and the pinned host allocator of the GPU operators (GpuDevice.h).
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "GpuDevice.h"
 
@@ -26,6 +27,32 @@ void usePinnedHostMemory(bool on) {
   memory::hostAllocator() = on ? memory::HostAllocator{memory::pinnedAlloc, memory::pinnedFree} : memory::HostAllocator{memory::mallocAlloc, memory::mallocFree};
 }
 
+// Device arenas and pinned areas outlive the operators: cudaMalloc + cudaMallocHost of a 60 MB slot cost ~25 ms, more
+// than a whole Q1 over 20 M rows.  Closed operators hand their slots back; the next operator (the next query, or the
+// next driver of this one) takes them from here.
+namespace {
+struct Arena { char* dev; char* pin; size_t cap; };
+std::mutex g_arenas_mu;
+std::vector<Arena> g_arenas;
+bool takeArena(size_t bytes, Arena& out) {
+  std::lock_guard<std::mutex> l(g_arenas_mu);
+  int best = -1;
+  for (size_t i = 0; i < g_arenas.size(); ++i) {
+    if (g_arenas[i].cap >= bytes && (best < 0 || g_arenas[i].cap < g_arenas[best].cap)) best = (int)i;
+  }
+  if (best < 0) return false;
+  out = g_arenas[best];
+  g_arenas.erase(g_arenas.begin() + best);
+  return true;
+}
+void giveArena(const Arena& a) {
+  std::lock_guard<std::mutex> l(g_arenas_mu);
+  if (g_arenas.size() < 64) { g_arenas.push_back(a); return; }
+  vgpu_free(a.dev);
+  vgpu_free_host(a.pin);
+}
+} // namespace
+
 Staging::Staging(void* computeStream) : compute_(computeStream) {
   check(vgpu_stream_create(&copy_), "vgpu_stream_create");
   for (auto& s : slots_) {
@@ -37,8 +64,7 @@ Staging::Staging(void* computeStream) : compute_(computeStream) {
 Staging::~Staging() {
   for (auto& s : slots_) {
     if (s.inFlight) vgpu_event_sync(s.freeEv);
-    if (s.dev) vgpu_free(s.dev);
-    if (s.pin) vgpu_free_host(s.pin);
+    if (s.dev) giveArena(Arena{s.dev, s.pin, s.cap});
     if (s.freeEv) vgpu_event_destroy(s.freeEv);
     if (s.readyEv) vgpu_event_destroy(s.readyEv);
   }
@@ -56,16 +82,21 @@ void Staging::begin(size_t bytes) {
   s.keep.clear();
   bytes = (bytes + 4095) & ~(size_t)4095;
   if (bytes > s.cap) {
-    if (s.dev) check(vgpu_free(s.dev), "vgpu_free");
-    if (s.pin) check(vgpu_free_host(s.pin), "vgpu_free_host");
+    if (s.dev) giveArena(Arena{s.dev, s.pin, s.cap});
     s.dev = s.pin = nullptr;
-    void* d = nullptr;
-    void* h = nullptr;
-    check(vgpu_alloc(bytes, &d), "vgpu_alloc");
-    check(vgpu_alloc_host(bytes, &h), "vgpu_alloc_host");
-    s.dev = (char*)d;
-    s.pin = (char*)h;
-    s.cap = bytes;
+    s.cap = 0;
+    Arena a;
+    if (takeArena(bytes, a)) {
+      s.dev = a.dev; s.pin = a.pin; s.cap = a.cap;
+    } else {
+      void* d = nullptr;
+      void* h = nullptr;
+      check(vgpu_alloc(bytes, &d), "vgpu_alloc");
+      check(vgpu_alloc_host(bytes, &h), "vgpu_alloc_host");
+      s.dev = (char*)d;
+      s.pin = (char*)h;
+      s.cap = bytes;
+    }
   }
   s.used = s.pinUsed = 0;
   active_ = true;
