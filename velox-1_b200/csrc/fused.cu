@@ -695,7 +695,9 @@ struct Gen {
   }
 
   void generate() {
-    quad = p.mode == kSinkLog;
+    // (VGPU_QUAD_ARRAY=1: tuning aid — the 4-consecutive-rows layout for the ARRAY / GLOBAL sinks as well)
+    static const bool quad_array = getenv("VGPU_QUAD_ARRAY") && getenv("VGPU_QUAD_ARRAY")[0] == '1';
+    quad = p.mode == kSinkLog || (quad_array && p.mode == kSinkArray);
     for (const auto& op : prog.ops) { mark(op.a); mark(op.b); mark(op.c); }
     for (const auto& o : prog.outputs) mark(o);
     mark(prog.filter);
