@@ -261,7 +261,7 @@ typedef enum {
   VGPU_ACC_SUM_F64 = 0,  /* double += (double)x, nulls ignored                                  */
   VGPU_ACC_SUM_I64 = 1,  /* checked int64 += x (SumAggregateBase.h:150-158)                     */
   VGPU_ACC_COUNT = 2,    /* += 1 per passing row whose input is not null; input NONE = count(*) */
-  VGPU_ACC_MIN = 3,      /* typed by the input operand (integers or double)                     */
+  VGPU_ACC_MIN = 3,      /* typed by the input operand (integers, double, or BOOLEAN as 0 / 1: bool_and) */
   VGPU_ACC_MAX = 4
 } vgpu_acc_kind;
 

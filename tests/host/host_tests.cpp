@@ -129,6 +129,67 @@ struct CustomTranslator : exec::PlanNodeTranslator {
   }
 };
 
+// Stand-in for the reference's own exec::OrderBy (velox/exec/OrderBy.cpp), which stays a CPU operator in a deployment:
+// registered through the PlanNodeTranslator seam so that TpchQueryBuilder's "...finalAggregation().orderBy(keys, false)"
+// plans run unchanged.  Sorts the (tiny) aggregation result on the host.
+struct TestOrderBy : exec::Operator {
+  TestOrderBy(exec::DriverCtx* c, int32_t id, std::shared_ptr<const OrderByNode> n) : Operator(c, n->outputType(), id, n->id(), "OrderBy"), node(std::move(n)) {}
+  bool needsInput() const override { return !noMoreInput_; }
+  void addInput(RowVectorPtr in) override { inputs.push_back(std::move(in)); }
+  exec::BlockingReason isBlocked(exec::ContinueFuture*) override { return exec::BlockingReason::kNotBlocked; }
+  bool isFinished() override { return done; }
+  static std::string cell(const VectorPtr& v, size_t i) {
+    gpu::Decoded d = gpu::decode(v);
+    const size_t r = d.constant ? 0 : d.indices.empty() ? i : (size_t)d.indices[i];
+    char buf[64];
+    switch (d.base->type()->kind()) {
+      case TypeKind::VARCHAR: return static_cast<const FlatVector<std::string>*>(d.base)->valueAt(r);
+      case TypeKind::BIGINT: snprintf(buf, sizeof(buf), "%020lld", (long long)(static_cast<const FlatVector<int64_t>*>(d.base)->valueAt(r) + (1ll << 62))); return buf;
+      case TypeKind::INTEGER: snprintf(buf, sizeof(buf), "%020lld", (long long)static_cast<const FlatVector<int32_t>*>(d.base)->valueAt(r) + (1ll << 40)); return buf;
+      default: throw VeloxRuntimeError("TestOrderBy: key type");
+    }
+  }
+  RowVectorPtr getOutput() override {
+    if (!noMoreInput_ || done) return nullptr;
+    done = true;
+    std::vector<std::pair<size_t, size_t>> rows; // (batch, row)
+    for (size_t b = 0; b < inputs.size(); ++b) for (size_t r = 0; r < inputs[b]->size(); ++r) rows.push_back({b, r});
+    if (rows.empty()) return nullptr;
+    std::vector<int> keyIdx;
+    for (auto& k : node->sortingKeys()) keyIdx.push_back(outputType_->getChildIdx(k));
+    std::stable_sort(rows.begin(), rows.end(), [&](auto& x, auto& y) {
+      for (size_t k = 0; k < keyIdx.size(); ++k) {
+        const std::string a = cell(inputs[x.first]->childAt(keyIdx[k]), x.second), b = cell(inputs[y.first]->childAt(keyIdx[k]), y.second);
+        if (a != b) return node->sortingOrders()[k].ascending ? a < b : a > b;
+      }
+      return false;
+    });
+    // gather: one dictionary per input batch is overkill for a handful of rows; rebuild flat columns
+    std::vector<VectorPtr> children;
+    for (size_t c = 0; c < outputType_->size(); ++c) {
+      const auto& t = outputType_->childAt(c);
+      VectorPtr v;
+      auto nullAt = [&](size_t i) { auto& src = inputs[rows[i].first]->childAt(c); return src->mayHaveNulls() && !bits::isBitSet(src->nulls().data(), rows[i].second); };
+      if (t->kind() == TypeKind::VARCHAR) { auto f = std::make_shared<FlatVector<std::string>>(t, rows.size()); for (size_t i = 0; i < rows.size(); ++i) if (!nullAt(i)) f->set(i, at<std::string>(inputs[rows[i].first]->childAt(c), rows[i].second)); v = f; }
+      else if (t->kind() == TypeKind::DOUBLE) { auto f = std::make_shared<FlatVector<double>>(t, rows.size()); for (size_t i = 0; i < rows.size(); ++i) if (!nullAt(i)) f->set(i, at<double>(inputs[rows[i].first]->childAt(c), rows[i].second)); v = f; }
+      else if (t->kind() == TypeKind::BIGINT) { auto f = std::make_shared<FlatVector<int64_t>>(t, rows.size()); for (size_t i = 0; i < rows.size(); ++i) if (!nullAt(i)) f->set(i, at<int64_t>(inputs[rows[i].first]->childAt(c), rows[i].second)); v = f; }
+      else throw VeloxRuntimeError("TestOrderBy: column type " + t->toString());
+      for (size_t i = 0; i < rows.size(); ++i) if (nullAt(i)) v->setNull(i, true);
+      children.push_back(v);
+    }
+    return std::make_shared<RowVector>(outputType_, rows.size(), std::move(children));
+  }
+  std::shared_ptr<const OrderByNode> node;
+  std::vector<RowVectorPtr> inputs;
+  bool done = false;
+};
+struct OrderByTranslator : exec::PlanNodeTranslator {
+  std::unique_ptr<exec::Operator> toOperator(exec::DriverCtx* c, int32_t id, const PlanNodePtr& n) override {
+    if (auto o = std::dynamic_pointer_cast<const OrderByNode>(n)) return std::make_unique<TestOrderBy>(c, id, o);
+    return nullptr;
+  }
+};
+
 static void cpuTests() {
   auto t = makeLineitem(1000, 1);
   auto rv = lineitemVector(t, 0, 1000);
@@ -190,7 +251,13 @@ static void cpuTests() {
     EXPECT(lp.stringLiterals == (std::vector<std::string>{"R", "O", "N"}));              // 'R' shared: one id per distinct literal
     EXPECT(lp.stringColumns == (std::set<std::string>{"l_returnflag", "l_linestatus"}));
     EXPECT(lowerExpressions(parse::parseExpr("l_returnflag is null", row), {}).stringColumns.empty()); // null flags only
-    EXPECT_THROW(lowerExpressions(parse::parseExpr("l_returnflag < 'R'", row), {}), VeloxUserError);   // ids do not preserve order
+    // ordering and LIKE do not work on ids: they become BOOLEAN columns the operator evaluates per dictionary base value
+    auto sp = lowerExpressions(parse::parseExpr("l_returnflag < 'R' and l_linestatus like 'O%' and not (l_returnflag < 'R')", row), {});
+    EXPECT(sp.stringPredicates.size() == 2 && sp.stringPredicates[0].fn == "lt" && sp.stringPredicates[1].fn == "like" && sp.columns.size() == 2);
+    EXPECT(LoweredProgram::evalStringPredicate("like", "REG AIR", "R%") && LoweredProgram::evalStringPredicate("like", "RAIL", "_A_L") &&
+           !LoweredProgram::evalStringPredicate("like", "AIR", "R%") && LoweredProgram::evalStringPredicate("like", "TAKE BACK RETURN", "%BACK%RETURN") &&
+           !LoweredProgram::evalStringPredicate("like", "", "_") && LoweredProgram::evalStringPredicate("like", "", "%"));
+    EXPECT_THROW(lowerExpressions(parse::parseExpr("l_returnflag < l_linestatus", row), {}), VeloxUserError); // column vs column: not on the device
   }
 
   section("PlanBuilder: aggregation masks");
@@ -634,6 +701,102 @@ static void gpuTests() {
       if (!errors[d].empty()) printf("  driver %d: %s\n", d, errors[d].c_str());
     }
     EXPECT(ok);
+  }
+
+  section("Q1 exactly as TpchQueryBuilder writes it: ...finalAggregation().orderBy(keys) over 4 k-row batches (TpchQueryBuilder.cpp:189-244)");
+  {
+    exec::Operator::registerOperator(std::make_unique<OrderByTranslator>());
+    auto small = batches(t, 4096); // the reference's default scan batch: many host batches are gathered per device launch
+    auto plan = PlanBuilder().values(small).filter("l_shipdate <= '1998-09-02'::DATE")
+                    .project({"l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_extendedprice * (1.0 - l_discount) as disc_price",
+                              "l_extendedprice * (1.0 - l_discount) * (1.0 + l_tax) as charge", "l_discount"})
+                    .partialAggregation({"l_returnflag", "l_linestatus"}, {"sum(l_quantity)", "sum(l_extendedprice)", "sum(disc_price)", "sum(charge)",
+                                                                             "avg(l_quantity)", "avg(l_extendedprice)", "avg(l_discount)", "count(*)"})
+                    .finalAggregation().orderBy({"l_returnflag", "l_linestatus"}, false).planNode();
+    auto out = exec::runPlan(plan);
+    auto big = exec::runPlan(PlanBuilder().values(in).filter("l_shipdate <= '1998-09-02'::DATE")
+                                 .project({"l_returnflag", "l_linestatus", "l_quantity"})
+                                 .singleAggregation({"l_returnflag", "l_linestatus"}, {"sum(l_quantity)", "count(*)"}).planNode());
+    std::map<std::string, std::pair<double, int64_t>> wantBy;
+    for (auto& o : big) for (size_t g = 0; g < o->size(); ++g) wantBy[at<std::string>(o->childAt(0), g) + at<std::string>(o->childAt(1), g)] = {at<double>(o->childAt(2), g), at<int64_t>(o->childAt(3), g)};
+    bool ok = out.size() == 1 && out[0]->size() == 6;
+    std::string prev;
+    for (size_t g = 0; ok && g < out[0]->size(); ++g) {
+      const std::string k = at<std::string>(out[0]->childAt(0), g) + at<std::string>(out[0]->childAt(1), g);
+      ok = ok && (g == 0 || prev < k) && wantBy.count(k) && close(at<double>(out[0]->childAt(2), g), wantBy[k].first) && at<int64_t>(out[0]->childAt(9), g) == wantBy[k].second;
+      prev = k;
+    }
+    EXPECT(ok);
+  }
+
+  section("string predicates on the dictionary base: LIKE, VARCHAR < / >= (PeeledEncoding.cpp; DuckParser.cpp:53-110)");
+  {
+    // l_shipmode / l_shipinstruct as dictionary VARCHAR columns with NULLs
+    std::vector<RowVectorPtr> sb;
+    for (size_t at0 = 0; at0 < t.orderkey.size(); at0 += 50000) {
+      const size_t to = std::min(t.orderkey.size(), at0 + 50000);
+      std::vector<int32_t> m(t.mode.begin() + at0, t.mode.begin() + to), si(t.instruct.begin() + at0, t.instruct.begin() + to);
+      std::vector<double> ep(t.extendedprice.begin() + at0, t.extendedprice.begin() + to);
+      auto mode = stringDictionary(m, kModes, 7);
+      for (size_t i = 0; i < m.size(); i += 17) mode->setNull(i, true);
+      sb.push_back(makeRowVector({"l_shipmode", "l_shipinstruct", "l_extendedprice"}, {mode, stringDictionary(si, kInstruct, 4), makeFlatVector<double>(DOUBLE(), ep)}));
+    }
+    auto out = exec::runPlan(PlanBuilder().values(sb)
+                                 .filter("l_shipmode like 'R%' and l_shipinstruct >= 'DELIVER' and not (l_shipinstruct like '%RETURN')")
+                                 .project({"l_shipmode", "l_extendedprice"})
+                                 .singleAggregation({"l_shipmode"}, {"sum(l_extendedprice) as s", "count(*) as n"}).planNode());
+    std::map<std::string, std::pair<double, int64_t>> want;
+    for (size_t i = 0; i < t.orderkey.size(); ++i) {
+      if ((i % 50000) % 17 == 0) continue; // NULL shipmode: LIKE is NULL, the row is dropped
+      const std::string m = kModes[t.mode[i]], si = kInstruct[t.instruct[i]];
+      if (m[0] != 'R' || !(si >= "DELIVER") || (si.size() >= 6 && si.substr(si.size() - 6) == "RETURN")) continue;
+      want[m].first += t.extendedprice[i];
+      ++want[m].second;
+    }
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      auto it = want.find(at<std::string>(o->childAt(0), g));
+      ok = ok && it != want.end() && close(at<double>(o->childAt(1), g), it->second.first) && at<int64_t>(o->childAt(2), g) == it->second.second;
+    }
+    EXPECT(ok && groups == want.size() && groups == 2); // RAIL and REG AIR
+  }
+
+  section("bool_and / bool_or (BoolAggregates.cpp), partial -> final");
+  {
+    auto out = exec::runPlan(PlanBuilder().values(in).project({"l_linestatus", "l_discount > 0.0 as any_disc", "l_tax < 0.09 as low_tax", "l_quantity > 0.49 as big"})
+                                 .partialAggregation({"l_linestatus"}, {"bool_and(low_tax) as a", "bool_or(big) as o", "bool_and(any_disc) as a2"})
+                                 .finalAggregation().planNode());
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      const bool isF = at<std::string>(o->childAt(0), g) == "F";
+      bool wa = true, wo = false, wa2 = true;
+      for (size_t i = 0; i < t.orderkey.size(); ++i) if ((t.status[i] == 0) == isF) { wa = wa && t.tax[i] < 0.09; wo = wo || t.quantity[i] > 0.49; wa2 = wa2 && t.discount[i] > 0.0; }
+      auto b = [&](int c) { return static_cast<const BoolVector*>(o->childAt(c).get())->valueAt(g); };
+      ok = ok && b(1) == wa && b(2) == wo && b(3) == wa2;
+    }
+    EXPECT(ok && groups == 2);
+  }
+
+  section("partial aggregation flushes past max_partial_aggregation_memory and the final stage merges (HashAggregation.cpp:326-348)");
+  {
+    exec::QueryConfig cfg;
+    cfg.maxPartialAggregationMemory = 1 << 20; // 1 MB of logged groups: several flushes over 300 k rows
+    cfg.coalesceRows = 32768;
+    auto plan = PlanBuilder().values(batches(t, 8192)).partialAggregation({"l_orderkey"}, {"sum(l_extendedprice) as s", "count(*) as n"}).finalAggregation().planNode();
+    auto driver = exec::createDriver(plan, cfg);
+    auto* partial = dynamic_cast<gpu::GpuHashAggregation*>(driver->operators()[1].get());
+    auto out = driver->run();
+    std::map<int64_t, std::pair<double, int64_t>> want;
+    for (size_t i = 0; i < t.orderkey.size(); ++i) { want[t.orderkey[i]].first += t.extendedprice[i]; ++want[t.orderkey[i]].second; }
+    size_t groups = 0;
+    bool ok = partial != nullptr && partial->stats().flushes >= 2;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      auto it = want.find(at<int64_t>(o->childAt(0), g));
+      ok = ok && it != want.end() && close(at<double>(o->childAt(1), g), it->second.first) && at<int64_t>(o->childAt(2), g) == it->second.second;
+    }
+    EXPECT(ok && groups == want.size());
   }
 
   section("edge cases: empty input, all-null input, integer overflow (SumTest.cpp:509-538,610-620)");

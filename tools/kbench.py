@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--only", default="q1,q6,q6fp,orderkey,randkey,c4")
+    ap.add_argument("--engines", default="log,table", help="HASH engines to time for orderkey / randkey")
     args = ap.parse_args()
     pkg = importlib.import_module("velox-1_b200")
     abi = pkg.abi
@@ -124,7 +125,7 @@ def main():
             del perm
         for label, keycol in cases:
             cols = [engine.DeviceColumn(I64, abi.FLAT, keycol, length=n), flat("l_extendedprice")]
-            for eng in ("log", "table"):
+            for eng in args.engines.split(","):
                 os.environ["VGPU_HASH_ENGINE"] = eng
                 agg = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], accs, expected_groups=groups)
 

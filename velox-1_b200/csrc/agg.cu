@@ -416,7 +416,8 @@ int agg_resolve(Agg& a, const Program& prog, cudaStream_t stream) {
       default: set_error("bad accumulator kind %d", s.kind); return VGPU_ERR_INVALID;
     }
     if (s.kind != VGPU_ACC_COUNT && s.input < 0) { set_error("accumulator %zu needs an input", i); return VGPU_ERR_INVALID; }
-    if (s.kind != VGPU_ACC_COUNT && t == VGPU_BOOLEAN) { set_error("boolean aggregate inputs are not supported"); return VGPU_ERR_UNSUPPORTED; }
+    // BOOLEAN inputs: MIN / MAX over FALSE(0) < TRUE(1) are bool_and / bool_or; sums of booleans are not defined
+    if ((s.kind == VGPU_ACC_SUM_F64 || s.kind == VGPU_ACC_SUM_I64) && t == VGPU_BOOLEAN) { set_error("sum over a boolean input is not supported"); return VGPU_ERR_UNSUPPORTED; }
     const int vc = find_or_add_cell(a, (uint8_t)kind, s.input);
     int nc = -1;
     if (s.kind != VGPU_ACC_COUNT) nc = find_or_add_cell(a, kCellCount, s.input);

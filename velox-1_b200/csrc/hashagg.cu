@@ -31,7 +31,8 @@
 namespace vg {
 
 enum : uint32_t { kRangeFront = 0, kRangeBack = 1, kRangePlain = 2 };
-constexpr uint32_t kChunk = 4096; // entries one CTA takes from a range at a time (deduplication and expansion passes)
+constexpr uint32_t kChunk = 1024; // entries one CTA takes from a range at a time (deduplication and expansion passes):
+                                  // small, so that the few thousand edge entries of a sorted input spread over many CTAs
 
 __device__ __forceinline__ uint64_t range_count(const LogRange& r) {
   return r.count64 ? (uint64_t) * reinterpret_cast<const unsigned long long*>(r.count) : (uint64_t) * reinterpret_cast<const uint32_t*>(r.count);
@@ -140,6 +141,16 @@ __global__ void fin_prepare_kernel(FinArgs a) {
   chunk_prefix_scan(a.ranges, a.n_ranges, a.chunk_prefix, kChunk, [&](const LogRange& r) { return !(sorted && r.back == kRangeFront); });
 }
 
+// The chunk prefix array in shared memory when it fits (a binary search over global memory is ~10 dependent L2
+// round trips per chunk, which dominated the deduplication of a sorted input's few edge entries).
+constexpr int kPrefixSmem = 2048;
+__device__ __forceinline__ const uint32_t* stage_prefix(const uint32_t* chunk_prefix, int n_ranges, uint32_t* s_prefix) {
+  if (n_ranges + 1 > kPrefixSmem) return chunk_prefix;
+  for (int i = threadIdx.x; i <= n_ranges; i += blockDim.x) s_prefix[i] = chunk_prefix[i];
+  __syncthreads();
+  return s_prefix;
+}
+
 // Range and entry window of chunk `chunk` (every thread of the CTA computes the same answer).
 __device__ __forceinline__ void locate_chunk(const LogRange* ranges, const uint32_t* chunk_prefix, int n_ranges, uint32_t chunk, int ew,
                                              const uint64_t*& first, uint64_t& n) {
@@ -158,11 +169,13 @@ __device__ __forceinline__ void locate_chunk(const LogRange* ranges, const uint3
 // Walks every entry that needs deduplication: the CTAs share the chunks of all taking-part ranges.
 template <typename F>
 __device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn) {
-  const uint32_t total = a.chunk_prefix[a.n_ranges];
+  __shared__ uint32_t s_prefix[kPrefixSmem];
+  const uint32_t* prefix = stage_prefix(a.chunk_prefix, a.n_ranges, s_prefix);
+  const uint32_t total = prefix[a.n_ranges];
   for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
     const uint64_t* first;
     uint64_t n;
-    locate_chunk(a.ranges, a.chunk_prefix, a.n_ranges, chunk, a.ew, first, n);
+    locate_chunk(a.ranges, prefix, a.n_ranges, chunk, a.ew, first, n);
     for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) fn(first + i * a.ew);
   }
 }
@@ -355,12 +368,14 @@ __global__ void expand_prepare_kernel(ExpandArgs a) {
 
 __global__ void expand_rows_kernel(ExpandArgs a) {
   __shared__ unsigned long long s_base;
+  __shared__ uint32_t s_prefix[kPrefixSmem];
   const int ew = a.map.ew, rw = 3 + 2 * a.map.n_accs;
-  const uint32_t total = a.chunk_prefix[a.n_ranges];
+  const uint32_t* prefix = stage_prefix(a.chunk_prefix, a.n_ranges, s_prefix);
+  const uint32_t total = prefix[a.n_ranges];
   for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
     const uint64_t* first;
     uint64_t n;
-    locate_chunk(a.ranges, a.chunk_prefix, a.n_ranges, chunk, ew, first, n);
+    locate_chunk(a.ranges, prefix, a.n_ranges, chunk, ew, first, n);
     __syncthreads();
     if (threadIdx.x == 0) s_base = atomicAdd(a.out_cursor, (unsigned long long)n);
     __syncthreads();
@@ -561,9 +576,10 @@ int log_finalize(Agg& a, cudaStream_t stream) {
   FinArgs f{};
   f.ew = a.ew;
   f.kinds = log_cell_kinds(a);
-  // shared-memory table of a partition: as many slots as fit ~64 KB (three CTAs per SM), at least 256
-  int slots = 4096;
-  while (slots > 256 && (size_t)slots * a.ew * 8 > 64 * 1024) slots >>= 1;
+  // shared-memory table of a partition: 2048 slots or what fits 32 KB (seven CTAs per SM), at least 256; partitions
+  // average <= 256 entries (fin_prepare), so the tables stay far below half full
+  int slots = 2048;
+  while (slots > 256 && (size_t)slots * a.ew * 8 > 32 * 1024) slots >>= 1;
   f.slots_max = slots;
   // the arrays are sized for the upper bound of the entries; the device picks the partition count from the real count
   const uint64_t bound = a.log_bound + a.ext_bound;
@@ -612,7 +628,7 @@ int log_finalize(Agg& a, cudaStream_t stream) {
   fin_scatter_kernel<<<wide, 256, 0, stream>>>(f);
   const size_t smem = (size_t)slots * a.ew * 8;
   VG_CUDA(cudaFuncSetAttribute(fin_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  fin_aggregate_kernel<<<(unsigned)std::min<size_t>(P, (size_t)num_sms() * 6), 256, smem, stream>>>(f);
+  fin_aggregate_kernel<<<(unsigned)std::min<size_t>(P, (size_t)num_sms() * 7), 256, smem, stream>>>(f);
   VG_CUDA(cudaGetLastError());
   count_launch(5);
   a.finalized = true;

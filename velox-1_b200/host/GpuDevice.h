@@ -105,7 +105,9 @@ size_t deviceWidth(int vgpuType); // bytes per value (0 for bit-packed BOOLEAN)
 
 // Appends the device image of `v` (numeric / boolean, any stack of dictionary / constant wrappers) to `b`.
 // `idsOfBase` (optional): replaces the base values by these int32 value ids (VARCHAR keys).
-void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase = nullptr);
+// `valuesOverride` (optional): a flat BOOLEAN vector of the base's length whose values replace the base's (string
+// predicates evaluated per base value); nulls, indices and wrappers stay those of `v`.
+void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase = nullptr, const BaseVector* valuesOverride = nullptr);
 // Upper bound of the device bytes bindColumn needs for `v`.
 size_t bindBytes(const VectorPtr& v);
 

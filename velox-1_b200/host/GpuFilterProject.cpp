@@ -83,20 +83,21 @@ size_t bindBytes(const VectorPtr& v) {
   return base * 8 + n * 4 + 2 * (bits::nwords(std::max(n, base)) * 8) + 5 * 256;
 }
 
-void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase) {
+void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase, const BaseVector* valuesOverride) {
   Decoded d = decode(v);
   vgpu_column c{};
-  const int t = idsOfBase ? VGPU_INTEGER : deviceType(d.base->type());
+  const int t = idsOfBase ? VGPU_INTEGER : deviceType(valuesOverride ? valuesOverride->type() : d.base->type());
   c.type = t;
   const size_t w = deviceWidth(t);
   const size_t baseN = d.base->size();
   auto baseBytes = [&](size_t n) { return w ? n * w : bits::nwords(n) * 8; };
-  const void* baseRaw = idsOfBase ? (const void*)idsOfBase->data() : rawValuesOf(d.base);
+  const void* baseRaw = idsOfBase ? (const void*)idsOfBase->data() : rawValuesOf(valuesOverride ? valuesOverride : d.base);
   if (d.constant) {
     c.encoding = VGPU_CONSTANT;
     c.constant_is_null = d.constantNull || (d.base->mayHaveNulls() && !bits::isBitSet(d.base->nulls().data(), 0));
     if (!c.constant_is_null) {
       if (idsOfBase) c.constant.i = (*idsOfBase)[0];
+      else if (valuesOverride) c.constant.i = static_cast<const BoolVector*>(valuesOverride)->valueAt(0);
       else switch (d.base->type()->kind()) {
         case TypeKind::BOOLEAN: c.constant.i = static_cast<const BoolVector*>(d.base)->valueAt(0); break;
         case TypeKind::TINYINT: c.constant.i = static_cast<const FlatVector<int8_t>*>(d.base)->valueAt(0); break;
@@ -189,7 +190,19 @@ RowVectorPtr GpuFilterProject::getOutput() {
   const size_t n = in->size();
   DeviceBatch batch;
   batch.stream = stream_;
+  std::vector<VectorPtr> predicateBases; // keep the BOOLEAN base vectors alive until the copies are issued
   for (auto& name : lowered_.columns) {
+    if (const auto* sp = lowered_.predicateOf(name)) {
+      // like / < / > ... on a VARCHAR column: evaluated once per BASE string, bound as a BOOLEAN column over the batch's
+      // own indices and nulls (a dictionary-encoded column costs no per-row host work)
+      const auto& child = in->childAt(inputType_->getChildIdx(sp->column));
+      const auto* base = static_cast<const FlatVector<std::string>*>(decode(child).base);
+      auto match = std::make_shared<BoolVector>(base->size());
+      for (size_t i = 0; i < base->size(); ++i) match->set(i, LoweredProgram::evalStringPredicate(sp->fn, base->valueAt(i), sp->literal));
+      predicateBases.push_back(match);
+      bindColumn(batch, child, nullptr, match.get());
+      continue;
+    }
     const auto& child = in->childAt(inputType_->getChildIdx(name));
     if (child->type()->kind() == TypeKind::VARCHAR && lowered_.stringColumns.count(name)) {
       // compared with =, <>, IN: the base strings become value ids of the operator's dictionary (one lookup per BASE

@@ -158,6 +158,11 @@ struct GpuHashAggregation::Impl {
           info.acc0 = addAcc(VGPU_ACC_SUM_F64, addOutput(exprOf(col + ".sum")));
           info.acc1 = addAcc(VGPU_ACC_SUM_I64, addOutput(exprOf(col + ".count")));
         }
+      } else if (a.function == "bool_and" || a.function == "bool_or") {
+        // bool_and = min, bool_or = max over FALSE < TRUE; NULL inputs ignored, NULL without input
+        // (velox/functions/prestosql/aggregates/BoolAggregates.cpp); the intermediate is the same BOOLEAN
+        VB_USER_CHECK(x->type()->kind() == TypeKind::BOOLEAN, a.function + " takes one BOOLEAN argument");
+        info.acc0 = addAcc(a.function == "bool_and" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(x));
       } else if (a.function == "min" || a.function == "max") {
         VB_USER_CHECK(x->type()->kind() != TypeKind::VARCHAR && x->type()->kind() != TypeKind::BOOLEAN, a.function + " over " + x->type()->toString() + " is not supported on the GPU");
         info.acc0 = addAcc(a.function == "min" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(x->type()->kind() == TypeKind::REAL ? castTo(x, DOUBLE()) : x));
@@ -203,7 +208,7 @@ struct GpuHashAggregation::Impl {
     for (size_t i = 0; i < keys.size(); ++i) specs[i] = vgpu_key_spec{(int32_t)i, mode == VGPU_AGG_HASH ? keys[i].bits : 0, keys[i].lo, keys[i].hi};
     lowered = lowerExpressions(hasFused ? fused.filter : nullptr, outputs);
     // string comparisons need the FilterProject operator's value-id dictionary: the adapter keeps the two operators
-    if (!lowered.stringColumns.empty() || !lowered.stringLiterals.empty()) throw VeloxUserError("VARCHAR comparisons are evaluated by GpuFilterProject, not inside the fused aggregation");
+    if (!lowered.stringColumns.empty() || !lowered.stringLiterals.empty() || !lowered.stringPredicates.empty()) throw VeloxUserError("VARCHAR comparisons are evaluated by GpuFilterProject, not inside the fused aggregation");
     const auto pdesc = lowered.desc();
     check(vgpu_program_create(&pdesc, &program), "vgpu_program_create");
     vgpu_agg_desc d{};
@@ -669,6 +674,7 @@ RowVectorPtr GpuHashAggregation::getOutput() {
       const auto outKind = a.outType->kind();
       const bool accIsDouble = kind == VGPU_ACC_SUM_F64 || ((kind == VGPU_ACC_MIN || kind == VGPU_ACC_MAX) && m.outputs[m.accs[a.acc0].input]->type()->isFloating());
       switch (outKind) {
+        case TypeKind::BOOLEAN: { auto f = std::make_shared<BoolVector>((size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, value(g, a.acc0) != 0); v = f; break; }
         case TypeKind::DOUBLE: { auto f = flatOf<double>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, asDouble(value(g, a.acc0))); v = f; break; }
         case TypeKind::REAL: { auto f = flatOf<float>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (float)asDouble(value(g, a.acc0))); v = f; break; }
         case TypeKind::BIGINT: { auto f = flatOf<int64_t>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, value(g, a.acc0)); v = f; break; }
@@ -678,6 +684,7 @@ RowVectorPtr GpuHashAggregation::getOutput() {
         default: throw VeloxRuntimeError("aggregate result type " + a.outType->toString() + " is not supported");
       }
       VB_CHECK(accIsDouble == a.outType->isFloating(), "accumulator / result type mismatch for " + a.fn);
+      (void)outKind;
       for (int64_t g = 0; g < n; ++g) if (nonNull(g, a.acc0) == 0) v->setNull(g, true);
     }
     children.push_back(v);

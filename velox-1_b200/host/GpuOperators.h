@@ -41,7 +41,7 @@ class GpuFilterProject : public exec::Operator {
   const FilterProjectExprs& exprsAndProjection() const { return exprs_; }
   const RowTypePtr& inputType() const { return inputType_; }
   // VARCHAR =, <>, IN run on this operator's value-id dictionary; such a FilterProject is not fused into an aggregation
-  bool comparesStrings() const { return !lowered_.stringColumns.empty() || !lowered_.stringLiterals.empty(); }
+  bool comparesStrings() const { return !lowered_.stringColumns.empty() || !lowered_.stringLiterals.empty() || !lowered_.stringPredicates.empty(); }
  private:
   FilterProjectExprs exprs_;
   RowTypePtr inputType_;

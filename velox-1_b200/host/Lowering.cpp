@@ -58,7 +58,9 @@ class Lowerer {
     Value res;
     const std::string fn = nameOf(e);
     res.opnd = (fn == "and" || fn == "or") ? genConjunct(e, fn) : genCall(e, fn);
-    if (shared || wantSlot) {
+    // a call that lowered to a plain input column (a string predicate bound by the operator) or a NULL is a leaf
+    const bool leafLike = res.opnd.kind == VGPU_OPND_COL || res.opnd.kind == VGPU_OPND_NULL;
+    if ((shared || wantSlot) && !leafLike) {
       if (res.opnd.kind != VGPU_OPND_SLOT) {
         const int slot = alloc(isBool(e));
         out.ops.back().dst_slot = (int16_t)slot;
@@ -150,7 +152,31 @@ class Lowerer {
     return v;
   }
 
+  // like / < / <= / > / >= between a VARCHAR column and a literal: a BOOLEAN virtual column (LoweredProgram::stringPredicates)
+  bool stringPredicate(const TypedExprPtr& e, const std::string& fn, vgpu_operand& res) {
+    if (fn != "like" && fn != "lt" && fn != "lte" && fn != "gt" && fn != "gte") return false;
+    const auto& in = e->inputs();
+    if (in.size() != 2 || in[0]->type()->kind() != TypeKind::VARCHAR) return false;
+    if (in[0]->kind() != ITypedExpr::Kind::kFieldAccess || in[1]->kind() != ITypedExpr::Kind::kConstant)
+      throw VeloxUserError("Scalar function " + fn + " over VARCHAR is supported between a column and a literal only");
+    auto lit = static_cast<const ConstantTypedExpr*>(in[1].get());
+    if (lit->isNull()) { res = opnd(VGPU_OPND_NULL, VGPU_BOOLEAN, 0); return true; }
+    const std::string column = static_cast<const FieldAccessTypedExpr*>(in[0].get())->name();
+    std::string name;
+    for (auto& p : out.stringPredicates) if (p.column == column && p.fn == fn && p.literal == lit->stringValue()) name = p.virtualName;
+    if (name.empty()) {
+      name = "$sp" + std::to_string(out.stringPredicates.size());
+      out.stringPredicates.push_back({name, column, fn, lit->stringValue()});
+    }
+    int idx = -1;
+    for (size_t i = 0; i < out.columns.size(); ++i) if (out.columns[i] == name) idx = (int)i;
+    if (idx < 0) { idx = (int)out.columns.size(); out.columns.push_back(name); }
+    res = opnd(VGPU_OPND_COL, VGPU_BOOLEAN, idx);
+    return true;
+  }
+
   vgpu_operand genCall(const TypedExprPtr& e, const std::string& fn) {
+    { vgpu_operand sp; if (stringPredicate(e, fn, sp)) return sp; }
     auto args = genArgs(e->inputs());
     const vgpu_operand none = opnd(VGPU_OPND_NONE, 0, 0);
     vgpu_operand res;
@@ -253,6 +279,25 @@ static TypedExprPtr desugarSwitch(const TypedExprPtr& e) {
     tail = std::make_shared<CallTypedExpr>(e->type(), std::move(args), "if");
   }
   return tail;
+}
+
+bool LoweredProgram::evalStringPredicate(const std::string& fn, const std::string& v, const std::string& lit) {
+  if (fn == "like") { // iterative wildcard match: % = any run of characters, _ = exactly one
+    size_t i = 0, j = 0, star = std::string::npos, mark = 0;
+    while (i < v.size()) {
+      if (j < lit.size() && (lit[j] == '_' || lit[j] == v[i])) { ++i; ++j; }
+      else if (j < lit.size() && lit[j] == '%') { star = j++; mark = i; }
+      else if (star != std::string::npos) { j = star + 1; i = ++mark; }
+      else return false;
+    }
+    while (j < lit.size() && lit[j] == '%') ++j;
+    return j == lit.size();
+  }
+  const int c = v.compare(lit); // bytewise, like StringView::compare
+  if (fn == "lt") return c < 0;
+  if (fn == "lte") return c <= 0;
+  if (fn == "gt") return c > 0;
+  return c >= 0;
 }
 
 LoweredProgram lowerExpressions(const TypedExprPtr& filterIn, const std::vector<TypedExprPtr>& outputsIn) {

@@ -19,6 +19,19 @@ struct LoweredProgram {
   // columns named in stringColumns through ONE string -> id dictionary that starts with these literals.
   std::vector<std::string> stringLiterals;
   std::set<std::string> stringColumns;
+  // Predicates over ONE VARCHAR column and a literal (like, lt, lte, gt, gte): the operator evaluates them on the HOST,
+  // once per BASE string of the batch's dictionary (the reference's peeled evaluation, velox/expression/PeeledEncoding.cpp:
+  // the result of a deterministic function over a dictionary is a dictionary over its results), and binds the outcome
+  // as a BOOLEAN column that keeps the batch's indices and nulls.  The program reads it as the input column
+  // `virtualName` = "$sp<k>".
+  struct StringPredicate { std::string virtualName, column, fn, literal; };
+  std::vector<StringPredicate> stringPredicates;
+  const StringPredicate* predicateOf(const std::string& virtualName) const {
+    for (auto& p : stringPredicates) if (p.virtualName == virtualName) return &p;
+    return nullptr;
+  }
+  // SQL LIKE with % and _ (no escape character) / bytewise ordering like StringView::compare.
+  static bool evalStringPredicate(const std::string& fn, const std::string& value, const std::string& literal);
   vgpu_program_desc desc() const {
     vgpu_program_desc d{};
     d.ops = ops.data(); d.n_ops = (int32_t)ops.size(); d.filter = filter;

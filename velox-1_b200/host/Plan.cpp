@@ -11,6 +11,7 @@ TypePtr AggregationNode::intermediateType(const std::string& fn, const TypePtr& 
   if (fn == "sum") return raw->isFloating() ? DOUBLE() : BIGINT(); // sum(real) keeps a double accumulator
   if (fn == "avg") return ROW({"sum", "count"}, {DOUBLE(), BIGINT()});
   if (fn == "min" || fn == "max") return raw;
+  if (fn == "bool_and" || fn == "bool_or") return BOOLEAN(); // functions/prestosql/aggregates/BoolAggregates.cpp
   throw VeloxUserError("Aggregate function not registered: " + fn);
 }
 TypePtr AggregationNode::finalType(const std::string& fn, const TypePtr& raw) {
@@ -18,6 +19,7 @@ TypePtr AggregationNode::finalType(const std::string& fn, const TypePtr& raw) {
   if (fn == "sum") return raw->kind() == TypeKind::REAL ? REAL() : raw->isFloating() ? DOUBLE() : BIGINT();
   if (fn == "avg") return raw->kind() == TypeKind::REAL ? REAL() : DOUBLE();
   if (fn == "min" || fn == "max") return raw;
+  if (fn == "bool_and" || fn == "bool_or") return BOOLEAN();
   throw VeloxUserError("Aggregate function not registered: " + fn);
 }
 
@@ -244,6 +246,18 @@ class Parser {
         } while (accept(","));
         VB_USER_CHECK(accept(")"), "IN: ')' expected");
         return negated ? std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{any}, "not") : any;
+      }
+      pos_ = save;
+    }
+    {
+      // x [NOT] LIKE 'pattern' (DuckParser.cpp maps the ~~ operator / LIKE to the function "like")
+      const size_t save = pos_;
+      const bool negated = acceptWord("not");
+      if (acceptWord("like")) {
+        auto pattern = parseAdd();
+        VB_USER_CHECK(a->type()->kind() == TypeKind::VARCHAR && pattern->type()->kind() == TypeKind::VARCHAR, "like expects VARCHAR arguments");
+        TypedExprPtr e = std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{a, pattern}, "like");
+        return negated ? std::make_shared<CallTypedExpr>(BOOLEAN(), std::vector<TypedExprPtr>{e}, "not") : e;
       }
       pos_ = save;
     }

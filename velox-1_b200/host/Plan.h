@@ -183,6 +183,28 @@ class AggregationNode : public PlanNode {
   RowTypePtr type_;
 };
 
+// velox/core/PlanNode.h OrderByNode: sorting keys with ascending / nulls-first flags.  The B200 path ends at the
+// aggregation; this node exists so that TpchQueryBuilder's plans (…finalAggregation().orderBy(keys, false),
+// velox/exec/tests/utils/TpchQueryBuilder.cpp:232) can be written unchanged — whoever runs the plan supplies the
+// operator (Velox's own exec::OrderBy in a deployment; tests/host registers a stand-in through a PlanNodeTranslator).
+struct SortOrder { bool ascending = true; bool nullsFirst = true; };
+class OrderByNode : public PlanNode {
+ public:
+  OrderByNode(PlanNodeId id, std::vector<std::string> keys, std::vector<SortOrder> orders, bool isPartial, PlanNodePtr source)
+      : PlanNode(std::move(id), {source}), keys_(std::move(keys)), orders_(std::move(orders)), isPartial_(isPartial) {
+    for (auto& k : keys_) sources()[0]->outputType()->getChildIdx(k); // throws on unknown columns
+  }
+  const std::vector<std::string>& sortingKeys() const { return keys_; }
+  const std::vector<SortOrder>& sortingOrders() const { return orders_; }
+  bool isPartial() const { return isPartial_; }
+  const RowTypePtr& outputType() const override { return sources()[0]->outputType(); }
+  std::string name() const override { return "OrderBy"; }
+ private:
+  std::vector<std::string> keys_;
+  std::vector<SortOrder> orders_;
+  bool isPartial_;
+};
+
 } // namespace core
 
 // ---- expression text -> typed expression ----------------------------------------------------------------
@@ -212,6 +234,8 @@ class PlanBuilder {
   PlanBuilder& finalAggregation();
   PlanBuilder& aggregation(const std::vector<std::string>& keys, const std::vector<std::string>& aggregates,
                            core::AggregationNode::Step step, bool ignoreNullKeys, const std::vector<std::string>& masks = {});
+  // keys: "name [ASC|DESC] [NULLS FIRST|NULLS LAST]" (PlanBuilder::orderBy, velox/exec/tests/utils/PlanBuilder.h)
+  PlanBuilder& orderBy(const std::vector<std::string>& keys, bool isPartial);
   // custom nodes (PlanBuilder::addNode, velox/exec/tests/utils/PlanBuilder.h:787-792)
   PlanBuilder& addNode(std::function<core::PlanNodePtr(std::string nodeId, core::PlanNodePtr source)> make);
   core::PlanNodePtr planNode() const { return node_; }

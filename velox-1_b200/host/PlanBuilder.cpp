@@ -113,6 +113,29 @@ PlanBuilder& PlanBuilder::followUp(AggregationNode::Step step) {
 PlanBuilder& PlanBuilder::intermediateAggregation() { return followUp(AggregationNode::Step::kIntermediate); }
 PlanBuilder& PlanBuilder::finalAggregation() { return followUp(AggregationNode::Step::kFinal); }
 
+PlanBuilder& PlanBuilder::orderBy(const std::vector<std::string>& keys, bool isPartial) {
+  std::vector<std::string> names;
+  std::vector<core::SortOrder> orders;
+  for (auto& k : keys) {
+    std::vector<std::string> words;
+    std::string w;
+    for (char c : k + " ") { if (c == ' ') { if (!w.empty()) words.push_back(w); w.clear(); } else w += (char)std::toupper((unsigned char)c); }
+    VB_USER_CHECK(!words.empty(), "orderBy: empty key");
+    core::SortOrder o;
+    size_t first = k.find_first_not_of(' ');
+    names.push_back(k.substr(first, k.find(' ', first) == std::string::npos ? std::string::npos : k.find(' ', first) - first));
+    for (size_t i = 1; i < words.size(); ++i) {
+      if (words[i] == "DESC") { o.ascending = false; o.nullsFirst = false; }
+      else if (words[i] == "ASC") { o.ascending = true; }
+      else if (words[i] == "NULLS" && i + 1 < words.size()) { o.nullsFirst = words[i + 1] == "FIRST"; ++i; }
+      else throw VeloxUserError("orderBy: cannot parse '" + k + "'");
+    }
+    orders.push_back(o);
+  }
+  node_ = std::make_shared<core::OrderByNode>(nextId(), std::move(names), std::move(orders), isPartial, node_);
+  return *this;
+}
+
 PlanBuilder& PlanBuilder::addNode(std::function<PlanNodePtr(std::string, PlanNodePtr)> make) {
   node_ = make(nextId(), node_);
   return *this;
