@@ -468,7 +468,7 @@ def run_ours(args, rank, world, local_rank):
                      "kernel_origin": kernel_note, "algorithmic_bytes_per_launch": n * Q1_BYTES_PER_ROW,
                      "peak_source": peak_src, "nominal_peak": 8000.0, "frac_of_nominal": achieved / 8000.0,
                      "note": "peak is the driver's copy (read+write) bandwidth; a read-only stream can exceed it "
-                             "(ncu: 84 % of its DRAM peak for this kernel, profiles/r01_q1_ncu_summary.json)"},
+                             "(ncu: 82 % of its DRAM peak, 2.64 GB read for 2.64 GB algorithmic, profiles/r02_q1_ncu_summary.json)"},
         "e2e": {"value": total_rows * e2e_steps / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": n * Q1_BYTES_PER_ROW,
                 "d2h_bytes_per_step": int(d2h[0]), "steps": e2e_steps, "chunk_rows": args.chunk_rows,
                 "note": "host RowVector-style pinned columns -> HBM in chunks on a copy stream, double-buffered against the scan"},
