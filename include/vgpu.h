@@ -53,9 +53,18 @@ typedef enum {
   VGPU_ERR_NCCL = 5
 } vgpu_status;
 
-/* Device value types.  Numbering of the first seven follows velox/type/Type.h:62-84 (TypeKind).
- * DATE is INTEGER (days since epoch).  VARCHAR never reaches the device as bytes: the host maps
- * strings to int32 value ids (VectorHasher::makeValueIds analogue) and keeps the dictionary. */
+/* Device value types.  Numbering follows velox/type/Type.h:62-84 (TypeKind).  DATE is INTEGER (days since epoch).
+ * VARCHAR reaches the device in one of two ways:
+ *  - as int32 value ids: the host maps strings to ids (VectorHasher::makeValueIds analogue) and keeps the dictionary;
+ *  - as VGPU_VARCHAR: `values` is the vector's own array of 16-byte StringViews (velox/type/StringView.h: u32 size,
+ *    4 prefix bytes, then 8 inline bytes or a pointer), 16-byte aligned, FLAT or as the base of a DICTIONARY.  The
+ *    kernels read a value as the BIGINT the reference uses for short string keys (velox/exec/VectorHasher.h:324-329
+ *    stringAsNumber: the bytes as a little-endian word + 1 << (8 * size); "" is 0), so programs read the column through
+ *    BIGINT operands and group keys come back as that number (vgpu_string_of_number turns it back into bytes).  Only
+ *    strings of at most 7 bytes have a number: a longer one that a passing row uses latches an error that
+ *    vgpu_check_errors reports as VGPU_ERR_UNSUPPORTED — the host checks lengths first and maps batches with long
+ *    strings to numbers >= 2^60 of its own.  A CONSTANT VGPU_VARCHAR column carries the number in `constant.i`.
+ *    VGPU_VARCHAR columns need the plan-specialised kernels (NVRTC or an AOT plan). */
 typedef enum {
   VGPU_BOOLEAN = 0, /* bit-packed, 1 bit per row */
   VGPU_TINYINT = 1,
@@ -63,8 +72,31 @@ typedef enum {
   VGPU_INTEGER = 3,
   VGPU_BIGINT = 4,
   VGPU_REAL = 5,
-  VGPU_DOUBLE = 6
+  VGPU_DOUBLE = 6,
+  VGPU_VARCHAR = 7 /* 16-byte StringViews, read as their stringAsNumber value */
 } vgpu_type;
+
+/* Host-side helpers for VGPU_VARCHAR keys: the number of a string of at most 7 bytes (-1 when longer), and back
+ * (returns the size; `out` receives the bytes, no terminator; -1 when `number` is not such a number). */
+static inline int64_t vgpu_number_of_string(const char* data, uint32_t size) {
+  uint64_t w = 0;
+  uint32_t i;
+  if (size > 7u) return -1;
+  for (i = 0; i < size; ++i) w |= (uint64_t)(uint8_t)data[i] << (8u * i);
+  return size == 0u ? 0 : (int64_t)(w + ((uint64_t)1 << (8u * size)));
+}
+static inline int32_t vgpu_string_of_number(int64_t number, char out[8]) {
+  const uint64_t w = (uint64_t)number;
+  int32_t size, i;
+  if (w == 0) return 0;
+  for (size = 1; size <= 7; ++size) {
+    if ((w >> (8 * size)) == 1u) { /* the marker bit of a string of `size` bytes */
+      for (i = 0; i < size; ++i) out[i] = (char)(w >> (8 * i));
+      return size;
+    }
+  }
+  return -1;
+}
 
 typedef enum { VGPU_FLAT = 0, VGPU_DICTIONARY = 1, VGPU_CONSTANT = 2 } vgpu_encoding;
 

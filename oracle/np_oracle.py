@@ -37,6 +37,23 @@ def decode(values, indices=None, not_null=None, base_not_null=None):
     return out, (None if nn.all() else nn)
 
 
+def string_as_number(s):
+    """VectorHasher::stringAsNumber (velox/exec/VectorHasher.h:324-329) over bits::loadPartialWord
+    (velox/common/base/BitUtil.h: the first `size` bytes as a little-endian word): a string of at most 7 bytes as an
+    int64; every length has its own range, so "a" != "a\\0".  Longer strings have no number (kUnmappable upstream)."""
+    if len(s) > 7:
+        return None
+    word = 0
+    for i, b in enumerate(bytes(s)):
+        word |= b << (8 * i)
+    return word if len(s) == 0 else word + (1 << (len(s) * 8))
+
+
+def strings_as_numbers(strings):
+    """A VARCHAR column of short strings as the BIGINT column the device reads it as."""
+    return np.array([string_as_number(s) for s in strings], dtype=np.int64)
+
+
 # ---- expression evaluation -------------------------------------------------------------------
 def _limits(t):
     i = np.iinfo(NP[t])

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libvgpu.so")
 
 # ---- enums (mirror include/vgpu.h) -----------------------------------------------------------
 OK, ERR_INVALID, ERR_CUDA, ERR_USER, ERR_UNSUPPORTED, ERR_NCCL = range(6)
-BOOLEAN, TINYINT, SMALLINT, INTEGER, BIGINT, REAL, DOUBLE = range(7)
+BOOLEAN, TINYINT, SMALLINT, INTEGER, BIGINT, REAL, DOUBLE, VARCHAR = range(8)
 FLAT, DICTIONARY, CONSTANT = range(3)
 OPND_NONE, OPND_ACC, OPND_SLOT, OPND_COL, OPND_IMM, OPND_NULL = range(6)
 OP_NOP, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG, OP_MOD = range(7)

@@ -86,13 +86,13 @@ struct Gen {
   // Alignment a column's walked array (values, or indices of a dictionary) needs for the block-wide vector loads.
   static int walk_log2(const DevCol& d) {
     const bool dict = d.encoding == VGPU_DICTIONARY;
-    return dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : 3));
+    return dict ? 2 : (d.type == VGPU_BOOLEAN ? -1 : (d.type == VGPU_TINYINT ? 0 : d.type == VGPU_SMALLINT ? 1 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 2 : d.type == VGPU_VARCHAR ? 4 : 3));
   }
   bool vector_loads_ok(const DevCol& d) const {
     if (p.in_rows) return false;
     const void* walk = d.encoding == VGPU_DICTIONARY ? (const void*)d.indices : d.values;
     const int lg = walk_log2(d);
-    const uintptr_t need = lg == 3 ? 16 : lg == 2 ? (quad ? 16 : 8) : 1;
+    const uintptr_t need = (lg == 3 || lg == 4) ? 16 : lg == 2 ? (quad ? 16 : 8) : 1;
     return (reinterpret_cast<uintptr_t>(walk) & (need - 1)) == 0;
   }
 
@@ -128,6 +128,12 @@ struct Gen {
           else out("    const u32 Q%d = r0 < n ? bits4(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u;\n", c, c);
         } else if (full) out("    const u32 Q%d = bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) | (bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) << 2);\n", c, c, c);
         else out("    const u32 Q%d = (r0 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r0) : 0u) | ((r1 < n ? bits2(reinterpret_cast<const u64*>(p.values[%d]), r1) : 0u) << 2);\n", c, c, c);
+        continue;
+      }
+      if (lg == 4) { // flat VARCHAR: one 16-byte StringView per row -> its number (sv_number)
+        out("    u64 Q%d[4];\n", c);
+        out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n      const i64 r = %s;\n", row_of_j().c_str());
+        out("      Q%d[j] = r < n ? sv_number(ld16(p.values[%d], %s * 16)) : 0ull;\n    }\n", c, c, p.in_rows ? "RR[j]" : "r");
         continue;
       }
       const bool real = !dict && d.type == VGPU_REAL;
@@ -174,12 +180,20 @@ struct Gen {
       const DevCol& d = p.cols[c];
       const char* ty = d.type == VGPU_TINYINT ? "signed char" : d.type == VGPU_SMALLINT ? "short" : d.type == VGPU_INTEGER ? "int" : d.type == VGPU_REAL ? "float" : "u64";
       out("  u64 DB%d = 0ull;\n  if (lane < p.base_len[%d]) {\n", c, c);
-      if (d.type == VGPU_REAL) out("    DB%d = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + lane));\n", c, c);
+      if (d.type == VGPU_VARCHAR) out("    DB%d = sv_number(ld16(p.values[%d], lane * 16));\n", c, c);
+      else if (d.type == VGPU_REAL) out("    DB%d = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + lane));\n", c, c);
       else if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) out("    DB%d = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + lane);\n", c, c);
       else out("    DB%d = (u64)(i64)__ldg(reinterpret_cast<const %s*>(p.values[%d]) + lane);\n", c, ty, c);
       out("  }\n");
       if (d.base_nulls) out("  const u32 DBN%d = (u32)__ldg(p.base_nulls[%d]);\n", c, c);
     }
+  }
+
+  // VARCHAR: bit 63 of the number marks a string longer than 7 bytes; it becomes the value's error latch, raised only
+  // when a passing row consumes it (a NULL row's bytes are never looked at).
+  void gen_varchar_fixup(int c) {
+    if (p.cols[c].type != VGPU_VARCHAR) return;
+    out("      c%d_.e = valid && !c%d_.n && (c%d_.v >> 63) != 0ull; c%d_.v &= 0x7fffffffffffffffull; if (c%d_.e) ec |= VGF_ERR_STRKEY;\n", c, c, c, c, c);
   }
 
   // Per-row decoded column values (inside the row loop).
@@ -200,11 +214,12 @@ struct Gen {
         out("      V c%d_; {\n", c);
         out("        bool isn = %s;\n", nn.c_str());
         out("        const u32 ix = (u32)Q%d[j] & 31u;\n", c);
-        if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE || d.type == VGPU_REAL) out("        const u64 got = __shfl_sync(0xffffffffu, DB%d, (int)ix);\n", c);
+        if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE || d.type == VGPU_REAL || d.type == VGPU_VARCHAR) out("        const u64 got = __shfl_sync(0xffffffffu, DB%d, (int)ix);\n", c);
         else out("        const u64 got = (u64)(i64)__shfl_sync(0xffffffffu, (int)DB%d, (int)ix);\n", c); // one 32-bit shuffle
         if (d.base_nulls) out("        isn = isn || !((DBN%d >> ix) & 1u);\n", c);
         out("        isn = isn || !valid;\n");
         out("        c%d_ = V{isn ? 0ull : got, isn, false};\n      }\n", c);
+        gen_varchar_fixup(c);
         out("      const V c%d = c%d_;\n", c, c);
         continue;
       }
@@ -215,18 +230,23 @@ struct Gen {
         if (is_bool) out("          cv%d_ = bit1(reinterpret_cast<const u64*>(p.values[%d]), ix);\n", c, c);
         else {
           const char* ty = d.type == VGPU_TINYINT ? "signed char" : d.type == VGPU_SMALLINT ? "short" : d.type == VGPU_INTEGER ? "int" : d.type == VGPU_REAL ? "float" : "u64";
-          if (d.type == VGPU_REAL) out("          raw = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + ix));\n", c);
+          if (d.type == VGPU_VARCHAR) out("          raw = sv_number(ld16(p.values[%d], ix * 16));\n", c);
+          else if (d.type == VGPU_REAL) out("          raw = d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + ix));\n", c);
           else if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) out("          raw = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + ix);\n", c);
           else out("          raw = (u64)(i64)__ldg(reinterpret_cast<const %s*>(p.values[%d]) + ix);\n", ty, c);
         }
         if (d.base_nulls) out("          if (!bit1(p.base_nulls[%d], ix)) isn = true;\n", c);
         out("        }\n        c%d_ = V{raw, isn, false};\n      }\n", c);
         if (is_bool) out("      const B cb%d = {cv%d_ && !c%d_.n, c%d_.n, false};\n", c, c, c, c);
-        else out("      const V c%d = c%d_;\n", c, c);
+        else { gen_varchar_fixup(c); out("      const V c%d = c%d_;\n", c, c); }
         continue;
       }
       if (is_bool) out("      const B cb%d = {(bool)((Q%d >> j) & 1u), %s, false};\n", c, c, nn.c_str());
-      else out("      const V c%d = {Q%d[j], %s, false};\n", c, c, nn.c_str());
+      else if (d.type == VGPU_VARCHAR) {
+        out("      V c%d_ = {Q%d[j], %s, false};\n", c, c, nn.c_str());
+        gen_varchar_fixup(c);
+        out("      const V c%d = c%d_;\n", c, c);
+      } else out("      const V c%d = {Q%d[j], %s, false};\n", c, c, nn.c_str());
     }
   }
 
@@ -709,6 +729,7 @@ struct Gen {
       // element alignment is all a column needs (a sliced vector's base is rarely 16-byte aligned); bitmaps are read as 32-bit words
       if (lg > 0 && (reinterpret_cast<uintptr_t>(walk) & ((1u << lg) - 1u)) != 0) { decline("column not aligned to its element size"); return; }
       if (lg < 0 && (reinterpret_cast<uintptr_t>(walk) & 7u) != 0) { decline("unaligned bitmap"); return; }
+      if (d.type == VGPU_VARCHAR && (reinterpret_cast<uintptr_t>(d.values) & 15u) != 0) { decline("VARCHAR values not 16-byte aligned"); return; }
       if (d.nulls && (reinterpret_cast<uintptr_t>(d.nulls) & 7u) != 0) { decline("unaligned nulls"); return; }
     }
     if (p.in_rows && p.mode == kSinkFilterProject) { decline("row selection with the FilterProject sink"); return; }

@@ -44,6 +44,7 @@ typedef int i32;
 #define VGF_ERR_CAST 4u
 #define VGF_ERR_KEYRANGE 8u
 #define VGF_ERR_TABLEFULL 16u
+#define VGF_ERR_STRKEY 32u
 // CellKind (internal.h)
 #define VGF_SUMF64 0
 #define VGF_SUMI64 1
@@ -101,6 +102,16 @@ __device__ __forceinline__ u64 sext32(u32 x) { return (u64)(i64)(i32)x; }
 // ---- loads (streaming: every input byte is read once) -------------------------------------------
 __device__ __forceinline__ uint4 ld16(const void* base, i64 byte_off) {
   return __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(base) + byte_off));
+}
+// A VARCHAR value (16-byte StringView: u32 size, 4 prefix bytes, then 8 inline bytes or a pointer) of at most 7
+// bytes as the integer the reference uses for short string keys (velox/exec/VectorHasher.h:324-329 stringAsNumber:
+// the bytes as a little-endian word plus 1 << (8 * size), so every length has its own range and "" is 0).
+// Bit 63 set = longer than 7 bytes (no such number).
+__device__ __forceinline__ u64 sv_number(uint4 sv) {
+  const u32 size = sv.x;
+  if (size > 7u) return 1ull << 63;
+  const u64 mark = 1ull << (8u * size);
+  return size == 0u ? 0ull : (pack64(sv.y, sv.z) & (mark - 1ull)) + mark;
 }
 __device__ __forceinline__ uint2 ld8(const void* base, i64 byte_off) {
   return __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(base) + byte_off));

@@ -32,7 +32,7 @@ namespace vg {
 static_assert(VGF_BOOLEAN == VGPU_BOOLEAN && VGF_DOUBLE == VGPU_DOUBLE && VGF_INTEGER == VGPU_INTEGER, "type codes");
 static_assert(VGF_ADD == VGPU_OP_ADD && VGF_MOD == VGPU_OP_MOD && VGF_EQ == VGPU_OP_EQ && VGF_GE == VGPU_OP_GE, "opcodes");
 static_assert(VGF_SUMF64 == kCellSumF64 && VGF_COUNT == kCellCount && VGF_MAXF64 == kCellMaxF64, "cell kinds");
-static_assert(VGF_ERR_OVERFLOW == kErrOverflow && VGF_ERR_KEYRANGE == kErrKeyRange && VGF_ERR_TABLEFULL == kErrTableFull, "error bits");
+static_assert(VGF_ERR_OVERFLOW == kErrOverflow && VGF_ERR_KEYRANGE == kErrKeyRange && VGF_ERR_TABLEFULL == kErrTableFull && VGF_ERR_STRKEY == kErrStringKey, "error bits");
 
 struct FusedKernel {
   void* module = nullptr;   // CUmodule

@@ -33,7 +33,8 @@ enum : uint32_t {
   kErrDivZero = 2u,      // "division by zero"
   kErrCastRange = 4u,    // cast out of range / NaN to integer
   kErrKeyRange = 8u,     // grouping key outside the declared [min,max] or unexpected NULL
-  kErrTableFull = 16u    // HBM hash table could not place a key (internal; host grows + retries)
+  kErrTableFull = 16u,   // HBM hash table could not place a key (internal; host grows + retries)
+  kErrStringKey = 32u    // a VGPU_VARCHAR value longer than 7 bytes was used (the host maps those to ids itself)
 };
 
 struct DevCol {

@@ -75,6 +75,7 @@ __device__ __forceinline__ int elem_bytes_log2(uint8_t type) {
     case VGPU_SMALLINT: return 1;
     case VGPU_INTEGER:
     case VGPU_REAL: return 2;
+    case VGPU_VARCHAR: return 4;
     default: return 3;
   }
 }
@@ -1323,6 +1324,7 @@ static int host_elem_log2(int type) {
     case VGPU_SMALLINT: return 1;
     case VGPU_INTEGER:
     case VGPU_REAL: return 2;
+    case VGPU_VARCHAR: return 4;
     default: return 3;
   }
 }
@@ -1373,7 +1375,7 @@ int plan_pipeline(const Program& prog, const vgpu_column* cols, int32_t ncols, i
     d.type = (uint8_t)in.type; d.encoding = (uint8_t)in.encoding; d.const_null = (uint8_t)(in.constant_is_null != 0);
     d.stage_off = -1; d.nulls_off = -1; d.bulk_ok = 0;
     d.small_dict = (in.encoding == VGPU_DICTIONARY && in.type != VGPU_BOOLEAN && in.base_length >= 1 && in.base_length <= 32) ? (uint8_t)in.base_length : 0;
-    if (in.type < VGPU_BOOLEAN || in.type > VGPU_DOUBLE) { set_error("column %d: bad type %d", c, in.type); return VGPU_ERR_INVALID; }
+    if (in.type < VGPU_BOOLEAN || in.type > VGPU_VARCHAR) { set_error("column %d: bad type %d", c, in.type); return VGPU_ERR_INVALID; }
     d.elem_log2 = (uint8_t)(in.encoding == VGPU_DICTIONARY ? 2 : host_elem_log2(in.type));
     if (!used[c] || in.encoding == VGPU_CONSTANT) continue;
     if (in.encoding == VGPU_DICTIONARY) {
@@ -1676,6 +1678,12 @@ int launch_pipeline(PipelineParams& p, int tab_bytes, int grid, cudaStream_t str
   p.smem_bmeta_off = p.smem_meta_off + meta_bytes;
   p.smem_tab_off = (p.smem_bmeta_off + bmeta_bytes + 127) & ~127;
   const int smem = p.smem_tab_off + tab_bytes;
+  for (int c = 0; c < p.n_cols; ++c) {
+    if (p.cols[c].type == VGPU_VARCHAR && p.cols[c].stage_off >= 0) {
+      set_error("column %d: VGPU_VARCHAR columns are read by the plan-specialised kernels only (NVRTC or an AOT plan is required)", c);
+      return VGPU_ERR_UNSUPPORTED;
+    }
+  }
   int rc = lower_mops(p);
   if (rc) return rc;
   auto run = [&](auto kernel) -> int {

@@ -73,10 +73,39 @@ def _bits_dev(mask: Optional[np.ndarray], device):
     return None if mask is None else _dev(pack_bits(np.asarray(mask, dtype=bool)).view(np.int64), device)
 
 
+def string_views(strings: Sequence[bytes]) -> np.ndarray:
+    """The 16-byte StringViews of `strings` (velox/type/StringView.h: u32 size, 4 prefix bytes, then the next 8 bytes
+    when the string has at most 12, else a pointer — left 0 here: the device never follows it) as an (n, 2) int64
+    array: what a FlatVector<StringView>'s values buffer holds, and what a VGPU_VARCHAR column points at."""
+    raw = np.zeros((len(strings), 16), dtype=np.uint8)
+    for i, s in enumerate(strings):
+        raw[i, 0:4] = np.frombuffer(np.uint32(len(s)).tobytes(), dtype=np.uint8)
+        head = s[:12] if len(s) <= 12 else s[:4]
+        raw[i, 4:4 + len(head)] = np.frombuffer(head, dtype=np.uint8)
+    return raw.view(np.int64).reshape(len(strings), 2)
+
+
+def number_of_string(s: bytes) -> int:
+    """include/vgpu.h vgpu_number_of_string (velox/exec/VectorHasher.h:324-329 stringAsNumber)."""
+    assert len(s) <= 7
+    return 0 if not s else int.from_bytes(s, "little") + (1 << (8 * len(s)))
+
+
+def string_of_number(number: int) -> bytes:
+    """include/vgpu.h vgpu_string_of_number."""
+    if number == 0:
+        return b""
+    size = (number.bit_length() - 1) // 8
+    assert 1 <= size <= 7 and number >> (8 * size) == 1, number
+    return (number - (1 << (8 * size))).to_bytes(size, "little")
+
+
 def flat_column(type: int, values: np.ndarray, not_null: Optional[np.ndarray] = None, device="cuda") -> DeviceColumn:
-    """Flat vector; `not_null` is a bool mask (True = present) or None."""
+    """Flat vector; `not_null` is a bool mask (True = present) or None.  VARCHAR: `values` = string_views(...)."""
     if type == abi.BOOLEAN:
         v = _dev(pack_bits(np.asarray(values, dtype=bool)).view(np.int64), device)
+    elif type == abi.VARCHAR:
+        v = _dev(np.asarray(values, dtype=np.int64).reshape(-1, 2), device)
     else:
         v = _dev(np.asarray(values, dtype=NP_OF[type]), device)
     return DeviceColumn(type, abi.FLAT, v, nulls=_bits_dev(not_null, device), length=len(values))
@@ -86,6 +115,8 @@ def dictionary_column(type: int, base: np.ndarray, indices: np.ndarray, not_null
                       base_not_null: Optional[np.ndarray] = None, device="cuda") -> DeviceColumn:
     if type == abi.BOOLEAN:
         b = _dev(pack_bits(np.asarray(base, dtype=bool)).view(np.int64), device)
+    elif type == abi.VARCHAR:
+        b = _dev(np.asarray(base, dtype=np.int64).reshape(-1, 2), device)
     else:
         b = _dev(np.asarray(base, dtype=NP_OF[type]), device)
     return DeviceColumn(type, abi.DICTIONARY, b, _dev(np.asarray(indices, dtype=np.int32), device),

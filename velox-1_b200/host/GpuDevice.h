@@ -105,9 +105,13 @@ size_t deviceWidth(int vgpuType); // bytes per value (0 for bit-packed BOOLEAN)
 
 // Appends the device image of `v` (numeric / boolean, any stack of dictionary / constant wrappers) to `b`.
 // `idsOfBase` (optional): replaces the base values by these int32 value ids (VARCHAR keys).
-// `valuesOverride` (optional): a flat BOOLEAN vector of the base's length whose values replace the base's (string
-// predicates evaluated per base value); nulls, indices and wrappers stay those of `v`.
-void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase = nullptr, const BaseVector* valuesOverride = nullptr);
+// `valuesOverride` (optional): a flat BOOLEAN or BIGINT vector of the base's length whose values replace the base's
+// (string predicates evaluated per base value; VARCHAR keys mapped to numbers on the host); nulls, indices and wrappers
+// stay those of `v`.
+// `stringViews`: the base is a StringViewVector and travels as VGPU_VARCHAR (its 16-byte views, read on the device as
+// the stringAsNumber value of strings of at most 7 bytes).
+void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase = nullptr, const BaseVector* valuesOverride = nullptr,
+                bool stringViews = false);
 // Upper bound of the device bytes bindColumn needs for `v`.
 size_t bindBytes(const VectorPtr& v);
 

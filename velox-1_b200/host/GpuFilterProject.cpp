@@ -19,6 +19,7 @@ size_t deviceWidth(int t) {
     case VGPU_TINYINT: return 1;
     case VGPU_SMALLINT: return 2;
     case VGPU_INTEGER: case VGPU_REAL: return 4;
+    case VGPU_VARCHAR: return 16;
     default: return 8;
   }
 }
@@ -70,6 +71,9 @@ const void* rawValuesOf(const BaseVector* flat) {
     case TypeKind::BIGINT: return static_cast<const FlatVector<int64_t>*>(flat)->rawValues();
     case TypeKind::REAL: return static_cast<const FlatVector<float>*>(flat)->rawValues();
     case TypeKind::DOUBLE: return static_cast<const FlatVector<double>*>(flat)->rawValues();
+    case TypeKind::VARCHAR:
+      if (auto sv = dynamic_cast<const StringViewVector*>(flat)) return sv->rawValues();
+      throw VeloxRuntimeError("no raw device image for a VARCHAR vector that is not a StringView vector");
     default: throw VeloxRuntimeError("no raw device image for " + flat->type()->toString());
   }
 }
@@ -80,13 +84,14 @@ size_t bindBytes(const VectorPtr& v) {
   size_t n = v->size(), base = n;
   while (cur->encoding() == VectorEncoding::DICTIONARY) { cur = static_cast<const DictionaryVector*>(cur)->valueVector().get(); base = cur->size(); }
   if (cur->encoding() == VectorEncoding::CONSTANT) { cur = static_cast<const ConstantVector*>(cur)->valueVector().get(); base = cur->size(); }
-  return base * 8 + n * 4 + 2 * (bits::nwords(std::max(n, base)) * 8) + 5 * 256;
+  return base * 16 + n * 4 + 2 * (bits::nwords(std::max(n, base)) * 8) + 5 * 256;
 }
 
-void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase, const BaseVector* valuesOverride) {
+void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* idsOfBase, const BaseVector* valuesOverride, bool stringViews) {
   Decoded d = decode(v);
   vgpu_column c{};
-  const int t = idsOfBase ? VGPU_INTEGER : deviceType(valuesOverride ? valuesOverride->type() : d.base->type());
+  VB_CHECK(!stringViews || dynamic_cast<const StringViewVector*>(d.base) != nullptr, "StringView binding of a vector that holds no StringViews");
+  const int t = stringViews ? VGPU_VARCHAR : idsOfBase ? VGPU_INTEGER : deviceType(valuesOverride ? valuesOverride->type() : d.base->type());
   c.type = t;
   const size_t w = deviceWidth(t);
   const size_t baseN = d.base->size();
@@ -97,7 +102,9 @@ void bindColumn(DeviceBatch& b, const VectorPtr& v, const std::vector<int32_t>* 
     c.constant_is_null = d.constantNull || (d.base->mayHaveNulls() && !bits::isBitSet(d.base->nulls().data(), 0));
     if (!c.constant_is_null) {
       if (idsOfBase) c.constant.i = (*idsOfBase)[0];
+      else if (valuesOverride && valuesOverride->type()->kind() == TypeKind::BIGINT) c.constant.i = static_cast<const FlatVector<int64_t>*>(valuesOverride)->valueAt(0);
       else if (valuesOverride) c.constant.i = static_cast<const BoolVector*>(valuesOverride)->valueAt(0);
+      else if (stringViews) { const auto& sv = static_cast<const StringViewVector*>(d.base)->valueAt(0); c.constant.i = vgpu_number_of_string(sv.data(), sv.size()); VB_CHECK(c.constant.i >= 0, "constant VARCHAR key longer than 7 bytes"); }
       else switch (d.base->type()->kind()) {
         case TypeKind::BOOLEAN: c.constant.i = static_cast<const BoolVector*>(d.base)->valueAt(0); break;
         case TypeKind::TINYINT: c.constant.i = static_cast<const FlatVector<int8_t>*>(d.base)->valueAt(0); break;
@@ -196,9 +203,9 @@ RowVectorPtr GpuFilterProject::getOutput() {
       // like / < / > ... on a VARCHAR column: evaluated once per BASE string, bound as a BOOLEAN column over the batch's
       // own indices and nulls (a dictionary-encoded column costs no per-row host work)
       const auto& child = in->childAt(inputType_->getChildIdx(sp->column));
-      const auto* base = static_cast<const FlatVector<std::string>*>(decode(child).base);
+      const auto* base = decode(child).base;
       auto match = std::make_shared<BoolVector>(base->size());
-      for (size_t i = 0; i < base->size(); ++i) match->set(i, LoweredProgram::evalStringPredicate(sp->fn, base->valueAt(i), sp->literal));
+      for (size_t i = 0; i < base->size(); ++i) match->set(i, LoweredProgram::evalStringPredicate(sp->fn, stringValueAt(base, i), sp->literal));
       predicateBases.push_back(match);
       bindColumn(batch, child, nullptr, match.get());
       continue;
@@ -207,11 +214,12 @@ RowVectorPtr GpuFilterProject::getOutput() {
     if (child->type()->kind() == TypeKind::VARCHAR && lowered_.stringColumns.count(name)) {
       // compared with =, <>, IN: the base strings become value ids of the operator's dictionary (one lookup per BASE
       // value: a dictionary-encoded column costs nothing per row and keeps its indices / nulls as they are)
-      const auto* base = static_cast<const FlatVector<std::string>*>(decode(child).base);
+      const auto* base = decode(child).base;
       std::vector<int32_t> ids(base->size());
       for (size_t i = 0; i < ids.size(); ++i) {
-        auto it = stringIds_.find(base->valueAt(i));
-        if (it == stringIds_.end()) it = stringIds_.emplace(base->valueAt(i), (int32_t)stringIds_.size()).first;
+        const std::string value = stringValueAt(base, i);
+        auto it = stringIds_.find(value);
+        if (it == stringIds_.end()) it = stringIds_.emplace(value, (int32_t)stringIds_.size()).first;
         ids[i] = it->second;
       }
       bindColumn(batch, child, &ids);

@@ -5,6 +5,9 @@
 // dictionary lookup per BASE string on the host, the per-row gather on the device) — and small batches (Velox's
 // default scan batch is ~4 k rows) are gathered there until QueryConfig::coalesceRows rows are resident; then ONE
 // vgpu_agg_add_input call runs filter + projections + grouping + accumulation over all of them.  No device allocation,
+// A VARCHAR key that arrives as StringViews (StringViewVector) is not looked up on the host at all: its 16-byte views
+// are copied as they are and the kernels read each as the integer of VectorHasher::stringAsNumber
+// (velox/exec/VectorHasher.h:324-329; strings over 7 bytes get host-assigned numbers instead).
 // no pageable copy and no stream synchronisation per batch; data errors (sum overflow, checked arithmetic) are
 // collected every QueryConfig::errorCheckEvery launches and at noMoreInput.
 // After noMoreInput: vgpu_agg_extract, then output batches of preferredOutputBatchRows groups.
@@ -13,6 +16,7 @@
 // Not restated: abandoning partial aggregation (:350-366), spilling, sorted / distinct aggregates.
 #include <chrono>
 #include <cmath>
+#include <limits>
 #include <unordered_map>
 
 #include "GpuDevice.h"
@@ -31,7 +35,26 @@ struct KeyInfo {
   int bits = 0;
   std::vector<std::string> strings;                 // id -> string
   std::unordered_map<std::string, int32_t> idOf;
+  // VARCHAR key carried as numbers instead of ids: stringAsNumber for strings of at most 7 bytes (computed on the
+  // device from the StringViews), kLongBase + index into longStrings for longer ones (computed here)
+  bool number = false;
+  int64_t seenLo = std::numeric_limits<int64_t>::max(), seenHi = std::numeric_limits<int64_t>::min();
+  std::vector<std::string> longStrings;
+  std::unordered_map<std::string, int64_t> longId;
 };
+constexpr int64_t kLongBase = 1ll << 60;
+// What one batch's VARCHAR number key looks like: its views can travel as they are, or numbers per BASE value.
+struct NumberBatch {
+  bool views = false;
+  std::shared_ptr<FlatVector<int64_t>> numbers;
+};
+const BaseVector* flatBaseOf(const BaseVector* v) {
+  while (v->encoding() == VectorEncoding::DICTIONARY) v = static_cast<const DictionaryVector*>(v)->valueVector().get();
+  if (v->encoding() == VectorEncoding::CONSTANT) v = static_cast<const ConstantVector*>(v)->valueVector().get();
+  VB_CHECK(v->encoding() == VectorEncoding::FLAT, "VARCHAR key over an unsupported encoding");
+  return v;
+}
+int bitsFor(int64_t card) { int b = 1; while (b < 63 && (1ll << b) < card) ++b; return b; }
 struct AggInfo {
   std::string fn;
   TypePtr rawType, outType;
@@ -179,22 +202,30 @@ struct GpuHashAggregation::Impl {
     bool small = !keys.empty();
     int64_t product = 1;
     for (auto& k : keys) {
-      if (k.varchar) { k.lo = 0; k.hi = std::max<int64_t>(7, 2 * (int64_t)k.strings.size() - 1); }
+      if (k.number) { // the range seen so far, padded by its own width on both sides (numbers are >= 0)
+        const int64_t lo = k.seenLo <= k.seenHi ? k.seenLo : 0, hi = k.seenLo <= k.seenHi ? k.seenHi : 0;
+        if (hi >= kLongBase) { k.lo = 0; k.hi = std::numeric_limits<int64_t>::max() / 4; small = false; }
+        else { const int64_t span = hi - lo + 1; k.lo = std::max<int64_t>(0, lo - span); k.hi = hi + span; }
+      }
+      else if (k.varchar) { k.lo = 0; k.hi = std::max<int64_t>(7, 2 * (int64_t)k.strings.size() - 1); }
       else if (k.type->kind() == TypeKind::TINYINT) { k.lo = -128; k.hi = 127; }
       else small = false;
-      product *= cardOf(k);
-      if (product > 4096) small = false;
+      if (small) { product *= cardOf(k); if (product > 4096) small = false; }
     }
     if (small && !forceHash) mode = VGPU_AGG_ARRAY;
     std::vector<vgpu_key_spec> specs(keys.size());
     if (mode == VGPU_AGG_HASH) {
-      if (keys.size() == 1 && !keys[0].varchar) {
+      if (keys.size() == 1 && (!keys[0].varchar || keys[0].number)) {
         keys[0].bits = 64;
-        outputs[0] = castTo(outputs[0], BIGINT());
+        if (!keys[0].varchar) outputs[0] = castTo(outputs[0], BIGINT());
       } else {
         int total = 0;
         for (auto& k : keys) {
-          if (k.varchar) { k.lo = 0; k.hi = (1 << 20) - 2; k.bits = 20; }
+          if (k.number) {
+            VB_CHECK(k.hi < (1ll << 40), "a VARCHAR key with long strings next to other grouping keys needs multi-word keys (not supported)");
+            k.bits = bitsFor(cardOf(k));
+          }
+          else if (k.varchar) { k.lo = 0; k.hi = (1 << 20) - 2; k.bits = 20; }
           else {
             VB_CHECK(k.type->kind() != TypeKind::BIGINT && k.type->isInteger(), "multi-key grouping on " + k.type->toString() + " needs key statistics (not supported yet)");
             k.lo = typeLo(k.type->kind()); k.hi = typeHi(k.type->kind());
@@ -205,6 +236,8 @@ struct GpuHashAggregation::Impl {
         VB_CHECK(total <= 64, "grouping keys do not fit the 64-bit normalized key");
       }
     }
+    // a number key is read through a BIGINT operand: the column's StringViews (or host-made numbers) are bound under it
+    for (size_t i = 0; i < keys.size(); ++i) if (keys[i].number) outputs[i] = std::make_shared<FieldAccessTypedExpr>(BIGINT(), keyColumn(i));
     for (size_t i = 0; i < keys.size(); ++i) specs[i] = vgpu_key_spec{(int32_t)i, mode == VGPU_AGG_HASH ? keys[i].bits : 0, keys[i].lo, keys[i].hi};
     lowered = lowerExpressions(hasFused ? fused.filter : nullptr, outputs);
     // string comparisons need the FilterProject operator's value-id dictionary: the adapter keeps the two operators
@@ -218,33 +251,89 @@ struct GpuHashAggregation::Impl {
     check(vgpu_agg_create(&d, &agg), "vgpu_agg_create");
   }
 
-  // ARRAY mode only: a VARCHAR key outgrew its id range.  Move the groups into a table with wider ranges.
+  // A VARCHAR key outgrew the range the table was laid out for (ids past the dictionary bound, numbers outside
+  // [lo, hi]): the groups are read back, the table is rebuilt for the ranges known now — the small-domain array may
+  // become the hash table here, HashTable::decideHashMode's kArray -> kNormalizedKey / kHash step — and the groups
+  // are merged back under their re-encoded keys.
   void regrow() {
+    checkErrors();
     std::vector<int64_t> old = extractAll();
-    std::vector<int64_t> card(keys.size());
-    for (size_t i = 0; i < keys.size(); ++i) card[i] = cardOf(keys[i]);
+    const int rw = rowWords();
+    const int64_t n = (int64_t)(old.size() / rw);
+    std::vector<std::vector<int64_t>> kv;
+    std::vector<std::vector<bool>> kn;
+    decodeKeys(old.data(), n, kv, kn);
     vgpu_agg_destroy(agg); agg = nullptr;
     vgpu_program_destroy(program); program = nullptr;
     create();
-    VB_CHECK(mode == VGPU_AGG_ARRAY, "VARCHAR grouping keys outgrew the small-domain table (more than 4096 key combinations)");
-    const int rw = rowWords();
-    for (size_t g = 0; g * rw < old.size(); ++g) { // re-number the mixed-radix group ids
-      int64_t id = old[g * rw], fresh = 0, mul = 1;
-      for (size_t i = 0; i < keys.size(); ++i) { fresh += (id % card[i]) * mul; id /= card[i]; mul *= cardOf(keys[i]); }
-      old[g * rw] = fresh;
+    const int64_t nulls = nullIds();
+    for (int64_t g = 0; g < n; ++g) {
+      int64_t key = 0, flags = 0, mul = 1;
+      int shift = 0;
+      for (size_t i = 0; i < keys.size(); ++i) {
+        const auto& k = keys[i];
+        const bool isNull = kn[i][(size_t)g];
+        const int64_t v = kv[i][(size_t)g];
+        if (mode == VGPU_AGG_HASH && k.bits == 64) { key = isNull ? 0 : v; flags = isNull ? 1 : 0; continue; }
+        VB_CHECK(isNull || (v >= k.lo && v <= k.hi), "group key outside the rebuilt key range");
+        const int64_t id = isNull ? 0 : v - k.lo + nulls;
+        if (mode == VGPU_AGG_ARRAY) { key += id * mul; mul *= cardOf(k); }
+        else { key |= id << shift; shift += k.bits; }
+      }
+      old[(size_t)g * rw] = key;
+      old[(size_t)g * rw + 1] = flags;
     }
     addEmpty();
     if (!old.empty()) {
       DeviceBatch b; b.stream = stream;
       void* d = b.upload(old.data(), old.size() * 8);
-      check(vgpu_agg_merge_rows(agg, d, (int64_t)(old.size() / rw), stream), "vgpu_agg_merge_rows");
+      check(vgpu_agg_merge_rows(agg, d, n, stream), "vgpu_agg_merge_rows");
       check(vgpu_stream_sync(stream), "vgpu_stream_sync");
     }
+    ++stats.regrows;
   }
+
+  // Packed group rows -> per key: value (an id for VARCHAR id keys, a number for VARCHAR number keys) and NULL flag.
+  void decodeKeys(const int64_t* base, int64_t n, std::vector<std::vector<int64_t>>& kv, std::vector<std::vector<bool>>& kn) const {
+    const int rw = rowWords();
+    kv.assign(keys.size(), std::vector<int64_t>((size_t)n));
+    kn.assign(keys.size(), std::vector<bool>((size_t)n, false));
+    const int64_t nulls = nullIds();
+    for (int64_t g = 0; g < n; ++g) {
+      const int64_t key = base[g * rw], flags = base[g * rw + 1];
+      if (mode == VGPU_AGG_ARRAY) {
+        int64_t id = key;
+        for (size_t i = 0; i < keys.size(); ++i) {
+          const int64_t card = cardOf(keys[i]), d = id % card;
+          id /= card;
+          kn[i][(size_t)g] = nulls && d == 0;
+          kv[i][(size_t)g] = d - nulls + keys[i].lo;
+        }
+      } else if (mode == VGPU_AGG_HASH) {
+        int shift = 0;
+        for (size_t i = 0; i < keys.size(); ++i) {
+          if (keys[i].bits == 64) { kn[i][(size_t)g] = flags & 1; kv[i][(size_t)g] = key; continue; }
+          const int64_t d = (int64_t)(((uint64_t)key >> shift) & ((1ull << keys[i].bits) - 1));
+          shift += keys[i].bits;
+          kn[i][(size_t)g] = nulls && d == 0;
+          kv[i][(size_t)g] = d - nulls + keys[i].lo;
+        }
+      }
+    }
+  }
+  // name of the input column a VARCHAR key reads
+  std::string keyColumn(size_t i) const { return static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name(); }
+  // device type an input column is bound as by the coalescing path
+  int columnDeviceType(const std::string& name) const {
+    for (size_t i = 0; i < keys.size(); ++i) if (keys[i].number && keyColumn(i) == name) return VGPU_VARCHAR;
+    return deviceType(inputColumnType(name));
+  }
+  // does a key value outside [lo, hi] break the table's layout?
+  bool needsRange(const KeyInfo& k) const { return mode == VGPU_AGG_ARRAY || (mode == VGPU_AGG_HASH && k.bits != 64); }
 
   void addEmpty() {
     std::vector<vgpu_column> cols(std::max<size_t>(1, lowered.columns.size()));
-    for (size_t i = 0; i < lowered.columns.size(); ++i) cols[i].type = deviceType(inputColumnType(lowered.columns[i]));
+    for (size_t i = 0; i < lowered.columns.size(); ++i) cols[i].type = columnDeviceType(lowered.columns[i]);
     check(vgpu_agg_add_input(agg, program, cols.data(), (int32_t)lowered.columns.size(), 0, nullptr, 0, stream), "vgpu_agg_add_input");
   }
 
@@ -268,20 +357,69 @@ struct GpuHashAggregation::Impl {
   // VARCHAR key column -> ids of its base strings (new strings get the next id)
   std::vector<int32_t> idsOf(KeyInfo& k, const VectorPtr& v) {
     // the flat vector of strings at the bottom of the wrappers (no per-row work for a dictionary: one lookup per base string)
-    const BaseVector* base = v.get();
-    while (base->encoding() == VectorEncoding::DICTIONARY) base = static_cast<const DictionaryVector*>(base)->valueVector().get();
-    if (base->encoding() == VectorEncoding::CONSTANT) base = static_cast<const ConstantVector*>(base)->valueVector().get();
-    VB_CHECK(base->encoding() == VectorEncoding::FLAT, "VARCHAR key over an unsupported encoding");
-    struct { const BaseVector* base; } d{base};
-    auto strs = static_cast<const FlatVector<std::string>*>(d.base);
-    std::vector<int32_t> ids(d.base->size());
+    const BaseVector* base = flatBaseOf(v.get());
+    std::vector<int32_t> ids(base->size());
     for (size_t i = 0; i < ids.size(); ++i) {
-      if (d.base->mayHaveNulls() && !bits::isBitSet(d.base->nulls().data(), i)) { ids[i] = 0; continue; }
-      auto it = k.idOf.find(strs->valueAt(i));
-      if (it == k.idOf.end()) { it = k.idOf.emplace(strs->valueAt(i), (int32_t)k.strings.size()).first; k.strings.push_back(strs->valueAt(i)); }
+      if (base->mayHaveNulls() && !bits::isBitSet(base->nulls().data(), i)) { ids[i] = 0; continue; }
+      const std::string value = stringValueAt(base, i);
+      auto it = k.idOf.find(value);
+      if (it == k.idOf.end()) { it = k.idOf.emplace(value, (int32_t)k.strings.size()).first; k.strings.push_back(value); }
       ids[i] = it->second;
     }
     return ids;
+  }
+
+  // VARCHAR number key: looks at the batch's BASE strings once.  Views of strings of at most 7 bytes need nothing but
+  // their range (the device computes the numbers); otherwise the numbers are made here, long strings getting
+  // kLongBase + their index in the key's own list.
+  NumberBatch numbersOf(KeyInfo& k, const VectorPtr& v, bool dryRun = false) {
+    const BaseVector* base = flatBaseOf(v.get());
+    NumberBatch out;
+    int64_t lo = k.seenLo, hi = k.seenHi;
+    const uint64_t* nn = base->mayHaveNulls() ? base->nulls().data() : nullptr;
+    if (auto sv = dynamic_cast<const StringViewVector*>(base)) {
+      const StringView* views = sv->rawValues();
+      bool anyLong = false;
+      for (size_t i = 0; i < base->size() && !anyLong; ++i) {
+        if (nn && !bits::isBitSet(nn, i)) continue;
+        const uint32_t size = views[i].size();
+        if (size > 7) { anyLong = true; break; }
+        uint64_t word;
+        memcpy(&word, views[i].data(), 8); // inline bytes; zero past the end
+        const int64_t number = size == 0 ? 0 : (int64_t)((word & ((1ull << (8 * size)) - 1)) + (1ull << (8 * size)));
+        lo = std::min(lo, number); hi = std::max(hi, number);
+      }
+      out.views = !anyLong;
+    }
+    if (!out.views) {
+      if (dryRun) return out;
+      lo = k.seenLo; hi = k.seenHi;
+      out.numbers = std::make_shared<FlatVector<int64_t>>(BIGINT(), base->size());
+      for (size_t i = 0; i < base->size(); ++i) {
+        if (nn && !bits::isBitSet(nn, i)) { out.numbers->set(i, 0); continue; }
+        const std::string value = stringValueAt(base, i);
+        int64_t number = vgpu_number_of_string(value.data(), (uint32_t)value.size());
+        if (number < 0) {
+          auto it = k.longId.find(value);
+          if (it == k.longId.end()) { it = k.longId.emplace(value, kLongBase + (int64_t)k.longStrings.size()).first; k.longStrings.push_back(value); }
+          number = it->second;
+        }
+        out.numbers->set(i, number);
+        lo = std::min(lo, number); hi = std::max(hi, number);
+      }
+    }
+    if (!dryRun) { k.seenLo = lo; k.seenHi = hi; }
+    return out;
+  }
+  std::string stringOfNumber(const KeyInfo& k, int64_t number) const {
+    if (number >= kLongBase) {
+      VB_CHECK((size_t)(number - kLongBase) < k.longStrings.size(), "group key number outside the long-string list");
+      return k.longStrings[(size_t)(number - kLongBase)];
+    }
+    char buf[8];
+    const int32_t size = vgpu_string_of_number(number, buf);
+    VB_CHECK(size >= 0, "group key is not the number of a string");
+    return std::string(buf, (size_t)size);
   }
 
   VectorPtr columnByName(const RowVectorPtr& in, const std::string& name, std::vector<VectorPtr>& keepAlive) {
@@ -332,7 +470,7 @@ struct GpuHashAggregation::Impl {
   size_t pendingBytes(int64_t cap) const {
     size_t bytes = 0;
     for (auto& name : lowered.columns) {
-      const int t = deviceType(inputColumnType(name));
+      const int t = columnDeviceType(name);
       bytes += (size_t)cap * std::max<size_t>(deviceWidth(t), 4) + bits::nwords((size_t)cap) * 8 + 1024;
     }
     return bytes + (1 << 16);
@@ -344,7 +482,7 @@ struct GpuHashAggregation::Impl {
     pending.assign(lowered.columns.size(), PendingColumn{});
     for (size_t c = 0; c < lowered.columns.size(); ++c) {
       auto& pc = pending[c];
-      pc.type = deviceType(inputColumnType(lowered.columns[c]));
+      pc.type = columnDeviceType(lowered.columns[c]);
       pc.width = deviceWidth(pc.type);
       pc.dValues = (char*)staging->reserve((size_t)pendingCap * pc.width);
       pc.hValues = (char*)staging->mirror(pc.dValues);
@@ -395,7 +533,10 @@ struct GpuHashAggregation::Impl {
       else if (pc.hostFrom < 0) pc.hostFrom = pendingRows;
       const uint64_t* rowNulls = nullptr;
       std::vector<uint64_t> merged;
-      if (varcharKeyOf[c] >= 0) {
+      if (varcharKeyOf[c] >= 0 && keys[(size_t)varcharKeyOf[c]].number) { // flat StringViews, as they are (addBatch checked)
+        if (small) memcpy(hdst, rawValuesOf(v.get()), n * pc.width); else staging->copyIn(dst, rawValuesOf(v.get()), n * pc.width, owner);
+        if (v->mayHaveNulls()) rowNulls = v->nulls().data();
+      } else if (varcharKeyOf[c] >= 0) {
         const auto& ids = keyIds[varcharKeyOf[c]]; // id per BASE string of this batch
         if (v->encoding() == VectorEncoding::FLAT) { // one id per row already
           if (small) memcpy(hdst, ids.data(), n * 4); else staging->copyIn(dst, ids.data(), n * 4);
@@ -462,31 +603,47 @@ struct GpuHashAggregation::Impl {
     ++stats.inputVectors;
     stats.inputRows += (int64_t)in->size();
     std::vector<std::vector<int32_t>> keyIds(keys.size());
+    std::vector<NumberBatch> keyNumbers(keys.size());
     std::vector<VectorPtr> keyVecs(keys.size());
-    bool grew = false;
+    bool grew = false, direct = false;
     for (size_t i = 0; i < keys.size(); ++i) {
-      if (!keys[i].varchar) continue;
-      auto fa = static_cast<const FieldAccessTypedExpr*>(outputs[i].get());
-      keyVecs[i] = in->childAt(inputType->getChildIdx(fa->name()));
-      keyIds[i] = idsOf(keys[i], keyVecs[i]);
-      if (agg && (int64_t)keys[i].strings.size() - 1 > keys[i].hi) grew = true;
+      auto& k = keys[i];
+      if (!k.varchar) continue;
+      keyVecs[i] = in->childAt(inputType->getChildIdx(keyColumn(i)));
+      if (!agg && !sawInput && ctx->queryConfig.stringViewKeys) {
+        // first batch: StringViews of short strings make this a number key — on its own, or next to other keys when
+        // its range is small enough to pack
+        const NumberBatch probe = numbersOf(k, keyVecs[i], /*dryRun=*/true);
+        if (probe.views) {
+          KeyInfo tmp = k;
+          numbersOf(tmp, keyVecs[i]);
+          k.number = keys.size() == 1 || tmp.seenLo > tmp.seenHi || tmp.seenHi - tmp.seenLo < 65536;
+        }
+      }
+      if (k.number) {
+        keyNumbers[i] = numbersOf(k, keyVecs[i]);
+        if (!(keyNumbers[i].views && keyVecs[i]->encoding() == VectorEncoding::FLAT)) direct = true;
+        if (agg && needsRange(k) && k.seenLo <= k.seenHi && (k.seenLo < k.lo || k.seenHi > k.hi)) grew = true;
+      } else {
+        keyIds[i] = idsOf(k, keyVecs[i]);
+        if (agg && needsRange(k) && (int64_t)k.strings.size() - 1 > k.hi) grew = true;
+      }
     }
     if (!staging) staging.reset(new Staging(stream));
     if (!agg) { create(); }
     else if (grew) {
-      flushPending(); // rows gathered so far carry ids of the old range
-      if (mode == VGPU_AGG_ARRAY) regrow();
-      else throw VeloxRuntimeError("more than 2^20 distinct strings in a grouping key");
+      flushPending(); // rows gathered so far carry keys of the old layout
+      regrow();
     }
     std::vector<VectorPtr> keepAlive;
     std::vector<VectorPtr> vecs(lowered.columns.size());
     std::vector<int> varcharKeyOf(lowered.columns.size(), -1);
     for (size_t c = 0; c < lowered.columns.size(); ++c) {
       const auto& name = lowered.columns[c];
-      for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name() == name) varcharKeyOf[c] = (int)i;
+      for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && keyColumn(i) == name) varcharKeyOf[c] = (int)i;
       vecs[c] = varcharKeyOf[c] >= 0 ? keyVecs[varcharKeyOf[c]] : columnByName(in, name, keepAlive);
     }
-    if (keepAlive.empty() && canCoalesce(in, vecs)) {
+    if (keepAlive.empty() && !direct && canCoalesce(in, vecs)) {
       appendPending(in, vecs, varcharKeyOf, keyIds);
     } else {
       // other encodings (dictionary / constant wrappers over numbers, booleans): this batch alone, through a slot of its own
@@ -498,7 +655,12 @@ struct GpuHashAggregation::Impl {
       batch.stream = stream;
       batch.staging = staging.get();
       for (size_t c = 0; c < vecs.size(); ++c) {
-        if (varcharKeyOf[c] >= 0) bindColumn(batch, vecs[c], &keyIds[varcharKeyOf[c]]);
+        const int ki = varcharKeyOf[c];
+        if (ki >= 0 && keys[(size_t)ki].number) {
+          if (keyNumbers[(size_t)ki].views) bindColumn(batch, vecs[c], nullptr, nullptr, /*stringViews=*/true);
+          else bindColumn(batch, vecs[c], nullptr, keyNumbers[(size_t)ki].numbers.get());
+        }
+        else if (ki >= 0) bindColumn(batch, vecs[c], &keyIds[(size_t)ki]);
         else bindColumn(batch, vecs[c]);
       }
       launch(batch, (int64_t)in->size());
@@ -604,34 +766,14 @@ RowVectorPtr GpuHashAggregation::getOutput() {
   const int64_t* base = m.rows.data() + m.cursor * rw;
   std::vector<VectorPtr> children;
   // ---- grouping keys (normalized key -> values; NULL is a key value of its own, GroupingSet.cpp:240-307)
-  std::vector<std::vector<int64_t>> kv(m.keys.size(), std::vector<int64_t>((size_t)n));
-  std::vector<std::vector<bool>> kn(m.keys.size(), std::vector<bool>((size_t)n, false));
-  const int64_t nullIds = m.nullIds();
-  for (int64_t g = 0; g < n; ++g) {
-    const int64_t key = base[g * rw], flags = base[g * rw + 1];
-    if (m.mode == VGPU_AGG_ARRAY) {
-      int64_t id = key;
-      for (size_t i = 0; i < m.keys.size(); ++i) {
-        const int64_t card = m.cardOf(m.keys[i]), d = id % card;
-        id /= card;
-        kn[i][g] = nullIds && d == 0;
-        kv[i][g] = d - nullIds + m.keys[i].lo;
-      }
-    } else if (m.mode == VGPU_AGG_HASH) {
-      int shift = 0;
-      for (size_t i = 0; i < m.keys.size(); ++i) {
-        if (m.keys[i].bits == 64) { kn[i][g] = flags & 1; kv[i][g] = key; continue; }
-        const int64_t d = (int64_t)(((uint64_t)key >> shift) & ((1ull << m.keys[i].bits) - 1));
-        shift += m.keys[i].bits;
-        kn[i][g] = nullIds && d == 0;
-        kv[i][g] = d - nullIds + m.keys[i].lo;
-      }
-    }
-  }
+  std::vector<std::vector<int64_t>> kv;
+  std::vector<std::vector<bool>> kn;
+  m.decodeKeys(base, n, kv, kn);
   for (size_t i = 0; i < m.keys.size(); ++i) {
     const auto& k = m.keys[i];
     VectorPtr v;
-    if (k.varchar) { auto f = flatOf<std::string>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) if (!kn[i][g]) { VB_CHECK(kv[i][g] >= 0 && (size_t)kv[i][g] < k.strings.size(), "group key id outside the VARCHAR dictionary"); f->set(g, k.strings[(size_t)kv[i][g]]); } v = f; }
+    if (k.number) { auto f = flatOf<std::string>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) if (!kn[i][g]) f->set(g, m.stringOfNumber(k, kv[i][g])); v = f; }
+    else if (k.varchar) { auto f = flatOf<std::string>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) if (!kn[i][g]) { VB_CHECK(kv[i][g] >= 0 && (size_t)kv[i][g] < k.strings.size(), "group key id outside the VARCHAR dictionary"); f->set(g, k.strings[(size_t)kv[i][g]]); } v = f; }
     else if (k.type->kind() == TypeKind::BIGINT) { auto f = flatOf<int64_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, kv[i][g]); v = f; }
     else if (k.type->kind() == TypeKind::INTEGER) { auto f = flatOf<int32_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int32_t)kv[i][g]); v = f; }
     else if (k.type->kind() == TypeKind::SMALLINT) { auto f = flatOf<int16_t>(k.type, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (int16_t)kv[i][g]); v = f; }

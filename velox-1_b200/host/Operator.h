@@ -21,6 +21,7 @@ struct QueryConfig {
   int32_t preferredOutputBatchRows = 1024; // velox/core/QueryConfig.h kPreferredOutputBatchRows ("preferred_output_batch_rows")
   // GPU knobs (the reference's QueryConfig is a string map; these would be its "gpu."-prefixed keys)
   int32_t device = 0;                      // gpu.device: CUDA device of this driver (one driver = one GPU stream)
+  bool stringViewKeys = true;              // gpu.string_view_keys: VARCHAR keys that arrive as StringViews are mapped to numbers on the device
   int64_t coalesceRows = 1 << 20;          // gpu.coalesce_rows: host batches are gathered on the device until this many rows before a kernel runs
   int32_t errorCheckEvery = 16;            // gpu.error_check_every: device launches between two data-error checks (plus one at noMoreInput)
   int64_t maxPartialAggregationMemory = 1ll << 34; // max_partial_aggregation_memory (device bytes of logged partial groups before a flush)

@@ -163,6 +163,48 @@ class FlatVector : public BaseVector {
   Buffer<T> values_;
 };
 
+// velox/type/StringView.h: 16 bytes — the size, the first 4 bytes, then the rest of a string of at most 12 bytes inline or
+// a pointer to the whole string.  The bytes after a short string are zero.
+struct StringView {
+  static constexpr uint32_t kInlineSize = 12;
+  StringView() { memset(this, 0, sizeof(*this)); }
+  StringView(const char* data, size_t size) {
+    memset(this, 0, sizeof(*this));
+    size_ = (uint32_t)size;
+    if (size <= kInlineSize) { if (size) memcpy(prefix_, data, size); } // prefix_ and value_.inlined are contiguous
+    else { memcpy(prefix_, data, 4); value_.data = data; }
+  }
+  uint32_t size() const { return size_; }
+  bool isInline() const { return size_ <= kInlineSize; }
+  const char* data() const { return isInline() ? prefix_ : value_.data; }
+  std::string str() const { return std::string(data(), size_); }
+ private:
+  uint32_t size_;
+  char prefix_[4];
+  union { char inlined[8]; const char* data; } value_;
+};
+static_assert(sizeof(StringView) == 16, "StringView layout");
+
+// FlatVector<StringView> of the reference: the views plus the buffers that own the bytes of the long strings.  This is
+// the form a scan hands VARCHAR columns over in; FlatVector<std::string> is the test-friendly form of the same thing.
+class StringViewVector : public BaseVector {
+ public:
+  explicit StringViewVector(const std::vector<std::string>& strings) : BaseVector(VARCHAR(), VectorEncoding::FLAT, strings.size()), values_(strings.size()) {
+    for (size_t i = 0; i < strings.size(); ++i) set(i, strings[i]);
+  }
+  StringViewVector(TypePtr type, size_t size) : BaseVector(std::move(type), VectorEncoding::FLAT, size), values_(size) {}
+  const StringView* rawValues() const { return values_.data(); }
+  const StringView& valueAt(size_t i) const { return values_[i]; }
+  void set(size_t i, const std::string& s) {
+    if (s.size() <= StringView::kInlineSize) { values_[i] = StringView(s.data(), s.size()); return; }
+    stringBuffers_.push_back(std::make_shared<std::string>(s));
+    values_[i] = StringView(stringBuffers_.back()->data(), s.size());
+  }
+ private:
+  Buffer<StringView> values_;
+  std::vector<std::shared_ptr<std::string>> stringBuffers_;
+};
+
 // BOOLEAN flat vectors are bit-packed like the reference's FlatVector<bool>.
 class BoolVector : public BaseVector {
  public:
@@ -216,6 +258,12 @@ class RowVector : public BaseVector {
   std::vector<VectorPtr> children_;
 };
 using RowVectorPtr = std::shared_ptr<RowVector>;
+
+// Value i of a FLAT VARCHAR vector of either form.
+inline std::string stringValueAt(const BaseVector* flat, size_t i) {
+  if (auto sv = dynamic_cast<const StringViewVector*>(flat)) return sv->valueAt(i).str();
+  return static_cast<const FlatVector<std::string>*>(flat)->valueAt(i);
+}
 
 // ---- small builders (velox/vector/tests/utils/VectorMaker.h analogue) ---------------------------
 template <typename T>
