@@ -10,6 +10,6 @@ cat gpurun_out/${TAG}_kbench.jsonl; tail -5 gpurun_out/${TAG}_kbench.err
 if [ -n "$NCU" ]; then
   CMD="python tools/kbench.py --only $NCU --iters 2 --warmup 1"
   $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_${NCU}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
+  ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_${NCU}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
   python tools/launch_summary.py gpurun_out/${TAG}_${NCU}_launches.csv | tail -40
 fi

@@ -16,6 +16,14 @@ def main(path):
             unit = r.get("Metric Unit", "ns")
             ms = v * {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "nsecond": 1e-6, "ms": 1.0, "msecond": 1.0}.get(unit, 1e-6)
             rows.append((r["Kernel Name"].split("(")[0], ms))
+    inst = {}
+    with open(path, newline="") as f:
+        for r in csv.DictReader([l for l in f if not l.startswith("==")]):
+            if r.get("Metric Name") == "smsp__inst_executed.sum":
+                k = r["Kernel Name"].split("(")[0]
+                a = inst.setdefault(k, [0, 0.0])
+                a[0] += 1
+                a[1] += float(r["Metric Value"].replace(",", ""))
     agg = OrderedDict()
     for k, ms in rows:
         a = agg.setdefault(k, [0, 0.0])
@@ -25,6 +33,8 @@ def main(path):
     for k, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print(f"{ms:10.4f} ms  {100 * ms / total:5.1f} %  x{n:<4d} avg {ms / n:8.4f} ms  {k}")
     print(f"{total:10.4f} ms total over {len(rows)} launches")
+    for k, (n, v) in inst.items():
+        print(f"warp instructions per launch: {v / n:14.0f}  {k}")
 
 
 if __name__ == "__main__":

@@ -442,7 +442,8 @@ struct Gen {
   void gen_input_prefetch() {
     if (p.in_rows) return;
     static const int dist = getenv("VGPU_PREFETCH_DIST") ? std::max(1, atoi(getenv("VGPU_PREFETCH_DIST"))) : 1; // blocks ahead (tuning aid)
-    out("    if (blk + %d * nwarps < n_full) {\n", dist);
+    const std::string ahead = p.mode == kSinkLog ? "(blk + " + std::to_string(dist) + ")" : "(blk + " + std::to_string(dist) + " * nwarps)";
+    out("    if (%s < n_full) {\n", ahead.c_str());
     for (int c = 0; c < p.n_cols; ++c) {
       if (!col_used[c]) continue;
       const DevCol& d = p.cols[c];
@@ -450,8 +451,8 @@ struct Gen {
       const bool dict = d.encoding == VGPU_DICTIONARY;
       const int w = dict ? 4 : (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) ? 8 : (d.type == VGPU_INTEGER || d.type == VGPU_REAL) ? 4 : 0;
       if (!w) continue;
-      out("      if (lane < %d) prefetch_l2(reinterpret_cast<const char*>(p.%s[%d]) + (blk + %d * nwarps) * %d + lane * 128);\n",
-          w, dict ? "indices" : "values", c, dist, 128 * w);
+      out("      if (lane < %d) prefetch_l2(reinterpret_cast<const char*>(p.%s[%d]) + %s * %d + lane * 128);\n",
+          w, dict ? "indices" : "values", c, ahead.c_str(), 128 * w);
     }
     out("    }\n");
   }
@@ -470,12 +471,12 @@ struct Gen {
       out("      X%d[j] = x%d; L%d[j] = l%d;\n", c, c, c, c);
     }
     out("      KEY[j] = key; KN[j] = knull; PASS[j] = pass;\n");
-    if (p.mode == kSinkLog && p.sorted_probe) {
-      // the batch's last row is the "row before" of the next batch's first one
-      out("      if (%s == n - 1) { p.sort_prev_out[0] = key; p.sort_prev_out[1] = 1ull; }\n", row_of_j().c_str());
-    }
     gen_raise();
     out("    }\n");
+    if (p.mode == kSinkLog && p.sorted_probe) {
+      // the batch's last row is the "row before" of the next batch's first one (one warp of the grid gets here)
+      out("    if (blk == n_blocks - 1) {\n      _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) if (%s == n - 1) { p.sort_prev_out[0] = KEY[j]; p.sort_prev_out[1] = 1ull; }\n    }\n", row_of_j().c_str());
+    }
   }
 
   // Run aggregation before any group state is touched.  Equal keys tend to arrive together (sorted or
@@ -566,100 +567,290 @@ struct Gen {
   // the back; when the whole input turns out to be sorted by key, the front entries are complete groups and only
   // the back entries need deduplication (hashagg.cu).  NULL keys and the key equal to the empty marker are rare and
   // go to two dedicated rows with atomics.
+  // ---- LOG sink: run aggregation + entry log ------------------------------------------------------------------
+  // A warp walks a CONTIGUOUS range of 128-row blocks.  Inside a block, runs of equal keys are folded in the thread
+  // (4 consecutive rows), then across lanes (one segmented scan); the block's LAST run is not logged but stays open and
+  // enters the next block as "the row before lane 0's first row", so a run is logged once, where it ends, however
+  // many blocks it covers.  What is left to deduplicate for a clustered input are the runs at the two ends of each
+  // warp's range.  Plans whose keys and accumulator inputs are plain flat columns (owned_runs_ok) settle most of
+  // those in the kernel as well: the warp reads on past its range, up to 31 rows, and finishes its open run; the
+  // next warp applies the same test to its own first rows (they continue the row before them and the run is shorter
+  // than 32 rows) and drops them.  Both sides evaluate the rule on the same rows, so it holds for unsorted inputs too
+  // (where every entry is deduplicated anyway).  Longer runs and the ends of a batch stay "edge" (back) entries.
+  bool owned_runs_ok() const {
+    static const bool off = getenv("VGPU_OWNED_RUNS") && getenv("VGPU_OWNED_RUNS")[0] == '0'; // tuning aid
+    if (off || !p.sorted_probe) return false;
+    for (int i = 0; i < n_live; ++i) {
+      const DevCell& cell = p.cells[live_cells[i]];
+      if (cell.input < 0) continue;
+      const vgpu_operand& o = p.outputs[cell.input];
+      if (o.kind != VGPU_OPND_COL || o.type == VGPU_BOOLEAN) return false;
+      const DevCol& d = p.cols[o.index];
+      if (d.encoding != VGPU_FLAT || d.type == VGPU_BOOLEAN || d.type == VGPU_VARCHAR) return false;
+    }
+    return true;
+  }
+  std::string row_load(int c, const char* r) const {
+    const DevCol& d = p.cols[c];
+    char buf[256];
+    if (d.type == VGPU_REAL) snprintf(buf, sizeof buf, "d2u((double)__ldg(reinterpret_cast<const float*>(p.values[%d]) + %s))", c, r);
+    else if (d.type == VGPU_BIGINT || d.type == VGPU_DOUBLE) snprintf(buf, sizeof buf, "__ldg(reinterpret_cast<const u64*>(p.values[%d]) + %s)", c, r);
+    else snprintf(buf, sizeof buf, "(u64)(i64)__ldg(reinterpret_cast<const %s*>(p.values[%d]) + %s)", d.type == VGPU_TINYINT ? "signed char" : d.type == VGPU_SMALLINT ? "short" : "int", c, r);
+    return buf;
+  }
+  int log_kind(int c) const { return p.cells[c].kind; }
+
+  // Kernel prologue: the warp's block range and its open run.
+  void gen_log_prologue() {
+    out("  const i64 per = (n_blocks + nwarps - 1) / nwarps;\n");
+    out("  const i64 blk_begin = wid * per < n_blocks ? wid * per : n_blocks;\n");
+    out("  const i64 blk_end = blk_begin + per < n_blocks ? blk_begin + per : n_blocks;\n");
+    out("  u64 ck = 0ull; bool cn = false, chave = false, cedge = false; // the open run: key, is-null, exists, is an edge run\n");
+    for (int i = 0; i < n_live; ++i) out("  u64 cv%d = cell_identity<%d>();\n", live_cells[i], log_kind(live_cells[i]));
+  }
+
+  // Stores one entry (key SKx, values SVx<c>) at offset OFFx of the CTA's region.
+  void gen_log_store(const char* cond, const char* off, const char* key, const char* vsuffix) {
+    const int EW = p.log_entry_words;
+    out("      if (%s) {\n        u64* e = region + (u64)%s * %d;\n", cond, off, EW);
+    if (EW == 2) {
+      const int c = p.log_cells[0];
+      out("        *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(%s, SV%d%s);\n", key, p.cells[c].skip ? 0 : c, vsuffix);
+    } else {
+      out("        e[0] = %s;\n", key);
+      for (int i = 0; i < p.log_n_cells; ++i) {
+        const int c = p.log_cells[i];
+        out("        e[%d] = SV%d%s;\n", 1 + i, p.cells[c].skip ? 0 : c, vsuffix);
+      }
+      for (int w = 1 + p.log_n_cells; w < EW; ++w) out("        e[%d] = 0ull;\n", w);
+    }
+    out("      }\n");
+  }
+  // The two dedicated groups (NULL key, the key equal to the empty marker) are updated in place.
+  void gen_log_special(const char* cond, const char* isnull, const char* vsuffix) {
+    out("      if (%s) {\n", cond);
+    out("        u64* sp = p.log_special + (%s ? 0 : %d);\n        sp[0] = 1ull;\n", isnull, 1 + p.log_n_cells);
+    for (int i = 0; i < p.log_n_cells; ++i) {
+      const int c = p.log_cells[i];
+      out("        hbm_update<%d>(sp + %d, SV%d%s, accerr);\n", log_kind(c), 1 + i, p.cells[c].skip ? 0 : c, vsuffix);
+    }
+    out("      }\n");
+  }
+
   void gen_log_body(bool full) {
     gen_keyed_rows(full);
-    const int EW = p.log_entry_words;
+    const bool own = owned_runs_ok();
+    out("    const bool first_iter = blk == blk_begin;\n");
     if (p.sorted_probe) {
-      // adjacent rows must be in non-decreasing (unsigned) key order: inside the thread, lane to lane, and against the row
-      // before the block (the previous batch's last row for block 0)
-      out("    {\n");
+      // adjacent rows must be in non-decreasing (unsigned) key order: inside the thread, lane to lane, and against the
+      // row before the block (the open run's key; for the warp's first block the row itself, or the previous batch's last)
+      out("    u64 before = ck; bool have_before = chave;\n");
+      out("    if (first_iter && lane == 0) {\n");
+      out("      if (blk > 0) { before = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + (blk * 128 - 1)); have_before = true; }\n", p.sorted_key_col);
+      out("      else { before = p.sort_prev_in[0]; have_before = p.sort_prev_in[1] != 0ull; }\n");
+      out("    }\n    {\n");
       if (full) out("      const bool ok0 = true, ok1 = true, ok2 = true, ok3 = true;\n");
       else out("      const bool ok0 = r0 < n, ok1 = r0 + 1 < n, ok2 = r0 + 2 < n, ok3 = r0 + 3 < n;\n");
       out("      bool bad = (ok1 && KEY[0] > KEY[1]) || (ok2 && KEY[1] > KEY[2]) || (ok3 && KEY[2] > KEY[3]);\n");
       out("      const u64 pk = __shfl_up_sync(0xffffffffu, KEY[3], 1);\n");
-      out("      u64 before = 0ull; bool have = false;\n");
-      out("      if (lane == 0) {\n");
-      out("        if (blk > 0) { before = __ldg(reinterpret_cast<const u64*>(p.values[%d]) + (blk * 128 - 1)); have = true; }\n", p.sorted_key_col);
-      out("        else { before = p.sort_prev_in[0]; have = p.sort_prev_in[1] != 0ull; }\n");
-      out("      }\n");
-      out("      bad = bad || (ok0 && (lane > 0 ? pk > KEY[0] : (have && before > KEY[0])));\n");
+      out("      bad = bad || (ok0 && (lane > 0 ? pk > KEY[0] : (have_before && before > KEY[0])));\n");
       out("      viol = viol || bad;\n    }\n");
     }
-    // Run aggregation over the thread's 4 consecutive rows, then across lanes.  r<c> is the running fold of the run
-    // that is open at row j; the run that ENDS at row j (the next passing row starts another one, or j is the
-    // thread's last row) leaves its key and value in slot j.  Slot 3 is the thread's tail run: it may continue in the
-    // next lane.  The thread's first run (its "head") may continue the previous lane's tail.
-    out("    u64 SK[4]; bool SN[4], SA[4];\n");
-    for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4];\n", live_cells[i]);
-    out("    u64 lastk = 0ull, firstk = 0ull; bool lastn = false, firstn = false, have = false;\n");
-    for (int i = 0; i < n_live; ++i) out("    u64 rf%d = cell_identity<%d>();\n", live_cells[i], p.cells[live_cells[i]].kind);
+    // Thread-local fold.  rf<c> is the running fold of the run that is open at row j; the run that ENDS before row j
+    // leaves its key and value in slot j - 1 (slot "4" for the run handed over by the previous block, which can only end
+    // in lane 0).  Slot 3 is the thread's tail run: it may continue in the next lane.
+    out("    u64 SK[4]; bool SN[4], SA[4];\n    u64 SK4 = 0ull; bool SN4 = false, SA4 = false;\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 SV%d[4], SV%d_4 = 0ull;\n", live_cells[i], live_cells[i]);
+    out("    const bool cin = chave && lane == 0;\n");
+    out("    u64 lastk = ck, firstk = 0ull; bool lastn = cn, firstn = false, have = cin;\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 rf%d = cin ? cv%d : cell_identity<%d>();\n", live_cells[i], live_cells[i], log_kind(live_cells[i]));
     out("    _Pragma(\"unroll\") for (int j = 0; j < 4; ++j) {\n");
     out("      const bool start = PASS[j] && !(have && lastk == KEY[j] && lastn == KN[j]);\n");
-    out("      if (j > 0) { SK[j - 1] = lastk; SN[j - 1] = lastn; SA[j - 1] = start && have;\n");
+    out("      if (j == 0) { SK4 = lastk; SN4 = lastn; SA4 = start && have;\n");
+    for (int i = 0; i < n_live; ++i) out("        SV%d_4 = rf%d;\n", live_cells[i], live_cells[i]);
+    out("      } else { SK[j - 1] = lastk; SN[j - 1] = lastn; SA[j - 1] = start && have;\n");
     for (int i = 0; i < n_live; ++i) out("        SV%d[j - 1] = rf%d;\n", live_cells[i], live_cells[i]);
     out("      }\n");
     out("      if (PASS[j] && !have) { firstk = KEY[j]; firstn = KN[j]; }\n");
     for (int i = 0; i < n_live; ++i) {
       const int c = live_cells[i];
-      const int kind = p.cells[c].kind;
-      out("      { const u64 v = L%d[j] ? X%d[j] : cell_identity<%d>(); rf%d = start ? v : cell_comb<%d>(rf%d, v, accerr); }\n", c, c, kind, c, kind, c);
+      out("      { const u64 v = L%d[j] ? X%d[j] : cell_identity<%d>(); rf%d = start ? v : cell_comb<%d>(rf%d, v, accerr); }\n", c, c, log_kind(c), c, log_kind(c), c);
     }
     out("      if (PASS[j]) { lastk = KEY[j]; lastn = KN[j]; have = true; }\n");
     out("    }\n");
     out("    SK[3] = lastk; SN[3] = lastn;\n");
-    out("    const bool hasT = have, single = have && !(SA[0] || SA[1] || SA[2]);\n");
+    out("    const bool hasT = have, single = have && !(SA4 || SA[0] || SA[1] || SA[2]);\n");
     out("    const u64 ptk = __shfl_up_sync(0xffffffffu, lastk, 1);\n");
     out("    const u32 pfl = __shfl_up_sync(0xffffffffu, (u32)hasT | ((u32)lastn << 1), 1);\n");
     out("    const bool link = lane > 0 && hasT && (pfl & 1u) && ptk == firstk && (bool)((pfl >> 1) & 1u) == firstn;\n");
     out("    bool f = !(link && single); // the carry flows through this lane's tail only when the tail is its only run\n");
     for (int i = 0; i < n_live; ++i) out("    u64 t%d = rf%d;\n", live_cells[i], live_cells[i]);
+    // (runs are short in practice: the scan stops as soon as no lane waits for a carry from further up)
     out("    _Pragma(\"unroll\") for (int d = 1; d < 32; d <<= 1) {\n");
+    out("      if (__all_sync(0xffffffffu, f)) break;\n");
     for (int i = 0; i < n_live; ++i) out("      const u64 u%d = __shfl_up_sync(0xffffffffu, t%d, d);\n", live_cells[i], live_cells[i]);
     out("      const bool uf = __shfl_up_sync(0xffffffffu, (u32)f, d) != 0u;\n");
-    out("      if (lane >= d && !f) {\n");
-    for (int i = 0; i < n_live; ++i) out("        t%d = cell_comb<%d>(u%d, t%d, accerr);\n", live_cells[i], p.cells[live_cells[i]].kind, live_cells[i], live_cells[i]);
-    out("        f = uf;\n      }\n    }\n");
+    out("      const bool take = lane >= d && !f;\n");
+    for (int i = 0; i < n_live; ++i) out("      t%d = take ? cell_comb<%d>(u%d, t%d, accerr) : t%d;\n", live_cells[i], log_kind(live_cells[i]), live_cells[i], live_cells[i], live_cells[i]);
+    out("      f = take ? uf : f;\n    }\n");
     // the head of a lane with several runs takes the previous lane's (scanned) tail
     for (int i = 0; i < n_live; ++i) {
       const int c = live_cells[i];
       out("    { const u64 carry = __shfl_up_sync(0xffffffffu, t%d, 1);\n", c);
       out("      if (link && !single) { if (SA[0]) SV%d[0] = cell_comb<%d>(carry, SV%d[0], accerr); else if (SA[1]) SV%d[1] = cell_comb<%d>(carry, SV%d[1], accerr); else SV%d[2] = cell_comb<%d>(carry, SV%d[2], accerr); } }\n",
-          c, p.cells[c].kind, c, c, p.cells[c].kind, c, c, p.cells[c].kind, c);
+          c, log_kind(c), c, c, log_kind(c), c, c, log_kind(c), c);
       out("    SV%d[3] = t%d;\n", c, c);
     }
     out("    const bool next_link = __shfl_down_sync(0xffffffffu, (u32)link, 1) != 0u && lane < 31;\n");
     out("    SA[3] = hasT && !next_link;\n");
-    out("    u32 KIND[4];\n");
-    if (p.sorted_probe && full) out("    const u64 KF = __shfl_sync(0xffffffffu, KEY[0], 0), KL = __shfl_sync(0xffffffffu, KEY[3], 31);\n");
-    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n");
-    out("      const bool special = SN[sgm] || SK[sgm] == VGF_EMPTY_KEY;\n");
-    if (p.sorted_probe && full) out("      const bool edge = SK[sgm] == KF || SK[sgm] == KL; // the run may continue in a neighbouring block\n");
-    else if (p.sorted_probe) out("      const bool edge = true;\n");
-    else out("      const bool edge = false;\n");
-    out("      KIND[sgm] = !SA[sgm] || special ? 0u : (edge ? 2u : 1u);\n");
-    out("      if (SA[sgm] && special) {\n");
-    out("        u64* sp = p.log_special + (SN[sgm] ? 0 : %d);\n        sp[0] = 1ull;\n", 1 + p.log_n_cells);
-    for (int i = 0; i < p.log_n_cells; ++i) {
-      const int c = p.log_cells[i];
-      const int src = p.cells[c].skip ? 0 : c;
-      out("        hbm_update<%d>(sp + %d, SV%d[sgm], accerr);\n", p.cells[c].kind, 1 + i, src);
-    }
-    out("      }\n    }\n");
-    out("    u32 IDX[4]; log_reserve(logcur, KIND, IDX);\n");
-    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (KIND[sgm] == 0u) continue;\n");
-    out("      u64* e = KIND[sgm] == 1u ? region + (u64)IDX[sgm] * %d : region_end - ((u64)IDX[sgm] + 1ull) * %d;\n", EW, EW);
-    if (EW == 2) {
-      const int c = p.log_cells[0];
-      out("      *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(SK[sgm], SV%d[sgm]);\n", p.cells[c].skip ? 0 : c);
+    // the block's last run stays open
+    out("    const u32 tm = __ballot_sync(0xffffffffu, hasT);\n");
+    out("    const int LT = 31 - __clz((int)tm); // tm == 0: no rows passed and nothing was handed over\n");
+    out("    bool nhave = tm != 0u;\n");
+    out("    const u64 nk = __shfl_sync(0xffffffffu, SK[3], LT & 31);\n");
+    out("    const bool nn = __shfl_sync(0xffffffffu, (u32)SN[3], LT & 31) != 0u;\n");
+    for (int i = 0; i < n_live; ++i) out("    const u64 nv%d = __shfl_sync(0xffffffffu, SV%d[3], LT & 31);\n", live_cells[i], live_cells[i]);
+    out("    if (lane == LT) SA[3] = false;\n");
+    // an edge run that is still open stays an edge run (same key: for a clustered input that is the same run; for any
+    // other input the entry is deduplicated anyway)
+    out("    bool nedge = cedge && nhave && nk == ck && nn == cn;\n");
+    out("    bool EDGE[4] = {false, false, false, false};\n");
+    // the warp's first block: the run of its first row may continue the previous warp's (or batch's) last run
+    out("    if (first_iter) {\n");
+    out("      const u32 pm = __ballot_sync(0xffffffffu, PASS[0] || PASS[1] || PASS[2] || PASS[3]);\n");
+    out("      const int Lf = __ffs((int)pm) - 1;\n");
+    out("      const u64 KF = __shfl_sync(0xffffffffu, firstk, Lf & 31);\n");
+    out("      const bool KFn = __shfl_sync(0xffffffffu, (u32)firstn, Lf & 31) != 0u;\n");
+    if (own) {
+      // position of the head run (the run of the block's first row): lanes 0 .. Lh-1 are that run and nothing else
+      if (full) out("      const u32 LV = 32u; const u32 nvalid = 128u;\n");
+      else out("      const u32 nvalid = (u32)(n - blk * 128); const u32 LV = (nvalid + 3u) >> 2;\n");
+      out("      const u32 chain = __ballot_sync(0xffffffffu, single && (link || lane == 0));\n");
+      out("      const u32 Lh = min(LV, (u32)__ffs((int)~chain) - 1u);\n");
+      out("      const bool whole = Lh >= LV;\n");
+      out("      const bool cont = __shfl_sync(0xffffffffu, (u32)(have_before && before == KEY[0]), 0) != 0u;\n");
+      out("      const bool link_h = __shfl_sync(0xffffffffu, (u32)link, (int)(Lh & 31u)) != 0u && Lh < 32u;\n");
+      out("      const u32 in_lane = __shfl_sync(0xffffffffu, SA[0] ? 1u : (SA[1] ? 2u : 3u), (int)(Lh & 31u));\n");
+      out("      const u32 hlen = whole ? nvalid : 4u * Lh + ((Lh == 0u || link_h) ? in_lane : 0u);\n");
+      out("      int hs = -1;\n");
+      out("      if (!whole) {\n");
+      out("        if (Lh > 0u && !link_h) { if (lane == (int)Lh - 1) hs = 3; }\n");
+      out("        else if (lane == (int)Lh) hs = SA[0] ? 0 : (SA[1] ? 1 : 2);\n");
+      out("      }\n");
+      out("      if (cont && blk > 0 && hlen < 32u) {\n");
+      out("        // the previous warp read these rows and folded them into its last run\n");
+      out("        _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) if (hs == sgm) SA[sgm] = false;\n");
+      out("        if (whole) nhave = false;\n");
+      out("      } else if (cont) {\n");
+      out("        _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) EDGE[sgm] = SK[sgm] == KF && SN[sgm] == KFn;\n");
+      out("        nedge = nedge || (nk == KF && nn == KFn);\n");
+      out("      }\n");
     } else {
-      out("      e[0] = SK[sgm];\n");
-      for (int i = 0; i < p.log_n_cells; ++i) {
-        const int c = p.log_cells[i];
-        out("      e[%d] = SV%d[sgm];\n", 1 + i, p.cells[c].skip ? 0 : c);
-      }
-      for (int w = 1 + p.log_n_cells; w < EW; ++w) out("      e[%d] = 0ull;\n", w);
+      out("      if (pm != 0u) {\n");
+      out("        _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) EDGE[sgm] = SK[sgm] == KF && SN[sgm] == KFn;\n");
+      out("        nedge = nedge || (nk == KF && nn == KFn);\n");
+      out("      }\n");
     }
     out("    }\n");
+    out("    u32 KIND[5];\n");
+    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n");
+    out("      const bool special = SN[sgm] || SK[sgm] == VGF_EMPTY_KEY;\n");
+    out("      KIND[sgm] = !SA[sgm] || special ? 0u : (EDGE[sgm] ? 2u : 1u);\n");
+    {
+      // (the special-group update of slot sgm)
+      out("      if (SA[sgm] && special) {\n");
+      out("        u64* sp = p.log_special + (SN[sgm] ? 0 : %d);\n        sp[0] = 1ull;\n", 1 + p.log_n_cells);
+      for (int i = 0; i < p.log_n_cells; ++i) {
+        const int c = p.log_cells[i];
+        out("        hbm_update<%d>(sp + %d, SV%d[sgm], accerr);\n", log_kind(c), 1 + i, p.cells[c].skip ? 0 : c);
+      }
+      out("      }\n");
+    }
+    out("    }\n");
+    out("    {\n      const bool special = SN4 || SK4 == VGF_EMPTY_KEY;\n");
+    out("      KIND[4] = !SA4 || special ? 0u : (cedge ? 2u : 1u);\n");
+    gen_log_special("SA4 && special", "SN4", "_4");
+    out("    }\n");
+    out("    u32 OFF[5]; log_reserve<5>(logcur, (u32)p.log_region_cap, KIND, OFF);\n");
+    out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (KIND[sgm] == 0u) continue;\n");
+    {
+      const int EW = p.log_entry_words;
+      out("      u64* e = region + (u64)OFF[sgm] * %d;\n", EW);
+      if (EW == 2) {
+        const int c = p.log_cells[0];
+        out("      *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(SK[sgm], SV%d[sgm]);\n", p.cells[c].skip ? 0 : c);
+      } else {
+        out("      e[0] = SK[sgm];\n");
+        for (int i = 0; i < p.log_n_cells; ++i) {
+          const int c = p.log_cells[i];
+          out("      e[%d] = SV%d[sgm];\n", 1 + i, p.cells[c].skip ? 0 : c);
+        }
+        for (int w = 1 + p.log_n_cells; w < EW; ++w) out("      e[%d] = 0ull;\n", w);
+      }
+    }
+    out("    }\n");
+    gen_log_store("KIND[4] != 0u", "OFF[4]", "SK4", "_4");
+    out("    ck = nk; cn = nn; chave = nhave; cedge = nedge;\n");
+    for (int i = 0; i < n_live; ++i) out("    cv%d = nv%d;\n", live_cells[i], live_cells[i]);
+  }
+
+  // After the warp's last block: its open run is logged.
+  void gen_log_epilogue() {
+    const bool own = owned_runs_ok();
+    out("  if (chave) { // (warp-uniform)\n");
+    out("    bool edge = true;\n");
+    if (own) {
+      // read on: the rows after the range that carry the open run's key (at most 31) belong to it; the next warp drops them
+      out("    {\n");
+      out("      const i64 r0e = blk_end * 128;\n");
+      out("      const i64 avail = n - r0e;\n");
+      out("      if (avail > 0) {\n");
+      out("        const i64 r = r0e + lane;\n");
+      out("        const bool in = lane < avail;\n");
+      out("        const u64 k = in ? __ldg(reinterpret_cast<const u64*>(p.values[%d]) + r) : 0ull;\n", p.sorted_key_col);
+      out("        const u32 eq = __ballot_sync(0xffffffffu, in && k == ck);\n");
+      out("        const u32 take = min(32u, (u32)__ffs((int)~eq) - 1u);\n");
+      out("        if (take < 32u) {\n");
+      for (int i = 0; i < n_live; ++i) out("          u64 ex%d = cell_identity<%d>();\n", live_cells[i], log_kind(live_cells[i]));
+      out("          if ((u32)lane < take) {\n");
+      out("            const bool pass = true; bool raise = false;\n");
+      bool declared[kMaxCols] = {false};
+      for (int i = 0; i < n_live; ++i) {
+        const DevCell& cell = p.cells[live_cells[i]];
+        if (cell.input < 0) continue;
+        const int c = p.outputs[cell.input].index;
+        if (declared[c]) continue;
+        declared[c] = true;
+        if (p.cols[c].nulls) out("            const V c%d = {%s, !bit1(p.nulls[%d], r), false};\n", c, row_load(c, "r").c_str(), c);
+        else out("            const V c%d = {%s, false, false};\n", c, row_load(c, "r").c_str());
+      }
+      for (int i = 0; i < n_live; ++i) {
+        const int c = live_cells[i];
+        gen_cell_input(c);
+        out("            if (l%d) ex%d = x%d;\n", c, c, c);
+      }
+      out("            (void)raise;\n          }\n");
+      out("          for (u32 d = 1; d < take; d <<= 1) {\n");
+      for (int i = 0; i < n_live; ++i) {
+        const int c = live_cells[i];
+        out("            ex%d = cell_comb<%d>(ex%d, __shfl_down_sync(0xffffffffu, ex%d, d), accerr);\n", c, log_kind(c), c, c);
+      }
+      out("          }\n");
+      for (int i = 0; i < n_live; ++i) {
+        const int c = live_cells[i];
+        out("          if (take > 0u) cv%d = cell_comb<%d>(cv%d, __shfl_sync(0xffffffffu, ex%d, 0), accerr);\n", c, log_kind(c), c, c);
+      }
+      out("          edge = cedge || (i64)take == avail; // complete, unless it began before the range or the batch ends here\n");
+      out("        }\n      }\n    }\n");
+    }
+    out("    const bool special = cn || ck == VGF_EMPTY_KEY;\n");
+    out("    u64 SK4 = ck; bool SN4 = cn;\n");
+    for (int i = 0; i < n_live; ++i) out("    u64 SV%d_4 = cv%d;\n", live_cells[i], live_cells[i]);
+    gen_log_special("lane == 0 && special", "SN4", "_4");
+    out("    u32 K1[1] = {lane == 0 && !special ? (edge ? 2u : 1u) : 0u}, O1[1];\n");
+    out("    log_reserve<1>(logcur, (u32)p.log_region_cap, K1, O1);\n");
+    gen_log_store("K1[0] != 0u", "O1[0]", "SK4", "_4");
+    out("    (void)SN4;\n  }\n");
   }
 
   void gen_fp_body(bool full) {
@@ -825,7 +1016,6 @@ struct Gen {
     if (p.mode == kSinkLog) {
       out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
       out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
-      out("  u64* const region_end = region + p.log_region_cap * %d;\n", p.log_entry_words);
       if (p.sorted_probe) out("  bool viol = false;\n");
     }
     if (p.mode == kSinkArray) {
@@ -851,7 +1041,10 @@ struct Gen {
         else out("  u64* mytab = tab;\n");
       }
     }
-    out("  for (i64 blk = wid; blk < n_blocks; blk += nwarps) {\n   if (blk < n_full) {\n");
+    if (p.mode == kSinkLog) {
+      gen_log_prologue();
+      out("  for (i64 blk = blk_begin; blk < blk_end; ++blk) {\n   if (blk < n_full) {\n");
+    } else out("  for (i64 blk = wid; blk < n_blocks; blk += nwarps) {\n   if (blk < n_full) {\n");
     if (p.mode == kSinkArray) gen_array_body(true, st, G); else if (p.mode == kSinkHash) gen_hash_body(true); else if (p.mode == kSinkLog) gen_log_body(true); else gen_fp_body(true);
     out("   } else {\n");
     if (p.mode == kSinkArray) gen_array_body(false, st, G); else if (p.mode == kSinkHash) gen_hash_body(false); else if (p.mode == kSinkLog) gen_log_body(false); else gen_fp_body(false);
@@ -879,6 +1072,7 @@ struct Gen {
       }
     }
     if (p.mode == kSinkLog) {
+      gen_log_epilogue();
       out("  __syncthreads();\n  if (threadIdx.x == 0) { p.log_counts[2 * blockIdx.x] = logcur[0]; p.log_counts[2 * blockIdx.x + 1] = logcur[1]; }\n");
       if (p.sorted_probe) out("  if (__any_sync(0xffffffffu, viol) && lane == 0) atomicOr(p.sort_state, 1ull);\n");
     }

@@ -568,31 +568,37 @@ __device__ __forceinline__ void ovf_reserve(const FusedParams& p, const bool par
 }
 
 // ---- LOG sink ---------------------------------------------------------------------------------------
-// Positions of the warp's active segments inside the CTA's log region.  kind[s]: 0 = none, 1 = front (a run that
-// cannot continue in another block), 2 = back (a run touching a block edge).  One shared-memory atomic per warp and
-// side; returns the entry index (front: counted from the region start, back: from its end).
-__device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */, const u32 kind[4], u32 idx[4]) {
-  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-  u32 mf[4], mb[4], nf = 0, nb = 0;
+// Places of the warp's active segments inside the CTA's log region.  kind[s]: 0 = none, 1 = front (a run that cannot
+// continue in another block), 2 = back (a run touching a block edge).  Front entries fill the region from its start,
+// back entries from its end; off[s] is the entry's offset from the region start.  Per-lane counts of both sides ride
+// in one word through one warp scan; one shared-memory atomic per warp and side.
+template <int N>
+__device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */, u32 cap, const u32 (&kind)[N], u32 (&off)[N]) {
+  const u32 lane = threadIdx.x & 31u;
+  u32 mine = 0;
 #pragma unroll
-  for (int s = 0; s < 4; ++s) {
-    mf[s] = __ballot_sync(0xffffffffu, kind[s] == 1u);
-    mb[s] = __ballot_sync(0xffffffffu, kind[s] == 2u);
-    nf += __popc(mf[s]);
-    nb += __popc(mb[s]);
+  for (int s = 0; s < N; ++s) mine += (kind[s] == 1u ? 1u : 0u) + (kind[s] == 2u ? 0x10000u : 0u);
+  u32 incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const u32 u = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (u32)d) incl += u;
   }
+  const u32 tot = __shfl_sync(0xffffffffu, incl, 31);
   u32 bf = 0, bb = 0;
   if (lane == 0) {
-    if (nf) bf = atomicAdd(&cur[0], nf);
-    if (nb) bb = atomicAdd(&cur[1], nb);
+    if (tot & 0xffffu) bf = atomicAdd(&cur[0], tot & 0xffffu);
+    if (tot >> 16) bb = atomicAdd(&cur[1], tot >> 16);
   }
   bf = __shfl_sync(0xffffffffu, bf, 0);
   bb = __shfl_sync(0xffffffffu, bb, 0);
+  const u32 excl = incl - mine;
+  u32 f = bf + (excl & 0xffffu), b = cap - 1u - (bb + (excl >> 16));
 #pragma unroll
-  for (int s = 0; s < 4; ++s) {
-    idx[s] = kind[s] == 1u ? bf + __popc(mf[s] & lt) : bb + __popc(mb[s] & lt);
-    bf += __popc(mf[s]);
-    bb += __popc(mb[s]);
+  for (int s = 0; s < N; ++s) {
+    off[s] = kind[s] == 1u ? f : b;
+    f += kind[s] == 1u ? 1u : 0u;
+    b -= kind[s] == 2u ? 1u : 0u;
   }
 }
 

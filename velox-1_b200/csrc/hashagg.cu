@@ -136,6 +136,7 @@ __global__ void fin_prepare_kernel(FinArgs a) {
     const unsigned long long per_part = min((unsigned long long)a.slots_max * 45 / 100, 256ull);
     int log2p = 4;
     while (log2p < a.log2p_max && (1ull << log2p) * per_part < n_dedupe) ++log2p;
+    if (n_dedupe <= (unsigned long long)a.slots_max * 45 / 100) log2p = 0; // one table holds them all
     a.hdr->log2p = (unsigned long long)log2p;
   }
   chunk_prefix_scan(a.ranges, a.n_ranges, a.chunk_prefix, kChunk, [&](const LogRange& r) { return !(sorted && r.back == kRangeFront); });
@@ -168,11 +169,11 @@ __device__ __forceinline__ void locate_chunk(const LogRange* ranges, const uint3
 
 // Walks every entry that needs deduplication: the CTAs share the chunks of all taking-part ranges.
 template <typename F>
-__device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn) {
+__device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn, uint32_t first_chunk, uint32_t chunk_stride) {
   __shared__ uint32_t s_prefix[kPrefixSmem];
   const uint32_t* prefix = stage_prefix(a.chunk_prefix, a.n_ranges, s_prefix);
   const uint32_t total = prefix[a.n_ranges];
-  for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
+  for (uint32_t chunk = first_chunk; chunk < total; chunk += chunk_stride) {
     const uint64_t* first;
     uint64_t n;
     locate_chunk(a.ranges, prefix, a.n_ranges, chunk, a.ew, first, n);
@@ -180,15 +181,20 @@ __device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn) 
   }
 }
 
+// log2p == 0 ("tiny"): so few entries that one shared-memory table holds them all — fin_aggregate_kernel reads them
+// straight from their ranges and the partitioning passes have nothing to do.  (A sorted input leaves only the runs at
+// the ends of its batches and the runs longer than a block to deduplicate.)
 __global__ void fin_hist_kernel(FinArgs a) {
   const int log2p = (int)a.hdr->log2p;
-  for_each_dedupe_entry(a, [&](const uint64_t* e) { atomicAdd(&a.hist[part_of_key(e[0], log2p)], 1u); });
+  if (log2p == 0) return;
+  for_each_dedupe_entry(a, [&](const uint64_t* e) { atomicAdd(&a.hist[part_of_key(e[0], log2p)], 1u); }, blockIdx.x, gridDim.x);
 }
 
 // Exclusive scan of hist[0..P) -> offsets[0..P], cursors = offsets.  One CTA.
 __global__ void fin_scan_kernel(FinArgs a) {
   __shared__ uint32_t warp_sum[32];
   __shared__ uint32_t carry;
+  if (a.hdr->log2p == 0ull) return;
   const int P = 1 << (int)a.hdr->log2p;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
@@ -216,6 +222,7 @@ __global__ void fin_scan_kernel(FinArgs a) {
 
 __global__ void fin_scatter_kernel(FinArgs a) {
   const int ew = a.ew, log2p = (int)a.hdr->log2p;
+  if (log2p == 0) return;
   for_each_dedupe_entry(a, [&](const uint64_t* e) {
     if (ew == 2) {
       const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(e);
@@ -228,7 +235,7 @@ __global__ void fin_scatter_kernel(FinArgs a) {
       d[0] = key;
       for (int w = 1; w < ew; ++w) d[w] = e[w];
     }
-  });
+  }, blockIdx.x, gridDim.x);
 }
 
 // Shared-memory fold of one cell (values of MIN/MAX over doubles are plain double bits here).
@@ -263,10 +270,12 @@ __global__ void fin_aggregate_kernel(FinArgs a) {
   __shared__ uint32_t s_warp[32];
   __shared__ unsigned long long s_base;
   const int ew = a.ew, nc = ew - 1, P = 1 << (int)a.hdr->log2p;
+  const bool tiny = a.hdr->log2p == 0ull;
+  if (tiny && blockIdx.x != 0) return;
   uint32_t err = 0;
   bool overflow = false;
   for (int p = blockIdx.x; p < P; p += gridDim.x) {
-    const uint32_t lo = a.offsets[p], cnt = a.offsets[p + 1] - lo;
+    const uint32_t lo = tiny ? 0u : a.offsets[p], cnt = tiny ? (uint32_t)a.hdr->n_dedupe : a.offsets[p + 1] - lo;
     if (cnt == 0) continue;
     uint32_t T = 64;
     while (T < 2 * cnt && T < (uint32_t)a.slots_max) T <<= 1;
@@ -277,9 +286,7 @@ __global__ void fin_aggregate_kernel(FinArgs a) {
       for (int c = 0; c < nc; ++c) vals[(size_t)s * nc + c] = cell_identity(a.kinds.kind[c]);
     }
     __syncthreads();
-    const uint64_t* src = a.part + (uint64_t)lo * ew;
-    for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
-      const uint64_t* e = src + (uint64_t)i * ew;
+    auto fold = [&](const uint64_t* e) {
       const uint64_t key = e[0];
       uint32_t h = (uint32_t)mix64(key) & (T - 1);
       bool placed = false;
@@ -288,8 +295,14 @@ __global__ void fin_aggregate_kernel(FinArgs a) {
         if (seen == kEmptyKey || seen == key) { placed = true; break; }
         h = (h + 1) & (T - 1);
       }
-      if (!placed) { overflow = true; continue; }
+      if (!placed) { overflow = true; return; }
       for (int c = 0; c < nc; ++c) smem_fold(a.kinds.kind[c], &vals[(size_t)h * nc + c], e[1 + c], err);
+    };
+    if (tiny) {
+      for_each_dedupe_entry(a, fold, 0u, 1u); // this CTA alone walks every chunk
+    } else {
+      const uint64_t* src = a.part + (uint64_t)lo * ew;
+      for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) fold(src + (uint64_t)i * ew);
     }
     __syncthreads();
     // compaction: thread t owns slots t, t + NT, ...
