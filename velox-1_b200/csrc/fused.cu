@@ -947,7 +947,7 @@ struct Gen {
       if (d.encoding == VGPU_DICTIONARY) need += 4;
     }
     if (p.mode == kSinkHash) need += 8 + 3 * n_live * 4;
-    if (p.mode == kSinkLog) need += 4 + 3 * n_live * 4;
+    if (p.mode == kSinkLog) need += 12 + 4 * n_live * 4; // + the open run and its slot (64 registers spill; measured: 384 x 2 beats 512 x 2 with spills)
     int acc_regs = 0, group_bytes = 0; // per thread: accumulator registers / bytes of one thread table
     for (int i = 0; i < n_live; ++i) {
       const bool cnt = p.cells[live_cells[i]].kind == kCellCount;

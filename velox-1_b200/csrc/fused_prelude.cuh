@@ -577,7 +577,7 @@ __device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */,
   const u32 lane = threadIdx.x & 31u;
   u32 mine = 0;
 #pragma unroll
-  for (int s = 0; s < N; ++s) mine += (kind[s] == 1u ? 1u : 0u) + (kind[s] == 2u ? 0x10000u : 0u);
+  for (int s = 0; s < N; ++s) mine += (kind[s] & 1u) + ((kind[s] & 2u) << 15);
   u32 incl = mine;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -596,9 +596,9 @@ __device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */,
   u32 f = bf + (excl & 0xffffu), b = cap - 1u - (bb + (excl >> 16));
 #pragma unroll
   for (int s = 0; s < N; ++s) {
-    off[s] = kind[s] == 1u ? f : b;
-    f += kind[s] == 1u ? 1u : 0u;
-    b -= kind[s] == 2u ? 1u : 0u;
+    off[s] = (kind[s] & 1u) ? f : b;
+    f += kind[s] & 1u;
+    b -= kind[s] >> 1;
   }
 }
 
