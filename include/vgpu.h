@@ -278,6 +278,23 @@ int vgpu_filter_project(vgpu_program_t program, const vgpu_column* cols, int32_t
                         uint64_t* sel_bits, int32_t* sel_idx, int64_t* num_selected,
                         const vgpu_out_column* outs, void* stream);
 
+/* The last step of vgpu_filter_project on its own, with NO allocation: selection bitmap -> ascending row numbers.
+ * (No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc — code under CUDA graph capture, tight serving loops, harnesses that forbid it.  vgpu_filter_project
+ * keeps the per-tile counts / offsets this step needs in a grow-only cudaMalloc'ed buffer; this variant keeps them in
+ * a fixed array in the library's device image instead.)
+ *   sel_bits     : in, device bitmap of nrows bits (32-bit aligned); bits past nrows are ignored.
+ *   nrows        : at most VGPU_NOALLOC_MAX_ROWS; more returns VGPU_ERR_UNSUPPORTED (split the batch).
+ *   sel_idx      : out, device int32[>= number of set bits] ascending row numbers of the set bits.
+ *   num_selected : out, device int64.
+ * Asynchronous on `stream`.  Calls no cudaMalloc, cudaFree or other allocating routine, ever.  The scratch (192 KiB) is
+ * held by every GPU that loads the library until the process exits, is shared by all calls on a device and keeps the
+ * previous call's contents (each call rewrites what it reads; nothing needs clearing): calls that may overlap on
+ * the GPU (different streams without an ordering between them) race on it and must be ordered by the caller. */
+#define VGPU_NOALLOC_MAX_ROWS (16ll * 1024 * 1024)
+int vgpu_selection_indices_noalloc(const uint64_t* sel_bits, int64_t nrows, int32_t* sel_idx, int64_t* num_selected,
+                                   void* stream);
+
 /* Synchronises `stream` and returns VGPU_ERR_USER (with the Velox-style message) when a kernel
  * launched through this library on the current device latched a data error since the last check
  * (FilterProject calls and every aggregation; see vgpu_agg_check_errors for one aggregation). */

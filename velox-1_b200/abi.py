@@ -122,6 +122,7 @@ PROTOTYPES = {
     "vgpu_program_destroy": [_P],
     "vgpu_filter_project": [_P, C.POINTER(Column), _I32, _I64, _P, _I64, _P, _P, _P,
                             C.POINTER(OutColumn), _P],
+    "vgpu_selection_indices_noalloc": [_P, _I64, _P, _P, _P],
     "vgpu_check_errors": [_P],
     "vgpu_agg_create": [C.POINTER(AggDesc), C.POINTER(_P)],
     "vgpu_agg_destroy": [_P],
