@@ -537,6 +537,24 @@ int vgpu_debug_agg_info(vgpu_agg_t agg, void* stream, int64_t info[8]);
  * windows and a device copy in place of the count all-gather.  The finals hold extracted groups on return. */
 int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t world, size_t window_bytes, void* stream);
 
+/* Fuses the exchange into the partial aggregation's scan (HASH aggregations; replaces the Exchange between the
+ * partial and final HashAggregation of velox/exec/HashPartitionFunction.cpp:59-92 + LocalPartition / PartitionedOutput
+ * for this path): after this call the kernels of vgpu_agg_add_input(partial, ...) store every group entry straight into
+ * the window of the rank that owns its key while they scan, so the NVLink transfer overlaps the scan; the following
+ * vgpu_comm_exchange_groups(comm, partial, final) only exchanges the counts and deduplicates.  Needs a mapped window
+ * (vgpu_comm_reserve_window) and at most 8 ranks; where that does not hold, or for batches whose shape the streaming
+ * kernel does not cover, the entries are logged locally and partitioned by vgpu_comm_exchange_groups as before.
+ * No other exchange may run through `comm` between the partial aggregation's first batch and its exchange.
+ * comm == NULL detaches.  The attachment survives vgpu_agg_reset. */
+int vgpu_agg_attach_exchange(vgpu_agg_t partial_agg, vgpu_comm_t comm);
+
+/* Test support: `world` communicators whose ranks all live on the CURRENT device (windows are plain local
+ * allocations, no NCCL), for vgpu_agg_attach_exchange + vgpu_debug_exchange_local_comms on boxes with fewer GPUs than
+ * ranks.  Destroy each with vgpu_comm_destroy. */
+int vgpu_debug_local_comms(int32_t world, size_t window_bytes, vgpu_comm_t* out);
+/* vgpu_comm_exchange_groups for all ranks of such a local group at once (the count all-gather is a device copy). */
+int vgpu_debug_exchange_local_comms(vgpu_comm_t* comms, vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t world, void* stream);
+
 /* Timing of the scan kernels (the fused / interpreter kernel of vgpu_agg_add_input and
  * vgpu_filter_project, not the small bookkeeping kernels): while on, CUDA events are recorded on
  * the launching stream right before and after each such kernel.  vgpu_debug_kernel_time waits for

@@ -47,16 +47,28 @@ def main():
     os.makedirs(scratch, exist_ok=True)
     results = {}
 
-    def run(name, mode, filt, outs, col_names, types, keys, accs):
+    streaming = mapped and world <= 8 and os.environ.get("VGPU_FUSED_EXCHANGE", "1") != "0"
+
+    def run(name, mode, filt, outs, col_names, types, keys, accs, fused=False):
         cols = [engine.flat_column(t, mine[c]) for c, t in zip(col_names, types)]
         prog = engine.Program(filt, outs)
         empty = [engine.flat_column(t, mine[c][:0]) for c, t in zip(col_names, types)]
         partial = engine.Aggregation(mode, keys, accs)
         final = engine.Aggregation(mode, keys, accs)
-        partial.add_input(prog, cols, n)
+        if fused:
+            exchange.attach(partial)                           # the scan stores its entries into the owners' windows
+            half = (n // 2 + 63) // 64 * 64                    # two batches
+            partial.add_input(prog, [engine.flat_column(t, mine[c][:half]) for c, t in zip(col_names, types)], half)
+            partial.add_input(prog, [engine.flat_column(t, mine[c][half:]) for c, t in zip(col_names, types)], n - half)
+        else:
+            partial.add_input(prog, cols, n)
         final.add_input(prog, empty, 0)
         exchange.shuffle(partial, final)                       # vgpu_comm_exchange_groups
         results[name] = H.decode_rows(final.extract(), keys, accs, [o.type for o in outs], mode)
+        if fused:
+            partial.finalize()
+            assert partial.num_groups() == 0, "fused exchange: entries stayed behind in the partial aggregation"
+            return
         if mode == abi.AGG_GLOBAL:
             return  # vgpu_agg_merge_rows has no notion of the owning rank of the single global row
         again = engine.Aggregation(mode, keys, accs)
@@ -76,22 +88,30 @@ def main():
     gb_accs = [(abi.ACC_SUM_F64, 1), (abi.ACC_COUNT, -1), (abi.ACC_MIN, 1), (abi.ACC_MAX, 1)]
     for key in ("l_partkey", "l_orderkey", "l_orderkey"):
         run(key, abi.AGG_HASH, None, [ex.col(0, I64), ex.col(1, D)], [key, "l_extendedprice"], [I64, D], [(0, 64, 0, 0)], gb_accs)
+    if streaming:
+        for rep in range(2):
+            run("l_orderkey fused", abi.AGG_HASH, None, [ex.col(0, I64), ex.col(1, D)], ["l_orderkey", "l_extendedprice"], [I64, D], [(0, 64, 0, 0)], gb_accs, fused=True)
+        run("l_partkey fused", abi.AGG_HASH, None, [ex.col(0, I64), ex.col(1, D)], ["l_partkey", "l_extendedprice"], [I64, D], [(0, 64, 0, 0)], gb_accs, fused=True)
     # NULL keys and the key equal to the tables' empty marker travel in the regions' dedicated slots
     mine["k_special"] = np.where(mine["l_orderkey"] % 7 == 0, -1, mine["l_orderkey"] % 1000).astype(np.int64)
     special_nn = (mine["l_orderkey"] % 5) != 0
 
-    def run_special():
+    def run_special(fused=False):
         cols = [engine.flat_column(I64, mine["k_special"], special_nn), engine.flat_column(D, mine["l_extendedprice"])]
         outs_s = [ex.col(0, I64), ex.col(1, D)]
         prog = engine.Program(None, outs_s)
         empty = [engine.flat_column(I64, mine["k_special"][:0]), engine.flat_column(D, mine["l_extendedprice"][:0])]
         partial = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], gb_accs)
         final = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], gb_accs)
+        if fused:
+            exchange.attach(partial)
         partial.add_input(prog, cols, n)
         final.add_input(prog, empty, 0)
         exchange.shuffle(partial, final)
-        results["special"] = H.decode_rows(final.extract(), [(0, 64, 0, 0)], gb_accs, [I64, D], abi.AGG_HASH)
+        results["special fused" if fused else "special"] = H.decode_rows(final.extract(), [(0, 64, 0, 0)], gb_accs, [I64, D], abi.AGG_HASH)
     run_special()
+    if streaming:
+        run_special(fused=True)
     with open(os.path.join(scratch, f"rank{rank}.pkl"), "wb") as fh:
         pickle.dump(results, fh)
     dist.barrier()
@@ -112,7 +132,7 @@ def main():
                 want = H.run_oracle_agg(f6, outs6, [(whole[c], None) for c in H.Q6_COLS], total, [], q6_accs)
                 assert sum(len(p[name]) for p in parts) == 1, "a global aggregation reports one row over all ranks"
                 H.assert_groups_equal(union, want, q6_accs)
-            elif name == "special":
+            elif name.startswith("special"):
                 ks = np.where(whole["l_orderkey"] % 7 == 0, -1, whole["l_orderkey"] % 1000).astype(np.int64)
                 knn = (whole["l_orderkey"] % 5) != 0
                 want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(ks, knn), (whole["l_extendedprice"], None)], total,
@@ -120,7 +140,7 @@ def main():
                 assert (None,) in union and (-1,) in union
                 H.assert_groups_equal(union, want, gb_accs)
             else:
-                want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(whole[name], None), (whole["l_extendedprice"], None)], total,
+                want = H.run_oracle_agg(None, [ex.col(0, I64), ex.col(1, D)], [(whole[name.split(" ")[0]], None), (whole["l_extendedprice"], None)], total,
                                         [(0, 64, 0, 0)], gb_accs)
                 H.assert_groups_equal(union, want, gb_accs)
             spread = [len(p[name]) for p in parts]

@@ -14,22 +14,37 @@ GB_ACCS = [(abi.ACC_SUM_F64, 1), (abi.ACC_COUNT, -1), (abi.ACC_MIN, 1), (abi.ACC
 RAW_KEY = [(0, 64, 0, 0)]
 
 
-def exchange(engine, world, mode, filt, outs, types, shards, keys, accs):
-    """shards[r] = list of (values, not_null) per column for rank r.  Returns the per-rank decoded final groups."""
+def exchange(engine, world, mode, filt, outs, types, shards, keys, accs, fused=False, batches=1, steps=1):
+    """shards[r] = list of (values, not_null) per column for rank r.  Returns the per-rank decoded final groups.
+    fused: the partial aggregations stream their entries into the owners' windows from inside the scan
+    (vgpu_agg_attach_exchange); batches: add_input calls per rank; steps: reset + scan + exchange rounds."""
     prog = engine.Program(filt, outs, n_columns=len(types))
-    partials, finals = [], []
-    for r in range(world):
-        cols = [engine.flat_column(t, v, nn) for t, (v, nn) in zip(types, shards[r])]
-        empty = [engine.flat_column(t, np.asarray(v)[:0]) for t, (v, nn) in zip(types, shards[r])]
-        p = engine.Aggregation(mode, keys, accs)
-        f = engine.Aggregation(mode, keys, accs)
-        p.add_input(prog, cols, len(shards[r][0][0]))
-        f.add_input(prog, empty, 0)
-        partials.append(p)
-        finals.append(f)
-    engine.exchange_local(partials, finals)
-    engine.check_errors()
-    return [H.decode_rows(f.extract(), keys, accs, [o.type for o in outs], mode) for f in finals]
+    group = engine.LocalExchangeGroup(world) if fused else None
+    partials = [engine.Aggregation(mode, keys, accs) for _ in range(world)]
+    finals = [engine.Aggregation(mode, keys, accs) for _ in range(world)]
+    for _ in range(steps):
+        for r in range(world):
+            p, f = partials[r], finals[r]
+            p.reset(); f.reset()
+            if fused:
+                group.attach(r, p)
+            n = len(shards[r][0][0])
+            step = ((n + batches - 1) // batches + 63) // 64 * 64 if batches > 1 else max(n, 1)
+            for lo in range(0, max(n, 1), step):
+                hi = min(n, lo + step)
+                cols = [engine.flat_column(t, np.asarray(v)[lo:hi], None if nn is None else np.asarray(nn)[lo:hi]) for t, (v, nn) in zip(types, shards[r])]
+                p.add_input(prog, cols, hi - lo)
+            empty = [engine.flat_column(t, np.asarray(v)[:0]) for t, (v, nn) in zip(types, shards[r])]
+            f.add_input(prog, empty, 0)
+        if fused:
+            group.shuffle(partials, finals)
+        else:
+            engine.exchange_local(partials, finals)
+        engine.check_errors()
+    got = [H.decode_rows(f.extract(), keys, accs, [o.type for o in outs], mode) for f in finals]
+    if fused:
+        group.close()
+    return got
 
 
 def union_of(per_rank):
@@ -40,8 +55,9 @@ def union_of(per_rank):
     return u
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("world", [1, 2, 3, 8])
-def test_hash_exchange_sorted_shards(engine, world):
+def test_hash_exchange_sorted_shards(engine, world, fused):
     # every rank scans its own order range (disjoint, sorted keys): the shape of config C5
     rng = np.random.default_rng(100 + world)
     shards, allk, allv = [], [], []
@@ -51,7 +67,8 @@ def test_hash_exchange_sorted_shards(engine, world):
         shards.append([(k, None), (v, None)])
         allk.append(k); allv.append(v)
     outs = [ex.col(0, I64), ex.col(1, D)]
-    got = exchange(engine, world, abi.AGG_HASH, None, outs, [I64, D], shards, RAW_KEY, GB_ACCS)
+    got = exchange(engine, world, abi.AGG_HASH, None, outs, [I64, D], shards, RAW_KEY, GB_ACCS, fused=fused,
+                   batches=3 if fused and world == 3 else 1, steps=2 if world == 2 else 1)
     k, v = np.concatenate(allk), np.concatenate(allv)
     want = H.run_oracle_agg(None, outs, [(k, None), (v, None)], len(k), RAW_KEY, GB_ACCS)
     H.assert_groups_equal(union_of(got), want, GB_ACCS)
@@ -60,8 +77,9 @@ def test_hash_exchange_sorted_shards(engine, world):
         assert min(sizes) > 0.8 * len(want) / world, sizes  # hash partitioning spreads the groups
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("world", [2, 5])
-def test_hash_exchange_shared_keys_nulls_and_marker(engine, world):
+def test_hash_exchange_shared_keys_nulls_and_marker(engine, world, fused):
     # the same keys on every rank, NULL keys and the key -1 (the tables' empty marker), nullable input
     rng = np.random.default_rng(200 + world)
     shards, cols = [], [[], [], [], []]
@@ -75,7 +93,7 @@ def test_hash_exchange_shared_keys_nulls_and_marker(engine, world):
         for c, x in zip(cols, (k, knn, v, vnn)):
             c.append(x)
     outs = [ex.col(0, I64), ex.col(1, D)]
-    got = exchange(engine, world, abi.AGG_HASH, None, outs, [I64, D], shards, RAW_KEY, GB_ACCS)
+    got = exchange(engine, world, abi.AGG_HASH, None, outs, [I64, D], shards, RAW_KEY, GB_ACCS, fused=fused, batches=2 if world == 5 else 1)
     k, knn, v, vnn = [np.concatenate(c) for c in cols]
     want = H.run_oracle_agg(None, outs, [(k, knn), (v, vnn)], len(k), RAW_KEY, GB_ACCS)
     u = union_of(got)
@@ -107,3 +125,35 @@ def test_dense_exchange_q1_and_global(engine, world):
     assert sum(len(g) for g in got6) == 1
     want6 = H.run_oracle_agg(f6, outs6, [(whole[6], None), (whole[3], None), (whole[2], None), (whole[4], None)], len(whole[0]), [], accs6)
     H.assert_groups_equal(union_of(got6), want6, accs6)
+
+
+def test_fused_exchange_really_streams_and_falls_back(engine):
+    # attached: nothing is logged locally (the partial's own groups are only the dedicated ones); a window that is too
+    # small makes the scan log locally and the exchange partition afterwards, with the same result
+    rng = np.random.default_rng(77)
+    k = np.sort(rng.integers(0, 50_000, 200_000)).astype(np.int64)
+    v = rng.normal(size=len(k))
+    outs = [ex.col(0, I64), ex.col(1, D)]
+    prog = engine.Program(None, outs, n_columns=2)
+    want = H.run_oracle_agg(None, outs, [(k, None), (v, None)], len(k), RAW_KEY, GB_ACCS)
+    for window, streams in ((256 << 20, True), (1 << 20, False)):
+        group = engine.LocalExchangeGroup(2, window)
+        partials = [engine.Aggregation(abi.AGG_HASH, RAW_KEY, GB_ACCS) for _ in range(2)]
+        finals = [engine.Aggregation(abi.AGG_HASH, RAW_KEY, GB_ACCS) for _ in range(2)]
+        half = len(k) // 2
+        for r, (lo, hi) in enumerate(((0, half), (half, len(k)))):
+            group.attach(r, partials[r])
+            partials[r].add_input(prog, [engine.flat_column(I64, k[lo:hi]), engine.flat_column(D, v[lo:hi])], hi - lo)
+            finals[r].add_input(prog, [engine.flat_column(I64, k[:0]), engine.flat_column(D, v[:0])], 0)
+        if streams:
+            group.shuffle(partials, finals)
+            engine.check_errors()
+            got = [H.decode_rows(f.extract(), RAW_KEY, GB_ACCS, [I64, D], abi.AGG_HASH) for f in finals]
+            H.assert_groups_equal(union_of(got), want, GB_ACCS)
+            partials[0].finalize()
+            assert partials[0].num_groups() == 0  # nothing stayed behind
+        else:
+            # too small for the per-CTA sub-regions: the entries were logged locally instead
+            partials[0].finalize()
+            assert partials[0].num_groups() > 1000
+        group.close()

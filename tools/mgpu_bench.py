@@ -69,7 +69,12 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
         return float(t[0])
 
     ms_partial = timed(False)
-    ms_full = timed(True) if world > 1 else ms_partial
+    ms_classic = timed(True) if world > 1 else ms_partial     # scan, then partition + peer stores, then final
+    fused = bool(world > 1 and mapped and world <= 8 and os.environ.get("VGPU_EXCHANGE") != "nccl"
+                 and os.environ.get("VGPU_FUSED_EXCHANGE", "1") != "0")
+    if fused:
+        exchange.attach(partial)                               # the scan itself stores the entries into the owners' windows
+    ms_full = timed(True) if fused else ms_classic
     engine.check_errors()
     result = final if world > 1 else partial
     rows = torch.from_numpy(result.extract()).cuda()          # [groups here, 5]: key, flags, rows, sum, nn
@@ -100,13 +105,15 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
         "rows_per_gpu": n, "groups_total": int(mine[0]), "ms_per_step": ms_full, "ms_partial_phase": ms_partial,
         "ms_exchange_and_final": ex_ms if world > 1 else 0.0, "rows_per_s": n * world / (ms_full * 1e-3),
         "exchanged_bytes_per_step": int(mine[3]),
-        "nvlink_gbs_per_gpu_out": (float(mine[3]) / world / (ex_ms * 1e-3) / 1e9) if world > 1 else 0.0,
-        "exchange_path": ("window: partition + NVLink peer stores in one kernel, counts in one ncclAllGather" if mapped and os.environ.get("VGPU_EXCHANGE") != "nccl"
+        "ms_per_step_unfused": ms_classic,
+        "nvlink_gbs_per_gpu_out": (float(mine[3]) / world / ((ms_full if fused else ex_ms) * 1e-3) / 1e9) if world > 1 else 0.0,
+        "exchange_path": ("window, fused into the scan: the LOG-sink kernel stores each entry into its owner's window over NVLink while it scans; counts and stream facts in one ncclAllGather" if fused
+                          else "window: partition + NVLink peer stores in one kernel, counts in one ncclAllGather" if mapped and os.environ.get("VGPU_EXCHANGE") != "nccl"
                           else ("nccl: partition, counts all-gather, grouped ncclSend/ncclRecv, merge" if world > 1 else "none")),
         "partial_engine": info,
         "result_check": (f"ok: {int(mine[0])} groups, sum of keys and sum of sums match torch reductions over all ranks" if ok
                          else f"FAILED: got {mine.tolist()} want {want.tolist()}"),
-        "note": "partial phase = reset + scan (run aggregation + entry log) + its own deduplication; full step = reset + scan + exchange + final deduplication",
+        "note": "partial phase = reset + scan (run aggregation + entry log) + its own deduplication; full step = reset + scan + exchange + final deduplication; ms_per_step_unfused = the same step with scan and exchange as separate kernels; nvlink_gbs is over the whole step when fused (the transfer overlaps the scan)",
     }
 
 

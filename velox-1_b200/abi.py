@@ -155,6 +155,9 @@ PROTOTYPES = {
     "vgpu_debug_last_kernel_note": [C.c_char_p, _SZ],
     "vgpu_debug_agg_info": [_P, _P, C.POINTER(_I64)],
     "vgpu_debug_exchange_local": [C.POINTER(_P), C.POINTER(_P), _I32, _SZ, _P],
+    "vgpu_agg_attach_exchange": [_P, _P],
+    "vgpu_debug_local_comms": [_I32, _SZ, C.POINTER(_P)],
+    "vgpu_debug_exchange_local_comms": [C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _I32, _P],
     "vgpu_debug_kernel_timing": [C.c_int],
     "vgpu_debug_kernel_time": [C.POINTER(C.c_double), C.POINTER(_I64)],
 }

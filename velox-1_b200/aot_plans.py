@@ -110,9 +110,17 @@ def case_when():
     return dict(name="N3 sum(case when)", filter=None, outputs=outs, cols=cols, mode=abi.AGG_ARRAY, keys=keys, accs=accs)
 
 
+def orderkey_streaming(world):
+    """C5: the C3 scan with the exchange fused in (entries leave for the owners' windows), `world` ranks."""
+    plan = orderkey(False)
+    plan["name"] = f"C5 GROUP BY l_orderkey, exchange fused in, {world} ranks"
+    plan["dry_send"] = f"{world},1"
+    return plan
+
+
 def plans():
     return [q1(), q6_global(), q6_filter_project(False), q6_filter_project(True), orderkey(False), orderkey(True), c4(),
-            case_when()]
+            case_when(), orderkey_streaming(2), orderkey_streaming(4), orderkey_streaming(8)]
 
 
 def generate(plan):
@@ -131,7 +139,12 @@ def generate(plan):
                                           outs, None))
     else:
         agg = engine.Aggregation(plan["mode"], plan["keys"], plan["accs"])
-        abi.check(lib.vgpu_agg_add_input(agg.handle, prog.handle, arr, len(plan["cols"]), n, None, 0, None))
+        if plan.get("dry_send"):
+            os.environ["VGPU_DRY_SEND"] = plan["dry_send"]
+        try:
+            abi.check(lib.vgpu_agg_add_input(agg.handle, prog.handle, arr, len(plan["cols"]), n, None, 0, None))
+        finally:
+            os.environ.pop("VGPU_DRY_SEND", None)
     note = abi.last_kernel_note()
     if note != "dry run":
         return None, note

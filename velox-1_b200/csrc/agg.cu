@@ -744,17 +744,31 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
           p.sorted_key_col = ko.index;
         }
       }
+      // exchange fused in: the entries leave for their owners' windows from inside the scan
+      const bool send = send_wanted(a, p);
       fk = fused_prepare(p, &fgrid);
       if (fused_dry_run()) return VGPU_OK;
       if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
+      if (fk && send) {
+        rc = send_bind(a, p, fgrid, stream);
+        if (rc == VGPU_ERR_UNSUPPORTED && !a.send_used) { // log locally instead; the exchange partitions afterwards
+          p.send_world = 0; p.send_hash = 0;
+          fk = fused_prepare(p, &fgrid);
+          if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
+        } else if (rc) return rc;
+      } else if (a.send_used) {
+        set_error("this batch cannot use the fused exchange the aggregation's earlier batches used");
+        return VGPU_ERR_UNSUPPORTED;
+      }
     }
     if (fk) {
       a.engine = kEngineLog;
       const int warps = fused_kernel_threads(fk) / 32;
       const uint64_t n_blocks = ((uint64_t)p.n_rows + 127) / 128;
       const uint64_t per_warp = (n_blocks + (uint64_t)fgrid * warps - 1) / ((uint64_t)fgrid * warps);
-      rc = log_begin_batch(a, p, fgrid, per_warp * warps * 128, stream);
+      rc = log_begin_batch(a, p, fgrid, per_warp * warps * 128, stream, p.send_world > 0);
       if (rc) return rc;
+      if (p.send_world > 0) a.send_used = true;
       a.log_bound += (uint64_t)p.n_rows;
       a.finalized = false;
       if (p.sorted_probe && a.log_batches == 1) // the stream's first key, for the exchange's "sources are disjoint" test
@@ -1009,6 +1023,7 @@ int agg_reset(Agg& a, cudaStream_t stream) {
   if (!a.resolved) return VGPU_OK;
   if (a.mode == VGPU_AGG_HASH && a.engine != kEngineTable) {
     // the entry layout and the slabs stay; a later ineligible batch may still move to the TABLE engine
+    send_reset(a);
     return log_reset(a, stream);
   }
   if (a.mode == VGPU_AGG_HASH) {
@@ -1037,6 +1052,7 @@ int agg_finalize(Agg& a, cudaStream_t stream) {
 }
 
 void agg_free(Agg& a) {
+  send_free(a);
   log_free(a);
   err_word_release(a.err);
   a.err = nullptr;

@@ -124,6 +124,15 @@ struct Agg {
   int64_t packed_rows = -1;    // -1 = stale
   size_t packed_cap = 0;       // rows
   int device = 0;
+  // Exchange fused into the scan (exchange.cu, vgpu_agg_attach_exchange): the LOG-sink kernels of this (partial)
+  // aggregation store their entries straight into the owners' windows.
+  struct vgpu_comm_s* send_comm = nullptr;
+  unsigned long long* send_counts = nullptr; // [send_grid][world], device: entries per CTA and destination so far
+  size_t send_counts_cap = 0;                // words
+  int send_grid = 0;                         // CTAs of the sending kernels (fixed while send_used)
+  uint64_t send_sub_cap = 0;                 // entries per CTA and destination
+  bool send_used = false;                    // entries of the current state have left through the window
+  uint64_t send_epoch = 0;                   // the exchange's epoch (window half) those entries were stored under
   bool emit_empty_global = true;  // GLOBAL: this rank reports the (possibly empty) single group
   Agg() { for (int c = 0; c < kMaxCells; ++c) hash_aliased[c] = true; }
 };
@@ -148,7 +157,17 @@ int log_setup(Agg& a, const PipelineParams& p, cudaStream_t stream);
 // Whether the cells this launch updates fit the entry layout chosen earlier.
 bool log_layout_covers(const Agg& a, const PipelineParams& p);
 // Makes room for one more batch of `region_need` entries per region in `regions` regions; fills the sink fields of p.
-int log_begin_batch(Agg& a, PipelineParams& p, int regions, uint64_t region_need, cudaStream_t stream);
+// no_slab: the entries go elsewhere (fused exchange): only the bookkeeping fields.
+int log_begin_batch(Agg& a, PipelineParams& p, int regions, uint64_t region_need, cudaStream_t stream, bool no_slab = false);
+
+// ---- exchange.cu -------------------------------------------------------------------------------
+// Whether the aggregation's next LOG batch can leave through its attached exchange (window mapped, world <= 8, same
+// stream of batches); sets p.send_world / p.send_hash for the kernel's signature.
+bool send_wanted(Agg& a, PipelineParams& p);
+// Binds the window addresses for a launch of `grid` CTAs.  VGPU_ERR_UNSUPPORTED: the window is too small / the grid changed.
+int send_bind(Agg& a, PipelineParams& p, int grid, cudaStream_t stream);
+void send_reset(Agg& a);
+void send_free(Agg& a);
 int log_finalize(Agg& a, cudaStream_t stream);
 // Group rows in the ABI layout (key, flags, rows, values, non-null counts) from the finalized state into `out`;
 // *n_out (device) receives the count.  `max_rows`: capacity of out.

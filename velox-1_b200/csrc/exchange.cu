@@ -26,6 +26,7 @@
 
 #include "agg.h"
 #include "device_common.cuh"
+#include "fused.h"
 #include "internal.h"
 
 namespace vg {
@@ -88,6 +89,7 @@ struct vgpu_comm_s {
   char* peer[kMaxWorld] = {nullptr};   // peer[r] = rank r's window in this process' address space (peer[rank] == win)
   uint64_t epoch = 0;                  // exchanges done through the window
   uint32_t* chunk_prefix = nullptr; size_t chunk_prefix_cap = 0;
+  bool local = false;                  // vgpu_debug_local_comms: all ranks on one device, peer[] are plain local allocations
 };
 
 namespace vg {
@@ -208,6 +210,18 @@ __global__ void xchg_meta_kernel(unsigned long long* msg, uint32_t world, const 
   msg[kMaxWorld + 3] = n;
 }
 
+// Fused exchange: the per-CTA counts summed per destination (the message's first `world` words), and the launch shape.
+__global__ void xchg_send_totals_kernel(unsigned long long* msg, const unsigned long long* counts, int grid, uint32_t world,
+                                        unsigned long long sub_cap) {
+  __shared__ unsigned long long s_sum[kMaxWorld];
+  if (threadIdx.x < kMaxWorld) s_sum[threadIdx.x] = 0ull;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < (uint32_t)grid * world; i += blockDim.x) atomicAdd(&s_sum[i % world], counts[i]);
+  __syncthreads();
+  if (threadIdx.x < world) msg[threadIdx.x] = s_sum[threadIdx.x];
+  if (threadIdx.x == 0) { msg[kMaxWorld + 4] = (unsigned long long)grid; msg[kMaxWorld + 5] = sub_cap; }
+}
+
 // The two dedicated groups (NULL key, key equal to the empty marker) go to their owners' slots in front of the region;
 // every other destination gets "absent" so that a stale slot of an earlier exchange cannot be read.
 struct SpecialArgs {
@@ -237,10 +251,20 @@ struct FoldSpecialArgs {
   uint32_t world;
   int ew;
   uint32_t* err;
+  // fused exchange: every source that sent entries must have used the launch shape this rank laid its ranges out for
+  const unsigned long long* meta;  // source s: meta + s * meta_stride -> {.., [3] entries, [4] CTAs, [5] entries per CTA and owner}
+  int meta_stride;
+  unsigned long long expect_grid, expect_sub_cap; // 0 = not a fused exchange
 };
 __global__ void xchg_fold_special_kernel(FoldSpecialArgs a) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   uint32_t err = 0;
+  if (a.expect_grid) {
+    for (uint32_t s = 0; s < a.world; ++s) {
+      const unsigned long long* m = a.meta + (size_t)s * a.meta_stride;
+      if (m[3] != 0ull && (m[4] != a.expect_grid || m[5] != a.expect_sub_cap)) err |= kErrTableFull;
+    }
+  }
   for (uint32_t s = 0; s < a.world; ++s) {
     for (int r = 0; r < 2; ++r) {
       const uint64_t* in = a.slot[s] + (size_t)r * a.ew;
@@ -356,7 +380,7 @@ int vgpu_comm_create(const uint8_t id[VGPU_COMM_ID_BYTES], int32_t rank, int32_t
 }
 static void window_close(vgpu_comm_s* c) {
   for (int r = 0; r < c->world; ++r) {
-    if (r != c->rank && c->peer[r]) cudaIpcCloseMemHandle(c->peer[r]);
+    if (r != c->rank && c->peer[r] && !c->local) cudaIpcCloseMemHandle(c->peer[r]);
     c->peer[r] = nullptr;
   }
   if (c->win) cudaFree(c->win);
@@ -366,7 +390,7 @@ static void window_close(vgpu_comm_s* c) {
 int vgpu_comm_destroy(vgpu_comm_t comm) {
   if (comm) {
     window_close(comm);
-    g_nccl.comm_destroy(comm->comm);
+    if (comm->comm) g_nccl.comm_destroy(comm->comm);
     cudaFree(comm->send); cudaFree(comm->recv); cudaFree(comm->dcounts); cudaFree(comm->chunk_prefix);
     delete comm;
   }
@@ -567,6 +591,80 @@ static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t str
   return log_finalize(fa, stream);
 }
 
+// ---- fused exchange (entries already left from inside the scan: fused_prelude.cuh send_entries) --------------------
+static constexpr size_t kFusedCountsBytes = 1024 * sizeof(unsigned long long); // = vg::kSendCountsBytes (below)
+
+// Sender: what is left to do after the scans — the count message, the dedicated groups, the stream facts.
+static int log_fused_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
+  const int W = comm->world, ew = pa.ew;
+  const int half = (int)(comm->epoch & 1);
+  VG_CUDA(cudaMemsetAsync(comm->dcounts, 0, sizeof(int64_t) * kMsgWords, stream));
+  xchg_send_totals_kernel<<<1, 256, 0, stream>>>((unsigned long long*)comm->dcounts, pa.send_counts, pa.send_grid, (uint32_t)W, pa.send_sub_cap);
+  SpecialArgs sp{};
+  sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew; sp.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
+  for (int d = 0; d < W; ++d) sp.peer_slot[d] = (uint64_t*)region_of(comm, d, half, comm->rank);
+  xchg_send_special_kernel<<<W, 64, 0, stream>>>(sp);
+  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)comm->dcounts, (uint32_t)W, pa.ctr, pa.log_probed ? 1 : 0, (pa.log_batches + 1) & 1);
+  VG_CUDA(cudaGetLastError());
+  count_launch(3);
+  return VGPU_OK;
+}
+
+// Receiver: one front and one back range per source and sending CTA, counted by the words the senders left beside them.
+static int log_fused_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream) {
+  const int W = comm->world, ew = pa.ew, grid = pa.send_grid;
+  const int half = (int)(comm->epoch & 1);
+  const size_t special_bytes = special_slot_bytes(ew);
+  const uint64_t sub_cap = pa.send_sub_cap;
+  int rc;
+  if (fa.engine == kEngineUndecided) { if ((rc = log_adopt_layout(fa, pa, stream))) return rc; }
+  if (fa.engine != kEngineLog || fa.ew != ew) { set_error("the final aggregation cannot take the partial stage's entries"); return VGPU_ERR_INVALID; }
+  FoldSpecialArgs fs{};
+  fs.special = fa.special; fs.kinds = log_cell_kinds(fa); fs.world = (uint32_t)W; fs.ew = ew; fs.err = fa.err;
+  fs.meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fs.meta_stride = kMsgWords;
+  fs.expect_grid = (unsigned long long)grid; fs.expect_sub_cap = sub_cap;
+  fa.ext_ranges.reserve(fa.ext_ranges.size() + (size_t)2 * W * grid);
+  for (int src = 0; src < W; ++src) {
+    const char* region = region_of(comm, comm->rank, half, src);
+    fs.slot[src] = (const uint64_t*)region;
+    const uint32_t* counts = reinterpret_cast<const uint32_t*>(region + special_bytes);
+    const uint64_t* entries = reinterpret_cast<const uint64_t*>(region + special_bytes + kFusedCountsBytes);
+    for (int c = 0; c < grid; ++c) {
+      LogRange r{};
+      r.base = entries + (uint64_t)c * sub_cap * ew;
+      r.cap = sub_cap;
+      r.count64 = 0;
+      r.count = counts + 2 * c;      // low half: front entries
+      r.back = 0;
+      fa.ext_ranges.push_back(r);
+      r.count = counts + 2 * c + 1;  // high half: back entries
+      r.back = 1;
+      fa.ext_ranges.push_back(r);
+    }
+  }
+  fa.ext_bound += sub_cap * (uint64_t)grid * (uint64_t)W;
+  fa.ext_meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fa.ext_sources = W;
+  fa.ext_meta_stride = kMsgWords;
+  fa.finalized = false;
+  fa.packed_rows = -1;
+  xchg_fold_special_kernel<<<1, 32, 0, stream>>>(fs);
+  VG_CUDA(cudaGetLastError());
+  count_launch();
+  ++comm->epoch;
+  return log_finalize(fa, stream);
+}
+
+static int exchange_log_fused(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int64_t* bytes_sent) {
+  int rc = log_fused_send(comm, pa, stream);
+  if (rc) return rc;
+  // the barrier between "everybody's scan has stored" and "anybody reads", carrying the stream facts
+  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, stream));
+  if (bytes_sent) *bytes_sent = -1; // known on the device only; see vgpu_comm_last_counts
+  return log_fused_receive(comm, pa, fa, stream);
+}
+
 static int exchange_log_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int64_t* bytes_sent) {
   int rc = log_p2p_send(comm, pa, stream);
   if (rc) return rc;
@@ -628,8 +726,62 @@ int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg
     if (comm->win && !no_p2p && dense_fits(comm, pa)) return exchange_dense_p2p(comm, pa, fa, stream, bytes_sent);
     return exchange_nccl(comm, pa, fa, stream, bytes_sent);
   }
+  if (pa.send_used) {
+    if (pa.send_comm != comm) { set_error("the partial aggregation's entries left through another exchange"); return VGPU_ERR_INVALID; }
+    if (pa.send_epoch != comm->epoch) { set_error("another exchange ran through this communicator since the partial aggregation's scan"); return VGPU_ERR_INVALID; }
+    return exchange_log_fused(comm, pa, fa, stream, bytes_sent);
+  }
   if (comm->win && !no_p2p && log_fits(comm, pa, fa)) return exchange_log_p2p(comm, pa, fa, stream, bytes_sent);
   return exchange_nccl(comm, pa, fa, stream, bytes_sent);
+}
+
+int vgpu_debug_local_comms(int32_t world, size_t window_bytes, vgpu_comm_t* out) {
+  if (!out || world < 1 || world > kMaxWorld) return VGPU_ERR_INVALID;
+  window_bytes = (window_bytes + 2 * kWinHeader + 4095) & ~(size_t)4095;
+  int rc = VGPU_OK;
+  for (int r = 0; r < world; ++r) out[r] = nullptr;
+  for (int r = 0; r < world && rc == VGPU_OK; ++r) {
+    vgpu_comm_s* c = new vgpu_comm_s();
+    out[r] = c;
+    c->comm = nullptr; c->rank = r; c->world = world; c->local = true;
+    if (cudaMalloc(&c->win, window_bytes) != cudaSuccess || cudaMemset(c->win, 0, window_bytes) != cudaSuccess ||
+        cudaMalloc(&c->dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
+    c->win_bytes = window_bytes;
+  }
+  if (rc) { for (int r = 0; r < world; ++r) { if (out[r]) vgpu_comm_destroy(out[r]); out[r] = nullptr; } return rc; }
+  for (int r = 0; r < world; ++r) for (int q = 0; q < world; ++q) out[r]->peer[q] = out[q]->win;
+  return VGPU_OK;
+}
+
+int vgpu_debug_exchange_local_comms(vgpu_comm_t* comms, vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t world, void* stream_) {
+  if (!comms || !partials || !finals || world < 1 || world > kMaxWorld) return VGPU_ERR_INVALID;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  for (int r = 0; r < world; ++r) {
+    if (!comms[r] || !comms[r]->local || comms[r]->world != world || !partials[r] || !finals[r]) { set_error("rank %d: not a local exchange of %d ranks", r, world); return VGPU_ERR_INVALID; }
+    Agg& pa = partials[r]->agg;
+    Agg& fa = finals[r]->agg;
+    if (!pa.resolved || !fa.resolved || pa.mode != fa.mode) { set_error("rank %d: aggregations not ready", r); return VGPU_ERR_INVALID; }
+    if (pa.send_used) { if (pa.send_comm != comms[r]) { set_error("rank %d: entries left through another exchange", r); return VGPU_ERR_INVALID; } continue; }
+    if (pa.mode == VGPU_AGG_HASH ? !log_fits(comms[r], pa, fa) : !dense_fits(comms[r], pa)) { set_error("rank %d: the window path does not apply", r); return VGPU_ERR_UNSUPPORTED; }
+  }
+  const bool hash = partials[0]->agg.mode == VGPU_AGG_HASH;
+  for (int r = 0; r < world; ++r) {
+    Agg& pa = partials[r]->agg;
+    int rc = !hash ? dense_p2p(comms[r], pa, finals[r]->agg, stream, 1, false) : pa.send_used ? log_fused_send(comms[r], pa, stream) : log_p2p_send(comms[r], pa, stream);
+    if (rc) return rc;
+  }
+  if (hash) { // the all-gather of the counts
+    for (int r = 0; r < world; ++r) for (int src = 0; src < world; ++src)
+      VG_CUDA(cudaMemcpyAsync(comms[r]->dcounts + kMsgWords + (size_t)src * kMsgWords, comms[src]->dcounts, sizeof(int64_t) * kMsgWords, cudaMemcpyDeviceToDevice, stream));
+  }
+  for (int r = 0; r < world; ++r) {
+    Agg& pa = partials[r]->agg;
+    Agg& fa = finals[r]->agg;
+    if (pa.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)partition_of(0, 0, (uint32_t)world, false) == r;
+    int rc = !hash ? dense_p2p(comms[r], pa, fa, stream, 2, true) : pa.send_used ? log_fused_receive(comms[r], pa, fa, stream) : log_p2p_receive(comms[r], pa, fa, stream);
+    if (rc) return rc;
+  }
+  return VGPU_OK;
 }
 
 // All `world` ranks of an exchange emulated on the CURRENT device, for boxes with fewer GPUs than ranks (tests,
@@ -639,49 +791,27 @@ int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg
 int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t world, size_t window_bytes, void* stream_) {
   if (!partials || !finals || world < 1 || world > kMaxWorld) return VGPU_ERR_INVALID;
   cudaStream_t stream = (cudaStream_t)stream_;
-  std::vector<vgpu_comm_s> comms(world);
-  window_bytes = (window_bytes + 2 * kWinHeader + 4095) & ~(size_t)4095;
-  int rc = VGPU_OK;
-  for (int r = 0; r < world && rc == VGPU_OK; ++r) {
-    comms[r].comm = nullptr; comms[r].rank = r; comms[r].world = world;
-    if (cudaMalloc(&comms[r].win, window_bytes) != cudaSuccess || cudaMemset(comms[r].win, 0, window_bytes) != cudaSuccess ||
-        cudaMalloc(&comms[r].dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
-    comms[r].win_bytes = window_bytes;
-  }
-  for (int r = 0; r < world; ++r) for (int q = 0; q < world; ++q) comms[r].peer[q] = comms[q].win;
-  auto body = [&]() -> int {
-    for (int r = 0; r < world; ++r) {
-      Agg& pa = partials[r]->agg;
-      Agg& fa = finals[r]->agg;
-      if (!pa.resolved || !fa.resolved || pa.mode != fa.mode) { set_error("rank %d: aggregations not ready", r); return VGPU_ERR_INVALID; }
-      if (pa.mode == VGPU_AGG_HASH ? !log_fits(&comms[r], pa, fa) : !dense_fits(&comms[r], pa)) { set_error("rank %d: the window path does not apply", r); return VGPU_ERR_UNSUPPORTED; }
-    }
-    const bool hash = partials[0]->agg.mode == VGPU_AGG_HASH;
-    for (int r = 0; r < world; ++r) {
-      int rc2 = hash ? log_p2p_send(&comms[r], partials[r]->agg, stream) : dense_p2p(&comms[r], partials[r]->agg, finals[r]->agg, stream, 1, false);
-      if (rc2) return rc2;
-    }
-    if (hash) { // the all-gather of the counts
-      for (int r = 0; r < world; ++r) for (int src = 0; src < world; ++src)
-        VG_CUDA(cudaMemcpyAsync(comms[r].dcounts + kMsgWords + (size_t)src * kMsgWords, comms[src].dcounts, sizeof(int64_t) * kMsgWords, cudaMemcpyDeviceToDevice, stream));
-    }
-    for (int r = 0; r < world; ++r) {
-      Agg& fa = finals[r]->agg;
-      if (partials[r]->agg.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)partition_of(0, 0, (uint32_t)world, false) == r;
-      int rc2 = hash ? log_p2p_receive(&comms[r], partials[r]->agg, fa, stream) : dense_p2p(&comms[r], partials[r]->agg, fa, stream, 2, true);
-      if (rc2) return rc2;
-      // the final aggregation must not keep pointers into the temporary windows: materialise its groups now
-      if (hash) { rc2 = agg_extract_all(fa, stream); if (rc2) return rc2; }
-    }
-    return VGPU_OK;
-  };
-  if (rc == VGPU_OK) rc = body();
+  std::vector<vgpu_comm_t> comms(world, nullptr);
+  int rc = vgpu_debug_local_comms(world, window_bytes, comms.data());
+  if (rc) return rc;
+  rc = vgpu_debug_exchange_local_comms(comms.data(), partials, finals, world, stream_);
+  // the final aggregations must not keep pointers into the temporary windows: materialise their groups now
+  for (int r = 0; r < world && rc == VGPU_OK; ++r) if (finals[r]->agg.mode == VGPU_AGG_HASH) rc = agg_extract_all(finals[r]->agg, stream);
   cudaStreamSynchronize(stream);
   for (int r = 0; r < world; ++r) {
     if (partials[r] && finals[r]) { Agg& fa = finals[r]->agg; fa.ext_ranges.clear(); fa.ext_bound = 0; fa.ext_meta = nullptr; fa.ext_sources = 0; }
-    cudaFree(comms[r].win); cudaFree(comms[r].dcounts); cudaFree(comms[r].chunk_prefix);
+    vgpu_comm_destroy(comms[r]);
   }
   return rc;
+}
+
+int vgpu_agg_attach_exchange(vgpu_agg_t agg, vgpu_comm_t comm) {
+  if (!agg) return VGPU_ERR_INVALID;
+  Agg& a = agg->agg;
+  if (a.send_used) { set_error("entries of the current state already left through an exchange: reset the aggregation first"); return VGPU_ERR_INVALID; }
+  if (comm && a.mode != VGPU_AGG_HASH) { set_error("only HASH aggregations stream their entries (ARRAY / GLOBAL states are exchanged whole)"); return VGPU_ERR_UNSUPPORTED; }
+  a.send_comm = comm;
+  return VGPU_OK;
 }
 
 // Entries this rank sent to each destination in the last window exchange of a HASH aggregation (and the whole
@@ -700,3 +830,84 @@ int vgpu_comm_last_counts(vgpu_comm_t comm, int64_t* matrix, void* stream) {
 }
 
 } // extern "C"
+
+// ---- the exchange fused into the scan ------------------------------------------------------------------------------
+// A partial aggregation with an attached exchange does not log its entries locally: the LOG-sink kernel stores each
+// entry into the window of the rank that owns its key while it scans (fused_prelude.cuh send_entries), so the NVLink
+// transfer overlaps the scan instead of following it.  Layout of the region source s has in owner o's window:
+//   [special slots][kSendCountsBytes: one packed count per sending CTA][grid sub-regions of sub_cap entries]
+// Sub-region c belongs to CTA c of the sender: front entries from its start, back entries from its end.
+namespace vg {
+namespace {
+constexpr int kSendMaxGrid = 1024;
+constexpr size_t kSendCountsBytes = (size_t)kSendMaxGrid * sizeof(unsigned long long);
+static_assert(kSendCountsBytes == kFusedCountsBytes, "one layout");
+constexpr uint64_t kSendMinSubCap = 256;
+
+uint64_t send_sub_cap_for(const vgpu_comm_s* comm, int ew, int grid) {
+  const size_t head = special_slot_bytes(ew) + kSendCountsBytes;
+  if (region_bytes(comm) <= head) return 0;
+  return (region_bytes(comm) - head) / ((size_t)ew * 8) / (size_t)grid;
+}
+} // namespace
+
+bool send_wanted(Agg& a, PipelineParams& p) {
+  p.send_world = 0; p.send_hash = 0;
+  if (fused_dry_run()) { // ahead-of-time plans: "world,hash" names the variant to generate
+    const char* e = getenv("VGPU_DRY_SEND");
+    int w = 0, h = 0;
+    if (e && sscanf(e, "%d,%d", &w, &h) == 2 && w >= 1 && w <= 8) { p.send_world = w; p.send_hash = h ? 1 : 0; return true; }
+    return false;
+  }
+  vgpu_comm_s* c = a.send_comm;
+  if (!c || !c->win || c->world > 8) return false;
+  static const bool off = getenv("VGPU_FUSED_EXCHANGE") && getenv("VGPU_FUSED_EXCHANGE")[0] == '0'; // tuning aid
+  if (off) return false;
+  if (!a.slabs.empty() || !a.ext_ranges.empty()) return false; // entries were already logged locally: stay local
+  p.send_world = c->world;
+  p.send_hash = agg_raw_bigint_key(a) ? 1 : 0;
+  return true;
+}
+
+int send_bind(Agg& a, PipelineParams& p, int grid, cudaStream_t stream) {
+  vgpu_comm_s* c = a.send_comm;
+  const int W = c->world, ew = a.ew;
+  if (grid > kSendMaxGrid) { set_error("fused exchange: %d CTAs exceed the %d count slots of a window region", grid, kSendMaxGrid); return VGPU_ERR_UNSUPPORTED; }
+  const uint64_t sub_cap = send_sub_cap_for(c, ew, grid);
+  if (sub_cap < kSendMinSubCap) { set_error("fused exchange: the window is too small (vgpu_comm_reserve_window)"); return VGPU_ERR_UNSUPPORTED; }
+  if (a.send_used && (grid != a.send_grid || sub_cap != a.send_sub_cap)) {
+    set_error("fused exchange: the launch shape changed between batches (%d -> %d CTAs)", a.send_grid, grid);
+    return VGPU_ERR_UNSUPPORTED;
+  }
+  const size_t words = (size_t)grid * W;
+  if (words > a.send_counts_cap) {
+    if (a.send_counts) { VG_CUDA(cudaStreamSynchronize(stream)); VG_CUDA(cudaFree(a.send_counts)); a.send_counts = nullptr; a.send_counts_cap = 0; }
+    VG_CUDA(cudaMalloc(&a.send_counts, words * sizeof(unsigned long long)));
+    a.send_counts_cap = words;
+  }
+  if (a.send_used && a.send_epoch != c->epoch) {
+    set_error("fused exchange: another exchange ran through this communicator between two batches of the aggregation");
+    return VGPU_ERR_INVALID;
+  }
+  if (!a.send_used) { VG_CUDA(cudaMemsetAsync(a.send_counts, 0, words * sizeof(unsigned long long), stream)); a.send_epoch = c->epoch; }
+  a.send_grid = grid;
+  a.send_sub_cap = sub_cap;
+  const int half = (int)(c->epoch & 1);
+  const size_t special_bytes = special_slot_bytes(ew);
+  p.send_sub_cap = sub_cap;
+  p.send_counts = a.send_counts;
+  for (int d = 0; d < 8; ++d) { p.send_base[d] = nullptr; p.send_peer_counts[d] = nullptr; }
+  for (int d = 0; d < W; ++d) {
+    char* region = region_of(c, d, half, c->rank);
+    p.send_peer_counts[d] = (unsigned long long*)(region + special_bytes);
+    p.send_base[d] = (uint64_t*)(region + special_bytes + kSendCountsBytes);
+  }
+  return VGPU_OK;
+}
+
+void send_reset(Agg& a) { a.send_used = false; }
+void send_free(Agg& a) {
+  cudaFree(a.send_counts);
+  a.send_counts = nullptr; a.send_counts_cap = 0; a.send_comm = nullptr; a.send_used = false;
+}
+} // namespace vg

@@ -610,9 +610,13 @@ struct Gen {
   }
 
   // Stores one entry (key SKx, values SVx<c>) at offset OFFx of the CTA's region.
-  void gen_log_store(const char* cond, const char* off, const char* key, const char* vsuffix) {
+  // (send mode: into the warp's staging area instead, with the entry's kind beside it)
+  bool send_mode() const { return p.mode == kSinkLog && p.send_world > 0; }
+  static constexpr int kSendStage = 160; // entries a warp can produce per block: 5 per lane
+  void gen_log_store(const char* cond, const char* off, const char* key, const char* vsuffix, const char* kind) {
     const int EW = p.log_entry_words;
-    out("      if (%s) {\n        u64* e = region + (u64)%s * %d;\n", cond, off, EW);
+    out("      if (%s) {\n        u64* e = %s + (u64)%s * %d;\n", cond, send_mode() ? "wl" : "region", off, EW);
+    if (send_mode()) out("        wk[%s] = (unsigned char)%s;\n", off, kind);
     if (EW == 2) {
       const int c = p.log_cells[0];
       out("        *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(%s, SV%d%s);\n", key, p.cells[c].skip ? 0 : c, vsuffix);
@@ -771,11 +775,13 @@ struct Gen {
     out("      KIND[4] = !SA4 || special ? 0u : (cedge ? 2u : 1u);\n");
     gen_log_special("SA4 && special", "SN4", "_4");
     out("    }\n");
-    out("    u32 OFF[5]; log_reserve<5>(logcur, (u32)p.log_region_cap, KIND, OFF);\n");
+    if (send_mode()) out("    u32 OFF[5]; const u32 stot = warp_compact<5>(KIND, OFF);\n");
+    else out("    u32 OFF[5]; log_reserve<5>(logcur, (u32)p.log_region_cap, KIND, OFF);\n");
     out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (KIND[sgm] == 0u) continue;\n");
     {
       const int EW = p.log_entry_words;
-      out("      u64* e = region + (u64)OFF[sgm] * %d;\n", EW);
+      out("      u64* e = %s + (u64)OFF[sgm] * %d;\n", send_mode() ? "wl" : "region", EW);
+      if (send_mode()) out("      wk[OFF[sgm]] = (unsigned char)KIND[sgm];\n");
       if (EW == 2) {
         const int c = p.log_cells[0];
         out("      *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(SK[sgm], SV%d[sgm]);\n", p.cells[c].skip ? 0 : c);
@@ -789,7 +795,8 @@ struct Gen {
       }
     }
     out("    }\n");
-    gen_log_store("KIND[4] != 0u", "OFF[4]", "SK4", "_4");
+    gen_log_store("KIND[4] != 0u", "OFF[4]", "SK4", "_4", "KIND[4]");
+    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
     out("    ck = nk; cn = nn; chave = nhave; cedge = nedge;\n");
     for (int i = 0; i < n_live; ++i) out("    cv%d = nv%d;\n", live_cells[i], live_cells[i]);
   }
@@ -848,8 +855,10 @@ struct Gen {
     for (int i = 0; i < n_live; ++i) out("    u64 SV%d_4 = cv%d;\n", live_cells[i], live_cells[i]);
     gen_log_special("lane == 0 && special", "SN4", "_4");
     out("    u32 K1[1] = {lane == 0 && !special ? (edge ? 2u : 1u) : 0u}, O1[1];\n");
-    out("    log_reserve<1>(logcur, (u32)p.log_region_cap, K1, O1);\n");
-    gen_log_store("K1[0] != 0u", "O1[0]", "SK4", "_4");
+    if (send_mode()) out("    const u32 stot = warp_compact<1>(K1, O1);\n");
+    else out("    log_reserve<1>(logcur, (u32)p.log_region_cap, K1, O1);\n");
+    gen_log_store("K1[0] != 0u", "O1[0]", "SK4", "_4", "K1[0]");
+    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
     out("    (void)SN4;\n  }\n");
   }
 
@@ -988,6 +997,11 @@ struct Gen {
     }
     plan.threads = NT;
     plan.smem_bytes = 0;
+    if (send_mode()) {
+      if (p.send_world > 8) { decline("fused exchange: more than 8 ranks"); return; }
+      plan.smem_bytes = (NT / 32) * (kSendStage * p.log_entry_words + kSendStage / 8) * 8;
+      if (plan.smem_bytes * CTAS > 200 * 1024) { decline("fused exchange: staging area exceeds shared memory"); return; }
+    }
     out("#define NT %d\n", NT);
     out("using namespace vgf;\n");
     if (p.mode == kSinkArray && st == AS_ATOMIC) {
@@ -1014,8 +1028,16 @@ struct Gen {
     gen_small_dict_registers();
     if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
     if (p.mode == kSinkLog) {
-      out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
-      out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
+      if (send_mode()) {
+        const int W = p.send_world, words = kSendStage * p.log_entry_words + kSendStage / 8;
+        out("  extern __shared__ __align__(16) u64 sendstage[];\n  __shared__ unsigned long long sendcur[%d];\n", W);
+        out("  if (threadIdx.x < %d) sendcur[threadIdx.x] = p.send_counts[blockIdx.x * %d + threadIdx.x];\n  __syncthreads();\n", W, W);
+        out("  u64* const wl = sendstage + (threadIdx.x >> 5) * %d;\n", words);
+        out("  unsigned char* const wk = reinterpret_cast<unsigned char*>(wl + %d);\n", kSendStage * p.log_entry_words);
+      } else {
+        out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
+        out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
+      }
       if (p.sorted_probe) out("  bool viol = false;\n");
     }
     if (p.mode == kSinkArray) {
@@ -1073,6 +1095,11 @@ struct Gen {
     }
     if (p.mode == kSinkLog) {
       gen_log_epilogue();
+      if (send_mode()) {
+        // the counts stay with this rank for the next launch and go to each owner's window beside the entries
+        out("  __syncthreads();\n  if (threadIdx.x < %d) {\n    p.send_counts[blockIdx.x * %d + threadIdx.x] = sendcur[threadIdx.x];\n", p.send_world, p.send_world);
+        out("    p.send_peer_counts[threadIdx.x][blockIdx.x] = sendcur[threadIdx.x];\n  }\n");
+      } else
       out("  __syncthreads();\n  if (threadIdx.x == 0) { p.log_counts[2 * blockIdx.x] = logcur[0]; p.log_counts[2 * blockIdx.x + 1] = logcur[1]; }\n");
       if (p.sorted_probe) out("  if (__any_sync(0xffffffffu, viol) && lane == 0) atomicOr(p.sort_state, 1ull);\n");
     }

@@ -92,6 +92,11 @@ struct FusedParams {
   u64* sort_state;
   const u64* sort_prev_in;
   u64* sort_prev_out;
+  // LOG sink, exchange fused in (internal.h PipelineParams::send...)
+  u64 send_sub_cap;
+  u64* send_base[8];
+  unsigned long long* send_peer_counts[8];
+  unsigned long long* send_counts;
 };
 
 __device__ __forceinline__ u64 d2u(double d) { return (u64)__double_as_longlong(d); }
@@ -600,6 +605,81 @@ __device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */,
     f += kind[s] & 1u;
     b -= kind[s] >> 1;
   }
+}
+
+// ---- LOG sink with the exchange fused in ----------------------------------------------------------
+// Places of the lane's active segments in the warp's staging area (kind != 0), in lane order; returns the warp's total.
+template <int N>
+__device__ __forceinline__ u32 warp_compact(const u32 (&kind)[N], u32 (&off)[N]) {
+  const u32 lane = threadIdx.x & 31u;
+  u32 mine = 0;
+#pragma unroll
+  for (int s = 0; s < N; ++s) mine += kind[s] != 0u ? 1u : 0u;
+  u32 incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const u32 u = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (u32)d) incl += u;
+  }
+  u32 at = incl - mine;
+#pragma unroll
+  for (int s = 0; s < N; ++s) { off[s] = at; at += kind[s] != 0u ? 1u : 0u; }
+  return __shfl_sync(0xffffffffu, incl, 31);
+}
+// Owner of a group among W ranks: device_common.cuh partition_of with W known at compile time (VELOX: one raw BIGINT
+// key hashed like folly::hasher<int64_t>, velox/exec/VectorHasher.cpp:68-108; else splitmix64 of the packed key).
+template <int W, bool VELOX>
+__device__ __forceinline__ u32 send_dest(u64 key) {
+  u64 k = key;
+  if (VELOX) {
+    k = (~k) + (k << 21);
+    k = k ^ (k >> 24);
+    k = k + (k << 3) + (k << 8);
+    k = k ^ (k >> 14);
+    k = k + (k << 2) + (k << 4);
+    k = k ^ (k >> 28);
+    k = k + (k << 31);
+  } else {
+    k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
+    k ^= k >> 27; k *= 0x94d049bb133111ebull;
+    k ^= k >> 31;
+  }
+  return (u32)(k % (u64)W);
+}
+// The warp's `tot` staged entries (wl: EW words each; wk: 1 = front, 2 = back) leave for their owners' windows:
+// lanes with the same owner and side take consecutive places of this CTA's sub-region there (one shared-memory
+// atomic per owner, side and step), then every lane stores its own entry over NVLink.
+template <int EW, int W, bool VELOX>
+__device__ __forceinline__ void send_entries(const FusedParams& p, unsigned long long* sendcur, const u64* wl, const unsigned char* wk, u32 tot, u32& err) {
+  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  for (u32 i0 = 0; i0 < tot; i0 += 32u) {
+    const u32 i = i0 + lane;
+    const bool act = i < tot;
+    const u64 key = act ? wl[(size_t)i * EW] : 0ull;
+    const u32 kind = act ? (u32)wk[i] : 1u;
+    const u32 dest = send_dest<W, VELOX>(key);
+    const u32 tag = act ? dest * 2u + (kind - 1u) : 0xffffffffu;
+    const u32 m = __match_any_sync(0xffffffffu, tag);
+    const int leader = __ffs((int)m) - 1;
+    const u32 cnt = (u32)__popc(m);
+    unsigned long long base = 0ull;
+    if ((int)lane == leader && act) base = atomicAdd(&sendcur[dest], (unsigned long long)cnt << (kind == 2u ? 32 : 0));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (act) {
+      const u64 front = base & 0xffffffffull, back = base >> 32;
+      if (front + back + cnt > p.send_sub_cap) {
+        err |= VGF_ERR_TABLEFULL; // the window is too small for this CTA's share (vgpu_comm_reserve_window)
+      } else {
+        const u64 rk = (u64)__popc(m & lt);
+        const u64 pos = kind == 1u ? front + rk : p.send_sub_cap - 1ull - (back + rk);
+        u64* out = p.send_base[dest] + ((u64)blockIdx.x * p.send_sub_cap + pos) * EW;
+        const u64* e = wl + (size_t)i * EW;
+        if (EW == 2) *reinterpret_cast<ulonglong2*>(out) = *reinterpret_cast<const ulonglong2*>(e);
+        else { _Pragma("unroll") for (int w = 0; w < EW; ++w) out[w] = e[w]; }
+      }
+    }
+  }
+  __syncwarp();
 }
 
 template <int KIND>

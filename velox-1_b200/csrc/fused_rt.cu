@@ -230,7 +230,7 @@ std::string signature(const PipelineParams& p) {
     for (int c = 0; c < p.n_cells; ++c) { put(&p.cells[c].kind, 1); put(&p.cells[c].input, 1); put(&p.cells[c].skip, 1); }
     if (p.mode == kSinkLog) {
       put(&p.log_entry_words, 4); put(&p.log_n_cells, 4); put(p.log_cells, (size_t)p.log_n_cells);
-      put(&p.sorted_probe, 4); put(&p.sorted_key_col, 4);
+      put(&p.sorted_probe, 4); put(&p.sorted_key_col, 4); put(&p.send_world, 4); put(&p.send_hash, 4);
     }
   } else {
     for (int k = 0; k < p.n_outputs; ++k) {
@@ -333,6 +333,8 @@ FusedKernel* fused_prepare(const PipelineParams& p, int* grid) {
   const int64_t blocks = (p.n_rows + 127) / 128;
   const int64_t want = (blocks + k->threads / 32 - 1) / (k->threads / 32);
   *grid = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)num_sms() * k->blocks_per_sm));
+  // exchange fused in: the launch shape names the sub-regions of the peers' windows, so it must not follow the batch size
+  if (p.mode == kSinkLog && p.send_world > 0) *grid = num_sms() * k->blocks_per_sm;
   return k;
 }
 
@@ -359,6 +361,8 @@ int fused_launch(FusedKernel* k, const PipelineParams& p, int grid, cudaStream_t
   fp.ovf = (vgf::u64*)p.ovf; fp.ovf_cap = p.ovf_cap; fp.ovf_cursor = (vgf::u64*)p.ovf_cursor;
   fp.log = (vgf::u64*)p.log; fp.log_region_cap = p.log_region_cap; fp.log_counts = p.log_counts; fp.log_special = (vgf::u64*)p.log_special;
   fp.sort_state = (vgf::u64*)p.sort_state; fp.sort_prev_in = (const vgf::u64*)p.sort_prev_in; fp.sort_prev_out = (vgf::u64*)p.sort_prev_out;
+  fp.send_sub_cap = p.send_sub_cap; fp.send_counts = p.send_counts;
+  for (int d = 0; d < 8; ++d) { fp.send_base[d] = (vgf::u64*)p.send_base[d]; fp.send_peer_counts[d] = p.send_peer_counts[d]; }
   fp.sel_words = p.sel_words;
   fp.tile_counts = p.tile_counts;
   for (int i = 0; i < p.n_outputs && i < 24; ++i) { fp.out_values[i] = p.outs[i].values; fp.out_nulls[i] = (vgf::u64*)p.outs[i].nulls; }

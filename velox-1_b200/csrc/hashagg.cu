@@ -483,13 +483,13 @@ static int slab_alloc(LogSlab& s, int regions, uint64_t region_cap, int ew) {
   return VGPU_OK;
 }
 
-int log_begin_batch(Agg& a, PipelineParams& p, int regions, uint64_t region_need, cudaStream_t stream) {
+int log_begin_batch(Agg& a, PipelineParams& p, int regions, uint64_t region_need, cudaStream_t stream, bool no_slab) {
   LogSlab* use = nullptr;
-  if (!a.slabs.empty()) {
+  if (!no_slab && !a.slabs.empty()) {
     LogSlab& s = a.slabs.back();
     if (s.regions >= regions && s.region_used + region_need <= s.region_cap) use = &s;
   }
-  if (!use) {
+  if (!use && !no_slab) {
     // a slab kept from before reset() that is large enough, else a new one (at least as large as everything logged
     // so far, so the number of slabs grows with the logarithm of the input)
     int pick = -1;
@@ -512,10 +512,12 @@ int log_begin_batch(Agg& a, PipelineParams& p, int regions, uint64_t region_need
     a.slabs.push_back(s);
     use = &a.slabs.back();
   }
-  use->region_used += region_need;
-  p.log = use->base;
-  p.log_region_cap = use->region_cap;
-  p.log_counts = use->counts;
+  if (use) {
+    use->region_used += region_need;
+    p.log = use->base;
+    p.log_region_cap = use->region_cap;
+    p.log_counts = use->counts;
+  }
   p.log_special = a.special;
   p.sort_state = a.ctr + kCtrSortState;
   p.sort_prev_in = a.ctr + kCtrPrevKey + 2 * ((a.log_batches + 1) & 1);

@@ -225,6 +225,17 @@ struct PipelineParams {
   unsigned long long* sort_state;
   const unsigned long long* sort_prev_in;
   unsigned long long* sort_prev_out;
+  // LOG sink with the exchange fused in (exchange.cu, vgpu_agg_attach_exchange): entries do not enter the local log but
+  // leave for their owners' windows as they are produced.  CTA c owns sub-region c of the region this rank has in every
+  // destination's window (send_sub_cap entries; front entries from its start, back entries from its end) and keeps
+  // its counts in send_counts[c * send_world + d] (low 32 bits front, high 32 back; carried from launch to launch);
+  // at its end it also stores them into the destination's window (send_peer_counts[d][c]).
+  int32_t send_world;           // 0 = off
+  int32_t send_hash;            // 1: one raw BIGINT key, owner = HashPartitionFunction's hash (device_common.cuh partition_of)
+  uint64_t send_sub_cap;
+  uint64_t* send_base[8];
+  unsigned long long* send_peer_counts[8];
+  unsigned long long* send_counts;
   // FILTER_PROJECT sink
   uint32_t* sel_words;
   int32_t* tile_counts;

@@ -334,6 +334,15 @@ class Exchange:
         abi.check(abi.lib().vgpu_comm_last_counts(self.handle, m, stream_ptr()))
         return np.array(list(m), dtype=np.int64).reshape(self.world, self.world)
 
+    def attach(self, partial: "Aggregation"):
+        """vgpu_agg_attach_exchange: the partial aggregation's scans store their entries straight into the owners'
+        windows (needs reserve_window); shuffle() then only exchanges counts and deduplicates."""
+        abi.check(abi.lib().vgpu_agg_attach_exchange(partial.handle, self.handle))
+
+    @staticmethod
+    def detach(partial: "Aggregation"):
+        abi.check(abi.lib().vgpu_agg_attach_exchange(partial.handle, None))
+
     @staticmethod
     def make_unique_id() -> bytes:
         idbuf = (C.c_uint8 * abi.COMM_ID_BYTES)()
@@ -407,6 +416,39 @@ def exchange_local(partials, finals, window_bytes=256 << 20):
     pa = (C.c_void_p * w)(*[p.handle for p in partials])
     fa = (C.c_void_p * w)(*[f.handle for f in finals])
     abi.check(abi.lib().vgpu_debug_exchange_local(pa, fa, w, window_bytes, stream_ptr()))
+
+
+class LocalExchangeGroup:
+    """`world` ranks of a window exchange on this one GPU (vgpu_debug_local_comms): for tests and smoke() of the exchange
+    fused into the scan.  attach(r, partial) before the partial's add_input; shuffle(partials, finals) for all ranks."""
+
+    def __init__(self, world: int, window_bytes=256 << 20):
+        self.world = world
+        self.handles = (C.c_void_p * world)()
+        abi.check(abi.lib().vgpu_debug_local_comms(world, window_bytes, self.handles))
+
+    def attach(self, rank: int, partial: "Aggregation"):
+        abi.check(abi.lib().vgpu_agg_attach_exchange(partial.handle, self.handles[rank]))
+
+    def shuffle(self, partials, finals):
+        w = self.world
+        pa = (C.c_void_p * w)(*[p.handle for p in partials])
+        fa = (C.c_void_p * w)(*[f.handle for f in finals])
+        abi.check(abi.lib().vgpu_debug_exchange_local_comms(self.handles, pa, fa, w, stream_ptr()))
+
+    def close(self):
+        if self.handles is not None:
+            torch.cuda.synchronize()
+            for h in self.handles:
+                if h:
+                    abi.lib().vgpu_comm_destroy(C.c_void_p(h))
+            self.handles = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def plan_alltoall(send_rows, recv_rows, row_bytes):
