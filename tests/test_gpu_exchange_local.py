@@ -157,3 +157,24 @@ def test_fused_exchange_really_streams_and_falls_back(engine):
             partials[0].finalize()
             assert partials[0].num_groups() > 1000
         group.close()
+
+
+@pytest.mark.parametrize("world", [4, 8])
+def test_fused_exchange_narrow_entries_many_ranks(engine, world):
+    # one accumulator = two-word entries: the shape of config C5, whose streaming kernel keeps per-owner buffers for up
+    # to 8 ranks; unsorted keys shared between the ranks plus sorted private ranges, two batches, two rounds
+    rng = np.random.default_rng(400 + world)
+    accs = [(abi.ACC_SUM_F64, 1)]
+    shards, allk, allv = [], [], []
+    for r in range(world):
+        own = np.repeat(10_000_000 + 3 * (r * 30_000 + np.arange(30_000, dtype=np.int64)), rng.integers(1, 6, 30_000))
+        shared = rng.integers(-5, 4000, 20_000).astype(np.int64)
+        k = np.concatenate([own, shared])
+        v = rng.integers(1, 1000, len(k)) * 0.5
+        shards.append([(k, None), (v, None)])
+        allk.append(k); allv.append(v)
+    outs = [ex.col(0, I64), ex.col(1, D)]
+    got = exchange(engine, world, abi.AGG_HASH, None, outs, [I64, D], shards, RAW_KEY, accs, fused=True, batches=2, steps=2)
+    k, v = np.concatenate(allk), np.concatenate(allv)
+    want = H.run_oracle_agg(None, outs, [(k, None), (v, None)], len(k), RAW_KEY, accs)
+    H.assert_groups_equal(union_of(got), want, accs)

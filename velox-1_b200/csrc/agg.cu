@@ -749,7 +749,11 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
       fk = fused_prepare(p, &fgrid);
       if (fused_dry_run()) return VGPU_OK;
       if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
-      if (fk && send) {
+      if (!fk && send && !a.send_used) { // the streaming variant does not cover this shape (entry too wide for its buffers): log locally
+        p.send_world = 0; p.send_hash = 0;
+        fk = fused_prepare(p, &fgrid);
+        if (!fk && fused_strict_failure()) return VGPU_ERR_INVALID;
+      } else if (fk && send) {
         rc = send_bind(a, p, fgrid, stream);
         if (rc == VGPU_ERR_UNSUPPORTED && !a.send_used) { // log locally instead; the exchange partitions afterwards
           p.send_world = 0; p.send_hash = 0;

@@ -613,6 +613,8 @@ struct Gen {
   // (send mode: into the warp's staging area instead, with the entry's kind beside it)
   bool send_mode() const { return p.mode == kSinkLog && p.send_world > 0; }
   static constexpr int kSendStage = 160; // entries a warp can produce per block: 5 per lane
+  // per warp: the staging area (entries, kinds), the per-owner fill counts, the per-owner buffers (fused_prelude.cuh kSendBuf)
+  int send_warp_words() const { return kSendStage * p.log_entry_words + kSendStage / 8 + 4 + p.send_world * 48 * p.log_entry_words; }
   void gen_log_store(const char* cond, const char* off, const char* key, const char* vsuffix, const char* kind) {
     const int EW = p.log_entry_words;
     out("      if (%s) {\n        u64* e = %s + (u64)%s * %d;\n", cond, send_mode() ? "wl" : "region", off, EW);
@@ -796,7 +798,7 @@ struct Gen {
     }
     out("    }\n");
     gen_log_store("KIND[4] != 0u", "OFF[4]", "SK4", "_4", "KIND[4]");
-    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
+    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, wbuf, wcnt, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
     out("    ck = nk; cn = nn; chave = nhave; cedge = nedge;\n");
     for (int i = 0; i < n_live; ++i) out("    cv%d = nv%d;\n", live_cells[i], live_cells[i]);
   }
@@ -858,7 +860,7 @@ struct Gen {
     if (send_mode()) out("    const u32 stot = warp_compact<1>(K1, O1);\n");
     else out("    log_reserve<1>(logcur, (u32)p.log_region_cap, K1, O1);\n");
     gen_log_store("K1[0] != 0u", "O1[0]", "SK4", "_4", "K1[0]");
-    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
+    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, wbuf, wcnt, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
     out("    (void)SN4;\n  }\n");
   }
 
@@ -999,8 +1001,8 @@ struct Gen {
     plan.smem_bytes = 0;
     if (send_mode()) {
       if (p.send_world > 8) { decline("fused exchange: more than 8 ranks"); return; }
-      plan.smem_bytes = (NT / 32) * (kSendStage * p.log_entry_words + kSendStage / 8) * 8;
-      if (plan.smem_bytes * CTAS > 200 * 1024) { decline("fused exchange: staging area exceeds shared memory"); return; }
+      plan.smem_bytes = (NT / 32) * send_warp_words() * 8;
+      if ((plan.smem_bytes + 2048) * CTAS > 224 * 1024) { decline("fused exchange: staging area exceeds shared memory"); return; }
     }
     out("#define NT %d\n", NT);
     out("using namespace vgf;\n");
@@ -1029,11 +1031,14 @@ struct Gen {
     if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
     if (p.mode == kSinkLog) {
       if (send_mode()) {
-        const int W = p.send_world, words = kSendStage * p.log_entry_words + kSendStage / 8;
+        const int W = p.send_world, words = send_warp_words();
         out("  extern __shared__ __align__(16) u64 sendstage[];\n  __shared__ unsigned long long sendcur[%d];\n", W);
         out("  if (threadIdx.x < %d) sendcur[threadIdx.x] = p.send_counts[blockIdx.x * %d + threadIdx.x];\n  __syncthreads();\n", W, W);
         out("  u64* const wl = sendstage + (threadIdx.x >> 5) * %d;\n", words);
         out("  unsigned char* const wk = reinterpret_cast<unsigned char*>(wl + %d);\n", kSendStage * p.log_entry_words);
+        out("  u32* const wcnt = reinterpret_cast<u32*>(wl + %d);\n", kSendStage * p.log_entry_words + kSendStage / 8);
+        out("  u64* const wbuf = wl + %d;\n", kSendStage * p.log_entry_words + kSendStage / 8 + 4);
+        out("  if ((threadIdx.x & 31) < 8) wcnt[threadIdx.x & 31] = 0u;\n  __syncwarp();\n");
       } else {
         out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
         out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
@@ -1097,6 +1102,7 @@ struct Gen {
       gen_log_epilogue();
       if (send_mode()) {
         // the counts stay with this rank for the next launch and go to each owner's window beside the entries
+        out("  send_drain<%d, %d>(p, sendcur, wbuf, wcnt, accerr);\n", p.log_entry_words, p.send_world);
         out("  __syncthreads();\n  if (threadIdx.x < %d) {\n    p.send_counts[blockIdx.x * %d + threadIdx.x] = sendcur[threadIdx.x];\n", p.send_world, p.send_world);
         out("    p.send_peer_counts[threadIdx.x][blockIdx.x] = sendcur[threadIdx.x];\n  }\n");
       } else
