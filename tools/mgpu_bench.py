@@ -75,6 +75,21 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
     if fused:
         exchange.attach(partial)                               # the scan itself stores the entries into the owners' windows
     ms_full = timed(True) if fused else ms_classic
+    scan_ms = None
+    if os.environ.get("VGPU_BENCH_PHASES"):  # diagnostic: the scan kernel's own duration inside the full step (events around it)
+        import ctypes as C
+        lib = abi.lib()
+        lib.vgpu_debug_kernel_timing(1)
+        for _ in range(5):
+            step(True)
+        sync()
+        tot, cnt = C.c_double(), C.c_int64()
+        lib.vgpu_debug_kernel_time(C.byref(tot), C.byref(cnt))
+        lib.vgpu_debug_kernel_timing(0)
+        t = torch.tensor([tot.value / max(cnt.value, 1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        scan_ms = float(t[0])
     engine.check_errors()
     result = final if world > 1 else partial
     rows = torch.from_numpy(result.extract()).cuda()          # [groups here, 5]: key, flags, rows, sum, nn
@@ -106,6 +121,7 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
         "ms_exchange_and_final": ex_ms if world > 1 else 0.0, "rows_per_s": n * world / (ms_full * 1e-3),
         "exchanged_bytes_per_step": int(mine[3]),
         "ms_per_step_unfused": ms_classic,
+        "ms_scan_kernel_in_step": scan_ms,
         "nvlink_gbs_per_gpu_out": (float(mine[3]) / world / ((ms_full if fused else ex_ms) * 1e-3) / 1e9) if world > 1 else 0.0,
         "exchange_path": ("window, fused into the scan: the LOG-sink kernel stores each entry into its owner's window over NVLink while it scans; counts and stream facts in one ncclAllGather" if fused
                           else "window: partition + NVLink peer stores in one kernel, counts in one ncclAllGather" if mapped and os.environ.get("VGPU_EXCHANGE") != "nccl"

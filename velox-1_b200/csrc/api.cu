@@ -258,7 +258,7 @@ static int report_error_bits(uint32_t bits) {
   else if (bits & kErrCastRange) set_error("Cannot cast value: out of range or NaN");
   else if (bits & kErrKeyRange) { set_error("grouping key outside the declared domain"); return VGPU_ERR_INVALID; }
   else if (bits & kErrStringKey) { set_error("VARCHAR value longer than 7 bytes read on the device (map long strings to ids on the host)"); return VGPU_ERR_UNSUPPORTED; }
-  else { set_error("internal: hash table full"); return VGPU_ERR_INVALID; }
+  else { set_error("internal: a device table or an exchange window region is full (hash table, log region, or the per-CTA share of vgpu_comm_reserve_window's window)"); return VGPU_ERR_INVALID; }
   return VGPU_ERR_USER;
 }
 

@@ -842,12 +842,12 @@ namespace {
 constexpr int kSendMaxGrid = 1024;
 constexpr size_t kSendCountsBytes = (size_t)kSendMaxGrid * sizeof(unsigned long long);
 static_assert(kSendCountsBytes == kFusedCountsBytes, "one layout");
-constexpr uint64_t kSendMinSubCap = 256;
+constexpr uint64_t kSendMinSubCap = 1024; // of which fused_prelude.cuh kSendBackRoom (256) are kept for back entries
 
 uint64_t send_sub_cap_for(const vgpu_comm_s* comm, int ew, int grid) {
   const size_t head = special_slot_bytes(ew) + kSendCountsBytes;
   if (region_bytes(comm) <= head) return 0;
-  return (region_bytes(comm) - head) / ((size_t)ew * 8) / (size_t)grid;
+  return ((region_bytes(comm) - head) / ((size_t)ew * 8) / (size_t)grid) & ~(size_t)15; // whole runs of 16 entries
 }
 } // namespace
 

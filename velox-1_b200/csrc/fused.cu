@@ -612,13 +612,40 @@ struct Gen {
   // Stores one entry (key SKx, values SVx<c>) at offset OFFx of the CTA's region.
   // (send mode: into the warp's staging area instead, with the entry's kind beside it)
   bool send_mode() const { return p.mode == kSinkLog && p.send_world > 0; }
-  static constexpr int kSendStage = 160; // entries a warp can produce per block: 5 per lane
+  static constexpr int kSendStage = 192; // fused_prelude.cuh kSendRing: 5 entries per lane per block + up to 31 pending
   // per warp: the staging area (entries, kinds), the per-owner fill counts, the per-owner buffers (fused_prelude.cuh kSendBuf)
-  int send_warp_words() const { return kSendStage * p.log_entry_words + kSendStage / 8 + 4 + p.send_world * 48 * p.log_entry_words; }
+  int send_warp_words() const { return kSendStage * p.log_entry_words + 4 + p.send_world * 48 * p.log_entry_words; }
+  std::string send_targs() const { return std::to_string(p.log_entry_words) + ", " + std::to_string(p.send_world) + ", " + (p.send_hash ? "true" : "false"); }
+  // Entry (key, values SV<c><vsuffix>) of kind `kind` in send mode: front entries into the warp's ring at `off`, back
+  // entries straight to their owner.
+  void gen_send_store(const char* kind, const char* off, const char* key, const char* vsuffix) {
+    const int EW = p.log_entry_words;
+    std::string vals;
+    for (int i = 0; i < p.log_n_cells; ++i) {
+      const int c = p.log_cells[i];
+      vals += ", SV" + std::to_string(p.cells[c].skip ? 0 : c) + vsuffix;
+    }
+    for (int w = 1 + p.log_n_cells; w < EW; ++w) vals += ", 0ull";
+    out("      if (%s == 1u) {\n        u32 at = sbeg + spend + %s; if (at >= %du) at -= %du;\n        u64* e = wl + (u64)at * %d;\n", kind, off, kSendStage, kSendStage, EW);
+    if (EW == 2) {
+      const int c = p.log_cells[0];
+      out("        *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(%s, SV%d%s);\n", key, p.cells[c].skip ? 0 : c, vsuffix);
+    } else {
+      out("        const u64 ent[%d] = {%s%s};\n        _Pragma(\"unroll\") for (int w = 0; w < %d; ++w) e[w] = ent[w];\n", EW, key, vals.c_str(), EW);
+    }
+    out("      } else if (%s == 2u) {\n        const u64 ent[%d] = {%s%s};\n", kind, EW, key, vals.c_str());
+    out("        send_back<%s>(scap, sfront, sback, sbase, ent, accerr);\n      }\n", send_targs().c_str());
+  }
+  // After the stores: whole steps of 32 entries leave the ring.
+  void gen_send_steps(const char* added) {
+    out("    __syncwarp();\n    spend += %s;\n", added);
+    out("    while (spend >= 32u) {\n      send_step<%s>(scap, sfront, sback, sbase, wl, wbuf, wcnt, sbeg, 32u, accerr);\n", send_targs().c_str());
+    out("      sbeg += 32u; if (sbeg >= %du) sbeg -= %du;\n      spend -= 32u;\n    }\n", kSendStage, kSendStage);
+  }
   void gen_log_store(const char* cond, const char* off, const char* key, const char* vsuffix, const char* kind) {
     const int EW = p.log_entry_words;
-    out("      if (%s) {\n        u64* e = %s + (u64)%s * %d;\n", cond, send_mode() ? "wl" : "region", off, EW);
-    if (send_mode()) out("        wk[%s] = (unsigned char)%s;\n", off, kind);
+    if (send_mode()) { gen_send_store(kind, off, key, vsuffix); return; }
+    out("      if (%s) {\n        u64* e = region + (u64)%s * %d;\n", cond, off, EW);
     if (EW == 2) {
       const int c = p.log_cells[0];
       out("        *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(%s, SV%d%s);\n", key, p.cells[c].skip ? 0 : c, vsuffix);
@@ -777,13 +804,14 @@ struct Gen {
     out("      KIND[4] = !SA4 || special ? 0u : (cedge ? 2u : 1u);\n");
     gen_log_special("SA4 && special", "SN4", "_4");
     out("    }\n");
-    if (send_mode()) out("    u32 OFF[5]; const u32 stot = warp_compact<5>(KIND, OFF);\n");
+    if (send_mode()) out("    u32 OFF[5]; const u32 sadd = warp_compact_front<5>(KIND, OFF);\n");
     else out("    u32 OFF[5]; log_reserve<5>(logcur, (u32)p.log_region_cap, KIND, OFF);\n");
     out("    _Pragma(\"unroll\") for (int sgm = 0; sgm < 4; ++sgm) {\n      if (KIND[sgm] == 0u) continue;\n");
-    {
+    if (send_mode()) {
+      gen_send_store("KIND[sgm]", "OFF[sgm]", "SK[sgm]", "[sgm]");
+    } else {
       const int EW = p.log_entry_words;
-      out("      u64* e = %s + (u64)OFF[sgm] * %d;\n", send_mode() ? "wl" : "region", EW);
-      if (send_mode()) out("      wk[OFF[sgm]] = (unsigned char)KIND[sgm];\n");
+      out("      u64* e = region + (u64)OFF[sgm] * %d;\n", EW);
       if (EW == 2) {
         const int c = p.log_cells[0];
         out("      *reinterpret_cast<ulonglong2*>(e) = make_ulonglong2(SK[sgm], SV%d[sgm]);\n", p.cells[c].skip ? 0 : c);
@@ -798,7 +826,7 @@ struct Gen {
     }
     out("    }\n");
     gen_log_store("KIND[4] != 0u", "OFF[4]", "SK4", "_4", "KIND[4]");
-    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, wbuf, wcnt, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
+    if (send_mode()) gen_send_steps("sadd");
     out("    ck = nk; cn = nn; chave = nhave; cedge = nedge;\n");
     for (int i = 0; i < n_live; ++i) out("    cv%d = nv%d;\n", live_cells[i], live_cells[i]);
   }
@@ -857,10 +885,10 @@ struct Gen {
     for (int i = 0; i < n_live; ++i) out("    u64 SV%d_4 = cv%d;\n", live_cells[i], live_cells[i]);
     gen_log_special("lane == 0 && special", "SN4", "_4");
     out("    u32 K1[1] = {lane == 0 && !special ? (edge ? 2u : 1u) : 0u}, O1[1];\n");
-    if (send_mode()) out("    const u32 stot = warp_compact<1>(K1, O1);\n");
+    if (send_mode()) out("    const u32 sadd = warp_compact_front<1>(K1, O1);\n");
     else out("    log_reserve<1>(logcur, (u32)p.log_region_cap, K1, O1);\n");
     gen_log_store("K1[0] != 0u", "O1[0]", "SK4", "_4", "K1[0]");
-    if (send_mode()) out("    __syncwarp();\n    send_entries<%d, %d, %s>(p, sendcur, wl, wk, wbuf, wcnt, stot, accerr);\n", p.log_entry_words, p.send_world, p.send_hash ? "true" : "false");
+    if (send_mode()) gen_send_steps("sadd");
     out("    (void)SN4;\n  }\n");
   }
 
@@ -1002,7 +1030,7 @@ struct Gen {
     if (send_mode()) {
       if (p.send_world > 8) { decline("fused exchange: more than 8 ranks"); return; }
       plan.smem_bytes = (NT / 32) * send_warp_words() * 8;
-      if ((plan.smem_bytes + 2048) * CTAS > 224 * 1024) { decline("fused exchange: staging area exceeds shared memory"); return; }
+      if ((plan.smem_bytes + 1280) * CTAS > 227 * 1024) { decline("fused exchange: staging area exceeds shared memory"); return; }
     }
     out("#define NT %d\n", NT);
     out("using namespace vgf;\n");
@@ -1031,14 +1059,18 @@ struct Gen {
     if (p.mode == kSinkHash) out("  u32 inserted = 0;\n");
     if (p.mode == kSinkLog) {
       if (send_mode()) {
-        const int W = p.send_world, words = send_warp_words();
-        out("  extern __shared__ __align__(16) u64 sendstage[];\n  __shared__ unsigned long long sendcur[%d];\n", W);
-        out("  if (threadIdx.x < %d) sendcur[threadIdx.x] = p.send_counts[blockIdx.x * %d + threadIdx.x];\n  __syncthreads();\n", W, W);
+        const int W = p.send_world, words = send_warp_words(), EW = p.log_entry_words;
+        out("  extern __shared__ __align__(16) u64 sendstage[];\n");
+        out("  __shared__ u32 sfront[%d], sback[%d];\n  __shared__ u64* sbase[%d];\n", W, W, W);
+        out("  const u32 scap = (u32)p.send_sub_cap;\n");
+        out("  if (threadIdx.x < %d) {\n    const unsigned long long c = p.send_counts[blockIdx.x * %d + threadIdx.x];\n", W, W);
+        out("    sfront[threadIdx.x] = (u32)c; sback[threadIdx.x] = (u32)(c >> 32);\n");
+        out("    sbase[threadIdx.x] = p.send_base[threadIdx.x] + (u64)blockIdx.x * p.send_sub_cap * %d;\n  }\n  __syncthreads();\n", EW);
         out("  u64* const wl = sendstage + (threadIdx.x >> 5) * %d;\n", words);
-        out("  unsigned char* const wk = reinterpret_cast<unsigned char*>(wl + %d);\n", kSendStage * p.log_entry_words);
-        out("  u32* const wcnt = reinterpret_cast<u32*>(wl + %d);\n", kSendStage * p.log_entry_words + kSendStage / 8);
-        out("  u64* const wbuf = wl + %d;\n", kSendStage * p.log_entry_words + kSendStage / 8 + 4);
+        out("  u32* const wcnt = reinterpret_cast<u32*>(wl + %d);\n", kSendStage * EW);
+        out("  u64* const wbuf = wl + %d;\n", kSendStage * EW + 4);
         out("  if ((threadIdx.x & 31) < 8) wcnt[threadIdx.x & 31] = 0u;\n  __syncwarp();\n");
+        out("  u32 sbeg = 0u, spend = 0u; // the warp's ring: first pending entry, pending entries\n");
       } else {
         out("  __shared__ u32 logcur[2];\n  if (threadIdx.x == 0) { logcur[0] = 0u; logcur[1] = 0u; }\n  __syncthreads();\n");
         out("  u64* const region = p.log + (u64)blockIdx.x * p.log_region_cap * %d;\n", p.log_entry_words);
@@ -1102,9 +1134,10 @@ struct Gen {
       gen_log_epilogue();
       if (send_mode()) {
         // the counts stay with this rank for the next launch and go to each owner's window beside the entries
-        out("  send_drain<%d, %d>(p, sendcur, wbuf, wcnt, accerr);\n", p.log_entry_words, p.send_world);
-        out("  __syncthreads();\n  if (threadIdx.x < %d) {\n    p.send_counts[blockIdx.x * %d + threadIdx.x] = sendcur[threadIdx.x];\n", p.send_world, p.send_world);
-        out("    p.send_peer_counts[threadIdx.x][blockIdx.x] = sendcur[threadIdx.x];\n  }\n");
+        out("  send_drain<%s>(scap, sfront, sback, sbase, wl, wbuf, wcnt, sbeg, spend, accerr);\n", send_targs().c_str());
+        // the counts stay with this rank for the next launch and go to each owner's window beside the entries
+        out("  __syncthreads();\n  if (threadIdx.x < %d) {\n    const unsigned long long c = (unsigned long long)sfront[threadIdx.x] | ((unsigned long long)sback[threadIdx.x] << 32);\n", p.send_world);
+        out("    p.send_counts[blockIdx.x * %d + threadIdx.x] = c;\n    p.send_peer_counts[threadIdx.x][blockIdx.x] = c;\n  }\n", p.send_world);
       } else
       out("  __syncthreads();\n  if (threadIdx.x == 0) { p.log_counts[2 * blockIdx.x] = logcur[0]; p.log_counts[2 * blockIdx.x + 1] = logcur[1]; }\n");
       if (p.sorted_probe) out("  if (__any_sync(0xffffffffu, viol) && lane == 0) atomicOr(p.sort_state, 1ull);\n");

@@ -608,13 +608,23 @@ __device__ __forceinline__ void log_reserve(u32* cur /* [2] in shared memory */,
 }
 
 // ---- LOG sink with the exchange fused in ----------------------------------------------------------
-// Places of the lane's active segments in the warp's staging area (kind != 0), in lane order; returns the warp's total.
+// Entries do not enter a local log: FRONT entries (complete runs) are compacted into a per-warp ring in shared memory
+// (kSendRing entries), taken from there 32 at a time, hashed to their owner and appended to a per-owner ring
+// (kSendBuf = 3 runs of kSendRun entries); a full run leaves as one aligned store of kSendRun entries into the owner's
+// peer-mapped window (measured on 8 GPUs: 64-byte runs reach ~1/3 of the NVLink rate, aligned 256-byte runs ~2/3).
+// BACK entries (the runs at the two ends of a warp's range: rare) are stored one by one at the end of the sub-region.
+// Per CTA and owner: sfront / sback count the entries stored so far, sbase is the CTA's sub-region in that window.
+// The last kSendBackRoom entries of a sub-region are kept for back entries, so that both sides check their own
+// counter against a constant (no second counter to read on the hot path).
+constexpr u32 kSendRing = 192, kSendRun = 16, kSendBuf = 48, kSendBackRoom = 256;
+
+// Places (after `pend` pending entries) of the lane's front segments in the warp's ring; returns how many were added.
 template <int N>
-__device__ __forceinline__ u32 warp_compact(const u32 (&kind)[N], u32 (&off)[N]) {
+__device__ __forceinline__ u32 warp_compact_front(const u32 (&kind)[N], u32 (&off)[N]) {
   const u32 lane = threadIdx.x & 31u;
   u32 mine = 0;
 #pragma unroll
-  for (int s = 0; s < N; ++s) mine += kind[s] != 0u ? 1u : 0u;
+  for (int s = 0; s < N; ++s) mine += kind[s] & 1u;
   u32 incl = mine;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -623,7 +633,7 @@ __device__ __forceinline__ u32 warp_compact(const u32 (&kind)[N], u32 (&off)[N])
   }
   u32 at = incl - mine;
 #pragma unroll
-  for (int s = 0; s < N; ++s) { off[s] = at; at += kind[s] != 0u ? 1u : 0u; }
+  for (int s = 0; s < N; ++s) { off[s] = at; at += kind[s] & 1u; }
   return __shfl_sync(0xffffffffu, incl, 31);
 }
 // Owner of a group among W ranks: device_common.cuh partition_of with W known at compile time (VELOX: one raw BIGINT
@@ -646,83 +656,88 @@ __device__ __forceinline__ u32 send_dest(u64 key) {
   }
   return (u32)(k % (u64)W);
 }
-// Front entries do not cross NVLink one by one: the warp keeps a small buffer per owner in shared memory and stores a
-// buffer as one contiguous run once it holds kSendFlush entries (>= 256 bytes; measured on 8 GPUs: 64-byte runs reach
-// ~1/3 of the link rate).  kSendBuf = kSendFlush + 32: one step adds at most 32 entries to one owner.
-constexpr u32 kSendFlush = 16, kSendBuf = 48;
-// Stores owner d's buffered entries (c > 0) behind the front entries this CTA has sent to d so far.
-template <int EW>
-__device__ __forceinline__ void send_flush(const FusedParams& p, unsigned long long* sendcur, const u64* buf, u32 d, u32 c, u32& err) {
-  const u32 lane = threadIdx.x & 31u;
-  unsigned long long base = 0ull;
-  if (lane == 0) base = atomicAdd(&sendcur[d], (unsigned long long)c);
-  base = __shfl_sync(0xffffffffu, base, 0);
-  const u64 front = base & 0xffffffffull, back = base >> 32;
-  if (front + back + c > p.send_sub_cap) { err |= VGF_ERR_TABLEFULL; return; } // the window is too small for this CTA's share
-  u64* out = p.send_base[d] + ((u64)blockIdx.x * p.send_sub_cap + front) * EW;
-  if (EW == 2) {
-    for (u32 i = lane; i < c; i += 32u) reinterpret_cast<ulonglong2*>(out)[i] = reinterpret_cast<const ulonglong2*>(buf)[i];
-  } else {
-    for (u32 i = lane; i < c * (u32)EW; i += 32u) out[i] = buf[i];
-  }
-}
-// The warp's `tot` staged entries (wl: EW words each; wk: 1 = front, 2 = back) go to their owners: front entries into
-// the owner's buffer (wbuf: W buffers of kSendBuf entries, wcnt: their fill), flushed when full enough; back entries
-// (rare: the runs at the ends of a warp's range) straight to the end of the owner's sub-region.
+// One BACK entry, straight to the end of its owner's sub-region (called by the one lane that holds it).
 template <int EW, int W, bool VELOX>
-__device__ __forceinline__ void send_entries(const FusedParams& p, unsigned long long* sendcur, const u64* wl, const unsigned char* wk,
-                                             u64* wbuf, u32* wcnt, u32 tot, u32& err) {
-  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-  for (u32 i0 = 0; i0 < tot; i0 += 32u) {
-    const u32 i = i0 + lane;
-    const bool act = i < tot;
-    const u64 key = act ? wl[(size_t)i * EW] : 0ull;
-    const u32 kind = act ? (u32)wk[i] : 0u;
-    const u32 dest = send_dest<W, VELOX>(key);
-    const u32 tag = kind == 1u ? dest : (kind == 2u ? 64u + lane : 0xffffffffu);
-    const u32 m = __match_any_sync(0xffffffffu, tag);
-    if (kind == 1u) {
-      const u32 at = wcnt[dest] + (u32)__popc(m & lt);
-      u64* b = wbuf + ((size_t)dest * kSendBuf + at) * EW;
-      const u64* e = wl + (size_t)i * EW;
-      if (EW == 2) *reinterpret_cast<ulonglong2*>(b) = *reinterpret_cast<const ulonglong2*>(e);
-      else { _Pragma("unroll") for (int w = 0; w < EW; ++w) b[w] = e[w]; }
-    } else if (kind == 2u) {
-      const unsigned long long base = atomicAdd(&sendcur[dest], 1ull << 32);
-      const u64 front = base & 0xffffffffull, back = base >> 32;
-      if (front + back + 1ull > p.send_sub_cap) {
-        err |= VGF_ERR_TABLEFULL;
-      } else {
-        u64* out = p.send_base[dest] + ((u64)blockIdx.x * p.send_sub_cap + (p.send_sub_cap - 1ull - back)) * EW;
-        const u64* e = wl + (size_t)i * EW;
-        _Pragma("unroll") for (int w = 0; w < EW; ++w) out[w] = e[w];
-      }
-    }
-    __syncwarp();
-    if (kind == 1u && (m & lt) == 0u) wcnt[dest] += (u32)__popc(m); // the first lane of each owner's group
-    __syncwarp();
-    const u32 mine = lane < (u32)W ? wcnt[lane] : 0u;
-    u32 full = __ballot_sync(0xffffffffu, mine >= kSendFlush);
-    while (full) {
-      const u32 d = (u32)__ffs((int)full) - 1u;
-      full &= full - 1u;
-      send_flush<EW>(p, sendcur, wbuf + (size_t)d * kSendBuf * EW, d, __shfl_sync(0xffffffffu, mine, (int)d), err);
-      if (lane == d) wcnt[d] = 0u;
-    }
-    __syncwarp();
+__device__ __noinline__ void send_back(u32 cap, u32* sfront, u32* sback, u64* const* sbase, const u64* ent, u32& err) {
+  const u32 d = send_dest<W, VELOX>(ent[0]);
+  const u32 back = atomicAdd(&sback[d], 1u);
+  if (back >= kSendBackRoom) { err |= VGF_ERR_TABLEFULL; return; } // more range ends than a sub-region keeps room for
+  u64* out = sbase[d] + (size_t)(cap - 1u - back) * EW;
+#pragma unroll
+  for (int w = 0; w < EW; ++w) out[w] = ent[w];
+}
+// Stores `go` (<= 32) entries of owner d's ring, starting at `head`, behind the front entries sent to d so far.
+template <int EW>
+__device__ __forceinline__ void send_run(u32 cap, u32* sfront, const u32* sback, u64* const* sbase, const u64* buf, u32 d, u32 head, u32 go, u32& err) {
+  const u32 lane = threadIdx.x & 31u;
+  u32 front = 0;
+  if (lane == 0) front = atomicAdd(&sfront[d], go);
+  front = __shfl_sync(0xffffffffu, front, 0);
+  if (front + go > cap - kSendBackRoom) { err |= VGF_ERR_TABLEFULL; return; } // the window is too small for this CTA's share
+  if (lane < go) {
+    u32 src = head + lane;
+    if (src >= kSendBuf) src -= kSendBuf;
+    u64* out = sbase[d] + (size_t)(front + lane) * EW;
+    const u64* e = buf + (size_t)src * EW;
+    if (EW == 2) *reinterpret_cast<ulonglong2*>(out) = *reinterpret_cast<const ulonglong2*>(e);
+    else { _Pragma("unroll") for (int w = 0; w < EW; ++w) out[w] = e[w]; }
   }
 }
-// End of the kernel: what is left in the warp's buffers.
-template <int EW, int W>
-__device__ __forceinline__ void send_drain(const FusedParams& p, unsigned long long* sendcur, const u64* wbuf, u32* wcnt, u32& err) {
-  const u32 lane = threadIdx.x & 31u;
+// Takes `n` (<= 32) entries from the warp's ring at `beg`, routes them to the owners' rings (wcnt[d] = head | fill << 8)
+// and sends every full run.
+template <int EW, int W, bool VELOX>
+__device__ __forceinline__ void send_step(u32 cap, u32* sfront, const u32* sback, u64* const* sbase, const u64* wl, u64* wbuf, u32* wcnt,
+                                          u32 beg, u32 n, u32& err) {
+  const u32 lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  const bool act = lane < n;
+  u32 idx = beg + lane;
+  if (idx >= kSendRing) idx -= kSendRing;
+  u64 ent[EW];
+#pragma unroll
+  for (int w = 0; w < EW; ++w) ent[w] = 0ull;
+  if (act) {
+    if (EW == 2) { const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wl + (size_t)idx * 2); ent[0] = v.x; ent[1] = v.y; }
+    else { _Pragma("unroll") for (int w = 0; w < EW; ++w) ent[w] = wl[(size_t)idx * EW + w]; }
+  }
+  const u32 dest = send_dest<W, VELOX>(ent[0]);
+  const u32 m = __match_any_sync(0xffffffffu, act ? dest : 0xffffffffu);
+  if (act) {
+    const u32 st = wcnt[dest];
+    u32 at = (st & 0xffu) + (st >> 8) + (u32)__popc(m & lt);
+    if (at >= kSendBuf) at -= kSendBuf;
+    u64* b = wbuf + ((size_t)dest * kSendBuf + at) * EW;
+    if (EW == 2) *reinterpret_cast<ulonglong2*>(b) = make_ulonglong2(ent[0], ent[1]);
+    else { _Pragma("unroll") for (int w = 0; w < EW; ++w) b[w] = ent[w]; }
+  }
+  __syncwarp();
+  if (act && (m & lt) == 0u) wcnt[dest] += (u32)__popc(m) << 8; // the first lane of each owner's group
   __syncwarp();
   const u32 mine = lane < (u32)W ? wcnt[lane] : 0u;
-  u32 left = __ballot_sync(0xffffffffu, mine > 0u);
+  u32 full = __ballot_sync(0xffffffffu, (mine >> 8) >= kSendRun);
+  while (full) {
+    const u32 d = (u32)__ffs((int)full) - 1u;
+    full &= full - 1u;
+    const u32 st = __shfl_sync(0xffffffffu, mine, (int)d), head = st & 0xffu, fill = st >> 8;
+    const u32 go = fill & ~(kSendRun - 1u); // whole runs only: the owner's cursor stays aligned to the run size
+    send_run<EW>(cap, sfront, sback, sbase, wbuf + (size_t)d * kSendBuf * EW, d, head, go, err);
+    if (lane == d) { u32 h = head + go; if (h >= kSendBuf) h -= kSendBuf; wcnt[d] = h | ((fill - go) << 8); }
+  }
+  __syncwarp();
+}
+// End of the kernel: the pending entries of the warp's ring, then whatever is left in the owners' rings.
+template <int EW, int W, bool VELOX>
+__device__ __forceinline__ void send_drain(u32 cap, u32* sfront, const u32* sback, u64* const* sbase, const u64* wl, u64* wbuf, u32* wcnt,
+                                           u32 beg, u32 pend, u32& err) {
+  const u32 lane = threadIdx.x & 31u;
+  if (pend) send_step<EW, W, VELOX>(cap, sfront, sback, sbase, wl, wbuf, wcnt, beg, pend, err);
+  __syncwarp();
+  const u32 mine = lane < (u32)W ? wcnt[lane] : 0u;
+  u32 left = __ballot_sync(0xffffffffu, (mine >> 8) > 0u);
   while (left) {
     const u32 d = (u32)__ffs((int)left) - 1u;
     left &= left - 1u;
-    send_flush<EW>(p, sendcur, wbuf + (size_t)d * kSendBuf * EW, d, __shfl_sync(0xffffffffu, mine, (int)d), err);
+    const u32 st = __shfl_sync(0xffffffffu, mine, (int)d), head = st & 0xffu, fill = st >> 8; // < kSendRun after the step
+    send_run<EW>(cap, sfront, sback, sbase, wbuf + (size_t)d * kSendBuf * EW, d, head, fill, err);
     if (lane == d) wcnt[d] = 0u;
   }
   __syncwarp();
