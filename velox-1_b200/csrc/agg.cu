@@ -633,8 +633,16 @@ static int log_migrate_to_table(Agg& a, cudaStream_t stream) {
   return rc;
 }
 
+int agg_wait_pending(Agg& a, cudaStream_t stream) {
+  if (!a.pending_set) return VGPU_OK;
+  VG_CUDA(cudaStreamWaitEvent(stream, a.pending, 0));
+  a.pending_set = false;
+  return VGPU_OK;
+}
+
 int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t ncols, int64_t nrows,
                   const int32_t* in_rows, int64_t n_in_rows, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   int rc = agg_resolve(a, prog, stream);
   if (rc) return rc;
   a.packed_rows = -1;
@@ -872,6 +880,7 @@ int agg_add_input(Agg& a, const Program& prog, const vgpu_column* cols, int32_t 
 }
 
 int agg_extract_all(Agg& a, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (a.packed_rows >= 0) return VGPU_OK;
   if (!a.resolved) { set_error("aggregation has seen no input; call add_input (an empty batch is fine) first"); return VGPU_ERR_INVALID; }
   size_t max_rows;
@@ -948,6 +957,7 @@ static DoneMap done_map(const RowMap& rm) {
 }
 
 int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (!a.resolved) { set_error("merge_rows before the cell plan is known; call add_input with an empty batch first"); return VGPU_ERR_INVALID; }
   a.packed_rows = -1;
   if (n <= 0) return VGPU_OK;
@@ -978,6 +988,7 @@ int agg_merge_rows(Agg& a, const void* rows, int64_t n, cudaStream_t stream) {
 
 // Small-domain (ARRAY / GLOBAL) exchange helpers: no host synchronisation.
 int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (a.mode == VGPU_AGG_HASH || !a.resolved) { set_error("dense rows need a resolved ARRAY / GLOBAL aggregation"); return VGPU_ERR_INVALID; }
   dense_rows_kernel<<<(a.n_groups + 255) / 256, 256, 0, stream>>>(a.state, a.n_groups, a.rm, (uint64_t*)rows_out);
   VG_CUDA(cudaGetLastError());
@@ -985,6 +996,7 @@ int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream) {
   return VGPU_OK;
 }
 int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int my_part, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (a.mode == VGPU_AGG_HASH || !a.resolved) { set_error("owned-row merge needs a resolved ARRAY / GLOBAL aggregation"); return VGPU_ERR_INVALID; }
   a.packed_rows = -1;
   if (n <= 0) return VGPU_OK;
@@ -995,6 +1007,7 @@ int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int m
 }
 
 int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (n_parts < 1 || n_parts > 32) { set_error("n_parts %d out of range", n_parts); return VGPU_ERR_INVALID; }
   int rc = agg_extract_all(a, stream);
   if (rc) return rc;
@@ -1022,6 +1035,7 @@ int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cuda
 }
 
 int agg_reset(Agg& a, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   a.packed_rows = -1;
   a.emit_empty_global = true;
   if (!a.resolved) return VGPU_OK;
@@ -1051,11 +1065,13 @@ int agg_reset(Agg& a, cudaStream_t stream) {
 }
 
 int agg_finalize(Agg& a, cudaStream_t stream) {
+  { const int wrc = agg_wait_pending(a, stream); if (wrc) return wrc; }
   if (a.mode == VGPU_AGG_HASH && a.engine == kEngineLog) return log_finalize(a, stream);
   return VGPU_OK; // the other sinks keep their groups final after every batch
 }
 
 void agg_free(Agg& a) {
+  if (a.pending) { if (a.pending_set) cudaEventSynchronize(a.pending); cudaEventDestroy(a.pending); a.pending = nullptr; a.pending_set = false; }
   send_free(a);
   log_free(a);
   err_word_release(a.err);

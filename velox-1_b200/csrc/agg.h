@@ -133,6 +133,10 @@ struct Agg {
   uint64_t send_sub_cap = 0;                 // entries per CTA and destination
   bool send_used = false;                    // entries of the current state have left through the window
   uint64_t send_epoch = 0;                   // the exchange's epoch (window half) those entries were stored under
+  // A dense exchange folds into this (final) aggregation on the communicator's side stream (exchange.cu): `pending` is
+  // recorded there after the fold, and the next operation on the aggregation makes its own stream wait for it.
+  cudaEvent_t pending = nullptr;
+  bool pending_set = false;
   bool emit_empty_global = true;  // GLOBAL: this rank reports the (possibly empty) single group
   Agg() { for (int c = 0; c < kMaxCells; ++c) hash_aliased[c] = true; }
 };
@@ -146,6 +150,7 @@ int agg_partition(Agg& a, int n_parts, void* rows_out, int64_t* counts_out, cuda
 int agg_dense_rows(Agg& a, void* rows_out, cudaStream_t stream);
 int agg_merge_owned_rows(Agg& a, const void* rows, int64_t n, int n_parts, int my_part, cudaStream_t stream);
 int agg_reset(Agg& a, cudaStream_t stream);
+int agg_wait_pending(Agg& a, cudaStream_t stream); // orders `stream` after a fold still running on an exchange's side stream
 void agg_free(Agg& a);
 bool agg_raw_bigint_key(const Agg& a); // one raw BIGINT key: partitions are assigned with the reference's own hash
 int agg_finalize(Agg& a, cudaStream_t stream);   // LOG engine: deduplicate what the scans logged (asynchronous)

@@ -439,6 +439,7 @@ int vgpu_agg_finalize(vgpu_agg_t agg, void* stream) {
 int vgpu_agg_check_errors(vgpu_agg_t agg, void* stream) {
   if (!agg) return VGPU_ERR_INVALID;
   if (!agg->agg.err) return VGPU_OK; // no kernel ran yet
+  { const int wrc = agg_wait_pending(agg->agg, (cudaStream_t)stream); if (wrc) return wrc; }
   uint32_t bits = 0;
   VG_CUDA(cudaMemcpyAsync(&bits, agg->agg.err, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));

@@ -233,7 +233,7 @@ struct GpuHashAggregation::Impl {
           }
           total += k.bits;
         }
-        VB_CHECK(total <= 64, "grouping keys do not fit the 64-bit normalized key");
+        VB_CHECK(total <= 63, "grouping keys do not fit the 63 bits of a normalized key (the device rejects wider packings)");
       }
     }
     // a number key is read through a BIGINT operand: the column's StringViews (or host-made numbers) are bound under it
