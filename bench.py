@@ -291,8 +291,8 @@ def run_ours(args, rank, world, local_rank):
         ids = [engine.Exchange.make_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         exchange = engine.Exchange(rank, world, ids[0])
-        # one peer-mapped window for the whole run: sized for the C5 leg's entries (two halves, 1.3 x slack)
-        window = exchange.reserve_window(int(2 * 1.3 * nominal_rows(args.sf) * 1.02 * 16) + (64 << 20))
+        # one peer-mapped window for the whole run: sized for the C5 leg's entries (three parts, 1.3 x slack)
+        window = exchange.reserve_window(int(3 * 1.3 * nominal_rows(args.sf) * 1.02 * 16) + (64 << 20))
 
     # ---- input: this rank's split of TPC-H SF(sf * world), generated on the device (the reference's dbgen streams) ----
     orders_per_rank = int(1500000 * args.sf)

@@ -434,8 +434,10 @@ int vgpu_comm_allgather(vgpu_comm_t comm, const void* send, void* recv, size_t b
 
 /* Peer-mapped window (collective; every rank passes the same size): each rank allocates `bytes` of device memory,
  * publishes a CUDA IPC handle and maps every peer's window, so that exchange kernels store their output straight into
- * the destination GPU's memory over NVLink / NVSwitch.  Two halves serve alternate exchanges; each half holds one
- * region per source rank.  For a HASH exchange of E entries of w words per rank, 2 * 1.3 * E * w * 8 bytes is ample.
+ * the destination GPU's memory over NVLink / NVSwitch.  Three parts serve successive exchanges in turn (an exchange's
+ * tail — count all-gather, fold, deduplication — runs on a side stream while the next scan already stores into the next
+ * part); each part holds one region per source rank.  For a HASH exchange of E entries of w words per rank,
+ * 3 * 1.3 * E * w * 8 bytes is ample.
  * *mapped (may be NULL) = 1 when every rank mapped every peer; otherwise the window is dropped on all ranks and
  * vgpu_comm_exchange_groups moves the payload with NCCL (the same result). */
 int vgpu_comm_reserve_window(vgpu_comm_t comm, size_t bytes, int32_t* mapped);

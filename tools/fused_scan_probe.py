@@ -21,7 +21,7 @@ for fused in (False, True):
     agg = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], accs)
     group = None
     if fused:
-        group = engine.LocalExchangeGroup(world, int(2 * 1.3 * n * 16) + (64 << 20))
+        group = engine.LocalExchangeGroup(world, int(3 * 1.3 * n * 16) + (64 << 20))
         group.attach(0, agg)
     ts = []
     for it in range(iters + 3):

@@ -32,10 +32,10 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
     final = engine.Aggregation(abi.AGG_HASH, [(0, 64, 0, 0)], accs, expected_groups=groups + groups // 8) if world > 1 else None
     mapped = False
     if world > 1 and window:
-        # two halves x world regions; a region must hold this rank's share of any sender's entries (hash-uniform)
+        # three parts x world regions; a region must hold this rank's share of any sender's entries (hash-uniform)
         per_rank = torch.tensor([n], dtype=torch.int64, device="cuda")
         dist.all_reduce(per_rank, op=dist.ReduceOp.MAX)
-        mapped = exchange.reserve_window(int(2 * 1.3 * int(per_rank[0]) * 16) + (64 << 20))
+        mapped = exchange.reserve_window(int(3 * 1.3 * int(per_rank[0]) * 16) + (64 << 20))
 
     def sync():
         torch.cuda.synchronize()
@@ -61,6 +61,8 @@ def groupby_leg(engine, abi, ex, exchange, dist, rank, world, keys_t, vals_t, st
         e0.record()
         for _ in range(steps):
             step(with_exchange)
+        if with_exchange and world > 1:
+            final.finalize()  # the last exchange's tail runs on the communicator's side stream: the timed stream waits for it
         e1.record()
         sync()
         t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")

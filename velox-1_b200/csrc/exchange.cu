@@ -69,6 +69,8 @@ int nccl_fail(int rc, const char* what) { set_error("NCCL error %d (%s) in %s", 
 
 constexpr int kMaxWorld = 32;
 constexpr int kMsgWords = kMaxWorld + 8;  // one rank's count message
+constexpr int kWinParts = 3;          // window parts used by exchanges e, e+1, e+2 in turn (see exchange_log_fused for why three)
+constexpr size_t kDcWords = (size_t)kMsgWords + 32 * kMsgWords + 32 * 32; // one part's message block
 constexpr size_t kWinHeader = 4096;   // per half: epoch flags of the dense exchange, one 64-byte line per source
 } // namespace
 
@@ -81,7 +83,7 @@ struct vgpu_comm_s {
   // grow-only device scratch of the NCCL payload path
   void* send = nullptr; size_t send_cap = 0;
   void* recv = nullptr; size_t recv_cap = 0;
-  int64_t* dcounts = nullptr;          // [kMsgWords] this rank's message + [32 * kMsgWords] the all-gathered messages [src]
+  int64_t* dcounts = nullptr;          // kWinParts blocks (one per window part) of: [kMsgWords] this rank's message + [32 * kMsgWords] the all-gathered messages [src]
                                        // message: [world] entries per destination (low 32 bits front, high 32 back), then kSrcMetaWords of stream facts
   // peer-mapped window
   char* win = nullptr;                 // this rank's window
@@ -91,8 +93,9 @@ struct vgpu_comm_s {
   uint32_t* chunk_prefix = nullptr; size_t chunk_prefix_cap = 0;
   // dense exchange: the wait-for-peers + fold half runs on a side stream, so the caller's stream goes on (next scan)
   cudaStream_t side = nullptr;
-  cudaEvent_t stored = nullptr, folded = nullptr; // phase 1 issued on the caller's stream / phase 2 done on the side stream
-  bool folded_valid = false;
+  cudaEvent_t stored = nullptr;                    // the caller's stream reached the point where the side stream takes over
+  cudaEvent_t folded = nullptr, folded_prev = nullptr; // end of the latest exchange's tail, and of the one before it
+  bool folded_valid = false, folded_prev_valid = false;
   bool local = false;                  // vgpu_debug_local_comms: all ranks on one device, peer[] are plain local allocations
 };
 
@@ -396,6 +399,7 @@ int vgpu_comm_destroy(vgpu_comm_t comm) {
     if (comm->side) { cudaStreamSynchronize(comm->side); cudaStreamDestroy(comm->side); }
     if (comm->stored) cudaEventDestroy(comm->stored);
     if (comm->folded) cudaEventDestroy(comm->folded);
+    if (comm->folded_prev) cudaEventDestroy(comm->folded_prev);
     window_close(comm);
     if (comm->comm) g_nccl.comm_destroy(comm->comm);
     cudaFree(comm->send); cudaFree(comm->recv); cudaFree(comm->dcounts); cudaFree(comm->chunk_prefix);
@@ -430,7 +434,7 @@ int vgpu_comm_reserve_window(vgpu_comm_t comm, size_t bytes, int32_t* mapped) {
   VG_CUDA(cudaDeviceSynchronize());
   window_close(comm);
   const int W = comm->world;
-  bytes = (bytes + 2 * kWinHeader + 4095) & ~(size_t)4095;
+  bytes = (bytes + kWinParts * kWinHeader + 4095) & ~(size_t)4095;
   struct Slot { cudaIpcMemHandle_t handle; int32_t ok; int32_t pad[15]; };
   static_assert(sizeof(Slot) == 128, "slot size");
   Slot mine{};
@@ -475,7 +479,8 @@ int vgpu_comm_reserve_window(vgpu_comm_t comm, size_t bytes, int32_t* mapped) {
 }
 
 // Layout of one half of a window: [kWinHeader bytes of flags][world regions].
-static size_t half_bytes(const vgpu_comm_s* c) { return (c->win_bytes / 2) & ~(size_t)255; }
+static size_t half_bytes(const vgpu_comm_s* c) { return (c->win_bytes / kWinParts) & ~(size_t)255; } // one part (the name is from the two-part days)
+static int64_t* dc_of(const vgpu_comm_s* c) { return c->dcounts + (size_t)(c->epoch % kWinParts) * kDcWords; } // the current exchange's message block
 static size_t region_bytes(const vgpu_comm_s* c) { return ((half_bytes(c) - kWinHeader) / c->world) & ~(size_t)255; }
 static char* region_of(const vgpu_comm_s* c, int owner_rank, int half, int source) {
   return c->peer[owner_rank] + (size_t)half * half_bytes(c) + kWinHeader + (size_t)source * region_bytes(c);
@@ -499,9 +504,9 @@ static int exchange_nccl(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t strea
   if ((rc = comm_reserve(&comm->send, &comm->send_cap, (size_t)std::max<int64_t>(n, 1) * row_bytes))) return rc;
   int64_t counts[32] = {0}, matrix[32 * 32];
   if ((rc = agg_partition(pa, W, comm->send, counts, stream))) return rc;
-  VG_CUDA(cudaMemcpyAsync(comm->dcounts, counts, sizeof(int64_t) * W, cudaMemcpyHostToDevice, stream));
-  int64_t* gathered = comm->dcounts + kMsgWords + 32 * kMsgWords;
-  VG_NCCL(g_nccl.allgather(comm->dcounts, gathered, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
+  VG_CUDA(cudaMemcpyAsync(dc_of(comm), counts, sizeof(int64_t) * W, cudaMemcpyHostToDevice, stream));
+  int64_t* gathered = dc_of(comm) + kMsgWords + 32 * kMsgWords;
+  VG_NCCL(g_nccl.allgather(dc_of(comm), gathered, sizeof(int64_t) * W, kNcclUint8, comm->comm, stream));
   VG_CUDA(cudaMemcpyAsync(matrix, gathered, sizeof(int64_t) * W * W, cudaMemcpyDeviceToHost, stream));
   VG_CUDA(cudaStreamSynchronize(stream));
   int64_t sc[32], so[32], rcv[32], ro[32], srun = 0, rrun = 0;
@@ -522,7 +527,7 @@ static uint64_t region_cap_entries(const vgpu_comm_s* comm, int ew) { return (re
 
 static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   const int W = comm->world, ew = pa.ew;
-  const int half = (int)(comm->epoch & 1);
+  const int half = (int)(comm->epoch % kWinParts);
   const size_t special_bytes = special_slot_bytes(ew);
   int rc;
   const LogRange* ranges = nullptr;
@@ -537,7 +542,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   s.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
   for (int d = 0; d < W; ++d) s.peer_region[d] = (uint64_t*)(region_of(comm, d, half, comm->rank) + special_bytes);
   s.region_cap = region_cap_entries(comm, ew);
-  s.cursor = (unsigned long long*)comm->dcounts;
+  s.cursor = (unsigned long long*)dc_of(comm);
   s.err = pa.err;
   {
     void* p = comm->chunk_prefix; size_t cap = comm->chunk_prefix_cap;
@@ -546,7 +551,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   }
   s.chunk_prefix = comm->chunk_prefix;
   if ((rc = log_chunk_prefix(ranges, n_ranges, chunk, comm->chunk_prefix, stream))) return rc;
-  VG_CUDA(cudaMemsetAsync(comm->dcounts, 0, sizeof(int64_t) * kMsgWords, stream));
+  VG_CUDA(cudaMemsetAsync(dc_of(comm), 0, sizeof(int64_t) * kMsgWords, stream));
   const size_t smem = (size_t)chunk * ew * 8;
   VG_CUDA(cudaFuncSetAttribute(xchg_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   xchg_send_kernel<<<num_sms() * 4, kSendThreads, smem, stream>>>(s);
@@ -554,7 +559,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew; sp.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
   for (int d = 0; d < W; ++d) sp.peer_slot[d] = (uint64_t*)region_of(comm, d, half, comm->rank);
   xchg_send_special_kernel<<<W, 64, 0, stream>>>(sp);
-  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)comm->dcounts, (uint32_t)W, pa.ctr, pa.log_probed && pa.ext_ranges.empty() ? 1 : 0,
+  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)dc_of(comm), (uint32_t)W, pa.ctr, pa.log_probed && pa.ext_ranges.empty() ? 1 : 0,
                                          (pa.log_batches + 1) & 1);
   VG_CUDA(cudaGetLastError());
   count_launch(4);
@@ -563,7 +568,7 @@ static int log_p2p_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
 
 static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream) {
   const int W = comm->world, ew = pa.ew;
-  const int half = (int)(comm->epoch & 1);
+  const int half = (int)(comm->epoch % kWinParts);
   const size_t special_bytes = special_slot_bytes(ew);
   const uint64_t region_cap = region_cap_entries(comm, ew);
   int rc;
@@ -576,7 +581,7 @@ static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t str
     LogRange r{};
     r.base = (const uint64_t*)(region_of(comm, comm->rank, half, src) + special_bytes);
     r.cap = region_cap;
-    const uint32_t* packed = reinterpret_cast<const uint32_t*>(comm->dcounts + kMsgWords + (size_t)src * kMsgWords + comm->rank); // message[src][dst = me]
+    const uint32_t* packed = reinterpret_cast<const uint32_t*>(dc_of(comm) + kMsgWords + (size_t)src * kMsgWords + comm->rank); // message[src][dst = me]
     r.count64 = 0;
     r.count = packed;       // low half: front entries
     r.back = 0;
@@ -586,7 +591,7 @@ static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t str
     fa.ext_ranges.push_back(r);
   }
   fa.ext_bound += region_cap * (uint64_t)W;
-  fa.ext_meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fa.ext_meta = (const unsigned long long*)(dc_of(comm) + kMsgWords + kMaxWorld);
   fa.ext_sources = W;
   fa.ext_meta_stride = kMsgWords;
   fa.finalized = false;
@@ -598,20 +603,41 @@ static int log_p2p_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t str
   return log_finalize(fa, stream);
 }
 
+// ---- side stream -------------------------------------------------------------------------------------------------------
+static int comm_side_init(vgpu_comm_s* comm) {
+  if (comm->side) return VGPU_OK;
+  VG_CUDA(cudaStreamCreateWithFlags(&comm->side, cudaStreamNonBlocking));
+  VG_CUDA(cudaEventCreateWithFlags(&comm->stored, cudaEventDisableTiming));
+  VG_CUDA(cudaEventCreateWithFlags(&comm->folded, cudaEventDisableTiming));
+  VG_CUDA(cudaEventCreateWithFlags(&comm->folded_prev, cudaEventDisableTiming));
+  return VGPU_OK;
+}
+// The current exchange's last work was just issued on `stream` (the side stream, or the caller's for the paths that
+// do not use one): remember it as "latest", the former latest as "the one before".
+static int comm_tail_issued(vgpu_comm_s* comm, cudaStream_t stream) {
+  int rc = comm_side_init(comm);
+  if (rc) return rc;
+  std::swap(comm->folded, comm->folded_prev);
+  comm->folded_prev_valid = comm->folded_valid;
+  VG_CUDA(cudaEventRecord(comm->folded, stream));
+  comm->folded_valid = true;
+  return VGPU_OK;
+}
+
 // ---- fused exchange (entries already left from inside the scan: fused_prelude.cuh send_entries) --------------------
 static constexpr size_t kFusedCountsBytes = 1024 * sizeof(unsigned long long); // = vg::kSendCountsBytes (below)
 
 // Sender: what is left to do after the scans — the count message, the dedicated groups, the stream facts.
 static int log_fused_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
   const int W = comm->world, ew = pa.ew;
-  const int half = (int)(comm->epoch & 1);
-  VG_CUDA(cudaMemsetAsync(comm->dcounts, 0, sizeof(int64_t) * kMsgWords, stream));
-  xchg_send_totals_kernel<<<1, 256, 0, stream>>>((unsigned long long*)comm->dcounts, pa.send_counts, pa.send_grid, (uint32_t)W, pa.send_sub_cap);
+  const int half = (int)(comm->epoch % kWinParts);
+  VG_CUDA(cudaMemsetAsync(dc_of(comm), 0, sizeof(int64_t) * kMsgWords, stream));
+  xchg_send_totals_kernel<<<1, 256, 0, stream>>>((unsigned long long*)dc_of(comm), pa.send_counts, pa.send_grid, (uint32_t)W, pa.send_sub_cap);
   SpecialArgs sp{};
   sp.special = pa.special; sp.world = (uint32_t)W; sp.ew = ew; sp.velox_hash = agg_raw_bigint_key(pa) ? 1 : 0;
   for (int d = 0; d < W; ++d) sp.peer_slot[d] = (uint64_t*)region_of(comm, d, half, comm->rank);
   xchg_send_special_kernel<<<W, 64, 0, stream>>>(sp);
-  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)comm->dcounts, (uint32_t)W, pa.ctr, pa.log_probed ? 1 : 0, (pa.log_batches + 1) & 1);
+  xchg_meta_kernel<<<1, 32, 0, stream>>>((unsigned long long*)dc_of(comm), (uint32_t)W, pa.ctr, pa.log_probed ? 1 : 0, (pa.log_batches + 1) & 1);
   VG_CUDA(cudaGetLastError());
   count_launch(3);
   return VGPU_OK;
@@ -620,7 +646,7 @@ static int log_fused_send(vgpu_comm_s* comm, Agg& pa, cudaStream_t stream) {
 // Receiver: one front and one back range per source and sending CTA, counted by the words the senders left beside them.
 static int log_fused_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream) {
   const int W = comm->world, ew = pa.ew, grid = pa.send_grid;
-  const int half = (int)(comm->epoch & 1);
+  const int half = (int)(comm->epoch % kWinParts);
   const size_t special_bytes = special_slot_bytes(ew);
   const uint64_t sub_cap = pa.send_sub_cap;
   int rc;
@@ -628,7 +654,7 @@ static int log_fused_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t s
   if (fa.engine != kEngineLog || fa.ew != ew) { set_error("the final aggregation cannot take the partial stage's entries"); return VGPU_ERR_INVALID; }
   FoldSpecialArgs fs{};
   fs.special = fa.special; fs.kinds = log_cell_kinds(fa); fs.world = (uint32_t)W; fs.ew = ew; fs.err = fa.err;
-  fs.meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fs.meta = (const unsigned long long*)(dc_of(comm) + kMsgWords + kMaxWorld);
   fs.meta_stride = kMsgWords;
   fs.expect_grid = (unsigned long long)grid; fs.expect_sub_cap = sub_cap;
   fa.ext_ranges.reserve(fa.ext_ranges.size() + (size_t)2 * W * grid);
@@ -651,7 +677,7 @@ static int log_fused_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t s
     }
   }
   fa.ext_bound += sub_cap * (uint64_t)grid * (uint64_t)W;
-  fa.ext_meta = (const unsigned long long*)(comm->dcounts + kMsgWords + kMaxWorld);
+  fa.ext_meta = (const unsigned long long*)(dc_of(comm) + kMsgWords + kMaxWorld);
   fa.ext_sources = W;
   fa.ext_meta_stride = kMsgWords;
   fa.finalized = false;
@@ -663,20 +689,44 @@ static int log_fused_receive(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t s
   return log_finalize(fa, stream);
 }
 
+// The caller's stream only issues the three small sender kernels; the count all-gather (the rendezvous with the peers),
+// the receiver's fold and its deduplication run on the communicator's side stream, so the caller's next scan overlaps
+// them.  That is why the window has THREE parts: scan e+1 stores into part (e+1) % 3 while the peers may still read
+// parts (e-1) % 3 and e % 3 in the tails of exchanges e-1 and e.  Scan e+1 has to know that every peer finished reading
+// part (e+1) % 3 = (e-2) % 3, i.e. its tail e-2: this rank's own tail e-1 is past its all-gather only when every peer
+// has entered that all-gather on its side stream, behind its tail e-2 — so scan e+1 waits for this rank's tail e-1
+// ("the one before the latest", send_bind).  The final aggregation remembers the tail's event (agg_wait_pending).
 static int exchange_log_fused(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int64_t* bytes_sent) {
-  int rc = log_fused_send(comm, pa, stream);
+  static const bool serial = getenv("VGPU_EXCHANGE_OVERLAP") && getenv("VGPU_EXCHANGE_OVERLAP")[0] == '0'; // tuning aid: everything on the caller's stream
+  int rc = comm_side_init(comm);
   if (rc) return rc;
+  rc = log_fused_send(comm, pa, stream);
+  if (rc) return rc;
+  cudaStream_t tail = serial ? stream : comm->side;
+  if (!serial) {
+    VG_CUDA(cudaEventRecord(comm->stored, stream));
+    VG_CUDA(cudaStreamWaitEvent(comm->side, comm->stored, 0));
+  }
   // the barrier between "everybody's scan has stored" and "anybody reads", carrying the stream facts
-  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, stream));
+  VG_NCCL(g_nccl.allgather(dc_of(comm), dc_of(comm) + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, tail));
   if (bytes_sent) *bytes_sent = -1; // known on the device only; see vgpu_comm_last_counts
-  return log_fused_receive(comm, pa, fa, stream);
+  rc = log_fused_receive(comm, pa, fa, tail);
+  if (rc) return rc;
+  rc = comm_tail_issued(comm, tail);
+  if (rc) return rc;
+  if (!serial) {
+    if (!fa.pending) VG_CUDA(cudaEventCreateWithFlags(&fa.pending, cudaEventDisableTiming));
+    VG_CUDA(cudaEventRecord(fa.pending, comm->side));
+    fa.pending_set = true;
+  }
+  return VGPU_OK;
 }
 
 static int exchange_log_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int64_t* bytes_sent) {
   int rc = log_p2p_send(comm, pa, stream);
   if (rc) return rc;
   // the counts, and the barrier between "everybody has stored" and "anybody reads"
-  VG_NCCL(g_nccl.allgather(comm->dcounts, comm->dcounts + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, stream));
+  VG_NCCL(g_nccl.allgather(dc_of(comm), dc_of(comm) + kMsgWords, sizeof(int64_t) * kMsgWords, kNcclUint8, comm->comm, stream));
   if (bytes_sent) *bytes_sent = -1; // known on the device only; see vgpu_comm_last_counts
   return log_p2p_receive(comm, pa, fa, stream);
 }
@@ -684,7 +734,7 @@ static int exchange_log_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t st
 // GLOBAL / ARRAY through the window.
 static int dense_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int phase, bool advance) {
   const int W = comm->world;
-  const int half = (int)(comm->epoch & 1);
+  const int half = (int)(comm->epoch % kWinParts);
   DenseArgs d{};
   d.state = pa.state; d.final_state = fa.state; d.G = pa.n_groups; d.n_cells = pa.n_cells;
   for (int c = 0; c < pa.n_cells; ++c) d.kind[c] = pa.cells[c].kind;
@@ -695,7 +745,7 @@ static int dense_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, i
     d.my_data[r] = (const uint64_t*)region_of(comm, comm->rank, half, r);
     d.my_flag[r] = (const unsigned long long*)(comm->win + (size_t)half * half_bytes(comm) + (size_t)r * 64);
   }
-  d.epoch = comm->epoch / 2 + 1; // per half: strictly increasing
+  d.epoch = comm->epoch / kWinParts + 1; // per part: strictly increasing
   d.err = fa.err;
   d.phase = phase;
   // the waiting half is one small CTA that must fit beside the resident CTAs of a scan running on another stream: it
@@ -719,12 +769,8 @@ static int dense_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, i
 static int exchange_dense_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t stream, int64_t* bytes_sent) {
   if (bytes_sent) *bytes_sent = (int64_t)((size_t)pa.n_groups * pa.n_cells * 8 * (comm->world - 1));
   static const bool serial = getenv("VGPU_DENSE_OVERLAP") && getenv("VGPU_DENSE_OVERLAP")[0] == '0'; // tuning aid: one launch, no side stream
-  if (serial) return dense_p2p(comm, pa, fa, stream, 3, true);
-  if (!comm->side) {
-    VG_CUDA(cudaStreamCreateWithFlags(&comm->side, cudaStreamNonBlocking));
-    VG_CUDA(cudaEventCreateWithFlags(&comm->stored, cudaEventDisableTiming));
-    VG_CUDA(cudaEventCreateWithFlags(&comm->folded, cudaEventDisableTiming));
-  }
+  if (serial) { const int src = dense_p2p(comm, pa, fa, stream, 3, true); return src ? src : comm_tail_issued(comm, stream); }
+  { const int irc = comm_side_init(comm); if (irc) return irc; }
   if (!fa.pending) VG_CUDA(cudaEventCreateWithFlags(&fa.pending, cudaEventDisableTiming));
   int rc = dense_p2p(comm, pa, fa, stream, 1, false);
   if (rc) return rc;
@@ -732,9 +778,9 @@ static int exchange_dense_p2p(vgpu_comm_s* comm, Agg& pa, Agg& fa, cudaStream_t 
   VG_CUDA(cudaStreamWaitEvent(comm->side, comm->stored, 0));
   rc = dense_p2p(comm, pa, fa, comm->side, 2, true);
   if (rc) return rc;
-  VG_CUDA(cudaEventRecord(comm->folded, comm->side));
+  rc = comm_tail_issued(comm, comm->side);
+  if (rc) return rc;
   VG_CUDA(cudaEventRecord(fa.pending, comm->side));
-  comm->folded_valid = true;
   fa.pending_set = true;
   return VGPU_OK;
 }
@@ -753,30 +799,32 @@ int vgpu_comm_exchange_groups(vgpu_comm_t comm, vgpu_agg_t partial_agg, vgpu_agg
   Agg& fa = final_agg->agg;
   if (pa.mode != fa.mode || pa.accs.size() != fa.accs.size()) { set_error("partial and final aggregations differ"); return VGPU_ERR_INVALID; }
   if (!pa.resolved || !fa.resolved) { set_error("both aggregations must have seen an (empty) vgpu_agg_add_input"); return VGPU_ERR_INVALID; }
-  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)));
-  // a dense exchange's fold may still run on the side stream: every exchange starts after it (see exchange_dense_p2p)
-  if (comm->folded_valid) VG_CUDA(cudaStreamWaitEvent(stream, comm->folded, 0));
+  if (!comm->dcounts) VG_CUDA(cudaMalloc(&comm->dcounts, sizeof(int64_t) * kDcWords * kWinParts));
   { int wrc = agg_wait_pending(pa, stream); if (wrc) return wrc; wrc = agg_wait_pending(fa, stream); if (wrc) return wrc; }
+  if (pa.mode == VGPU_AGG_HASH && pa.send_used) {
+    if (pa.send_comm != comm) { set_error("the partial aggregation's entries left through another exchange"); return VGPU_ERR_INVALID; }
+    if (pa.send_epoch != comm->epoch) { set_error("another exchange ran through this communicator since the partial aggregation's scan"); return VGPU_ERR_INVALID; }
+    return exchange_log_fused(comm, pa, fa, stream, bytes_sent);
+  }
+  // every other path starts behind the latest exchange's tail, which may still run on the side stream (exchange_dense_p2p,
+  // exchange_log_fused), and leaves its own end as the new "latest"
+  if (comm->folded_valid) VG_CUDA(cudaStreamWaitEvent(stream, comm->folded, 0));
+  auto done = [&](int rc) -> int { if (rc) return rc; return comm_tail_issued(comm, stream); };
   const bool no_p2p = getenv("VGPU_EXCHANGE") && strcmp(getenv("VGPU_EXCHANGE"), "nccl") == 0;
   if (pa.mode != VGPU_AGG_HASH) {
     if (pa.n_groups != fa.n_groups || pa.n_cells != fa.n_cells) { set_error("partial and final aggregations differ in their key domains"); return VGPU_ERR_INVALID; }
     // a global aggregation's single row (present even without input) is reported by the rank that owns group 0 only
     if (pa.mode == VGPU_AGG_GLOBAL) fa.emit_empty_global = (int)partition_of(0, 0, (uint32_t)comm->world, false) == comm->rank;
     if (comm->win && !no_p2p && dense_fits(comm, pa)) return exchange_dense_p2p(comm, pa, fa, stream, bytes_sent);
-    return exchange_nccl(comm, pa, fa, stream, bytes_sent);
+    return done(exchange_nccl(comm, pa, fa, stream, bytes_sent));
   }
-  if (pa.send_used) {
-    if (pa.send_comm != comm) { set_error("the partial aggregation's entries left through another exchange"); return VGPU_ERR_INVALID; }
-    if (pa.send_epoch != comm->epoch) { set_error("another exchange ran through this communicator since the partial aggregation's scan"); return VGPU_ERR_INVALID; }
-    return exchange_log_fused(comm, pa, fa, stream, bytes_sent);
-  }
-  if (comm->win && !no_p2p && log_fits(comm, pa, fa)) return exchange_log_p2p(comm, pa, fa, stream, bytes_sent);
-  return exchange_nccl(comm, pa, fa, stream, bytes_sent);
+  if (comm->win && !no_p2p && log_fits(comm, pa, fa)) return done(exchange_log_p2p(comm, pa, fa, stream, bytes_sent));
+  return done(exchange_nccl(comm, pa, fa, stream, bytes_sent));
 }
 
 int vgpu_debug_local_comms(int32_t world, size_t window_bytes, vgpu_comm_t* out) {
   if (!out || world < 1 || world > kMaxWorld) return VGPU_ERR_INVALID;
-  window_bytes = (window_bytes + 2 * kWinHeader + 4095) & ~(size_t)4095;
+  window_bytes = (window_bytes + kWinParts * kWinHeader + 4095) & ~(size_t)4095;
   int rc = VGPU_OK;
   for (int r = 0; r < world; ++r) out[r] = nullptr;
   for (int r = 0; r < world && rc == VGPU_OK; ++r) {
@@ -784,7 +832,7 @@ int vgpu_debug_local_comms(int32_t world, size_t window_bytes, vgpu_comm_t* out)
     out[r] = c;
     c->comm = nullptr; c->rank = r; c->world = world; c->local = true;
     if (cudaMalloc(&c->win, window_bytes) != cudaSuccess || cudaMemset(c->win, 0, window_bytes) != cudaSuccess ||
-        cudaMalloc(&c->dcounts, sizeof(int64_t) * (kMsgWords + 32 * kMsgWords + 32 * 32)) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
+        cudaMalloc(&c->dcounts, sizeof(int64_t) * kDcWords * kWinParts) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "local window");
     c->win_bytes = window_bytes;
   }
   if (rc) { for (int r = 0; r < world; ++r) { if (out[r]) vgpu_comm_destroy(out[r]); out[r] = nullptr; } return rc; }
@@ -811,7 +859,7 @@ int vgpu_debug_exchange_local_comms(vgpu_comm_t* comms, vgpu_agg_t* partials, vg
   }
   if (hash) { // the all-gather of the counts
     for (int r = 0; r < world; ++r) for (int src = 0; src < world; ++src)
-      VG_CUDA(cudaMemcpyAsync(comms[r]->dcounts + kMsgWords + (size_t)src * kMsgWords, comms[src]->dcounts, sizeof(int64_t) * kMsgWords, cudaMemcpyDeviceToDevice, stream));
+      VG_CUDA(cudaMemcpyAsync(dc_of(comms[r]) + kMsgWords + (size_t)src * kMsgWords, dc_of(comms[src]), sizeof(int64_t) * kMsgWords, cudaMemcpyDeviceToDevice, stream));
   }
   for (int r = 0; r < world; ++r) {
     Agg& pa = partials[r]->agg;
@@ -859,7 +907,9 @@ int vgpu_comm_last_counts(vgpu_comm_t comm, int64_t* matrix, void* stream) {
   if (!comm || !matrix || !comm->dcounts) return VGPU_ERR_INVALID;
   const int W = comm->world;
   std::vector<int64_t> msgs((size_t)W * kMsgWords);
-  VG_CUDA(cudaMemcpyAsync(msgs.data(), comm->dcounts + kMsgWords, sizeof(int64_t) * W * kMsgWords, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  if (comm->side) VG_CUDA(cudaStreamSynchronize(comm->side));
+  const int64_t* last = comm->dcounts + (size_t)((comm->epoch + kWinParts - 1) % kWinParts) * kDcWords; // the exchange that just ran
+  VG_CUDA(cudaMemcpyAsync(msgs.data(), last + kMsgWords, sizeof(int64_t) * W * kMsgWords, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   VG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   for (int s = 0; s < W; ++s) for (int d = 0; d < W; ++d) {
     const uint64_t w = (uint64_t)msgs[(size_t)s * kMsgWords + d];
@@ -931,7 +981,10 @@ int send_bind(Agg& a, PipelineParams& p, int grid, cudaStream_t stream) {
   if (!a.send_used) { VG_CUDA(cudaMemsetAsync(a.send_counts, 0, words * sizeof(unsigned long long), stream)); a.send_epoch = c->epoch; }
   a.send_grid = grid;
   a.send_sub_cap = sub_cap;
-  const int half = (int)(c->epoch & 1);
+  // the part this scan stores into was read by the peers in the tail of the exchange three back: every peer is past
+  // that once this rank's tail "before the latest" is complete (exchange_log_fused)
+  if (c->folded_prev_valid) VG_CUDA(cudaStreamWaitEvent(stream, c->folded_prev, 0));
+  const int half = (int)(c->epoch % kWinParts);
   const size_t special_bytes = special_slot_bytes(ew);
   p.send_sub_cap = sub_cap;
   p.send_counts = a.send_counts;
