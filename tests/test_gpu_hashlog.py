@@ -344,3 +344,22 @@ def test_int32_max_key_next_to_null_in_a_two_key_hash(engine):
     # a declared domain that does not fit its field is rejected
     with pytest.raises(abi.VgpuError):
         run_hash(engine, None, outs, spec, 6, [(0, 32, i32.min, i32.max), (1, 4, 0, 7)], accs)
+
+
+@pytest.mark.parametrize("cardinality,batches", [(4, 1), (50, 3), (1000, 1)])
+def test_unsorted_keys_of_low_cardinality_take_the_combining_pass(engine, cardinality, batches):
+    # many more entries than keys, nothing sorted: finalize folds every chunk in shared memory before partitioning
+    # (fin_combine_kernel) and a partition's CTA folds runs of one key in registers; NULL keys and the marker key included
+    rng = np.random.default_rng(1000 + cardinality)
+    n = 400_003
+    k = rng.integers(-1, cardinality - 1, n).astype(np.int64)
+    knn = rng.random(n) > 0.02
+    v = rng.integers(-1000, 1000, n) * 0.125
+    vnn = rng.random(n) > 0.1
+    spec = [(I64, k, knn), (D, v, vnn)]
+    outs = [ex.col(0, I64), ex.col(1, D)]
+    got, info = run_hash(engine, None, outs, spec, n, RAW_KEY, GB_ACCS, batches=batches)
+    H.assert_groups_equal(got, oracle(None, outs, spec, n, RAW_KEY, GB_ACCS), GB_ACCS)
+    assert len(got) == cardinality + 1  # + the NULL key
+    if info["engine"] == 1 and cardinality <= 50:
+        assert info["deduped_entries"] < n // 20, info  # the count after the combining pass

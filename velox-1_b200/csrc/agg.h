@@ -27,6 +27,8 @@ enum : int {
   kCtrPrevKey = 49,    // [2][2]: {key, valid} of the last row of the previous batch, double-buffered by batch parity
   kCtrFin = 53,        // finalize header: see FinHeader (6 words)
   kCtrFirstKey = 59,   // key of the very first logged row (meaningful while the input is sorted)
+  kCtrCombine = 60,    // finalize's pre-combining pass: [0] 0 = off, 1 = wanted (sample says duplicates abound), 2 = done;
+                       // [1] combined entries, [2] CTAs finished (ticket), [3] spare
   kCtrWords = 64
 };
 

@@ -53,6 +53,8 @@ struct FinArgs {
   const unsigned long long* src_meta; // received streams: {sorted, first key, last key, entries} per source, or nullptr
   int n_src, src_stride, local_entries; // local_entries: this aggregation logged input of its own as well
   FinHeader* hdr;
+  unsigned long long* comb;      // Agg::ctr + kCtrCombine (see agg.h)
+  int combine_ok;                // host: the pre-combining pass may run (its table fits shared memory)
   uint32_t* hist;                // [P + 1]
   uint32_t* offsets;             // [P + 1]
   uint32_t* cursors;             // [P]
@@ -97,6 +99,10 @@ __device__ __forceinline__ void chunk_prefix_scan(const LogRange* ranges, int n_
   if (threadIdx.x == 0) chunk_prefix[n_ranges] = s_carry;
 }
 
+__device__ __forceinline__ void locate_chunk(const LogRange* ranges, const uint32_t* chunk_prefix, int n_ranges, uint32_t chunk, int ew,
+                                             const uint64_t*& first, uint64_t& n);
+constexpr int kSampleChunks = 16;
+
 __global__ void fin_prepare_kernel(FinArgs a) {
   __shared__ unsigned long long s_front[32], s_other[32];
   bool sorted = a.probed && *a.sort_state == 0ull;
@@ -140,6 +146,41 @@ __global__ void fin_prepare_kernel(FinArgs a) {
     a.hdr->log2p = (unsigned long long)log2p;
   }
   chunk_prefix_scan(a.ranges, a.n_ranges, a.chunk_prefix, kChunk, [&](const LogRange& r) { return !(sorted && r.back == kRangeFront); });
+  // Do duplicates abound among the entries to deduplicate (unsorted input of low or medium cardinality)?  Sample
+  // kSampleChunks chunks spread over the ranges: distinct keys per chunk against entries per chunk.  If fewer than 60 %
+  // are distinct, fin_combine_kernel folds every chunk in shared memory first, so that a key with millions of entries
+  // does not end up as one partition walked by one CTA (measured: 4 keys over 60 M unsorted rows took 318 ms).
+  __syncthreads();
+  __shared__ unsigned long long s_keys[2 * kChunk];
+  __shared__ unsigned int s_sampled, s_distinct;
+  if (threadIdx.x == 0) { s_sampled = 0; s_distinct = 0; }
+  const uint32_t total_chunks = a.chunk_prefix[a.n_ranges];
+  const bool sample = a.combine_ok && a.hdr->n_dedupe > 65536ull && total_chunks >= (uint32_t)kSampleChunks;
+  if (sample) {
+    for (int sc = 0; sc < kSampleChunks; ++sc) {
+      for (int i = threadIdx.x; i < (int)(2 * kChunk); i += blockDim.x) s_keys[i] = kEmptyKey;
+      __syncthreads();
+      const uint64_t* first;
+      uint64_t n;
+      locate_chunk(a.ranges, a.chunk_prefix, a.n_ranges, (uint32_t)((uint64_t)sc * total_chunks / kSampleChunks), a.ew, first, n);
+      for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint64_t key = first[i * a.ew];
+        uint32_t h = (uint32_t)mix64(key) & (2 * kChunk - 1);
+        for (;;) {
+          const unsigned long long seen = atomicCAS(&s_keys[h], kEmptyKey, (unsigned long long)key);
+          if (seen == kEmptyKey) { atomicAdd(&s_distinct, 1u); break; }
+          if (seen == key) break;
+          h = (h + 1) & (2 * kChunk - 1);
+        }
+      }
+      if (threadIdx.x == 0) s_sampled += (unsigned int)n;
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x == 0) {
+    a.comb[0] = sample && (unsigned long long)s_distinct * 10ull < (unsigned long long)s_sampled * 6ull ? 1ull : 0ull;
+    a.comb[1] = 0ull; a.comb[2] = 0ull;
+  }
 }
 
 // The chunk prefix array in shared memory when it fits (a binary search over global memory is ~10 dependent L2
@@ -170,6 +211,16 @@ __device__ __forceinline__ void locate_chunk(const LogRange* ranges, const uint3
 // Walks every entry that needs deduplication: the CTAs share the chunks of all taking-part ranges.
 template <typename F>
 __device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn, uint32_t first_chunk, uint32_t chunk_stride) {
+  if (a.comb[0] == 2ull) { // fin_combine_kernel ran: the entries to deduplicate are its output, one plain array
+    const uint64_t n_all = a.comb[1];
+    const uint32_t total = (uint32_t)((n_all + kChunk - 1) / kChunk);
+    for (uint32_t chunk = first_chunk; chunk < total; chunk += chunk_stride) {
+      const uint64_t c0 = (uint64_t)chunk * kChunk, n = min((uint64_t)kChunk, n_all - c0);
+      const uint64_t* first = a.groups + c0 * a.ew;
+      for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) fn(first + i * a.ew);
+    }
+    return;
+  }
   __shared__ uint32_t s_prefix[kPrefixSmem];
   const uint32_t* prefix = stage_prefix(a.chunk_prefix, a.n_ranges, s_prefix);
   const uint32_t total = prefix[a.n_ranges];
@@ -181,13 +232,104 @@ __device__ __forceinline__ void for_each_dedupe_entry(const FinArgs& a, F&& fn, 
   }
 }
 
+__device__ __forceinline__ void smem_fold(uint8_t kind, unsigned long long* cell, uint64_t v, uint32_t& err);
+
+// Pre-combining pass (only when fin_prepare_kernel's sample found many duplicates): every chunk of kChunk entries is
+// folded in a shared-memory table of 2 * kChunk slots (never full) and its distinct keys are appended to `groups`, which
+// serves as the pass's output buffer until fin_aggregate_kernel overwrites it with the final groups (the partitioning
+// passes have moved the entries on to `part` by then).  The last CTA to finish publishes the new entry count and
+// partition count.  Unsorted input of low cardinality shrinks by orders of magnitude here; a second round is not needed:
+// what is left per key is at most one entry per chunk.
+__global__ void fin_combine_kernel(FinArgs a) {
+  if (a.comb[0] != 1ull) return;
+  extern __shared__ __align__(16) unsigned long long smem[];
+  __shared__ uint32_t s_prefix[kPrefixSmem];
+  __shared__ uint32_t s_warp[32];
+  __shared__ unsigned long long s_base;
+  const int ew = a.ew, nc = ew - 1;
+  const uint32_t T = 2 * kChunk;
+  unsigned long long* keys = smem;
+  unsigned long long* vals = smem + T;
+  const uint32_t* prefix = stage_prefix(a.chunk_prefix, a.n_ranges, s_prefix);
+  const uint32_t total = prefix[a.n_ranges];
+  uint32_t err = 0;
+  for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
+    for (uint32_t s = threadIdx.x; s < T; s += blockDim.x) {
+      keys[s] = kEmptyKey;
+      for (int c = 0; c < nc; ++c) vals[(size_t)s * nc + c] = cell_identity(a.kinds.kind[c]);
+    }
+    __syncthreads();
+    const uint64_t* first;
+    uint64_t n;
+    locate_chunk(a.ranges, prefix, a.n_ranges, chunk, ew, first, n);
+    for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) {
+      const uint64_t* e = first + i * ew;
+      const uint64_t key = e[0];
+      uint32_t h = (uint32_t)mix64(key) & (T - 1);
+      for (;;) {
+        const unsigned long long seen = atomicCAS(&keys[h], kEmptyKey, (unsigned long long)key);
+        if (seen == kEmptyKey || seen == key) break;
+        h = (h + 1) & (T - 1);
+      }
+      for (int c = 0; c < nc; ++c) smem_fold(a.kinds.kind[c], &vals[(size_t)h * nc + c], e[1 + c], err);
+    }
+    __syncthreads();
+    uint32_t mine = 0;
+    for (uint32_t s = threadIdx.x; s < T; s += blockDim.x) mine += keys[s] != kEmptyKey;
+    uint32_t x = mine;
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)(threadIdx.x & 31) >= o) x += y; }
+    if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = x;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      uint32_t w = threadIdx.x < (blockDim.x >> 5) ? s_warp[threadIdx.x] : 0u;
+      for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, w, o); if ((int)threadIdx.x >= o) w += y; }
+      s_warp[threadIdx.x] = w;
+      if (threadIdx.x == 31) s_base = w ? atomicAdd(&a.comb[1], (unsigned long long)w) : 0ull;
+    }
+    __syncthreads();
+    uint64_t at = s_base + ((threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0u) + x - mine;
+    for (uint32_t s = threadIdx.x; s < T; s += blockDim.x) {
+      if (keys[s] == kEmptyKey) continue;
+      uint64_t* d = a.groups + at * ew;
+      d[0] = keys[s];
+      for (int c = 0; c < nc; ++c) d[1 + c] = vals[(size_t)s * nc + c];
+      ++at;
+    }
+    __syncthreads();
+  }
+  if (err) atomicOr(a.err, err);
+  // the last CTA to get here publishes the result
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned long long done = atomicAdd(&a.comb[2], 1ull) + 1ull;
+    if (done == (unsigned long long)gridDim.x) {
+      __threadfence();
+      const unsigned long long n_dedupe = *reinterpret_cast<volatile unsigned long long*>(&a.comb[1]);
+      a.hdr->n_dedupe = n_dedupe;
+      const unsigned long long per_part = min((unsigned long long)a.slots_max * 45 / 100, 256ull);
+      int log2p = 4; // (never "tiny": fin_aggregate_kernel must read `part`, not the buffer it writes)
+      while (log2p < a.log2p_max && (1ull << log2p) * per_part < n_dedupe) ++log2p;
+      a.hdr->log2p = (unsigned long long)log2p;
+      __threadfence();
+      a.comb[0] = 2ull;
+    }
+  }
+}
+
 // log2p == 0 ("tiny"): so few entries that one shared-memory table holds them all — fin_aggregate_kernel reads them
 // straight from their ranges and the partitioning passes have nothing to do.  (A sorted input leaves only the runs at
 // the ends of its batches and the runs longer than a block to deduplicate.)
 __global__ void fin_hist_kernel(FinArgs a) {
   const int log2p = (int)a.hdr->log2p;
   if (log2p == 0) return;
-  for_each_dedupe_entry(a, [&](const uint64_t* e) { atomicAdd(&a.hist[part_of_key(e[0], log2p)], 1u); }, blockIdx.x, gridDim.x);
+  // lanes that meet in one partition add once (hot partitions: few distinct keys among many entries)
+  for_each_dedupe_entry(a, [&](const uint64_t* e) {
+    const uint32_t p = part_of_key(e[0], log2p);
+    const unsigned am = __activemask();
+    const unsigned m = __match_any_sync(am, p);
+    if ((threadIdx.x & 31u) == (unsigned)(__ffs((int)m) - 1)) atomicAdd(&a.hist[p], (uint32_t)__popc(m));
+  }, blockIdx.x, gridDim.x);
 }
 
 // Exclusive scan of hist[0..P) -> offsets[0..P], cursors = offsets.  One CTA.
@@ -224,13 +366,18 @@ __global__ void fin_scatter_kernel(FinArgs a) {
   const int ew = a.ew, log2p = (int)a.hdr->log2p;
   if (log2p == 0) return;
   for_each_dedupe_entry(a, [&](const uint64_t* e) {
+    const uint32_t pt = part_of_key(e[0], log2p);
+    const unsigned am = __activemask();
+    const unsigned m = __match_any_sync(am, pt);
+    const int leader = __ffs((int)m) - 1;
+    uint32_t pos0 = 0;
+    if ((int)(threadIdx.x & 31u) == leader) pos0 = atomicAdd(&a.cursors[pt], (uint32_t)__popc(m));
+    const uint32_t pos = __shfl_sync(m, pos0, leader) + (uint32_t)__popc(m & ((1u << (threadIdx.x & 31u)) - 1u));
     if (ew == 2) {
       const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(e);
-      const uint32_t pos = atomicAdd(&a.cursors[part_of_key(v.x, log2p)], 1u);
       *reinterpret_cast<ulonglong2*>(a.part + (uint64_t)pos * 2) = v;
     } else {
       const uint64_t key = e[0];
-      const uint32_t pos = atomicAdd(&a.cursors[part_of_key(key, log2p)], 1u);
       uint64_t* d = a.part + (uint64_t)pos * ew;
       d[0] = key;
       for (int w = 1; w < ew; ++w) d[w] = e[w];
@@ -300,6 +447,26 @@ __global__ void fin_aggregate_kernel(FinArgs a) {
     };
     if (tiny) {
       for_each_dedupe_entry(a, fold, 0u, 1u); // this CTA alone walks every chunk
+    } else if (nc <= 4) {
+      // A partition whose entries carry few distinct keys (input of medium cardinality: the partition count follows the
+      // entries, not the keys) would hammer one table slot with atomics: a thread folds runs of equal keys in registers
+      // first (entries of one key sit together often enough: a thread's entries are kNT apart in the partition).
+      const uint64_t* src = a.part + (uint64_t)lo * ew;
+      uint64_t ck = kEmptyKey, cv[4] = {0, 0, 0, 0};
+      for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
+        const uint64_t* e = src + (uint64_t)i * ew;
+        const uint64_t key = e[0];
+        if (key == ck) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) if (c < nc) cv[c] = fold2(a.kinds.kind[c], cv[c], e[1 + c], err);
+        } else {
+          if (ck != kEmptyKey) { uint64_t held[5] = {ck, cv[0], cv[1], cv[2], cv[3]}; fold(held); }
+          ck = key;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) if (c < nc) cv[c] = e[1 + c];
+        }
+      }
+      if (ck != kEmptyKey) { uint64_t held[5] = {ck, cv[0], cv[1], cv[2], cv[3]}; fold(held); }
     } else {
       const uint64_t* src = a.part + (uint64_t)lo * ew;
       for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) fold(src + (uint64_t)i * ew);
@@ -628,6 +795,9 @@ int log_finalize(Agg& a, cudaStream_t stream) {
   f.sort_state = a.ctr + kCtrSortState;
   f.src_meta = a.ext_meta; f.n_src = a.ext_sources; f.src_stride = a.ext_meta_stride; f.local_entries = a.slabs.empty() ? 0 : 1;
   f.hdr = reinterpret_cast<FinHeader*>(a.ctr + kCtrFin);
+  f.comb = a.ctr + kCtrCombine;
+  const size_t combine_smem = (size_t)2 * kChunk * a.ew * 8;
+  f.combine_ok = combine_smem <= 96 * 1024 ? 1 : 0;
   f.hist = a.hist;
   f.offsets = a.hist + (P + 1);
   f.cursors = a.hist + 2 * (P + 1);
@@ -637,6 +807,11 @@ int log_finalize(Agg& a, cudaStream_t stream) {
   f.err = a.err;
   VG_CUDA(cudaMemsetAsync(a.hist, 0, (P + 1) * sizeof(uint32_t), stream));
   fin_prepare_kernel<<<1, 1024, 0, stream>>>(f);
+  if (f.combine_ok) { // returns at once unless the sample found many duplicates
+    VG_CUDA(cudaFuncSetAttribute(fin_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    fin_combine_kernel<<<num_sms() * 4, 256, combine_smem, stream>>>(f);
+    count_launch();
+  }
   const int wide = num_sms() * 8;
   fin_hist_kernel<<<wide, 256, 0, stream>>>(f);
   fin_scan_kernel<<<1, 1024, 0, stream>>>(f);
