@@ -362,4 +362,4 @@ def test_unsorted_keys_of_low_cardinality_take_the_combining_pass(engine, cardin
     H.assert_groups_equal(got, oracle(None, outs, spec, n, RAW_KEY, GB_ACCS), GB_ACCS)
     assert len(got) == cardinality + 1  # + the NULL key
     if info["engine"] == 1 and cardinality <= 50:
-        assert info["deduped_entries"] < n // 20, info  # the count after the combining pass
+        assert info["deduped_entries"] < n // 4, info  # the count after the combining pass (one entry per key and chunk; ranges end in partial chunks)
