@@ -12,6 +12,7 @@
 
 #include "../../oracle/velox_cpu.h"
 #include "../../velox-1_b200/host/GpuDevice.h"
+#include "../../velox-1_b200/host/PrestoPage.h"
 
 using namespace vb200;
 using namespace vb200::core;
@@ -311,6 +312,100 @@ static void cpuTests() {
     auto c = std::make_shared<ConstantVector>(makeFlatVector<double>(DOUBLE(), {2.5}), 7);
     auto dc = gpu::decode(c);
     EXPECT(dc.constant && !dc.constantNull && dc.size == 7);
+  }
+
+  section("PrestoPage: hand-computed bytes, round trip, checksum (PrestoSerializer.cpp:1070-1158,1947-2030)");
+  {
+    namespace pp = serializer::presto;
+    EXPECT(pp::crc32("123456789", 9) == 0xCBF43926u); // the CRC-32 check value
+    // one BIGINT column [1, NULL, 3]
+    auto k = makeFlatVector<int64_t>(BIGINT(), {1, 2, 3});
+    k->setNull(1, true);
+    const std::string page = pp::serializePage(makeRowVector({"k"}, {k}));
+    auto le32 = [](int32_t v) { return std::string(reinterpret_cast<const char*>(&v), 4); };
+    auto le64 = [](int64_t v) { return std::string(reinterpret_cast<const char*>(&v), 8); };
+    std::string want = le32(3) + std::string(1, '\0') + le32(40) + le32(40) + le64(0)      // numRows, codec, sizes, checksum
+                       + le32(1) + le32(10) + "LONG_ARRAY" + le32(3)                      // columns, encoding, positions
+                       + std::string(1, '\1') + std::string(1, '\x40')                    // has nulls; row 1 = bit 6
+                       + le64(1) + le64(3);                                               // the non-null values
+    EXPECT(page == want);
+    // VARCHAR ["ab", NULL, ""] and ROW(sum DOUBLE, count BIGINT) with a NULL row (avg's intermediate)
+    auto s3 = makeFlatVector<std::string>(VARCHAR(), {"ab", "zz", ""});
+    s3->setNull(1, true);
+    const std::string vpage = pp::serializePage(makeRowVector({"s"}, {s3}));
+    std::string vwant = le32(3) + std::string(1, '\0') + le32(46) + le32(46) + le64(0) + le32(1) + le32(14) + "VARIABLE_WIDTH" + le32(3)
+                        + le32(2) + le32(2) + le32(2) + std::string(1, '\1') + std::string(1, '\x40') + le32(2) + "ab";
+    EXPECT(vpage == vwant);
+    auto sum = makeFlatVector<double>(DOUBLE(), {1.5, 0.0, -2.25});
+    auto cnt = makeFlatVector<int64_t>(BIGINT(), {2, 0, 7});
+    auto rowType = ROW({"sum", "count"}, {DOUBLE(), BIGINT()});
+    auto avg = std::make_shared<RowVector>(rowType, 3, std::vector<VectorPtr>{sum, cnt});
+    avg->setNull(1, true);
+    const std::string rpage = pp::serializePage(makeRowVector({"a"}, {avg}));
+    double d0 = 1.5, d2 = -2.25;
+    int64_t b0, b2;
+    memcpy(&b0, &d0, 8); memcpy(&b2, &d2, 8);
+    std::string rdata = le32(1) + le32(3) + "ROW" + le32(2)
+                        + le32(10) + "LONG_ARRAY" + le32(2) + std::string(1, '\0') + le64(b0) + le64(b2)
+                        + le32(10) + "LONG_ARRAY" + le32(2) + std::string(1, '\0') + le64(2) + le64(7)
+                        + le32(3) + le32(0) + le32(1) + le32(1) + le32(2) + std::string(1, '\1') + std::string(1, '\x40');
+    EXPECT(rpage == le32(3) + std::string(1, '\0') + le32((int32_t)rdata.size()) + le32((int32_t)rdata.size()) + le64(0) + rdata);
+    // round trip of an aggregation-shaped result with every supported type, dictionary and constant wrappers, checksum on
+    Lcg r{4242};
+    const size_t n = 1000;
+    std::vector<int64_t> keys(n);
+    std::vector<std::string> names(n);
+    std::vector<double> sums(n);
+    std::vector<int32_t> dates(n), idx(n);
+    for (size_t i = 0; i < n; ++i) { keys[i] = r.range(-1000000, 1000000); names[i] = std::string((size_t)r.range(0, 20), (char)('a' + i % 26)); sums[i] = r.range(-5000, 5000) * 0.125; dates[i] = r.range(8000, 11000); idx[i] = r.range(0, 9); }
+    auto kv = makeFlatVector<int64_t>(BIGINT(), keys);
+    auto nv = std::make_shared<StringViewVector>(names);
+    auto sv = makeFlatVector<double>(DOUBLE(), sums);
+    auto dv = wrapInDictionary(idx, makeFlatVector<int32_t>(DATE(), std::vector<int32_t>(dates.begin(), dates.begin() + 10)));
+    auto bv = std::make_shared<BoolVector>(n);
+    auto cv = std::make_shared<ConstantVector>(makeFlatVector<float>(REAL(), {2.5f}), n);
+    auto tv = makeFlatVector<int8_t>(TINYINT(), std::vector<int8_t>(n, 7));
+    auto hv = makeFlatVector<int16_t>(SMALLINT(), std::vector<int16_t>(n, -3));
+    for (size_t i = 0; i < n; ++i) { bv->set(i, i % 3 == 0); if (i % 11 == 0) kv->setNull(i, true); if (i % 7 == 0) nv->setNull(i, true); if (i % 5 == 0) sv->setNull(i, true); if (i % 13 == 0) bv->setNull(i, true); }
+    auto avgN = std::make_shared<RowVector>(rowType, n, std::vector<VectorPtr>{makeFlatVector<double>(DOUBLE(), sums), makeFlatVector<int64_t>(BIGINT(), keys)});
+    for (size_t i = 0; i < n; i += 9) avgN->setNull(i, true);
+    auto whole = makeRowVector({"k", "name", "s", "d", "b", "c", "t", "h", "avg"}, {kv, nv, sv, dv, bv, cv, tv, hv, avgN});
+    const std::string big = pp::serializePage(whole, /*withChecksum=*/true);
+    auto back = pp::deserializePage(big, whole->rowType());
+    bool ok = back->size() == n;
+    for (size_t i = 0; i < n && ok; ++i) {
+      ok = ok && isNullAt(back->childAt(0), i) == (i % 11 == 0) && (i % 11 == 0 || at<int64_t>(back->childAt(0), i) == keys[i]);
+      ok = ok && isNullAt(back->childAt(1), i) == (i % 7 == 0) && (i % 7 == 0 || at<std::string>(back->childAt(1), i) == names[i]);
+      ok = ok && isNullAt(back->childAt(2), i) == (i % 5 == 0) && (i % 5 == 0 || at<double>(back->childAt(2), i) == sums[i]);
+      ok = ok && at<int32_t>(back->childAt(3), i) == dates[(size_t)idx[i]];
+      ok = ok && isNullAt(back->childAt(4), i) == (i % 13 == 0) && (i % 13 == 0 || static_cast<const BoolVector*>(back->childAt(4).get())->valueAt(i) == (i % 3 == 0));
+      ok = ok && at<float>(back->childAt(5), i) == 2.5f && at<int8_t>(back->childAt(6), i) == 7 && at<int16_t>(back->childAt(7), i) == -3;
+      auto row = std::dynamic_pointer_cast<RowVector>(back->childAt(8));
+      ok = ok && row && isNullAt(row, i) == (i % 9 == 0);
+      if (ok && i % 9 != 0) ok = at<double>(row->childAt(0), i) == sums[i] && at<int64_t>(row->childAt(1), i) == keys[i];
+    }
+    EXPECT(ok);
+    EXPECT(pp::serializePage(back, true) == big); // flat again: the same bytes
+    std::string bad = big;
+    bad[bad.size() / 2] ^= 0x10;
+    EXPECT_THROW(pp::deserializePage(bad, whole->rowType()), VeloxRuntimeError);
+    EXPECT_THROW(pp::deserializePage(big.substr(0, big.size() - 3), whole->rowType()), VeloxRuntimeError);
+    // PartitionedOutput: every row lands in exactly one page, on the partition the reference's hash names
+    auto pages = pp::partitionAndSerialize(whole, 0, 4);
+    size_t total = 0;
+    bool placed = true;
+    for (int p = 0; p < 4; ++p) {
+      if (pages[(size_t)p].empty()) continue;
+      auto part = pp::deserializePage(pages[(size_t)p], whole->rowType());
+      total += part->size();
+      for (size_t i = 0; i < part->size(); ++i) {
+        int32_t want = -1;
+        const bool isNull = isNullAt(part->childAt(0), i);
+        vgpu_partition_of(isNull ? 0 : at<int64_t>(part->childAt(0), i), isNull ? 1 : 0, 4, 1, &want);
+        placed = placed && want == p;
+      }
+    }
+    EXPECT(total == n && placed);
   }
 }
 
@@ -1011,6 +1106,25 @@ int main(int argc, char** argv) {
     if (mode == "cpu") cpuTests();
     else if (mode == "gpu") gpuTests();
     else if (mode == "bench") benchMode(argc, argv);
+    else if (mode == "presto" && argc > 2) { // the bytes of a fixed page, for the Python restatement to compare with (tests/test_presto_page_cpu.py)
+      auto k = makeFlatVector<int64_t>(BIGINT(), {5, -1, 1ll << 40, 0, 77});
+      k->setNull(3, true);
+      auto s5 = makeFlatVector<std::string>(VARCHAR(), {"AIR", "", "REG AIR", "x", "TRUCK"});
+      s5->setNull(3, true);
+      auto d5 = makeFlatVector<double>(DOUBLE(), {0.5, -0.0, 1e300, 3.25, 2.0});
+      auto c5 = makeFlatVector<int64_t>(BIGINT(), {1, 2, 3, 4, 5});
+      auto avg = std::make_shared<RowVector>(ROW({"sum", "count"}, {DOUBLE(), BIGINT()}), 5, std::vector<VectorPtr>{d5, c5});
+      avg->setNull(1, true);
+      auto i5 = makeFlatVector<int32_t>(INTEGER(), {1, 2, 3, 4, 5});
+      auto b5 = std::make_shared<BoolVector>(5);
+      b5->set(0, true); b5->set(4, true); b5->setNull(2, true);
+      const std::string page = serializer::presto::serializePage(makeRowVector({"k", "s", "avg", "i", "b"}, {k, s5, avg, i5, b5}), true);
+      FILE* f = fopen(argv[2], "wb");
+      if (!f || fwrite(page.data(), 1, page.size(), f) != page.size()) { printf("cannot write %s\n", argv[2]); return 2; }
+      fclose(f);
+      printf("presto: %zu bytes\n", page.size());
+      return 0;
+    }
     else { printf("usage: host_tests cpu|gpu|bench [rows]\n"); return 2; }
   } catch (const std::exception& e) {
     printf("  FAILED: uncaught exception: %s\n", e.what());
