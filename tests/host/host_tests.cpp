@@ -1017,10 +1017,38 @@ static void gpuTests() {
     std::map<int64_t, std::pair<double, int64_t>> want;
     for (size_t i = 0; i < t.orderkey.size(); ++i) { want[t.orderkey[i]].first += t.extendedprice[i]; ++want[t.orderkey[i]].second; }
     size_t groups = 0;
-    bool ok = partial != nullptr && partial->stats().flushes >= 2;
+    bool ok = partial != nullptr && partial->stats().flushes >= 2 && !partial->stats().abandonedPartialAggregation; // ~4 rows per group: it reduces
     for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
       auto it = want.find(at<int64_t>(o->childAt(0), g));
       ok = ok && it != want.end() && close(at<double>(o->childAt(1), g), it->second.first) && at<int64_t>(o->childAt(2), g) == it->second.second;
+    }
+    EXPECT(ok && groups == want.size());
+  }
+
+  section("partial aggregation that does not reduce its input is abandoned (HashAggregation.cpp:229-233,355-364)");
+  {
+    // every key occurs twice, 1000 rows apart in different batches... of 8192 rows: 2 rows per group inside a launch at best -> >= 80 % groups
+    const size_t n = 262144;
+    std::vector<int64_t> k(n), v(n);
+    std::map<int64_t, std::pair<int64_t, int64_t>> want;
+    Lcg r{808};
+    for (size_t i = 0; i < n; ++i) { k[i] = (int64_t)(i < n / 2 ? i : i - n / 2) * 7 + 1; v[i] = r.range(-50, 50); want[k[i]].first += v[i]; ++want[k[i]].second; }
+    std::vector<RowVectorPtr> in2;
+    for (size_t at0 = 0; at0 < n; at0 += 8192)
+      in2.push_back(makeRowVector({"k", "v"}, {makeFlatVector<int64_t>(BIGINT(), std::vector<int64_t>(k.begin() + at0, k.begin() + at0 + 8192)),
+                                              makeFlatVector<int64_t>(BIGINT(), std::vector<int64_t>(v.begin() + at0, v.begin() + at0 + 8192))}));
+    exec::QueryConfig cfg;
+    cfg.coalesceRows = 32768;
+    cfg.abandonPartialAggregationMinRows = 50000;
+    auto plan = PlanBuilder().values(in2).partialAggregation({"k"}, {"sum(v) as s", "count(*) as c"}).finalAggregation().planNode();
+    auto driver = exec::createDriver(plan, cfg);
+    auto* partial = dynamic_cast<gpu::GpuHashAggregation*>(driver->operators()[1].get());
+    auto out = driver->run();
+    size_t groups = 0;
+    bool ok = partial != nullptr && partial->stats().abandonedPartialAggregation && partial->stats().flushes >= 4 && partial->stats().outputRows > (int64_t)want.size();
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      auto it = want.find(at<int64_t>(o->childAt(0), g));
+      ok = ok && it != want.end() && at<int64_t>(o->childAt(1), g) == it->second.first && at<int64_t>(o->childAt(2), g) == it->second.second;
     }
     EXPECT(ok && groups == want.size());
   }

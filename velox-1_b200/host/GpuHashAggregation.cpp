@@ -13,7 +13,8 @@
 // After noMoreInput: vgpu_agg_extract, then output batches of preferredOutputBatchRows groups.
 // A partial aggregation flushes (HashAggregation.cpp:326-348): when the device state passes
 // maxPartialAggregationMemory its groups are emitted downstream and the state is reset.
-// Not restated: abandoning partial aggregation (:350-366), spilling, sorted / distinct aggregates.
+// A partial aggregation that does not reduce its input is abandoned (:229-233,355-364): its groups leave after every launch.
+// Not restated: spilling, sorted / distinct aggregates.
 #include <chrono>
 #include <cmath>
 #include <limits>
@@ -102,6 +103,7 @@ struct GpuHashAggregation::Impl {
   int64_t pendingRows = 0, pendingCap = 0;
   int64_t launchesSinceCheck = 0;
   int64_t rowsSinceFlush = 0;
+  int64_t nextAbandonCheck = 0, launchesAtLastFlush = 0;
   GpuHashAggregation::Stats stats;
   int rowWords() const { return 3 + 2 * (int)accs.size(); }
   // ids per key in the device's numbering: [lo, hi] plus one id for NULL unless NULL keys are dropped
@@ -717,9 +719,27 @@ void GpuHashAggregation::addInput(RowVectorPtr input) {
   // Partial aggregation flushes when its state passes max_partial_aggregation_memory (HashAggregation.cpp:326-348): the
   // groups so far go downstream as partial results (the final aggregation merges duplicates) and the state starts over.
   if (m.node->step() == Step::kPartial && !m.keys.empty() && m.agg) {
+    // Abandoning a partial aggregation that does not reduce its input (HashAggregation.cpp:229-233,253-258,355-364): once
+    // more than abandon_partial_aggregation_min_rows rows came in and the groups are at least
+    // abandon_partial_aggregation_min_pct % of them, the groups so far go downstream and from then on every device launch's
+    // groups follow at once — the device still folds what one launch holds, which a partial stage may always do.  The
+    // group count needs a finalize + read-back, so it is looked at when the row count passes the threshold and then
+    // each time it has doubled, not per batch.
+    auto& qc = m.ctx->queryConfig;
+    bool flushNow = false;
+    if (!m.stats.abandonedPartialAggregation && m.rowsSinceFlush > qc.abandonPartialAggregationMinRows && m.rowsSinceFlush >= m.nextAbandonCheck) {
+      m.flushPending();
+      m.checkErrors();
+      int64_t groups = 0;
+      check(vgpu_agg_num_groups(m.agg, m.stream, &groups), "vgpu_agg_num_groups");
+      if (100 * groups / m.rowsSinceFlush >= qc.abandonPartialAggregationMinPct) { m.stats.abandonedPartialAggregation = true; flushNow = true; }
+      else m.nextAbandonCheck = 2 * m.rowsSinceFlush;
+    } else if (m.stats.abandonedPartialAggregation && m.stats.deviceLaunches != m.launchesAtLastFlush) {
+      flushNow = true;
+    }
     int64_t bytes = 0;
     check(vgpu_agg_memory_bytes(m.agg, &bytes), "vgpu_agg_memory_bytes");
-    if (bytes > m.ctx->queryConfig.maxPartialAggregationMemory) {
+    if (flushNow || bytes > m.ctx->queryConfig.maxPartialAggregationMemory) {
       m.flushPending();
       m.checkErrors();
       m.rows = m.extractAll();
@@ -728,6 +748,8 @@ void GpuHashAggregation::addInput(RowVectorPtr input) {
       partialFull_ = m.nGroups > 0;
       if (!partialFull_) { check(vgpu_agg_reset(m.agg, m.stream), "vgpu_agg_reset"); m.nGroups = -1; }
       ++m.stats.flushes;
+      m.launchesAtLastFlush = m.stats.deviceLaunches;
+      if (!m.stats.abandonedPartialAggregation) { m.rowsSinceFlush = 0; m.nextAbandonCheck = 0; } // HashAggregation::resetPartialOutputIfNeed
     }
   }
 }

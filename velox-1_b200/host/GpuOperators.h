@@ -74,6 +74,7 @@ class GpuHashAggregation : public exec::Operator {
     int64_t deviceLaunches = 0;      // vgpu_agg_add_input calls (coalesced host batches per launch = inputVectors / deviceLaunches)
     int64_t h2dBytes = 0, stagedBytes = 0; // bytes copied to HBM; of those, bytes that went through the pinned staging ring
     int64_t flushes = 0;             // partial-aggregation flushes (HashAggregation.cpp:326-348)
+    bool abandonedPartialAggregation = false; // the partial aggregation did not reduce its input (HashAggregation.cpp:229-233,355-364): groups leave after every device launch
     int64_t regrows = 0;             // table rebuilt because a VARCHAR key left the laid-out range (array -> wider array / hash)
     double addInputWallMs = 0, getOutputWallMs = 0;
   };

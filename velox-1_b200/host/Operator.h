@@ -24,6 +24,8 @@ struct QueryConfig {
   bool stringViewKeys = true;              // gpu.string_view_keys: VARCHAR keys that arrive as StringViews are mapped to numbers on the device
   int64_t coalesceRows = 1 << 20;          // gpu.coalesce_rows: host batches are gathered on the device until this many rows before a kernel runs
   int32_t errorCheckEvery = 16;            // gpu.error_check_every: device launches between two data-error checks (plus one at noMoreInput)
+  int32_t abandonPartialAggregationMinRows = 100000; // abandon_partial_aggregation_min_rows (velox/core/QueryConfig.h)
+  int32_t abandonPartialAggregationMinPct = 80;      // abandon_partial_aggregation_min_pct
   int64_t maxPartialAggregationMemory = 1ll << 34; // max_partial_aggregation_memory (device bytes of logged partial groups before a flush)
 };
 
