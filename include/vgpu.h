@@ -546,6 +546,9 @@ int vgpu_debug_exchange_local(vgpu_agg_t* partials, vgpu_agg_t* finals, int32_t 
  * vgpu_comm_exchange_groups(comm, partial, final) only exchanges the counts and deduplicates.  Needs a mapped window
  * (vgpu_comm_reserve_window) and at most 8 ranks; where that does not hold, or for batches whose shape the streaming
  * kernel does not cover, the entries are logged locally and partitioned by vgpu_comm_exchange_groups as before.
+ * Entries that may continue in another warp's rows or another batch (two per warp and batch at most) are stored one by
+ * one into a reserve of 256 entries per sending CTA and destination; an aggregation fed by hundreds of small batches
+ * before one exchange can exhaust it (reported by vgpu_agg_check_errors as a full window region) and should not attach.
  * No other exchange may run through `comm` between the partial aggregation's first batch and its exchange.
  * comm == NULL detaches.  The attachment survives vgpu_agg_reset. */
 int vgpu_agg_attach_exchange(vgpu_agg_t partial_agg, vgpu_comm_t comm);
