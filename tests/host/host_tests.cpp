@@ -1053,6 +1053,74 @@ static void gpuTests() {
     EXPECT(ok && groups == want.size());
   }
 
+  section("min / max over VARCHAR through order-preserving ids (MinMaxAggregates.cpp:282-534), partial -> final, id space renumbered");
+  {
+    // batch 0 brings "a" and "zzzz"; later batches bring 120 strings in DESCENDING order, each landing in the ever
+    // smaller gap right after "a": the id space is used up and spread out again while accumulators hold ids
+    std::vector<std::string> pool = {"a", "zzzz"};
+    for (int i = 0; i < 120; ++i) { char buf[32]; snprintf(buf, sizeof buf, "m%03d long enough to leave the inline form", 500 - i); pool.push_back(buf); }
+    pool.push_back("");
+    Lcg r{31337};
+    std::vector<RowVectorPtr> in3;
+    struct W { bool any = false; std::string mn, mx; int64_t n = 0; };
+    std::map<int32_t, W> want;
+    size_t next = 2;
+    for (int b = 0; b < 16; ++b) {
+      const size_t n = 3000;
+      const size_t avail = b == 0 ? 2 : std::min(pool.size(), next + 9);
+      next = avail;
+      std::vector<int32_t> k(n), ix(n);
+      std::vector<std::string> names(n);
+      for (size_t i = 0; i < n; ++i) {
+        k[i] = r.range(0, 6);
+        const size_t pick = b == 0 ? (size_t)r.range(0, 1) : (size_t)r.range((int)(avail >= 12 ? avail - 12 : 0), (int)avail - 1);
+        names[i] = pool[pick];
+        ix[i] = (int32_t)pick;
+      }
+      VectorPtr nameVec;
+      if (b % 2 == 0) nameVec = makeFlatVector<std::string>(VARCHAR(), names);
+      else nameVec = wrapInDictionary(ix, std::make_shared<StringViewVector>(pool));
+      for (size_t i = 0; i < n; ++i) {
+        const bool isNull = i % 17 == 3;
+        if (isNull) nameVec->setNull(i, true);
+        auto& w = want[k[i]];
+        ++w.n;
+        if (isNull) continue;
+        if (!w.any) { w.any = true; w.mn = w.mx = names[i]; }
+        else { w.mn = std::min(w.mn, names[i]); w.mx = std::max(w.mx, names[i]); }
+      }
+      in3.push_back(makeRowVector({"k", "name"}, {makeFlatVector<int32_t>(INTEGER(), k), nameVec}));
+    }
+    for (int variant = 0; variant < 2; ++variant) {
+      auto builder = PlanBuilder().values(in3);
+      auto plan = variant == 0 ? builder.singleAggregation({"k"}, {"min(name) as lo", "max(name) as hi", "count(*) as c"}).planNode()
+                               : builder.partialAggregation({"k"}, {"min(name) as lo", "max(name) as hi", "count(*) as c"}).finalAggregation().planNode();
+      auto driver = exec::createDriver(plan);
+      auto out = driver->run();
+      size_t groups = 0;
+      bool ok = true;
+      for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+        auto it = want.find(at<int32_t>(o->childAt(0), g));
+        ok = ok && it != want.end() && at<int64_t>(o->childAt(3), g) == it->second.n && it->second.any && !isNullAt(o->childAt(1), g) &&
+             at<std::string>(o->childAt(1), g) == it->second.mn && at<std::string>(o->childAt(2), g) == it->second.mx;
+      }
+      EXPECT(ok && groups == want.size());
+      auto* first = dynamic_cast<gpu::GpuHashAggregation*>(driver->operators()[1].get());
+      EXPECT(first != nullptr && first->stats().regrows >= 1); // the ids were spread out again at least once
+    }
+    // a group whose strings are all NULL: NULL result
+    auto kk = makeFlatVector<int32_t>(INTEGER(), {1, 1, 2});
+    auto ss = makeFlatVector<std::string>(VARCHAR(), {"x", "y", "z"});
+    ss->setNull(2, true);
+    auto out = exec::runPlan(PlanBuilder().values({makeRowVector({"k", "s"}, {kk, ss})}).singleAggregation({"k"}, {"min(s)", "max(s)"}).planNode());
+    bool ok = out.size() == 1 && out[0]->size() == 2;
+    for (size_t g = 0; ok && g < 2; ++g) {
+      if (at<int32_t>(out[0]->childAt(0), g) == 1) ok = at<std::string>(out[0]->childAt(1), g) == "x" && at<std::string>(out[0]->childAt(2), g) == "y";
+      else ok = isNullAt(out[0]->childAt(1), g) && isNullAt(out[0]->childAt(2), g);
+    }
+    EXPECT(ok);
+  }
+
   section("edge cases: empty input, all-null input, integer overflow (SumTest.cpp:509-538,610-620)");
   {
     auto none = exec::runPlan(PlanBuilder().values(in).filter("l_quantity > 1.0").singleAggregation({"l_orderkey"}, {"sum(l_quantity)"}).planNode());

@@ -60,6 +60,16 @@ struct AggInfo {
   std::string fn;
   TypePtr rawType, outType;
   int acc0 = -1, acc1 = -1;
+  std::string ordColumn; // min / max over VARCHAR: the accumulator holds order-preserving ids of this input column's strings
+};
+// min / max over VARCHAR (MinMaxAggregates.cpp:282-534 compare StringViews): every distinct string of the column gets a
+// 64-bit id whose order is the strings' byte order, the device runs its integer MIN / MAX over the ids, the output maps
+// ids back.  A new string takes the midpoint between its neighbours' ids (2^32 past the ends); when a gap is used up all
+// ids are spread out again and the accumulators already on the device are rewritten (remapOrd).
+struct OrdDict {
+  std::map<std::string, int64_t> idOf;
+  std::unordered_map<int64_t, std::string> strOf;
+  static constexpr int64_t kStep = 1ll << 32;
 };
 TypedExprPtr castTo(const TypedExprPtr& e, const TypePtr& t) { return e->type()->equals(*t) ? e : std::make_shared<CastTypedExpr>(t, e); }
 int64_t typeLo(TypeKind k) { return k == TypeKind::TINYINT ? -128 : k == TypeKind::SMALLINT ? -32768 : -2147483648ll; }
@@ -104,6 +114,7 @@ struct GpuHashAggregation::Impl {
   int64_t launchesSinceCheck = 0;
   int64_t rowsSinceFlush = 0;
   int64_t nextAbandonCheck = 0, launchesAtLastFlush = 0;
+  std::map<std::string, OrdDict> ordDicts; // VARCHAR inputs of min / max, by input column name
   GpuHashAggregation::Stats stats;
   int rowWords() const { return 3 + 2 * (int)accs.size(); }
   // ids per key in the device's numbering: [lo, hi] plus one id for NULL unless NULL keys are dropped
@@ -189,7 +200,15 @@ struct GpuHashAggregation::Impl {
         VB_USER_CHECK(x->type()->kind() == TypeKind::BOOLEAN, a.function + " takes one BOOLEAN argument");
         info.acc0 = addAcc(a.function == "bool_and" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(x));
       } else if (a.function == "min" || a.function == "max") {
-        VB_USER_CHECK(x->type()->kind() != TypeKind::VARCHAR && x->type()->kind() != TypeKind::BOOLEAN, a.function + " over " + x->type()->toString() + " is not supported on the GPU");
+        VB_USER_CHECK(x->type()->kind() != TypeKind::BOOLEAN, a.function + " over " + x->type()->toString() + " is not supported on the GPU");
+        if (x->type()->kind() == TypeKind::VARCHAR) {
+          VB_USER_CHECK(x->kind() == ITypedExpr::Kind::kFieldAccess && !a.mask, a.function + " over VARCHAR takes a plain, unmasked column on the GPU");
+          info.ordColumn = static_cast<const FieldAccessTypedExpr*>(x.get())->name();
+          for (size_t k = 0; k < keys.size(); ++k)
+            VB_USER_CHECK(!keys[k].varchar || keyColumn(k) != info.ordColumn, a.function + " over a VARCHAR grouping key is not supported on the GPU");
+          ordDicts[info.ordColumn];
+          info.acc0 = addAcc(a.function == "min" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(std::make_shared<FieldAccessTypedExpr>(BIGINT(), info.ordColumn)));
+        } else
         info.acc0 = addAcc(a.function == "min" ? VGPU_ACC_MIN : VGPU_ACC_MAX, addOutput(x->type()->kind() == TypeKind::REAL ? castTo(x, DOUBLE()) : x));
       } else {
         throw VeloxUserError("Aggregate function not registered: " + a.function);
@@ -327,6 +346,7 @@ struct GpuHashAggregation::Impl {
   std::string keyColumn(size_t i) const { return static_cast<const FieldAccessTypedExpr*>(outputs[i].get())->name(); }
   // device type an input column is bound as by the coalescing path
   int columnDeviceType(const std::string& name) const {
+    if (ordDicts.count(name)) return VGPU_BIGINT;
     for (size_t i = 0; i < keys.size(); ++i) if (keys[i].number && keyColumn(i) == name) return VGPU_VARCHAR;
     return deviceType(inputColumnType(name));
   }
@@ -354,6 +374,70 @@ struct GpuHashAggregation::Impl {
     check(rc, "vgpu_agg_extract");
     out.resize((size_t)got * rowWords());
     return out;
+  }
+
+  // ---- order-preserving ids for min / max over VARCHAR -----------------------------------------------------------
+  // Id of `s`, inserting it if new.  Returns false when the gap between its neighbours is used up (nothing inserted).
+  static bool ordInsert(OrdDict& d, const std::string& s) {
+    auto it = d.idOf.lower_bound(s);
+    if (it != d.idOf.end() && it->first == s) return true;
+    int64_t id = 0;
+    if (d.idOf.empty()) id = 0;
+    else if (it == d.idOf.begin()) id = it->second - OrdDict::kStep;
+    else if (it == d.idOf.end()) id = std::prev(it)->second + OrdDict::kStep;
+    else {
+      const int64_t lo = std::prev(it)->second, hi = it->second;
+      if (hi - lo < 2) return false;
+      id = lo + (hi - lo) / 2;
+    }
+    d.idOf.emplace_hint(it, s, id);
+    d.strOf[id] = s;
+    return true;
+  }
+  // Spreads the ids out again (kStep apart, centred on 0) and rewrites the accumulators that hold ids of `column`.
+  void ordRenumber(const std::string& column) {
+    OrdDict& d = ordDicts[column];
+    std::unordered_map<int64_t, int64_t> moved;
+    int64_t id = -(int64_t)(d.idOf.size() / 2) * OrdDict::kStep;
+    d.strOf.clear();
+    for (auto& kv : d.idOf) { moved[kv.second] = id; kv.second = id; d.strOf[id] = kv.first; id += OrdDict::kStep; }
+    ++stats.regrows;
+    if (!agg || !sawInput) return;
+    flushPending();
+    checkErrors();
+    std::vector<int64_t> rowsNow = extractAll();
+    const int rw = rowWords(), na = (int)accs.size();
+    const int64_t n = (int64_t)(rowsNow.size() / rw);
+    for (auto& a : aggs) {
+      if (a.ordColumn != column) continue;
+      for (int64_t g = 0; g < n; ++g) {
+        if (rowsNow[(size_t)g * rw + 3 + na + a.acc0] == 0) continue; // NULL so far
+        auto it = moved.find(rowsNow[(size_t)g * rw + 3 + a.acc0]);
+        VB_CHECK(it != moved.end(), "min / max accumulator holds an id that is not in the column's dictionary");
+        rowsNow[(size_t)g * rw + 3 + a.acc0] = it->second;
+      }
+    }
+    check(vgpu_agg_reset(agg, stream), "vgpu_agg_reset");
+    if (n > 0) {
+      DeviceBatch b; b.stream = stream;
+      void* dRows = b.upload(rowsNow.data(), rowsNow.size() * 8);
+      check(vgpu_agg_merge_rows(agg, dRows, n, stream), "vgpu_agg_merge_rows");
+      check(vgpu_stream_sync(stream), "vgpu_stream_sync");
+    }
+  }
+  // Ids of the batch's BASE strings of `column` (a flat BIGINT vector of the base's length; NULL bases get 0).
+  std::shared_ptr<FlatVector<int64_t>> ordIdsOf(const std::string& column, const VectorPtr& v) {
+    OrdDict& d = ordDicts[column];
+    const BaseVector* base = flatBaseOf(v.get());
+    const uint64_t* nn = base->mayHaveNulls() ? base->nulls().data() : nullptr;
+    for (size_t i = 0; i < base->size(); ++i) {
+      if (nn && !bits::isBitSet(nn, i)) continue;
+      const std::string s = stringValueAt(base, i);
+      if (!ordInsert(d, s)) { ordRenumber(column); VB_CHECK(ordInsert(d, s), "order-preserving id space exhausted"); }
+    }
+    auto ids = std::make_shared<FlatVector<int64_t>>(BIGINT(), base->size());
+    for (size_t i = 0; i < base->size(); ++i) ids->set(i, nn && !bits::isBitSet(nn, i) ? 0 : d.idOf.find(stringValueAt(base, i))->second);
+    return ids;
   }
 
   // VARCHAR key column -> ids of its base strings (new strings get the next id)
@@ -637,6 +721,7 @@ struct GpuHashAggregation::Impl {
       flushPending(); // rows gathered so far carry keys of the old layout
       regrow();
     }
+    if (!ordDicts.empty()) direct = true; // their ids are made per batch: no gathering of small batches
     std::vector<VectorPtr> keepAlive;
     std::vector<VectorPtr> vecs(lowered.columns.size());
     std::vector<int> varcharKeyOf(lowered.columns.size(), -1);
@@ -645,6 +730,8 @@ struct GpuHashAggregation::Impl {
       for (size_t i = 0; i < keys.size(); ++i) if (keys[i].varchar && keyColumn(i) == name) varcharKeyOf[c] = (int)i;
       vecs[c] = varcharKeyOf[c] >= 0 ? keyVecs[varcharKeyOf[c]] : columnByName(in, name, keepAlive);
     }
+    std::vector<std::shared_ptr<FlatVector<int64_t>>> ordIds(lowered.columns.size());
+    for (size_t c = 0; c < lowered.columns.size(); ++c) if (ordDicts.count(lowered.columns[c])) ordIds[c] = ordIdsOf(lowered.columns[c], vecs[c]);
     if (keepAlive.empty() && !direct && canCoalesce(in, vecs)) {
       appendPending(in, vecs, varcharKeyOf, keyIds);
     } else {
@@ -663,6 +750,7 @@ struct GpuHashAggregation::Impl {
           else bindColumn(batch, vecs[c], nullptr, keyNumbers[(size_t)ki].numbers.get());
         }
         else if (ki >= 0) bindColumn(batch, vecs[c], &keyIds[(size_t)ki]);
+        else if (ordDicts.count(lowered.columns[c])) bindColumn(batch, vecs[c], nullptr, ordIds[c].get());
         else bindColumn(batch, vecs[c]);
       }
       launch(batch, (int64_t)in->size());
@@ -838,6 +926,19 @@ RowVectorPtr GpuHashAggregation::getOutput() {
       const auto outKind = a.outType->kind();
       const bool accIsDouble = kind == VGPU_ACC_SUM_F64 || ((kind == VGPU_ACC_MIN || kind == VGPU_ACC_MAX) && m.outputs[m.accs[a.acc0].input]->type()->isFloating());
       switch (outKind) {
+        case TypeKind::VARCHAR: { // min / max over VARCHAR: ids back to strings
+          VB_CHECK(!a.ordColumn.empty(), "VARCHAR aggregate result without a dictionary");
+          const OrdDict& dict = m.ordDicts.at(a.ordColumn);
+          auto f = flatOf<std::string>(a.outType, (size_t)n);
+          for (int64_t g = 0; g < n; ++g) {
+            if (nonNull(g, a.acc0) == 0) continue;
+            auto it = dict.strOf.find(value(g, a.acc0));
+            VB_CHECK(it != dict.strOf.end(), "min / max result is not an id of the column's dictionary");
+            f->set(g, it->second);
+          }
+          v = f;
+          break;
+        }
         case TypeKind::BOOLEAN: { auto f = std::make_shared<BoolVector>((size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, value(g, a.acc0) != 0); v = f; break; }
         case TypeKind::DOUBLE: { auto f = flatOf<double>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, asDouble(value(g, a.acc0))); v = f; break; }
         case TypeKind::REAL: { auto f = flatOf<float>(a.outType, (size_t)n); for (int64_t g = 0; g < n; ++g) f->set(g, (float)asDouble(value(g, a.acc0))); v = f; break; }
