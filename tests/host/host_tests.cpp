@@ -1053,6 +1053,56 @@ static void gpuTests() {
     EXPECT(ok && groups == want.size());
   }
 
+  section("two BIGINT grouping keys: normalized key over the ranges seen so far, table rebuilt when a range grows (VectorHasher.cpp:526-577, HashTable.cpp:1376-1461)");
+  {
+    Lcg r{2024};
+    std::vector<RowVectorPtr> in4;
+    std::map<std::pair<int64_t, int64_t>, std::pair<int64_t, int64_t>> want; // (a, b or INT64_MIN for NULL) -> (count, sum)
+    for (int b = 0; b < 6; ++b) {
+      const size_t n = 20000;
+      // a: order-key like, the range moves up with every batch; b: small at first, then jumps far out (negative too)
+      std::vector<int64_t> ka(n), kb(n), v(n);
+      for (size_t i = 0; i < n; ++i) {
+        ka[i] = 6000000000ll + (int64_t)b * 40000 + r.range(0, 29999);
+        kb[i] = b < 3 ? r.range(0, 9) : (int64_t)r.range(-3, 3) * 1000000007ll;
+        v[i] = r.range(-9, 9);
+      }
+      auto bv = makeFlatVector<int64_t>(BIGINT(), kb);
+      for (size_t i = 0; i < n; i += 23) bv->setNull(i, true);
+      for (size_t i = 0; i < n; ++i) { auto& w = want[{ka[i], i % 23 == 0 ? INT64_MIN : kb[i]}]; ++w.first; w.second += v[i]; }
+      in4.push_back(makeRowVector({"a", "b", "v"}, {makeFlatVector<int64_t>(BIGINT(), ka), bv, makeFlatVector<int64_t>(BIGINT(), v)}));
+    }
+    exec::QueryConfig cfg;
+    cfg.coalesceRows = 32768;
+    auto plan = PlanBuilder().values(in4).partialAggregation({"a", "b"}, {"count(*) as c", "sum(v) as s"}).finalAggregation().planNode();
+    auto driver = exec::createDriver(plan, cfg);
+    auto out = driver->run();
+    size_t groups = 0;
+    bool ok = true;
+    for (auto& o : out) for (size_t g = 0; g < o->size(); ++g, ++groups) {
+      auto it = want.find({at<int64_t>(o->childAt(0), g), isNullAt(o->childAt(1), g) ? INT64_MIN : at<int64_t>(o->childAt(1), g)});
+      ok = ok && it != want.end() && at<int64_t>(o->childAt(2), g) == it->second.first && at<int64_t>(o->childAt(3), g) == it->second.second;
+    }
+    EXPECT(ok && groups == want.size());
+    auto* partial = dynamic_cast<gpu::GpuHashAggregation*>(driver->operators()[1].get());
+    EXPECT(partial != nullptr && partial->stats().regrows >= 1);
+    // two INTEGER keys over their whole type range would need 66 bits; their seen ranges need far fewer
+    std::vector<int32_t> x = {INT32_MIN + 5, 7, INT32_MIN + 5, 7, 0}, y = {1, 1000000, 1, 1000000, 1};
+    auto ints = exec::runPlan(PlanBuilder().values({makeRowVector({"x", "y"}, {makeFlatVector<int32_t>(INTEGER(), x), makeFlatVector<int32_t>(INTEGER(), y)})})
+                                  .singleAggregation({"x", "y"}, {"count(*)"}).planNode());
+    size_t ig = 0;
+    bool iok = true;
+    for (auto& o : ints) for (size_t g = 0; g < o->size(); ++g, ++ig) {
+      const int32_t gx = at<int32_t>(o->childAt(0), g), gy = at<int32_t>(o->childAt(1), g);
+      iok = iok && at<int64_t>(o->childAt(2), g) == ((gx == 0) ? 1 : 2) && ((gx == INT32_MIN + 5 && gy == 1) || (gx == 7 && gy == 1000000) || (gx == 0 && gy == 1));
+    }
+    EXPECT(iok && ig == 3);
+    // ranges that do not fit 63 bits together: refused, not mis-grouped
+    std::vector<int64_t> wa = {INT64_MIN + 1, INT64_MAX - 1}, wb = {INT64_MIN + 1, INT64_MAX - 1};
+    EXPECT_THROW(exec::runPlan(PlanBuilder().values({makeRowVector({"a", "b"}, {makeFlatVector<int64_t>(BIGINT(), wa), makeFlatVector<int64_t>(BIGINT(), wb)})})
+                                   .singleAggregation({"a", "b"}, {"count(*)"}).planNode()), VeloxRuntimeError);
+  }
+
   section("min / max over VARCHAR through order-preserving ids (MinMaxAggregates.cpp:282-534), partial -> final, id space renumbered");
   {
     // batch 0 brings "a" and "zzzz"; later batches bring 120 strings in DESCENDING order, each landing in the ever

@@ -42,7 +42,19 @@ struct KeyInfo {
   int64_t seenLo = std::numeric_limits<int64_t>::max(), seenHi = std::numeric_limits<int64_t>::min();
   std::vector<std::string> longStrings;
   std::unordered_map<std::string, int64_t> longId;
+  // INTEGER / BIGINT key next to other keys: packed as `value - lo + 1` over the range seen so far (VectorHasher's range
+  // mode feeding HashTable's kNormalizedKey, velox/exec/VectorHasher.cpp:526-577, HashTable.cpp:1376-1461): the host
+  // keeps min / max of the key column per batch (seenLo / seenHi) and the table is rebuilt when a value leaves [lo, hi]
+  bool ranged = false;
+  std::string rangedColumn;
 };
+// [lo, hi] widened by its own width on both sides, saturating (so that a slowly growing range does not rebuild every batch)
+void padRange(int64_t lo, int64_t hi, int64_t& outLo, int64_t& outHi) {
+  const __int128 span = (__int128)hi - lo + 1;
+  const __int128 l = (__int128)lo - span, h = (__int128)hi + span;
+  outLo = l < (__int128)std::numeric_limits<int64_t>::min() ? std::numeric_limits<int64_t>::min() : (int64_t)l;
+  outHi = h > (__int128)std::numeric_limits<int64_t>::max() ? std::numeric_limits<int64_t>::max() : (int64_t)h;
+}
 constexpr int64_t kLongBase = 1ll << 60;
 // What one batch's VARCHAR number key looks like: its views can travel as they are, or numbers per BASE value.
 struct NumberBatch {
@@ -119,7 +131,10 @@ struct GpuHashAggregation::Impl {
   int rowWords() const { return 3 + 2 * (int)accs.size(); }
   // ids per key in the device's numbering: [lo, hi] plus one id for NULL unless NULL keys are dropped
   int64_t nullIds() const { return node->ignoreNullKeys() ? 0 : 1; }
-  int64_t cardOf(const KeyInfo& k) const { return k.hi - k.lo + 1 + nullIds(); }
+  int64_t cardOf(const KeyInfo& k) const { // saturating: a ranged BIGINT key may span most of int64
+    const __int128 c = (__int128)k.hi - k.lo + 1 + nullIds();
+    return c > (__int128)std::numeric_limits<int64_t>::max() ? std::numeric_limits<int64_t>::max() : (int64_t)c;
+  }
 
   // expression a name refers to on the operator's input (through the fused projections, if any)
   TypedExprPtr exprOf(const std::string& name) const {
@@ -229,6 +244,10 @@ struct GpuHashAggregation::Impl {
         else { const int64_t span = hi - lo + 1; k.lo = std::max<int64_t>(0, lo - span); k.hi = hi + span; }
       }
       else if (k.varchar) { k.lo = 0; k.hi = std::max<int64_t>(7, 2 * (int64_t)k.strings.size() - 1); }
+      else if (k.ranged) {
+        if (k.seenLo <= k.seenHi) padRange(k.seenLo, k.seenHi, k.lo, k.hi); else { k.lo = 0; k.hi = 0; }
+        if (cardOf(k) > 4096) small = false;
+      }
       else if (k.type->kind() == TypeKind::TINYINT) { k.lo = -128; k.hi = 127; }
       else small = false;
       if (small) { product *= cardOf(k); if (product > 4096) small = false; }
@@ -247,6 +266,7 @@ struct GpuHashAggregation::Impl {
             k.bits = bitsFor(cardOf(k));
           }
           else if (k.varchar) { k.lo = 0; k.hi = (1 << 20) - 2; k.bits = 20; }
+          else if (k.ranged) k.bits = cardOf(k) < (1ll << 62) ? bitsFor(cardOf(k)) : 64; // (too wide with its padding: retried without, below)
           else {
             VB_CHECK(k.type->kind() != TypeKind::BIGINT && k.type->isInteger(), "multi-key grouping on " + k.type->toString() + " needs key statistics (not supported yet)");
             k.lo = typeLo(k.type->kind()); k.hi = typeHi(k.type->kind());
@@ -254,7 +274,18 @@ struct GpuHashAggregation::Impl {
           }
           total += k.bits;
         }
-        VB_CHECK(total <= 63, "grouping keys do not fit the 63 bits of a normalized key (the device rejects wider packings)");
+        if (total > 63) { // give up the padding of the ranged keys before giving up
+          total = 0;
+          for (auto& k : keys) {
+            if (k.ranged && k.seenLo <= k.seenHi) {
+              k.lo = k.seenLo; k.hi = k.seenHi;
+              VB_CHECK(cardOf(k) < (1ll << 62), "the range of grouping key " + k.name + " does not fit a normalized key (multi-word keys are not supported)");
+              k.bits = bitsFor(cardOf(k));
+            }
+            total += k.bits;
+          }
+        }
+        VB_CHECK(total <= 63, "grouping keys do not fit the 63 bits of a normalized key (multi-word keys are not supported)");
       }
     }
     // a number key is read through a BIGINT operand: the column's StringViews (or host-made numbers) are bound under it
@@ -438,6 +469,23 @@ struct GpuHashAggregation::Impl {
     auto ids = std::make_shared<FlatVector<int64_t>>(BIGINT(), base->size());
     for (size_t i = 0; i < base->size(); ++i) ids->set(i, nn && !bits::isBitSet(nn, i) ? 0 : d.idOf.find(stringValueAt(base, i))->second);
     return ids;
+  }
+
+  // min / max of an INTEGER / BIGINT key column's (base) values into the key's seen range
+  static void scanRange(KeyInfo& k, const VectorPtr& v) {
+    const BaseVector* base = flatBaseOf(v.get());
+    const uint64_t* nn = base->mayHaveNulls() ? base->nulls().data() : nullptr;
+    int64_t lo = k.seenLo, hi = k.seenHi;
+    auto scan = [&](auto* raw) {
+      for (size_t i = 0; i < base->size(); ++i) {
+        if (nn && !bits::isBitSet(nn, i)) continue;
+        const int64_t x = (int64_t)raw[i];
+        lo = std::min(lo, x); hi = std::max(hi, x);
+      }
+    };
+    if (base->type()->kind() == TypeKind::BIGINT) scan(static_cast<const FlatVector<int64_t>*>(base)->rawValues());
+    else scan(static_cast<const FlatVector<int32_t>*>(base)->rawValues());
+    k.seenLo = lo; k.seenHi = hi;
   }
 
   // VARCHAR key column -> ids of its base strings (new strings get the next id)
@@ -694,6 +742,11 @@ struct GpuHashAggregation::Impl {
     bool grew = false, direct = false;
     for (size_t i = 0; i < keys.size(); ++i) {
       auto& k = keys[i];
+      if (k.ranged) {
+        scanRange(k, in->childAt(inputType->getChildIdx(k.rangedColumn)));
+        if (agg && k.seenLo <= k.seenHi && (k.seenLo < k.lo || k.seenHi > k.hi)) grew = true;
+        continue;
+      }
       if (!k.varchar) continue;
       keyVecs[i] = in->childAt(inputType->getChildIdx(keyColumn(i)));
       if (!agg && !sawInput && ctx->queryConfig.stringViewKeys) {
@@ -783,6 +836,17 @@ GpuHashAggregation::GpuHashAggregation(exec::DriverCtx* ctx, int32_t id, std::sh
     VB_USER_CHECK(k.varchar || k.type->isInteger(), "grouping on " + k.type->toString() + " is not supported on the GPU");
     m.keys.push_back(std::move(k));
     m.outputs.push_back(e);
+  }
+  if (m.keys.size() > 1) {
+    for (size_t i = 0; i < m.keys.size(); ++i) {
+      auto& k = m.keys[i];
+      const auto kind = k.type->kind();
+      if (k.varchar || (kind != TypeKind::INTEGER && kind != TypeKind::BIGINT) || m.outputs[i]->kind() != ITypedExpr::Kind::kFieldAccess) continue;
+      const std::string column = static_cast<const FieldAccessTypedExpr*>(m.outputs[i].get())->name();
+      if (m.inputType->getChildIdxIfExists(column) < 0) continue;
+      k.ranged = true;
+      k.rangedColumn = column;
+    }
   }
   m.planAccumulators();
 }
